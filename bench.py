@@ -1,0 +1,331 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the FDT grounding + ClipInfoCELoss hot path (BASELINE.json).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode bf16|fp32]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one forward+backward of the whole path over one synthetic batch: for both modalities
+q.codebook^T -> token max-pool -> sparsemax -> weighted pooling, then L2-normalise -> all-gather ->
+global logits -> bidirectional InfoNCE, and the backward of all of it (gradients for q_img, q_txt, the
+codebook and logit_scale). Workload: ViT-B/32 shapes (P=49, T=77, D=512), codebook 16384 x 512, GLOBAL
+batch 32768 (BASELINE.json metric), split evenly over the N ranks ("strong" scaling: total work fixed).
+Prints ONE JSON line on rank 0 (contract in the task statement). `--impl reference` times the CPU
+restatement of the reference's path (oracle/fdt_oracle.py; the reference is pure PyTorch and cannot
+travel to the GPU box) on the host cores.
+"""
+import argparse
+import json
+import math
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "iterated-learning-for-vlm_b200"))
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+P_TOK, T_TOK, D_DIM, K_CODES = 49, 77, 512, 16384
+TEMPERATURE = 1000.0
+METRIC = "loss+grounding fwd/bwd pairs/sec"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--global-batch", type=int, default=32768)
+    ap.add_argument("--codes", type=int, default=K_CODES)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample", type=int, default=64, help="rows of the workload timed on the host cores")
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return dict(tflops=float(d.get("bf16_tflops_sustained", d.get("bf16_tflops"))), hbm=float(d["hbm_gbs"]),
+                    src="measured (MEASURED_PEAKS.json, sustained bf16)")
+    return dict(tflops=1590.0, hbm=6650.0, src="fallback (B200_PROFILING.md)")
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference path, on the host cores
+# ---------------------------------------------------------------------------------------------------
+def cpu_reference_run(sample_rows, steps, warmup, codes):
+    from oracle import fdt_oracle as O
+    cores = len(os.sched_getaffinity(0))
+    torch.set_num_threads(cores)
+    inp = O.synth_inputs(sample_rows, P_TOK, T_TOK, codes, D_DIM, seed=0)
+    times = []
+    for i in range(warmup + steps):
+        ranks = [dict(q_img=O.make_leaf(inp["q_img"]), q_txt=O.make_leaf(inp["q_txt"]), mask=inp["mask"],
+                      sd=O.make_leaf(inp["sd"]), p=O.make_leaf(inp["p"]))]
+        t0 = time.perf_counter()
+        O.step(ranks, temperature=TEMPERATURE)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    t = sum(times) / len(times)
+    return dict(value=sample_rows / t, unit="pairs/s", cores=cores, kind="port",
+                sample="%d rows of the workload (P=%d,T=%d,K=%d,D=%d; logits %dx%d), fp32 torch CPU, %d steps, %.2f s/step"
+                       % (sample_rows, P_TOK, T_TOK, codes, D_DIM, sample_rows, sample_rows, len(times), t)), t
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    steps = max(1, min(args.steps, 5))
+    warmup = max(1, min(args.warmup, 2))
+    cb, t = cpu_reference_run(args.cpu_sample, steps, warmup, args.codes)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "pairs/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, note="CPU arm: each step is a %d-row sample of the workload" % args.cpu_sample),
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, note=None):
+    c = {"workload": "FDT ViT-B/32 codebook grounding (codebook %dx%d, P=%d, T=%d, sparsemax, max-pool, T=1000) + "
+                     "ClipInfoCELoss fwd/bwd, global batch %d" % (args.codes, D_DIM, P_TOK, T_TOK, args.global_batch),
+         "global_batch": args.global_batch, "per_gpu_batch": args.global_batch // max(args.gpus, 1),
+         "parallelism": "dp%d (row-sharded logits, all-gather + reduce-scatter)" % args.gpus,
+         "l2_policy": "inputs larger than L2 (q: %.1f GB per rank)" % (
+             args.global_batch // max(args.gpus, 1) * (P_TOK + T_TOK) * D_DIM * 4 / 1e9)}
+    if note:
+        c["note"] = note
+    return c
+
+
+# ---------------------------------------------------------------------------------------------------
+# clocks sampler
+# ---------------------------------------------------------------------------------------------------
+class Clocks:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for ts, row in self.rows:
+            if ts < t0 or ts > t1 + 0.2:
+                continue
+            f = [x.strip() for x in row.split(",")]
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------
+def run_ours(args):
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the ilfdt path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == max(args.gpus, 1) or world == 1, "launch with torchrun --nproc-per-node == --gpus"
+
+    import ilfdt
+    from ilfdt import functional as Fn
+    from ilfdt import ops
+    ilfdt.set_compute_dtype(args.mode)
+
+    K = args.codes
+    b = args.global_batch // world
+    g = torch.Generator(device=dev).manual_seed(1000 + rank)
+    q_img = torch.randn(b, P_TOK, D_DIM, device=dev, generator=g)
+    q_txt = torch.randn(b, T_TOK, D_DIM, device=dev, generator=g)
+    lens = torch.randint(5, T_TOK + 1, (b,), device=dev, generator=g)
+    mask = torch.zeros(b, T_TOK, device=dev)
+    mask[torch.arange(T_TOK, device=dev).view(1, -1) >= lens.view(-1, 1)] = float("-inf")
+    gs = torch.Generator(device=dev).manual_seed(0)   # same codebook on every rank
+    sd = torch.nn.Parameter(torch.randn(K, D_DIM, device=dev, generator=gs))
+    p = torch.nn.Parameter(torch.full((1,), math.log(1 / 0.07), device=dev))
+    label_offset = rank * b if world > 1 else 0
+
+    def step(qi, qt, mk):
+        """The hot path exactly as ilfdt.model.clip_fdt.Clip_FDT.forward + ClipInfoCELoss run it."""
+        qi.requires_grad_(True)
+        qt.requires_grad_(True)
+        sd.grad = None
+        p.grad = None
+        qi.grad = None
+        qt.grad = None
+        mode = Fn.get_compute_dtype()
+        _, f_i = Fn.GroundingFunction.apply(qi, sd, None, TEMPERATURE, mode)
+        _, f_t = Fn.GroundingFunction.apply(qt, sd, mk, TEMPERATURE, mode)
+        x_i = Fn.L2NormFunction.apply(f_i, 1e-10)
+        x_t = Fn.L2NormFunction.apply(f_t, 1e-10)
+        s = p.exp()
+        s.data = torch.clamp(s.data, max=100)
+        g_i = Fn.AllGather.apply(x_i).view(-1, D_DIM)
+        g_t = Fn.AllGather.apply(x_t).view(-1, D_DIM)
+        loss = Fn.InfoNCEFunction.apply(x_i, x_t, g_i, g_t, s, label_offset, mode)
+        loss.backward()
+        return loss
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing (value) ----
+    for _ in range(args.warmup):
+        step(q_img, q_txt, mask)
+    sync()
+    clocks = Clocks(local)
+    if rank == 0:
+        clocks.start()
+        time.sleep(0.3)
+    ops.PROFILE.clear()
+    ops.PROFILE_ON = True
+    ops.LAUNCHES = 0
+    sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(args.steps):
+        loss = step(q_img, q_txt, mask)
+    e1.record()
+    sync()
+    t1 = time.perf_counter()
+    ops.PROFILE_ON = False
+    launches = ops.LAUNCHES
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        tms = torch.tensor([ms], device=dev)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = tms.item()
+    clk = clocks.stop(t0, t1) if rank == 0 else None
+    ms_per_step = ms / args.steps
+    value = args.global_batch / (ms_per_step * 1e-3)
+    loss_val = float(loss.item())
+
+    # ---- dominant kernel: the fused q.codebook^T + max-pool tcgen05 kernel (ilfdt_ground_fwd) ----
+    pk = peaks()
+    roof = None
+    prof = ops.profile_summary()
+    if "ground_fwd" in prof:
+        n_launch, tot_ms = prof["ground_fwd"]
+        flops_per_step = 2.0 * b * (P_TOK + T_TOK) * D_DIM * K          # both launches (image + text) of one step
+        avg_pair_ms = tot_ms / (n_launch / 2.0)
+        achieved = flops_per_step / (avg_pair_ms * 1e-3) / 1e12
+        roof = {"bound": "tensor", "kernel": "umma_kernel<EPI_POOLMAX> (ilfdt_ground_fwd, image+text launches)",
+                "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
+                "traffic": None, "peak_source": pk["src"], "avg_launch_ms": tot_ms / n_launch,
+                "share_of_step": (tot_ms / args.steps) / ms_per_step,
+                "algorithmic_flops_per_launch_pair": flops_per_step}
+    kernel_ms = {k: v[1] / args.steps for k, v in prof.items()}
+
+    # ---- end to end through the public call with HOST buffers ----
+    e2e = None
+    if not args.no_e2e:
+        h_qi = torch.empty(q_img.shape, dtype=torch.float32, pin_memory=True).copy_(q_img)
+        h_qt = torch.empty(q_txt.shape, dtype=torch.float32, pin_memory=True).copy_(q_txt)
+        h_mk = torch.empty(mask.shape, dtype=torch.float32, pin_memory=True).copy_(mask)
+        h_loss = torch.empty((), dtype=torch.float32, pin_memory=True)
+        d_qi, d_qt, d_mk = torch.empty_like(q_img), torch.empty_like(q_txt), torch.empty_like(mask)
+        del q_img, q_txt
+
+        def e2e_step():
+            d_qi.requires_grad_(False)
+            d_qt.requires_grad_(False)
+            d_qi.copy_(h_qi, non_blocking=True)
+            d_qt.copy_(h_qt, non_blocking=True)
+            d_mk.copy_(h_mk, non_blocking=True)
+            l = step(d_qi, d_qt, d_mk)
+            h_loss.copy_(l.detach(), non_blocking=True)
+
+        for _ in range(max(1, min(args.warmup, 2))):
+            e2e_step()
+        sync()
+        e0.record()
+        for _ in range(args.steps):
+            e2e_step()
+        e1.record()
+        sync()
+        ems = e0.elapsed_time(e1)
+        if world > 1:
+            tms = torch.tensor([ems], device=dev)
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+            ems = tms.item()
+        e2e = {"value": args.global_batch / (ems / args.steps * 1e-3), "unit": "pairs/s",
+               "h2d_bytes_per_step": int((h_qi.numel() + h_qt.numel() + h_mk.numel()) * 4),
+               "d2h_bytes_per_step": 4, "ms_per_step": ems / args.steps,
+               "note": "fp32 q_img/q_txt/mask copied from pinned host memory every step (per rank), loss read back"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu, _ = cpu_reference_run(args.cpu_sample, 3, 1, K)
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": args.mode, "data": "synthetic", "config": workload_config(args),
+                "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk,
+                "loss": loss_val, "kernel_ms_per_step": kernel_ms}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,166 @@
+/*
+ * ilfdt.h -- C ABI of libilfdt.so: the B200 (sm_100a) kernels behind the FDT-grounding +
+ * ClipInfoCELoss hot path of iterated-learning FDT-CLIP training.
+ *
+ * This is the drop-in boundary. The reference (hellomuffin/iterated-learning-for-vlm)
+ * is pure PyTorch and has no FFI of its own; each entry point below names the reference lines
+ * (paths relative to the reference root) whose arithmetic it replaces. The Python host side
+ * (iterated-learning-for-vlm_b200/ilfdt) binds these with ctypes; INTEGRATION.md shows the stub.
+ *
+ * Conventions
+ *   - every function returns an int32 status: 0 = ok, negative = ILFDT_E_*; the message for the
+ *     last failure on the calling thread is ilfdt_last_error().
+ *   - the caller owns ALL memory. Pointers are device pointers unless named host_*. Tensors are
+ *     dense row-major with the shapes given. Nothing here allocates user-visible buffers,
+ *     synchronises the host, or keeps global mutable state (one small per-thread error string).
+ *   - `stream` is a cudaStream_t passed as void*. Work is enqueued on it and the call returns.
+ *   - dtype arguments are ILFDT_F32 or ILFDT_BF16. F32 selects the fp32-exact SIMT kernels
+ *     (parity mode, <=1e-5 rel); BF16 selects the tcgen05/TMEM/TMA tensor-core kernels with fp32
+ *     accumulation (throughput mode, <=2e-2 rel).
+ *   - `ws`/`ws_bytes`: caller-provided scratch; query the size with the matching *_ws_bytes().
+ *   - there is no CPU fallback: on a device that is not sm_100 every compute call returns
+ *     ILFDT_E_ARCH.
+ */
+#ifndef ILFDT_H_
+#define ILFDT_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ILFDT_ABI_VERSION 1
+
+enum {
+  ILFDT_OK = 0,
+  ILFDT_E_INVALID_ARG = -1,
+  ILFDT_E_UNSUPPORTED_SHAPE = -2,
+  ILFDT_E_CUDA = -3,
+  ILFDT_E_NCCL = -4,
+  ILFDT_E_ARCH = -5
+};
+
+enum { ILFDT_F32 = 0, ILFDT_BF16 = 1 };
+enum { ILFDT_POOL_MAX = 0, ILFDT_POOL_SUM = 1, ILFDT_POOL_MEAN = 2 };
+
+/* ---- library ---------------------------------------------------------------------------- */
+int32_t ilfdt_abi_version(void);
+const char* ilfdt_last_error(void);
+/* 0 if `device` is an sm_100 part and the kernels can run there, ILFDT_E_ARCH otherwise. */
+int32_t ilfdt_device_check(int32_t device);
+
+/* ---- layout helpers (feed the bf16 tensor-core kernels) ----------------------------------- */
+/* dst_bf16[i] = bf16(src[i]) */
+int32_t ilfdt_cast_bf16(const float* src, void* dst_bf16, int64_t n, void* stream);
+/* src [rows, cols] f32 or bf16 -> dst_bf16 [cols, rows] */
+int32_t ilfdt_transpose_bf16(const void* src, int32_t src_dtype, int64_t rows, int64_t cols,
+                             void* dst_bf16, void* stream);
+
+/* ---- a1: Query_model score block, prototype/model/clip_fdt.py:113-145 --------------------- */
+/* q [b, n_tok, D], sd [K, D] (dtype = F32 or BF16, both the same), mask [b, n_tok] f32 with 0 for a
+ * real token and -inf for a pad (text_transformer.py:182-194) or NULL.
+ * pooled[b,K] = pool_t( ((q.sd^T) / sqrt_d) * (mask==0) / temperature )   (clip_fdt.py:118-145),
+ * arg[b,K] = the token index the max came from (int16; pool MAX only, may be NULL otherwise).
+ * The [b,n_tok,K] scores never exist in memory. */
+int64_t ilfdt_ground_fwd_ws_bytes(int32_t dtype, int64_t b, int64_t n_tok, int64_t K, int64_t D);
+int32_t ilfdt_ground_fwd(const void* q, const void* sd, int32_t dtype, const float* mask,
+                         int64_t b, int64_t n_tok, int64_t K, int64_t D,
+                         float sqrt_d, float temperature, int32_t pool_type,
+                         float* pooled, int16_t* arg, void* ws, int64_t ws_bytes, void* stream);
+
+/* ---- a2: Sparsemax, prototype/model/sparsemax.py:22-71 ------------------------------------ */
+/* z [rows, K] -> w [rows, K] (simplex projection of each row), tau[rows], nnz[rows];
+ * w_bf16 (optional, may be NULL) receives a bf16 copy of w for the pooling GEMM. */
+int32_t ilfdt_sparsemax_fwd(const float* z, int64_t rows, int64_t K, float* w, void* w_bf16,
+                            float* tau, int32_t* nnz, void* stream);
+/* dz = nz * (g - mean_nz(g)),  nz = (w > 0): the gradient autograd derives through sort/cumsum. */
+int32_t ilfdt_sparsemax_bwd(const float* w, const float* g, int64_t rows, int64_t K, float* dz,
+                            void* stream);
+
+/* ---- generic contraction used by a3 (pooling, clip_fdt.py:154) and its backward ------------ */
+/* out[n, m] (+)= alpha * sum_k A[m,k] * B[n,k];  A [M,Kr], B [N,Kr] both with the reduction
+ * index contiguous; out is f32 [N, M] with leading dimension ldo (elements).
+ * BF16: tcgen05 kernel (M % 128 == 0, Kr % 64 == 0 required); F32: SIMT kernel, any shape. */
+int32_t ilfdt_gemm_nt(const void* A, const void* B, int32_t dtype, int64_t M, int64_t N, int64_t Kr,
+                      float alpha, int32_t accumulate, float* out, int64_t ldo, void* stream);
+/* fp32 only, arbitrary strides: C(m,n) (+)= alpha * sum_k A(m,k) B(n,k), X(i,j) = X[i*rs + j*cs] */
+int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs,
+                               const float* B, int64_t b_rs, int64_t b_cs,
+                               float* C, int64_t c_rs, int64_t c_cs,
+                               int64_t M, int64_t N, int64_t Kr, float alpha, int32_t accumulate,
+                               void* stream);
+
+/* ---- a13: backward of the score block through max-pool + sparsemax ------------------------- */
+/* Inputs: g [b,K] = dLoss/dw (f32, OVERWRITTEN with coef), w [b,K], arg [b,K], q, sd, mask as in
+ * ilfdt_ground_fwd.  coef[b,k] = nz*(g - mean_nz g) * keep[b,arg] / (sqrt_d*temperature);
+ * dq[b,arg[b,k],:] += coef*sd[k,:]  (dq [b,n_tok,D] f32, fully written);
+ * dsd[k,:] += coef*q[b,arg[b,k],:]   (dsd [K,D] f32, ACCUMULATED into).
+ * Only support entries (w>0) are touched: cost scales with nnz, not with n_tok*K. */
+int32_t ilfdt_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd,
+                         int32_t dtype, const float* mask, int64_t b, int64_t n_tok, int64_t K,
+                         int64_t D, float sqrt_d, float temperature,
+                         float* dq, float* dsd, void* stream);
+
+/* ---- a5: L2 normalise, clip_fdt.py:411-412 / clip.py:133-134 ------------------------------ */
+/* x = f / (||f|| + eps); x_bf16 optional copy; norm[rows] = ||f||. */
+int32_t ilfdt_l2norm_fwd(const float* f, int64_t rows, int64_t D, float eps, float* x, void* x_bf16,
+                         float* norm, void* stream);
+/* df = (g - x * (x.g) * ||f||/(||f||+eps)) / (||f|| + eps) */
+int32_t ilfdt_l2norm_bwd(const float* x, const float* norm, const float* g, int64_t rows, int64_t D,
+                         float eps, float* df, void* stream);
+
+/* ---- a8 + a10: logits and ClipInfoCELoss, clip_fdt.py:421-422, loss_functions/loss.py:40-50 --- */
+/* logits[b, B] = scale[0] * x[b,:] . g[B,:]   (materialising route; accuracy()/visualisation).
+ * `scale` is a DEVICE pointer to the (already clamped) exp(logit_scale), so that no call on this
+ * path ever needs the host to read a parameter back. */
+int32_t ilfdt_logits(const void* x, const void* g, int32_t dtype, int64_t b, int64_t B, int64_t D,
+                     const float* scale, float* out, void* stream);
+
+/* Fused InfoNCE forward. x_img/x_txt [b,D] local rows, g_img/g_txt [B,D] gathered (rank-major),
+ * label of local row r is label_offset + r (loss.py:41-45). Produces per-row log-sum-exp and label
+ * logit of logits_per_image = scale*x_img.g_txt^T and logits_per_text = scale*x_txt.g_img^T and
+ * loss[0] = (mean(lse_i-diag_i) + mean(lse_t-diag_t))/2.  The [b,B] logits are never stored in
+ * BF16 mode; F32 mode streams them through `ws` in row chunks. */
+int64_t ilfdt_nce_ws_bytes(int32_t dtype, int64_t b, int64_t B, int64_t D);
+int32_t ilfdt_nce_fwd(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt,
+                      int32_t dtype, int64_t b, int64_t B, int64_t D, const float* scale,
+                      int64_t label_offset, float* lse_i, float* lse_t, float* diag_i, float* diag_t,
+                      float* loss, void* ws, int64_t ws_bytes, void* stream);
+/* Fused InfoNCE backward. grad_out: device pointer to dLoss (scalar). P = (softmax - onehot) *
+ * grad_out/(2b) is recomputed tile by tile from lse_*. Outputs (all f32, overwritten):
+ * dx_img, dx_txt [b,D]; dg_img, dg_txt [B,D] (gradient w.r.t. the gathered copies, to be
+ * reduce-scattered by the caller: AllGather.backward, clip_fdt.py:182-188); dscale[0] = dLoss/dscale.
+ * In BF16 mode g_img_t/g_txt_t [D,B] and x_img_t/x_txt_t [D,b] are bf16 transposes of the inputs
+ * (ilfdt_transpose_bf16); F32 mode ignores them (may be NULL). */
+int32_t ilfdt_nce_bwd(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt,
+                      const void* x_img_t, const void* x_txt_t, const void* g_img_t, const void* g_txt_t,
+                      int32_t dtype, int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset,
+                      const float* lse_i, const float* lse_t, const float* grad_out,
+                      float* dx_img, float* dx_txt, float* dg_img, float* dg_txt, float* dscale,
+                      void* ws, int64_t ws_bytes, void* stream);
+
+/* Cross-entropy over STORED logits [b,B] (the route taken when a caller hands ClipInfoCELoss real
+ * tensors instead of the fused stash): lse[r], diag[r] = logits[r, label_offset + r]. */
+int32_t ilfdt_ce_rows_fwd(const float* logits, int64_t b, int64_t B, int64_t label_offset, float* lse,
+                          float* diag, void* stream);
+/* dlogits[r,c] = (exp(logits[r,c] - lse[r]) - [c == label_offset + r]) * grad_out[0] * coef */
+int32_t ilfdt_ce_rows_bwd(const float* logits, int64_t b, int64_t B, int64_t label_offset, const float* lse,
+                          const float* grad_out, float coef, float* dlogits, void* stream);
+
+/* ---- N1: accuracy(logits_per_image, labels, topk=(1,5)), prototype/utils/misc.py:464-477 ------ */
+/* counts[0] = #rows whose label logit is the row max, counts[1] = #rows where fewer than 5 entries
+ * exceed it.  logits f32 [b,B]. */
+int32_t ilfdt_topk_hits(const float* logits, int64_t b, int64_t B, int64_t label_offset,
+                        int32_t* counts, void* stream);
+
+/* ---- a12: codebook reset / store / keep, clip_fdt.py:281-283, train_solver.py:211-215,549-553 -- */
+/* dst[i] ~ N(0,1): Philox4x32-10 keyed by seed, counter (i/4, generation), Box-Muller. Same values
+ * on every rank for the same (seed, generation). */
+int32_t ilfdt_randn_fill(float* dst, int64_t n, uint64_t seed, uint32_t generation, void* stream);
+int32_t ilfdt_copy(void* dst, const void* src, int64_t bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ILFDT_H_ */

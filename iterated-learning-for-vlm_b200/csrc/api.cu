@@ -1,0 +1,326 @@
+// extern "C" entry points of libilfdt.so (see include/ilfdt.h for the contract of each).
+#include "common.cuh"
+#include "launch.h"
+#include <algorithm>
+
+namespace ilfdt {
+
+int sm_count() {
+  static thread_local int cached_dev = -1, cached = 148;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev != cached_dev) {
+    int n = 148;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess) cached = n;
+    cached_dev = dev;
+  }
+  return cached;
+}
+
+int32_t require_sm100() {
+  static thread_local int ok_dev = -1;
+  int dev = 0;
+  ILFDT_CUDA_OK(cudaGetDevice(&dev));
+  if (dev == ok_dev) return ILFDT_OK;
+  int major = 0, minor = 0;
+  ILFDT_CUDA_OK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  ILFDT_CUDA_OK(cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev));
+  ILFDT_REQUIRE(major == 10, ILFDT_E_ARCH,
+                "libilfdt is built for sm_100a only; device %d is sm_%d%d and there is no fallback path", dev, major,
+                minor);
+  ok_dev = dev;
+  return ILFDT_OK;
+}
+
+// F32 route of the InfoNCE step: logits are streamed through the workspace in row chunks.
+static int64_t nce_f32_chunk_rows(int64_t b, int64_t B) {
+  const int64_t budget_elems = 1ll << 26;  // 256 MiB of fp32
+  return std::max<int64_t>(1, std::min<int64_t>(b, budget_elems / std::max<int64_t>(B, 1)));
+}
+
+static int32_t nce_fwd_f32(const float* x_img, const float* x_txt, const float* g_img, const float* g_txt, int64_t b,
+                           int64_t B, int64_t D, const float* scale, int64_t label_offset, float* lse_i, float* lse_t,
+                           float* diag_i, float* diag_t, void* ws, int64_t ws_bytes, cudaStream_t st) {
+  const int64_t R = nce_f32_chunk_rows(b, B);
+  ILFDT_REQUIRE(ws != nullptr && ws_bytes >= R * B * 4, ILFDT_E_INVALID_ARG, "nce_fwd(f32): workspace too small");
+  float* L = reinterpret_cast<float*>(ws);
+  for (int dir = 0; dir < 2; ++dir) {
+    const float* X = dir == 0 ? x_img : x_txt;
+    const float* G = dir == 0 ? g_txt : g_img;  // clip_fdt.py:421-422
+    float* lse = dir == 0 ? lse_i : lse_t;
+    float* diag = dir == 0 ? diag_i : diag_t;
+    for (int64_t r0 = 0; r0 < b; r0 += R) {
+      const int64_t rows = std::min(R, b - r0);
+      int32_t rc = launch_gemm_f32(X + r0 * D, D, 1, G, D, 1, L, B, 1, rows, B, D, 1.f, scale, 0, st);
+      if (rc != ILFDT_OK) return rc;
+      rc = launch_lse_rows(L, B, rows, B, label_offset + r0, lse + r0, diag + r0, st);
+      if (rc != ILFDT_OK) return rc;
+    }
+  }
+  return ILFDT_OK;
+}
+
+static int32_t nce_bwd_f32(const float* x_img, const float* x_txt, const float* g_img, const float* g_txt, int64_t b,
+                           int64_t B, int64_t D, const float* scale, int64_t label_offset, const float* lse_i,
+                           const float* lse_t, const float* grad_out, float* dx_img, float* dx_txt, float* dg_img,
+                           float* dg_txt, float* dscale, void* ws, int64_t ws_bytes, cudaStream_t st) {
+  const int64_t R = nce_f32_chunk_rows(b, B);
+  ILFDT_REQUIRE(ws != nullptr && ws_bytes >= R * B * 4, ILFDT_E_INVALID_ARG, "nce_bwd(f32): workspace too small");
+  float* L = reinterpret_cast<float*>(ws);
+  ILFDT_CUDA_OK(cudaMemsetAsync(dscale, 0, 4, st));
+  const float coef = 1.f / (2.f * (float)b);  // CE mean over the local rows, then /2 (loss.py:47-49)
+  for (int dir = 0; dir < 2; ++dir) {
+    const float* X = dir == 0 ? x_img : x_txt;
+    const float* G = dir == 0 ? g_txt : g_img;
+    const float* lse = dir == 0 ? lse_i : lse_t;
+    float* dX = dir == 0 ? dx_img : dx_txt;
+    float* dG = dir == 0 ? dg_txt : dg_img;
+    for (int64_t r0 = 0; r0 < b; r0 += R) {
+      const int64_t rows = std::min(R, b - r0);
+      int32_t rc = launch_gemm_f32(X + r0 * D, D, 1, G, D, 1, L, B, 1, rows, B, D, 1.f, scale, 0, st);
+      if (rc != ILFDT_OK) return rc;
+      rc = launch_softmax_grad_rows(L, L, B, rows, B, label_offset + r0, lse + r0, grad_out, coef, scale, dscale, st);
+      if (rc != ILFDT_OK) return rc;
+      // dX[r,:] = scale * sum_c P[r,c] G[c,:]
+      rc = launch_gemm_f32(L, B, 1, G, 1, D, dX + r0 * D, D, 1, rows, D, B, 1.f, scale, 0, st);
+      if (rc != ILFDT_OK) return rc;
+      // dG[c,:] (+)= scale * sum_r P[r,c] X[r,:]
+      rc = launch_gemm_f32(L, 1, B, X + r0 * D, 1, D, dG, D, 1, B, D, rows, 1.f, scale, r0 > 0 ? 1 : 0, st);
+      if (rc != ILFDT_OK) return rc;
+    }
+  }
+  return ILFDT_OK;
+}
+
+}  // namespace ilfdt
+
+using namespace ilfdt;
+
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+#define ARCH_GUARD()                        \
+  do {                                      \
+    int32_t rc__ = require_sm100();         \
+    if (rc__ != ILFDT_OK) return rc__;      \
+  } while (0)
+#define DTYPE_GUARD(dt) \
+  ILFDT_REQUIRE((dt) == ILFDT_F32 || (dt) == ILFDT_BF16, ILFDT_E_INVALID_ARG, "dtype must be ILFDT_F32 or ILFDT_BF16")
+
+extern "C" {
+
+int32_t ilfdt_abi_version(void) { return ILFDT_ABI_VERSION; }
+const char* ilfdt_last_error(void) { return err_buf(); }
+
+int32_t ilfdt_device_check(int32_t device) {
+  int major = 0;
+  ILFDT_CUDA_OK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+  ILFDT_REQUIRE(major == 10, ILFDT_E_ARCH, "device %d is not an sm_100 part (major=%d)", device, major);
+  return ILFDT_OK;
+}
+
+int32_t ilfdt_cast_bf16(const float* src, void* dst_bf16, int64_t n, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(n >= 0 && (n == 0 || (src && dst_bf16)), ILFDT_E_INVALID_ARG, "cast_bf16: null pointer");
+  return launch_cast_bf16(src, dst_bf16, n, ST(stream));
+}
+
+int32_t ilfdt_transpose_bf16(const void* src, int32_t src_dtype, int64_t rows, int64_t cols, void* dst_bf16,
+                             void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(src_dtype);
+  ILFDT_REQUIRE(rows >= 0 && cols >= 0 && (rows * cols == 0 || (src && dst_bf16)), ILFDT_E_INVALID_ARG,
+                "transpose_bf16: bad arguments");
+  return launch_transpose_bf16(src, src_dtype, rows, cols, dst_bf16, ST(stream));
+}
+
+int64_t ilfdt_ground_fwd_ws_bytes(int32_t dtype, int64_t b, int64_t n_tok, int64_t K, int64_t D) {
+  (void)n_tok; (void)D;
+  return dtype == ILFDT_F32 ? b * K * 8 : 0;
+}
+
+int32_t ilfdt_ground_fwd(const void* q, const void* sd, int32_t dtype, const float* mask, int64_t b, int64_t n_tok,
+                         int64_t K, int64_t D, float sqrt_d, float temperature, int32_t pool_type, float* pooled,
+                         int16_t* arg, void* ws, int64_t ws_bytes, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(dtype);
+  ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && K >= 1 && D >= 1, ILFDT_E_INVALID_ARG, "ground_fwd: bad shape");
+  ILFDT_REQUIRE(b == 0 || (q && sd && pooled), ILFDT_E_INVALID_ARG, "ground_fwd: null pointer");
+  ILFDT_REQUIRE(sqrt_d > 0.f && temperature != 0.f, ILFDT_E_INVALID_ARG, "ground_fwd: bad scale");
+  ILFDT_REQUIRE(pool_type >= ILFDT_POOL_MAX && pool_type <= ILFDT_POOL_MEAN, ILFDT_E_INVALID_ARG,
+                "ground_fwd: bad pool_type");
+  ILFDT_REQUIRE(pool_type != ILFDT_POOL_MAX || arg != nullptr || b == 0, ILFDT_E_INVALID_ARG,
+                "ground_fwd: arg required for max pooling");
+  if (b == 0) return ILFDT_OK;
+  if (dtype == ILFDT_F32)
+    return launch_ground_fwd_f32(reinterpret_cast<const float*>(q), reinterpret_cast<const float*>(sd), mask, b,
+                                 n_tok, K, D, sqrt_d, temperature, pool_type, pooled, arg, ws, ws_bytes, ST(stream));
+  ILFDT_REQUIRE(pool_type == ILFDT_POOL_MAX, ILFDT_E_UNSUPPORTED_SHAPE,
+                "ground_fwd(bf16): only max pooling is fused on the tensor-core path (use ILFDT_F32)");
+  ILFDT_REQUIRE(temperature > 0.f, ILFDT_E_INVALID_ARG, "ground_fwd(bf16): temperature must be positive");
+  return launch_ground_fwd_bf16(q, sd, mask, b, n_tok, K, D, sqrt_d, temperature, pooled, arg, ST(stream));
+}
+
+int32_t ilfdt_sparsemax_fwd(const float* z, int64_t rows, int64_t K, float* w, void* w_bf16, float* tau,
+                            int32_t* nnz, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(rows >= 0 && K >= 1 && (rows == 0 || (z && w)), ILFDT_E_INVALID_ARG, "sparsemax_fwd: bad arguments");
+  return launch_sparsemax_fwd(z, rows, K, w, w_bf16, tau, nnz, ST(stream));
+}
+
+int32_t ilfdt_sparsemax_bwd(const float* w, const float* g, int64_t rows, int64_t K, float* dz, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(rows >= 0 && K >= 1 && (rows == 0 || (w && g && dz)), ILFDT_E_INVALID_ARG,
+                "sparsemax_bwd: bad arguments");
+  return launch_sparsemax_bwd(w, g, rows, K, dz, ST(stream));
+}
+
+int32_t ilfdt_gemm_nt(const void* A, const void* B, int32_t dtype, int64_t M, int64_t N, int64_t Kr, float alpha,
+                      int32_t accumulate, float* out, int64_t ldo, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(dtype);
+  ILFDT_REQUIRE(M >= 0 && N >= 0 && Kr >= 1 && ldo >= M, ILFDT_E_INVALID_ARG, "gemm_nt: bad shape");
+  ILFDT_REQUIRE(M * N == 0 || (A && B && out), ILFDT_E_INVALID_ARG, "gemm_nt: null pointer");
+  if (dtype == ILFDT_F32)
+    return launch_gemm_f32(reinterpret_cast<const float*>(A), Kr, 1, reinterpret_cast<const float*>(B), Kr, 1, out, 1,
+                           ldo, M, N, Kr, alpha, nullptr, accumulate, ST(stream));
+  return launch_gemm_nt_bf16(A, B, M, N, Kr, alpha, nullptr, accumulate, out, ldo, ST(stream));
+}
+
+int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs, const float* B, int64_t b_rs, int64_t b_cs,
+                               float* C, int64_t c_rs, int64_t c_cs, int64_t M, int64_t N, int64_t Kr, float alpha,
+                               int32_t accumulate, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(M >= 0 && N >= 0 && Kr >= 1, ILFDT_E_INVALID_ARG, "gemm_f32_strided: bad shape");
+  ILFDT_REQUIRE(M * N == 0 || (A && B && C), ILFDT_E_INVALID_ARG, "gemm_f32_strided: null pointer");
+  return launch_gemm_f32(A, a_rs, a_cs, B, b_rs, b_cs, C, c_rs, c_cs, M, N, Kr, alpha, nullptr, accumulate, ST(stream));
+}
+
+int32_t ilfdt_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd, int32_t dtype,
+                         const float* mask, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
+                         float temperature, float* dq, float* dsd, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(dtype);
+  ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && K >= 1 && D >= 1, ILFDT_E_INVALID_ARG, "ground_bwd: bad shape");
+  ILFDT_REQUIRE(b == 0 || (g && w && arg && q && sd && dq && dsd), ILFDT_E_INVALID_ARG, "ground_bwd: null pointer");
+  return launch_ground_bwd(g, w, arg, q, sd, dtype, mask, b, n_tok, K, D, sqrt_d, temperature, dq, dsd, ST(stream));
+}
+
+int32_t ilfdt_l2norm_fwd(const float* f, int64_t rows, int64_t D, float eps, float* x, void* x_bf16, float* norm,
+                         void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(rows >= 0 && D >= 1 && (rows == 0 || f), ILFDT_E_INVALID_ARG, "l2norm_fwd: bad arguments");
+  return launch_l2norm_fwd(f, rows, D, eps, x, x_bf16, norm, ST(stream));
+}
+
+int32_t ilfdt_l2norm_bwd(const float* x, const float* norm, const float* g, int64_t rows, int64_t D, float eps,
+                         float* df, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(rows >= 0 && D >= 1 && (rows == 0 || (x && norm && g && df)), ILFDT_E_INVALID_ARG,
+                "l2norm_bwd: bad arguments");
+  return launch_l2norm_bwd(x, norm, g, rows, D, eps, df, ST(stream));
+}
+
+int32_t ilfdt_logits(const void* x, const void* g, int32_t dtype, int64_t b, int64_t B, int64_t D,
+                     const float* scale, float* out, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(dtype);
+  ILFDT_REQUIRE(b >= 0 && B >= 0 && D >= 1 && (b * B == 0 || (x && g && out && scale)), ILFDT_E_INVALID_ARG,
+                "logits: bad arguments");
+  if (dtype == ILFDT_F32)
+    return launch_gemm_f32(reinterpret_cast<const float*>(x), D, 1, reinterpret_cast<const float*>(g), D, 1, out, B, 1,
+                           b, B, D, 1.f, scale, 0, ST(stream));
+  // out[row, col]: lanes = gathered rows (col), columns = local rows -> coalesced stores
+  return launch_gemm_nt_bf16(g, x, B, b, D, 1.f, scale, 0, out, B, ST(stream));
+}
+
+int64_t ilfdt_nce_ws_bytes(int32_t dtype, int64_t b, int64_t B, int64_t D) {
+  if (dtype == ILFDT_F32) return nce_f32_chunk_rows(b, B) * B * 4;
+  return std::max(nce_fwd_bf16_ws_bytes(b, B), nce_bwd_bf16_ws_bytes(b, B, D));
+}
+
+int32_t ilfdt_nce_fwd(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt, int32_t dtype,
+                      int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset, float* lse_i,
+                      float* lse_t,
+                      float* diag_i, float* diag_t, float* loss, void* ws, int64_t ws_bytes, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(dtype);
+  ILFDT_REQUIRE(b >= 1 && B >= b && D >= 1, ILFDT_E_INVALID_ARG, "nce_fwd: need 1 <= b <= B");
+  ILFDT_REQUIRE(label_offset >= 0 && label_offset + b <= B, ILFDT_E_INVALID_ARG, "nce_fwd: labels out of range");
+  ILFDT_REQUIRE(x_img && x_txt && g_img && g_txt && lse_i && lse_t && diag_i && diag_t && loss && scale, ILFDT_E_INVALID_ARG,
+                "nce_fwd: null pointer");
+  int32_t rc;
+  if (dtype == ILFDT_F32)
+    rc = nce_fwd_f32(reinterpret_cast<const float*>(x_img), reinterpret_cast<const float*>(x_txt),
+                     reinterpret_cast<const float*>(g_img), reinterpret_cast<const float*>(g_txt), b, B, D, scale,
+                     label_offset, lse_i, lse_t, diag_i, diag_t, ws, ws_bytes, ST(stream));
+  else
+    rc = launch_nce_fwd_bf16(x_img, x_txt, g_img, g_txt, b, B, D, scale, label_offset, lse_i, lse_t, diag_i, diag_t,
+                             ws, ws_bytes, ST(stream));
+  if (rc != ILFDT_OK) return rc;
+  return launch_nce_loss(lse_i, diag_i, lse_t, diag_t, b, loss, ST(stream));
+}
+
+int32_t ilfdt_nce_bwd(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt, const void* x_img_t,
+                      const void* x_txt_t, const void* g_img_t, const void* g_txt_t, int32_t dtype, int64_t b,
+                      int64_t B, int64_t D, const float* scale, int64_t label_offset, const float* lse_i,
+                      const float* lse_t, const float* grad_out, float* dx_img, float* dx_txt, float* dg_img, float* dg_txt,
+                      float* dscale, void* ws, int64_t ws_bytes, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(dtype);
+  ILFDT_REQUIRE(b >= 1 && B >= b && D >= 1, ILFDT_E_INVALID_ARG, "nce_bwd: need 1 <= b <= B");
+  ILFDT_REQUIRE(label_offset >= 0 && label_offset + b <= B, ILFDT_E_INVALID_ARG, "nce_bwd: labels out of range");
+  ILFDT_REQUIRE(x_img && x_txt && g_img && g_txt && lse_i && lse_t && grad_out && dx_img && dx_txt && dg_img &&
+                    dg_txt && dscale && scale,
+                ILFDT_E_INVALID_ARG, "nce_bwd: null pointer");
+  if (dtype == ILFDT_F32)
+    return nce_bwd_f32(reinterpret_cast<const float*>(x_img), reinterpret_cast<const float*>(x_txt),
+                       reinterpret_cast<const float*>(g_img), reinterpret_cast<const float*>(g_txt), b, B, D, scale,
+                       label_offset, lse_i, lse_t, grad_out, dx_img, dx_txt, dg_img, dg_txt, dscale, ws, ws_bytes,
+                       ST(stream));
+  ILFDT_REQUIRE(x_img_t && x_txt_t && g_img_t && g_txt_t, ILFDT_E_INVALID_ARG,
+                "nce_bwd(bf16): transposed operands required");
+  return launch_nce_bwd_bf16(x_img, x_txt, g_img, g_txt, x_img_t, x_txt_t, g_img_t, g_txt_t, b, B, D, scale,
+                             label_offset, lse_i, lse_t, grad_out, dx_img, dx_txt, dg_img, dg_txt, dscale, ws,
+                             ws_bytes, ST(stream));
+}
+
+int32_t ilfdt_ce_rows_fwd(const float* logits, int64_t b, int64_t B, int64_t label_offset, float* lse, float* diag,
+                          void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(b >= 0 && B >= 1 && (b == 0 || (logits && lse && diag)), ILFDT_E_INVALID_ARG, "ce_rows_fwd: bad arguments");
+  ILFDT_REQUIRE(label_offset >= 0 && label_offset + b <= B, ILFDT_E_INVALID_ARG, "ce_rows_fwd: labels out of range");
+  return launch_lse_rows(logits, B, b, B, label_offset, lse, diag, ST(stream));
+}
+
+int32_t ilfdt_ce_rows_bwd(const float* logits, int64_t b, int64_t B, int64_t label_offset, const float* lse,
+                          const float* grad_out, float coef, float* dlogits, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(b >= 0 && B >= 1 && (b == 0 || (logits && lse && grad_out && dlogits)), ILFDT_E_INVALID_ARG,
+                "ce_rows_bwd: bad arguments");
+  ILFDT_REQUIRE(label_offset >= 0 && label_offset + b <= B, ILFDT_E_INVALID_ARG, "ce_rows_bwd: labels out of range");
+  return launch_softmax_grad_rows(logits, dlogits, B, b, B, label_offset, lse, grad_out, coef, nullptr, nullptr,
+                                  ST(stream));
+}
+
+int32_t ilfdt_topk_hits(const float* logits, int64_t b, int64_t B, int64_t label_offset, int32_t* counts,
+                        void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(b >= 0 && B >= b && counts && (b == 0 || logits), ILFDT_E_INVALID_ARG, "topk_hits: bad arguments");
+  ILFDT_REQUIRE(label_offset >= 0 && label_offset + b <= B, ILFDT_E_INVALID_ARG, "topk_hits: labels out of range");
+  return launch_topk_hits(logits, b, B, label_offset, counts, ST(stream));
+}
+
+int32_t ilfdt_randn_fill(float* dst, int64_t n, uint64_t seed, uint32_t generation, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(n >= 0 && (n == 0 || dst), ILFDT_E_INVALID_ARG, "randn_fill: bad arguments");
+  return launch_randn_fill(dst, n, seed, generation, ST(stream));
+}
+
+int32_t ilfdt_copy(void* dst, const void* src, int64_t bytes, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(bytes >= 0 && (bytes == 0 || (dst && src)), ILFDT_E_INVALID_ARG, "copy: bad arguments");
+  if (bytes == 0) return ILFDT_OK;
+  ILFDT_CUDA_OK(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice, ST(stream)));
+  return ILFDT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,478 @@
+// tcgen05 / TMEM / TMA contraction kernel with fused epilogues (bf16 inputs, fp32 accumulation).
+//
+//   acc[m, n] = sum_k A[m, k] * B[n, k]        A [M, Kr], B [N, Kr] bf16, reduction index contiguous
+//
+// Mapping: the 128 rows of an A tile are the 128 TMEM lanes, the (<= 256) rows of a B tile are TMEM
+// columns, so an epilogue thread owns one A row and walks the B rows sequentially in registers:
+//   * grounding (a1):   A = codebook (lane = code), B = tokens  -> per-sample max/argmax over the
+//                       token columns is a private running max, no cross-lane reduction;
+//   * InfoNCE fwd (a10): A = local embeddings (lane = logits row), B = gathered embeddings
+//                       -> online log-sum-exp over the columns is private too;
+//   * plain contraction: out[n, m] store is coalesced across lanes.
+// Neither the [b, n_tok, K] scores nor the [b, B] logits are ever written to memory.
+//
+// Structure (one CTA per SM, persistent over work items = (A tile, range of B tiles)):
+//   warp 0   TMA producer: A tile either resident for the whole item (Kr <= 512: 8 x 16 KB slots,
+//            loaded once per item) or streamed with B; B tiles through a 3/4-stage mbarrier ring
+//   warp 1   MMA issuer: one elected lane issues tcgen05.mma (128 x block_n x 16) into one of two
+//            TMEM accumulators (2 x 256 columns = all 512), tcgen05.commit frees smem stages
+//   warps 2-5 epilogue: tcgen05.ld 32 columns at a time, fused reduction, release the accumulator
+// so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include "umma.cuh"
+#include "launch.h"
+#include <algorithm>
+#include <mutex>
+
+namespace ilfdt {
+
+using namespace umma;
+
+constexpr int UM_BM = 128;
+constexpr int UM_BK = 64;
+constexpr int UM_A_BYTES = UM_BM * UM_BK * 2;  // 16 KB
+constexpr int UM_B_BYTES = 256 * UM_BK * 2;    // 32 KB (max block_n)
+constexpr int UM_THREADS = 192;
+constexpr int UM_DATA_BYTES = 229376;          // 224 KB of operand staging
+constexpr int UM_SMEM_BYTES = UM_DATA_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+constexpr int UM_TMEM_COLS = 512;
+constexpr int UM_ACC_COLS = 256;
+
+enum { EPI_STORE_T = 0, EPI_POOLMAX = 1, EPI_LSE = 2 };
+
+struct UmmaParams {
+  int num_m_tiles, num_n_tiles, nchunk, tiles_per_chunk;
+  int nkb;      // ceil(Kr / 64)
+  int block_n;  // UMMA N: rows of B per tile (multiple of 16, <= 256)
+  int n_step;   // rows of B advanced per tile (<= block_n)
+  int m_rows, n_rows;
+  uint32_t idesc;
+  // EPI_STORE_T
+  float* out;
+  int64_t ldo;
+  float alpha;
+  const float* alpha_dev;
+  int accumulate;
+  // EPI_POOLMAX
+  const float* mask;
+  int n_tok, spt, n_samples;
+  float pool_scale;
+  float* pooled;
+  int16_t* arg;
+  // EPI_LSE
+  const float* scale_dev;
+  long long label_offset;
+  float* part_m;
+  float* part_s;
+  float* diag;
+};
+
+struct UmmaBars {
+  uint64_t full[4], empty[4], tmem_full[2], tmem_empty[2], a_full, a_empty;
+  uint32_t tmem_ptr;
+};
+
+template <int EPI, bool A_RES>
+__global__ void __launch_bounds__(UM_THREADS, 1)
+umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const UmmaParams p) {
+  extern __shared__ uint8_t um_smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(um_smem_raw) + 1023) & ~(uintptr_t)1023);
+  UmmaBars* bars = reinterpret_cast<UmmaBars*>(smem + UM_DATA_BYTES);
+  constexpr int STAGES = A_RES ? 3 : 4;
+  constexpr int STAGE_BYTES = A_RES ? UM_B_BYTES : (UM_A_BYTES + UM_B_BYTES);
+  uint8_t* ring = A_RES ? smem + 8 * UM_A_BYTES : smem;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_items = p.num_m_tiles * p.nchunk;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 4; ++i) { mbar_init(&bars->full[i], 1); mbar_init(&bars->empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&bars->tmem_full[i], 1); mbar_init(&bars->tmem_empty[i], 4); }
+    mbar_init(&bars->a_full, 1);
+    mbar_init(&bars->a_empty, 1);
+    fence_barrier_init();
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    tmem_alloc(&bars->tmem_ptr, UM_TMEM_COLS);
+    tmem_relinquish();
+  }
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem_base = bars->tmem_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      uint32_t stage = 0, phase = 0, it = 0;
+      const uint32_t tx_bytes = (A_RES ? 0u : (uint32_t)UM_A_BYTES) + (uint32_t)p.block_n * 128u;
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
+        const int m_tile = item % p.num_m_tiles, chunk = item / p.num_m_tiles;
+        const int n_begin = chunk * p.tiles_per_chunk, n_end = min(p.num_n_tiles, n_begin + p.tiles_per_chunk);
+        if (A_RES) {
+          mbar_wait(&bars->a_empty, (it & 1) ^ 1);
+          mbar_expect_tx(&bars->a_full, (uint32_t)p.nkb * UM_A_BYTES);
+          for (int kb = 0; kb < p.nkb; ++kb)
+            tma_load_2d(smem + kb * UM_A_BYTES, &tmA, &bars->a_full, kb * UM_BK, m_tile * UM_BM, kEvictLast);
+        }
+        for (int n = n_begin; n < n_end; ++n) {
+          for (int kb = 0; kb < p.nkb; ++kb) {
+            mbar_wait(&bars->empty[stage], phase ^ 1);
+            mbar_expect_tx(&bars->full[stage], tx_bytes);
+            uint8_t* st = ring + stage * STAGE_BYTES;
+            if (!A_RES) {
+              tma_load_2d(st, &tmA, &bars->full[stage], kb * UM_BK, m_tile * UM_BM, kEvictNormal);
+              st += UM_A_BYTES;
+            }
+            tma_load_2d(st, &tmB, &bars->full[stage], kb * UM_BK, n * p.n_step, kEvictNormal);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (elect_one()) {
+      uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0, it = 0;
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
+        const int chunk = item / p.num_m_tiles;
+        const int n_begin = chunk * p.tiles_per_chunk, n_end = min(p.num_n_tiles, n_begin + p.tiles_per_chunk);
+        if (A_RES) {
+          mbar_wait(&bars->a_full, it & 1);
+          fence_after_sync();
+        }
+        for (int n = n_begin; n < n_end; ++n) {
+          mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
+          fence_after_sync();
+          const uint32_t tmem_d = tmem_base + acc * UM_ACC_COLS;
+          for (int kb = 0; kb < p.nkb; ++kb) {
+            mbar_wait(&bars->full[stage], phase);
+            fence_after_sync();
+            uint8_t* st = ring + stage * STAGE_BYTES;
+            const uint64_t adesc = make_smem_desc_sw128(smem_u32(A_RES ? smem + kb * UM_A_BYTES : st));
+            const uint64_t bdesc = make_smem_desc_sw128(smem_u32(A_RES ? st : st + UM_A_BYTES));
+#pragma unroll
+            for (int k4 = 0; k4 < UM_BK / 16; ++k4)
+              mma_f16(tmem_d, advance_desc_k(adesc, k4 * 32), advance_desc_k(bdesc, k4 * 32), p.idesc,
+                      (kb | k4) != 0 ? 1u : 0u);
+            mma_commit(&bars->empty[stage]);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
+          mma_commit(&bars->tmem_full[acc]);
+          acc ^= 1;
+          if (acc == 0) acc_phase ^= 1;
+        }
+        if (A_RES) mma_commit(&bars->a_empty);
+      }
+    }
+  } else {
+    // ===================== epilogue warps (2..5) =====================
+    const int quad = warp & 3;  // TMEM lane quadrant this warp may access
+    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    uint32_t acc = 0, acc_phase = 0;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      const int m_tile = item % p.num_m_tiles, chunk = item / p.num_m_tiles;
+      const int n_begin = chunk * p.tiles_per_chunk, n_end = min(p.num_n_tiles, n_begin + p.tiles_per_chunk);
+      const int row = m_tile * UM_BM + quad * 32 + lane;  // A row owned by this thread
+      const bool row_ok = row < p.m_rows;
+      // EPI_LSE state (base-2 domain)
+      float run_m = -INFINITY, run_s = 0.f;
+      const float scale = (EPI == EPI_LSE) ? __ldg(p.scale_dev) : 1.f;
+      const float scale_log2 = scale * 1.4426950408889634f;
+      const float alpha = (EPI == EPI_STORE_T) ? (p.alpha_dev ? p.alpha * __ldg(p.alpha_dev) : p.alpha) : 1.f;
+      for (int n = n_begin; n < n_end; ++n) {
+        mbar_wait(&bars->tmem_full[acc], acc_phase);
+        fence_after_sync();
+        const uint32_t taddr = tmem_base + lane_addr + acc * UM_ACC_COLS;
+        const int n0 = n * p.n_step;
+
+        if (EPI == EPI_STORE_T) {
+          const int ncols = min(p.n_step, p.n_rows - n0);
+          for (int c0 = 0; c0 < ncols; c0 += 32) {
+            uint32_t v[32];
+            tmem_ld32(taddr + c0, v);
+            tmem_ld_wait();
+            if (row_ok) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                if (c0 + j < ncols) {
+                  float* o = p.out + (int64_t)(n0 + c0 + j) * p.ldo + row;
+                  float r = alpha * __uint_as_float(v[j]);
+                  *o = p.accumulate ? (*o + r) : r;
+                }
+              }
+            }
+          }
+        } else if (EPI == EPI_POOLMAX) {
+          // columns = tokens of samples [s0, s0 + nsmp), n_tok columns each
+          const int s0 = n * p.spt;
+          const int nsmp = min(p.spt, p.n_samples - s0);
+          const int ncols = nsmp * p.n_tok;
+          int tok = 0, smp = s0, best_i = 0;
+          float best = 0.f;
+          for (int c0 = 0; c0 < ncols; c0 += 32) {
+            uint32_t keep = 0xffffffffu;
+            if (p.mask != nullptr) {
+              const int col = c0 + lane;
+              const float mv = (col < ncols) ? __ldg(p.mask + (int64_t)n0 + col) : 0.f;
+              keep = __ballot_sync(0xffffffffu, mv == 0.f);
+            }
+            uint32_t v[32];
+            tmem_ld32(taddr + c0, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (c0 + j < ncols) {  // warp-uniform
+                // pads contribute score 0 (clip_fdt.py:125-130)
+                const float x = ((keep >> j) & 1u) ? __uint_as_float(v[j]) : 0.f;
+                if (tok == 0 || x > best) { best = x; best_i = tok; }
+                if (++tok == p.n_tok) {
+                  if (row_ok) {
+                    const int64_t o = (int64_t)smp * p.m_rows + row;
+                    p.pooled[o] = best * p.pool_scale;
+                    p.arg[o] = (int16_t)best_i;
+                  }
+                  tok = 0;
+                  ++smp;
+                }
+              }
+            }
+          }
+        } else {  // EPI_LSE
+          const int ncols = min(p.n_step, p.n_rows - n0);
+          const long long label = p.label_offset + row;
+          const long long wl0 = p.label_offset + m_tile * UM_BM + quad * 32;  // labels of this warp: [wl0, wl0+32)
+          for (int c0 = 0; c0 < ncols; c0 += 32) {
+            uint32_t v[32];
+            tmem_ld32(taddr + c0, v);
+            tmem_ld_wait();
+            float t[32];
+            float cm = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              t[j] = (c0 + j < ncols) ? __uint_as_float(v[j]) * scale_log2 : -INFINITY;
+              cm = fmaxf(cm, t[j]);
+            }
+            const float nm = fmaxf(run_m, cm);
+            float s = 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) s += exp2f(t[j] - nm);
+            run_s = run_s * exp2f(run_m - nm) + s;
+            run_m = nm;
+            const long long cbeg = (long long)n0 + c0;
+            if (wl0 < cbeg + 32 && wl0 + 32 > cbeg) {  // warp-uniform: some label falls in this chunk
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (row_ok && cbeg + j == label && c0 + j < ncols) p.diag[row] = __uint_as_float(v[j]) * scale;
+            }
+          }
+        }
+        fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+      if (EPI == EPI_LSE && row_ok) {
+        p.part_m[(int64_t)chunk * p.m_rows + row] = run_m;
+        p.part_s[(int64_t)chunk * p.m_rows + row] = run_s;
+      }
+    }
+  }
+
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    fence_after_sync();
+    tmem_dealloc(tmem_base, UM_TMEM_COLS);
+  }
+}
+
+// lse[r] = ln2 * (M + log2(sum_c s_c * 2^(m_c - M)))
+__global__ void lse_combine_kernel(const float* __restrict__ part_m, const float* __restrict__ part_s, int nchunk,
+                                   int64_t rows, float* __restrict__ lse) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  float M = -INFINITY;
+  for (int c = 0; c < nchunk; ++c) M = fmaxf(M, part_m[(int64_t)c * rows + r]);
+  float s = 0.f;
+  for (int c = 0; c < nchunk; ++c) s += part_s[(int64_t)c * rows + r] * exp2f(part_m[(int64_t)c * rows + r] - M);
+  lse[r] = 0.6931471805599453f * (M + log2f(s));
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(f);
+  });
+  return fn;
+}
+
+int32_t make_tmap_bf16(CUtensorMap* out, const void* base, int64_t rows, int64_t inner, int64_t row_stride_elems,
+                       int box_rows) {
+  PFN_encodeTiled enc = get_encode_fn();
+  ILFDT_REQUIRE(enc != nullptr, ILFDT_E_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  ILFDT_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (row_stride_elems * 2) % 16 == 0,
+                ILFDT_E_INVALID_ARG, "TMA operand must be 16-byte aligned with a 16-byte multiple row pitch");
+  ILFDT_REQUIRE(box_rows >= 1 && box_rows <= 256, ILFDT_E_INVALID_ARG, "TMA box rows %d out of range", box_rows);
+  cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)rows};
+  cuuint64_t gstr[1] = {(cuuint64_t)row_stride_elems * 2};
+  cuuint32_t box[2] = {(cuuint32_t)UM_BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  ILFDT_REQUIRE(r == CUDA_SUCCESS, ILFDT_E_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return ILFDT_OK;
+}
+
+// Pick the number of B-tile chunks so that (A tiles x chunks) fills the persistent grid evenly while
+// each item still amortises its resident A tile over several B tiles.
+static void plan_items(int num_m_tiles, int num_n_tiles, int sms, int& nchunk, int& tiles_per_chunk) {
+  int best_c = 1;
+  double best_eff = -1.0;
+  const int max_c = std::max(1, std::min(num_n_tiles, 4096));
+  for (int c = 1; c <= max_c; ++c) {
+    const int tpc = (int)cdiv(num_n_tiles, c);
+    const int real_c = (int)cdiv(num_n_tiles, tpc);
+    const int64_t items = (int64_t)num_m_tiles * real_c;
+    const int64_t waves = cdiv(items, sms);
+    double eff = (double)items / (double)(waves * sms);
+    // every item pays one A-tile load (~8 B-tile-stages worth): prefer longer items
+    eff *= (double)tpc / (double)(tpc + 0.5);
+    if (eff > best_eff + 1e-9) { best_eff = eff; best_c = real_c; }
+    if (tpc == 1) break;
+  }
+  nchunk = best_c;
+  tiles_per_chunk = (int)cdiv(num_n_tiles, nchunk);
+  nchunk = (int)cdiv(num_n_tiles, tiles_per_chunk);
+}
+
+template <int EPI, bool A_RES>
+static int32_t launch_umma_t(const CUtensorMap& tmA, const CUtensorMap& tmB, const UmmaParams& p, cudaStream_t st) {
+  static thread_local int configured_dev = -1;
+  int dev = 0;
+  ILFDT_CUDA_OK(cudaGetDevice(&dev));
+  if (configured_dev != dev) {
+    ILFDT_CUDA_OK(cudaFuncSetAttribute(umma_kernel<EPI, A_RES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       UM_SMEM_BYTES));
+    configured_dev = dev;
+  }
+  const int items = p.num_m_tiles * p.nchunk;
+  const int grid = std::min(items, sm_count());
+  umma_kernel<EPI, A_RES><<<grid, UM_THREADS, UM_SMEM_BYTES, st>>>(tmA, tmB, p);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
+template <int EPI>
+static int32_t launch_umma(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, UmmaParams& p,
+                           cudaStream_t st) {
+  ILFDT_REQUIRE(Kr % 8 == 0 && Kr >= 8, ILFDT_E_UNSUPPORTED_SHAPE, "tensor-core path needs Kr %% 8 == 0 (Kr=%lld)",
+                (long long)Kr);
+  ILFDT_REQUIRE(M < (1ll << 31) && N < (1ll << 31), ILFDT_E_UNSUPPORTED_SHAPE, "dimension too large");
+  ILFDT_REQUIRE(p.block_n % 16 == 0 && p.block_n >= 16 && p.block_n <= 256 && p.n_step <= p.block_n,
+                ILFDT_E_INVALID_ARG, "bad block_n %d / n_step %d", p.block_n, p.n_step);
+  p.m_rows = (int)M;
+  p.n_rows = (int)N;
+  p.nkb = (int)cdiv(Kr, UM_BK);
+  p.num_m_tiles = (int)cdiv(M, UM_BM);
+  p.num_n_tiles = (int)cdiv(N, p.n_step);
+  p.idesc = make_idesc_bf16(UM_BM, p.block_n);
+  const bool a_res = p.nkb <= 8;
+  if (p.nchunk <= 0) {
+    if (a_res) plan_items(p.num_m_tiles, p.num_n_tiles, sm_count(), p.nchunk, p.tiles_per_chunk);
+    else { p.nchunk = p.num_n_tiles; p.tiles_per_chunk = 1; }
+  }
+  CUtensorMap tmA, tmB;
+  int32_t rc = make_tmap_bf16(&tmA, A, M, Kr, Kr, UM_BM);
+  if (rc != ILFDT_OK) return rc;
+  rc = make_tmap_bf16(&tmB, B, N, Kr, Kr, p.block_n);
+  if (rc != ILFDT_OK) return rc;
+  return a_res ? launch_umma_t<EPI, true>(tmA, tmB, p, st) : launch_umma_t<EPI, false>(tmA, tmB, p, st);
+}
+
+int32_t launch_gemm_nt_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha,
+                            const float* alpha_dev, int accumulate, float* out, int64_t ldo, cudaStream_t st) {
+  if (M == 0 || N == 0) return ILFDT_OK;
+  UmmaParams p{};
+  p.block_n = (int)std::min<int64_t>(256, round_up(N, 16));
+  p.n_step = p.block_n;
+  p.out = out;
+  p.ldo = ldo;
+  p.alpha = alpha;
+  p.alpha_dev = alpha_dev;
+  p.accumulate = accumulate;
+  return launch_umma<EPI_STORE_T>(A, B, M, N, Kr, p, st);
+}
+
+int32_t launch_ground_fwd_bf16(const void* q, const void* sd, const float* mask, int64_t b, int64_t n_tok, int64_t K,
+                               int64_t D, float sqrt_d, float temperature, float* pooled, int16_t* arg,
+                               cudaStream_t st) {
+  if (b == 0) return ILFDT_OK;
+  ILFDT_REQUIRE(n_tok >= 1 && n_tok <= 256, ILFDT_E_UNSUPPORTED_SHAPE,
+                "ground_fwd(bf16): n_tok=%lld not in [1,256] (use the fp32 path)", (long long)n_tok);
+  ILFDT_REQUIRE(D <= 512 && D % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "ground_fwd(bf16): D=%lld must be <= 512, %% 8",
+                (long long)D);
+  ILFDT_REQUIRE(b * n_tok < (1ll << 31), ILFDT_E_UNSUPPORTED_SHAPE, "ground_fwd(bf16): b*n_tok too large");
+  UmmaParams p{};
+  p.spt = (int)std::min<int64_t>(256 / n_tok, b);
+  p.n_step = p.spt * (int)n_tok;
+  p.block_n = (int)round_up(p.n_step, 16);
+  p.mask = mask;
+  p.n_tok = (int)n_tok;
+  p.n_samples = (int)b;
+  p.pool_scale = 1.f / (sqrt_d * temperature);
+  p.pooled = pooled;
+  p.arg = arg;
+  return launch_umma<EPI_POOLMAX>(sd, q, K, b * n_tok, D, p, st);
+}
+
+int64_t nce_fwd_bf16_ws_bytes(int64_t b, int64_t B) {
+  // partial (m, s) per (chunk, row) for both directions; chunks <= number of B tiles
+  const int64_t max_chunks = cdiv(B, 256);
+  return 2 * 2 * max_chunks * b * 4 + 256;
+}
+
+int32_t launch_nce_fwd_bf16(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt, int64_t b,
+                            int64_t B, int64_t D, const float* scale, int64_t label_offset, float* lse_i, float* lse_t,
+                            float* diag_i, float* diag_t, void* ws, int64_t ws_bytes, cudaStream_t st) {
+  ILFDT_REQUIRE(D <= 512 && D % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "nce_fwd(bf16): D=%lld must be <= 512, %% 8",
+                (long long)D);
+  ILFDT_REQUIRE(ws != nullptr && ws_bytes >= nce_fwd_bf16_ws_bytes(b, B), ILFDT_E_INVALID_ARG,
+                "nce_fwd(bf16): workspace too small");
+  const int64_t max_chunks = cdiv(B, 256);
+  float* part = reinterpret_cast<float*>(ws);
+  for (int dir = 0; dir < 2; ++dir) {
+    UmmaParams p{};
+    p.block_n = (int)std::min<int64_t>(256, round_up(B, 16));
+    p.n_step = p.block_n;
+    p.scale_dev = scale;
+    p.label_offset = label_offset;
+    p.part_m = part + (int64_t)dir * 2 * max_chunks * b;
+    p.part_s = p.part_m + max_chunks * b;
+    p.diag = dir == 0 ? diag_i : diag_t;
+    // logits_per_image = x_img . g_txt^T ; logits_per_text = x_txt . g_img^T  (clip_fdt.py:421-422)
+    int32_t rc = launch_umma<EPI_LSE>(dir == 0 ? x_img : x_txt, dir == 0 ? g_txt : g_img, b, B, D, p, st);
+    if (rc != ILFDT_OK) return rc;
+    lse_combine_kernel<<<(unsigned)cdiv(b, 256), 256, 0, st>>>(p.part_m, p.part_s, p.nchunk, b,
+                                                              dir == 0 ? lse_i : lse_t);
+    ILFDT_LAUNCH_OK();
+  }
+  return ILFDT_OK;
+}
+
+}  // namespace ilfdt

@@ -1,0 +1,59 @@
+// Internal launch entry points (host side). Each returns an ILFDT_* status.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ilfdt {
+
+// kernels_simt.cu
+int32_t launch_gemm_f32(const float* A, int64_t a_rs, int64_t a_cs, const float* B, int64_t b_rs, int64_t b_cs,
+                        float* C, int64_t c_rs, int64_t c_cs, int64_t M, int64_t N, int64_t Kr, float alpha,
+                        const float* alpha_dev, int accumulate, cudaStream_t st);
+int32_t launch_ground_fwd_f32(const float* q, const float* sd, const float* mask, int64_t b, int64_t n_tok,
+                              int64_t K, int64_t D, float sqrt_d, float temperature, int pool_type, float* pooled,
+                              int16_t* arg, void* ws, int64_t ws_bytes, cudaStream_t st);
+int32_t launch_l2norm_fwd(const float* f, int64_t rows, int64_t D, float eps, float* x, void* xb, float* norm,
+                          cudaStream_t st);
+int32_t launch_l2norm_bwd(const float* x, const float* norm, const float* g, int64_t rows, int64_t D, float eps,
+                          float* df, cudaStream_t st);
+int32_t launch_lse_rows(const float* L, int64_t ld, int64_t rows, int64_t cols, int64_t label0, float* lse,
+                        float* diag, cudaStream_t st);
+int32_t launch_softmax_grad_rows(const float* L, float* out, int64_t ld, int64_t rows, int64_t cols, int64_t label0, const float* lse,
+                                 const float* go, float coef, const float* scale_dev, float* dscale_acc, cudaStream_t st);
+int32_t launch_nce_loss(const float* lse_i, const float* diag_i, const float* lse_t, const float* diag_t, int64_t b,
+                        float* loss, cudaStream_t st);
+int32_t launch_topk_hits(const float* L, int64_t b, int64_t B, int64_t label0, int32_t* counts, cudaStream_t st);
+int32_t launch_cast_bf16(const float* src, void* dst, int64_t n, cudaStream_t st);
+int32_t launch_transpose_bf16(const void* src, int src_dtype, int64_t rows, int64_t cols, void* dst, cudaStream_t st);
+int32_t launch_randn_fill(float* dst, int64_t n, uint64_t seed, uint32_t gen, cudaStream_t st);
+
+// sparsemax.cu
+int32_t launch_sparsemax_fwd(const float* z, int64_t rows, int64_t K, float* w, void* wb, float* tau, int32_t* nnz,
+                             cudaStream_t st);
+int32_t launch_sparsemax_bwd(const float* w, const float* g, int64_t rows, int64_t K, float* dz, cudaStream_t st);
+
+// ground_bwd.cu
+int32_t launch_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd, int dtype,
+                          const float* mask, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
+                          float temperature, float* dq, float* dsd, cudaStream_t st);
+
+// gemm_umma.cu (tcgen05)
+int32_t launch_gemm_nt_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha,
+                            const float* alpha_dev, int accumulate, float* out, int64_t ldo, cudaStream_t st);
+int32_t launch_ground_fwd_bf16(const void* q, const void* sd, const float* mask, int64_t b, int64_t n_tok, int64_t K,
+                               int64_t D, float sqrt_d, float temperature, float* pooled, int16_t* arg,
+                               cudaStream_t st);
+int64_t nce_fwd_bf16_ws_bytes(int64_t b, int64_t B);
+int32_t launch_nce_fwd_bf16(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt, int64_t b,
+                            int64_t B, int64_t D, const float* scale, int64_t label_offset, float* lse_i, float* lse_t,
+                            float* diag_i, float* diag_t, void* ws, int64_t ws_bytes, cudaStream_t st);
+
+// nce_bwd_umma.cu (tcgen05)
+int64_t nce_bwd_bf16_ws_bytes(int64_t b, int64_t B, int64_t D);
+int32_t launch_nce_bwd_bf16(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt,
+                            const void* x_img_t, const void* x_txt_t, const void* g_img_t, const void* g_txt_t,
+                            int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset, const float* lse_i,
+                            const float* lse_t, const float* grad_out, float* dx_img, float* dx_txt, float* dg_img,
+                            float* dg_txt, float* dscale, void* ws, int64_t ws_bytes, cudaStream_t st);
+
+}  // namespace ilfdt

@@ -1,0 +1,389 @@
+// a13 (loss part): fused InfoNCE backward on tcgen05 -- the [b, B] logits / probabilities are
+// recomputed tile by tile in TMEM and consumed on-chip; they never reach HBM.
+//
+// One kernel, launched four times per step (dX_img, dG_txt, dX_txt, dG_img). Per launch:
+//   "lane" matrix  XL [RL, D]  (its 128-row tiles are the TMEM lanes; the gradient is w.r.t. XL)
+//   "stream" matrix Y  [RS, D]  (rows streamed 64 at a time) and its transpose YT [D, RS]
+//   S[i, j]   = XL[i,:] . Y[j,:]                      MMA1  128 x 64 x D      -> TMEM (double buffered)
+//   P[i, j]   = (exp(scale*S - lse) - [i ~ j]) * gw     softmax warps: TMEM -> regs -> bf16 -> smem (SW128)
+//   dOut[i,:] += P[i, j-block] . YT[:, j-block]^T       MMA2  128 x 256 x 64    -> TMEM (256 columns)
+//   dOut      *= scale                                  epilogue
+// lse is indexed by the lane row (dX launches: lane = local logits row) or by the stream row (dG
+// launches: lane = gathered row, stream = local logits row). A CTA owns (lane tile, 256-wide half of
+// D, slice of the stream range); S is recomputed for each half (TMEM holds 512 columns: 256 for dOut
+// + 2 x 64 for S).  The MMA thread software-pipelines MMA1(t+1) ahead of MMA2(t) so the tensor pipe
+// stays busy while the softmax warps convert tile t.
+#include "umma.cuh"
+#include "launch.h"
+#include <algorithm>
+
+namespace ilfdt {
+
+using namespace umma;
+
+constexpr int NB_THREADS = 192;
+constexpr int NB_XL_BYTES = 8 * 16384;          // lane tile, all k-blocks: 128 KB
+constexpr int NB_Y_STAGE = 64 * 64 * 2;         // 64 stream rows x 64 k      : 8 KB
+constexpr int NB_Y_STAGES = 2;
+constexpr int NB_P_BYTES = 128 * 64 * 2;        // P tile 128 lanes x 64 stream: 16 KB
+constexpr int NB_YT_STAGE = 256 * 64 * 2;       // 256 D-columns x 64 stream   : 32 KB
+constexpr int NB_YT_STAGES = 2;
+constexpr int NB_OFF_Y = NB_XL_BYTES;
+constexpr int NB_OFF_P = NB_OFF_Y + NB_Y_STAGES * NB_Y_STAGE;
+constexpr int NB_OFF_YT = NB_OFF_P + NB_P_BYTES;
+constexpr int NB_OFF_BARS = NB_OFF_YT + NB_YT_STAGES * NB_YT_STAGE;  // 229376
+constexpr int NB_SMEM_BYTES = NB_OFF_BARS + 1024 + 1024;
+constexpr int NB_TMEM_COLS = 512;
+constexpr int NB_TMEM_S = 256;  // S buffers at columns 256 and 320
+
+struct NceBwdParams {
+  int RL, RS, D;
+  int nkb;              // ceil(D / 64)
+  int num_lane_tiles, num_halves, nsplit, tiles_per_split, num_stream_tiles;
+  int lse_by_lane;      // 1: lse[lane row], label(lane i) = stream label_offset + i
+                        // 0: lse[stream row], label(stream j) = lane label_offset + j
+  long long label_offset;
+  const float* lse;
+  const float* grad_out;
+  float inv_2b;
+  const float* scale_dev;
+  float* out;           // [RL, D]
+  int use_atomic;
+  float* dscale;        // accumulated only by lse_by_lane launches, half 0
+  uint32_t idesc1, idesc2;
+};
+
+struct NceBwdBars {
+  uint64_t xl_full, xl_empty;
+  uint64_t y_full[NB_Y_STAGES], y_empty[NB_Y_STAGES];
+  uint64_t yt_full[NB_YT_STAGES], yt_empty[NB_YT_STAGES];
+  uint64_t s_full[2], s_empty[2];
+  uint64_t p_full, p_empty;
+  uint64_t d_full, d_empty;
+  uint32_t tmem_ptr;
+  float lse_s[2][64];
+};
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__global__ void __launch_bounds__(NB_THREADS, 1)
+nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__ CUtensorMap tmY,
+               const __grid_constant__ CUtensorMap tmYT, const NceBwdParams p) {
+  extern __shared__ uint8_t nb_smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(nb_smem_raw) + 1023) & ~(uintptr_t)1023);
+  NceBwdBars* bars = reinterpret_cast<NceBwdBars*>(smem + NB_OFF_BARS);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_items = p.num_lane_tiles * p.num_halves * p.nsplit;
+
+  if (threadIdx.x == 0) {
+    mbar_init(&bars->xl_full, 1);
+    mbar_init(&bars->xl_empty, 1);
+    for (int i = 0; i < NB_Y_STAGES; ++i) { mbar_init(&bars->y_full[i], 1); mbar_init(&bars->y_empty[i], 1); }
+    for (int i = 0; i < NB_YT_STAGES; ++i) { mbar_init(&bars->yt_full[i], 1); mbar_init(&bars->yt_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&bars->s_full[i], 1); mbar_init(&bars->s_empty[i], 4); }
+    mbar_init(&bars->p_full, 4);
+    mbar_init(&bars->p_empty, 1);
+    mbar_init(&bars->d_full, 1);
+    mbar_init(&bars->d_empty, 4);
+    fence_barrier_init();
+    tma_prefetch_desc(&tmXL);
+    tma_prefetch_desc(&tmY);
+    tma_prefetch_desc(&tmYT);
+  }
+  if (warp == 1) {
+    tmem_alloc(&bars->tmem_ptr, NB_TMEM_COLS);
+    tmem_relinquish();
+  }
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem_base = bars->tmem_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      uint32_t ys = 0, yph = 0, ts = 0, tph = 0, it = 0;
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
+        const int split = item % p.nsplit, lh = item / p.nsplit;
+        const int half = lh % p.num_halves, lt = lh / p.num_halves;
+        const int t_begin = split * p.tiles_per_split, t_end = min(p.num_stream_tiles, t_begin + p.tiles_per_split);
+        mbar_wait(&bars->xl_empty, (it & 1) ^ 1);
+        mbar_expect_tx(&bars->xl_full, (uint32_t)p.nkb * 16384u);
+        for (int kb = 0; kb < p.nkb; ++kb)
+          tma_load_2d(smem + kb * 16384, &tmXL, &bars->xl_full, kb * 64, lt * 128, kEvictLast);
+        for (int t = t_begin; t < t_end; ++t) {
+          for (int kb = 0; kb < p.nkb; ++kb) {
+            mbar_wait(&bars->y_empty[ys], yph ^ 1);
+            mbar_expect_tx(&bars->y_full[ys], NB_Y_STAGE);
+            tma_load_2d(smem + NB_OFF_Y + ys * NB_Y_STAGE, &tmY, &bars->y_full[ys], kb * 64, t * 64, kEvictNormal);
+            if (++ys == NB_Y_STAGES) { ys = 0; yph ^= 1; }
+          }
+          mbar_wait(&bars->yt_empty[ts], tph ^ 1);
+          mbar_expect_tx(&bars->yt_full[ts], NB_YT_STAGE);
+          tma_load_2d(smem + NB_OFF_YT + ts * NB_YT_STAGE, &tmYT, &bars->yt_full[ts], t * 64, half * 256,
+                      kEvictNormal);
+          if (++ts == NB_YT_STAGES) { ts = 0; tph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (elect_one()) {
+      uint32_t ys = 0, yph = 0, ts = 0, tph = 0, it = 0;
+      uint32_t tile_ctr = 0;  // global count of S tiles issued by this CTA (S buffer = ctr & 1)
+      uint32_t p_ctr = 0;     // global count of MMA2 issued (P buffer phases)
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
+        const int split = item % p.nsplit;
+        const int t_begin = split * p.tiles_per_split, t_end = min(p.num_stream_tiles, t_begin + p.tiles_per_split);
+        const int ntile = t_end - t_begin;
+        mbar_wait(&bars->xl_full, it & 1);
+        mbar_wait(&bars->d_empty, (it & 1) ^ 1);  // epilogue of the previous item drained dOut
+        fence_after_sync();
+        for (int i = 0; i <= ntile; ++i) {
+          if (i < ntile) {
+            // ---- MMA1: S tile i ----
+            const uint32_t sb = tile_ctr & 1, sph = (tile_ctr >> 1) & 1;
+            mbar_wait(&bars->s_empty[sb], sph ^ 1);
+            fence_after_sync();
+            const uint32_t tmem_s = tmem_base + NB_TMEM_S + sb * 64;
+            for (int kb = 0; kb < p.nkb; ++kb) {
+              mbar_wait(&bars->y_full[ys], yph);
+              fence_after_sync();
+              const uint64_t adesc = make_smem_desc_sw128(smem_u32(smem + kb * 16384));
+              const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smem + NB_OFF_Y + ys * NB_Y_STAGE));
+#pragma unroll
+              for (int k4 = 0; k4 < 4; ++k4)
+                mma_f16(tmem_s, advance_desc_k(adesc, k4 * 32), advance_desc_k(bdesc, k4 * 32), p.idesc1,
+                        (kb | k4) != 0 ? 1u : 0u);
+              mma_commit(&bars->y_empty[ys]);
+              if (++ys == NB_Y_STAGES) { ys = 0; yph ^= 1; }
+            }
+            mma_commit(&bars->s_full[sb]);
+            ++tile_ctr;
+          }
+          if (i > 0) {
+            // ---- MMA2: dOut += P(tile i-1) . YT(tile i-1)^T ----
+            mbar_wait(&bars->p_full, p_ctr & 1);
+            mbar_wait(&bars->yt_full[ts], tph);
+            fence_after_sync();
+            const uint64_t adesc = make_smem_desc_sw128(smem_u32(smem + NB_OFF_P));
+            const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smem + NB_OFF_YT + ts * NB_YT_STAGE));
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4)
+              mma_f16(tmem_base, advance_desc_k(adesc, k4 * 32), advance_desc_k(bdesc, k4 * 32), p.idesc2,
+                      (i > 1 || k4 != 0) ? 1u : 0u);
+            mma_commit(&bars->p_empty);
+            mma_commit(&bars->yt_empty[ts]);
+            if (++ts == NB_YT_STAGES) { ts = 0; tph ^= 1; }
+            ++p_ctr;
+          }
+        }
+        mma_commit(&bars->d_full);
+        mma_commit(&bars->xl_empty);
+      }
+    }
+  } else {
+    // ===================== softmax + epilogue warps (2..5) =====================
+    const int quad = warp & 3;
+    const int tid128 = (warp - 2) * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    const int r_in_tile = quad * 32 + lane;
+    const float gw = __ldg(p.grad_out) * p.inv_2b;
+    const float scale = __ldg(p.scale_dev);
+    const float scale_log2 = scale * 1.4426950408889634f;
+    uint32_t tile_ctr = 0, p_ctr = 0, it = 0;
+    uint8_t* p_row = smem + NB_OFF_P + r_in_tile * 128;
+    const int sw = r_in_tile & 7;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
+      const int split = item % p.nsplit, lh = item / p.nsplit;
+      const int half = lh % p.num_halves, lt = lh / p.num_halves;
+      const int t_begin = split * p.tiles_per_split, t_end = min(p.num_stream_tiles, t_begin + p.tiles_per_split);
+      const int row = lt * 128 + r_in_tile;
+      const bool row_ok = row < p.RL;
+      const float lse_lane = (p.lse_by_lane && row_ok) ? __ldg(p.lse + row) * 1.4426950408889634f : 0.f;
+      float ds_acc = 0.f;
+      for (int t = t_begin; t < t_end; ++t) {
+        const uint32_t sb = tile_ctr & 1, sph = (tile_ctr >> 1) & 1;
+        const int j0 = t * 64;
+        if (!p.lse_by_lane) {
+          if (tid128 < 64) bars->lse_s[sb][tid128] = (j0 + tid128 < p.RS) ? __ldg(p.lse + j0 + tid128) * 1.4426950408889634f : 0.f;
+          named_bar_sync(1, 128);
+        }
+        mbar_wait(&bars->s_full[sb], sph);
+        fence_after_sync();
+        uint32_t v0[32], v1[32];
+        tmem_ld32(tmem_base + lane_addr + NB_TMEM_S + sb * 64, v0);
+        tmem_ld32(tmem_base + lane_addr + NB_TMEM_S + sb * 64 + 32, v1);
+        tmem_ld_wait();
+        fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->s_empty[sb]);
+        ++tile_ctr;
+
+        // label column (stream index) matching this lane row, or -1
+        long long jl;
+        if (p.lse_by_lane) jl = p.label_offset + row;  // stream j == label_offset + lane row
+        else jl = (long long)row - p.label_offset;     // lane row == label_offset + stream j
+        uint32_t packed[32];
+#pragma unroll
+        for (int h2 = 0; h2 < 2; ++h2) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            float pv[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              const int jj = h2 * 32 + j + e;
+              const float s_raw = __uint_as_float(h2 == 0 ? v0[j + e] : v1[j + e]);
+              const float l2 = p.lse_by_lane ? lse_lane : bars->lse_s[sb][jj];
+              float pr = exp2f(fmaf(s_raw, scale_log2, -l2));
+              pr -= ((long long)(j0 + jj) == jl) ? 1.f : 0.f;
+              pr *= gw;
+              pr = (j0 + jj < p.RS) ? pr : 0.f;
+              ds_acc = fmaf(pr, s_raw, ds_acc);
+              pv[e] = pr;
+            }
+            __nv_bfloat162 b2 = __floats2bfloat162_rn(pv[0], pv[1]);
+            packed[h2 * 16 + (j >> 1)] = *reinterpret_cast<uint32_t*>(&b2);
+          }
+        }
+        // P buffer free? (MMA2 of the previous tile finished reading it)
+        mbar_wait(&bars->p_empty, (p_ctr & 1) ^ 1);
+        // 8 chunks of 16 B (8 bf16 each), 128-byte swizzle: chunk c of row r lives at c ^ (r & 7)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          uint4 val = make_uint4(packed[c * 4], packed[c * 4 + 1], packed[c * 4 + 2], packed[c * 4 + 3]);
+          *reinterpret_cast<uint4*>(p_row + ((c ^ sw) << 4)) = val;
+        }
+        fence_proxy_async_smem();  // make the generic-proxy writes visible to the tensor core (async proxy)
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->p_full);
+        ++p_ctr;
+      }
+      // ---- epilogue: dOut (TMEM columns 0..255) -> global ----
+      mbar_wait(&bars->d_full, it & 1);
+      fence_after_sync();
+      const int dcols = min(256, p.D - half * 256);
+      for (int c0 = 0; c0 < dcols; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + lane_addr + c0, v);
+        tmem_ld_wait();
+        if (row_ok) {
+          float* o = p.out + (int64_t)row * p.D + half * 256 + c0;
+          if (p.use_atomic) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (c0 + j < dcols) atomicAdd(o + j, __uint_as_float(v[j]) * scale);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              if (c0 + j + 3 < dcols) {
+                *reinterpret_cast<float4*>(o + j) =
+                    make_float4(__uint_as_float(v[j]) * scale, __uint_as_float(v[j + 1]) * scale,
+                                __uint_as_float(v[j + 2]) * scale, __uint_as_float(v[j + 3]) * scale);
+              } else {
+                for (int e = 0; e < 4; ++e)
+                  if (c0 + j + e < dcols) o[j + e] = __uint_as_float(v[j + e]) * scale;
+              }
+            }
+          }
+        }
+      }
+      fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars->d_empty);
+      if (p.dscale != nullptr && half == 0) {
+        float s = row_ok ? ds_acc : 0.f;
+        s = warp_sum(s);
+        if (lane == 0) atomicAdd(p.dscale, s);
+      }
+    }
+  }
+
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    fence_after_sync();
+    tmem_dealloc(tmem_base, NB_TMEM_COLS);
+  }
+}
+
+int64_t nce_bwd_bf16_ws_bytes(int64_t b, int64_t B, int64_t D) {
+  (void)b; (void)B; (void)D;
+  return 256;
+}
+
+static int32_t launch_one(const void* XL, const void* Y, const void* YT, int64_t RL, int64_t RS, int64_t D,
+                          int lse_by_lane, int64_t label_offset, const float* lse, const float* grad_out, float inv_2b,
+                          const float* scale, float* out, float* dscale, cudaStream_t st) {
+  NceBwdParams p{};
+  p.RL = (int)RL; p.RS = (int)RS; p.D = (int)D;
+  p.nkb = (int)cdiv(D, 64);
+  p.num_lane_tiles = (int)cdiv(RL, 128);
+  p.num_halves = (int)cdiv(D, 256);
+  p.num_stream_tiles = (int)cdiv(RS, 64);
+  const int base_items = p.num_lane_tiles * p.num_halves;
+  const int sms = sm_count();
+  int nsplit = 1;
+  if (base_items < sms) nsplit = std::min<int>(p.num_stream_tiles, std::max<int>(1, (sms + base_items - 1) / base_items));
+  p.tiles_per_split = (int)cdiv(p.num_stream_tiles, nsplit);
+  p.nsplit = (int)cdiv(p.num_stream_tiles, p.tiles_per_split);
+  p.lse_by_lane = lse_by_lane;
+  p.label_offset = label_offset;
+  p.lse = lse;
+  p.grad_out = grad_out;
+  p.inv_2b = inv_2b;
+  p.scale_dev = scale;
+  p.out = out;
+  p.use_atomic = p.nsplit > 1 ? 1 : 0;
+  p.dscale = dscale;
+  p.idesc1 = make_idesc_bf16(128, 64);
+  p.idesc2 = make_idesc_bf16(128, 256);
+  if (p.use_atomic) ILFDT_CUDA_OK(cudaMemsetAsync(out, 0, (size_t)RL * D * 4, st));
+  CUtensorMap tmXL, tmY, tmYT;
+  int32_t rc = make_tmap_bf16(&tmXL, XL, RL, D, D, 128);
+  if (rc != ILFDT_OK) return rc;
+  rc = make_tmap_bf16(&tmY, Y, RS, D, D, 64);
+  if (rc != ILFDT_OK) return rc;
+  rc = make_tmap_bf16(&tmYT, YT, D, RS, RS, 256);
+  if (rc != ILFDT_OK) return rc;
+  static thread_local int configured_dev = -1;
+  int dev = 0;
+  ILFDT_CUDA_OK(cudaGetDevice(&dev));
+  if (configured_dev != dev) {
+    ILFDT_CUDA_OK(cudaFuncSetAttribute(nce_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NB_SMEM_BYTES));
+    configured_dev = dev;
+  }
+  const int items = base_items * p.nsplit;
+  nce_bwd_kernel<<<std::min(items, sms), NB_THREADS, NB_SMEM_BYTES, st>>>(tmXL, tmY, tmYT, p);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
+int32_t launch_nce_bwd_bf16(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt,
+                            const void* x_img_t, const void* x_txt_t, const void* g_img_t, const void* g_txt_t,
+                            int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset, const float* lse_i,
+                            const float* lse_t, const float* grad_out, float* dx_img, float* dx_txt, float* dg_img,
+                            float* dg_txt, float* dscale, void* ws, int64_t ws_bytes, cudaStream_t st) {
+  (void)ws; (void)ws_bytes;
+  ILFDT_REQUIRE(D <= 512 && D % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "nce_bwd(bf16): D=%lld must be <= 512, %% 8",
+                (long long)D);
+  ILFDT_REQUIRE(b % 8 == 0 && B % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE,
+                "nce_bwd(bf16): b and B must be multiples of 8 (TMA row pitch of the transposed operands)");
+  ILFDT_CUDA_OK(cudaMemsetAsync(dscale, 0, 4, st));
+  const float inv_2b = 1.f / (2.f * (float)b);
+  int32_t rc;
+  // logits_per_image = x_img . g_txt^T : dX_img (lse_i by lane), dG_txt (lse_i by stream)
+  rc = launch_one(x_img, g_txt, g_txt_t, b, B, D, 1, label_offset, lse_i, grad_out, inv_2b, scale, dx_img, dscale, st);
+  if (rc != ILFDT_OK) return rc;
+  rc = launch_one(g_txt, x_img, x_img_t, B, b, D, 0, label_offset, lse_i, grad_out, inv_2b, scale, dg_txt, nullptr, st);
+  if (rc != ILFDT_OK) return rc;
+  // logits_per_text = x_txt . g_img^T : dX_txt (lse_t by lane), dG_img (lse_t by stream)
+  rc = launch_one(x_txt, g_img, g_img_t, b, B, D, 1, label_offset, lse_t, grad_out, inv_2b, scale, dx_txt, dscale, st);
+  if (rc != ILFDT_OK) return rc;
+  rc = launch_one(g_img, x_txt, x_txt_t, B, b, D, 0, label_offset, lse_t, grad_out, inv_2b, scale, dg_img, nullptr, st);
+  return rc;
+}
+
+}  // namespace ilfdt

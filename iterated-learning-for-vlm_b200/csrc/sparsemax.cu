@@ -1,0 +1,173 @@
+// a2: Sparsemax forward / backward (prototype/model/sparsemax.py:22-71).
+//
+// The reference sorts each row (O(K log K) radix sort + cumsum + ~8 elementwise passes). The
+// simplex projection only needs the threshold tau with sum(max(0, z - tau)) = 1, so here one CTA
+// per row stages the row in shared memory (one HBM read), subtracts the row max (sparsemax.py:40),
+// and runs Michelot's fixed-point iteration tau <- (sum_{z>tau} z - 1) / |{z>tau}| with fp64
+// block reductions (finite, monotone, converges to the same tau the sorted-prefix rule of
+// sparsemax.py:50-59 defines), then writes max(0, z - tau) (one HBM write).
+// Algorithmic bytes: 8*K per row (read scores + write weights) -> HBM-bound.
+#include "common.cuh"
+#include "launch.h"
+
+namespace ilfdt {
+
+constexpr int SPX_THREADS = 512;
+
+struct SpxRed {
+  double s[SPX_THREADS / 32];
+  int c[SPX_THREADS / 32];
+  float f[SPX_THREADS / 32];
+};
+
+__device__ __forceinline__ float block_max(float v, SpxRed& r) {
+  v = warp_max(v);
+  if ((threadIdx.x & 31) == 0) r.f[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float m = r.f[0];
+#pragma unroll
+  for (int w = 1; w < SPX_THREADS / 32; ++w) m = fmaxf(m, r.f[w]);
+  __syncthreads();
+  return m;
+}
+
+__device__ __forceinline__ void block_sum_cnt(double& s, int& c, SpxRed& r) {
+  s = warp_sum(s);
+  c = warp_sum(c);
+  if ((threadIdx.x & 31) == 0) { r.s[threadIdx.x >> 5] = s; r.c[threadIdx.x >> 5] = c; }
+  __syncthreads();
+  double ts = 0.0;
+  int tc = 0;
+#pragma unroll
+  for (int w = 0; w < SPX_THREADS / 32; ++w) { ts += r.s[w]; tc += r.c[w]; }
+  __syncthreads();
+  s = ts;
+  c = tc;
+}
+
+__global__ void __launch_bounds__(SPX_THREADS)
+sparsemax_fwd_kernel(const float* __restrict__ z, int K, float* __restrict__ w,
+                     __nv_bfloat16* __restrict__ wb, float* __restrict__ tau_out, int* __restrict__ nnz_out) {
+  extern __shared__ float row[];
+  __shared__ SpxRed red;
+  const int64_t r = blockIdx.x;
+  const float* zr = z + r * K;
+  const bool vec = (K % 4 == 0) && ((reinterpret_cast<uintptr_t>(zr) & 15) == 0);
+
+  float mx = -INFINITY;
+  if (vec) {
+    for (int i = threadIdx.x * 4; i < K; i += SPX_THREADS * 4) {
+      float4 v = __ldg(reinterpret_cast<const float4*>(zr + i));
+      *reinterpret_cast<float4*>(row + i) = v;
+      mx = fmaxf(fmaxf(mx, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+    }
+  } else {
+    for (int i = threadIdx.x; i < K; i += SPX_THREADS) {
+      float v = __ldg(zr + i);
+      row[i] = v;
+      mx = fmaxf(mx, v);
+    }
+  }
+  mx = block_max(mx, red);  // also orders the smem writes (__syncthreads inside)
+
+  // z <- z - max (sparsemax.py:40), in fp32 like the reference; thread-private smem slots.
+  for (int i = threadIdx.x; i < K; i += SPX_THREADS) row[i] = row[i] - mx;
+  // (each thread only ever touches its own stride of `row` from here on -> no barrier needed)
+
+  // Michelot: start from the whole row active. tau is strictly increasing until the active set
+  // is stable; the count is the convergence test.
+  double tau = -INFINITY;
+  int cnt_prev = -1;
+  for (int it = 0; it < 256; ++it) {
+    double s = 0.0;
+    int c = 0;
+    const float tf = (float)tau;  // compare in the precision the output uses
+    for (int i = threadIdx.x; i < K; i += SPX_THREADS) {
+      float v = row[i];
+      if (it == 0 || v > tf) { s += (double)v; ++c; }
+    }
+    block_sum_cnt(s, c, red);
+    if (c == cnt_prev) break;
+    cnt_prev = c;
+    tau = (s - 1.0) / (double)c;
+  }
+  const float tf = (float)tau;
+  int nz = 0;
+  float* wr = w + r * K;
+  __nv_bfloat16* wbr = wb ? wb + r * K : nullptr;
+  // the subtraction loop wrote stride-1 slots; the vector pass below reads float4 groups.
+  __syncthreads();
+  if (vec) {
+    for (int i = threadIdx.x * 4; i < K; i += SPX_THREADS * 4) {
+      float4 v = *reinterpret_cast<const float4*>(row + i);
+      float4 o = make_float4(fmaxf(v.x - tf, 0.f), fmaxf(v.y - tf, 0.f), fmaxf(v.z - tf, 0.f),
+                             fmaxf(v.w - tf, 0.f));
+      nz += (o.x > 0.f) + (o.y > 0.f) + (o.z > 0.f) + (o.w > 0.f);
+      *reinterpret_cast<float4*>(wr + i) = o;
+      if (wbr) {
+        __nv_bfloat162 p[2] = {__floats2bfloat162_rn(o.x, o.y), __floats2bfloat162_rn(o.z, o.w)};
+        *reinterpret_cast<uint2*>(wbr + i) = *reinterpret_cast<uint2*>(p);
+      }
+    }
+  } else {
+    for (int i = threadIdx.x; i < K; i += SPX_THREADS) {
+      float o = fmaxf(row[i] - tf, 0.f);
+      nz += (o > 0.f);
+      wr[i] = o;
+      if (wbr) wbr[i] = __float2bfloat16_rn(o);
+    }
+  }
+  double dummy = 0.0;
+  block_sum_cnt(dummy, nz, red);
+  if (threadIdx.x == 0) {
+    if (tau_out) tau_out[r] = tf;
+    if (nnz_out) nnz_out[r] = nz;
+  }
+}
+
+// dz = nz * (g - mean_nz(g)). One CTA per row; g row cached in registers is not possible for
+// arbitrary K, so two passes (second one hits L2/L1).
+__global__ void __launch_bounds__(SPX_THREADS)
+sparsemax_bwd_kernel(const float* __restrict__ w, const float* __restrict__ g, int K, float* __restrict__ dz) {
+  __shared__ SpxRed red;
+  const int64_t r = blockIdx.x;
+  const float* wr = w + r * K;
+  const float* gr = g + r * K;
+  double s = 0.0;
+  int c = 0;
+  for (int i = threadIdx.x; i < K; i += SPX_THREADS)
+    if (wr[i] > 0.f) { s += (double)gr[i]; ++c; }
+  block_sum_cnt(s, c, red);
+  const float mean = c > 0 ? (float)(s / (double)c) : 0.f;
+  for (int i = threadIdx.x; i < K; i += SPX_THREADS) dz[r * K + i] = wr[i] > 0.f ? gr[i] - mean : 0.f;
+}
+
+int32_t launch_sparsemax_fwd(const float* z, int64_t rows, int64_t K, float* w, void* wb, float* tau, int32_t* nnz,
+                             cudaStream_t st) {
+  if (rows == 0) return ILFDT_OK;
+  ILFDT_REQUIRE(K >= 1 && K * 4 <= 200 * 1024, ILFDT_E_UNSUPPORTED_SHAPE,
+                "sparsemax: K=%lld does not fit one CTA's shared memory (max 51200)", (long long)K);
+  ILFDT_REQUIRE(rows < (1ll << 31), ILFDT_E_UNSUPPORTED_SHAPE, "sparsemax: too many rows");
+  size_t smem = (size_t)K * 4;
+  static thread_local int configured_dev = -1;
+  int dev = 0;
+  ILFDT_CUDA_OK(cudaGetDevice(&dev));
+  if (configured_dev != dev) {
+    ILFDT_CUDA_OK(cudaFuncSetAttribute(sparsemax_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       200 * 1024));
+    configured_dev = dev;
+  }
+  sparsemax_fwd_kernel<<<(unsigned)rows, SPX_THREADS, smem, st>>>(z, (int)K, w, reinterpret_cast<__nv_bfloat16*>(wb),
+                                                                  tau, nnz);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
+int32_t launch_sparsemax_bwd(const float* w, const float* g, int64_t rows, int64_t K, float* dz, cudaStream_t st) {
+  if (rows == 0) return ILFDT_OK;
+  sparsemax_bwd_kernel<<<(unsigned)rows, SPX_THREADS, 0, st>>>(w, g, (int)K, dz);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
+}  // namespace ilfdt

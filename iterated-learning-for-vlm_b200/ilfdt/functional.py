@@ -1,0 +1,234 @@
+"""torch.autograd.Function wrappers: each forward/backward is a handful of libilfdt calls. These are
+the seams between the reference-shaped nn.Modules (ilfdt.model, ilfdt.loss_functions) and the
+kernels. Reference lines cited are relative to the reference repo root."""
+import os
+
+import torch
+import torch.distributed as dist
+
+from . import ops
+
+# "bf16": tcgen05 tensor-core kernels, fp32 accumulation (<= 2e-2 rel vs the fp32 reference)
+# "fp32": SIMT fp32 kernels (<= 1e-5 rel) -- the parity mode
+_COMPUTE_DTYPE = os.environ.get("ILFDT_COMPUTE_DTYPE", "bf16")
+
+
+def set_compute_dtype(name):
+    global _COMPUTE_DTYPE
+    if name not in ("bf16", "fp32"):
+        raise ValueError("compute dtype must be 'bf16' or 'fp32'")
+    _COMPUTE_DTYPE = name
+
+
+def get_compute_dtype():
+    return _COMPUTE_DTYPE
+
+
+class compute_dtype:
+    """Context manager: with ilfdt.compute_dtype('fp32'): ..."""
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        self.prev = get_compute_dtype()
+        set_compute_dtype(self.name)
+
+    def __exit__(self, *a):
+        set_compute_dtype(self.prev)
+
+
+# bf16 copies of the codebook are shared by the two Query_models of one step
+_sd_cache = {}
+
+
+def _sd_bf16(sd):
+    key = (sd.data_ptr(), sd._version, tuple(sd.shape))
+    hit = _sd_cache.get("k")
+    if hit is not None and hit[0] == key:
+        return hit[1], hit[2]
+    sd_b = ops.cast_bf16(sd.detach())
+    sd_bt = ops.transpose_bf16(sd_b)
+    _sd_cache["k"] = (key, sd_b, sd_bt)
+    return sd_b, sd_bt
+
+
+class GroundingFunction(torch.autograd.Function):
+    """Query_model.forward from q onward (clip_fdt.py:113-157), sparsemax + max pooling:
+    (q [b,N,D], sd [K,D], mask [b,N] | None) -> (att_weight [b,K], att_ft [b,D])."""
+
+    @staticmethod
+    def forward(ctx, q, sd, mask, temperature, mode):
+        q = q.contiguous()
+        sd_c = sd.contiguous()
+        mask_f = None if mask is None else mask.to(torch.float32).contiguous()
+        if mode == "bf16":
+            q_k = ops.cast_bf16(q)
+            sd_k, sd_kt = _sd_bf16(sd_c)
+        else:
+            q_k, sd_k, sd_kt = q, sd_c, None
+        pooled, arg = ops.ground_fwd(q_k, sd_k, mask_f, temperature, "max")
+        w, w_b, _tau, _nnz = ops.sparsemax_fwd(pooled, want_bf16=(mode == "bf16"))
+        del pooled
+        if mode == "bf16":
+            f = ops.gemm_nt(sd_kt, w_b)                     # f[b,D] = w[b,K] . sdT[D,K]^T  (clip_fdt.py:154)
+        else:
+            f = ops.gemm_f32(w, sd_c)
+        ctx.mode, ctx.temperature = mode, float(temperature)
+        ctx.save_for_backward(q_k, sd_k, mask_f, w, arg, w_b)
+        return w, f
+
+    @staticmethod
+    def backward(ctx, dw, df):
+        q_k, sd_k, mask_f, w, arg, w_b = ctx.saved_tensors
+        mode = ctx.mode
+        b, K = w.shape
+        D = sd_k.shape[1]
+        dsd = torch.zeros(K, D, dtype=torch.float32, device=w.device)
+        if df is not None:
+            df = df.contiguous().float()
+            if mode == "bf16":
+                df_b = ops.cast_bf16(df)
+                g = ops.gemm_nt(sd_k, df_b)                  # g[b,K] = df . sd^T
+                # dsd[K,D] += w^T . df : both operands need the sample index contiguous
+                ops.gemm_nt(ops.transpose_bf16(df_b), ops.transpose_bf16(w_b), out=dsd, accumulate=True)
+            else:
+                g = ops.gemm_f32(df, sd_k, b_t=True)
+                ops.gemm_f32(w, df, a_t=True, out=dsd, accumulate=True)
+            if dw is not None:
+                g.add_(dw)
+        else:
+            g = dw.contiguous().float().clone()
+        dq = ops.ground_bwd(g, w, arg, q_k, sd_k, mask_f, ctx.temperature, dsd)
+        return dq, dsd, None, None, None
+
+
+class SparsemaxFunction(torch.autograd.Function):
+    """prototype/model/sparsemax.py:22-71 on a [rows, K] view."""
+
+    @staticmethod
+    def forward(ctx, z2d):
+        w, _, _, _ = ops.sparsemax_fwd(z2d.contiguous().float())
+        ctx.save_for_backward(w)
+        return w
+
+    @staticmethod
+    def backward(ctx, g):
+        (w,) = ctx.saved_tensors
+        return ops.sparsemax_bwd(w, g.contiguous().float())
+
+
+class L2NormFunction(torch.autograd.Function):
+    """x = f / (||f|| + eps)   (clip_fdt.py:411-412; clip.py:133-134)"""
+
+    @staticmethod
+    def forward(ctx, f, eps):
+        x, _, norm = ops.l2norm_fwd(f.contiguous().float(), eps)
+        ctx.eps = eps
+        ctx.save_for_backward(x, norm)
+        return x
+
+    @staticmethod
+    def backward(ctx, g):
+        x, norm = ctx.saved_tensors
+        return ops.l2norm_bwd(x, norm, g.contiguous().float(), ctx.eps), None
+
+
+class AllGather(torch.autograd.Function):
+    """clip_fdt.py:164-188. forward: all ranks' rows, rank-major [W, b, ...]; backward: the reference
+    all-reduces the whole [W,b,...] gradient and slices its own rows -- identical to a
+    reduce-scatter(SUM), which moves W times fewer bytes over NVLink."""
+
+    @staticmethod
+    def forward(ctx, tensor):
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            ctx.world, ctx.rank = dist.get_world_size(), dist.get_rank()
+            t = tensor.contiguous()
+            out = torch.empty((ctx.world,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+            dist.all_gather_into_tensor(out.view(-1, *t.shape[1:]) if t.dim() > 0 else out, t)
+            return out
+        ctx.world, ctx.rank = 1, 0
+        return tensor.unsqueeze(0).clone()
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        if ctx.world == 1:
+            return grad_output[0]
+        g = grad_output.contiguous()
+        if dist.get_backend() != "nccl":  # gloo (CPU tests) has no reduce_scatter: the reference's route
+            g = g.clone()
+            dist.all_reduce(g, op=dist.ReduceOp.SUM)
+            return g[ctx.rank]
+        out = torch.empty(g.shape[1:], dtype=g.dtype, device=g.device)
+        dist.reduce_scatter_tensor(out, g.view(-1, *g.shape[2:]) if g.dim() > 2 else g.view(-1), op=dist.ReduceOp.SUM)
+        return out
+
+
+class LogitsFunction(torch.autograd.Function):
+    """Materialised logits = scale * x @ g^T (clip_fdt.py:421-422); used when a caller really reads
+    the [b,B] matrix (accuracy(), visualisation, or a loss other than ClipInfoCELoss)."""
+
+    @staticmethod
+    def forward(ctx, x, g, scale, mode):
+        x, g = x.contiguous(), g.contiguous()
+        sc = scale.detach().reshape(1).float().contiguous()
+        if mode == "bf16":
+            out = ops.logits(ops.cast_bf16(x), ops.cast_bf16(g), sc)
+        else:
+            out = ops.logits(x, g, sc)
+        ctx.save_for_backward(x, g, sc, out)
+        ctx.scale_shape = scale.shape
+        return out
+
+    @staticmethod
+    def backward(ctx, dL):
+        x, g, sc, out = ctx.saved_tensors
+        dL = dL.contiguous().float()
+        # fp32 SIMT contractions: this route is off the training hot path
+        dLs = dL * sc
+        dx = ops.gemm_f32(dLs, g)
+        dg = ops.gemm_f32(dLs, x, a_t=True)
+        dscale = ((dL * out).sum() / sc).reshape(ctx.scale_shape)
+        return dx, dg, dscale, None
+
+
+class InfoNCEFunction(torch.autograd.Function):
+    """Fused logits + ClipInfoCELoss (clip_fdt.py:421-422 + loss_functions/loss.py:40-50):
+    (x_img, x_txt [b,D]; g_img, g_txt [B,D]; scale [1]) -> loss []. No [b,B] tensor is created."""
+
+    @staticmethod
+    def forward(ctx, x_img, x_txt, g_img, g_txt, scale, label_offset, mode):
+        ts = [t.contiguous().float() for t in (x_img, x_txt, g_img, g_txt)]
+        sc = scale.detach().reshape(1).float().contiguous()
+        if mode == "bf16":
+            ts = [ops.cast_bf16(t) for t in ts]
+        loss, lse_i, lse_t, _, _ = ops.nce_fwd(ts[0], ts[1], ts[2], ts[3], sc, label_offset)
+        ctx.save_for_backward(ts[0], ts[1], ts[2], ts[3], sc, lse_i, lse_t)
+        ctx.label_offset, ctx.scale_shape = int(label_offset), scale.shape
+        return loss
+
+    @staticmethod
+    def backward(ctx, go):
+        x_img, x_txt, g_img, g_txt, sc, lse_i, lse_t = ctx.saved_tensors
+        go = go.reshape(1).float().contiguous()
+        dx_img, dx_txt, dg_img, dg_txt, dscale = ops.nce_bwd(x_img, x_txt, g_img, g_txt, sc, ctx.label_offset,
+                                                             lse_i, lse_t, go)
+        return dx_img, dx_txt, dg_img, dg_txt, dscale.reshape(ctx.scale_shape), None, None
+
+
+class CrossEntropyRowsFunction(torch.autograd.Function):
+    """mean_r(lse(row r) - row[label_offset + r]) over stored logits: F.cross_entropy of loss.py:47-48
+    for callers that pass real [b,B] tensors."""
+
+    @staticmethod
+    def forward(ctx, logits, label_offset):
+        lg = logits.contiguous().float()
+        lse, diag = ops.ce_rows_fwd(lg, label_offset)
+        ctx.save_for_backward(lg, lse)
+        ctx.label_offset = int(label_offset)
+        return (lse - diag).mean()
+
+    @staticmethod
+    def backward(ctx, go):
+        lg, lse = ctx.saved_tensors
+        return ops.ce_rows_bwd(lg, ctx.label_offset, lse, go.reshape(1).float().contiguous(), 1.0 / lg.shape[0]), None

@@ -1,0 +1,119 @@
+"""Lazy [b,B] logits (SURVEY.md 8b "fused fast path").
+
+The reference's model.forward returns the two logit matrices and its ClipInfoCELoss reads them
+(clip_fdt.py:421-428, loss.py:40-50). At global batch 32k they are 2 x b x B fp32 (8 GiB on one GPU),
+written once and re-read three times. The drop-in forward returns `LazyLogits` handles instead: the
+drop-in ClipInfoCELoss recognises them and runs the fused kernels on the stashed embeddings; any other
+consumer (accuracy(), visualisation, indexing, torch functions) transparently materialises the matrix
+with the logits kernel, with autograd intact.
+"""
+import torch
+import torch.distributed as dist
+
+from . import functional as Fn
+
+
+class ContrastiveStash:
+    """What clip_fdt.py:411-419 produced: normalised local rows, gathered rows, clamped scale."""
+
+    def __init__(self, x_img, x_txt, g_img, g_txt, scale, mode):
+        self.x_img, self.x_txt, self.g_img, self.g_txt = x_img, x_txt, g_img, g_txt
+        self.scale, self.mode = scale, mode
+        self._mat = [None, None]
+
+    @property
+    def b(self):
+        return self.x_img.shape[0]
+
+    @property
+    def B(self):
+        return self.g_img.shape[0]
+
+    def label_offset(self):
+        """loss.py:41-45: arange(b) when the logits are square, else rank*b + arange(b)."""
+        if self.B == self.b:
+            return 0
+        rank = dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
+        return rank * self.b
+
+    def materialize(self, which):
+        if self._mat[which] is None:
+            x, g = (self.x_img, self.g_txt) if which == 0 else (self.x_txt, self.g_img)
+            self._mat[which] = Fn.LogitsFunction.apply(x, g, self.scale, self.mode)
+        return self._mat[which]
+
+    def fused_loss(self):
+        return Fn.InfoNCEFunction.apply(self.x_img, self.x_txt, self.g_img, self.g_txt, self.scale,
+                                        self.label_offset(), self.mode)
+
+
+class LazyLogits:
+    """Stands in for logits_per_image (which=0) / logits_per_text (which=1)."""
+
+    def __init__(self, stash, which):
+        object.__setattr__(self, "_stash", stash)
+        object.__setattr__(self, "_which", which)
+
+    # -- cheap metadata that does not need the matrix --
+    @property
+    def shape(self):
+        return torch.Size((self._stash.b, self._stash.B))
+
+    def size(self, dim=None):
+        return self.shape if dim is None else self.shape[dim]
+
+    def dim(self):
+        return 2
+
+    def __len__(self):
+        return self._stash.b
+
+    @property
+    def dtype(self):
+        return torch.float32
+
+    @property
+    def device(self):
+        return self._stash.x_img.device
+
+    @property
+    def is_materialized(self):
+        return self._stash._mat[self._which] is not None
+
+    def materialize(self):
+        return self._stash.materialize(self._which)
+
+    # -- everything else behaves like the real tensor --
+    def __getattr__(self, name):
+        return getattr(self.materialize(), name)
+
+    def __getitem__(self, idx):
+        return self.materialize()[idx]
+
+    @classmethod
+    def __torch_function__(cls, func, types, args=(), kwargs=None):
+        def conv(a):
+            if isinstance(a, LazyLogits):
+                return a.materialize()
+            if isinstance(a, (list, tuple)):
+                return type(a)(conv(x) for x in a)
+            return a
+
+        kwargs = {k: conv(v) for k, v in (kwargs or {}).items()}
+        return func(*conv(args), **kwargs)
+
+    def _binary(self, other, op):
+        other = other.materialize() if isinstance(other, LazyLogits) else other
+        return op(self.materialize(), other)
+
+    def __add__(self, o): return self._binary(o, torch.add)
+    def __radd__(self, o): return self._binary(o, torch.add)
+    def __sub__(self, o): return self._binary(o, torch.sub)
+    def __mul__(self, o): return self._binary(o, torch.mul)
+    def __rmul__(self, o): return self._binary(o, torch.mul)
+    def __truediv__(self, o): return self._binary(o, torch.div)
+    def __matmul__(self, o): return self._binary(o, torch.matmul)
+
+    def __repr__(self):
+        return "LazyLogits(which=%d, shape=%s, materialized=%s)" % (self._which, tuple(self.shape),
+                                                                   self.is_materialized)

@@ -1,0 +1,274 @@
+"""Tensor-level wrappers over the C ABI: allocate outputs with torch (device memory + stream are the
+only things PyTorch provides here), pass raw pointers, raise on error. No arithmetic happens in
+Python and nothing falls back to torch ops."""
+import math
+
+import torch
+
+from . import _lib
+from ._lib import BF16, F32, POOL_TYPES, check
+
+_DT = {torch.float32: F32, torch.bfloat16: BF16}
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+# ---- launch accounting / per-op device timing (bench.py) -------------------------------------------
+LAUNCHES = 0          # kernels launched through this module since it was last zeroed
+PROFILE_ON = False    # when True every C call is bracketed by CUDA events on the launching stream
+PROFILE = {}          # op name -> [(start_event, end_event), ...]
+_KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_sparsemax_fwd": 1,
+                     "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2,
+                     "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5,
+                     "ilfdt_nce_bwd": 4, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
+                     "ilfdt_randn_fill": 1, "ilfdt_copy": 0}
+
+
+def _call(name, *args):
+    global LAUNCHES
+    fn = getattr(_lib.load(), name)
+    if PROFILE_ON:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = fn(*args)
+        e1.record()
+        PROFILE.setdefault(name[len("ilfdt_"):], []).append((e0, e1))
+    else:
+        rc = fn(*args)
+    check(rc)
+    LAUNCHES += _KERNELS_PER_CALL.get(name, 1)
+
+
+def profile_summary():
+    """{op: (calls, total device ms)} for everything recorded while PROFILE_ON (synchronises)."""
+    torch.cuda.synchronize()
+    return {k: (len(v), sum(a.elapsed_time(b) for a, b in v)) for k, v in PROFILE.items()}
+
+
+def _ptr(t):
+    return 0 if t is None else t.data_ptr()
+
+
+def _req(t, dtype=None, name="tensor"):
+    if not t.is_cuda:
+        raise RuntimeError("ilfdt: %s must be a CUDA tensor (there is no CPU path)" % name)
+    if not t.is_contiguous():
+        raise RuntimeError("ilfdt: %s must be contiguous" % name)
+    if dtype is not None and t.dtype != dtype:
+        raise RuntimeError("ilfdt: %s must be %s, got %s" % (name, dtype, t.dtype))
+    return t
+
+
+def cast_bf16(x):
+    _req(x, torch.float32, "x")
+    out = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    _call("ilfdt_cast_bf16", _ptr(x), _ptr(out), x.numel(), _stream())
+    return out
+
+
+def transpose_bf16(x):
+    """x [R, C] (f32 or bf16) -> bf16 [C, R]"""
+    _req(x, None, "x")
+    assert x.dim() == 2 and x.dtype in _DT
+    out = torch.empty(x.shape[1], x.shape[0], dtype=torch.bfloat16, device=x.device)
+    _call("ilfdt_transpose_bf16", _ptr(x), _DT[x.dtype], x.shape[0], x.shape[1], _ptr(out), _stream())
+    return out
+
+
+def ground_fwd(q, sd, mask, temperature, pool_type="max"):
+    """q [b,N,D], sd [K,D] (both f32 or both bf16), mask [b,N] f32 (0 / -inf) or None
+    -> pooled [b,K] f32, arg [b,K] int16 (max pooling) or None."""
+    lib = _lib.load()
+    _req(q, None, "q"); _req(sd, q.dtype, "sd")
+    b, n_tok, D = q.shape
+    K = sd.shape[0]
+    assert sd.shape[1] == D
+    if mask is not None:
+        _req(mask, torch.float32, "mask")
+        assert tuple(mask.shape) == (b, n_tok)
+    dt = _DT[q.dtype]
+    pt = POOL_TYPES[pool_type]
+    pooled = torch.empty(b, K, dtype=torch.float32, device=q.device)
+    arg = torch.empty(b, K, dtype=torch.int16, device=q.device) if pool_type == "max" else None
+    ws_bytes = lib.ilfdt_ground_fwd_ws_bytes(dt, b, n_tok, K, D) if pool_type == "max" else 0
+    ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=q.device) if ws_bytes else None
+    _call("ilfdt_ground_fwd", _ptr(q), _ptr(sd), dt, _ptr(mask), b, n_tok, K, D, float(math.sqrt(D)),
+                               float(temperature), pt, _ptr(pooled), _ptr(arg), _ptr(ws), ws_bytes, _stream())
+    return pooled, arg
+
+
+def sparsemax_fwd(z, want_bf16=False):
+    _req(z, torch.float32, "z")
+    rows, K = z.shape
+    w = torch.empty_like(z)
+    wb = torch.empty(rows, K, dtype=torch.bfloat16, device=z.device) if want_bf16 else None
+    tau = torch.empty(rows, dtype=torch.float32, device=z.device)
+    nnz = torch.empty(rows, dtype=torch.int32, device=z.device)
+    _call("ilfdt_sparsemax_fwd", _ptr(z), rows, K, _ptr(w), _ptr(wb), _ptr(tau), _ptr(nnz), _stream())
+    return w, wb, tau, nnz
+
+
+def sparsemax_bwd(w, g):
+    _req(w, torch.float32, "w"); _req(g, torch.float32, "g")
+    dz = torch.empty_like(w)
+    _call("ilfdt_sparsemax_bwd", _ptr(w), _ptr(g), w.shape[0], w.shape[1], _ptr(dz), _stream())
+    return dz
+
+
+def gemm_nt(A, B, alpha=1.0, out=None, accumulate=False):
+    """out[N, M] (+)= alpha * B[N,Kr] . A[M,Kr]^T   (both operands reduction-contiguous; f32 or bf16)."""
+    _req(A, None, "A"); _req(B, A.dtype, "B")
+    M, Kr = A.shape
+    N = B.shape[0]
+    assert B.shape[1] == Kr
+    if out is None:
+        assert not accumulate
+        out = torch.empty(N, M, dtype=torch.float32, device=A.device)
+    _req(out, torch.float32, "out")
+    _call("ilfdt_gemm_nt", _ptr(A), _ptr(B), _DT[A.dtype], M, N, Kr, float(alpha), int(accumulate),
+                                    _ptr(out), out.shape[1], _stream())
+    return out
+
+
+def gemm_f32(A, B, a_t=False, b_t=False, alpha=1.0, out=None, accumulate=False):
+    """fp32 C = alpha * op(A) @ op(B) for 2-D row-major tensors (op = transpose if *_t)."""
+    _req(A, torch.float32, "A"); _req(B, torch.float32, "B")
+    M, Kr = (A.shape[1], A.shape[0]) if a_t else A.shape
+    Kb, N = (B.shape[1], B.shape[0]) if b_t else B.shape
+    assert Kr == Kb
+    a_rs, a_cs = (1, A.shape[1]) if a_t else (A.shape[1], 1)      # A(m,k)
+    b_rs, b_cs = (B.shape[1], 1) if b_t else (1, B.shape[1])      # B(n,k) = op(B)[k,n]
+    if out is None:
+        assert not accumulate
+        out = torch.empty(M, N, dtype=torch.float32, device=A.device)
+    _req(out, torch.float32, "out")
+    _call("ilfdt_gemm_f32_strided", _ptr(A), a_rs, a_cs, _ptr(B), b_rs, b_cs, _ptr(out), N, 1, M, N, Kr,
+                                             float(alpha), int(accumulate), _stream())
+    return out
+
+
+def ground_bwd(g, w, arg, q, sd, mask, temperature, dsd):
+    """g [b,K] is overwritten with coef. Returns dq [b,N,D] f32; accumulates into dsd [K,D] f32."""
+    _req(g, torch.float32, "g"); _req(w, torch.float32, "w"); _req(arg, torch.int16, "arg")
+    _req(q, None, "q"); _req(sd, q.dtype, "sd"); _req(dsd, torch.float32, "dsd")
+    b, n_tok, D = q.shape
+    K = sd.shape[0]
+    dq = torch.empty(b, n_tok, D, dtype=torch.float32, device=q.device)
+    _call("ilfdt_ground_bwd", _ptr(g), _ptr(w), _ptr(arg), _ptr(q), _ptr(sd), _DT[q.dtype], _ptr(mask), b,
+                                       n_tok, K, D, float(math.sqrt(D)), float(temperature), _ptr(dq), _ptr(dsd),
+                                       _stream())
+    return dq
+
+
+def l2norm_fwd(f, eps, want_bf16=False):
+    _req(f, torch.float32, "f")
+    rows, D = f.shape
+    x = torch.empty_like(f)
+    xb = torch.empty(rows, D, dtype=torch.bfloat16, device=f.device) if want_bf16 else None
+    norm = torch.empty(rows, dtype=torch.float32, device=f.device)
+    _call("ilfdt_l2norm_fwd", _ptr(f), rows, D, float(eps), _ptr(x), _ptr(xb), _ptr(norm), _stream())
+    return x, xb, norm
+
+
+def l2norm_bwd(x, norm, g, eps):
+    _req(x, torch.float32, "x"); _req(g, torch.float32, "g")
+    df = torch.empty_like(x)
+    _call("ilfdt_l2norm_bwd", _ptr(x), _ptr(norm), _ptr(g), x.shape[0], x.shape[1], float(eps), _ptr(df),
+                                       _stream())
+    return df
+
+
+def logits(x, g, scale):
+    """x [b,D], g [B,D] (f32 or bf16), scale: f32 device tensor with 1 element -> [b,B] f32"""
+    _req(x, None, "x"); _req(g, x.dtype, "g"); _req(scale, torch.float32, "scale")
+    b, D = x.shape
+    B = g.shape[0]
+    out = torch.empty(b, B, dtype=torch.float32, device=x.device)
+    _call("ilfdt_logits", _ptr(x), _ptr(g), _DT[x.dtype], b, B, D, _ptr(scale), _ptr(out), _stream())
+    return out
+
+
+def _nce_ws(dt, b, B, D, device):
+    n = _lib.load().ilfdt_nce_ws_bytes(dt, b, B, D)
+    return torch.empty(max(n, 1), dtype=torch.uint8, device=device), n
+
+
+def nce_fwd(x_img, x_txt, g_img, g_txt, scale, label_offset):
+    for t in (x_img, x_txt, g_img, g_txt):
+        _req(t, x_img.dtype, "embedding")
+    _req(scale, torch.float32, "scale")
+    b, D = x_img.shape
+    B = g_img.shape[0]
+    dev = x_img.device
+    dt = _DT[x_img.dtype]
+    lse_i, lse_t, diag_i, diag_t = (torch.empty(b, dtype=torch.float32, device=dev) for _ in range(4))
+    loss = torch.empty((), dtype=torch.float32, device=dev)
+    ws, n = _nce_ws(dt, b, B, D, dev)
+    _call("ilfdt_nce_fwd", _ptr(x_img), _ptr(x_txt), _ptr(g_img), _ptr(g_txt), dt, b, B, D, _ptr(scale),
+                                    int(label_offset), _ptr(lse_i), _ptr(lse_t), _ptr(diag_i), _ptr(diag_t),
+                                    _ptr(loss), _ptr(ws), n, _stream())
+    return loss, lse_i, lse_t, diag_i, diag_t
+
+
+def nce_bwd(x_img, x_txt, g_img, g_txt, scale, label_offset, lse_i, lse_t, grad_out, transposed=None):
+    """Returns dx_img, dx_txt [b,D], dg_img, dg_txt [B,D], dscale [] (all f32)."""
+    b, D = x_img.shape
+    B = g_img.shape[0]
+    dev = x_img.device
+    dt = _DT[x_img.dtype]
+    _req(grad_out, torch.float32, "grad_out")
+    dx_img = torch.empty(b, D, dtype=torch.float32, device=dev)
+    dx_txt = torch.empty_like(dx_img)
+    dg_img = torch.empty(B, D, dtype=torch.float32, device=dev)
+    dg_txt = torch.empty_like(dg_img)
+    dscale = torch.empty((), dtype=torch.float32, device=dev)
+    tr = [None] * 4
+    if dt == BF16:
+        tr = transposed if transposed is not None else [transpose_bf16(t) for t in (x_img, x_txt, g_img, g_txt)]
+    ws, n = _nce_ws(dt, b, B, D, dev)
+    _call("ilfdt_nce_bwd", _ptr(x_img), _ptr(x_txt), _ptr(g_img), _ptr(g_txt), _ptr(tr[0]), _ptr(tr[1]),
+                                    _ptr(tr[2]), _ptr(tr[3]), dt, b, B, D, _ptr(scale), int(label_offset),
+                                    _ptr(lse_i), _ptr(lse_t), _ptr(grad_out), _ptr(dx_img), _ptr(dx_txt),
+                                    _ptr(dg_img), _ptr(dg_txt), _ptr(dscale), _ptr(ws), n, _stream())
+    return dx_img, dx_txt, dg_img, dg_txt, dscale
+
+
+def ce_rows_fwd(logits_f32, label_offset):
+    _req(logits_f32, torch.float32, "logits")
+    b, B = logits_f32.shape
+    lse = torch.empty(b, dtype=torch.float32, device=logits_f32.device)
+    diag = torch.empty_like(lse)
+    _call("ilfdt_ce_rows_fwd", _ptr(logits_f32), b, B, int(label_offset), _ptr(lse), _ptr(diag), _stream())
+    return lse, diag
+
+
+def ce_rows_bwd(logits_f32, label_offset, lse, grad_out, coef):
+    b, B = logits_f32.shape
+    out = torch.empty_like(logits_f32)
+    _call("ilfdt_ce_rows_bwd", _ptr(logits_f32), b, B, int(label_offset), _ptr(lse), _ptr(grad_out),
+                                        float(coef), _ptr(out), _stream())
+    return out
+
+
+def topk_hits(logits_f32, label_offset):
+    _req(logits_f32, torch.float32, "logits")
+    counts = torch.empty(2, dtype=torch.int32, device=logits_f32.device)
+    _call("ilfdt_topk_hits", _ptr(logits_f32), logits_f32.shape[0], logits_f32.shape[1], int(label_offset),
+                                      _ptr(counts), _stream())
+    return counts
+
+
+def randn_fill_(t, seed, generation):
+    _req(t, torch.float32, "t")
+    _call("ilfdt_randn_fill", _ptr(t), t.numel(), int(seed) & (2 ** 64 - 1), int(generation) & 0xFFFFFFFF,
+                                       _stream())
+    return t
+
+
+def copy_(dst, src):
+    _req(dst, None, "dst"); _req(src, dst.dtype, "src")
+    assert dst.numel() == src.numel()
+    _call("ilfdt_copy", _ptr(dst), _ptr(src), dst.numel() * dst.element_size(), _stream())
+    return dst

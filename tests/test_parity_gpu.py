@@ -1,0 +1,553 @@
+"""GPU parity tests: libilfdt (through the ctypes C ABI) against the CPU oracle (oracle/fdt_oracle.py,
+pinned to the reference by tests/test_oracle_pinned.py) on identical seeded inputs, and against the
+golden vectors generated from the unmodified reference (tests/golden/*.npz).
+
+Tolerances (BASELINE.json north_star): fp32 mode <= 1e-5 relative (||delta||_inf / ||ref||_inf per
+tensor), bf16 mode <= 2e-2 relative; integer outputs (labels, argmax, counts, support sets) exact.
+"""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import fdt_oracle as O  # noqa: E402
+
+FP32_TOL = 1e-5
+BF16_TOL = 2e-2
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def rel_err(a, ref):
+    a = a.detach().double().cpu()
+    ref = ref.detach().double().cpu()
+    scale = max(ref.abs().max().item(), 1e-30)
+    return (a - ref).abs().max().item() / scale
+
+
+def assert_close(a, ref, tol, what=""):
+    e = rel_err(a, ref)
+    assert e <= tol, "%s: relative error %.3e > %.1e" % (what, e, tol)
+
+
+def bf16_round(t):
+    return t.to(torch.bfloat16).to(torch.float32)
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from ilfdt import ops as _ops
+    from ilfdt import _lib
+    _lib.load()
+    return _ops
+
+
+# ---------------------------------------------------------------------------------------------------
+# contractions
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,N,K", [(1, 1, 1), (128, 128, 16), (130, 77, 50), (300, 513, 129), (64, 1000, 512)])
+@pytest.mark.parametrize("a_t,b_t", [(False, False), (False, True), (True, False), (True, True)])
+def test_gemm_f32_strided(ops, M, N, K, a_t, b_t):
+    g = torch.Generator().manual_seed(M * 7 + N * 3 + K)
+    A = torch.randn((K, M) if a_t else (M, K), generator=g)
+    B = torch.randn((N, K) if b_t else (K, N), generator=g)
+    ref = (A.t() if a_t else A).double() @ (B.t() if b_t else B).double()
+    out = ops.gemm_f32(A.to(_dev()), B.to(_dev()), a_t=a_t, b_t=b_t, alpha=0.5)
+    assert_close(out, 0.5 * ref, FP32_TOL, "gemm_f32")
+    out2 = ops.gemm_f32(A.to(_dev()), B.to(_dev()), a_t=a_t, b_t=b_t, out=out.clone(), accumulate=True)
+    assert_close(out2, 1.5 * ref, FP32_TOL, "gemm_f32 accumulate")
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (128, 256, 512), (256, 300, 512), (200, 77, 128), (512, 1000, 1024),
+                                   (128, 16, 8), (384, 2050, 16384)])
+def test_gemm_nt_tcgen05(ops, M, N, K):
+    g = torch.Generator().manual_seed(M + N + K)
+    A = bf16_round(torch.randn(M, K, generator=g))
+    B = bf16_round(torch.randn(N, K, generator=g))
+    ref = B.double() @ A.double().t()
+    out = ops.gemm_nt(A.to(_dev()).to(torch.bfloat16), B.to(_dev()).to(torch.bfloat16), alpha=2.0)
+    # inputs are exactly representable in bf16, accumulation is fp32: only summation-order error remains
+    assert_close(out, 2.0 * ref, 2e-5, "gemm_nt bf16")
+    out2 = ops.gemm_nt(A.to(_dev()).to(torch.bfloat16), B.to(_dev()).to(torch.bfloat16), out=out.clone(),
+                       accumulate=True)
+    assert_close(out2, 3.0 * ref, 2e-5, "gemm_nt bf16 accumulate")
+
+
+# ---------------------------------------------------------------------------------------------------
+# a1: score block forward
+# ---------------------------------------------------------------------------------------------------
+def _mask(b, T, lens):
+    m = torch.zeros(b, T)
+    for i, n in enumerate(lens):
+        m[i, n:] = float("-inf")
+    return m
+
+
+GROUND_CASES = [
+    # b, n_tok, K, D, masked
+    (7, 9, 200, 64, True),
+    (5, 49, 256, 512, False),
+    (6, 77, 384, 512, True),
+    (3, 196, 130, 512, False),
+    (1, 1, 1, 8, True),
+    (33, 5, 1000, 128, True),
+]
+
+
+@pytest.mark.parametrize("b,n_tok,K,D,masked", GROUND_CASES)
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_ground_fwd(ops, b, n_tok, K, D, masked, mode):
+    g = torch.Generator().manual_seed(b * 1000 + n_tok + K)
+    q = torch.randn(b, n_tok, D, generator=g)
+    sd = torch.randn(K, D, generator=g)
+    lens = torch.randint(1, n_tok + 1, (b,), generator=g).tolist()
+    mask = _mask(b, n_tok, lens) if masked else None
+    temp = 7.0
+    if mode == "bf16":
+        q, sd = bf16_round(q), bf16_round(sd)
+    ref, tok = O.pooled_scores(q.double(), sd.double(), None if mask is None else mask.double(), temp, "max",
+                               return_token_scores=True)
+    dt = torch.bfloat16 if mode == "bf16" else torch.float32
+    pooled, arg = ops.ground_fwd(q.to(_dev()).to(dt), sd.to(_dev()).to(dt), None if mask is None else mask.to(_dev()),
+                                 temp, "max")
+    assert_close(pooled, ref, FP32_TOL if mode == "fp32" else 2e-5, "pooled (%s)" % mode)
+    # argmax consistency: the token the kernel reports attains the pooled score (ties / pads aside)
+    s_full = torch.matmul(q.double(), sd.double().t()) / math.sqrt(D)
+    if mask is not None:
+        s_full = s_full * ((mask == 0) * 1.0).unsqueeze(-1).double()
+    s_full = s_full / temp
+    picked = torch.gather(s_full, 1, arg.cpu().long().unsqueeze(1)).squeeze(1)
+    assert arg.min().item() >= 0 and arg.max().item() < n_tok
+    assert (picked - ref).abs().max().item() <= 1e-5 * max(ref.abs().max().item(), 1e-30)
+
+
+@pytest.mark.parametrize("pool", ["sum", "mean"])
+def test_ground_fwd_sum_mean_fp32(ops, pool):
+    g = torch.Generator().manual_seed(5)
+    b, n_tok, K, D = 6, 11, 150, 48
+    q = torch.randn(b, n_tok, D, generator=g)
+    sd = torch.randn(K, D, generator=g)
+    mask = _mask(b, n_tok, [11, 3, 1, 7, 11, 5])
+    ref = O.pooled_scores(q.double(), sd.double(), mask.double(), 3.0, pool)
+    pooled, arg = ops.ground_fwd(q.to(_dev()), sd.to(_dev()), mask.to(_dev()), 3.0, pool)
+    assert arg is None
+    assert_close(pooled, ref, FP32_TOL, "pooled " + pool)
+
+
+# ---------------------------------------------------------------------------------------------------
+# a2: sparsemax
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", list("abcdef"))
+def test_sparsemax_golden(ops, golden_dir, case):
+    from ilfdt.model.sparsemax import Sparsemax
+    z = np.load(os.path.join(golden_dir, "sparsemax.npz"))
+    x = torch.tensor(z[f"{case}_x"], device=_dev(), requires_grad=True)
+    dim = int(z[f"{case}_dim"])
+    y = Sparsemax(dim=dim)(x)
+    ref = torch.tensor(z[f"{case}_y"])
+    assert_close(y, ref, 2e-6, "sparsemax fwd")
+    assert torch.equal(y.detach().cpu() > 0, ref > 0), "support set differs from the reference"
+    (y * torch.tensor(z[f"{case}_up"], device=_dev())).sum().backward()
+    assert_close(x.grad, torch.tensor(z[f"{case}_dx"]), 2e-5, "sparsemax bwd")
+
+
+@pytest.mark.parametrize("rows,K,scale", [(8, 16384, 4e-4), (4, 4096, 1.0), (3, 1000, 0.05), (2, 51200, 1e-3), (5, 7, 2.0)])
+def test_sparsemax_large_rows(ops, rows, K, scale):
+    g = torch.Generator().manual_seed(K)
+    x = (2.2e-3 + torch.randn(rows, K, generator=g) * scale).float()
+    w, wb, tau, nnz = ops.sparsemax_fwd(x.to(_dev()), want_bf16=True)
+    ref = O.sparsemax(x)
+    assert_close(w, ref, 2e-5, "sparsemax")
+    s = w.sum(1)
+    assert torch.allclose(s, torch.ones_like(s), atol=1e-4)
+    assert torch.equal((w > 0).sum(1).int().cpu(), nnz.cpu())
+    # support sets: identical except where the fp64 arbiter says the element sits within rounding of tau
+    wc = w.cpu()
+    for i in range(rows):
+        t64, supp, _ = O.sparsemax_tau_exact(x[i].numpy())
+        zi = (x[i] - x[i].max()).double().numpy()
+        diff = np.nonzero((wc[i].numpy() > 0) != (ref[i].numpy() > 0))[0]
+        for j in diff:
+            assert abs(zi[j] - t64) < 1e-7, "support mismatch at (%d,%d) with margin %.3e" % (i, j, abs(zi[j] - t64))
+    assert_close(wb.float(), ref, 1e-2, "bf16 copy of w")
+
+
+def test_sparsemax_bwd_closed_form(ops):
+    g = torch.Generator().manual_seed(3)
+    x = (torch.randn(9, 3000, generator=g) * 0.01).requires_grad_(True)
+    up = torch.randn(9, 3000, generator=g)
+    y = O.sparsemax(x)
+    (y * up).sum().backward()
+    w, _, _, _ = ops.sparsemax_fwd(x.detach().to(_dev()))
+    dz = ops.sparsemax_bwd(w, up.to(_dev()))
+    assert_close(dz, x.grad, 1e-4, "sparsemax bwd vs autograd through sort/cumsum")
+
+
+# ---------------------------------------------------------------------------------------------------
+# a1-a3 + a13: grounding forward/backward through the autograd Function
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("b,n_tok,K,D,masked", [(7, 9, 200, 64, True), (5, 49, 256, 512, False), (6, 77, 384, 512, True),
+                                               (4, 12, 9000, 256, True)])
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_grounding_fwd_bwd(ops, b, n_tok, K, D, masked, mode):
+    from ilfdt.functional import GroundingFunction
+    g = torch.Generator().manual_seed(b + n_tok + K)
+    q = torch.randn(b, n_tok, D, generator=g)
+    sd = torch.randn(K, D, generator=g)
+    lens = torch.randint(1, n_tok + 1, (b,), generator=g).tolist()
+    mask = _mask(b, n_tok, lens) if masked else None
+    temp = 40.0
+    up_w = torch.randn(b, K, generator=g)
+    up_f = torch.randn(b, D, generator=g)
+    if mode == "bf16":
+        q, sd = bf16_round(q), bf16_round(sd)
+    qo = q.double().requires_grad_(True)
+    so = sd.double().requires_grad_(True)
+    w_ref, f_ref, pooled_ref = O.grounding(qo, so, None if mask is None else mask.double(), temp)
+    ((w_ref * up_w.double()).sum() + (f_ref * up_f.double()).sum()).backward()
+
+    qd = q.to(_dev()).requires_grad_(True)
+    sdd = sd.to(_dev()).requires_grad_(True)
+    w, f = GroundingFunction.apply(qd, sdd, None if mask is None else mask.to(_dev()), temp, mode)
+    ((w * up_w.to(_dev())).sum() + (f * up_f.to(_dev())).sum()).backward()
+    tol = FP32_TOL if mode == "fp32" else BF16_TOL
+    assert_close(w, w_ref, tol, "att_weight")
+    assert_close(f, f_ref, tol, "att_ft")
+    assert_close(qd.grad, qo.grad, tol * (5 if mode == "fp32" else 1), "dq")
+    assert_close(sdd.grad, so.grad, tol * (5 if mode == "fp32" else 1), "dsd")
+    if mode == "fp32":
+        # support sets identical, except entries the fp64 run itself puts within rounding of tau
+        mism = (w.cpu() > 0) != (w_ref > 0)
+        if mism.any():
+            margin = torch.maximum(w.cpu().double(), w_ref)[mism].max().item()
+            assert margin < 1e-8, "support sets differ at entries with weight up to %.3e" % margin
+
+
+# ---------------------------------------------------------------------------------------------------
+# a5: L2 normalise
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("eps", [1e-10, 0.0])
+def test_l2norm(ops, eps):
+    from ilfdt.functional import L2NormFunction
+    g = torch.Generator().manual_seed(1)
+    f = torch.randn(37, 512, generator=g)
+    up = torch.randn(37, 512, generator=g)
+    fo = f.double().requires_grad_(True)
+    xo = O.l2_normalise(fo, eps)
+    (xo * up.double()).sum().backward()
+    fd = f.to(_dev()).requires_grad_(True)
+    x = L2NormFunction.apply(fd, eps)
+    (x * up.to(_dev())).sum().backward()
+    assert_close(x, xo, FP32_TOL, "l2norm")
+    assert_close(fd.grad, fo.grad, FP32_TOL, "l2norm bwd")
+
+
+# ---------------------------------------------------------------------------------------------------
+# a8 + a10: logits + InfoNCE
+# ---------------------------------------------------------------------------------------------------
+def _nce_oracle(x_img, x_txt, g_img, g_txt, p, offset, upstream):
+    xs = [t.double().requires_grad_(True) for t in (x_img, x_txt, g_img, g_txt)]
+    pp = p.double().requires_grad_(True)
+    s = O.logit_scale_forward(pp)
+    l_i, l_t = O.fdt_logits(xs[0], xs[1], xs[2], xs[3], s)
+    bs = l_i.shape[0]
+    labels = offset + torch.arange(bs)
+    loss = (torch.nn.functional.cross_entropy(l_i, labels) + torch.nn.functional.cross_entropy(l_t, labels)) / 2
+    (loss * upstream).backward()
+    return loss.detach(), l_i.detach(), l_t.detach(), [t.grad for t in xs], pp.grad
+
+
+@pytest.mark.parametrize("b,B,D,offset", [(8, 8, 32, 0), (64, 64, 512, 0), (128, 512, 512, 256), (200, 1000, 512, 400),
+                                         (256, 256, 512, 0), (40, 328, 64, 288)])
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+@pytest.mark.parametrize("pval", [math.log(1 / 0.07), 5.0])
+def test_infonce(ops, b, B, D, offset, mode, pval):
+    from ilfdt.functional import InfoNCEFunction, LogitsFunction
+    g = torch.Generator().manual_seed(b + B)
+    g_img = torch.nn.functional.normalize(torch.randn(B, D, generator=g), dim=-1)
+    g_txt = torch.nn.functional.normalize(g_img + 0.7 * torch.randn(B, D, generator=g), dim=-1)
+    if mode == "bf16":
+        g_img, g_txt = bf16_round(g_img), bf16_round(g_txt)
+    x_img, x_txt = g_img[offset:offset + b].clone(), g_txt[offset:offset + b].clone()
+    p = torch.full((1,), pval)
+    upstream = 0.37
+    loss_ref, li_ref, lt_ref, grads_ref, dp_ref = _nce_oracle(x_img, x_txt, g_img, g_txt, p, offset, upstream)
+
+    ts = [t.to(_dev()).requires_grad_(True) for t in (x_img, x_txt, g_img, g_txt)]
+    pd = p.to(_dev()).requires_grad_(True)
+    s = pd.exp()
+    s.data = torch.clamp(s.data, max=100)
+    loss = InfoNCEFunction.apply(ts[0], ts[1], ts[2], ts[3], s, offset, mode)
+    (loss * upstream).backward()
+    tol = FP32_TOL if mode == "fp32" else BF16_TOL
+    assert_close(loss, loss_ref, tol, "loss")
+    for name, t, r in zip(("dx_img", "dx_txt", "dg_img", "dg_txt"), ts, grads_ref):
+        assert_close(t.grad, r, tol * (3 if mode == "fp32" else 1), name)
+    assert_close(pd.grad, dp_ref, tol * (10 if mode == "fp32" else 1), "d logit_scale")
+    # materialising route
+    with torch.no_grad():
+        s2 = torch.clamp(p.exp(), max=100).to(_dev())
+        li = LogitsFunction.apply(ts[0].detach(), ts[3].detach(), s2, mode)
+        lt = LogitsFunction.apply(ts[1].detach(), ts[2].detach(), s2, mode)
+    assert_close(li, li_ref, tol, "logits_per_image")
+    assert_close(lt, lt_ref, tol, "logits_per_text")
+    counts = ops.topk_hits(li.contiguous(), offset).cpu()
+    lab = offset + torch.arange(b)
+    top5 = li.cpu().topk(min(5, B), 1).indices
+    assert counts[0].item() == (top5[:, 0] == lab).sum().item() or B < 5
+    assert counts[1].item() == (top5 == lab.view(-1, 1)).any(1).sum().item()
+
+
+# ---------------------------------------------------------------------------------------------------
+# whole step against the golden vectors produced by the unmodified reference
+# ---------------------------------------------------------------------------------------------------
+class _FakeVisual(torch.nn.Module):
+    def __init__(self, patch_ft):
+        super().__init__()
+        self.conv1 = torch.nn.Conv2d(1, 1, 1)
+        self.patch_ft = patch_ft
+
+    def forward(self, image, return_dense=False, return_raw_feature=False):
+        cls = self.patch_ft.mean(1)
+        return cls, self.patch_ft, cls
+
+
+class _FakeText(torch.nn.Module):
+    def __init__(self, word_ft, pad_mask):
+        super().__init__()
+        self.text_projection = torch.nn.Linear(1, 1)
+        self.word_ft, self.pad_mask = word_ft, pad_mask
+
+    def forward(self, texts, return_dense=False, return_padmask=False, return_raw_feature=False, raw_text=True):
+        cls = self.word_ft.mean(1)
+        return [cls, self.word_ft, cls, self.pad_mask]
+
+
+def _build_rank_model(z, r, dev):
+    from ilfdt.model.clip_fdt import Clip_FDT
+    pre = f"r{r}_"
+    params = {k[len(pre) + 6:]: z[k] for k in z.files if k.startswith(pre + "param_")}
+    patch = torch.tensor(z[pre + "patch"], device=dev, requires_grad=True)
+    word = torch.tensor(z[pre + "word"], device=dev, requires_grad=True)
+    mask = torch.tensor(z[pre + "mask"], device=dev)
+    K, D = params["space_dict"].shape
+    m = Clip_FDT(_FakeVisual(patch), _FakeText(word, mask), True, K, D, patch.shape[-1], word.shape[-1], "sparsemax",
+                 "max", float(z[pre + "temp"])).to(dev)
+    sd = {k: torch.tensor(v) for k, v in params.items()}
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not unexpected
+    assert all(k.startswith(("visual.", "encode_text.")) for k in missing), missing
+    return m, patch, word
+
+
+@pytest.mark.parametrize("tag", ["w1", "w1_clamp"])
+def test_fdt_step_golden_dropin(ops, golden_dir, tag):
+    """Clip_FDT.forward + ClipInfoCELoss + backward through the drop-in modules == the reference's outputs."""
+    import ilfdt
+    from ilfdt.loss_functions import ClipInfoCELoss
+    z = np.load(os.path.join(golden_dir, f"clip_fdt_step_{tag}.npz"))
+    with ilfdt.compute_dtype("fp32"):
+        m, patch, word = _build_rank_model(z, 0, _dev())
+        (l_i, l_t), (sd_a, sd_b) = m(torch.zeros(patch.shape[0], 1, device=_dev()), ["x"] * patch.shape[0])
+        loss, labels = ClipInfoCELoss()(l_i, l_t)
+        assert not l_i.is_materialized, "fused route must not form the logits"
+        loss.backward()
+        pre = "r0_"
+        assert_close(loss, torch.tensor(z[pre + "loss"]), FP32_TOL, "loss")
+        assert np.array_equal(labels.cpu().numpy(), z[pre + "labels"])
+        assert_close(l_i.materialize(), torch.tensor(z[pre + "logits_per_image"]), FP32_TOL, "logits_per_image")
+        assert_close(l_t.materialize(), torch.tensor(z[pre + "logits_per_text"]), FP32_TOL, "logits_per_text")
+        gtol = 1e-4  # the golden gradients themselves are fp32 autograd through sort/cumsum
+        assert_close(patch.grad, torch.tensor(z[pre + "d_patch"]), gtol, "d_patch")
+        assert_close(word.grad, torch.tensor(z[pre + "d_word"]), gtol, "d_word")
+        for k, v in m.named_parameters():
+            if k.startswith(("visual.", "encode_text.")):
+                continue
+            ref = z[pre + "grad_" + k]
+            if ref.size == 0:
+                assert v.grad is None, k   # logit_scale_sd: unused in the reference too
+            else:
+                assert_close(v.grad, torch.tensor(ref), gtol, "grad " + k)
+        assert sd_a is m.space_dict and sd_b is m.space_dict
+
+
+@pytest.mark.parametrize("tag", ["w2", "w2_clamp"])
+def test_fdt_step_golden_two_ranks_emulated(ops, golden_dir, tag):
+    """W=2 golden (reference under gloo, 2 processes) against a single-GPU emulation of both ranks: the
+    gathered tensors are a differentiable concatenation, so autograd sums the gradient w.r.t. every rank's
+    gathered copy exactly like AllGather.backward's all-reduce + slice (clip_fdt.py:182-188)."""
+    import ilfdt
+    from ilfdt import functional as Fn
+    z = np.load(os.path.join(golden_dir, f"clip_fdt_step_{tag}.npz"))
+    W = int(z["world"])
+    with ilfdt.compute_dtype("fp32"):
+        models, feats = [], []
+        for r in range(W):
+            m, patch, word = _build_rank_model(z, r, _dev())
+            _, f_i, _ = m.img_query_model(patch, m.space_dict)
+            _, f_t, _ = m.txt_query_model(word, m.space_dict, mask=m.encode_text.pad_mask)
+            x_i, x_t = Fn.L2NormFunction.apply(f_i, 1e-10), Fn.L2NormFunction.apply(f_t, 1e-10)
+            models.append((m, patch, word))
+            feats.append((x_i, x_t))
+        g_img = torch.cat([f[0] for f in feats], 0)
+        g_txt = torch.cat([f[1] for f in feats], 0)
+        total = 0
+        losses = []
+        for r in range(W):
+            m = models[r][0]
+            s = m.logit_scale.exp()
+            s.data = torch.clamp(s.data, max=100)
+            b = feats[r][0].shape[0]
+            loss = Fn.InfoNCEFunction.apply(feats[r][0], feats[r][1], g_img, g_txt, s, r * b, "fp32")
+            losses.append(loss)
+            total = total + loss / W
+        total.backward()
+        for r in range(W):
+            pre = f"r{r}_"
+            m, patch, word = models[r]
+            assert_close(losses[r], torch.tensor(z[pre + "loss"]), FP32_TOL, "loss")
+            assert_close(patch.grad, torch.tensor(z[pre + "d_patch"]), 1e-4, "d_patch")
+            assert_close(word.grad, torch.tensor(z[pre + "d_word"]), 1e-4, "d_word")
+            assert_close(m.space_dict.grad, torch.tensor(z[pre + "grad_space_dict"]), 1e-4, "d space_dict")
+            assert_close(m.logit_scale.grad, torch.tensor(z[pre + "grad_logit_scale"]), 1e-4, "d logit_scale")
+
+
+@pytest.mark.parametrize("tag", ["w1", "w2"])
+def test_clip_step_golden(ops, golden_dir, tag):
+    import ilfdt
+    from ilfdt import functional as Fn
+    z = np.load(os.path.join(golden_dir, f"clip_step_{tag}.npz"))
+    W = int(z["world"])
+    with ilfdt.compute_dtype("fp32"):
+        leaves, feats = [], []
+        for r in range(W):
+            pre = f"r{r}_"
+            f_i = torch.tensor(z[pre + "f_img"], device=_dev(), requires_grad=True)
+            f_t = torch.tensor(z[pre + "f_txt"], device=_dev(), requires_grad=True)
+            p = torch.tensor(z[pre + "p"], device=_dev()).reshape(1).requires_grad_(True)
+            leaves.append((f_i, f_t, p))
+            feats.append((Fn.L2NormFunction.apply(f_i, 0.0), Fn.L2NormFunction.apply(f_t, 1e-10)))  # clip.py:133-134
+        g_img = torch.cat([f[0] for f in feats], 0)
+        g_txt = torch.cat([f[1] for f in feats], 0)
+        total, losses = 0, []
+        for r in range(W):
+            s = leaves[r][2].exp()
+            s.data = torch.clamp(s.data, max=100)
+            b = feats[r][0].shape[0]
+            loss = Fn.InfoNCEFunction.apply(feats[r][0], feats[r][1], g_img, g_txt, s, r * b if W > 1 else 0, "fp32")
+            losses.append(loss)
+            total = total + loss / W
+        total.backward()
+        for r in range(W):
+            pre = f"r{r}_"
+            assert_close(losses[r], torch.tensor(z[pre + "loss"]), FP32_TOL, "loss")
+            assert_close(leaves[r][0].grad, torch.tensor(z[pre + "d_f_img"]), 1e-4, "d_f_img")
+            assert_close(leaves[r][1].grad, torch.tensor(z[pre + "d_f_txt"]), 1e-4, "d_f_txt")
+            assert_close(leaves[r][2].grad.reshape(-1), torch.tensor(z[pre + "d_p"]).reshape(-1), 1e-4, "d_p")
+
+
+# ---------------------------------------------------------------------------------------------------
+# whole step, bf16 tensor-core mode, against the fp64 oracle on a mid-size case + drop-in plumbing
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_full_step_vs_oracle(ops, mode):
+    import ilfdt
+    from ilfdt.loss_functions import ClipInfoCELoss
+    from ilfdt.model.clip_fdt import Clip_FDT
+    b, P, T, K, D = 32, 49, 77, 2048, 512
+    inp = O.synth_inputs(b, P, T, K, D, seed=1)
+    temp = 1000.0
+    # oracle (fp64) on the same q: q_map replaced by identity features of width D
+    ranks = [dict(q_img=O.make_leaf(inp["q_img"].double()), q_txt=O.make_leaf(inp["q_txt"].double()),
+                  mask=inp["mask"].double(), sd=O.make_leaf(inp["sd"].double()), p=O.make_leaf(inp["p"].double()))]
+    ref = O.step(ranks, temperature=temp)[0]
+
+    class Id(torch.nn.Module):
+        def forward(self, x):
+            return x
+
+    patch = inp["q_img"].to(_dev()).requires_grad_(True)
+    word = inp["q_txt"].to(_dev()).requires_grad_(True)
+    with ilfdt.compute_dtype(mode):
+        m = Clip_FDT(_FakeVisual(patch), _FakeText(word, inp["mask"].to(_dev())), True, K, D, D, D, "sparsemax", "max",
+                     temp).to(_dev())
+        m.img_query_model.q_map = Id()
+        m.txt_query_model.q_map = Id()
+        with torch.no_grad():
+            m.space_dict.copy_(inp["sd"].to(_dev()))
+        (l_i, l_t), _ = m(torch.zeros(b, 1, device=_dev()), ["x"] * b)
+        loss, labels = ClipInfoCELoss()(l_i, l_t)
+        loss.backward()
+        tol = 2e-5 if mode == "fp32" else BF16_TOL
+        assert_close(loss, ref["loss"], tol, "loss")
+        assert_close(l_i.materialize(), ref["logits_per_image"], tol, "logits_per_image")
+        assert_close(patch.grad, ref["d_q_img"], tol * 5 if mode == "fp32" else tol, "d q_img")
+        assert_close(word.grad, ref["d_q_txt"], tol * 5 if mode == "fp32" else tol, "d q_txt")
+        assert_close(m.space_dict.grad, ref["d_sd"], tol * 5 if mode == "fp32" else tol, "d space_dict")
+        assert_close(m.logit_scale.grad, ref["d_p"], tol * 10 if mode == "fp32" else tol, "d logit_scale")
+        assert torch.equal(labels.cpu(), ref["labels"])
+        # materialised route gives the same loss (ilfdt_ce_rows_*), and accuracy()'s topk works on the lazy handle
+        loss2, _ = ClipInfoCELoss()(l_i.materialize(), l_t.materialize())
+        assert_close(loss2, ref["loss"], tol, "loss via stored logits")
+        assert l_i.topk(5, 1, True, True)[1].shape == (b, 5)
+
+
+# ---------------------------------------------------------------------------------------------------
+# a12: codebook reset
+# ---------------------------------------------------------------------------------------------------
+def test_randn_fill_and_codebook_reset(ops):
+    n = 1 << 16
+    t = torch.empty(n + 3, device=_dev())
+    ops.randn_fill_(t, 1234, 3)
+    ref = torch.tensor(O.philox_randn(n + 3, 1234, 3))
+    assert (t.cpu() - ref).abs().max().item() < 2e-4   # same Philox words; fp32 vs fp64 Box-Muller
+    x = t.double().cpu()
+    assert abs(x.mean()) < 0.02 and abs(x.std() - 1) < 0.02
+    t2 = torch.empty_like(t)
+    ops.randn_fill_(t2, 1234, 3)
+    assert torch.equal(t, t2)                           # deterministic => identical on every rank
+    ops.randn_fill_(t2, 1234, 4)
+    assert not torch.equal(t, t2)
+
+    from ilfdt.model.clip_fdt import Clip_FDT
+    m = Clip_FDT(torch.nn.Identity(), torch.nn.Identity(), True, 256, 64, 32, 32, "sparsemax", "max", 10.0).to(_dev())
+    ptr = m.space_dict.data_ptr()
+    before = m.space_dict.detach().clone()
+    m.store_codebook_value()
+    m.reset_codebook()
+    assert m.space_dict.data_ptr() == ptr and m.space_dict.is_cuda   # in place, stays on the device (F8)
+    assert not torch.equal(before, m.space_dict.detach())
+    m.keep_codebook_value()
+    assert torch.equal(before, m.space_dict.detach())
+    assert m.stored_codebook.data_ptr() != m.space_dict.data_ptr()   # copy, not aliasing (F8)
+
+
+# ---------------------------------------------------------------------------------------------------
+# full-size properties (BASELINE.json config 3 shapes): no oracle at this size, only invariants
+# ---------------------------------------------------------------------------------------------------
+def test_full_size_properties(ops):
+    b, P, K, D = 256, 49, 16384, 512
+    g = torch.Generator(device="cuda").manual_seed(0)
+    q = torch.randn(b, P, D, device=_dev(), generator=g).to(torch.bfloat16)
+    sd = torch.randn(K, D, device=_dev(), generator=g).to(torch.bfloat16)
+    pooled, arg = ops.ground_fwd(q, sd, None, 1000.0, "max")
+    w, wb, tau, nnz = ops.sparsemax_fwd(pooled, want_bf16=True)
+    s = w.sum(1)
+    assert torch.allclose(s, torch.ones_like(s), atol=1e-4), "rows must lie on the simplex"
+    assert (w >= 0).all() and nnz.min().item() >= 1
+    # pooled[b,k] is attained at token arg[b,k] and dominates every token (sampled codes)
+    ks = torch.randint(0, K, (64,), generator=torch.Generator().manual_seed(1)).to(_dev())
+    sc = torch.matmul(q.float(), sd[ks].float().t()) / math.sqrt(D) / 1000.0      # [b,P,64]
+    mx, am = sc.max(1)
+    assert (pooled[:, ks] - mx).abs().max().item() <= 2e-5 * mx.abs().max().item()
+    picked = torch.gather(sc, 1, arg[:, ks].long().unsqueeze(1)).squeeze(1)
+    assert (picked - mx).abs().max().item() <= 2e-5 * mx.abs().max().item()
+    # idempotence of the projection: sparsemax(w) == w for points already on the simplex
+    w2, _, _, _ = ops.sparsemax_fwd(w)
+    assert (w2 - w).abs().max().item() <= 1e-6
