@@ -194,12 +194,10 @@ def run_ours(args):
 
     def step(qi, qt, mk):
         """The hot path exactly as ilfdt.model.clip_fdt.Clip_FDT.forward + ClipInfoCELoss run it."""
-        qi.requires_grad_(True)
-        qt.requires_grad_(True)
+        qi = qi.detach().requires_grad_(True)
+        qt = qt.detach().requires_grad_(True)
         sd.grad = None
         p.grad = None
-        qi.grad = None
-        qt.grad = None
         mode = Fn.get_compute_dtype()
         _, f_i = Fn.GroundingFunction.apply(qi, sd, None, TEMPERATURE, mode)
         _, f_t = Fn.GroundingFunction.apply(qt, sd, mk, TEMPERATURE, mode)
@@ -269,21 +267,21 @@ def run_ours(args):
     # ---- end to end through the public call with HOST buffers ----
     e2e = None
     if not args.no_e2e:
-        h_qi = torch.empty(q_img.shape, dtype=torch.float32, pin_memory=True).copy_(q_img)
-        h_qt = torch.empty(q_txt.shape, dtype=torch.float32, pin_memory=True).copy_(q_txt)
-        h_mk = torch.empty(mask.shape, dtype=torch.float32, pin_memory=True).copy_(mask)
-        h_loss = torch.empty((), dtype=torch.float32, pin_memory=True)
-        d_qi, d_qt, d_mk = torch.empty_like(q_img), torch.empty_like(q_txt), torch.empty_like(mask)
-        del q_img, q_txt
+        with torch.no_grad():
+            h_qi = torch.empty(q_img.shape, dtype=torch.float32, pin_memory=True).copy_(q_img)
+            h_qt = torch.empty(q_txt.shape, dtype=torch.float32, pin_memory=True).copy_(q_txt)
+            h_mk = torch.empty(mask.shape, dtype=torch.float32, pin_memory=True).copy_(mask)
+            h_loss = torch.empty((), dtype=torch.float32, pin_memory=True)
+        d_qi, d_qt, d_mk = q_img, q_txt, mask   # reuse the device buffers as the H2D targets
 
         def e2e_step():
-            d_qi.requires_grad_(False)
-            d_qt.requires_grad_(False)
-            d_qi.copy_(h_qi, non_blocking=True)
-            d_qt.copy_(h_qt, non_blocking=True)
-            d_mk.copy_(h_mk, non_blocking=True)
+            with torch.no_grad():
+                d_qi.copy_(h_qi, non_blocking=True)
+                d_qt.copy_(h_qt, non_blocking=True)
+                d_mk.copy_(h_mk, non_blocking=True)
             l = step(d_qi, d_qt, d_mk)
-            h_loss.copy_(l.detach(), non_blocking=True)
+            with torch.no_grad():
+                h_loss.copy_(l.detach(), non_blocking=True)
 
         for _ in range(max(1, min(args.warmup, 2))):
             e2e_step()

@@ -62,6 +62,9 @@ class GroundingFunction(torch.autograd.Function):
         q = q.contiguous()
         sd_c = sd.contiguous()
         mask_f = None if mask is None else mask.to(torch.float32).contiguous()
+        if mode == "bf16" and not (q.shape[2] % 8 == 0 and q.shape[2] <= 512 and q.shape[1] <= 256
+                                   and sd.shape[0] % 8 == 0):
+            mode = "fp32"   # shapes outside the tcgen05 kernel's tiling take the fp32 CUDA kernels
         if mode == "bf16":
             q_k = ops.cast_bf16(q)
             sd_k, sd_kt = _sd_bf16(sd_c)
@@ -91,7 +94,10 @@ class GroundingFunction(torch.autograd.Function):
                 df_b = ops.cast_bf16(df)
                 g = ops.gemm_nt(sd_k, df_b)                  # g[b,K] = df . sd^T
                 # dsd[K,D] += w^T . df : both operands need the sample index contiguous
-                ops.gemm_nt(ops.transpose_bf16(df_b), ops.transpose_bf16(w_b), out=dsd, accumulate=True)
+                if b % 8 == 0:
+                    ops.gemm_nt(ops.transpose_bf16(df_b), ops.transpose_bf16(w_b), out=dsd, accumulate=True)
+                else:  # TMA needs a 16-byte row pitch on the [*, b] transposes: ragged batch -> fp32 SIMT kernel
+                    ops.gemm_f32(w, df, a_t=True, out=dsd, accumulate=True)
             else:
                 g = ops.gemm_f32(df, sd_k, b_t=True)
                 ops.gemm_f32(w, df, a_t=True, out=dsd, accumulate=True)
@@ -200,7 +206,10 @@ class InfoNCEFunction(torch.autograd.Function):
     def forward(ctx, x_img, x_txt, g_img, g_txt, scale, label_offset, mode):
         ts = [t.contiguous().float() for t in (x_img, x_txt, g_img, g_txt)]
         sc = scale.detach().reshape(1).float().contiguous()
-        if mode == "bf16":
+        # the tensor-core kernels TMA-load [D, b] / [D, B] transposes: row pitch must be a multiple of
+        # 16 bytes. Ragged batches take the fp32 kernels (still CUDA, still fused per row chunk).
+        if mode == "bf16" and ts[0].shape[0] % 8 == 0 and ts[2].shape[0] % 8 == 0 and ts[0].shape[1] % 8 == 0 \
+                and ts[0].shape[1] <= 512:
             ts = [ops.cast_bf16(t) for t in ts]
         loss, lse_i, lse_t, _, _ = ops.nce_fwd(ts[0], ts[1], ts[2], ts[3], sc, label_offset)
         ctx.save_for_backward(ts[0], ts[1], ts[2], ts[3], sc, lse_i, lse_t)
