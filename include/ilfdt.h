@@ -53,6 +53,10 @@ int32_t ilfdt_device_check(int32_t device);
 /* ---- layout helpers (feed the bf16 tensor-core kernels) ----------------------------------- */
 /* dst_bf16[i] = bf16(src[i]) */
 int32_t ilfdt_cast_bf16(const float* src, void* dst_bf16, int64_t n, void* stream);
+/* dst_bf16[r, :] = rowmask[r] == 0 ? bf16(src[r, :]) : 0.  Folding the pad mask into the operand makes the
+ * tensor-core score of a pad token exactly the 0 that clip_fdt.py:125-130 produces by multiplying. */
+int32_t ilfdt_cast_bf16_rows(const float* src, const float* rowmask, int64_t rows, int64_t cols, void* dst_bf16,
+                             void* stream);
 /* src [rows, cols] f32 or bf16 -> dst_bf16 [cols, rows] */
 int32_t ilfdt_transpose_bf16(const void* src, int32_t src_dtype, int64_t rows, int64_t cols,
                              void* dst_bf16, void* stream);

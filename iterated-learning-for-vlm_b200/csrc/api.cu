@@ -123,6 +123,14 @@ int32_t ilfdt_cast_bf16(const float* src, void* dst_bf16, int64_t n, void* strea
   return launch_cast_bf16(src, dst_bf16, n, ST(stream));
 }
 
+int32_t ilfdt_cast_bf16_rows(const float* src, const float* rowmask, int64_t rows, int64_t cols, void* dst_bf16,
+                             void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(rows >= 0 && cols >= 0 && (rows * cols == 0 || (src && dst_bf16)), ILFDT_E_INVALID_ARG,
+                "cast_bf16_rows: bad arguments");
+  return launch_cast_bf16_rows(src, rowmask, rows, cols, dst_bf16, ST(stream));
+}
+
 int32_t ilfdt_transpose_bf16(const void* src, int32_t src_dtype, int64_t rows, int64_t cols, void* dst_bf16,
                              void* stream) {
   ARCH_GUARD();

@@ -31,7 +31,7 @@ constexpr int UM_BM = 128;
 constexpr int UM_BK = 64;
 constexpr int UM_A_BYTES = UM_BM * UM_BK * 2;  // 16 KB
 constexpr int UM_B_BYTES = 256 * UM_BK * 2;    // 32 KB (max block_n)
-constexpr int UM_THREADS = 192;
+constexpr int UM_THREADS = 320;  // TMA warp + MMA warp + 2 groups of 4 epilogue warps
 constexpr int UM_DATA_BYTES = 229376;          // 224 KB of operand staging
 constexpr int UM_SMEM_BYTES = UM_DATA_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
 constexpr int UM_TMEM_COLS = 512;
@@ -71,7 +71,48 @@ struct UmmaBars {
   uint32_t tmem_ptr;
 };
 
-template <int EPI, bool A_RES>
+// Max/argmax over the token columns of each sample with everything static: NTOK tokens per sample,
+// SPT = 256 / NTOK samples per tile. ~3 instructions per accumulator element (FMNMX, FSETP, SEL), no
+// loop-carried chain longer than one sample, TMEM loads double-buffered against the arithmetic.
+template <int NTOK>
+__device__ __forceinline__ void poolmax_static(uint32_t taddr, int s0, int n_samples, int row, bool row_ok,
+                                               int m_rows, float pool_scale, float* __restrict__ pooled,
+                                               int16_t* __restrict__ arg) {
+  constexpr int SPT = 256 / NTOK, NCOLS = SPT * NTOK, NCH = (NCOLS + 31) / 32;
+  float best[SPT];
+  int bidx[SPT];
+  uint32_t v[2][32];
+  tmem_ld32(taddr, v[0]);
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    tmem_ld_wait();
+    if (c + 1 < NCH) tmem_ld32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
+#pragma unroll
+    for (int s = 0; s < SPT; ++s) {
+      const int lo = s * NTOK > c * 32 ? s * NTOK : c * 32;
+      const int hi = (s + 1) * NTOK < c * 32 + 32 ? (s + 1) * NTOK : c * 32 + 32;
+      if (lo < hi) {
+        float cm = __uint_as_float(v[c & 1][lo - c * 32]);
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (c * 32 + j > lo && c * 32 + j < hi) cm = fmaxf(cm, __uint_as_float(v[c & 1][j]));
+        int ci = lo - s * NTOK;
+#pragma unroll
+        for (int j = 31; j >= 0; --j)  // descending: the lowest token index among ties wins
+          if (c * 32 + j >= lo && c * 32 + j < hi && __uint_as_float(v[c & 1][j]) == cm) ci = c * 32 + j - s * NTOK;
+        if (lo == s * NTOK) { best[s] = cm; bidx[s] = ci; }
+        else if (cm > best[s]) { best[s] = cm; bidx[s] = ci; }
+        if (hi == (s + 1) * NTOK && row_ok && s0 + s < n_samples) {
+          const int64_t o = (int64_t)(s0 + s) * m_rows + row;
+          pooled[o] = best[s] * pool_scale;
+          arg[o] = (int16_t)bidx[s];
+        }
+      }
+    }
+  }
+}
+
+template <int EPI, bool A_RES, int NTOK>
 __global__ void __launch_bounds__(UM_THREADS, 1)
 umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const UmmaParams p) {
   extern __shared__ uint8_t um_smem_raw[];
@@ -167,10 +208,13 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
     }
   } else {
-    // ===================== epilogue warps (2..5) =====================
+    // ===================== epilogue warps (2..9) =====================
+    // two groups of four warps; group g drains accumulator g, i.e. every other tile, so each group has
+    // two MMA tile times to finish one epilogue.
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
+    const uint32_t group = (uint32_t)(warp - 2) >> 2;
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
-    uint32_t acc = 0, acc_phase = 0;
+    uint32_t tile_seq = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
       const int m_tile = item % p.num_m_tiles, chunk = item / p.num_m_tiles;
       const int n_begin = chunk * p.tiles_per_chunk, n_end = min(p.num_n_tiles, n_begin + p.tiles_per_chunk);
@@ -181,7 +225,9 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const float scale = (EPI == EPI_LSE) ? __ldg(p.scale_dev) : 1.f;
       const float scale_log2 = scale * 1.4426950408889634f;
       const float alpha = (EPI == EPI_STORE_T) ? (p.alpha_dev ? p.alpha * __ldg(p.alpha_dev) : p.alpha) : 1.f;
-      for (int n = n_begin; n < n_end; ++n) {
+      for (int n = n_begin; n < n_end; ++n, ++tile_seq) {
+        const uint32_t acc = tile_seq & 1, acc_phase = (tile_seq >> 1) & 1;
+        if (acc != group) continue;
         mbar_wait(&bars->tmem_full[acc], acc_phase);
         fence_after_sync();
         const uint32_t taddr = tmem_base + lane_addr + acc * UM_ACC_COLS;
@@ -204,8 +250,11 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             }
           }
+        } else if (EPI == EPI_POOLMAX && NTOK > 0) {
+          poolmax_static<(NTOK > 0 ? NTOK : 1)>(taddr, n * p.spt, p.n_samples, row, row_ok, p.m_rows, p.pool_scale,
+                                                p.pooled, p.arg);
         } else if (EPI == EPI_POOLMAX) {
-          // columns = tokens of samples [s0, s0 + nsmp), n_tok columns each
+          // generic token count / explicit mask: columns = tokens of samples [s0, s0 + nsmp), n_tok columns each
           const int s0 = n * p.spt;
           const int nsmp = min(p.spt, p.n_samples - s0);
           const int ncols = nsmp * p.n_tok;
@@ -271,12 +320,10 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         fence_before_sync();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
-        acc ^= 1;
-        if (acc == 0) acc_phase ^= 1;
       }
-      if (EPI == EPI_LSE && row_ok) {
-        p.part_m[(int64_t)chunk * p.m_rows + row] = run_m;
-        p.part_s[(int64_t)chunk * p.m_rows + row] = run_s;
+      if (EPI == EPI_LSE && row_ok) {  // one partial per (chunk, epilogue group)
+        p.part_m[(int64_t)(chunk * 2 + group) * p.m_rows + row] = run_m;
+        p.part_s[(int64_t)(chunk * 2 + group) * p.m_rows + row] = run_s;
       }
     }
   }
@@ -361,19 +408,19 @@ static void plan_items(int num_m_tiles, int num_n_tiles, int sms, int& nchunk, i
   nchunk = (int)cdiv(num_n_tiles, tiles_per_chunk);
 }
 
-template <int EPI, bool A_RES>
+template <int EPI, bool A_RES, int NTOK = 0>
 static int32_t launch_umma_t(const CUtensorMap& tmA, const CUtensorMap& tmB, const UmmaParams& p, cudaStream_t st) {
   static thread_local int configured_dev = -1;
   int dev = 0;
   ILFDT_CUDA_OK(cudaGetDevice(&dev));
   if (configured_dev != dev) {
-    ILFDT_CUDA_OK(cudaFuncSetAttribute(umma_kernel<EPI, A_RES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    ILFDT_CUDA_OK(cudaFuncSetAttribute(umma_kernel<EPI, A_RES, NTOK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        UM_SMEM_BYTES));
     configured_dev = dev;
   }
   const int items = p.num_m_tiles * p.nchunk;
   const int grid = std::min(items, sm_count());
-  umma_kernel<EPI, A_RES><<<grid, UM_THREADS, UM_SMEM_BYTES, st>>>(tmA, tmB, p);
+  umma_kernel<EPI, A_RES, NTOK><<<grid, UM_THREADS, UM_SMEM_BYTES, st>>>(tmA, tmB, p);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }
@@ -402,6 +449,15 @@ static int32_t launch_umma(const void* A, const void* B, int64_t M, int64_t N, i
   if (rc != ILFDT_OK) return rc;
   rc = make_tmap_bf16(&tmB, B, N, Kr, Kr, p.block_n);
   if (rc != ILFDT_OK) return rc;
+  if (EPI == EPI_POOLMAX && a_res && p.mask == nullptr) {
+    switch (p.n_tok) {
+      case 49: return launch_umma_t<EPI_POOLMAX, true, 49>(tmA, tmB, p, st);
+      case 77: return launch_umma_t<EPI_POOLMAX, true, 77>(tmA, tmB, p, st);
+      case 196: return launch_umma_t<EPI_POOLMAX, true, 196>(tmA, tmB, p, st);
+      case 256: return launch_umma_t<EPI_POOLMAX, true, 256>(tmA, tmB, p, st);
+      default: break;
+    }
+  }
   return a_res ? launch_umma_t<EPI, true>(tmA, tmB, p, st) : launch_umma_t<EPI, false>(tmA, tmB, p, st);
 }
 
@@ -443,7 +499,7 @@ int32_t launch_ground_fwd_bf16(const void* q, const void* sd, const float* mask,
 
 int64_t nce_fwd_bf16_ws_bytes(int64_t b, int64_t B) {
   // partial (m, s) per (chunk, row) for both directions; chunks <= number of B tiles
-  const int64_t max_chunks = cdiv(B, 256);
+  const int64_t max_chunks = 2 * cdiv(B, 256);
   return 2 * 2 * max_chunks * b * 4 + 256;
 }
 
@@ -454,7 +510,7 @@ int32_t launch_nce_fwd_bf16(const void* x_img, const void* x_txt, const void* g_
                 (long long)D);
   ILFDT_REQUIRE(ws != nullptr && ws_bytes >= nce_fwd_bf16_ws_bytes(b, B), ILFDT_E_INVALID_ARG,
                 "nce_fwd(bf16): workspace too small");
-  const int64_t max_chunks = cdiv(B, 256);
+  const int64_t max_chunks = 2 * cdiv(B, 256);
   float* part = reinterpret_cast<float*>(ws);
   for (int dir = 0; dir < 2; ++dir) {
     UmmaParams p{};
@@ -468,7 +524,7 @@ int32_t launch_nce_fwd_bf16(const void* x_img, const void* x_txt, const void* g_
     // logits_per_image = x_img . g_txt^T ; logits_per_text = x_txt . g_img^T  (clip_fdt.py:421-422)
     int32_t rc = launch_umma<EPI_LSE>(dir == 0 ? x_img : x_txt, dir == 0 ? g_txt : g_img, b, B, D, p, st);
     if (rc != ILFDT_OK) return rc;
-    lse_combine_kernel<<<(unsigned)cdiv(b, 256), 256, 0, st>>>(p.part_m, p.part_s, p.nchunk, b,
+    lse_combine_kernel<<<(unsigned)cdiv(b, 256), 256, 0, st>>>(p.part_m, p.part_s, 2 * p.nchunk, b,
                                                               dir == 0 ? lse_i : lse_t);
     ILFDT_LAUNCH_OK();
   }

@@ -380,6 +380,38 @@ int32_t launch_cast_bf16(const float* src, void* dst, int64_t n, cudaStream_t st
   return ILFDT_OK;
 }
 
+__global__ void cast_bf16_rows_kernel(const float* __restrict__ src, const float* __restrict__ rowmask, int64_t rows,
+                                      int cols, __nv_bfloat16* __restrict__ dst) {
+  // one warp per row-segment of 256 elements (8 per lane); cols % 8 == 0
+  const int64_t total = rows * (int64_t)(cols / 8);
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int64_t r = i / (cols / 8);
+  const int64_t e = i * 8;
+  const bool keep = __ldg(rowmask + r) == 0.f;
+  uint4 o = make_uint4(0, 0, 0, 0);
+  if (keep) {
+    float4 a = __ldg(reinterpret_cast<const float4*>(src + e));
+    float4 b = __ldg(reinterpret_cast<const float4*>(src + e) + 1);
+    __nv_bfloat162 t[4] = {__floats2bfloat162_rn(a.x, a.y), __floats2bfloat162_rn(a.z, a.w),
+                           __floats2bfloat162_rn(b.x, b.y), __floats2bfloat162_rn(b.z, b.w)};
+    o = *reinterpret_cast<uint4*>(t);
+  }
+  *reinterpret_cast<uint4*>(dst + e) = o;
+}
+int32_t launch_cast_bf16_rows(const float* src, const float* rowmask, int64_t rows, int64_t cols, void* dst,
+                              cudaStream_t st) {
+  if (rows * cols == 0) return ILFDT_OK;
+  if (rowmask == nullptr) return launch_cast_bf16(src, dst, rows * cols, st);
+  ILFDT_REQUIRE(cols % 8 == 0 && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0,
+                ILFDT_E_UNSUPPORTED_SHAPE, "cast_bf16_rows: cols %% 8 == 0 and 16-byte aligned pointers required");
+  const int64_t total = rows * (cols / 8);
+  cast_bf16_rows_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(src, rowmask, rows, (int)cols,
+                                                                   reinterpret_cast<__nv_bfloat16*>(dst));
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
 template <typename T>
 __global__ void transpose_bf16_kernel(const T* __restrict__ src, int64_t rows, int64_t cols,
                                       __nv_bfloat16* __restrict__ dst) {

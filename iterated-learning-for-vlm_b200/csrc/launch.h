@@ -24,6 +24,8 @@ int32_t launch_nce_loss(const float* lse_i, const float* diag_i, const float* ls
                         float* loss, cudaStream_t st);
 int32_t launch_topk_hits(const float* L, int64_t b, int64_t B, int64_t label0, int32_t* counts, cudaStream_t st);
 int32_t launch_cast_bf16(const float* src, void* dst, int64_t n, cudaStream_t st);
+int32_t launch_cast_bf16_rows(const float* src, const float* rowmask, int64_t rows, int64_t cols, void* dst,
+                              cudaStream_t st);
 int32_t launch_transpose_bf16(const void* src, int src_dtype, int64_t rows, int64_t cols, void* dst, cudaStream_t st);
 int32_t launch_randn_fill(float* dst, int64_t n, uint64_t seed, uint32_t gen, cudaStream_t st);
 

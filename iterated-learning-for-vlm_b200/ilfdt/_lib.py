@@ -24,6 +24,7 @@ SIGNATURES = {
     "ilfdt_last_error": (ctypes.c_char_p, []),
     "ilfdt_device_check": (_i32, [_i32]),
     "ilfdt_cast_bf16": (_i32, [_p, _p, _i64, _p]),
+    "ilfdt_cast_bf16_rows": (_i32, [_p, _p, _i64, _i64, _p, _p]),
     "ilfdt_transpose_bf16": (_i32, [_p, _i32, _i64, _i64, _p, _p]),
     "ilfdt_ground_fwd_ws_bytes": (_i64, [_i32, _i64, _i64, _i64, _i64]),
     "ilfdt_ground_fwd": (_i32, [_p, _p, _i32, _p, _i64, _i64, _i64, _i64, _f, _f, _i32, _p, _p, _p, _i64, _p]),

@@ -66,11 +66,14 @@ class GroundingFunction(torch.autograd.Function):
                                    and sd.shape[0] % 8 == 0):
             mode = "fp32"   # shapes outside the tcgen05 kernel's tiling take the fp32 CUDA kernels
         if mode == "bf16":
-            q_k = ops.cast_bf16(q)
+            # pad rows are zeroed in the bf16 operand: their tensor-core score is exactly the 0 the
+            # reference's mask multiply yields (clip_fdt.py:125-130), so the fused epilogue needs no mask
+            q_k = ops.cast_bf16_rows(q, mask_f)
             sd_k, sd_kt = _sd_bf16(sd_c)
+            pooled, arg = ops.ground_fwd(q_k, sd_k, None, temperature, "max")
         else:
             q_k, sd_k, sd_kt = q, sd_c, None
-        pooled, arg = ops.ground_fwd(q_k, sd_k, mask_f, temperature, "max")
+            pooled, arg = ops.ground_fwd(q_k, sd_k, mask_f, temperature, "max")
         w, w_b, _tau, _nnz = ops.sparsemax_fwd(pooled, want_bf16=(mode == "bf16"))
         del pooled
         if mode == "bf16":

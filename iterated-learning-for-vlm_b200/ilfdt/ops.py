@@ -19,7 +19,7 @@ def _stream():
 LAUNCHES = 0          # kernels launched through this module since it was last zeroed
 PROFILE_ON = False    # when True every C call is bracketed by CUDA events on the launching stream
 PROFILE = {}          # op name -> [(start_event, end_event), ...]
-_KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_sparsemax_fwd": 1,
+_KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_sparsemax_fwd": 1,
                      "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2,
                      "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5,
                      "ilfdt_nce_bwd": 4, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
@@ -65,6 +65,20 @@ def cast_bf16(x):
     _req(x, torch.float32, "x")
     out = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
     _call("ilfdt_cast_bf16", _ptr(x), _ptr(out), x.numel(), _stream())
+    return out
+
+
+def cast_bf16_rows(x, rowmask):
+    """x [..., C] f32 -> bf16 with the rows whose mask entry is non-zero (-inf = pad) zeroed."""
+    _req(x, torch.float32, "x")
+    if rowmask is None:
+        return cast_bf16(x)
+    _req(rowmask, torch.float32, "rowmask")
+    cols = x.shape[-1]
+    rows = x.numel() // cols
+    assert rowmask.numel() == rows
+    out = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    _call("ilfdt_cast_bf16_rows", _ptr(x), _ptr(rowmask), rows, cols, _ptr(out), _stream())
     return out
 
 

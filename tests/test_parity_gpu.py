@@ -117,6 +117,12 @@ def test_ground_fwd(ops, b, n_tok, K, D, masked, mode):
     pooled, arg = ops.ground_fwd(q.to(_dev()).to(dt), sd.to(_dev()).to(dt), None if mask is None else mask.to(_dev()),
                                  temp, "max")
     assert_close(pooled, ref, FP32_TOL if mode == "fp32" else 2e-5, "pooled (%s)" % mode)
+    if mode == "bf16" and mask is not None and D % 8 == 0:
+        # production route: pad rows zeroed at cast time, no mask in the (statically unrolled) epilogue
+        q_pre = ops.cast_bf16_rows(q.to(_dev()), mask.to(_dev()))
+        pooled2, arg2 = ops.ground_fwd(q_pre, sd.to(_dev()).to(dt), None, temp, "max")
+        assert_close(pooled2, ref, 2e-5, "pooled (pre-masked operand)")
+        assert torch.equal(pooled2, pooled), "masked epilogue and pre-masked operand must agree bit for bit"
     # argmax consistency: the token the kernel reports attains the pooled score (ties / pads aside)
     s_full = torch.matmul(q.double(), sd.double().t()) / math.sqrt(D)
     if mask is not None:
