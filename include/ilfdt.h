@@ -100,11 +100,33 @@ int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs,
  * ilfdt_ground_fwd.  coef[b,k] = nz*(g - mean_nz g) * keep[b,arg] / (sqrt_d*temperature);
  * dq[b,arg[b,k],:] += coef*sd[k,:]  (dq [b,n_tok,D] f32, fully written);
  * dsd[k,:] += coef*q[b,arg[b,k],:]   (dsd [K,D] f32, ACCUMULATED into).
- * Only support entries (w>0) are touched: cost scales with nnz, not with n_tok*K. */
+ * Only support entries (w>0) are touched: cost scales with nnz, not with n_tok*K.
+ * w == NULL: g already holds dLoss/dpooled (softmax / sigmoid attention): no support, no mean to
+ * subtract, every non-zero entry is scattered. */
 int32_t ilfdt_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd,
                          int32_t dtype, const float* mask, int64_t b, int64_t n_tok, int64_t K,
                          int64_t D, float sqrt_d, float temperature,
                          float* dq, float* dsd, void* stream);
+
+/* ---- non-default Query_model variants, clip_fdt.py:67-78,140-157 ----------------------------------- */
+enum { ILFDT_ATT_SOFTMAX = 1, ILFDT_ATT_SIGMOID = 2 };
+/* kind SOFTMAX: w = softmax(z) per row (clip_fdt.py:72). kind SIGMOID: w = sigmoid(z) (:76), rowsum[r] = sum_k w
+ * (the denominator of :156-157; may be NULL for softmax). z, w [rows, K] f32. */
+int32_t ilfdt_att_fwd(const float* z, int64_t rows, int64_t K, int32_t kind, float* w, float* rowsum, void* stream);
+/* SOFTMAX: dz = w * (g - sum_k w g).  SIGMOID: dz = (g + rowbias[r]) * w * (1 - w) (rowbias may be NULL). */
+int32_t ilfdt_att_bwd(const float* w, const float* g, const float* rowbias, int64_t rows, int64_t K, int32_t kind,
+                      float* dz, void* stream);
+/* f = u / s[row]   (att_ft / att_weight.sum, clip_fdt.py:156-157) and its backward:
+ * du = df / s, ds[r] = -(df[r,:] . f[r,:]) / s[r]. u, f, df, du [rows, D]; s, ds [rows]. */
+int32_t ilfdt_rownorm_fwd(const float* u, const float* s, int64_t rows, int64_t D, float* f, void* stream);
+int32_t ilfdt_rownorm_bwd(const float* df, const float* f, const float* s, int64_t rows, int64_t D, float* du,
+                          float* ds, void* stream);
+/* sum / mean token pooling goes through the token-summed query: out[b,:] = sum_t keep[b,t] q[b,t,:]  (q f32
+ * [b,n_tok,D]) and, for the backward, out[b,t,:] = keep[b,t] * scale * v[b,:]. */
+int32_t ilfdt_token_sum(const float* q, const float* mask, int64_t b, int64_t n_tok, int64_t D, float* out,
+                        void* stream);
+int32_t ilfdt_token_bcast(const float* v, const float* mask, int64_t b, int64_t n_tok, int64_t D, float scale,
+                          float* out, void* stream);
 
 /* ---- a5: L2 normalise, clip_fdt.py:411-412 / clip.py:133-134 ------------------------------ */
 /* x = f / (||f|| + eps); x_bf16 optional copy; norm[rows] = ||f||. */

@@ -208,8 +208,53 @@ int32_t ilfdt_ground_bwd(float* g, const float* w, const int16_t* arg, const voi
   ARCH_GUARD();
   DTYPE_GUARD(dtype);
   ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && K >= 1 && D >= 1, ILFDT_E_INVALID_ARG, "ground_bwd: bad shape");
-  ILFDT_REQUIRE(b == 0 || (g && w && arg && q && sd && dq && dsd), ILFDT_E_INVALID_ARG, "ground_bwd: null pointer");
+  ILFDT_REQUIRE(b == 0 || (g && arg && q && sd && dq && dsd), ILFDT_E_INVALID_ARG, "ground_bwd: null pointer");
   return launch_ground_bwd(g, w, arg, q, sd, dtype, mask, b, n_tok, K, D, sqrt_d, temperature, dq, dsd, ST(stream));
+}
+
+int32_t ilfdt_att_fwd(const float* z, int64_t rows, int64_t K, int32_t kind, float* w, float* rowsum, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(rows >= 0 && K >= 1 && (rows == 0 || (z && w)), ILFDT_E_INVALID_ARG, "att_fwd: bad arguments");
+  ILFDT_REQUIRE(kind == ILFDT_ATT_SOFTMAX || kind == ILFDT_ATT_SIGMOID, ILFDT_E_INVALID_ARG, "att_fwd: bad kind");
+  return launch_att_fwd(z, rows, K, kind, w, rowsum, ST(stream));
+}
+
+int32_t ilfdt_att_bwd(const float* w, const float* g, const float* rowbias, int64_t rows, int64_t K, int32_t kind,
+                      float* dz, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(rows >= 0 && K >= 1 && (rows == 0 || (w && g && dz)), ILFDT_E_INVALID_ARG, "att_bwd: bad arguments");
+  ILFDT_REQUIRE(kind == ILFDT_ATT_SOFTMAX || kind == ILFDT_ATT_SIGMOID, ILFDT_E_INVALID_ARG, "att_bwd: bad kind");
+  return launch_att_bwd(w, g, rowbias, rows, K, kind, dz, ST(stream));
+}
+
+int32_t ilfdt_rownorm_fwd(const float* u, const float* s, int64_t rows, int64_t D, float* f, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(rows >= 0 && D >= 1 && (rows == 0 || (u && s && f)), ILFDT_E_INVALID_ARG, "rownorm_fwd: bad arguments");
+  return launch_rownorm_fwd(u, s, rows, D, f, ST(stream));
+}
+
+int32_t ilfdt_rownorm_bwd(const float* df, const float* f, const float* s, int64_t rows, int64_t D, float* du,
+                          float* ds, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(rows >= 0 && D >= 1 && (rows == 0 || (df && f && s && du && ds)), ILFDT_E_INVALID_ARG,
+                "rownorm_bwd: bad arguments");
+  return launch_rownorm_bwd(df, f, s, rows, D, du, ds, ST(stream));
+}
+
+int32_t ilfdt_token_sum(const float* q, const float* mask, int64_t b, int64_t n_tok, int64_t D, float* out,
+                        void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && D >= 1 && (b == 0 || (q && out)), ILFDT_E_INVALID_ARG,
+                "token_sum: bad arguments");
+  return launch_token_sum(q, mask, b, n_tok, D, out, ST(stream));
+}
+
+int32_t ilfdt_token_bcast(const float* v, const float* mask, int64_t b, int64_t n_tok, int64_t D, float scale,
+                          float* out, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && D >= 1 && (b == 0 || (v && out)), ILFDT_E_INVALID_ARG,
+                "token_bcast: bad arguments");
+  return launch_token_bcast(v, mask, b, n_tok, D, scale, out, ST(stream));
 }
 
 int32_t ilfdt_l2norm_fwd(const float* f, int64_t rows, int64_t D, float eps, float* x, void* x_bf16, float* norm,

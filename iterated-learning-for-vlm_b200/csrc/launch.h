@@ -50,6 +50,18 @@ int32_t launch_nce_fwd_bf16(const void* x_img, const void* x_txt, const void* g_
                             int64_t B, int64_t D, const float* scale, int64_t label_offset, float* lse_i, float* lse_t,
                             float* diag_i, float* diag_t, void* ws, int64_t ws_bytes, cudaStream_t st);
 
+// rowops.cu
+int32_t launch_att_fwd(const float* z, int64_t rows, int64_t K, int kind, float* w, float* rowsum, cudaStream_t st);
+int32_t launch_att_bwd(const float* w, const float* g, const float* rowbias, int64_t rows, int64_t K, int kind,
+                       float* dz, cudaStream_t st);
+int32_t launch_rownorm_fwd(const float* u, const float* s, int64_t rows, int64_t D, float* f, cudaStream_t st);
+int32_t launch_rownorm_bwd(const float* df, const float* f, const float* s, int64_t rows, int64_t D, float* du,
+                           float* ds, cudaStream_t st);
+int32_t launch_token_sum(const float* q, const float* mask, int64_t b, int64_t n_tok, int64_t D, float* out,
+                         cudaStream_t st);
+int32_t launch_token_bcast(const float* v, const float* mask, int64_t b, int64_t n_tok, int64_t D, float scale,
+                           float* out, cudaStream_t st);
+
 // nce_bwd_umma.cu (tcgen05)
 int64_t nce_bwd_bf16_ws_bytes(int64_t b, int64_t B, int64_t D);
 int32_t launch_nce_bwd_bf16(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt,

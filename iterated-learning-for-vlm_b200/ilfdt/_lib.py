@@ -33,6 +33,12 @@ SIGNATURES = {
     "ilfdt_gemm_nt": (_i32, [_p, _p, _i32, _i64, _i64, _i64, _f, _i32, _p, _i64, _p]),
     "ilfdt_gemm_f32_strided": (_i32, [_p, _i64, _i64, _p, _i64, _i64, _p, _i64, _i64, _i64, _i64, _i64, _f, _i32, _p]),
     "ilfdt_ground_bwd": (_i32, [_p, _p, _p, _p, _p, _i32, _p, _i64, _i64, _i64, _i64, _f, _f, _p, _p, _p]),
+    "ilfdt_att_fwd": (_i32, [_p, _i64, _i64, _i32, _p, _p, _p]),
+    "ilfdt_att_bwd": (_i32, [_p, _p, _p, _i64, _i64, _i32, _p, _p]),
+    "ilfdt_rownorm_fwd": (_i32, [_p, _p, _i64, _i64, _p, _p]),
+    "ilfdt_rownorm_bwd": (_i32, [_p, _p, _p, _i64, _i64, _p, _p, _p]),
+    "ilfdt_token_sum": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p]),
+    "ilfdt_token_bcast": (_i32, [_p, _p, _i64, _i64, _i64, _f, _p, _p]),
     "ilfdt_l2norm_fwd": (_i32, [_p, _i64, _i64, _f, _p, _p, _p, _p]),
     "ilfdt_l2norm_bwd": (_i32, [_p, _p, _p, _i64, _i64, _f, _p, _p]),
     "ilfdt_logits": (_i32, [_p, _p, _i32, _i64, _i64, _i64, _p, _p, _p]),

@@ -1,6 +1,7 @@
 """torch.autograd.Function wrappers: each forward/backward is a handful of libilfdt calls. These are
 the seams between the reference-shaped nn.Modules (ilfdt.model, ilfdt.loss_functions) and the
 kernels. Reference lines cited are relative to the reference repo root."""
+import math
 import os
 
 import torch
@@ -110,6 +111,60 @@ class GroundingFunction(torch.autograd.Function):
             g = dw.contiguous().float().clone()
         dq = ops.ground_bwd(g, w, arg, q_k, sd_k, mask_f, ctx.temperature, dsd)
         return dq, dsd, None, None, None
+
+
+class GroundingVariantFunction(torch.autograd.Function):
+    """Query_model.forward from q onward for the non-default-tuned combinations of
+    att_func_type in {softmax, sigmoid, sparsemax} x pool_type in {sum, mean, max} (clip_fdt.py:67-78,
+    140-157). fp32 CUDA kernels throughout (these are epilogue variants, not the tuned path)."""
+
+    @staticmethod
+    def forward(ctx, q, sd, mask, temperature, att, pool):
+        q = q.contiguous().float()
+        sd_c = sd.contiguous().float()
+        mask_f = None if mask is None else mask.to(torch.float32).contiguous()
+        pooled, arg = ops.ground_fwd(q, sd_c, mask_f, temperature, pool)
+        rowsum = None
+        if att == "sparsemax":
+            w = ops.sparsemax_fwd(pooled)[0]
+        else:
+            w, rowsum = ops.att_fwd(pooled, att)
+        u = ops.gemm_f32(w, sd_c)                                   # clip_fdt.py:154
+        f = ops.rownorm_fwd(u, rowsum) if att == "sigmoid" else u   # :156-157
+        ctx.att, ctx.pool, ctx.temperature = att, pool, float(temperature)
+        ctx.save_for_backward(q, sd_c, mask_f, w, arg, rowsum, f)
+        return w, f
+
+    @staticmethod
+    def backward(ctx, dw, df):
+        q, sd_c, mask_f, w, arg, rowsum, f = ctx.saved_tensors
+        att, pool = ctx.att, ctx.pool
+        b, n_tok, D = q.shape
+        K = sd_c.shape[0]
+        dsd = torch.zeros(K, D, dtype=torch.float32, device=q.device)
+        ds = None
+        if df is not None:
+            df = df.contiguous().float()
+            du = df
+            if att == "sigmoid":
+                du, ds = ops.rownorm_bwd(df, f, rowsum)
+            g = ops.gemm_f32(du, sd_c, b_t=True)
+            ops.gemm_f32(w, du, a_t=True, out=dsd, accumulate=True)
+            if dw is not None:
+                g.add_(dw)
+        else:
+            g = dw.contiguous().float().clone()
+        if att == "sparsemax":
+            dz = ops.sparsemax_bwd(w, g)
+        else:
+            dz = ops.att_bwd(w, g, att, rowbias=ds if att == "sigmoid" else None)
+        if pool == "max":
+            dq = ops.ground_bwd(dz, None, arg, q, sd_c, mask_f, ctx.temperature, dsd)
+        else:
+            c = 1.0 / (math.sqrt(D) * ctx.temperature) / (n_tok if pool == "mean" else 1)
+            dq = ops.token_bcast(ops.gemm_f32(dz, sd_c), mask_f, n_tok, c)
+            ops.gemm_f32(dz, ops.token_sum(q, mask_f), a_t=True, alpha=c, out=dsd, accumulate=True)
+        return dq, dsd, None, None, None, None
 
 
 class SparsemaxFunction(torch.autograd.Function):

@@ -33,15 +33,11 @@ class Query_model(nn.Module):
         super().__init__()
         assert att_func_type in ['softmax', 'sigmoid', 'sparsemax']
         assert pool_type in ['mean', 'max', 'sum']
-        if att_func_type != 'sparsemax' or pool_type != 'max':
-            # the shipped configs use sparsemax + max (config_cc3m.yaml:14-21); the other epilogue
-            # variants are not built yet and there is deliberately no PyTorch fallback
-            raise NotImplementedError(
-                "ilfdt Query_model: only att_func_type='sparsemax', pool_type='max' is implemented on the "
-                "CUDA path (got %s/%s)" % (att_func_type, pool_type))
         self.att_func_type = att_func_type
         self.pool_type = pool_type
-        self.att_activation = Sparsemax(dim=-1)
+        # kept for state_dict / attribute compatibility (clip_fdt.py:71-78); the arithmetic runs in libilfdt
+        self.att_activation = Sparsemax(dim=-1) if att_func_type == 'sparsemax' else (
+            nn.Softmax(dim=-1) if att_func_type == 'softmax' else nn.Sigmoid())
         self.att_dim = sd_dim
         self.temperature = temperature   # plain Python float, rewritten by the solver (train_solver.py:363-364)
         self.q_map = nn.Sequential(
@@ -56,8 +52,13 @@ class Query_model(nn.Module):
         q = self.q_map(ft)
         if mask is not None:
             assert mask.shape == q.shape[:2]
-        att_weight, att_ft = Fn.GroundingFunction.apply(q, sd, mask, float(self.temperature),
-                                                        Fn.get_compute_dtype())
+        if self.att_func_type == 'sparsemax' and self.pool_type == 'max':
+            # the shipped configuration (config_cc3m.yaml:14-21): tuned tensor-core path
+            att_weight, att_ft = Fn.GroundingFunction.apply(q, sd, mask, float(self.temperature),
+                                                            Fn.get_compute_dtype())
+        else:
+            att_weight, att_ft = Fn.GroundingVariantFunction.apply(q, sd, mask, float(self.temperature),
+                                                                   self.att_func_type, self.pool_type)
         if return_token_att:
             return self._token_scores(q, sd, mask), att_ft, sd
         return att_weight, att_ft, sd

@@ -165,7 +165,9 @@ def gemm_f32(A, B, a_t=False, b_t=False, alpha=1.0, out=None, accumulate=False):
 
 def ground_bwd(g, w, arg, q, sd, mask, temperature, dsd):
     """g [b,K] is overwritten with coef. Returns dq [b,N,D] f32; accumulates into dsd [K,D] f32."""
-    _req(g, torch.float32, "g"); _req(w, torch.float32, "w"); _req(arg, torch.int16, "arg")
+    _req(g, torch.float32, "g"); _req(arg, torch.int16, "arg")
+    if w is not None:   # None: g already is dLoss/dpooled (softmax / sigmoid attention)
+        _req(w, torch.float32, "w")
     _req(q, None, "q"); _req(sd, q.dtype, "sd"); _req(dsd, torch.float32, "dsd")
     b, n_tok, D = q.shape
     K = sd.shape[0]
@@ -174,6 +176,58 @@ def ground_bwd(g, w, arg, q, sd, mask, temperature, dsd):
                                        n_tok, K, D, float(math.sqrt(D)), float(temperature), _ptr(dq), _ptr(dsd),
                                        _stream())
     return dq
+
+
+ATT_KINDS = {"softmax": 1, "sigmoid": 2}
+
+
+def att_fwd(z, kind):
+    """softmax / sigmoid over the last dim of z [rows,K] -> (w, rowsum [rows])"""
+    _req(z, torch.float32, "z")
+    rows, K = z.shape
+    w = torch.empty_like(z)
+    rowsum = torch.empty(rows, dtype=torch.float32, device=z.device)
+    _call("ilfdt_att_fwd", _ptr(z), rows, K, ATT_KINDS[kind], _ptr(w), _ptr(rowsum), _stream())
+    return w, rowsum
+
+
+def att_bwd(w, g, kind, rowbias=None):
+    _req(w, torch.float32, "w"); _req(g, torch.float32, "g")
+    dz = torch.empty_like(w)
+    _call("ilfdt_att_bwd", _ptr(w), _ptr(g), _ptr(rowbias), w.shape[0], w.shape[1], ATT_KINDS[kind], _ptr(dz),
+          _stream())
+    return dz
+
+
+def rownorm_fwd(u, s):
+    _req(u, torch.float32, "u"); _req(s, torch.float32, "s")
+    f = torch.empty_like(u)
+    _call("ilfdt_rownorm_fwd", _ptr(u), _ptr(s), u.shape[0], u.shape[1], _ptr(f), _stream())
+    return f
+
+
+def rownorm_bwd(df, f, s):
+    _req(df, torch.float32, "df"); _req(f, torch.float32, "f")
+    du = torch.empty_like(df)
+    ds = torch.empty_like(s)
+    _call("ilfdt_rownorm_bwd", _ptr(df), _ptr(f), _ptr(s), df.shape[0], df.shape[1], _ptr(du), _ptr(ds), _stream())
+    return du, ds
+
+
+def token_sum(q, mask):
+    _req(q, torch.float32, "q")
+    b, n_tok, D = q.shape
+    out = torch.empty(b, D, dtype=torch.float32, device=q.device)
+    _call("ilfdt_token_sum", _ptr(q), _ptr(mask), b, n_tok, D, _ptr(out), _stream())
+    return out
+
+
+def token_bcast(v, mask, n_tok, scale):
+    _req(v, torch.float32, "v")
+    b, D = v.shape
+    out = torch.empty(b, n_tok, D, dtype=torch.float32, device=v.device)
+    _call("ilfdt_token_bcast", _ptr(v), _ptr(mask), b, n_tok, D, float(scale), _ptr(out), _stream())
+    return out
 
 
 def l2norm_fwd(f, eps, want_bf16=False):

@@ -66,8 +66,9 @@ def test_no_cpu_fallback(built_lib):
     with pytest.raises(RuntimeError):
         GroundingFunction.apply(torch.randn(2, 3, 8), torch.randn(5, 8), None, 1.0, "fp32")
     from ilfdt.model.clip_fdt import Query_model
-    with pytest.raises(NotImplementedError):
-        Query_model(8, 8)  # softmax/sum defaults are not built on the CUDA path: loud, not silent
+    qm = Query_model(8, 8)  # reference defaults: softmax attention, sum pooling (clip_fdt.py:55)
+    with pytest.raises(RuntimeError):
+        qm(torch.randn(2, 3, 8), torch.randn(5, 8))  # CPU tensors: loud, not a silent torch fallback
 
 
 def test_product_path_never_imports_the_oracle():

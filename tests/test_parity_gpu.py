@@ -235,6 +235,41 @@ def test_grounding_fwd_bwd(ops, b, n_tok, K, D, masked, mode):
             assert margin < 1e-8, "support sets differ at entries with weight up to %.3e" % margin
 
 
+QM_VARIANTS = [("smax", "sparsemax", "max"), ("smaxT", "sparsemax", "max"), ("softsum", "softmax", "sum"),
+               ("sigmean", "sigmoid", "mean"), ("softmax_max", "softmax", "max"), ("smax_mean", "sparsemax", "mean")]
+
+
+@pytest.mark.parametrize("name,att,pool", QM_VARIANTS)
+@pytest.mark.parametrize("tag", ["nomask", "mask"])
+def test_query_model_golden_all_variants(ops, golden_dir, name, att, pool, tag):
+    """The drop-in Query_model (every att_func_type x pool_type the reference's constructor accepts) against the
+    outputs and gradients of the unmodified reference Query_model (tests/golden/query_model.npz)."""
+    import ilfdt
+    from ilfdt.model.clip_fdt import Query_model
+    z = np.load(os.path.join(golden_dir, "query_model.npz"))
+    dev = _dev()
+    ft = torch.tensor(z[name + "_ft"], device=dev, requires_grad=True)
+    sd = torch.tensor(z[name + "_sd"], device=dev, requires_grad=True)
+    mask = torch.tensor(z[name + "_mask"], device=dev) if tag == "mask" else None
+    qm = Query_model(ft.shape[-1], sd.shape[-1], temperature=float(z[name + "_temp"]), att_func_type=att,
+                     pool_type=pool).to(dev)
+    qm.load_state_dict({k[len(name) + 7:]: torch.tensor(z[k]) for k in z.files if k.startswith(name + "_state_")})
+    pre = f"{name}_{tag}_"
+    with ilfdt.compute_dtype("fp32"):
+        w, f, sd_out = qm(ft, sd, mask=mask)
+        assert sd_out is sd
+        ((w * torch.tensor(z[name + "_up_w"], device=dev)).sum()
+         + (f * torch.tensor(z[name + "_up_f"], device=dev)).sum()).backward()
+        tok, f2, _ = qm(ft, sd, mask=mask, return_token_att=True)
+    assert_close(w, torch.tensor(z[pre + "w"]), 2e-5, "att_weight")
+    assert_close(f, torch.tensor(z[pre + "f"]), 2e-5, "att_ft")
+    assert_close(tok, torch.tensor(z[pre + "token_att"]), 2e-5, "token_att")
+    assert_close(ft.grad, torch.tensor(z[pre + "d_ft"]), 1e-4, "d_ft")
+    assert_close(sd.grad, torch.tensor(z[pre + "d_sd"]), 1e-4, "d_sd")
+    for k, v in qm.named_parameters():
+        assert_close(v.grad, torch.tensor(z[pre + "d_" + k]), 1e-4, "d_" + k)
+
+
 # ---------------------------------------------------------------------------------------------------
 # a5: L2 normalise
 # ---------------------------------------------------------------------------------------------------
