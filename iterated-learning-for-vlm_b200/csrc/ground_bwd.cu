@@ -330,6 +330,7 @@ ground_bwd_dq_sorted_kernel(float* __restrict__ g, const float* __restrict__ w, 
   int* base = hist + GB_WARPS * n_tok;                                      // [n_tok + 1]
   __shared__ double red_s[GB_WARPS];
   __shared__ int red_c[GB_WARPS];
+  __shared__ int next_tok;
   const int64_t b = blockIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float* gr = g + b * K;
@@ -405,7 +406,7 @@ ground_bwd_dq_sorted_kernel(float* __restrict__ g, const float* __restrict__ w, 
         const int t = lane * per + j;
         if (t < n_tok) { run += base[t + 1]; base[t + 1] = run; }
       }
-      if (lane == 0) base[0] = 0;
+      if (lane == 0) { base[0] = 0; next_tok = 0; }
     }
     __syncthreads();
     // pass 2: stable placement
@@ -426,7 +427,11 @@ ground_bwd_dq_sorted_kernel(float* __restrict__ g, const float* __restrict__ w, 
     }
     __syncthreads();
 
-    for (int t = warp; t < n_tok; t += GB_WARPS) {
+    for (;;) {  // tokens are handed out dynamically: entry counts per token are uneven
+      int t = 0;
+      if (lane == 0) t = atomicAdd(&next_tok, 1);
+      t = __shfl_sync(0xffffffffu, t, 0);
+      if (t >= n_tok) break;
       const int lo = base[t], hi = base[t + 1];
       float acc[NV][8];
 #pragma unroll

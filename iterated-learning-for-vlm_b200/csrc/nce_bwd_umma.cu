@@ -21,13 +21,13 @@ namespace ilfdt {
 
 using namespace umma;
 
-constexpr int NB_THREADS = 192;
+constexpr int NB_THREADS = 320;  // TMA warp, MMA warp, 2 softmax groups of 4 warps (group g owns S buffer g)
 constexpr int NB_XL_BYTES = 8 * 16384;          // lane tile, all k-blocks: 128 KB
 constexpr int NB_Y_STAGE = 64 * 64 * 2;         // 64 stream rows x 64 k      : 8 KB
-constexpr int NB_Y_STAGES = 2;
+constexpr int NB_Y_STAGES = 6;          // deep ring: MMA1 consumes 8 of these 8 KB boxes per S tile (2 stages left it TMA-latency-bound)
 constexpr int NB_P_BYTES = 128 * 64 * 2;        // P tile 128 lanes x 64 stream: 16 KB
 constexpr int NB_YT_STAGE = 256 * 64 * 2;       // 256 D-columns x 64 stream   : 32 KB
-constexpr int NB_YT_STAGES = 2;
+constexpr int NB_YT_STAGES = 1;
 constexpr int NB_OFF_Y = NB_XL_BYTES;
 constexpr int NB_OFF_P = NB_OFF_Y + NB_Y_STAGES * NB_Y_STAGE;
 constexpr int NB_OFF_YT = NB_OFF_P + NB_P_BYTES;
@@ -86,7 +86,7 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
     mbar_init(&bars->p_full, 4);
     mbar_init(&bars->p_empty, 1);
     mbar_init(&bars->d_full, 1);
-    mbar_init(&bars->d_empty, 4);
+    mbar_init(&bars->d_empty, 8);
     fence_barrier_init();
     tma_prefetch_desc(&tmXL);
     tma_prefetch_desc(&tmY);
@@ -187,13 +187,14 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
   } else {
     // ===================== softmax + epilogue warps (2..5) =====================
     const int quad = warp & 3;
-    const int tid128 = (warp - 2) * 32 + lane;
+    const uint32_t group = (uint32_t)(warp - 2) >> 2;
+    const int tid128 = ((warp - 2) & 3) * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     const int r_in_tile = quad * 32 + lane;
     const float gw = __ldg(p.grad_out) * p.inv_2b;
     const float scale = __ldg(p.scale_dev);
     const float scale_log2 = scale * 1.4426950408889634f;
-    uint32_t tile_ctr = 0, p_ctr = 0, it = 0;
+    uint32_t tile_ctr = 0, it = 0;
     uint8_t* p_row = smem + NB_OFF_P + r_in_tile * 128;
     const int sw = r_in_tile & 7;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
@@ -201,15 +202,19 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
       const int half = lh % p.num_halves, lt = lh / p.num_halves;
       const int t_begin = split * p.tiles_per_split, t_end = min(p.num_stream_tiles, t_begin + p.tiles_per_split);
       const int row = lt * 128 + r_in_tile;
+      // label column (stream index) matching this lane row, or an index that never occurs
+      const long long jl = p.lse_by_lane ? p.label_offset + row          // stream j == label_offset + lane row
+                                         : (long long)row - p.label_offset;  // lane row == label_offset + stream j
       const bool row_ok = row < p.RL;
       const float lse_lane = (p.lse_by_lane && row_ok) ? __ldg(p.lse + row) * 1.4426950408889634f : 0.f;
       float ds_acc = 0.f;
-      for (int t = t_begin; t < t_end; ++t) {
+      for (int t = t_begin; t < t_end; ++t, ++tile_ctr) {
         const uint32_t sb = tile_ctr & 1, sph = (tile_ctr >> 1) & 1;
+        if (sb != group) continue;  // the other softmax group converts this tile
         const int j0 = t * 64;
         if (!p.lse_by_lane) {
           if (tid128 < 64) bars->lse_s[sb][tid128] = (j0 + tid128 < p.RS) ? __ldg(p.lse + j0 + tid128) * 1.4426950408889634f : 0.f;
-          named_bar_sync(1, 128);
+          named_bar_sync(1 + (int)group, 128);
         }
         mbar_wait(&bars->s_full[sb], sph);
         fence_after_sync();
@@ -220,12 +225,6 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
         fence_before_sync();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->s_empty[sb]);
-        ++tile_ctr;
-
-        // label column (stream index) matching this lane row, or -1
-        long long jl;
-        if (p.lse_by_lane) jl = p.label_offset + row;  // stream j == label_offset + lane row
-        else jl = (long long)row - p.label_offset;     // lane row == label_offset + stream j
         uint32_t packed[32];
 #pragma unroll
         for (int h2 = 0; h2 < 2; ++h2) {
@@ -249,7 +248,7 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
           }
         }
         // P buffer free? (MMA2 of the previous tile finished reading it)
-        mbar_wait(&bars->p_empty, (p_ctr & 1) ^ 1);
+        mbar_wait(&bars->p_empty, (tile_ctr & 1) ^ 1);  // P is single-buffered: phases follow the global tile index
         // 8 chunks of 16 B (8 bf16 each), 128-byte swizzle: chunk c of row r lives at c ^ (r & 7)
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
@@ -259,13 +258,12 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
         fence_proxy_async_smem();  // make the generic-proxy writes visible to the tensor core (async proxy)
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->p_full);
-        ++p_ctr;
       }
       // ---- epilogue: dOut (TMEM columns 0..255) -> global ----
       mbar_wait(&bars->d_full, it & 1);
       fence_after_sync();
       const int dcols = min(256, p.D - half * 256);
-      for (int c0 = 0; c0 < dcols; c0 += 32) {
+      for (int c0 = (int)group * 128; c0 < min(dcols, (int)group * 128 + 128); c0 += 32) {  // each group stores 128 columns
         uint32_t v[32];
         tmem_ld32(tmem_base + lane_addr + c0, v);
         tmem_ld_wait();
