@@ -207,7 +207,7 @@ def run_ours(args):
         s.data = torch.clamp(s.data, max=100)
         g_i = Fn.AllGather.apply(x_i).view(-1, D_DIM)
         g_t = Fn.AllGather.apply(x_t).view(-1, D_DIM)
-        loss = Fn.InfoNCEFunction.apply(x_i, x_t, g_i, g_t, s, label_offset, mode)
+        loss = Fn.InfoNCEFunction.apply(x_i, x_t, g_i, g_t, s, label_offset, mode, True)
         loss.backward()
         return loss
 

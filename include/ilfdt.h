@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define ILFDT_ABI_VERSION 1
+#define ILFDT_ABI_VERSION 2
 
 enum {
   ILFDT_OK = 0,
@@ -157,14 +157,25 @@ int32_t ilfdt_nce_fwd(const void* x_img, const void* x_txt, const void* g_img, c
  * grad_out/(2b) is recomputed tile by tile from lse_*. Outputs (all f32, overwritten):
  * dx_img, dx_txt [b,D]; dg_img, dg_txt [B,D] (gradient w.r.t. the gathered copies, to be
  * reduce-scattered by the caller: AllGather.backward, clip_fdt.py:182-188); dscale[0] = dLoss/dscale.
- * In BF16 mode g_img_t/g_txt_t [D,B] and x_img_t/x_txt_t [D,b] are bf16 transposes of the inputs
- * (ilfdt_transpose_bf16); F32 mode ignores them (may be NULL). */
+ * For callers whose g_* are independent tensors; training uses ilfdt_nce_bwd_gathered. */
 int32_t ilfdt_nce_bwd(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt,
-                      const void* x_img_t, const void* x_txt_t, const void* g_img_t, const void* g_txt_t,
                       int32_t dtype, int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset,
                       const float* lse_i, const float* lse_t, const float* grad_out,
                       float* dx_img, float* dx_txt, float* dg_img, float* dg_txt, float* dscale,
                       void* ws, int64_t ws_bytes, void* stream);
+/* Fused InfoNCE backward when g_img/g_txt ARE the all-gather of every rank's x_img/x_txt (rank-major,
+ * this rank's rows at label_offset = rank*b; clip_fdt.py:418-419). With the all-gathered per-row
+ * log-sum-exps lse_i_all/lse_t_all [B] (ilfdt_nce_fwd outputs of all ranks) and every rank's upstream
+ * dLoss grad_out_all [B/b], each rank forms the TOTAL gradient of its own rows directly,
+ *   dx_img[i] = scale * sum_j ( P_img[i,j] + P_txt[j,i] ) g_txt[j],   dx_txt likewise,
+ * which equals the reference's dX + (all_reduce(dG))[rank] (clip_fdt.py:182-188) with the [B,D]
+ * gradient exchange replaced by a [B]-float all-gather and half the contractions. dscale[0] is the
+ * rank-local dLoss/dscale of this rank's own logits rows, as in ilfdt_nce_bwd. */
+int32_t ilfdt_nce_bwd_gathered(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt,
+                               int32_t dtype, int64_t b, int64_t B, int64_t D, const float* scale,
+                               int64_t label_offset, const float* lse_i_all, const float* lse_t_all,
+                               const float* grad_out_all, float* dx_img, float* dx_txt, float* dscale,
+                               void* ws, int64_t ws_bytes, void* stream);
 
 /* Cross-entropy over STORED logits [b,B] (the route taken when a caller hands ClipInfoCELoss real
  * tensors instead of the fused stash): lse[r], diag[r] = logits[r, label_offset + r]. */

@@ -92,6 +92,37 @@ static int32_t nce_bwd_f32(const float* x_img, const float* x_txt, const float* 
   return ILFDT_OK;
 }
 
+// Gathered form of the F32 route (see ilfdt_nce_bwd_gathered): per direction, for a chunk of local rows,
+// L = scale * X . G^T, P = lane softmax + stream softmax terms, dX = scale * P . G.
+static int32_t nce_bwd_gathered_f32(const float* x_img, const float* x_txt, const float* g_img, const float* g_txt,
+                                    int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset,
+                                    const float* lse_i_all, const float* lse_t_all, const float* go_all, float* dx_img,
+                                    float* dx_txt, float* dscale, void* ws, int64_t ws_bytes, cudaStream_t st) {
+  const int64_t R = nce_f32_chunk_rows(b, B);
+  ILFDT_REQUIRE(ws != nullptr && ws_bytes >= R * B * 4, ILFDT_E_INVALID_ARG, "nce_bwd(f32): workspace too small");
+  float* L = reinterpret_cast<float*>(ws);
+  ILFDT_CUDA_OK(cudaMemsetAsync(dscale, 0, 4, st));
+  const float coef = 1.f / (2.f * (float)b);
+  for (int dir = 0; dir < 2; ++dir) {
+    const float* X = dir == 0 ? x_img : x_txt;
+    const float* G = dir == 0 ? g_txt : g_img;
+    const float* lse_lane = (dir == 0 ? lse_i_all : lse_t_all) + label_offset;
+    const float* lse_stream = dir == 0 ? lse_t_all : lse_i_all;
+    float* dX = dir == 0 ? dx_img : dx_txt;
+    for (int64_t r0 = 0; r0 < b; r0 += R) {
+      const int64_t rows = std::min(R, b - r0);
+      int32_t rc = launch_gemm_f32(X + r0 * D, D, 1, G, D, 1, L, B, 1, rows, B, D, 1.f, scale, 0, st);
+      if (rc != ILFDT_OK) return rc;
+      rc = launch_softmax_grad_sym_rows(L, L, B, rows, B, label_offset + r0, lse_lane + r0, lse_stream,
+                                        go_all + label_offset / b, go_all, b, coef, scale, dscale, st);
+      if (rc != ILFDT_OK) return rc;
+      rc = launch_gemm_f32(L, B, 1, G, 1, D, dX + r0 * D, D, 1, rows, D, B, 1.f, scale, 0, st);
+      if (rc != ILFDT_OK) return rc;
+    }
+  }
+  return ILFDT_OK;
+}
+
 }  // namespace ilfdt
 
 using namespace ilfdt;
@@ -312,8 +343,7 @@ int32_t ilfdt_nce_fwd(const void* x_img, const void* x_txt, const void* g_img, c
   return launch_nce_loss(lse_i, diag_i, lse_t, diag_t, b, loss, ST(stream));
 }
 
-int32_t ilfdt_nce_bwd(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt, const void* x_img_t,
-                      const void* x_txt_t, const void* g_img_t, const void* g_txt_t, int32_t dtype, int64_t b,
+int32_t ilfdt_nce_bwd(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt, int32_t dtype, int64_t b,
                       int64_t B, int64_t D, const float* scale, int64_t label_offset, const float* lse_i,
                       const float* lse_t, const float* grad_out, float* dx_img, float* dx_txt, float* dg_img, float* dg_txt,
                       float* dscale, void* ws, int64_t ws_bytes, void* stream) {
@@ -329,11 +359,30 @@ int32_t ilfdt_nce_bwd(const void* x_img, const void* x_txt, const void* g_img, c
                        reinterpret_cast<const float*>(g_img), reinterpret_cast<const float*>(g_txt), b, B, D, scale,
                        label_offset, lse_i, lse_t, grad_out, dx_img, dx_txt, dg_img, dg_txt, dscale, ws, ws_bytes,
                        ST(stream));
-  ILFDT_REQUIRE(x_img_t && x_txt_t && g_img_t && g_txt_t, ILFDT_E_INVALID_ARG,
-                "nce_bwd(bf16): transposed operands required");
-  return launch_nce_bwd_bf16(x_img, x_txt, g_img, g_txt, x_img_t, x_txt_t, g_img_t, g_txt_t, b, B, D, scale,
-                             label_offset, lse_i, lse_t, grad_out, dx_img, dx_txt, dg_img, dg_txt, dscale, ws,
-                             ws_bytes, ST(stream));
+  return launch_nce_bwd_bf16(x_img, x_txt, g_img, g_txt, b, B, D, scale, label_offset, lse_i, lse_t, grad_out, dx_img,
+                             dx_txt, dg_img, dg_txt, dscale, ws, ws_bytes, ST(stream));
+}
+
+int32_t ilfdt_nce_bwd_gathered(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt, int32_t dtype,
+                               int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset,
+                               const float* lse_i_all, const float* lse_t_all, const float* grad_out_all, float* dx_img,
+                               float* dx_txt, float* dscale, void* ws, int64_t ws_bytes, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(dtype);
+  ILFDT_REQUIRE(b >= 1 && B >= b && D >= 1 && B % b == 0, ILFDT_E_INVALID_ARG,
+                "nce_bwd_gathered: need 1 <= b, B a multiple of b");
+  ILFDT_REQUIRE(label_offset >= 0 && label_offset + b <= B && label_offset % b == 0, ILFDT_E_INVALID_ARG,
+                "nce_bwd_gathered: label_offset must be rank*b");
+  ILFDT_REQUIRE(x_img && x_txt && g_img && g_txt && lse_i_all && lse_t_all && grad_out_all && dx_img && dx_txt &&
+                    dscale && scale,
+                ILFDT_E_INVALID_ARG, "nce_bwd_gathered: null pointer");
+  if (dtype == ILFDT_F32)
+    return nce_bwd_gathered_f32(reinterpret_cast<const float*>(x_img), reinterpret_cast<const float*>(x_txt),
+                                reinterpret_cast<const float*>(g_img), reinterpret_cast<const float*>(g_txt), b, B, D,
+                                scale, label_offset, lse_i_all, lse_t_all, grad_out_all, dx_img, dx_txt, dscale, ws,
+                                ws_bytes, ST(stream));
+  return launch_nce_bwd_gathered_bf16(x_img, x_txt, g_img, g_txt, b, B, D, scale, label_offset, lse_i_all, lse_t_all,
+                                      grad_out_all, dx_img, dx_txt, dscale, ST(stream));
 }
 
 int32_t ilfdt_ce_rows_fwd(const float* logits, int64_t b, int64_t B, int64_t label_offset, float* lse, float* diag,

@@ -290,6 +290,51 @@ softmax_grad_rows_kernel(const float* L, float* out, int64_t ld, int64_t cols, i
   }
 }
 
+// Gathered form (ilfdt_nce_bwd_gathered, fp32 route), in place on a chunk of stored logits:
+//   out[r,c] = wl * (exp(L[r,c] - lse_lane[r]) - d) + ws_c * (exp(L[r,c] - lse_stream[c]) - d),  d = [c == label0 + r]
+// with wl = go_lane[0]*coef, ws_c = go_stream[c / rows_per_go]*coef. dscale accumulates the lane term only.
+__global__ void __launch_bounds__(256)
+softmax_grad_sym_rows_kernel(const float* L, float* out, int64_t ld, int64_t cols, int64_t label0,
+                             const float* __restrict__ lse_lane, const float* __restrict__ lse_stream,
+                             const float* __restrict__ go_lane, const float* __restrict__ go_stream,
+                             int64_t rows_per_go, float coef, const float* __restrict__ scale_dev,
+                             float* __restrict__ dscale_acc) {
+  const int64_t row = blockIdx.x;
+  const float* lr = L + row * ld;
+  float* orow = out + row * ld;
+  const float l = lse_lane[row];
+  const float wl = go_lane[0] * coef;
+  const float inv_scale = 1.f / __ldg(scale_dev);
+  float part = 0.f;
+  for (int64_t c = threadIdx.x; c < cols; c += blockDim.x) {
+    const float v = lr[c];
+    const float d = (c == label0 + row) ? 1.f : 0.f;
+    const float pl = (expf(v - l) - d) * wl;
+    const float ps = (expf(v - lse_stream[c]) - d) * (go_stream[c / rows_per_go] * coef);
+    part = fmaf(pl, v * inv_scale, part);
+    orow[c] = pl + ps;
+  }
+  part = warp_sum(part);
+  __shared__ float sm[8];
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = part;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w2 = 1; w2 < (int)(blockDim.x >> 5); ++w2) part += sm[w2];
+    atomicAdd(dscale_acc, part);
+  }
+}
+
+int32_t launch_softmax_grad_sym_rows(const float* L, float* out, int64_t ld, int64_t rows, int64_t cols, int64_t label0,
+                                     const float* lse_lane, const float* lse_stream, const float* go_lane,
+                                     const float* go_stream, int64_t rows_per_go, float coef, const float* scale_dev,
+                                     float* dscale_acc, cudaStream_t st) {
+  if (rows == 0) return ILFDT_OK;
+  softmax_grad_sym_rows_kernel<<<(unsigned)rows, 256, 0, st>>>(L, out, ld, cols, label0, lse_lane, lse_stream, go_lane,
+                                                              go_stream, rows_per_go, coef, scale_dev, dscale_acc);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
 int32_t launch_lse_rows(const float* L, int64_t ld, int64_t rows, int64_t cols, int64_t label0, float* lse,
                         float* diag, cudaStream_t st) {
   if (rows == 0) return ILFDT_OK;

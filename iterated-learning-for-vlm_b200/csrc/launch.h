@@ -20,6 +20,10 @@ int32_t launch_lse_rows(const float* L, int64_t ld, int64_t rows, int64_t cols, 
                         float* diag, cudaStream_t st);
 int32_t launch_softmax_grad_rows(const float* L, float* out, int64_t ld, int64_t rows, int64_t cols, int64_t label0, const float* lse,
                                  const float* go, float coef, const float* scale_dev, float* dscale_acc, cudaStream_t st);
+int32_t launch_softmax_grad_sym_rows(const float* L, float* out, int64_t ld, int64_t rows, int64_t cols, int64_t label0,
+                                     const float* lse_lane, const float* lse_stream, const float* go_lane,
+                                     const float* go_stream, int64_t rows_per_go, float coef, const float* scale_dev,
+                                     float* dscale_acc, cudaStream_t st);
 int32_t launch_nce_loss(const float* lse_i, const float* diag_i, const float* lse_t, const float* diag_t, int64_t b,
                         float* loss, cudaStream_t st);
 int32_t launch_topk_hits(const float* L, int64_t b, int64_t B, int64_t label0, int32_t* counts, cudaStream_t st);
@@ -65,9 +69,12 @@ int32_t launch_token_bcast(const float* v, const float* mask, int64_t b, int64_t
 // nce_bwd_umma.cu (tcgen05)
 int64_t nce_bwd_bf16_ws_bytes(int64_t b, int64_t B, int64_t D);
 int32_t launch_nce_bwd_bf16(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt,
-                            const void* x_img_t, const void* x_txt_t, const void* g_img_t, const void* g_txt_t,
                             int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset, const float* lse_i,
                             const float* lse_t, const float* grad_out, float* dx_img, float* dx_txt, float* dg_img,
                             float* dg_txt, float* dscale, void* ws, int64_t ws_bytes, cudaStream_t st);
+int32_t launch_nce_bwd_gathered_bf16(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt,
+                                     int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset,
+                                     const float* lse_i_all, const float* lse_t_all, const float* go_all,
+                                     float* dx_img, float* dx_txt, float* dscale, cudaStream_t st);
 
 }  // namespace ilfdt

@@ -1,18 +1,25 @@
 // a13 (loss part): fused InfoNCE backward on tcgen05 -- the [b, B] logits / probabilities are
 // recomputed tile by tile in TMEM and consumed on-chip; they never reach HBM.
 //
-// One kernel, launched four times per step (dX_img, dG_txt, dX_txt, dG_img). Per launch:
+// One kernel. Per launch:
 //   "lane" matrix  XL [RL, D]  (its 128-row tiles are the TMEM lanes; the gradient is w.r.t. XL)
-//   "stream" matrix Y  [RS, D]  (rows streamed 64 at a time) and its transpose YT [D, RS]
+//   "stream" matrix Y  [RS, D]  (rows streamed 64 at a time)
 //   S[i, j]   = XL[i,:] . Y[j,:]                      MMA1  128 x 64 x D      -> TMEM (double buffered)
-//   P[i, j]   = (exp(scale*S - lse) - [i ~ j]) * gw     softmax warps: TMEM -> regs -> bf16 -> smem (SW128)
-//   dOut[i,:] += P[i, j-block] . YT[:, j-block]^T       MMA2  128 x 256 x 64    -> TMEM (256 columns)
+//   P[i, j]   = wl   * (exp(scale*S - lse_lane[i])   - [i ~ j])     (MODE 0, 2: "lane" softmax)
+//             + ws_j * (exp(scale*S - lse_stream[j]) - [i ~ j])     (MODE 1, 2: "stream" softmax)
+//                                                       softmax warps: TMEM -> regs -> bf16 -> smem (SW128)
+//   dOut[i,:] += P[i, j-block] . Y[j-block, half]       MMA2  128 x 256 x 64    -> TMEM (256 columns)
 //   dOut      *= scale                                  epilogue
-// lse is indexed by the lane row (dX launches: lane = local logits row) or by the stream row (dG
-// launches: lane = gathered row, stream = local logits row). A CTA owns (lane tile, 256-wide half of
-// D, slice of the stream range); S is recomputed for each half (TMEM holds 512 columns: 256 for dOut
-// + 2 x 64 for S).  The MMA thread software-pipelines MMA1(t+1) ahead of MMA2(t) so the tensor pipe
-// stays busy while the softmax warps convert tile t.
+// MMA2 reads the SAME row-major Y boxes TMA delivers for MMA1 (64 rows x 128 B, 128-byte swizzle) as an
+// MN-major B operand (N = D contiguous, K = stream row), so no transposed copy of any operand exists.
+// MODE 2 is the gathered form used in training: for local image rows i the total gradient is
+//   dX_img[i] = scale * sum_j (P_img[i,j] + P_txt[j,i]) G_txt[j]   with P_txt[j,i] built from lse_txt[j] of ALL ranks,
+// i.e. one launch per modality produces the local rows' full gradient (what dX + reduce-scatter(dG) gives in
+// the reference, clip_fdt.py:182-188) and nothing has to be reduce-scattered. MODE 0 / 1 are the separate
+// dX / dG launches for callers whose gathered operand is an independent tensor.
+// A CTA owns (lane tile, 256-wide half of D, slice of the stream range); S is recomputed for each half
+// (TMEM holds 512 columns: 256 for dOut + 2 x 64 for S).  The MMA thread software-pipelines MMA1(t+1)
+// ahead of MMA2(t) so the tensor pipe stays busy while the softmax warps convert tile t.
 #include "umma.cuh"
 #include "launch.h"
 #include <algorithm>
@@ -32,7 +39,7 @@ constexpr int NB_OFF_Y = NB_XL_BYTES;
 constexpr int NB_OFF_P = NB_OFF_Y + NB_Y_STAGES * NB_Y_STAGE;
 constexpr int NB_OFF_YT = NB_OFF_P + NB_P_BYTES;
 constexpr int NB_OFF_BARS = NB_OFF_YT + NB_YT_STAGES * NB_YT_STAGE;  // 229376
-constexpr int NB_SMEM_BYTES = NB_OFF_BARS + 1024 + 1024;
+constexpr int NB_SMEM_BYTES = NB_OFF_BARS + 1024 + 2048;  // 232448 = the sm_100 opt-in maximum
 constexpr int NB_TMEM_COLS = 512;
 constexpr int NB_TMEM_S = 256;  // S buffers at columns 256 and 320
 
@@ -40,11 +47,13 @@ struct NceBwdParams {
   int RL, RS, D;
   int nkb;              // ceil(D / 64)
   int num_lane_tiles, num_halves, nsplit, tiles_per_split, num_stream_tiles;
-  int lse_by_lane;      // 1: lse[lane row], label(lane i) = stream label_offset + i
-                        // 0: lse[stream row], label(stream j) = lane label_offset + j
+  int label_by_lane;    // 1: label(lane i) = stream label_offset + i;  0: label(stream j) = lane label_offset + j
   long long label_offset;
-  const float* lse;
-  const float* grad_out;
+  const float* lse_lane;    // [RL]  (MODE 0, 2)
+  const float* lse_stream;  // [RS]  (MODE 1, 2)
+  const float* go_lane;     // 1 float: upstream dLoss of the rank owning the lane rows
+  const float* go_stream;   // [ceil(RS / rows_per_go)]: upstream dLoss of the rank owning each stream row
+  long long rows_per_go;
   float inv_2b;
   const float* scale_dev;
   float* out;           // [RL, D]
@@ -61,16 +70,24 @@ struct NceBwdBars {
   uint64_t p_full, p_empty;
   uint64_t d_full, d_empty;
   uint32_t tmem_ptr;
-  float lse_s[2][64];
+  // per-stream-column constants of the tile a softmax group is converting, [group][..]: lane weight
+  // (0 beyond RS), stream weight, stream lse * log2(e)
+  alignas(16) float col_wl[2][64];
+  alignas(16) float col_ws[2][64];
+  alignas(16) float col_l2[2][64];
 };
+
+static_assert(sizeof(NceBwdBars) <= 2048, "barrier block outgrew its shared-memory slot");
+static_assert(NB_SMEM_BYTES <= 232448, "over the sm_100 dynamic shared memory limit");
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+template <int MODE>
 __global__ void __launch_bounds__(NB_THREADS, 1)
 nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__ CUtensorMap tmY,
-               const __grid_constant__ CUtensorMap tmYT, const NceBwdParams p) {
+               const NceBwdParams p) {
   extern __shared__ uint8_t nb_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(nb_smem_raw) + 1023) & ~(uintptr_t)1023);
   NceBwdBars* bars = reinterpret_cast<NceBwdBars*>(smem + NB_OFF_BARS);
@@ -90,7 +107,6 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
     fence_barrier_init();
     tma_prefetch_desc(&tmXL);
     tma_prefetch_desc(&tmY);
-    tma_prefetch_desc(&tmYT);
   }
   if (warp == 1) {
     tmem_alloc(&bars->tmem_ptr, NB_TMEM_COLS);
@@ -122,8 +138,9 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
           }
           mbar_wait(&bars->yt_empty[ts], tph ^ 1);
           mbar_expect_tx(&bars->yt_full[ts], NB_YT_STAGE);
-          tma_load_2d(smem + NB_OFF_YT + ts * NB_YT_STAGE, &tmYT, &bars->yt_full[ts], t * 64, half * 256,
-                      kEvictNormal);
+          for (int j = 0; j < 4; ++j)  // the CTA's 256 D-columns of the same 64 stream rows (columns >= D: zero fill)
+            tma_load_2d(smem + NB_OFF_YT + ts * NB_YT_STAGE + j * 8192, &tmY, &bars->yt_full[ts], half * 256 + j * 64,
+                        t * 64, kEvictNormal);
           if (++ts == NB_YT_STAGES) { ts = 0; tph ^= 1; }
         }
       }
@@ -169,10 +186,12 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
             mbar_wait(&bars->yt_full[ts], tph);
             fence_after_sync();
             const uint64_t adesc = make_smem_desc_sw128(smem_u32(smem + NB_OFF_P));
-            const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smem + NB_OFF_YT + ts * NB_YT_STAGE));
+            // B = Y[64 stream rows (K), 256 D-columns (N)], N contiguous: MN-major, 4 boxes of 64 columns 8 KB
+            // apart (leading offset), 8-row groups 1 KB apart (stride offset); a K step of 16 rows = 2 KB
+            const uint64_t bdesc = make_smem_desc_sw128_mn(smem_u32(smem + NB_OFF_YT + ts * NB_YT_STAGE), 8192);
 #pragma unroll
             for (int k4 = 0; k4 < 4; ++k4)
-              mma_f16(tmem_base, advance_desc_k(adesc, k4 * 32), advance_desc_k(bdesc, k4 * 32), p.idesc2,
+              mma_f16(tmem_base, advance_desc_k(adesc, k4 * 32), advance_desc_k(bdesc, k4 * 2048), p.idesc2,
                       (i > 1 || k4 != 0) ? 1u : 0u);
             mma_commit(&bars->p_empty);
             mma_commit(&bars->yt_empty[ts]);
@@ -191,7 +210,7 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
     const int tid128 = ((warp - 2) & 3) * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     const int r_in_tile = quad * 32 + lane;
-    const float gw = __ldg(p.grad_out) * p.inv_2b;
+    const float wl = (MODE != 1) ? __ldg(p.go_lane) * p.inv_2b : 0.f;
     const float scale = __ldg(p.scale_dev);
     const float scale_log2 = scale * 1.4426950408889634f;
     uint32_t tile_ctr = 0, it = 0;
@@ -203,19 +222,29 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
       const int t_begin = split * p.tiles_per_split, t_end = min(p.num_stream_tiles, t_begin + p.tiles_per_split);
       const int row = lt * 128 + r_in_tile;
       // label column (stream index) matching this lane row, or an index that never occurs
-      const long long jl = p.lse_by_lane ? p.label_offset + row          // stream j == label_offset + lane row
-                                         : (long long)row - p.label_offset;  // lane row == label_offset + stream j
+      const long long jl = p.label_by_lane ? p.label_offset + row          // stream j == label_offset + lane row
+                                           : (long long)row - p.label_offset;  // lane row == label_offset + stream j
       const bool row_ok = row < p.RL;
-      const float lse_lane = (p.lse_by_lane && row_ok) ? __ldg(p.lse + row) * 1.4426950408889634f : 0.f;
+      const float lse_lane = (MODE != 1 && row_ok) ? __ldg(p.lse_lane + row) * 1.4426950408889634f : 0.f;
       float ds_acc = 0.f;
       for (int t = t_begin; t < t_end; ++t, ++tile_ctr) {
         const uint32_t sb = tile_ctr & 1, sph = (tile_ctr >> 1) & 1;
         if (sb != group) continue;  // the other softmax group converts this tile
         const int j0 = t * 64;
-        if (!p.lse_by_lane) {
-          if (tid128 < 64) bars->lse_s[sb][tid128] = (j0 + tid128 < p.RS) ? __ldg(p.lse + j0 + tid128) * 1.4426950408889634f : 0.f;
-          named_bar_sync(1 + (int)group, 128);
+        float* c_wl = bars->col_wl[sb];
+        float* c_ws = bars->col_ws[sb];
+        float* c_l2 = bars->col_l2[sb];
+        if (tid128 < 64) {
+          const long long n = (long long)j0 + tid128;
+          const bool ok = n < p.RS;
+          c_wl[tid128] = ok ? wl : 0.f;
+          if (MODE != 0) {
+            c_ws[tid128] = ok ? __ldg(p.go_stream + n / p.rows_per_go) * p.inv_2b : 0.f;
+            c_l2[tid128] = ok ? __ldg(p.lse_stream + n) * 1.4426950408889634f : 0.f;
+          }
         }
+        named_bar_sync(1 + (int)group, 128);
+        const int jd = (jl >= j0 && jl < (long long)j0 + 64) ? (int)(jl - j0) : -1;
         mbar_wait(&bars->s_full[sb], sph);
         fence_after_sync();
         uint32_t v0[32], v1[32];
@@ -235,12 +264,13 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
             for (int e = 0; e < 2; ++e) {
               const int jj = h2 * 32 + j + e;
               const float s_raw = __uint_as_float(h2 == 0 ? v0[j + e] : v1[j + e]);
-              const float l2 = p.lse_by_lane ? lse_lane : bars->lse_s[sb][jj];
-              float pr = exp2f(fmaf(s_raw, scale_log2, -l2));
-              pr -= ((long long)(j0 + jj) == jl) ? 1.f : 0.f;
-              pr *= gw;
-              pr = (j0 + jj < p.RS) ? pr : 0.f;
-              ds_acc = fmaf(pr, s_raw, ds_acc);
+              const float dlt = (jj == jd) ? 1.f : 0.f;
+              float pr = 0.f;
+              if (MODE != 1) {
+                pr = (exp2f(fmaf(s_raw, scale_log2, -lse_lane)) - dlt) * c_wl[jj];
+                ds_acc = fmaf(pr, s_raw, ds_acc);   // dLoss/dscale of the LANE rows' own logits only
+              }
+              if (MODE != 0) pr = fmaf(exp2f(fmaf(s_raw, scale_log2, -c_l2[jj])) - dlt, c_ws[jj], pr);
               pv[e] = pr;
             }
             __nv_bfloat162 b2 = __floats2bfloat162_rn(pv[0], pv[1]);
@@ -258,6 +288,7 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
         fence_proxy_async_smem();  // make the generic-proxy writes visible to the tensor core (async proxy)
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->p_full);
+        named_bar_sync(1 + (int)group, 128);  // every reader of col_* is done before the next tile's values land
       }
       // ---- epilogue: dOut (TMEM columns 0..255) -> global ----
       mbar_wait(&bars->d_full, it & 1);
@@ -291,7 +322,7 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
       fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->d_empty);
-      if (p.dscale != nullptr && half == 0) {
+      if (MODE != 1 && p.dscale != nullptr && half == 0) {
         float s = row_ok ? ds_acc : 0.f;
         s = warp_sum(s);
         if (lane == 0) atomicAdd(p.dscale, s);
@@ -312,10 +343,23 @@ int64_t nce_bwd_bf16_ws_bytes(int64_t b, int64_t B, int64_t D) {
   return 256;
 }
 
-static int32_t launch_one(const void* XL, const void* Y, const void* YT, int64_t RL, int64_t RS, int64_t D,
-                          int lse_by_lane, int64_t label_offset, const float* lse, const float* grad_out, float inv_2b,
-                          const float* scale, float* out, float* dscale, cudaStream_t st) {
+struct NceBwdLaunch {
+  const void* XL; const void* Y;      // lane matrix [RL, D], stream matrix [RS, D] (bf16)
+  int64_t RL, RS, D;
+  int mode;                            // 0 lane softmax, 1 stream softmax, 2 both
+  int label_by_lane;
+  int64_t label_offset;
+  const float* lse_lane; const float* lse_stream;
+  const float* go_lane; const float* go_stream;
+  int64_t rows_per_go;
+  float inv_2b;
+  const float* scale;
+  float* out; float* dscale;
+};
+
+static int32_t launch_one(const NceBwdLaunch& a, cudaStream_t st) {
   NceBwdParams p{};
+  const int64_t RL = a.RL, RS = a.RS, D = a.D;
   p.RL = (int)RL; p.RS = (int)RS; p.D = (int)D;
   p.nkb = (int)cdiv(D, 64);
   p.num_lane_tiles = (int)cdiv(RL, 128);
@@ -323,65 +367,108 @@ static int32_t launch_one(const void* XL, const void* Y, const void* YT, int64_t
   p.num_stream_tiles = (int)cdiv(RS, 64);
   const int base_items = p.num_lane_tiles * p.num_halves;
   const int sms = sm_count();
+  // split the stream range so that the persistent grid is full and even: items = base_items * nsplit
   int nsplit = 1;
-  if (base_items < sms) nsplit = std::min<int>(p.num_stream_tiles, std::max<int>(1, (sms + base_items - 1) / base_items));
+  if (base_items % sms != 0) {
+    double best = -1.0;
+    const int max_split = (int)std::min<int64_t>(p.num_stream_tiles, std::max<int64_t>(1, cdiv(4 * sms, base_items)));
+    for (int c = 1; c <= max_split; ++c) {
+      const int tps = (int)cdiv(p.num_stream_tiles, c);
+      const int rc = (int)cdiv(p.num_stream_tiles, tps);
+      const int64_t items = (int64_t)base_items * rc;
+      double eff = (double)items / (double)(cdiv(items, sms) * sms);
+      eff *= (double)tps / (double)(tps + 6.0);   // every item pays a lane-tile load, an epilogue and (split) atomics
+      if (eff > best + 1e-9) { best = eff; nsplit = rc; }
+    }
+  }
   p.tiles_per_split = (int)cdiv(p.num_stream_tiles, nsplit);
   p.nsplit = (int)cdiv(p.num_stream_tiles, p.tiles_per_split);
-  p.lse_by_lane = lse_by_lane;
-  p.label_offset = label_offset;
-  p.lse = lse;
-  p.grad_out = grad_out;
-  p.inv_2b = inv_2b;
-  p.scale_dev = scale;
-  p.out = out;
+  p.label_by_lane = a.label_by_lane;
+  p.label_offset = a.label_offset;
+  p.lse_lane = a.lse_lane;
+  p.lse_stream = a.lse_stream;
+  p.go_lane = a.go_lane;
+  p.go_stream = a.go_stream;
+  p.rows_per_go = std::max<int64_t>(1, a.rows_per_go);
+  p.inv_2b = a.inv_2b;
+  p.scale_dev = a.scale;
+  p.out = a.out;
   p.use_atomic = p.nsplit > 1 ? 1 : 0;
-  p.dscale = dscale;
+  p.dscale = a.dscale;
   p.idesc1 = make_idesc_bf16(128, 64);
-  p.idesc2 = make_idesc_bf16(128, 256);
-  if (p.use_atomic) ILFDT_CUDA_OK(cudaMemsetAsync(out, 0, (size_t)RL * D * 4, st));
-  CUtensorMap tmXL, tmY, tmYT;
-  int32_t rc = make_tmap_bf16(&tmXL, XL, RL, D, D, 128);
+  p.idesc2 = make_idesc_bf16(128, 256, 0, 1);   // B = Y box read MN-major
+  if (p.use_atomic) ILFDT_CUDA_OK(cudaMemsetAsync(a.out, 0, (size_t)RL * D * 4, st));
+  CUtensorMap tmXL, tmY;
+  int32_t rc = make_tmap_bf16(&tmXL, a.XL, RL, D, D, 128);
   if (rc != ILFDT_OK) return rc;
-  rc = make_tmap_bf16(&tmY, Y, RS, D, D, 64);
-  if (rc != ILFDT_OK) return rc;
-  rc = make_tmap_bf16(&tmYT, YT, D, RS, RS, 256);
+  rc = make_tmap_bf16(&tmY, a.Y, RS, D, D, 64);
   if (rc != ILFDT_OK) return rc;
   static thread_local int configured_dev = -1;
   int dev = 0;
   ILFDT_CUDA_OK(cudaGetDevice(&dev));
   if (configured_dev != dev) {
-    ILFDT_CUDA_OK(cudaFuncSetAttribute(nce_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NB_SMEM_BYTES));
+    ILFDT_CUDA_OK(cudaFuncSetAttribute(nce_bwd_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, NB_SMEM_BYTES));
+    ILFDT_CUDA_OK(cudaFuncSetAttribute(nce_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, NB_SMEM_BYTES));
+    ILFDT_CUDA_OK(cudaFuncSetAttribute(nce_bwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, NB_SMEM_BYTES));
     configured_dev = dev;
   }
   const int items = base_items * p.nsplit;
-  nce_bwd_kernel<<<std::min(items, sms), NB_THREADS, NB_SMEM_BYTES, st>>>(tmXL, tmY, tmYT, p);
+  const int grid = std::min(items, sms);
+  if (a.mode == 0) nce_bwd_kernel<0><<<grid, NB_THREADS, NB_SMEM_BYTES, st>>>(tmXL, tmY, p);
+  else if (a.mode == 1) nce_bwd_kernel<1><<<grid, NB_THREADS, NB_SMEM_BYTES, st>>>(tmXL, tmY, p);
+  else nce_bwd_kernel<2><<<grid, NB_THREADS, NB_SMEM_BYTES, st>>>(tmXL, tmY, p);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }
 
 int32_t launch_nce_bwd_bf16(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt,
-                            const void* x_img_t, const void* x_txt_t, const void* g_img_t, const void* g_txt_t,
                             int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset, const float* lse_i,
                             const float* lse_t, const float* grad_out, float* dx_img, float* dx_txt, float* dg_img,
                             float* dg_txt, float* dscale, void* ws, int64_t ws_bytes, cudaStream_t st) {
   (void)ws; (void)ws_bytes;
   ILFDT_REQUIRE(D <= 512 && D % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "nce_bwd(bf16): D=%lld must be <= 512, %% 8",
                 (long long)D);
-  ILFDT_REQUIRE(b % 8 == 0 && B % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE,
-                "nce_bwd(bf16): b and B must be multiples of 8 (TMA row pitch of the transposed operands)");
   ILFDT_CUDA_OK(cudaMemsetAsync(dscale, 0, 4, st));
-  const float inv_2b = 1.f / (2.f * (float)b);
+  NceBwdLaunch a{};
+  a.D = D; a.label_offset = label_offset; a.inv_2b = 1.f / (2.f * (float)b); a.scale = scale;
+  a.go_lane = grad_out; a.go_stream = grad_out; a.rows_per_go = std::max<int64_t>(B, 1);
   int32_t rc;
   // logits_per_image = x_img . g_txt^T : dX_img (lse_i by lane), dG_txt (lse_i by stream)
-  rc = launch_one(x_img, g_txt, g_txt_t, b, B, D, 1, label_offset, lse_i, grad_out, inv_2b, scale, dx_img, dscale, st);
-  if (rc != ILFDT_OK) return rc;
-  rc = launch_one(g_txt, x_img, x_img_t, B, b, D, 0, label_offset, lse_i, grad_out, inv_2b, scale, dg_txt, nullptr, st);
-  if (rc != ILFDT_OK) return rc;
+  a.XL = x_img; a.Y = g_txt; a.RL = b; a.RS = B; a.mode = 0; a.label_by_lane = 1;
+  a.lse_lane = lse_i; a.lse_stream = nullptr; a.out = dx_img; a.dscale = dscale;
+  if ((rc = launch_one(a, st)) != ILFDT_OK) return rc;
+  a.XL = g_txt; a.Y = x_img; a.RL = B; a.RS = b; a.mode = 1; a.label_by_lane = 0;
+  a.lse_lane = nullptr; a.lse_stream = lse_i; a.out = dg_txt; a.dscale = nullptr;
+  if ((rc = launch_one(a, st)) != ILFDT_OK) return rc;
   // logits_per_text = x_txt . g_img^T : dX_txt (lse_t by lane), dG_img (lse_t by stream)
-  rc = launch_one(x_txt, g_img, g_img_t, b, B, D, 1, label_offset, lse_t, grad_out, inv_2b, scale, dx_txt, dscale, st);
-  if (rc != ILFDT_OK) return rc;
-  rc = launch_one(g_img, x_txt, x_txt_t, B, b, D, 0, label_offset, lse_t, grad_out, inv_2b, scale, dg_img, nullptr, st);
-  return rc;
+  a.XL = x_txt; a.Y = g_img; a.RL = b; a.RS = B; a.mode = 0; a.label_by_lane = 1;
+  a.lse_lane = lse_t; a.lse_stream = nullptr; a.out = dx_txt; a.dscale = dscale;
+  if ((rc = launch_one(a, st)) != ILFDT_OK) return rc;
+  a.XL = g_img; a.Y = x_txt; a.RL = B; a.RS = b; a.mode = 1; a.label_by_lane = 0;
+  a.lse_lane = nullptr; a.lse_stream = lse_t; a.out = dg_img; a.dscale = nullptr;
+  return launch_one(a, st);
+}
+
+// Gathered form: g_* are the all-gather of every rank's x_* (rank-major), lse_*_all [B] the all-gather of the
+// forward's per-row log-sum-exp, go_all [B / b] every rank's upstream dLoss. Two launches produce the local rows'
+// TOTAL gradient; there is no gradient w.r.t. the gathered copies left to reduce-scatter.
+int32_t launch_nce_bwd_gathered_bf16(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt,
+                                     int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset,
+                                     const float* lse_i_all, const float* lse_t_all, const float* go_all,
+                                     float* dx_img, float* dx_txt, float* dscale, cudaStream_t st) {
+  ILFDT_REQUIRE(D <= 512 && D % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "nce_bwd(bf16): D=%lld must be <= 512, %% 8",
+                (long long)D);
+  ILFDT_CUDA_OK(cudaMemsetAsync(dscale, 0, 4, st));
+  NceBwdLaunch a{};
+  a.D = D; a.label_offset = label_offset; a.inv_2b = 1.f / (2.f * (float)b); a.scale = scale;
+  a.RL = b; a.RS = B; a.mode = 2; a.label_by_lane = 1;
+  a.go_lane = go_all + label_offset / b; a.go_stream = go_all; a.rows_per_go = b;
+  a.dscale = dscale;
+  int32_t rc;
+  a.XL = x_img; a.Y = g_txt; a.lse_lane = lse_i_all + label_offset; a.lse_stream = lse_t_all; a.out = dx_img;
+  if ((rc = launch_one(a, st)) != ILFDT_OK) return rc;
+  a.XL = x_txt; a.Y = g_img; a.lse_lane = lse_t_all + label_offset; a.lse_stream = lse_i_all; a.out = dx_txt;
+  return launch_one(a, st);
 }
 
 }  // namespace ilfdt

@@ -141,6 +141,20 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;
   return d;
 }
+// MN-major operand (the M/N index is the contiguous one) in the same physical tile TMA writes with the
+// 128-byte swizzle: each K index is one 128-byte row holding 64 consecutive M/N elements; 8 such rows form
+// the 1024-byte swizzle atom (stride offset = distance between 8-row K groups = 1024 B when rows are
+// packed); the next 64 M/N elements start `lbo_bytes` further (leading offset). CUTLASS canonical form
+// ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte units (cute/atom/mma_traits_sm100.hpp, make_umma_desc<MN>).
+__device__ __forceinline__ uint64_t make_smem_desc_sw128_mn(uint32_t smem_addr, uint32_t lbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
 // Advancing by k bf16 elements inside the 128-byte swizzle atom = adding k*2 bytes to the start address.
 __device__ __forceinline__ uint64_t advance_desc_k(uint64_t desc, uint32_t bytes) {
   return desc + (uint64_t)(bytes >> 4);
@@ -149,8 +163,9 @@ __device__ __forceinline__ uint64_t advance_desc_k(uint64_t desc, uint32_t bytes
 // Instruction descriptor, kind::f16: bf16 x bf16 -> fp32, both operands K-major.
 //   [4,6) D format: 1 = F32   [7,10) A format: 1 = BF16   [10,13) B format: 1 = BF16
 //   [15] A major (0 = K)  [16] B major (0 = K)  [17,23) N >> 3   [24,29) M >> 4
-__host__ __device__ inline uint32_t make_idesc_bf16(int m, int n) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+__host__ __device__ inline uint32_t make_idesc_bf16(int m, int n, int a_mn_major = 0, int b_mn_major = 0) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(a_mn_major & 1) << 15) | ((uint32_t)(b_mn_major & 1) << 16) |
+         ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 }  // namespace umma

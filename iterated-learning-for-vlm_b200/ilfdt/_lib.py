@@ -44,8 +44,10 @@ SIGNATURES = {
     "ilfdt_logits": (_i32, [_p, _p, _i32, _i64, _i64, _i64, _p, _p, _p]),
     "ilfdt_nce_ws_bytes": (_i64, [_i32, _i64, _i64, _i64]),
     "ilfdt_nce_fwd": (_i32, [_p, _p, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _i64, _p]),
-    "ilfdt_nce_bwd": (_i32, [_p, _p, _p, _p, _p, _p, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _p, _p,
+    "ilfdt_nce_bwd": (_i32, [_p, _p, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _p, _p,
                              _p, _p, _p, _p, _p, _p, _i64, _p]),
+    "ilfdt_nce_bwd_gathered": (_i32, [_p, _p, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _p, _p,
+                                      _p, _p, _p, _p, _i64, _p]),
     "ilfdt_ce_rows_fwd": (_i32, [_p, _i64, _i64, _i64, _p, _p, _p]),
     "ilfdt_ce_rows_bwd": (_i32, [_p, _i64, _i64, _i64, _p, _p, _f, _p, _p]),
     "ilfdt_topk_hits": (_i32, [_p, _i64, _i64, _i64, _p, _p]),
@@ -70,7 +72,7 @@ def load():
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.ilfdt_abi_version() != 1:
+    if lib.ilfdt_abi_version() != 2:
         raise RuntimeError("libilfdt ABI version mismatch")
     _lib = lib
     return lib

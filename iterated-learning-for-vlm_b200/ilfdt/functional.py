@@ -258,29 +258,49 @@ class LogitsFunction(torch.autograd.Function):
 
 class InfoNCEFunction(torch.autograd.Function):
     """Fused logits + ClipInfoCELoss (clip_fdt.py:421-422 + loss_functions/loss.py:40-50):
-    (x_img, x_txt [b,D]; g_img, g_txt [B,D]; scale [1]) -> loss []. No [b,B] tensor is created."""
+    (x_img, x_txt [b,D]; g_img, g_txt [B,D]; scale [1]) -> loss []. No [b,B] tensor is created.
+
+    gathered=True states that g_img/g_txt are AllGather(x_img)/AllGather(x_txt) (what Clip_FDT/CLIP.forward
+    build, clip_fdt.py:418-419). The backward then all-gathers the per-row log-sum-exps (2b+1 floats per rank)
+    and each rank forms the total gradient of its own rows in two launches; g_img/g_txt receive no gradient,
+    so AllGather.backward (the reference's [B,D] all_reduce, clip_fdt.py:182-188) never runs. The result is
+    the same sum the reference's dX + all_reduce(dG)[rank] produces."""
 
     @staticmethod
-    def forward(ctx, x_img, x_txt, g_img, g_txt, scale, label_offset, mode):
+    def forward(ctx, x_img, x_txt, g_img, g_txt, scale, label_offset, mode, gathered=False):
         ts = [t.contiguous().float() for t in (x_img, x_txt, g_img, g_txt)]
         sc = scale.detach().reshape(1).float().contiguous()
-        # the tensor-core kernels TMA-load [D, b] / [D, B] transposes: row pitch must be a multiple of
-        # 16 bytes. Ragged batches take the fp32 kernels (still CUDA, still fused per row chunk).
-        if mode == "bf16" and ts[0].shape[0] % 8 == 0 and ts[2].shape[0] % 8 == 0 and ts[0].shape[1] % 8 == 0 \
-                and ts[0].shape[1] <= 512:
+        # the tensor-core kernels need 16-byte TMA row pitches: D % 8. Other shapes take the fp32 kernels
+        # (still CUDA, still fused per row chunk).
+        if mode == "bf16" and ts[0].shape[1] % 8 == 0 and ts[0].shape[1] <= 512:
             ts = [ops.cast_bf16(t) for t in ts]
         loss, lse_i, lse_t, _, _ = ops.nce_fwd(ts[0], ts[1], ts[2], ts[3], sc, label_offset)
         ctx.save_for_backward(ts[0], ts[1], ts[2], ts[3], sc, lse_i, lse_t)
-        ctx.label_offset, ctx.scale_shape = int(label_offset), scale.shape
+        ctx.label_offset, ctx.scale_shape, ctx.gathered = int(label_offset), scale.shape, bool(gathered)
         return loss
 
     @staticmethod
     def backward(ctx, go):
         x_img, x_txt, g_img, g_txt, sc, lse_i, lse_t = ctx.saved_tensors
         go = go.reshape(1).float().contiguous()
+        if ctx.gathered:
+            b, B = x_img.shape[0], g_img.shape[0]
+            if B == b:
+                lse_i_all, lse_t_all, go_all = lse_i, lse_t, go
+            else:
+                world = B // b
+                mine = torch.cat([lse_i, lse_t, go])                      # 2b+1 floats
+                every = torch.empty(world, 2 * b + 1, dtype=torch.float32, device=mine.device)
+                dist.all_gather_into_tensor(every.view(-1), mine)
+                lse_i_all = every[:, :b].contiguous().view(-1)
+                lse_t_all = every[:, b:2 * b].contiguous().view(-1)
+                go_all = every[:, 2 * b].contiguous()
+            dx_img, dx_txt, dscale = ops.nce_bwd_gathered(x_img, x_txt, g_img, g_txt, sc, ctx.label_offset,
+                                                          lse_i_all, lse_t_all, go_all)
+            return dx_img, dx_txt, None, None, dscale.reshape(ctx.scale_shape), None, None, None
         dx_img, dx_txt, dg_img, dg_txt, dscale = ops.nce_bwd(x_img, x_txt, g_img, g_txt, sc, ctx.label_offset,
                                                              lse_i, lse_t, go)
-        return dx_img, dx_txt, dg_img, dg_txt, dscale.reshape(ctx.scale_shape), None, None
+        return dx_img, dx_txt, dg_img, dg_txt, dscale.reshape(ctx.scale_shape), None, None, None
 
 
 class CrossEntropyRowsFunction(torch.autograd.Function):

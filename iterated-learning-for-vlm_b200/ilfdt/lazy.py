@@ -16,9 +16,12 @@ from . import functional as Fn
 class ContrastiveStash:
     """What clip_fdt.py:411-419 produced: normalised local rows, gathered rows, clamped scale."""
 
-    def __init__(self, x_img, x_txt, g_img, g_txt, scale, mode):
+    def __init__(self, x_img, x_txt, g_img, g_txt, scale, mode, gathered=False):
         self.x_img, self.x_txt, self.g_img, self.g_txt = x_img, x_txt, g_img, g_txt
         self.scale, self.mode = scale, mode
+        # True when g_* are AllGather(x_*) of this very step (the models' forward): enables the backward that
+        # needs no [B,D] gradient exchange (functional.InfoNCEFunction)
+        self.gathered = gathered
         self._mat = [None, None]
 
     @property
@@ -44,7 +47,7 @@ class ContrastiveStash:
 
     def fused_loss(self):
         return Fn.InfoNCEFunction.apply(self.x_img, self.x_txt, self.g_img, self.g_txt, self.scale,
-                                        self.label_offset(), self.mode)
+                                        self.label_offset(), self.mode, self.gathered)
 
 
 class LazyLogits:

@@ -47,5 +47,5 @@ class CLIP(nn.Module):
         # clip.py:146-147 scales the features before the matmul; the kernels scale the product, which
         # differs by rounding only (tolerance stated in tests/test_parity_gpu.py)
         stash = ContrastiveStash(image_features, text_features, gathered_image_features, gathered_text_features,
-                                 logit_scale, Fn.get_compute_dtype())
+                                 logit_scale, Fn.get_compute_dtype(), gathered=True)
         return LazyLogits(stash, 0), LazyLogits(stash, 1)

@@ -246,7 +246,7 @@ class Clip_FDT(nn.Module):
         # :421-422 -- the two [b,B] logit matrices are returned lazily: ClipInfoCELoss consumes the stash
         # through the fused kernels; any other use materialises them with the logits kernel.
         stash = ContrastiveStash(sd_img_ft, sd_txt_ft, gathered_img, gathered_txt, logit_scale,
-                                 Fn.get_compute_dtype())
+                                 Fn.get_compute_dtype(), gathered=True)
         return (LazyLogits(stash, 0), LazyLogits(stash, 1)), (img_k, txt_k)
 
 

@@ -22,7 +22,7 @@ PROFILE = {}          # op name -> [(start_event, end_event), ...]
 _KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_sparsemax_fwd": 1,
                      "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2,
                      "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5,
-                     "ilfdt_nce_bwd": 4, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
+                     "ilfdt_nce_bwd": 4, "ilfdt_nce_bwd_gathered": 2, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
                      "ilfdt_randn_fill": 1, "ilfdt_copy": 0}
 
 
@@ -280,7 +280,7 @@ def nce_fwd(x_img, x_txt, g_img, g_txt, scale, label_offset):
     return loss, lse_i, lse_t, diag_i, diag_t
 
 
-def nce_bwd(x_img, x_txt, g_img, g_txt, scale, label_offset, lse_i, lse_t, grad_out, transposed=None):
+def nce_bwd(x_img, x_txt, g_img, g_txt, scale, label_offset, lse_i, lse_t, grad_out):
     """Returns dx_img, dx_txt [b,D], dg_img, dg_txt [B,D], dscale [] (all f32)."""
     b, D = x_img.shape
     B = g_img.shape[0]
@@ -292,15 +292,31 @@ def nce_bwd(x_img, x_txt, g_img, g_txt, scale, label_offset, lse_i, lse_t, grad_
     dg_img = torch.empty(B, D, dtype=torch.float32, device=dev)
     dg_txt = torch.empty_like(dg_img)
     dscale = torch.empty((), dtype=torch.float32, device=dev)
-    tr = [None] * 4
-    if dt == BF16:
-        tr = transposed if transposed is not None else [transpose_bf16(t) for t in (x_img, x_txt, g_img, g_txt)]
     ws, n = _nce_ws(dt, b, B, D, dev)
-    _call("ilfdt_nce_bwd", _ptr(x_img), _ptr(x_txt), _ptr(g_img), _ptr(g_txt), _ptr(tr[0]), _ptr(tr[1]),
-                                    _ptr(tr[2]), _ptr(tr[3]), dt, b, B, D, _ptr(scale), int(label_offset),
-                                    _ptr(lse_i), _ptr(lse_t), _ptr(grad_out), _ptr(dx_img), _ptr(dx_txt),
-                                    _ptr(dg_img), _ptr(dg_txt), _ptr(dscale), _ptr(ws), n, _stream())
+    _call("ilfdt_nce_bwd", _ptr(x_img), _ptr(x_txt), _ptr(g_img), _ptr(g_txt), dt, b, B, D, _ptr(scale),
+          int(label_offset), _ptr(lse_i), _ptr(lse_t), _ptr(grad_out), _ptr(dx_img), _ptr(dx_txt),
+          _ptr(dg_img), _ptr(dg_txt), _ptr(dscale), _ptr(ws), n, _stream())
     return dx_img, dx_txt, dg_img, dg_txt, dscale
+
+
+def nce_bwd_gathered(x_img, x_txt, g_img, g_txt, scale, label_offset, lse_i_all, lse_t_all, grad_out_all):
+    """g_* = all-gather of x_*; lse_*_all [B], grad_out_all [B/b] gathered over ranks.
+    Returns the local rows' total gradient dx_img, dx_txt [b,D] and the rank-local dscale []."""
+    b, D = x_img.shape
+    B = g_img.shape[0]
+    dev = x_img.device
+    dt = _DT[x_img.dtype]
+    for t, nm, cnt in ((lse_i_all, "lse_i_all", B), (lse_t_all, "lse_t_all", B), (grad_out_all, "grad_out_all", B // b)):
+        _req(t, torch.float32, nm)
+        assert t.numel() == cnt, nm
+    dx_img = torch.empty(b, D, dtype=torch.float32, device=dev)
+    dx_txt = torch.empty_like(dx_img)
+    dscale = torch.empty((), dtype=torch.float32, device=dev)
+    ws, n = _nce_ws(dt, b, B, D, dev)
+    _call("ilfdt_nce_bwd_gathered", _ptr(x_img), _ptr(x_txt), _ptr(g_img), _ptr(g_txt), dt, b, B, D, _ptr(scale),
+          int(label_offset), _ptr(lse_i_all), _ptr(lse_t_all), _ptr(grad_out_all), _ptr(dx_img), _ptr(dx_txt),
+          _ptr(dscale), _ptr(ws), n, _stream())
+    return dx_img, dx_txt, dscale
 
 
 def ce_rows_fwd(logits_f32, label_offset):

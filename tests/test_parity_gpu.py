@@ -345,6 +345,58 @@ def test_infonce(ops, b, B, D, offset, mode, pval):
     assert counts[1].item() == (top5 == lab.view(-1, 1)).any(1).sum().item()
 
 
+@pytest.mark.parametrize("W,b,D", [(1, 64, 512), (2, 128, 512), (4, 72, 512), (3, 40, 64), (2, 300, 256)])
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_infonce_gathered_backward(ops, W, b, D, mode):
+    """ilfdt_nce_bwd_gathered: W ranks emulated on one GPU. Each rank's output must equal the gradient the
+    reference obtains for its rows: d/dx of sum_r go_r * loss_r with g = all-gather(x) (AllGather.backward =
+    all_reduce + slice, clip_fdt.py:182-188), and dscale must be the rank-local d loss_r / d scale."""
+    B = W * b
+    g = torch.Generator().manual_seed(7 * W + b)
+    x_img = torch.nn.functional.normalize(torch.randn(B, D, generator=g), dim=-1)
+    x_txt = torch.nn.functional.normalize(x_img + 0.7 * torch.randn(B, D, generator=g), dim=-1)
+    if mode == "bf16":
+        x_img, x_txt = bf16_round(x_img), bf16_round(x_txt)
+    go = torch.tensor([0.37, -0.2, 1.1, 0.0][:W])
+    scale = 1 / 0.07
+    # oracle (fp64 autograd): the leaves are the per-rank rows, the gathered copies are their concatenation
+    xi = x_img.double().requires_grad_(True)
+    xt = x_txt.double().requires_grad_(True)
+    sc = [torch.tensor(scale, dtype=torch.float64, requires_grad=True) for _ in range(W)]
+    total = 0
+    for r in range(W):
+        rows = slice(r * b, (r + 1) * b)
+        l_i = sc[r] * xi[rows] @ xt.t()
+        l_t = sc[r] * xt[rows] @ xi.t()
+        labels = r * b + torch.arange(b)
+        loss_r = (torch.nn.functional.cross_entropy(l_i, labels) + torch.nn.functional.cross_entropy(l_t, labels)) / 2
+        total = total + go[r].double() * loss_r
+    total.backward()
+
+    dev = _dev()
+    cast = (lambda t: ops.cast_bf16(t)) if mode == "bf16" else (lambda t: t)
+    G_i, G_t = cast(x_img.to(dev).contiguous()), cast(x_txt.to(dev).contiguous())
+    s_dev = torch.full((1,), scale, device=dev)
+    lse_i_all = torch.empty(B, device=dev)
+    lse_t_all = torch.empty(B, device=dev)
+    for r in range(W):
+        rows = slice(r * b, (r + 1) * b)
+        _, li, lt, _, _ = ops.nce_fwd(G_i[rows].contiguous(), G_t[rows].contiguous(), G_i, G_t, s_dev, r * b)
+        lse_i_all[rows], lse_t_all[rows] = li, lt
+    go_dev = go.to(dev)
+    tol = 5e-5 if mode == "fp32" else BF16_TOL
+    for r in range(W):
+        rows = slice(r * b, (r + 1) * b)
+        dx_i, dx_t, dsc = ops.nce_bwd_gathered(G_i[rows].contiguous(), G_t[rows].contiguous(), G_i, G_t, s_dev, r * b,
+                                               lse_i_all, lse_t_all, go_dev)
+        assert_close(dx_i, xi.grad[rows], tol, f"dx_img rank {r}")
+        assert_close(dx_t, xt.grad[rows], tol, f"dx_txt rank {r}")
+        if go[r] != 0:
+            assert_close(dsc, sc[r].grad, tol * (10 if mode == "fp32" else 1), f"dscale rank {r}")
+        else:
+            assert abs(dsc.item()) < 1e-12
+
+
 # ---------------------------------------------------------------------------------------------------
 # whole step against the golden vectors produced by the unmodified reference
 # ---------------------------------------------------------------------------------------------------

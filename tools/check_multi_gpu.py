@@ -20,7 +20,7 @@ def main():
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     ok = True
-    for mode, tol in (("fp32", 2e-5), ("bf16", 2e-3)):
+    for mode, tol in (("fp32", 2e-5), ("bf16", 1e-2)):
         b, P, T, K, D = 64, 49, 77, 2048, 512
         g = torch.Generator().manual_seed(7)
         q_img = torch.randn(world * b, P, D, generator=g)
@@ -46,7 +46,7 @@ def main():
         s.data = torch.clamp(s.data, max=100)
         g_i = Fn.AllGather.apply(x_i).view(-1, D)
         g_t = Fn.AllGather.apply(x_t).view(-1, D)
-        loss = Fn.InfoNCEFunction.apply(x_i, x_t, g_i, g_t, s, rank * b, mode)
+        loss = Fn.InfoNCEFunction.apply(x_i, x_t, g_i, g_t, s, rank * b, mode, True)   # gathered backward: lse all-gather
         (loss / world).backward()
 
         # ---- emulation of all ranks on this device ----
