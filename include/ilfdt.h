@@ -57,6 +57,10 @@ int32_t ilfdt_cast_bf16(const float* src, void* dst_bf16, int64_t n, void* strea
  * tensor-core score of a pad token exactly the 0 that clip_fdt.py:125-130 produces by multiplying. */
 int32_t ilfdt_cast_bf16_rows(const float* src, const float* rowmask, int64_t rows, int64_t cols, void* dst_bf16,
                              void* stream);
+/* The same for a q that already is bf16 (a producer running under bf16 autocast, or host buffers kept in
+ * bf16): dst_bf16[r, :] = rowmask[r] == 0 ? src_bf16[r, :] : 0. */
+int32_t ilfdt_mask_rows_bf16(const void* src_bf16, const float* rowmask, int64_t rows, int64_t cols,
+                             void* dst_bf16, void* stream);
 /* src [rows, cols] f32 or bf16 -> dst_bf16 [cols, rows] */
 int32_t ilfdt_transpose_bf16(const void* src, int32_t src_dtype, int64_t rows, int64_t cols,
                              void* dst_bf16, void* stream);
@@ -98,7 +102,8 @@ int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs,
 /* ---- a13: backward of the score block through max-pool + sparsemax ------------------------- */
 /* Inputs: g [b,K] = dLoss/dw (f32, OVERWRITTEN with coef), w [b,K], arg [b,K], q, sd, mask as in
  * ilfdt_ground_fwd.  coef[b,k] = nz*(g - mean_nz g) * keep[b,arg] / (sqrt_d*temperature);
- * dq[b,arg[b,k],:] += coef*sd[k,:]  (dq [b,n_tok,D] f32, fully written);
+ * dq[b,arg[b,k],:] += coef*sd[k,:]  (dq [b,n_tok,D], dq_dtype F32 or BF16 = the dtype q had at the caller,
+ * fully written);
  * dsd[k,:] += coef*q[b,arg[b,k],:]   (dsd [K,D] f32, ACCUMULATED into).
  * Only support entries (w>0) are touched: cost scales with nnz, not with n_tok*K.
  * w == NULL: g already holds dLoss/dpooled (softmax / sigmoid attention): no support, no mean to
@@ -106,7 +111,7 @@ int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs,
 int32_t ilfdt_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd,
                          int32_t dtype, const float* mask, int64_t b, int64_t n_tok, int64_t K,
                          int64_t D, float sqrt_d, float temperature,
-                         float* dq, float* dsd, void* stream);
+                         void* dq, int32_t dq_dtype, float* dsd, void* stream);
 
 /* ---- non-default Query_model variants, clip_fdt.py:67-78,140-157 ----------------------------------- */
 enum { ILFDT_ATT_SOFTMAX = 1, ILFDT_ATT_SIGMOID = 2 };

@@ -162,6 +162,14 @@ int32_t ilfdt_cast_bf16_rows(const float* src, const float* rowmask, int64_t row
   return launch_cast_bf16_rows(src, rowmask, rows, cols, dst_bf16, ST(stream));
 }
 
+int32_t ilfdt_mask_rows_bf16(const void* src_bf16, const float* rowmask, int64_t rows, int64_t cols, void* dst_bf16,
+                             void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(rows >= 0 && cols >= 0 && (rows * cols == 0 || (src_bf16 && rowmask && dst_bf16)), ILFDT_E_INVALID_ARG,
+                "mask_rows_bf16: bad arguments");
+  return launch_mask_rows_bf16(src_bf16, rowmask, rows, cols, dst_bf16, ST(stream));
+}
+
 int32_t ilfdt_transpose_bf16(const void* src, int32_t src_dtype, int64_t rows, int64_t cols, void* dst_bf16,
                              void* stream) {
   ARCH_GUARD();
@@ -235,12 +243,14 @@ int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs, const
 
 int32_t ilfdt_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd, int32_t dtype,
                          const float* mask, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
-                         float temperature, float* dq, float* dsd, void* stream) {
+                         float temperature, void* dq, int32_t dq_dtype, float* dsd, void* stream) {
   ARCH_GUARD();
   DTYPE_GUARD(dtype);
+  DTYPE_GUARD(dq_dtype);
   ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && K >= 1 && D >= 1, ILFDT_E_INVALID_ARG, "ground_bwd: bad shape");
   ILFDT_REQUIRE(b == 0 || (g && arg && q && sd && dq && dsd), ILFDT_E_INVALID_ARG, "ground_bwd: null pointer");
-  return launch_ground_bwd(g, w, arg, q, sd, dtype, mask, b, n_tok, K, D, sqrt_d, temperature, dq, dsd, ST(stream));
+  return launch_ground_bwd(g, w, arg, q, sd, dtype, mask, b, n_tok, K, D, sqrt_d, temperature, dq, dq_dtype, dsd,
+                           ST(stream));
 }
 
 int32_t ilfdt_att_fwd(const float* z, int64_t rows, int64_t K, int32_t kind, float* w, float* rowsum, void* stream) {

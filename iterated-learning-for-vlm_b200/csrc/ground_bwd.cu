@@ -11,6 +11,7 @@
 #include "common.cuh"
 #include "launch.h"
 #include <algorithm>
+#include <cstdlib>
 
 namespace ilfdt {
 
@@ -475,54 +476,320 @@ ground_bwd_dq_sorted_kernel(float* __restrict__ g, const float* __restrict__ w, 
 }
 
 // ---------------------------------------------------------------------------------------------
-// kernel 2, tiled: a CTA owns GT_CODES = 16 consecutive codes (4 warps x 4 codes, 64 fp32 accumulators per
-// lane) and sweeps the samples 32 at a time. The [32 samples x 16 codes] tiles of coef / arg are read
-// with fully coalesced 16-byte loads (the strided per-warp reads of the kernel above cost 18x their
-// bytes in DRAM traffic, ncu r01), transposed through shared memory (double buffered, one barrier per
-// tile, next tile's global loads in flight during the gathers), then lane = sample as before.
+// kernel 1, v3: per-sample CTA of 256 threads; the preprocessing that dominated the sorted kernel above
+// (ncu r01: ~60 % of its stall samples sat in the scalar, dependent-load coef / histogram / placement
+// passes) is rebuilt around coalesced 16-byte loads and thread-private counters:
+//   pass 0  mean of g over the support (float4 loads, fp64 accumulation)
+//   pass A  each thread owns 64 codes of the 16384-code chunk as 16 coalesced float4 groups: coef is
+//           computed, written back over g (for kernel 2) and the thread's per-token counts go to its
+//           private column of hist[token][thread] (uint16, no atomics, no match_any)
+//   scan    per token over the 256 thread columns, then over tokens -> bucket bases
+//   pass B  the thread re-walks its (register-resident) live mask / tokens and drops each code index at
+//           base[token] + its running column offset: a counting sort whose order (thread, group, element)
+//           is fixed, so the summation order and the result are deterministic
+//   gather  warps take tokens dynamically; a bucket is read 32 entries at a time (code index from shared
+//           memory, coef from the L2-resident row just written), 4 codebook rows in flight per warp.
 // ---------------------------------------------------------------------------------------------
-constexpr int GT_WARPS = 4, GT_CPW = 4, GT_CODES = GT_WARPS * GT_CPW, GT_THREADS = GT_WARPS * 32;
+constexpr int G3_THREADS = 256, G3_WARPS = G3_THREADS / 32, G3_PER = 64, G3_CHUNK = G3_THREADS * G3_PER;  // 16384
+constexpr int G3_GROUPS = G3_PER / 4;
+constexpr int G3_MAX_TOK = 96;
 
-template <typename T, int NV>
-__global__ void __launch_bounds__(GT_THREADS)
-ground_bwd_dsd_tiled_kernel(const float* __restrict__ coef, const int16_t* __restrict__ arg, const T* __restrict__ q,
-                            int64_t b_total, int n_tok, int K, int D, int64_t b_per_split, int use_atomic,
-                            float* __restrict__ dsd) {
-  __shared__ float cf_s[2][GT_CODES][33];
-  __shared__ int16_t tk_s[2][GT_CODES][34];
+template <typename TO>
+struct StoreRow8;
+template <>
+struct StoreRow8<float> {
+  __device__ __forceinline__ static void st(float* o, const float (&a)[8], bool add) {
+    float4 x = make_float4(a[0], a[1], a[2], a[3]), y = make_float4(a[4], a[5], a[6], a[7]);
+    if (add) {
+      const float4 px = *reinterpret_cast<float4*>(o), py = *reinterpret_cast<float4*>(o + 4);
+      x.x += px.x; x.y += px.y; x.z += px.z; x.w += px.w;
+      y.x += py.x; y.y += py.y; y.z += py.z; y.w += py.w;
+    }
+    *reinterpret_cast<float4*>(o) = x;
+    *reinterpret_cast<float4*>(o + 4) = y;
+  }
+};
+template <>
+struct StoreRow8<__nv_bfloat16> {
+  __device__ __forceinline__ static void st(__nv_bfloat16* o, const float (&a)[8], bool add) {
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = a[j];
+    if (add) {
+      float p[8];
+      Load8<__nv_bfloat16>::ld(o, p);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += p[j];
+    }
+    uint4 r;
+    __nv_bfloat162 b0 = __floats2bfloat162_rn(v[0], v[1]), b1 = __floats2bfloat162_rn(v[2], v[3]);
+    __nv_bfloat162 b2 = __floats2bfloat162_rn(v[4], v[5]), b3 = __floats2bfloat162_rn(v[6], v[7]);
+    r.x = *reinterpret_cast<uint32_t*>(&b0); r.y = *reinterpret_cast<uint32_t*>(&b1);
+    r.z = *reinterpret_cast<uint32_t*>(&b2); r.w = *reinterpret_cast<uint32_t*>(&b3);
+    *reinterpret_cast<uint4*>(o) = r;
+  }
+};
+
+template <typename T, int NV, typename TO>
+__global__ void __launch_bounds__(G3_THREADS, 3)
+ground_bwd_dq_v3_kernel(float* __restrict__ g, const float* __restrict__ w, const int16_t* __restrict__ arg,
+                        const T* __restrict__ sd, const float* __restrict__ mask, int n_tok, int K, int D,
+                        float inv_scale, TO* __restrict__ dq) {
+  extern __shared__ __align__(16) unsigned char gb_smem[];
+  uint16_t* hist = reinterpret_cast<uint16_t*>(gb_smem);                                    // [n_tok][256]
+  uint16_t* sorted_k = reinterpret_cast<uint16_t*>(gb_smem + (size_t)n_tok * G3_THREADS * 2);  // [G3_CHUNK]
+  int* base = reinterpret_cast<int*>(sorted_k + G3_CHUNK);                                  // [n_tok + 1]
+  float* keep_s = reinterpret_cast<float*>(base + G3_MAX_TOK + 1);                          // [n_tok]
+  __shared__ double red_s[G3_WARPS];
+  __shared__ int red_c[G3_WARPS];
+  __shared__ int next_tok;
+  const int64_t b = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  float* gr = g + b * K;
+  const float* wr = w ? w + b * K : nullptr;
+  const int16_t* ar = arg + b * K;
+
+  for (int t = tid; t < n_tok; t += G3_THREADS) keep_s[t] = (mask == nullptr || mask[b * n_tok + t] == 0.f) ? 1.f : 0.f;
+
+  // pass 0: mean of g over the support
+  double s = 0.0;
+  int c = 0;
+  if (wr != nullptr) {
+    for (int i = tid * 4; i < K; i += G3_THREADS * 4) {
+      const float4 wv = __ldg(reinterpret_cast<const float4*>(wr + i));
+      const float4 gv = *reinterpret_cast<const float4*>(gr + i);
+      if (wv.x > 0.f) { s += (double)gv.x; ++c; }
+      if (wv.y > 0.f) { s += (double)gv.y; ++c; }
+      if (wv.z > 0.f) { s += (double)gv.z; ++c; }
+      if (wv.w > 0.f) { s += (double)gv.w; ++c; }
+    }
+  }
+  s = warp_sum(s);
+  c = warp_sum(c);
+  if (lane == 0) { red_s[warp] = s; red_c[warp] = c; }
+  __syncthreads();
+  s = 0.0; c = 0;
+#pragma unroll
+  for (int i = 0; i < G3_WARPS; ++i) { s += red_s[i]; c += red_c[i]; }
+  const float mean = c > 0 ? (float)(s / (double)c) : 0.f;
+
+  for (int k0 = 0; k0 < K; k0 += G3_CHUNK) {
+    // zero the counters (the previous chunk's gather phase is over: barrier at the loop tail)
+    {
+      uint4* h4 = reinterpret_cast<uint4*>(hist);
+      const int n16 = n_tok * G3_THREADS * 2 / 16;
+      for (int i = tid; i < n16; i += G3_THREADS) h4[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    __syncthreads();
+    // pass A
+    uint32_t live[G3_GROUPS / 8];   // 4 bits per group
+    uint32_t tk[G3_GROUPS];         // 4 tokens per group, one byte each
+#pragma unroll
+    for (int i = 0; i < G3_GROUPS / 8; ++i) live[i] = 0u;
+#pragma unroll
+    for (int i = 0; i < G3_GROUPS; ++i) {
+      const int kk = (i * G3_THREADS + tid) * 4;
+      const int k = k0 + kk;
+      uint32_t lv = 0u, tkp = 0u;
+      if (k < K) {
+        float4 wv = make_float4(1.f, 1.f, 1.f, 1.f);
+        if (wr != nullptr) wv = __ldg(reinterpret_cast<const float4*>(wr + k));
+        const float4 gv = *reinterpret_cast<const float4*>(gr + k);
+        const uint2 av = __ldg(reinterpret_cast<const uint2*>(ar + k));
+        const int t0 = av.x & 0xffff, t1 = av.x >> 16, t2 = av.y & 0xffff, t3 = av.y >> 16;
+        float4 cf;
+        cf.x = wv.x > 0.f ? (gv.x - mean) * keep_s[t0] * inv_scale : 0.f;
+        cf.y = wv.y > 0.f ? (gv.y - mean) * keep_s[t1] * inv_scale : 0.f;
+        cf.z = wv.z > 0.f ? (gv.z - mean) * keep_s[t2] * inv_scale : 0.f;
+        cf.w = wv.w > 0.f ? (gv.w - mean) * keep_s[t3] * inv_scale : 0.f;
+        *reinterpret_cast<float4*>(gr + k) = cf;   // g now holds coef for kernel 2
+        tkp = (uint32_t)t0 | ((uint32_t)t1 << 8) | ((uint32_t)t2 << 16) | ((uint32_t)t3 << 24);
+        if (cf.x != 0.f) { lv |= 1u; hist[t0 * G3_THREADS + tid] += 1; }
+        if (cf.y != 0.f) { lv |= 2u; hist[t1 * G3_THREADS + tid] += 1; }
+        if (cf.z != 0.f) { lv |= 4u; hist[t2 * G3_THREADS + tid] += 1; }
+        if (cf.w != 0.f) { lv |= 8u; hist[t3 * G3_THREADS + tid] += 1; }
+      }
+      tk[i] = tkp;
+      live[i >> 3] |= lv << ((i & 7) * 4);
+    }
+    __syncthreads();
+    // scan over the thread columns of each token: hist[t][*] -> exclusive prefix, total -> base[t + 1]
+    for (int t = warp; t < n_tok; t += G3_WARPS) {
+      uint4 v = *reinterpret_cast<uint4*>(hist + t * G3_THREADS + lane * 8);
+      uint32_t x[8] = {v.x & 0xffff, v.x >> 16, v.y & 0xffff, v.y >> 16, v.z & 0xffff, v.z >> 16, v.w & 0xffff, v.w >> 16};
+      uint32_t run = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { const uint32_t y = x[j]; x[j] = run; run += y; }
+      uint32_t incl = run;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += n;
+      }
+      const uint32_t off = incl - run;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) x[j] += off;
+      v.x = x[0] | (x[1] << 16); v.y = x[2] | (x[3] << 16); v.z = x[4] | (x[5] << 16); v.w = x[6] | (x[7] << 16);
+      *reinterpret_cast<uint4*>(hist + t * G3_THREADS + lane * 8) = v;
+      if (lane == 31) base[t + 1] = (int)incl;
+    }
+    __syncthreads();
+    if (warp == 0) {  // inclusive scan of base[1..n_tok] (n_tok <= 96: 3 per lane)
+      int loc[3], sum = 0;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const int t = lane * 3 + j;
+        loc[j] = t < n_tok ? base[t + 1] : 0;
+        sum += loc[j];
+      }
+      int incl = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += n;
+      }
+      int run = incl - sum;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const int t = lane * 3 + j;
+        run += loc[j];
+        if (t < n_tok) base[t + 1] = run;
+      }
+      if (lane == 0) { base[0] = 0; next_tok = 0; }
+    }
+    __syncthreads();
+    // pass B: placement
+#pragma unroll
+    for (int i = 0; i < G3_GROUPS; ++i) {
+      const uint32_t lv = (live[i >> 3] >> ((i & 7) * 4)) & 15u;
+      const int kk = (i * G3_THREADS + tid) * 4;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (lv & (1u << j)) {
+          const int t = (tk[i] >> (8 * j)) & 255;
+          const int h = hist[t * G3_THREADS + tid];
+          hist[t * G3_THREADS + tid] = (uint16_t)(h + 1);
+          sorted_k[base[t] + h] = (uint16_t)(kk + j);
+        }
+      }
+    }
+    __syncthreads();
+    // gather
+    const float* coef_row = gr + k0;
+    for (;;) {
+      int t = 0;
+      if (lane == 0) t = atomicAdd(&next_tok, 1);
+      t = __shfl_sync(0xffffffffu, t, 0);
+      if (t >= n_tok) break;
+      const int lo = base[t], hi = base[t + 1];
+      float acc[NV][8];
+#pragma unroll
+      for (int i = 0; i < NV; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+      for (int e0 = lo; e0 < hi; e0 += 32) {
+        int myk = 0;
+        float myc = 0.f;
+        if (e0 + lane < hi) {
+          myk = sorted_k[e0 + lane];
+          myc = coef_row[myk];
+        }
+        const int n = min(32, hi - e0);
+        int j = 0;
+        if constexpr (sizeof(T) == 2)  // bf16 rows: keep 4 of them in flight as raw 16-byte vectors
+        for (; j + 4 <= n; j += 4) {
+          uint4 raw[4][NV];
+          float cc[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int kq = __shfl_sync(0xffffffffu, myk, j + u);
+            cc[u] = __shfl_sync(0xffffffffu, myc, j + u);
+            const T* row = sd + (int64_t)(k0 + kq) * D;
+#pragma unroll
+            for (int i = 0; i < NV; ++i) raw[u][i] = __ldg(reinterpret_cast<const uint4*>(row + (i * 32 + lane) * 8));
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+              const uint32_t ww[4] = {raw[u][i].x, raw[u][i].y, raw[u][i].z, raw[u][i].w};
+#pragma unroll
+              for (int q2 = 0; q2 < 4; ++q2) {
+                acc[i][2 * q2] = fmaf(cc[u], __uint_as_float(ww[q2] << 16), acc[i][2 * q2]);
+                acc[i][2 * q2 + 1] = fmaf(cc[u], __uint_as_float(ww[q2] & 0xffff0000u), acc[i][2 * q2 + 1]);
+              }
+            }
+        }
+        for (; j < n; ++j) {
+          const int kq = __shfl_sync(0xffffffffu, myk, j);
+          const float c0 = __shfl_sync(0xffffffffu, myc, j);
+          gb_axpy<T, NV>(sd + (int64_t)(k0 + kq) * D, c0, lane, acc);
+        }
+      }
+      TO* out = dq + (b * n_tok + t) * (int64_t)D;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) StoreRow8<TO>::st(out + (i * 32 + lane) * 8, acc[i], k0 > 0);
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernel 2, v3: the tiled kernel above with its shape opened up for tuning: WARPS x CPW codes per CTA and U
+// q rows in flight per warp (ncu r01: the 4x4/U=2 shape ran 3.5 warps per scheduler, stalled on the row
+// gathers with neither L2 nor the issue slots saturated -- the kernel is bound by loads in flight).
+// ---------------------------------------------------------------------------------------------
+template <typename T, int NV, int WARPS, int CPW, int U>
+__global__ void __launch_bounds__(WARPS * 32)
+ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restrict__ arg, const T* __restrict__ q,
+                         int64_t b_total, int n_tok, int K, int D, int64_t b_per_split, int use_atomic,
+                         float* __restrict__ dsd) {
+  constexpr int CODES = WARPS * CPW, THREADS = WARPS * 32, QUADS = CODES / 4, SLOTS = 32 * QUADS;
+  constexpr int LPT = (SLOTS + THREADS - 1) / THREADS;   // (sample, 4-code quad) slots per thread per tile
+  __shared__ float cf_s[2][CODES][33];
+  __shared__ int16_t tk_s[2][CODES][34];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int k0 = blockIdx.x * GT_CODES;
+  const int k0 = blockIdx.x * CODES;
   const int64_t b_begin = (int64_t)blockIdx.y * b_per_split;
   const int64_t b_end = min(b_total, b_begin + b_per_split);
   const int nblk = (int)((b_end - b_begin + 31) / 32);
-  // loader role: thread -> (sample row, 4-code quad)
-  const int ld_s = threadIdx.x >> 2, ld_q = (threadIdx.x & 3) * 4;
 
-  float acc[GT_CPW][NV][8];
+  float acc[CPW][NV][8];
 #pragma unroll
-  for (int c = 0; c < GT_CPW; ++c)
+  for (int c = 0; c < CPW; ++c)
 #pragma unroll
     for (int i = 0; i < NV; ++i)
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[c][i][j] = 0.f;
 
-  float4 rc = make_float4(0.f, 0.f, 0.f, 0.f);
-  uint2 rt = make_uint2(0u, 0u);
+  float4 rc[LPT];
+  uint2 rt[LPT];
   auto load_tile = [&](int blk) {
-    const int64_t bb = b_begin + (int64_t)blk * 32 + ld_s;
-    if (bb < b_end) {
-      rc = __ldg(reinterpret_cast<const float4*>(coef + bb * K + k0 + ld_q));
-      rt = __ldg(reinterpret_cast<const uint2*>(arg + bb * K + k0 + ld_q));
-    } else {
-      rc = make_float4(0.f, 0.f, 0.f, 0.f);
-      rt = make_uint2(0u, 0u);
+#pragma unroll
+    for (int l = 0; l < LPT; ++l) {
+      const int slot = threadIdx.x + l * THREADS;
+      const int ld_s = slot / QUADS, ld_q = (slot % QUADS) * 4;
+      const int64_t bb = b_begin + (int64_t)blk * 32 + ld_s;
+      rc[l] = make_float4(0.f, 0.f, 0.f, 0.f);
+      rt[l] = make_uint2(0u, 0u);
+      if (slot < SLOTS && bb < b_end) {
+        rc[l] = __ldg(reinterpret_cast<const float4*>(coef + bb * K + k0 + ld_q));
+        rt[l] = __ldg(reinterpret_cast<const uint2*>(arg + bb * K + k0 + ld_q));
+      }
     }
   };
   auto store_tile = [&](int buf) {
-    cf_s[buf][ld_q + 0][ld_s] = rc.x; cf_s[buf][ld_q + 1][ld_s] = rc.y;
-    cf_s[buf][ld_q + 2][ld_s] = rc.z; cf_s[buf][ld_q + 3][ld_s] = rc.w;
-    tk_s[buf][ld_q + 0][ld_s] = (int16_t)(rt.x & 0xffff); tk_s[buf][ld_q + 1][ld_s] = (int16_t)(rt.x >> 16);
-    tk_s[buf][ld_q + 2][ld_s] = (int16_t)(rt.y & 0xffff); tk_s[buf][ld_q + 3][ld_s] = (int16_t)(rt.y >> 16);
+#pragma unroll
+    for (int l = 0; l < LPT; ++l) {
+      const int slot = threadIdx.x + l * THREADS;
+      if (slot < SLOTS) {
+        const int ld_s = slot / QUADS, ld_q = (slot % QUADS) * 4;
+        cf_s[buf][ld_q + 0][ld_s] = rc[l].x; cf_s[buf][ld_q + 1][ld_s] = rc[l].y;
+        cf_s[buf][ld_q + 2][ld_s] = rc[l].z; cf_s[buf][ld_q + 3][ld_s] = rc[l].w;
+        tk_s[buf][ld_q + 0][ld_s] = (int16_t)(rt[l].x & 0xffff); tk_s[buf][ld_q + 1][ld_s] = (int16_t)(rt[l].x >> 16);
+        tk_s[buf][ld_q + 2][ld_s] = (int16_t)(rt[l].y & 0xffff); tk_s[buf][ld_q + 3][ld_s] = (int16_t)(rt[l].y >> 16);
+      }
+    }
   };
 
   if (nblk > 0) {
@@ -535,34 +802,47 @@ ground_bwd_dsd_tiled_kernel(const float* __restrict__ coef, const int16_t* __res
     if (blk + 1 < nblk) load_tile(blk + 1);
     const int64_t b0 = b_begin + (int64_t)blk * 32;
 #pragma unroll
-    for (int c = 0; c < GT_CPW; ++c) {
-      const float cf = cf_s[buf][warp * GT_CPW + c][lane];
-      const int t = tk_s[buf][warp * GT_CPW + c][lane];
+    for (int c = 0; c < CPW; ++c) {
+      const float cf = cf_s[buf][warp * CPW + c][lane];
+      const int t = tk_s[buf][warp * CPW + c][lane];
+      // row index of this lane's entry: (sample * n_tok + token)
+      const int64_t myrow = (b0 + lane) * n_tok + t;
       unsigned m = __ballot_sync(0xffffffffu, cf != 0.f);
       while (m) {
-        const int j0 = __ffs(m) - 1;
-        m &= m - 1;
-        const int t0 = __shfl_sync(0xffffffffu, t, j0);
-        const float c0 = __shfl_sync(0xffffffffu, cf, j0);
-        const T* r0 = q + ((b0 + j0) * n_tok + t0) * (int64_t)D;
-        if (m) {
-          const int j1 = __ffs(m) - 1;
-          m &= m - 1;
-          const int t1 = __shfl_sync(0xffffffffu, t, j1);
-          const float c1 = __shfl_sync(0xffffffffu, cf, j1);
-          const T* r1 = q + ((b0 + j1) * n_tok + t1) * (int64_t)D;
-          float v0[NV][8], v1[NV][8];
+        const int n = min(__popc(m), U);
+        float cc[U];
+        uint4 raw[U][NV];
 #pragma unroll
-          for (int i = 0; i < NV; ++i) {
-            Load8<T>::ld(r0 + (i * 32 + lane) * 8, v0[i]);
-            Load8<T>::ld(r1 + (i * 32 + lane) * 8, v1[i]);
+        for (int u = 0; u < U; ++u) {
+          if (u < n) {
+            const int j = __ffs(m) - 1;
+            m &= m - 1;
+            cc[u] = __shfl_sync(0xffffffffu, cf, j);
+            const int64_t rr = __shfl_sync(0xffffffffu, myrow, j);
+            const T* row = q + rr * D;
+            if constexpr (sizeof(T) == 2) {
+#pragma unroll
+              for (int i = 0; i < NV; ++i) raw[u][i] = __ldg(reinterpret_cast<const uint4*>(row + (i * 32 + lane) * 8));
+            } else {
+              gb_axpy<T, NV>(row, cc[u], lane, acc[c]);
+            }
           }
+        }
+        if constexpr (sizeof(T) == 2) {
 #pragma unroll
-          for (int i = 0; i < NV; ++i)
+          for (int u = 0; u < U; ++u) {
+            if (u < n) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[c][i][j] = fmaf(c1, v1[i][j], fmaf(c0, v0[i][j], acc[c][i][j]));
-        } else {
-          gb_axpy<T, NV>(r0, c0, lane, acc[c]);
+              for (int i = 0; i < NV; ++i) {
+                const uint32_t ww[4] = {raw[u][i].x, raw[u][i].y, raw[u][i].z, raw[u][i].w};
+#pragma unroll
+                for (int q2 = 0; q2 < 4; ++q2) {
+                  acc[c][i][2 * q2] = fmaf(cc[u], __uint_as_float(ww[q2] << 16), acc[c][i][2 * q2]);
+                  acc[c][i][2 * q2 + 1] = fmaf(cc[u], __uint_as_float(ww[q2] & 0xffff0000u), acc[c][i][2 * q2 + 1]);
+                }
+              }
+            }
+          }
         }
       }
     }
@@ -570,8 +850,8 @@ ground_bwd_dsd_tiled_kernel(const float* __restrict__ coef, const int16_t* __res
     __syncthreads();
   }
 #pragma unroll
-  for (int c = 0; c < GT_CPW; ++c) {
-    float* out = dsd + (int64_t)(k0 + warp * GT_CPW + c) * D;
+  for (int c = 0; c < CPW; ++c) {
+    float* out = dsd + (int64_t)(k0 + warp * CPW + c) * D;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       float* o = out + (i * 32 + lane) * 8;
@@ -579,23 +859,69 @@ ground_bwd_dsd_tiled_kernel(const float* __restrict__ coef, const int16_t* __res
 #pragma unroll
         for (int j = 0; j < 8; ++j) atomicAdd(o + j, acc[c][i][j]);
       } else {
-        float4 pa = *reinterpret_cast<float4*>(o), pb = *reinterpret_cast<float4*>(o + 4);
-        pa.x += acc[c][i][0]; pa.y += acc[c][i][1]; pa.z += acc[c][i][2]; pa.w += acc[c][i][3];
-        pb.x += acc[c][i][4]; pb.y += acc[c][i][5]; pb.z += acc[c][i][6]; pb.w += acc[c][i][7];
-        *reinterpret_cast<float4*>(o) = pa;
-        *reinterpret_cast<float4*>(o + 4) = pb;
+        StoreRow8<float>::st(o, acc[c][i], true);
       }
     }
   }
 }
 
+template <typename T, int NV, int WARPS, int CPW, int U>
+static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, int64_t b, int64_t n_tok, int64_t K,
+                             int64_t D, float* dsd, cudaStream_t st) {
+  constexpr int CODES = WARPS * CPW;
+  const int64_t groups = K / CODES;
+  int64_t nsplit = 1;
+  const int64_t target = 4ll * sm_count();
+  if (groups < target) nsplit = std::min<int64_t>(cdiv(target, groups), std::max<int64_t>(1, b / 256));
+  nsplit = std::min<int64_t>(std::max<int64_t>(nsplit, 1), 65535);
+  int64_t per = round_up(cdiv(b, nsplit), 32);
+  nsplit = cdiv(b, per);
+  dim3 grid((unsigned)groups, (unsigned)nsplit);
+  ground_bwd_dsd_v3_kernel<T, NV, WARPS, CPW, U><<<grid, WARPS * 32, 0, st>>>(g, arg, q, b, (int)n_tok, (int)K, (int)D,
+                                                                             per, nsplit > 1 ? 1 : 0, dsd);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
+template <typename T, int NV, typename TO>
+static int32_t launch_dq_v3(float* g, const float* w, const int16_t* arg, const T* sd, const float* mask, int64_t b,
+                            int64_t n_tok, int64_t K, int64_t D, float inv_scale, TO* dq, cudaStream_t st) {
+  const size_t smem = (size_t)n_tok * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 + (G3_MAX_TOK + 1) * sizeof(int) +
+                      G3_MAX_TOK * sizeof(float);
+  ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_v3_kernel<T, NV, TO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)((size_t)G3_MAX_TOK * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 +
+                                           (G3_MAX_TOK + 1) * sizeof(int) + G3_MAX_TOK * sizeof(float))));
+  ground_bwd_dq_v3_kernel<T, NV, TO><<<(unsigned)b, G3_THREADS, smem, st>>>(g, w, arg, sd, mask, (int)n_tok, (int)K,
+                                                                           (int)D, inv_scale, dq);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
 template <typename T, int NV>
 static int32_t launch_ground_bwd_t(float* g, const float* w, const int16_t* arg, const T* q, const T* sd,
                                    const float* mask, int64_t b, int64_t n_tok, int64_t K, int64_t D,
-                                   float inv_scale, float* dq, float* dsd, cudaStream_t st) {
+                                   float inv_scale, void* dq_v, int dq_dtype, float* dsd, cudaStream_t st) {
   bool done = false;
+  float* dq = reinterpret_cast<float*>(dq_v);
+  static const int skip = getenv("ILFDT_GBWD_SKIP") ? atoi(getenv("ILFDT_GBWD_SKIP")) : 0;  // tuning only: 1 = no dq, 2 = no dsd
+  if (skip == 1) done = true;
   if constexpr (NV > 0) {
-    if (n_tok <= 256) {
+    const bool v3_ok = n_tok <= G3_MAX_TOK && K % 4 == 0 &&
+                       ((reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(w)) & 15) == 0 &&
+                       (reinterpret_cast<uintptr_t>(arg) & 7) == 0;
+    if (v3_ok && !done) {
+      int32_t rc = dq_dtype == ILFDT_BF16
+                       ? launch_dq_v3<T, NV, __nv_bfloat16>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale,
+                                                            reinterpret_cast<__nv_bfloat16*>(dq_v), st)
+                       : launch_dq_v3<T, NV, float>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, st);
+      if (rc != ILFDT_OK) return rc;
+      done = true;
+    }
+  }
+  ILFDT_REQUIRE(done || dq_dtype == ILFDT_F32, ILFDT_E_UNSUPPORTED_SHAPE,
+                "ground_bwd: bf16 dq needs D in {256,512,768,1024}, n_tok <= %d, K %% 4 == 0", G3_MAX_TOK);
+  if constexpr (NV > 0) {
+    if (!done && n_tok <= 256) {
       const size_t smem2 = GB_CHUNK * sizeof(GbEnt2) + (size_t)(GB_WARPS * n_tok + n_tok + 1) * sizeof(int);
       ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_sorted_kernel<T, NV>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -614,20 +940,25 @@ static int32_t launch_ground_bwd_t(float* g, const float* w, const int16_t* arg,
                                                                       (int)D, inv_scale, dq);
     ILFDT_LAUNCH_OK();
   }
+  if (skip == 2) return ILFDT_OK;
   if constexpr (NV > 0) {
-    if (K % GT_CODES == 0 && ((reinterpret_cast<uintptr_t>(g) & 15) | (reinterpret_cast<uintptr_t>(arg) & 7)) == 0) {
-      const int64_t groups = K / GT_CODES;
-      int64_t nsplit = 1;
-      const int64_t target = 4ll * sm_count();
-      if (groups < target) nsplit = std::min<int64_t>(cdiv(target, groups), std::max<int64_t>(1, b / 256));
-      nsplit = std::min<int64_t>(std::max<int64_t>(nsplit, 1), 65535);
-      int64_t per = round_up(cdiv(b, nsplit), 32);
-      nsplit = cdiv(b, per);
-      dim3 grid((unsigned)groups, (unsigned)nsplit);
-      ground_bwd_dsd_tiled_kernel<T, NV><<<grid, GT_THREADS, 0, st>>>(g, arg, q, b, (int)n_tok, (int)K, (int)D, per,
-                                                                     nsplit > 1 ? 1 : 0, dsd);
-      ILFDT_LAUNCH_OK();
-      return ILFDT_OK;
+    // shape of kernel 2 (warps x codes per warp, rows in flight), tuned on B200 at b = 8192, K = 16384, D = 512
+    // (tools/tune_gbwd.py): 4x1 codes with 4 rows in flight beat the original 4x4/2 by 1.4x. ILFDT_DSD_CFG
+    // overrides the shape for tuning runs.
+    static const int cfg = getenv("ILFDT_DSD_CFG") ? atoi(getenv("ILFDT_DSD_CFG")) : 0;
+    if (K % 32 == 0 && ((reinterpret_cast<uintptr_t>(g) & 15) | (reinterpret_cast<uintptr_t>(arg) & 7)) == 0) {
+      if constexpr (NV <= 2) {
+        switch (cfg) {
+          case 1: return launch_dsd_v3<T, NV, 4, 4, 2>(g, arg, q, b, n_tok, K, D, dsd, st);
+          case 2: return launch_dsd_v3<T, NV, 4, 4, 4>(g, arg, q, b, n_tok, K, D, dsd, st);
+          case 5: return launch_dsd_v3<T, NV, 8, 1, 4>(g, arg, q, b, n_tok, K, D, dsd, st);
+          case 7: return launch_dsd_v3<T, NV, 4, 2, 4>(g, arg, q, b, n_tok, K, D, dsd, st);
+          case 14: return launch_dsd_v3<T, NV, 8, 1, 2>(g, arg, q, b, n_tok, K, D, dsd, st);
+          default: return launch_dsd_v3<T, NV, 4, 1, 4>(g, arg, q, b, n_tok, K, D, dsd, st);
+        }
+      } else {
+        return launch_dsd_v3<T, NV, 4, 1, 2>(g, arg, q, b, n_tok, K, D, dsd, st);
+      }
     }
   }
   // split the sample range when there are too few code groups to fill the machine
@@ -647,31 +978,31 @@ static int32_t launch_ground_bwd_t(float* g, const float* w, const int16_t* arg,
 
 template <typename T>
 static int32_t dispatch_nv(float* g, const float* w, const int16_t* arg, const T* q, const T* sd, const float* mask,
-                           int64_t b, int64_t n_tok, int64_t K, int64_t D, float inv_scale, float* dq, float* dsd,
-                           cudaStream_t st) {
+                           int64_t b, int64_t n_tok, int64_t K, int64_t D, float inv_scale, void* dq, int dq_dtype,
+                           float* dsd, cudaStream_t st) {
   const bool aligned = ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(sd) |
                          reinterpret_cast<uintptr_t>(dq) | reinterpret_cast<uintptr_t>(dsd)) & 31) == 0;
-  if (aligned && D == 512) return launch_ground_bwd_t<T, 2>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dsd, st);
-  if (aligned && D == 256) return launch_ground_bwd_t<T, 1>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dsd, st);
-  if (aligned && D == 768) return launch_ground_bwd_t<T, 3>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dsd, st);
-  if (aligned && D == 1024) return launch_ground_bwd_t<T, 4>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dsd, st);
+  if (aligned && D == 512) return launch_ground_bwd_t<T, 2>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 256) return launch_ground_bwd_t<T, 1>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 768) return launch_ground_bwd_t<T, 3>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 1024) return launch_ground_bwd_t<T, 4>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
   ILFDT_REQUIRE(D <= 1024, ILFDT_E_UNSUPPORTED_SHAPE, "ground_bwd: D=%lld > 1024", (long long)D);
-  return launch_ground_bwd_t<T, 0>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dsd, st);
+  return launch_ground_bwd_t<T, 0>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
 }
 
 int32_t launch_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd, int dtype,
                           const float* mask, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
-                          float temperature, float* dq, float* dsd, cudaStream_t st) {
+                          float temperature, void* dq, int dq_dtype, float* dsd, cudaStream_t st) {
   if (b == 0) return ILFDT_OK;
   ILFDT_REQUIRE(b < (1ll << 31) && K < (1ll << 31) && n_tok <= 32767, ILFDT_E_UNSUPPORTED_SHAPE,
                 "ground_bwd: shape out of range");
   const float inv_scale = 1.f / (sqrt_d * temperature);
   if (dtype == ILFDT_F32)
     return dispatch_nv<float>(g, w, arg, reinterpret_cast<const float*>(q), reinterpret_cast<const float*>(sd), mask,
-                              b, n_tok, K, D, inv_scale, dq, dsd, st);
+                              b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
   return dispatch_nv<__nv_bfloat16>(g, w, arg, reinterpret_cast<const __nv_bfloat16*>(q),
                                     reinterpret_cast<const __nv_bfloat16*>(sd), mask, b, n_tok, K, D, inv_scale, dq,
-                                    dsd, st);
+                                    dq_dtype, dsd, st);
 }
 
 }  // namespace ilfdt

@@ -457,6 +457,28 @@ int32_t launch_cast_bf16_rows(const float* src, const float* rowmask, int64_t ro
   return ILFDT_OK;
 }
 
+// bf16 -> bf16 copy with the masked (pad) rows zeroed: the q operand of the tensor-core score kernel when
+// the caller already holds q in bf16 (same contract as cast_bf16_rows for fp32 q).
+__global__ void mask_rows_bf16_kernel(const uint4* __restrict__ src, const float* __restrict__ rowmask, int64_t rows,
+                                      int cols8, uint4* __restrict__ dst) {
+  const int64_t total = rows * (int64_t)cols8;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const bool keep = __ldg(rowmask + i / cols8) == 0.f;
+  dst[i] = keep ? __ldg(src + i) : make_uint4(0u, 0u, 0u, 0u);
+}
+int32_t launch_mask_rows_bf16(const void* src, const float* rowmask, int64_t rows, int64_t cols, void* dst,
+                              cudaStream_t st) {
+  if (rows * cols == 0) return ILFDT_OK;
+  ILFDT_REQUIRE(cols % 8 == 0 && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0,
+                ILFDT_E_UNSUPPORTED_SHAPE, "mask_rows_bf16: cols %% 8 == 0 and 16-byte aligned pointers required");
+  const int64_t total = rows * (cols / 8);
+  mask_rows_bf16_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(reinterpret_cast<const uint4*>(src), rowmask, rows,
+                                                                   (int)(cols / 8), reinterpret_cast<uint4*>(dst));
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
 template <typename T>
 __global__ void transpose_bf16_kernel(const T* __restrict__ src, int64_t rows, int64_t cols,
                                       __nv_bfloat16* __restrict__ dst) {

@@ -30,6 +30,8 @@ int32_t launch_topk_hits(const float* L, int64_t b, int64_t B, int64_t label0, i
 int32_t launch_cast_bf16(const float* src, void* dst, int64_t n, cudaStream_t st);
 int32_t launch_cast_bf16_rows(const float* src, const float* rowmask, int64_t rows, int64_t cols, void* dst,
                               cudaStream_t st);
+int32_t launch_mask_rows_bf16(const void* src, const float* rowmask, int64_t rows, int64_t cols, void* dst,
+                              cudaStream_t st);
 int32_t launch_transpose_bf16(const void* src, int src_dtype, int64_t rows, int64_t cols, void* dst, cudaStream_t st);
 int32_t launch_randn_fill(float* dst, int64_t n, uint64_t seed, uint32_t gen, cudaStream_t st);
 
@@ -41,7 +43,7 @@ int32_t launch_sparsemax_bwd(const float* w, const float* g, int64_t rows, int64
 // ground_bwd.cu
 int32_t launch_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd, int dtype,
                           const float* mask, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
-                          float temperature, float* dq, float* dsd, cudaStream_t st);
+                          float temperature, void* dq, int dq_dtype, float* dsd, cudaStream_t st);
 
 // gemm_umma.cu (tcgen05)
 int32_t launch_gemm_nt_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha,

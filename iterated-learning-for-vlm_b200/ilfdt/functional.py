@@ -62,6 +62,9 @@ class GroundingFunction(torch.autograd.Function):
     def forward(ctx, q, sd, mask, temperature, mode):
         q = q.contiguous()
         sd_c = sd.contiguous()
+        ctx.q_dtype = q.dtype
+        if q.dtype == torch.bfloat16 and mode != "bf16":
+            raise RuntimeError("ilfdt: a bf16 q needs compute dtype 'bf16'")
         mask_f = None if mask is None else mask.to(torch.float32).contiguous()
         if mode == "bf16" and not (q.shape[2] % 8 == 0 and q.shape[2] <= 512 and q.shape[1] <= 256
                                    and sd.shape[0] % 8 == 0):
@@ -109,7 +112,13 @@ class GroundingFunction(torch.autograd.Function):
                 g.add_(dw)
         else:
             g = dw.contiguous().float().clone()
-        dq = ops.ground_bwd(g, w, arg, q_k, sd_k, mask_f, ctx.temperature, dsd)
+        dq_dtype = torch.float32
+        if ctx.q_dtype == torch.bfloat16 and mode == "bf16" and D in (256, 512, 768, 1024) and q_k.shape[1] <= 96 \
+                and K % 4 == 0:
+            dq_dtype = torch.bfloat16      # written directly by the scatter kernel
+        dq = ops.ground_bwd(g, w, arg, q_k, sd_k, mask_f, ctx.temperature, dsd, dq_dtype)
+        if dq.dtype != ctx.q_dtype:
+            dq = ops.cast_bf16(dq)
         return dq, dsd, None, None, None
 
 

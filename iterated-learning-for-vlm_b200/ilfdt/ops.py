@@ -19,7 +19,7 @@ def _stream():
 LAUNCHES = 0          # kernels launched through this module since it was last zeroed
 PROFILE_ON = False    # when True every C call is bracketed by CUDA events on the launching stream
 PROFILE = {}          # op name -> [(start_event, end_event), ...]
-_KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_sparsemax_fwd": 1,
+_KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mask_rows_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_sparsemax_fwd": 1,
                      "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2,
                      "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5,
                      "ilfdt_nce_bwd": 4, "ilfdt_nce_bwd_gathered": 2, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
@@ -69,7 +69,18 @@ def cast_bf16(x):
 
 
 def cast_bf16_rows(x, rowmask):
-    """x [..., C] f32 -> bf16 with the rows whose mask entry is non-zero (-inf = pad) zeroed."""
+    """x [..., C] f32 or bf16 -> bf16 with the rows whose mask entry is non-zero (-inf = pad) zeroed."""
+    if x.dtype == torch.bfloat16:
+        _req(x, torch.bfloat16, "x")
+        if rowmask is None:
+            return x
+        _req(rowmask, torch.float32, "rowmask")
+        cols = x.shape[-1]
+        rows = x.numel() // cols
+        assert rowmask.numel() == rows
+        out = torch.empty_like(x)
+        _call("ilfdt_mask_rows_bf16", _ptr(x), _ptr(rowmask), rows, cols, _ptr(out), _stream())
+        return out
     _req(x, torch.float32, "x")
     if rowmask is None:
         return cast_bf16(x)
@@ -163,18 +174,17 @@ def gemm_f32(A, B, a_t=False, b_t=False, alpha=1.0, out=None, accumulate=False):
     return out
 
 
-def ground_bwd(g, w, arg, q, sd, mask, temperature, dsd):
-    """g [b,K] is overwritten with coef. Returns dq [b,N,D] f32; accumulates into dsd [K,D] f32."""
+def ground_bwd(g, w, arg, q, sd, mask, temperature, dsd, dq_dtype=torch.float32):
+    """g [b,K] is overwritten with coef. Returns dq [b,N,D] (dq_dtype); accumulates into dsd [K,D] f32."""
     _req(g, torch.float32, "g"); _req(arg, torch.int16, "arg")
     if w is not None:   # None: g already is dLoss/dpooled (softmax / sigmoid attention)
         _req(w, torch.float32, "w")
     _req(q, None, "q"); _req(sd, q.dtype, "sd"); _req(dsd, torch.float32, "dsd")
     b, n_tok, D = q.shape
     K = sd.shape[0]
-    dq = torch.empty(b, n_tok, D, dtype=torch.float32, device=q.device)
+    dq = torch.empty(b, n_tok, D, dtype=dq_dtype, device=q.device)
     _call("ilfdt_ground_bwd", _ptr(g), _ptr(w), _ptr(arg), _ptr(q), _ptr(sd), _DT[q.dtype], _ptr(mask), b,
-                                       n_tok, K, D, float(math.sqrt(D)), float(temperature), _ptr(dq), _ptr(dsd),
-                                       _stream())
+          n_tok, K, D, float(math.sqrt(D)), float(temperature), _ptr(dq), _DT[dq_dtype], _ptr(dsd), _stream())
     return dq
 
 

@@ -199,7 +199,8 @@ def test_sparsemax_bwd_closed_form(ops):
 # a1-a3 + a13: grounding forward/backward through the autograd Function
 # ---------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("b,n_tok,K,D,masked", [(7, 9, 200, 64, True), (5, 49, 256, 512, False), (6, 77, 384, 512, True),
-                                               (4, 12, 9000, 256, True)])
+                                               (4, 12, 9000, 256, True), (3, 20, 20000, 256, True),
+                                               (3, 120, 512, 512, True)])
 @pytest.mark.parametrize("mode", ["fp32", "bf16"])
 def test_grounding_fwd_bwd(ops, b, n_tok, K, D, masked, mode):
     from ilfdt.functional import GroundingFunction
@@ -233,6 +234,34 @@ def test_grounding_fwd_bwd(ops, b, n_tok, K, D, masked, mode):
         if mism.any():
             margin = torch.maximum(w.cpu().double(), w_ref)[mism].max().item()
             assert margin < 1e-8, "support sets differ at entries with weight up to %.3e" % margin
+
+
+@pytest.mark.parametrize("b,n_tok,K,D,masked", [(6, 49, 1024, 512, False), (5, 77, 2048, 512, True), (3, 20, 20000, 256, True)])
+def test_grounding_bf16_q_input(ops, b, n_tok, K, D, masked):
+    """A q that already is bf16 (producer under autocast / bf16 host buffers) skips the cast: forward outputs are
+    bit-identical to the fp32-q call on the same values and dq comes back in bf16 from the scatter kernel."""
+    from ilfdt.functional import GroundingFunction
+    g = torch.Generator().manual_seed(b * n_tok + K)
+    q = bf16_round(torch.randn(b, n_tok, D, generator=g))
+    sd = bf16_round(torch.randn(K, D, generator=g))
+    mask = _mask(b, n_tok, torch.randint(1, n_tok + 1, (b,), generator=g).tolist()) if masked else None
+    up_f = torch.randn(b, D, generator=g).to(_dev())
+    md = None if mask is None else mask.to(_dev())
+    q32 = q.to(_dev()).requires_grad_(True)
+    sd32 = sd.to(_dev()).requires_grad_(True)
+    w32, f32 = GroundingFunction.apply(q32, sd32, md, 30.0, "bf16")
+    (f32 * up_f).sum().backward()
+    q16 = q.to(_dev()).to(torch.bfloat16).requires_grad_(True)
+    sd16 = sd.to(_dev()).requires_grad_(True)
+    w16, f16 = GroundingFunction.apply(q16, sd16, md, 30.0, "bf16")
+    (f16 * up_f).sum().backward()
+    assert torch.equal(w32, w16) and torch.equal(f32, f16)
+    assert q16.grad.dtype == torch.bfloat16
+    assert_close(q16.grad.float(), q32.grad, 8e-3, "dq (bf16 storage)")
+    assert_close(sd16.grad, sd32.grad, 1e-6, "dsd")
+    if mask is not None:
+        pad = (mask != 0).to(_dev())
+        assert q16.grad.float()[pad].abs().max().item() == 0.0
 
 
 QM_VARIANTS = [("smax", "sparsemax", "max"), ("smaxT", "sparsemax", "max"), ("softsum", "softmax", "sum"),
