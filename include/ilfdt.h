@@ -78,6 +78,24 @@ int32_t ilfdt_ground_fwd(const void* q, const void* sd, int32_t dtype, const flo
                          float* pooled, int16_t* arg, void* ws, int64_t ws_bytes, void* stream);
 
 /* ---- a2: Sparsemax, prototype/model/sparsemax.py:22-71 ------------------------------------ */
+/* a1 for padded text in BF16 (clip_fdt.py:113-145 with a pad mask). Every pad token scores exactly 0
+ * (clip_fdt.py:125-130), so only the rows [0, len_s] of sample s -- its valid tokens plus ONE pad -- can affect the
+ * max over tokens. ilfdt_text_compact plans on the DEVICE (no host sync): samples are bucketed by
+ * R = min(16*ceil((len+1)/16), n_tok), q (f32 or bf16) is cast into a compacted bf16 operand in bucket order with the
+ * pad rows zeroed, and `plan` (ilfdt_text_plan_ints(b) int32) receives per bucket {samples, first row, first slot,
+ * rows per sample} followed by slot_of[b], row_base[b], sample_of[b]. ilfdt_ground_fwd_text runs the tensor-core
+ * kernel once per bucket; pooled / arg [b,K] are bit-identical to ilfdt_ground_fwd on the full-width operand.
+ * groups_ws: b bytes of scratch; q_compact_bf16: room for b*n_tok rows. The backward takes plan's row_base
+ * (ilfdt_ground_bwd q_row_base). Supported when every bucket size has a static epilogue (n_tok 77, 49, <= 64 ...):
+ * ilfdt_ground_fwd_text_supported. */
+int64_t ilfdt_text_plan_ints(int64_t b);
+int32_t ilfdt_ground_fwd_text_supported(int64_t n_tok);
+int32_t ilfdt_text_compact(const void* q, int32_t q_dtype, const float* mask, int64_t b, int64_t n_tok, int64_t D,
+                           void* groups_ws, int32_t* plan, void* q_compact_bf16, void* stream);
+int32_t ilfdt_ground_fwd_text(const void* q_compact_bf16, const void* sd_bf16, const int32_t* plan, int64_t b,
+                              int64_t n_tok, int64_t K, int64_t D, float sqrt_d, float temperature, float* pooled,
+                              int16_t* arg, void* stream);
+
 /* z [rows, K] -> w [rows, K] (simplex projection of each row), tau[rows], nnz[rows];
  * w_bf16 (optional, may be NULL) receives a bf16 copy of w for the pooling GEMM. */
 int32_t ilfdt_sparsemax_fwd(const float* z, int64_t rows, int64_t K, float* w, void* w_bf16,
@@ -107,10 +125,12 @@ int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs,
  * dsd[k,:] += coef*q[b,arg[b,k],:]   (dsd [K,D] f32, ACCUMULATED into).
  * Only support entries (w>0) are touched: cost scales with nnz, not with n_tok*K.
  * w == NULL: g already holds dLoss/dpooled (softmax / sigmoid attention): no support, no mean to
- * subtract, every non-zero entry is scattered. */
+ * subtract, every non-zero entry is scattered.
+ * q_row_base: NULL when q is the full [b,n_tok,D] operand; else row_base[b] of ilfdt_text_compact's plan
+ * (q is then the compacted text operand: token t of sample s lives in row q_row_base[s] + t). */
 int32_t ilfdt_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd,
-                         int32_t dtype, const float* mask, int64_t b, int64_t n_tok, int64_t K,
-                         int64_t D, float sqrt_d, float temperature,
+                         int32_t dtype, const float* mask, const int32_t* q_row_base, int64_t b, int64_t n_tok,
+                         int64_t K, int64_t D, float sqrt_d, float temperature,
                          void* dq, int32_t dq_dtype, float* dsd, void* stream);
 
 /* ---- non-default Query_model variants, clip_fdt.py:67-78,140-157 ----------------------------------- */

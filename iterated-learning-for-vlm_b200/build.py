@@ -17,7 +17,8 @@ CSRC = os.path.join(HERE, "csrc")
 OUT_DIR = os.path.join(HERE, "ilfdt")
 OUT = os.path.join(OUT_DIR, "libilfdt.so")
 OBJ_DIR = os.path.join(HERE, "build")
-SOURCES = ["api.cu", "kernels_simt.cu", "sparsemax.cu", "ground_bwd.cu", "gemm_umma.cu", "nce_bwd_umma.cu", "rowops.cu"]
+SOURCES = ["api.cu", "kernels_simt.cu", "sparsemax.cu", "ground_bwd.cu", "gemm_umma.cu", "nce_bwd_umma.cu", "rowops.cu",
+           "text_buckets.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC",
          "--expt-relaxed-constexpr", "-Xptxas", "-v"]
@@ -57,7 +58,7 @@ def build(force=False, verbose=False):
             raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))
         return obj, r.stderr
 
-    with ThreadPoolExecutor(max_workers=min(6, os.cpu_count() or 1)) as ex:
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
         results = list(ex.map(compile_one, SOURCES))
     if verbose:
         for _, log in results:

@@ -206,6 +206,31 @@ int32_t ilfdt_ground_fwd(const void* q, const void* sd, int32_t dtype, const flo
   return launch_ground_fwd_bf16(q, sd, mask, b, n_tok, K, D, sqrt_d, temperature, pooled, arg, ST(stream));
 }
 
+int64_t ilfdt_text_plan_ints(int64_t b) { return text_plan_ints(b); }
+int32_t ilfdt_ground_fwd_text_supported(int64_t n_tok) { return ground_fwd_text_supported(n_tok) ? 1 : 0; }
+
+int32_t ilfdt_text_compact(const void* q, int32_t q_dtype, const float* mask, int64_t b, int64_t n_tok, int64_t D,
+                           void* groups_ws, int32_t* plan, void* q_compact_bf16, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(q_dtype);
+  ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && D >= 1, ILFDT_E_INVALID_ARG, "text_compact: bad shape");
+  ILFDT_REQUIRE(b == 0 || (q && mask && groups_ws && plan && q_compact_bf16), ILFDT_E_INVALID_ARG,
+                "text_compact: null pointer");
+  return launch_text_compact(q, q_dtype, mask, b, n_tok, D, reinterpret_cast<uint8_t*>(groups_ws), plan, q_compact_bf16,
+                             ST(stream));
+}
+
+int32_t ilfdt_ground_fwd_text(const void* q_compact_bf16, const void* sd_bf16, const int32_t* plan, int64_t b,
+                              int64_t n_tok, int64_t K, int64_t D, float sqrt_d, float temperature, float* pooled,
+                              int16_t* arg, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && K >= 1 && D >= 1, ILFDT_E_INVALID_ARG, "ground_fwd_text: bad shape");
+  ILFDT_REQUIRE(b == 0 || (q_compact_bf16 && sd_bf16 && plan && pooled && arg), ILFDT_E_INVALID_ARG,
+                "ground_fwd_text: null pointer");
+  return launch_ground_fwd_text_bf16(q_compact_bf16, sd_bf16, plan, b, n_tok, K, D, sqrt_d, temperature, pooled, arg,
+                                     ST(stream));
+}
+
 int32_t ilfdt_sparsemax_fwd(const float* z, int64_t rows, int64_t K, float* w, void* w_bf16, float* tau,
                             int32_t* nnz, void* stream) {
   ARCH_GUARD();
@@ -242,15 +267,15 @@ int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs, const
 }
 
 int32_t ilfdt_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd, int32_t dtype,
-                         const float* mask, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
-                         float temperature, void* dq, int32_t dq_dtype, float* dsd, void* stream) {
+                         const float* mask, const int32_t* q_row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D,
+                         float sqrt_d, float temperature, void* dq, int32_t dq_dtype, float* dsd, void* stream) {
   ARCH_GUARD();
   DTYPE_GUARD(dtype);
   DTYPE_GUARD(dq_dtype);
   ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && K >= 1 && D >= 1, ILFDT_E_INVALID_ARG, "ground_bwd: bad shape");
   ILFDT_REQUIRE(b == 0 || (g && arg && q && sd && dq && dsd), ILFDT_E_INVALID_ARG, "ground_bwd: null pointer");
-  return launch_ground_bwd(g, w, arg, q, sd, dtype, mask, b, n_tok, K, D, sqrt_d, temperature, dq, dq_dtype, dsd,
-                           ST(stream));
+  return launch_ground_bwd(g, w, arg, q, sd, dtype, mask, q_row_base, b, n_tok, K, D, sqrt_d, temperature, dq, dq_dtype,
+                           dsd, ST(stream));
 }
 
 int32_t ilfdt_att_fwd(const float* z, int64_t rows, int64_t K, int32_t kind, float* w, float* rowsum, void* stream) {

@@ -58,6 +58,9 @@ struct UmmaParams {
   float pool_scale;
   float* pooled;
   int16_t* arg;
+  // EPI_POOLMAX over one bucket of the compacted text operand (text_buckets.cu): extent read from DEVICE memory
+  const int* dyn;          // {samples, first row, first slot, rows per sample} or nullptr
+  const int* sample_map;   // slot -> sample (rows of pooled / arg), or nullptr
   // EPI_LSE
   const float* scale_dev;
   long long label_offset;
@@ -77,7 +80,7 @@ struct UmmaBars {
 template <int NTOK>
 __device__ __forceinline__ void poolmax_static(uint32_t taddr, int s0, int n_samples, int row, bool row_ok,
                                                int m_rows, float pool_scale, float* __restrict__ pooled,
-                                               int16_t* __restrict__ arg) {
+                                               int16_t* __restrict__ arg, const int* __restrict__ sample_map, int slot0) {
   constexpr int SPT = 256 / NTOK, NCOLS = SPT * NTOK, NCH = (NCOLS + 31) / 32;
   float best[SPT];
   int bidx[SPT];
@@ -103,7 +106,8 @@ __device__ __forceinline__ void poolmax_static(uint32_t taddr, int s0, int n_sam
         if (lo == s * NTOK) { best[s] = cm; bidx[s] = ci; }
         else if (cm > best[s]) { best[s] = cm; bidx[s] = ci; }
         if (hi == (s + 1) * NTOK && row_ok && s0 + s < n_samples) {
-          const int64_t o = (int64_t)(s0 + s) * m_rows + row;
+          const int smp = sample_map ? __ldg(sample_map + slot0 + s0 + s) : s0 + s;
+          const int64_t o = (int64_t)smp * m_rows + row;
           pooled[o] = best[s] * pool_scale;
           arg[o] = (int16_t)bidx[s];
         }
@@ -123,7 +127,17 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint8_t* ring = A_RES ? smem + 8 * UM_A_BYTES : smem;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int num_items = p.num_m_tiles * p.nchunk;
+  int num_items = p.num_m_tiles * p.nchunk;
+  // bucket launches: number of B tiles, first B row and the chunking follow the device-side plan
+  int dyn_samples = p.n_samples, dyn_row0 = 0, dyn_slot0 = 0, num_n_tiles = p.num_n_tiles, tiles_per_chunk = p.tiles_per_chunk;
+  if (EPI == EPI_POOLMAX && p.dyn != nullptr) {
+    dyn_samples = __ldg(p.dyn);
+    dyn_row0 = __ldg(p.dyn + 1);
+    dyn_slot0 = __ldg(p.dyn + 2);
+    num_n_tiles = (dyn_samples + p.spt - 1) / p.spt;
+    tiles_per_chunk = (num_n_tiles + p.nchunk - 1) / p.nchunk;
+    num_items = num_n_tiles == 0 ? 0 : p.num_m_tiles * ((num_n_tiles + tiles_per_chunk - 1) / tiles_per_chunk);
+  }
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < 4; ++i) { mbar_init(&bars->full[i], 1); mbar_init(&bars->empty[i], 1); }
@@ -150,7 +164,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const uint32_t tx_bytes = (A_RES ? 0u : (uint32_t)UM_A_BYTES) + (uint32_t)p.block_n * 128u;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
         const int m_tile = item % p.num_m_tiles, chunk = item / p.num_m_tiles;
-        const int n_begin = chunk * p.tiles_per_chunk, n_end = min(p.num_n_tiles, n_begin + p.tiles_per_chunk);
+        const int n_begin = chunk * tiles_per_chunk, n_end = min(num_n_tiles, n_begin + tiles_per_chunk);
         if (A_RES) {
           mbar_wait(&bars->a_empty, (it & 1) ^ 1);
           mbar_expect_tx(&bars->a_full, (uint32_t)p.nkb * UM_A_BYTES);
@@ -166,7 +180,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               tma_load_2d(st, &tmA, &bars->full[stage], kb * UM_BK, m_tile * UM_BM, kEvictNormal);
               st += UM_A_BYTES;
             }
-            tma_load_2d(st, &tmB, &bars->full[stage], kb * UM_BK, n * p.n_step, kEvictNormal);
+            tma_load_2d(st, &tmB, &bars->full[stage], kb * UM_BK, dyn_row0 + n * p.n_step, kEvictNormal);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
         }
@@ -178,7 +192,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0, it = 0;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
         const int chunk = item / p.num_m_tiles;
-        const int n_begin = chunk * p.tiles_per_chunk, n_end = min(p.num_n_tiles, n_begin + p.tiles_per_chunk);
+        const int n_begin = chunk * tiles_per_chunk, n_end = min(num_n_tiles, n_begin + tiles_per_chunk);
         if (A_RES) {
           mbar_wait(&bars->a_full, it & 1);
           fence_after_sync();
@@ -217,7 +231,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     uint32_t tile_seq = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
       const int m_tile = item % p.num_m_tiles, chunk = item / p.num_m_tiles;
-      const int n_begin = chunk * p.tiles_per_chunk, n_end = min(p.num_n_tiles, n_begin + p.tiles_per_chunk);
+      const int n_begin = chunk * tiles_per_chunk, n_end = min(num_n_tiles, n_begin + tiles_per_chunk);
       const int row = m_tile * UM_BM + quad * 32 + lane;  // A row owned by this thread
       const bool row_ok = row < p.m_rows;
       // EPI_LSE state (base-2 domain)
@@ -251,8 +265,8 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
           }
         } else if (EPI == EPI_POOLMAX && NTOK > 0) {
-          poolmax_static<(NTOK > 0 ? NTOK : 1)>(taddr, n * p.spt, p.n_samples, row, row_ok, p.m_rows, p.pool_scale,
-                                                p.pooled, p.arg);
+          poolmax_static<(NTOK > 0 ? NTOK : 1)>(taddr, n * p.spt, dyn_samples, row, row_ok, p.m_rows, p.pool_scale,
+                                                p.pooled, p.arg, p.sample_map, dyn_slot0);
         } else if (EPI == EPI_POOLMAX) {
           // generic token count / explicit mask: columns = tokens of samples [s0, s0 + nsmp), n_tok columns each
           const int s0 = n * p.spt;
@@ -451,6 +465,10 @@ static int32_t launch_umma(const void* A, const void* B, int64_t M, int64_t N, i
   if (rc != ILFDT_OK) return rc;
   if (EPI == EPI_POOLMAX && a_res && p.mask == nullptr) {
     switch (p.n_tok) {
+      case 16: return launch_umma_t<EPI_POOLMAX, true, 16>(tmA, tmB, p, st);
+      case 32: return launch_umma_t<EPI_POOLMAX, true, 32>(tmA, tmB, p, st);
+      case 48: return launch_umma_t<EPI_POOLMAX, true, 48>(tmA, tmB, p, st);
+      case 64: return launch_umma_t<EPI_POOLMAX, true, 64>(tmA, tmB, p, st);
       case 49: return launch_umma_t<EPI_POOLMAX, true, 49>(tmA, tmB, p, st);
       case 77: return launch_umma_t<EPI_POOLMAX, true, 77>(tmA, tmB, p, st);
       case 196: return launch_umma_t<EPI_POOLMAX, true, 196>(tmA, tmB, p, st);
@@ -495,6 +513,49 @@ int32_t launch_ground_fwd_bf16(const void* q, const void* sd, const float* mask,
   p.pooled = pooled;
   p.arg = arg;
   return launch_umma<EPI_POOLMAX>(sd, q, K, b * n_tok, D, p, st);
+}
+
+// Bucketed text grounding: q is the compacted operand of text_buckets.cu, plan its device-side description. One
+// statically unrolled launch per bucket size R = min(16 g, n_tok); each launch reads its bucket's extent on the device.
+bool ground_fwd_text_supported(int64_t n_tok) {
+  for (int64_t g = 1; 16 * (g - 1) < n_tok; ++g) {
+    const int64_t R = std::min<int64_t>(16 * g, n_tok);
+    if (!(R == 16 || R == 32 || R == 48 || R == 64 || R == 49 || R == 77 || R == 196 || R == 256)) return false;
+  }
+  return true;
+}
+
+int32_t launch_ground_fwd_text_bf16(const void* q_compact, const void* sd, const int* plan, int64_t b, int64_t n_tok,
+                                    int64_t K, int64_t D, float sqrt_d, float temperature, float* pooled, int16_t* arg,
+                                    cudaStream_t st) {
+  if (b == 0) return ILFDT_OK;
+  ILFDT_REQUIRE(ground_fwd_text_supported(n_tok), ILFDT_E_UNSUPPORTED_SHAPE,
+                "ground_fwd_text: n_tok=%lld has a bucket size without a static epilogue", (long long)n_tok);
+  ILFDT_REQUIRE(D <= 512 && D % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "ground_fwd_text: D=%lld must be <= 512, %% 8",
+                (long long)D);
+  ILFDT_REQUIRE(b * n_tok < (1ll << 31), ILFDT_E_UNSUPPORTED_SHAPE, "ground_fwd_text: b*n_tok too large");
+  const int ngmax = (int)cdiv(n_tok, 16);
+  for (int g = 1; g <= ngmax; ++g) {
+    const int R = (int)std::min<int64_t>(16 * g, n_tok);
+    UmmaParams p{};
+    p.spt = 256 / R;
+    p.n_step = p.spt * R;
+    p.block_n = (int)round_up(p.n_step, 16);
+    p.mask = nullptr;
+    p.n_tok = R;
+    p.n_samples = (int)b;
+    p.pool_scale = 1.f / (sqrt_d * temperature);
+    p.pooled = pooled;
+    p.arg = arg;
+    p.dyn = plan + 4 * (g - 1);
+    p.sample_map = plan + 4 * 16 + 2 * b;
+    // chunking from the expected bucket size (an even share); the kernel re-derives tiles per chunk on the device
+    const int est_tiles = (int)std::max<int64_t>(1, cdiv(cdiv(b, ngmax), p.spt));
+    plan_items((int)cdiv(K, UM_BM), est_tiles, sm_count(), p.nchunk, p.tiles_per_chunk);
+    int32_t rc = launch_umma<EPI_POOLMAX>(sd, q_compact, K, b * n_tok, D, p, st);
+    if (rc != ILFDT_OK) return rc;
+  }
+  return ILFDT_OK;
 }
 
 int64_t nce_fwd_bf16_ws_bytes(int64_t b, int64_t B) {

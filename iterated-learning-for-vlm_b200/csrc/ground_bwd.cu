@@ -742,8 +742,8 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const float* __restrict__ w, cons
 template <typename T, int NV, int WARPS, int CPW, int U>
 __global__ void __launch_bounds__(WARPS * 32)
 ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restrict__ arg, const T* __restrict__ q,
-                         int64_t b_total, int n_tok, int K, int D, int64_t b_per_split, int use_atomic,
-                         float* __restrict__ dsd) {
+                         const int* __restrict__ row_base, int64_t b_total, int n_tok, int K, int D,
+                         int64_t b_per_split, int use_atomic, float* __restrict__ dsd) {
   constexpr int CODES = WARPS * CPW, THREADS = WARPS * 32, QUADS = CODES / 4, SLOTS = 32 * QUADS;
   constexpr int LPT = (SLOTS + THREADS - 1) / THREADS;   // (sample, 4-code quad) slots per thread per tile
   __shared__ float cf_s[2][CODES][33];
@@ -801,12 +801,13 @@ ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restri
     const int buf = blk & 1;
     if (blk + 1 < nblk) load_tile(blk + 1);
     const int64_t b0 = b_begin + (int64_t)blk * 32;
+    // first q row of this lane's sample: sample * n_tok, or its slab in the compacted text operand (text_buckets.cu)
+    const int64_t mybase = row_base ? (b0 + lane < b_end ? (int64_t)__ldg(row_base + b0 + lane) : 0) : (b0 + lane) * n_tok;
 #pragma unroll
     for (int c = 0; c < CPW; ++c) {
       const float cf = cf_s[buf][warp * CPW + c][lane];
       const int t = tk_s[buf][warp * CPW + c][lane];
-      // row index of this lane's entry: (sample * n_tok + token)
-      const int64_t myrow = (b0 + lane) * n_tok + t;
+      const int64_t myrow = mybase + t;
       unsigned m = __ballot_sync(0xffffffffu, cf != 0.f);
       while (m) {
         const int n = min(__popc(m), U);
@@ -866,8 +867,8 @@ ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restri
 }
 
 template <typename T, int NV, int WARPS, int CPW, int U>
-static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, int64_t b, int64_t n_tok, int64_t K,
-                             int64_t D, float* dsd, cudaStream_t st) {
+static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, const int* row_base, int64_t b, int64_t n_tok,
+                             int64_t K, int64_t D, float* dsd, cudaStream_t st) {
   constexpr int CODES = WARPS * CPW;
   const int64_t groups = K / CODES;
   int64_t nsplit = 1;
@@ -877,8 +878,8 @@ static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, int
   int64_t per = round_up(cdiv(b, nsplit), 32);
   nsplit = cdiv(b, per);
   dim3 grid((unsigned)groups, (unsigned)nsplit);
-  ground_bwd_dsd_v3_kernel<T, NV, WARPS, CPW, U><<<grid, WARPS * 32, 0, st>>>(g, arg, q, b, (int)n_tok, (int)K, (int)D,
-                                                                             per, nsplit > 1 ? 1 : 0, dsd);
+  ground_bwd_dsd_v3_kernel<T, NV, WARPS, CPW, U><<<grid, WARPS * 32, 0, st>>>(g, arg, q, row_base, b, (int)n_tok, (int)K,
+                                                                             (int)D, per, nsplit > 1 ? 1 : 0, dsd);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }
@@ -899,7 +900,7 @@ static int32_t launch_dq_v3(float* g, const float* w, const int16_t* arg, const 
 
 template <typename T, int NV>
 static int32_t launch_ground_bwd_t(float* g, const float* w, const int16_t* arg, const T* q, const T* sd,
-                                   const float* mask, int64_t b, int64_t n_tok, int64_t K, int64_t D,
+                                   const float* mask, const int* row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D,
                                    float inv_scale, void* dq_v, int dq_dtype, float* dsd, cudaStream_t st) {
   bool done = false;
   float* dq = reinterpret_cast<float*>(dq_v);
@@ -949,18 +950,20 @@ static int32_t launch_ground_bwd_t(float* g, const float* w, const int16_t* arg,
     if (K % 32 == 0 && ((reinterpret_cast<uintptr_t>(g) & 15) | (reinterpret_cast<uintptr_t>(arg) & 7)) == 0) {
       if constexpr (NV <= 2) {
         switch (cfg) {
-          case 1: return launch_dsd_v3<T, NV, 4, 4, 2>(g, arg, q, b, n_tok, K, D, dsd, st);
-          case 2: return launch_dsd_v3<T, NV, 4, 4, 4>(g, arg, q, b, n_tok, K, D, dsd, st);
-          case 5: return launch_dsd_v3<T, NV, 8, 1, 4>(g, arg, q, b, n_tok, K, D, dsd, st);
-          case 7: return launch_dsd_v3<T, NV, 4, 2, 4>(g, arg, q, b, n_tok, K, D, dsd, st);
-          case 14: return launch_dsd_v3<T, NV, 8, 1, 2>(g, arg, q, b, n_tok, K, D, dsd, st);
-          default: return launch_dsd_v3<T, NV, 4, 1, 4>(g, arg, q, b, n_tok, K, D, dsd, st);
+          case 1: return launch_dsd_v3<T, NV, 4, 4, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
+          case 2: return launch_dsd_v3<T, NV, 4, 4, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
+          case 5: return launch_dsd_v3<T, NV, 8, 1, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
+          case 7: return launch_dsd_v3<T, NV, 4, 2, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
+          case 14: return launch_dsd_v3<T, NV, 8, 1, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
+          default: return launch_dsd_v3<T, NV, 4, 1, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
         }
       } else {
-        return launch_dsd_v3<T, NV, 4, 1, 2>(g, arg, q, b, n_tok, K, D, dsd, st);
+        return launch_dsd_v3<T, NV, 4, 1, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
       }
     }
   }
+  ILFDT_REQUIRE(row_base == nullptr, ILFDT_E_UNSUPPORTED_SHAPE,
+                "ground_bwd: a compacted q needs D in {256,...,1024}, K %% 32 == 0 and aligned pointers");
   // split the sample range when there are too few code groups to fill the machine
   const int64_t groups = cdiv(K, GS_WARPS);
   int64_t nsplit = 1;
@@ -978,20 +981,20 @@ static int32_t launch_ground_bwd_t(float* g, const float* w, const int16_t* arg,
 
 template <typename T>
 static int32_t dispatch_nv(float* g, const float* w, const int16_t* arg, const T* q, const T* sd, const float* mask,
-                           int64_t b, int64_t n_tok, int64_t K, int64_t D, float inv_scale, void* dq, int dq_dtype,
+                           const int* row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D, float inv_scale, void* dq, int dq_dtype,
                            float* dsd, cudaStream_t st) {
   const bool aligned = ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(sd) |
                          reinterpret_cast<uintptr_t>(dq) | reinterpret_cast<uintptr_t>(dsd)) & 31) == 0;
-  if (aligned && D == 512) return launch_ground_bwd_t<T, 2>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
-  if (aligned && D == 256) return launch_ground_bwd_t<T, 1>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
-  if (aligned && D == 768) return launch_ground_bwd_t<T, 3>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
-  if (aligned && D == 1024) return launch_ground_bwd_t<T, 4>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 512) return launch_ground_bwd_t<T, 2>(g, w, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 256) return launch_ground_bwd_t<T, 1>(g, w, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 768) return launch_ground_bwd_t<T, 3>(g, w, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 1024) return launch_ground_bwd_t<T, 4>(g, w, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
   ILFDT_REQUIRE(D <= 1024, ILFDT_E_UNSUPPORTED_SHAPE, "ground_bwd: D=%lld > 1024", (long long)D);
-  return launch_ground_bwd_t<T, 0>(g, w, arg, q, sd, mask, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  return launch_ground_bwd_t<T, 0>(g, w, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
 }
 
 int32_t launch_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd, int dtype,
-                          const float* mask, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
+                          const float* mask, const int* row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
                           float temperature, void* dq, int dq_dtype, float* dsd, cudaStream_t st) {
   if (b == 0) return ILFDT_OK;
   ILFDT_REQUIRE(b < (1ll << 31) && K < (1ll << 31) && n_tok <= 32767, ILFDT_E_UNSUPPORTED_SHAPE,
@@ -999,9 +1002,9 @@ int32_t launch_ground_bwd(float* g, const float* w, const int16_t* arg, const vo
   const float inv_scale = 1.f / (sqrt_d * temperature);
   if (dtype == ILFDT_F32)
     return dispatch_nv<float>(g, w, arg, reinterpret_cast<const float*>(q), reinterpret_cast<const float*>(sd), mask,
-                              b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+                              row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
   return dispatch_nv<__nv_bfloat16>(g, w, arg, reinterpret_cast<const __nv_bfloat16*>(q),
-                                    reinterpret_cast<const __nv_bfloat16*>(sd), mask, b, n_tok, K, D, inv_scale, dq,
+                                    reinterpret_cast<const __nv_bfloat16*>(sd), mask, row_base, b, n_tok, K, D, inv_scale, dq,
                                     dq_dtype, dsd, st);
 }
 

@@ -42,8 +42,8 @@ int32_t launch_sparsemax_bwd(const float* w, const float* g, int64_t rows, int64
 
 // ground_bwd.cu
 int32_t launch_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd, int dtype,
-                          const float* mask, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
-                          float temperature, void* dq, int dq_dtype, float* dsd, cudaStream_t st);
+                          const float* mask, const int* row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D,
+                          float sqrt_d, float temperature, void* dq, int dq_dtype, float* dsd, cudaStream_t st);
 
 // gemm_umma.cu (tcgen05)
 int32_t launch_gemm_nt_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha,
@@ -52,6 +52,14 @@ int32_t launch_ground_fwd_bf16(const void* q, const void* sd, const float* mask,
                                int64_t D, float sqrt_d, float temperature, float* pooled, int16_t* arg,
                                cudaStream_t st);
 int64_t nce_fwd_bf16_ws_bytes(int64_t b, int64_t B);
+bool ground_fwd_text_supported(int64_t n_tok);
+int32_t launch_ground_fwd_text_bf16(const void* q_compact, const void* sd, const int* plan, int64_t b, int64_t n_tok,
+                                    int64_t K, int64_t D, float sqrt_d, float temperature, float* pooled, int16_t* arg,
+                                    cudaStream_t st);
+// text_buckets.cu
+int64_t text_plan_ints(int64_t b);
+int32_t launch_text_compact(const void* q, int q_dtype, const float* mask, int64_t b, int64_t n_tok, int64_t D,
+                            uint8_t* groups_ws, int* plan, void* q_out, cudaStream_t st);
 int32_t launch_nce_fwd_bf16(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt, int64_t b,
                             int64_t B, int64_t D, const float* scale, int64_t label_offset, float* lse_i, float* lse_t,
                             float* diag_i, float* diag_t, void* ws, int64_t ws_bytes, cudaStream_t st);

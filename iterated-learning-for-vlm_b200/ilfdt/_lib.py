@@ -29,11 +29,15 @@ SIGNATURES = {
     "ilfdt_transpose_bf16": (_i32, [_p, _i32, _i64, _i64, _p, _p]),
     "ilfdt_ground_fwd_ws_bytes": (_i64, [_i32, _i64, _i64, _i64, _i64]),
     "ilfdt_ground_fwd": (_i32, [_p, _p, _i32, _p, _i64, _i64, _i64, _i64, _f, _f, _i32, _p, _p, _p, _i64, _p]),
+    "ilfdt_text_plan_ints": (_i64, [_i64]),
+    "ilfdt_ground_fwd_text_supported": (_i32, [_i64]),
+    "ilfdt_text_compact": (_i32, [_p, _i32, _p, _i64, _i64, _i64, _p, _p, _p, _p]),
+    "ilfdt_ground_fwd_text": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _p, _p, _p]),
     "ilfdt_sparsemax_fwd": (_i32, [_p, _i64, _i64, _p, _p, _p, _p, _p]),
     "ilfdt_sparsemax_bwd": (_i32, [_p, _p, _i64, _i64, _p, _p]),
     "ilfdt_gemm_nt": (_i32, [_p, _p, _i32, _i64, _i64, _i64, _f, _i32, _p, _i64, _p]),
     "ilfdt_gemm_f32_strided": (_i32, [_p, _i64, _i64, _p, _i64, _i64, _p, _i64, _i64, _i64, _i64, _i64, _f, _i32, _p]),
-    "ilfdt_ground_bwd": (_i32, [_p, _p, _p, _p, _p, _i32, _p, _i64, _i64, _i64, _i64, _f, _f, _p, _i32, _p, _p]),
+    "ilfdt_ground_bwd": (_i32, [_p, _p, _p, _p, _p, _i32, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _p, _i32, _p, _p]),
     "ilfdt_att_fwd": (_i32, [_p, _i64, _i64, _i32, _p, _p, _p]),
     "ilfdt_att_bwd": (_i32, [_p, _p, _p, _i64, _i64, _i32, _p, _p]),
     "ilfdt_rownorm_fwd": (_i32, [_p, _p, _i64, _i64, _p, _p]),

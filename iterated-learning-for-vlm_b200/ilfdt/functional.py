@@ -39,6 +39,9 @@ class compute_dtype:
         set_compute_dtype(self.prev)
 
 
+# padded text in bf16 mode: contract only the rows that can matter (csrc/text_buckets.cu); 0 = full-width operand
+COMPACT_TEXT = os.environ.get("ILFDT_COMPACT_TEXT", "1") != "0"
+
 # bf16 copies of the codebook are shared by the two Query_models of one step
 _sd_cache = {}
 
@@ -63,18 +66,27 @@ class GroundingFunction(torch.autograd.Function):
         q = q.contiguous()
         sd_c = sd.contiguous()
         ctx.q_dtype = q.dtype
+        ctx.set_materialize_grads(False)   # an unused att_weight output must not become a [b,K] tensor of zeros
         if q.dtype == torch.bfloat16 and mode != "bf16":
             raise RuntimeError("ilfdt: a bf16 q needs compute dtype 'bf16'")
         mask_f = None if mask is None else mask.to(torch.float32).contiguous()
         if mode == "bf16" and not (q.shape[2] % 8 == 0 and q.shape[2] <= 512 and q.shape[1] <= 256
                                    and sd.shape[0] % 8 == 0):
             mode = "fp32"   # shapes outside the tcgen05 kernel's tiling take the fp32 CUDA kernels
+        row_base = None
         if mode == "bf16":
-            # pad rows are zeroed in the bf16 operand: their tensor-core score is exactly the 0 the
-            # reference's mask multiply yields (clip_fdt.py:125-130), so the fused epilogue needs no mask
-            q_k = ops.cast_bf16_rows(q, mask_f)
             sd_k, sd_kt = _sd_bf16(sd_c)
-            pooled, arg = ops.ground_fwd(q_k, sd_k, None, temperature, "max")
+            if mask_f is not None and COMPACT_TEXT and ops.text_supported(q.shape[1]):
+                # padded text: valid rows + ONE pad per sample can change the max over tokens (every pad scores
+                # exactly 0, clip_fdt.py:125-130); the cast writes that compacted, bucketed operand directly
+                q_k, plan = ops.text_compact(q, mask_f)
+                row_base = plan.row_base
+                pooled, arg = ops.ground_fwd_text(q_k, sd_k, plan, q.shape[1], temperature)
+            else:
+                # pad rows are zeroed in the bf16 operand: their tensor-core score is exactly the 0 the
+                # reference's mask multiply yields (clip_fdt.py:125-130), so the fused epilogue needs no mask
+                q_k = ops.cast_bf16_rows(q, mask_f)
+                pooled, arg = ops.ground_fwd(q_k, sd_k, None, temperature, "max")
         else:
             q_k, sd_k, sd_kt = q, sd_c, None
             pooled, arg = ops.ground_fwd(q_k, sd_k, mask_f, temperature, "max")
@@ -85,12 +97,13 @@ class GroundingFunction(torch.autograd.Function):
         else:
             f = ops.gemm_f32(w, sd_c)
         ctx.mode, ctx.temperature = mode, float(temperature)
-        ctx.save_for_backward(q_k, sd_k, mask_f, w, arg, w_b)
+        ctx.n_tok = q.shape[1]
+        ctx.save_for_backward(q_k, sd_k, mask_f, w, arg, w_b, row_base)
         return w, f
 
     @staticmethod
     def backward(ctx, dw, df):
-        q_k, sd_k, mask_f, w, arg, w_b = ctx.saved_tensors
+        q_k, sd_k, mask_f, w, arg, w_b, row_base = ctx.saved_tensors
         mode = ctx.mode
         b, K = w.shape
         D = sd_k.shape[1]
@@ -113,10 +126,10 @@ class GroundingFunction(torch.autograd.Function):
         else:
             g = dw.contiguous().float().clone()
         dq_dtype = torch.float32
-        if ctx.q_dtype == torch.bfloat16 and mode == "bf16" and D in (256, 512, 768, 1024) and q_k.shape[1] <= 96 \
+        if ctx.q_dtype == torch.bfloat16 and mode == "bf16" and D in (256, 512, 768, 1024) and ctx.n_tok <= 96 \
                 and K % 4 == 0:
             dq_dtype = torch.bfloat16      # written directly by the scatter kernel
-        dq = ops.ground_bwd(g, w, arg, q_k, sd_k, mask_f, ctx.temperature, dsd, dq_dtype)
+        dq = ops.ground_bwd(g, w, arg, q_k, sd_k, mask_f, ctx.temperature, dsd, dq_dtype, row_base, ctx.n_tok)
         if dq.dtype != ctx.q_dtype:
             dq = ops.cast_bf16(dq)
         return dq, dsd, None, None, None
@@ -131,6 +144,7 @@ class GroundingVariantFunction(torch.autograd.Function):
     def forward(ctx, q, sd, mask, temperature, att, pool):
         q = q.contiguous().float()
         sd_c = sd.contiguous().float()
+        ctx.set_materialize_grads(False)
         mask_f = None if mask is None else mask.to(torch.float32).contiguous()
         pooled, arg = ops.ground_fwd(q, sd_c, mask_f, temperature, pool)
         rowsum = None

@@ -19,7 +19,7 @@ def _stream():
 LAUNCHES = 0          # kernels launched through this module since it was last zeroed
 PROFILE_ON = False    # when True every C call is bracketed by CUDA events on the launching stream
 PROFILE = {}          # op name -> [(start_event, end_event), ...]
-_KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mask_rows_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_sparsemax_fwd": 1,
+_KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mask_rows_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_ground_fwd_text": 5, "ilfdt_text_compact": 3, "ilfdt_sparsemax_fwd": 1,
                      "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2,
                      "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5,
                      "ilfdt_nce_bwd": 4, "ilfdt_nce_bwd_gathered": 2, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
@@ -124,6 +124,49 @@ def ground_fwd(q, sd, mask, temperature, pool_type="max"):
     return pooled, arg
 
 
+class TextPlan:
+    """Device-side plan of ilfdt_text_compact: buckets, slot_of / row_base / sample_of (all int32 views of one buffer)."""
+
+    def __init__(self, buf, b):
+        self.buf, self.b = buf, b
+        self.buckets = buf[:64].view(16, 4)          # {samples, first row, first slot, rows per sample}
+        self.slot_of = buf[64:64 + b]
+        self.row_base = buf[64 + b:64 + 2 * b]
+        self.sample_of = buf[64 + 2 * b:64 + 3 * b]
+
+
+def text_supported(n_tok):
+    return bool(_lib.load().ilfdt_ground_fwd_text_supported(int(n_tok)))
+
+
+def text_compact(q, mask):
+    """q [b,N,D] f32 or bf16, mask [b,N] f32 (0 valid / non-zero pad) -> (compacted bf16 operand [b*N, D] of which only
+    the planned rows are written, TextPlan). Valid rows + one pad per sample survive, bucketed by 16-row groups."""
+    lib = _lib.load()
+    _req(q, None, "q"); _req(mask, torch.float32, "mask")
+    assert q.dtype in _DT
+    b, n_tok, D = q.shape
+    assert tuple(mask.shape) == (b, n_tok)
+    plan = torch.empty(lib.ilfdt_text_plan_ints(b), dtype=torch.int32, device=q.device)
+    groups = torch.empty(max(b, 1), dtype=torch.uint8, device=q.device)
+    out = torch.empty(b * n_tok, D, dtype=torch.bfloat16, device=q.device)
+    _call("ilfdt_text_compact", _ptr(q), _DT[q.dtype], _ptr(mask), b, n_tok, D, _ptr(groups), _ptr(plan), _ptr(out),
+          _stream())
+    return out, TextPlan(plan, b)
+
+
+def ground_fwd_text(q_compact, sd, plan, n_tok, temperature):
+    """compacted bf16 operand + plan, bf16 sd [K,D] -> pooled [b,K] f32, arg [b,K] int16 (max pooling)."""
+    _req(q_compact, torch.bfloat16, "q_compact"); _req(sd, torch.bfloat16, "sd")
+    b = plan.b
+    K, D = sd.shape
+    pooled = torch.empty(b, K, dtype=torch.float32, device=sd.device)
+    arg = torch.empty(b, K, dtype=torch.int16, device=sd.device)
+    _call("ilfdt_ground_fwd_text", _ptr(q_compact), _ptr(sd), _ptr(plan.buf), b, n_tok, K, D, float(math.sqrt(D)),
+          float(temperature), _ptr(pooled), _ptr(arg), _stream())
+    return pooled, arg
+
+
 def sparsemax_fwd(z, want_bf16=False):
     _req(z, torch.float32, "z")
     rows, K = z.shape
@@ -174,16 +217,21 @@ def gemm_f32(A, B, a_t=False, b_t=False, alpha=1.0, out=None, accumulate=False):
     return out
 
 
-def ground_bwd(g, w, arg, q, sd, mask, temperature, dsd, dq_dtype=torch.float32):
-    """g [b,K] is overwritten with coef. Returns dq [b,N,D] (dq_dtype); accumulates into dsd [K,D] f32."""
+def ground_bwd(g, w, arg, q, sd, mask, temperature, dsd, dq_dtype=torch.float32, row_base=None, n_tok=None):
+    """g [b,K] is overwritten with coef. Returns dq [b,N,D] (dq_dtype); accumulates into dsd [K,D] f32.
+    row_base (int32 [b]) + n_tok: q is the compacted text operand [rows, D] of text_compact."""
     _req(g, torch.float32, "g"); _req(arg, torch.int16, "arg")
     if w is not None:   # None: g already is dLoss/dpooled (softmax / sigmoid attention)
         _req(w, torch.float32, "w")
     _req(q, None, "q"); _req(sd, q.dtype, "sd"); _req(dsd, torch.float32, "dsd")
-    b, n_tok, D = q.shape
+    if row_base is None:
+        b, n_tok, D = q.shape
+    else:
+        _req(row_base, torch.int32, "row_base")
+        b, D = g.shape[0], q.shape[-1]
     K = sd.shape[0]
     dq = torch.empty(b, n_tok, D, dtype=dq_dtype, device=q.device)
-    _call("ilfdt_ground_bwd", _ptr(g), _ptr(w), _ptr(arg), _ptr(q), _ptr(sd), _DT[q.dtype], _ptr(mask), b,
+    _call("ilfdt_ground_bwd", _ptr(g), _ptr(w), _ptr(arg), _ptr(q), _ptr(sd), _DT[q.dtype], _ptr(mask), _ptr(row_base), b,
           n_tok, K, D, float(math.sqrt(D)), float(temperature), _ptr(dq), _DT[dq_dtype], _ptr(dsd), _stream())
     return dq
 

@@ -264,6 +264,49 @@ def test_grounding_bf16_q_input(ops, b, n_tok, K, D, masked):
         assert q16.grad.float()[pad].abs().max().item() == 0.0
 
 
+@pytest.mark.parametrize("b,n_tok,K,D", [(37, 77, 384, 512), (300, 77, 1024, 512), (64, 49, 256, 256), (9, 64, 512, 64),
+                                        (1500, 77, 256, 512)])
+@pytest.mark.parametrize("qdtype", ["f32", "bf16"])
+def test_ground_fwd_text_buckets_equal_full_width(ops, b, n_tok, K, D, qdtype):
+    """ilfdt_text_compact + ilfdt_ground_fwd_text (valid rows + one pad per sample, bucketed by 16-row groups) must
+    reproduce the full-width tensor-core kernel bit for bit -- pooled AND argmax: every pad scores exactly 0
+    (clip_fdt.py:125-130). Also checks the device-side plan (a permutation, slabs disjoint and in range)."""
+    g = torch.Generator().manual_seed(b + n_tok)
+    q = torch.randn(b, n_tok, D, generator=g)
+    sd = torch.randn(K, D, generator=g)
+    lens = torch.randint(1, n_tok + 1, (b,), generator=g)
+    lens[0] = n_tok            # no pad at all
+    lens[1 % b] = 1
+    lens[2 % b] = 16
+    lens[3 % b] = 15
+    mask = _mask(b, n_tok, lens.tolist())
+    mask[4 % b, :] = float("-inf")          # a sample with no valid token
+    mask[5 % b, 3] = float("-inf")          # an interior pad
+    dev = _dev()
+    assert ops.text_supported(n_tok)
+    qd = q.to(dev) if qdtype == "f32" else q.to(dev).to(torch.bfloat16)
+    q_full = ops.cast_bf16_rows(qd, mask.to(dev))
+    sd_k = ops.cast_bf16(sd.to(dev))
+    pooled_f, arg_f = ops.ground_fwd(q_full, sd_k, None, 30.0, "max")
+    q_c, plan = ops.text_compact(qd, mask.to(dev))
+    pooled_t, arg_t = ops.ground_fwd_text(q_c, sd_k, plan, n_tok, 30.0)
+    assert torch.equal(pooled_f, pooled_t)
+    assert torch.equal(arg_f, arg_t)
+    # plan sanity
+    slot_of, row_base, sample_of = plan.slot_of.cpu().long(), plan.row_base.cpu().long(), plan.sample_of.cpu().long()
+    assert sorted(slot_of.tolist()) == list(range(b))
+    assert torch.equal(sample_of[slot_of], torch.arange(b))
+    valid_last = torch.tensor([int((mask[i] == 0).nonzero().max()) + 1 if (mask[i] == 0).any() else 0 for i in range(b)])
+    rows = torch.minimum(((torch.clamp(valid_last + 1, max=n_tok) + 15) // 16) * 16, torch.tensor(n_tok))
+    order = torch.argsort(row_base)
+    ends = (row_base + rows)[order]
+    assert (row_base[order][1:] >= ends[:-1]).all() and ends[-1] <= b * n_tok
+    # the compacted rows are the full-width operand's rows
+    for s_ in (0, 1 % b, 2 % b, 4 % b, 5 % b, b - 1):
+        r0, n = int(row_base[s_]), int(rows[s_])
+        assert torch.equal(q_c[r0:r0 + n], q_full[s_, :n])
+
+
 QM_VARIANTS = [("smax", "sparsemax", "max"), ("smaxT", "sparsemax", "max"), ("softsum", "softmax", "sum"),
                ("sigmean", "sigmoid", "mean"), ("softmax_max", "softmax", "max"), ("smax_mean", "sparsemax", "mean")]
 
