@@ -253,15 +253,30 @@ def run_ours(args):
     roof = None
     prof = ops.profile_summary()
     if "ground_fwd" in prof:
+        # dominant kernel: umma_kernel<EPI_POOLMAX, 49> = the image launch of ilfdt_ground_fwd (one per step).
+        # ALGORITHMIC FLOPs per launch = 2 * b * P * D * K.
         n_launch, tot_ms = prof["ground_fwd"]
-        flops_per_step = 2.0 * b * (P_TOK + T_TOK) * D_DIM * K          # both launches (image + text) of one step
-        avg_pair_ms = tot_ms / (n_launch / 2.0)
-        achieved = flops_per_step / (avg_pair_ms * 1e-3) / 1e12
-        roof = {"bound": "tensor", "kernel": "umma_kernel<EPI_POOLMAX> (ilfdt_ground_fwd, image+text launches)",
+        flops_per_launch = 2.0 * b * P_TOK * D_DIM * K
+        avg_ms = tot_ms / n_launch
+        achieved = flops_per_launch / (avg_ms * 1e-3) / 1e12
+        roof = {"bound": "tensor", "kernel": "umma_kernel<EPI_POOLMAX,49> (ilfdt_ground_fwd, image launch)",
                 "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
-                "traffic": None, "peak_source": pk["src"], "avg_launch_ms": tot_ms / n_launch,
+                # dram__bytes_read.sum + dram__bytes_write.sum of this launch from the committed ncu --set full capture
+                # (profiles/r01_ncu_ground_v2_b32768.txt: 3.05 GB + 3.19 GB); only valid for that shape
+                "traffic": 6.235e9 if (b == 32768 and K == 16384) else None, "traffic_unit": "bytes per launch (ncu)",
+                "peak_source": pk["src"], "avg_launch_ms": avg_ms,
                 "share_of_step": (tot_ms / args.steps) / ms_per_step,
-                "algorithmic_flops_per_launch_pair": flops_per_step}
+                "algorithmic_flops_per_launch": flops_per_launch}
+        if "ground_fwd_text" in prof:
+            # text launches (one per 16-row bucket): algorithmic = full-width 2*b*T*D*K; executed = rows kept by the
+            # pad compaction (valid tokens + one pad, rounded to 16)
+            n_t, tot_t = prof["ground_fwd_text"]
+            rows_kept = torch.clamp(((torch.clamp(lens + 1, max=T_TOK) + 15) // 16) * 16, max=T_TOK).sum().item()
+            ms_t = tot_t / n_t
+            roof["text"] = {"kernel": "umma_kernel<EPI_POOLMAX,R> x 5 buckets (ilfdt_ground_fwd_text)", "avg_ms": ms_t,
+                            "algorithmic_tflops": 2.0 * b * T_TOK * D_DIM * K / (ms_t * 1e-3) / 1e12,
+                            "executed_tflops": 2.0 * rows_kept * D_DIM * K / (ms_t * 1e-3) / 1e12,
+                            "rows_kept_frac": rows_kept / float(b * T_TOK)}
     kernel_ms = {k: v[1] / args.steps for k, v in prof.items()}
 
     # ---- end to end through the public call with HOST buffers ----

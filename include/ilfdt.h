@@ -110,6 +110,11 @@ int32_t ilfdt_sparsemax_bwd(const float* w, const float* g, int64_t rows, int64_
  * BF16: tcgen05 kernel (M % 128 == 0, Kr % 64 == 0 required); F32: SIMT kernel, any shape. */
 int32_t ilfdt_gemm_nt(const void* A, const void* B, int32_t dtype, int64_t M, int64_t N, int64_t Kr,
                       float alpha, int32_t accumulate, float* out, int64_t ldo, void* stream);
+/* out[N, M] (+)= alpha * B[Kr,N]^T . A[Kr,M] for bf16 operands stored with the REDUCTION index outermost (tcgen05
+ * MN-major operands: no transposed copies). dsd[K,D] += w[b,K]^T . df[b,D] of the pooling backward
+ * (clip_fdt.py:154): A = df, B = w, M = D, N = K, Kr = b. M, N multiples of 8. */
+int32_t ilfdt_gemm_tn(const void* A_bf16, const void* B_bf16, int64_t M, int64_t N, int64_t Kr, float alpha,
+                      int32_t accumulate, float* out, int64_t ldo, void* stream);
 /* fp32 only, arbitrary strides: C(m,n) (+)= alpha * sum_k A(m,k) B(n,k), X(i,j) = X[i*rs + j*cs] */
 int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs,
                                const float* B, int64_t b_rs, int64_t b_cs,

@@ -257,6 +257,14 @@ int32_t ilfdt_gemm_nt(const void* A, const void* B, int32_t dtype, int64_t M, in
   return launch_gemm_nt_bf16(A, B, M, N, Kr, alpha, nullptr, accumulate, out, ldo, ST(stream));
 }
 
+int32_t ilfdt_gemm_tn(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha, int32_t accumulate,
+                      float* out, int64_t ldo, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(M >= 0 && N >= 0 && Kr >= 1 && ldo >= M, ILFDT_E_INVALID_ARG, "gemm_tn: bad shape");
+  ILFDT_REQUIRE((M == 0 || N == 0) || (A && B && out), ILFDT_E_INVALID_ARG, "gemm_tn: null pointer");
+  return launch_gemm_tn_bf16(A, B, M, N, Kr, alpha, accumulate, out, ldo, ST(stream));
+}
+
 int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs, const float* B, int64_t b_rs, int64_t b_cs,
                                float* C, int64_t c_rs, int64_t c_cs, int64_t M, int64_t N, int64_t Kr, float alpha,
                                int32_t accumulate, void* stream) {

@@ -47,6 +47,7 @@ struct UmmaParams {
   int m_rows, n_rows;
   uint32_t idesc;
   // EPI_STORE_T
+  int mn_major;   // 1: A is stored [Kr, M], B is stored [Kr, N] (the M / N index contiguous): both read as MN-major operands
   float* out;
   int64_t ldo;
   float alpha;
@@ -176,6 +177,16 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             mbar_wait(&bars->empty[stage], phase ^ 1);
             mbar_expect_tx(&bars->full[stage], tx_bytes);
             uint8_t* st = ring + stage * STAGE_BYTES;
+            if (EPI == EPI_STORE_T && !A_RES && p.mn_major) {
+              // boxes of [64 reduction rows x 64 M- or N-columns]: 2 for the 128-wide A tile, block_n / 64 for B
+              for (int j = 0; j < 2; ++j)
+                tma_load_2d(st + j * 8192, &tmA, &bars->full[stage], m_tile * UM_BM + j * 64, kb * UM_BK, kEvictNormal);
+              st += UM_A_BYTES;
+              for (int j = 0; j < p.block_n / 64; ++j)
+                tma_load_2d(st + j * 8192, &tmB, &bars->full[stage], n * p.n_step + j * 64, kb * UM_BK, kEvictNormal);
+              if (++stage == STAGES) { stage = 0; phase ^= 1; }
+              continue;
+            }
             if (!A_RES) {
               tma_load_2d(st, &tmA, &bars->full[stage], kb * UM_BK, m_tile * UM_BM, kEvictNormal);
               st += UM_A_BYTES;
@@ -205,12 +216,22 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             mbar_wait(&bars->full[stage], phase);
             fence_after_sync();
             uint8_t* st = ring + stage * STAGE_BYTES;
+            if (EPI == EPI_STORE_T && !A_RES && p.mn_major) {
+              // MN-major operands: 64-column blocks 8 KB apart (leading offset), a 16-row K step = 2 KB
+              const uint64_t adesc = make_smem_desc_sw128_mn(smem_u32(st), 8192);
+              const uint64_t bdesc = make_smem_desc_sw128_mn(smem_u32(st + UM_A_BYTES), 8192);
+#pragma unroll
+              for (int k4 = 0; k4 < UM_BK / 16; ++k4)
+                mma_f16(tmem_d, advance_desc_k(adesc, k4 * 2048), advance_desc_k(bdesc, k4 * 2048), p.idesc,
+                        (kb | k4) != 0 ? 1u : 0u);
+            } else {
             const uint64_t adesc = make_smem_desc_sw128(smem_u32(A_RES ? smem + kb * UM_A_BYTES : st));
             const uint64_t bdesc = make_smem_desc_sw128(smem_u32(A_RES ? st : st + UM_A_BYTES));
 #pragma unroll
             for (int k4 = 0; k4 < UM_BK / 16; ++k4)
               mma_f16(tmem_d, advance_desc_k(adesc, k4 * 32), advance_desc_k(bdesc, k4 * 32), p.idesc,
                       (kb | k4) != 0 ? 1u : 0u);
+            }
             mma_commit(&bars->empty[stage]);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
@@ -491,6 +512,39 @@ int32_t launch_gemm_nt_bf16(const void* A, const void* B, int64_t M, int64_t N, 
   p.alpha_dev = alpha_dev;
   p.accumulate = accumulate;
   return launch_umma<EPI_STORE_T>(A, B, M, N, Kr, p, st);
+}
+
+// out[n, m] (+)= alpha * sum_k A[k, m] * B[k, n]: A [Kr, M], B [Kr, N] bf16 with the REDUCTION index outermost (e.g.
+// dsd[K,D] += w[b,K]^T . df[b,D] straight from the row-major w and df: no transposed copies). tcgen05 reads both as
+// MN-major operands.
+int32_t launch_gemm_tn_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha, int accumulate,
+                            float* out, int64_t ldo, cudaStream_t st) {
+  if (M == 0 || N == 0) return ILFDT_OK;
+  ILFDT_REQUIRE(M % 8 == 0 && N % 8 == 0 && Kr >= 1, ILFDT_E_UNSUPPORTED_SHAPE,
+                "gemm_tn(bf16): M, N must be multiples of 8 (TMA row pitch)");
+  ILFDT_REQUIRE(M < (1ll << 31) && N < (1ll << 31) && Kr < (1ll << 31), ILFDT_E_UNSUPPORTED_SHAPE, "dimension too large");
+  UmmaParams p{};
+  p.block_n = (int)std::min<int64_t>(256, round_up(N, 64));
+  p.n_step = p.block_n;
+  p.out = out;
+  p.ldo = ldo;
+  p.alpha = alpha;
+  p.accumulate = accumulate;
+  p.mn_major = 1;
+  p.m_rows = (int)M;
+  p.n_rows = (int)N;
+  p.nkb = (int)cdiv(Kr, UM_BK);
+  p.num_m_tiles = (int)cdiv(M, UM_BM);
+  p.num_n_tiles = (int)cdiv(N, p.n_step);
+  p.idesc = make_idesc_bf16(UM_BM, p.block_n, 1, 1);
+  p.nchunk = p.num_n_tiles;
+  p.tiles_per_chunk = 1;
+  CUtensorMap tmA, tmB;
+  int32_t rc = make_tmap_bf16(&tmA, A, Kr, M, M, 64);   // rows = reduction index, inner = M; box 64 x 64
+  if (rc != ILFDT_OK) return rc;
+  rc = make_tmap_bf16(&tmB, B, Kr, N, N, 64);
+  if (rc != ILFDT_OK) return rc;
+  return launch_umma_t<EPI_STORE_T, false>(tmA, tmB, p, st);
 }
 
 int32_t launch_ground_fwd_bf16(const void* q, const void* sd, const float* mask, int64_t b, int64_t n_tok, int64_t K,

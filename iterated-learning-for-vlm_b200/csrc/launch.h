@@ -48,6 +48,8 @@ int32_t launch_ground_bwd(float* g, const float* w, const int16_t* arg, const vo
 // gemm_umma.cu (tcgen05)
 int32_t launch_gemm_nt_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha,
                             const float* alpha_dev, int accumulate, float* out, int64_t ldo, cudaStream_t st);
+int32_t launch_gemm_tn_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha, int accumulate,
+                            float* out, int64_t ldo, cudaStream_t st);
 int32_t launch_ground_fwd_bf16(const void* q, const void* sd, const float* mask, int64_t b, int64_t n_tok, int64_t K,
                                int64_t D, float sqrt_d, float temperature, float* pooled, int16_t* arg,
                                cudaStream_t st);

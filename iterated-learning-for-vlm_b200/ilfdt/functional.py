@@ -113,11 +113,8 @@ class GroundingFunction(torch.autograd.Function):
             if mode == "bf16":
                 df_b = ops.cast_bf16(df)
                 g = ops.gemm_nt(sd_k, df_b)                  # g[b,K] = df . sd^T
-                # dsd[K,D] += w^T . df : both operands need the sample index contiguous
-                if b % 8 == 0:
-                    ops.gemm_nt(ops.transpose_bf16(df_b), ops.transpose_bf16(w_b), out=dsd, accumulate=True)
-                else:  # TMA needs a 16-byte row pitch on the [*, b] transposes: ragged batch -> fp32 SIMT kernel
-                    ops.gemm_f32(w, df, a_t=True, out=dsd, accumulate=True)
+                # dsd[K,D] += w^T . df straight from the row-major w [b,K] and df [b,D] (MN-major tensor-core operands)
+                ops.gemm_tn(df_b, w_b, out=dsd, accumulate=True)
             else:
                 g = ops.gemm_f32(df, sd_k, b_t=True)
                 ops.gemm_f32(w, df, a_t=True, out=dsd, accumulate=True)

@@ -200,6 +200,20 @@ def gemm_nt(A, B, alpha=1.0, out=None, accumulate=False):
     return out
 
 
+def gemm_tn(A, B, alpha=1.0, out=None, accumulate=False):
+    """out[N, M] (+)= alpha * B[Kr,N]^T . A[Kr,M]   (bf16 operands with the reduction index outermost)."""
+    _req(A, torch.bfloat16, "A"); _req(B, torch.bfloat16, "B")
+    Kr, M = A.shape
+    N = B.shape[1]
+    assert B.shape[0] == Kr
+    if out is None:
+        assert not accumulate
+        out = torch.empty(N, M, dtype=torch.float32, device=A.device)
+    _req(out, torch.float32, "out")
+    _call("ilfdt_gemm_tn", _ptr(A), _ptr(B), M, N, Kr, float(alpha), int(accumulate), _ptr(out), out.shape[1], _stream())
+    return out
+
+
 def gemm_f32(A, B, a_t=False, b_t=False, alpha=1.0, out=None, accumulate=False):
     """fp32 C = alpha * op(A) @ op(B) for 2-D row-major tensors (op = transpose if *_t)."""
     _req(A, torch.float32, "A"); _req(B, torch.float32, "B")

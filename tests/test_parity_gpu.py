@@ -79,6 +79,19 @@ def test_gemm_nt_tcgen05(ops, M, N, K):
     assert_close(out2, 3.0 * ref, 2e-5, "gemm_nt bf16 accumulate")
 
 
+@pytest.mark.parametrize("M,N,K", [(512, 256, 64), (512, 16384, 300), (64, 200, 1000), (256, 384, 37), (8, 8, 5)])
+def test_gemm_tn_tcgen05(ops, M, N, K):
+    """MN-major tensor-core operands: out[N,M] = B[K,N]^T . A[K,M] from row-major A, B (reduction index outermost)."""
+    g = torch.Generator().manual_seed(3 * M + N + K)
+    A = bf16_round(torch.randn(K, M, generator=g))
+    B = bf16_round(torch.randn(K, N, generator=g))
+    ref = B.double().t() @ A.double()
+    out = ops.gemm_tn(A.to(_dev()).to(torch.bfloat16), B.to(_dev()).to(torch.bfloat16), alpha=0.5)
+    assert_close(out, 0.5 * ref, 2e-5, "gemm_tn bf16")
+    out2 = ops.gemm_tn(A.to(_dev()).to(torch.bfloat16), B.to(_dev()).to(torch.bfloat16), out=out.clone(), accumulate=True)
+    assert_close(out2, 1.5 * ref, 2e-5, "gemm_tn bf16 accumulate")
+
+
 # ---------------------------------------------------------------------------------------------------
 # a1: score block forward
 # ---------------------------------------------------------------------------------------------------
