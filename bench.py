@@ -55,8 +55,8 @@ def peaks():
     if os.path.exists(path):
         d = json.load(open(path))
         return dict(tflops=float(d.get("bf16_tflops_sustained", d.get("bf16_tflops"))), hbm=float(d["hbm_gbs"]),
-                    src="measured (MEASURED_PEAKS.json, sustained bf16)")
-    return dict(tflops=1590.0, hbm=6650.0, src="fallback (B200_PROFILING.md)")
+                    burst=float(d.get("bf16_tflops", 0.0)) or None, src="measured (MEASURED_PEAKS.json, sustained bf16)")
+    return dict(tflops=1590.0, hbm=6650.0, burst=1590.0, src="fallback (B200_PROFILING.md)")
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -259,13 +259,14 @@ def run_ours(args):
         flops_per_launch = 2.0 * b * P_TOK * D_DIM * K
         avg_ms = tot_ms / n_launch
         achieved = flops_per_launch / (avg_ms * 1e-3) / 1e12
-        roof = {"bound": "tensor", "kernel": "umma_kernel<EPI_POOLMAX,49> (ilfdt_ground_fwd, image launch)",
+        roof = {"bound": "tensor", "kernel": "ground2_kernel<49> (tcgen05 cta_group::2; ilfdt_ground_fwd, image launch)",
                 "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
                 # dram__bytes_read.sum + dram__bytes_write.sum of this launch from the committed ncu --set full capture
                 # (profiles/r01_ncu_ground_v2_b32768.txt: 3.05 GB + 3.19 GB); only valid for that shape
                 "traffic": 6.235e9 if (b == 32768 and K == 16384) else None, "traffic_unit": "bytes per launch (ncu)",
                 "peak_source": pk["src"], "avg_launch_ms": avg_ms,
                 "share_of_step": (tot_ms / args.steps) / ms_per_step,
+                "frac_of_burst_peak": (achieved / pk["burst"]) if pk.get("burst") else None,
                 "algorithmic_flops_per_launch": flops_per_launch}
         if "ground_fwd_text" in prof:
             # text launches (one per 16-row bucket): algorithmic = full-width 2*b*T*D*K; executed = rows kept by the
@@ -273,7 +274,7 @@ def run_ours(args):
             n_t, tot_t = prof["ground_fwd_text"]
             rows_kept = torch.clamp(((torch.clamp(lens + 1, max=T_TOK) + 15) // 16) * 16, max=T_TOK).sum().item()
             ms_t = tot_t / n_t
-            roof["text"] = {"kernel": "umma_kernel<EPI_POOLMAX,R> x 5 buckets (ilfdt_ground_fwd_text)", "avg_ms": ms_t,
+            roof["text"] = {"kernel": "ground2_kernel<R> x 5 buckets (ilfdt_ground_fwd_text)", "avg_ms": ms_t,
                             "algorithmic_tflops": 2.0 * b * T_TOK * D_DIM * K / (ms_t * 1e-3) / 1e12,
                             "executed_tflops": 2.0 * rows_kept * D_DIM * K / (ms_t * 1e-3) / 1e12,
                             "rows_kept_frac": rows_kept / float(b * T_TOK)}

@@ -19,6 +19,7 @@
 //   warps 2-5 epilogue: tcgen05.ld 32 columns at a time, fused reduction, release the accumulator
 // so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include "umma.cuh"
+#include "poolmax.cuh"
 #include "launch.h"
 #include <algorithm>
 #include <mutex>
@@ -74,48 +75,6 @@ struct UmmaBars {
   uint64_t full[4], empty[4], tmem_full[2], tmem_empty[2], a_full, a_empty;
   uint32_t tmem_ptr;
 };
-
-// Max/argmax over the token columns of each sample with everything static: NTOK tokens per sample,
-// SPT = 256 / NTOK samples per tile. ~3 instructions per accumulator element (FMNMX, FSETP, SEL), no
-// loop-carried chain longer than one sample, TMEM loads double-buffered against the arithmetic.
-template <int NTOK>
-__device__ __forceinline__ void poolmax_static(uint32_t taddr, int s0, int n_samples, int row, bool row_ok,
-                                               int m_rows, float pool_scale, float* __restrict__ pooled,
-                                               int16_t* __restrict__ arg, const int* __restrict__ sample_map, int slot0) {
-  constexpr int SPT = 256 / NTOK, NCOLS = SPT * NTOK, NCH = (NCOLS + 31) / 32;
-  float best[SPT];
-  int bidx[SPT];
-  uint32_t v[2][32];
-  tmem_ld32(taddr, v[0]);
-#pragma unroll
-  for (int c = 0; c < NCH; ++c) {
-    tmem_ld_wait();
-    if (c + 1 < NCH) tmem_ld32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
-#pragma unroll
-    for (int s = 0; s < SPT; ++s) {
-      const int lo = s * NTOK > c * 32 ? s * NTOK : c * 32;
-      const int hi = (s + 1) * NTOK < c * 32 + 32 ? (s + 1) * NTOK : c * 32 + 32;
-      if (lo < hi) {
-        float cm = __uint_as_float(v[c & 1][lo - c * 32]);
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (c * 32 + j > lo && c * 32 + j < hi) cm = fmaxf(cm, __uint_as_float(v[c & 1][j]));
-        int ci = lo - s * NTOK;
-#pragma unroll
-        for (int j = 31; j >= 0; --j)  // descending: the lowest token index among ties wins
-          if (c * 32 + j >= lo && c * 32 + j < hi && __uint_as_float(v[c & 1][j]) == cm) ci = c * 32 + j - s * NTOK;
-        if (lo == s * NTOK) { best[s] = cm; bidx[s] = ci; }
-        else if (cm > best[s]) { best[s] = cm; bidx[s] = ci; }
-        if (hi == (s + 1) * NTOK && row_ok && s0 + s < n_samples) {
-          const int smp = sample_map ? __ldg(sample_map + slot0 + s0 + s) : s0 + s;
-          const int64_t o = (int64_t)smp * m_rows + row;
-          pooled[o] = best[s] * pool_scale;
-          arg[o] = (int16_t)bidx[s];
-        }
-      }
-    }
-  }
-}
 
 template <int EPI, bool A_RES, int NTOK>
 __global__ void __launch_bounds__(UM_THREADS, 1)
@@ -556,6 +515,9 @@ int32_t launch_ground_fwd_bf16(const void* q, const void* sd, const float* mask,
   ILFDT_REQUIRE(D <= 512 && D % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "ground_fwd(bf16): D=%lld must be <= 512, %% 8",
                 (long long)D);
   ILFDT_REQUIRE(b * n_tok < (1ll << 31), ILFDT_E_UNSUPPORTED_SHAPE, "ground_fwd(bf16): b*n_tok too large");
+  if (mask == nullptr && ground2_enabled() && ground2_supported(n_tok, D) && b >= 256 / n_tok)
+    return launch_ground2(q, sd, b * n_tok, b, n_tok, K, D, 1.f / (sqrt_d * temperature), pooled, arg, nullptr, nullptr, b,
+                          st);
   UmmaParams p{};
   p.spt = (int)std::min<int64_t>(256 / n_tok, b);
   p.n_step = p.spt * (int)n_tok;
@@ -591,6 +553,12 @@ int32_t launch_ground_fwd_text_bf16(const void* q_compact, const void* sd, const
   const int ngmax = (int)cdiv(n_tok, 16);
   for (int g = 1; g <= ngmax; ++g) {
     const int R = (int)std::min<int64_t>(16 * g, n_tok);
+    if (ground2_enabled() && ground2_supported(R, D)) {
+      int32_t rc2 = launch_ground2(q_compact, sd, b * n_tok, b, R, K, D, 1.f / (sqrt_d * temperature), pooled, arg,
+                                   plan + 4 * (g - 1), plan + 4 * 16 + 2 * b, cdiv(b, ngmax), st);
+      if (rc2 != ILFDT_OK) return rc2;
+      continue;
+    }
     UmmaParams p{};
     p.spt = 256 / R;
     p.n_step = p.spt * R;
