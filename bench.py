@@ -105,7 +105,7 @@ def workload_config(args, note=None):
     c = {"workload": "FDT ViT-B/32 codebook grounding (codebook %dx%d, P=%d, T=%d, sparsemax, max-pool, T=1000) + "
                      "ClipInfoCELoss fwd/bwd, global batch %d" % (args.codes, D_DIM, P_TOK, T_TOK, args.global_batch),
          "global_batch": args.global_batch, "per_gpu_batch": args.global_batch // max(args.gpus, 1),
-         "parallelism": "dp%d (row-sharded logits, all-gather + reduce-scatter)" % args.gpus,
+         "parallelism": "dp%d (row-sharded logits, all-gather of embeddings fwd + all-gather of row lse bwd)" % args.gpus,
          "l2_policy": "inputs larger than L2 (q: %.1f GB per rank)" % (
              args.global_batch // max(args.gpus, 1) * (P_TOK + T_TOK) * D_DIM * 4 / 1e9)}
     if note:
@@ -253,7 +253,7 @@ def run_ours(args):
     roof = None
     prof = ops.profile_summary()
     if "ground_fwd" in prof:
-        # dominant kernel: umma_kernel<EPI_POOLMAX, 49> = the image launch of ilfdt_ground_fwd (one per step).
+        # dominant kernel: ground2_kernel<49> = the image launch of ilfdt_ground_fwd (one per step).
         # ALGORITHMIC FLOPs per launch = 2 * b * P * D * K.
         n_launch, tot_ms = prof["ground_fwd"]
         flops_per_launch = 2.0 * b * P_TOK * D_DIM * K
@@ -262,8 +262,8 @@ def run_ours(args):
         roof = {"bound": "tensor", "kernel": "ground2_kernel<49> (tcgen05 cta_group::2; ilfdt_ground_fwd, image launch)",
                 "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
                 # dram__bytes_read.sum + dram__bytes_write.sum of this launch from the committed ncu --set full capture
-                # (profiles/r01_ncu_ground_v2_b32768.txt: 3.05 GB + 3.19 GB); only valid for that shape
-                "traffic": 6.235e9 if (b == 32768 and K == 16384) else None, "traffic_unit": "bytes per launch (ncu)",
+                # (profiles/r01_ncu_step_b32768_ground2_ncebwd.txt: 3.05 GB + 3.20 GB); only valid for that shape
+                "traffic": 6.245e9 if (b == 32768 and K == 16384) else None, "traffic_unit": "bytes per launch (ncu)",
                 "peak_source": pk["src"], "avg_launch_ms": avg_ms,
                 "share_of_step": (tot_ms / args.steps) / ms_per_step,
                 "frac_of_burst_peak": (achieved / pk["burst"]) if pk.get("burst") else None,

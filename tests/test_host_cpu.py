@@ -142,9 +142,41 @@ def _gloo_worker(rank, world, port, out):
     ok = torch.allclose(x.grad, expect)
     st = ContrastiveStash(x, x, flat, flat, torch.ones(1), "fp32")
     ok = ok and st.label_offset() == rank * 3 and torch.equal(y[rank], x.detach())
-    out[rank] = bool(ok)
+    out[rank] = bool(ok) and _gathered_identity(rank, world)
     dist.barrier()
     dist.destroy_process_group()
+
+
+def _gathered_identity(rank, world):
+    """The exchange the gathered InfoNCE backward relies on (functional.InfoNCEFunction.backward): all-gather of the
+    per-row log-sum-exp, then dX_img[i] = s * sum_j (P_img[i,j] + P_txt[j,i]) G_txt[j] must equal what autograd through
+    AllGather (sum over ranks of d/d gathered copy, own slice: clip_fdt.py:182-188) gives."""
+    from ilfdt.functional import AllGather
+    b, D, s = 5, 8, 7.0
+    g = torch.Generator().manual_seed(100 + rank)
+    xi = torch.nn.functional.normalize(torch.randn(b, D, generator=g), dim=-1).requires_grad_(True)
+    xt = torch.nn.functional.normalize(torch.randn(b, D, generator=g), dim=-1).requires_grad_(True)
+    gi, gt = AllGather.apply(xi).view(-1, D), AllGather.apply(xt).view(-1, D)
+    li, lt = s * xi @ gt.t(), s * xt @ gi.t()
+    lab = rank * b + torch.arange(b)
+    go = float(rank + 1)                                   # a different upstream gradient on every rank
+    loss = 0.5 * (torch.nn.functional.cross_entropy(li, lab) + torch.nn.functional.cross_entropy(lt, lab))
+    (go * loss).backward()
+    with torch.no_grad():
+        pack = torch.cat([torch.logsumexp(li, 1), torch.logsumexp(lt, 1), torch.tensor([go])])
+        allp = [torch.empty_like(pack) for _ in range(world)]
+        dist.all_gather(allp, pack)
+        lse_i = torch.cat([a[:b] for a in allp]); lse_t = torch.cat([a[b:2 * b] for a in allp])
+        go_all = torch.stack([a[2 * b] for a in allp]).repeat_interleave(b)
+        onehot = torch.zeros(b, world * b); onehot[torch.arange(b), lab] = 1.0
+        def total(x_loc, g_oth, lse_loc_all, lse_oth_all):
+            S = s * x_loc @ g_oth.t()                        # [b, B]: my rows against everyone's other modality
+            p_lane = (torch.exp(S - lse_loc_all[lab][:, None]) - onehot) * go / (2 * b)
+            p_strm = (torch.exp(S - lse_oth_all[None, :]) - onehot) * go_all[None, :] / (2 * b)
+            return s * (p_lane + p_strm) @ g_oth
+        ok = torch.allclose(total(xi, gt.detach(), lse_i, lse_t), xi.grad, atol=1e-6)
+        ok = ok and torch.allclose(total(xt, gi.detach(), lse_t, lse_i), xt.grad, atol=1e-6)
+    return bool(ok)
 
 
 def _gloo_entry(rank, world, port, path):
