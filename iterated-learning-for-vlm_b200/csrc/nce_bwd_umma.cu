@@ -28,20 +28,19 @@ namespace ilfdt {
 
 using namespace umma;
 
-constexpr int NB_THREADS = 320;  // TMA warp, MMA warp, 2 softmax groups of 4 warps (group g owns S buffer g)
+constexpr int NB_THREADS = 352;  // Y TMA warp, MMA warp, 2 softmax groups of 4 warps (group g owns S buffer g), YT TMA warp
 constexpr int NB_XL_BYTES = 8 * 16384;          // lane tile, all k-blocks: 128 KB
 constexpr int NB_Y_STAGE = 64 * 64 * 2;         // 64 stream rows x 64 k      : 8 KB
-constexpr int NB_Y_STAGES = 6;          // deep ring: MMA1 consumes 8 of these 8 KB boxes per S tile (2 stages left it TMA-latency-bound)
-constexpr int NB_P_BYTES = 128 * 64 * 2;        // P tile 128 lanes x 64 stream: 16 KB
+constexpr int NB_Y_STAGES = 4;          // MMA1 consumes 8 of these 8 KB boxes per S tile (2 stages left it TMA-latency-bound)
 constexpr int NB_YT_STAGE = 256 * 64 * 2;       // 256 D-columns x 64 stream   : 32 KB
-constexpr int NB_YT_STAGES = 1;
+constexpr int NB_YT_STAGES = 2;
 constexpr int NB_OFF_Y = NB_XL_BYTES;
-constexpr int NB_OFF_P = NB_OFF_Y + NB_Y_STAGES * NB_Y_STAGE;
-constexpr int NB_OFF_YT = NB_OFF_P + NB_P_BYTES;
+constexpr int NB_OFF_YT = NB_OFF_Y + NB_Y_STAGES * NB_Y_STAGE;
 constexpr int NB_OFF_BARS = NB_OFF_YT + NB_YT_STAGES * NB_YT_STAGE;  // 229376
 constexpr int NB_SMEM_BYTES = NB_OFF_BARS + 1024 + 2048;  // 232448 = the sm_100 opt-in maximum
 constexpr int NB_TMEM_COLS = 512;
 constexpr int NB_TMEM_S = 256;  // S buffers at columns 256 and 320
+constexpr int NB_TMEM_P = 384;  // P (bf16 pairs, the A operand of MMA2) at columns 384 and 416, one buffer per softmax group
 
 struct NceBwdParams {
   int RL, RS, D;
@@ -67,14 +66,17 @@ struct NceBwdBars {
   uint64_t y_full[NB_Y_STAGES], y_empty[NB_Y_STAGES];
   uint64_t yt_full[NB_YT_STAGES], yt_empty[NB_YT_STAGES];
   uint64_t s_full[2], s_empty[2];
-  uint64_t p_full, p_empty;
+  uint64_t p_full[2], p_empty[2];
   uint64_t d_full, d_empty;
   uint32_t tmem_ptr;
-  // per-stream-column constants of the tile a softmax group is converting, [group][..]: lane weight
-  // (0 beyond RS), stream weight, stream lse * log2(e)
-  alignas(16) float col_wl[2][64];
+  // per-stream-column constants of the tile a softmax group is converting, [group][..]: stream weight,
+  // stream lse * log2(e).  (Columns beyond RS need no masking: TMA zero-fills their Y rows, so S = 0 and
+  // whatever finite P they get multiplies zeros in MMA2.)
   alignas(16) float col_ws[2][64];
   alignas(16) float col_l2[2][64];
+  // fast path: -(stream lse * log2(e) - log2(stream weight)); +inf exponent offset (=> 0) beyond RS or for weight 0
+  alignas(16) float col_lf[2][64];
+  uint32_t col_neg[2][2];   // [group][loader warp]: some weight of the tile is negative (general path needed)
 };
 
 static_assert(sizeof(NceBwdBars) <= 2048, "barrier block outgrew its shared-memory slot");
@@ -82,6 +84,12 @@ static_assert(NB_SMEM_BYTES <= 232448, "over the sm_100 dynamic shared memory li
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
 
 template <int MODE>
@@ -100,8 +108,7 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
     for (int i = 0; i < NB_Y_STAGES; ++i) { mbar_init(&bars->y_full[i], 1); mbar_init(&bars->y_empty[i], 1); }
     for (int i = 0; i < NB_YT_STAGES; ++i) { mbar_init(&bars->yt_full[i], 1); mbar_init(&bars->yt_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&bars->s_full[i], 1); mbar_init(&bars->s_empty[i], 4); }
-    mbar_init(&bars->p_full, 4);
-    mbar_init(&bars->p_empty, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&bars->p_full[i], 4); mbar_init(&bars->p_empty[i], 1); }
     mbar_init(&bars->d_full, 1);
     mbar_init(&bars->d_empty, 8);
     fence_barrier_init();
@@ -120,10 +127,10 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
-      uint32_t ys = 0, yph = 0, ts = 0, tph = 0, it = 0;
+      uint32_t ys = 0, yph = 0, it = 0;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
         const int split = item % p.nsplit, lh = item / p.nsplit;
-        const int half = lh % p.num_halves, lt = lh / p.num_halves;
+        const int lt = lh / p.num_halves;
         const int t_begin = split * p.tiles_per_split, t_end = min(p.num_stream_tiles, t_begin + p.tiles_per_split);
         mbar_wait(&bars->xl_empty, (it & 1) ^ 1);
         mbar_expect_tx(&bars->xl_full, (uint32_t)p.nkb * 16384u);
@@ -136,6 +143,18 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
             tma_load_2d(smem + NB_OFF_Y + ys * NB_Y_STAGE, &tmY, &bars->y_full[ys], kb * 64, t * 64, kEvictNormal);
             if (++ys == NB_Y_STAGES) { ys = 0; yph ^= 1; }
           }
+        }
+      }
+    }
+  } else if (warp == 10) {
+    // ===================== TMA producer of the MMA2 operand (own warp: the Y ring must not queue behind it) =====
+    if (elect_one()) {
+      uint32_t ts = 0, tph = 0;
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        const int split = item % p.nsplit, lh = item / p.nsplit;
+        const int half = lh % p.num_halves;
+        const int t_begin = split * p.tiles_per_split, t_end = min(p.num_stream_tiles, t_begin + p.tiles_per_split);
+        for (int t = t_begin; t < t_end; ++t) {
           mbar_wait(&bars->yt_empty[ts], tph ^ 1);
           mbar_expect_tx(&bars->yt_full[ts], NB_YT_STAGE);
           for (int j = 0; j < 4; ++j)  // the CTA's 256 D-columns of the same 64 stream rows (columns >= D: zero fill)
@@ -158,9 +177,11 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
         mbar_wait(&bars->xl_full, it & 1);
         mbar_wait(&bars->d_empty, (it & 1) ^ 1);  // epilogue of the previous item drained dOut
         fence_after_sync();
-        for (int i = 0; i <= ntile; ++i) {
-          if (i < ntile) {
-            // ---- MMA1: S tile i ----
+        int n1 = 0;  // S tiles issued in this item
+        for (int i = 0; i < ntile; ++i) {
+          // ---- MMA1 runs up to two tiles ahead of MMA2 (S is double buffered and released as soon as the softmax
+          //      warps hold it in registers), so the tensor pipe computes S(i+1), S(i+2) while P(i) is being formed ----
+          while (n1 < ntile && n1 <= i + 2) {
             const uint32_t sb = tile_ctr & 1, sph = (tile_ctr >> 1) & 1;
             mbar_wait(&bars->s_empty[sb], sph ^ 1);
             fence_after_sync();
@@ -179,21 +200,23 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
             }
             mma_commit(&bars->s_full[sb]);
             ++tile_ctr;
+            ++n1;
           }
-          if (i > 0) {
-            // ---- MMA2: dOut += P(tile i-1) . YT(tile i-1)^T ----
-            mbar_wait(&bars->p_full, p_ctr & 1);
+          {
+            // ---- MMA2: dOut += P(tile i) . YT(tile i)^T ----
+            const uint32_t pb = p_ctr & 1;   // P buffer = softmax group = S buffer of the tile
+            mbar_wait(&bars->p_full[pb], (p_ctr >> 1) & 1);
             mbar_wait(&bars->yt_full[ts], tph);
             fence_after_sync();
-            const uint64_t adesc = make_smem_desc_sw128(smem_u32(smem + NB_OFF_P));
+            const uint32_t a_tmem = tmem_base + NB_TMEM_P + pb * 32;   // 16 K-elements = 8 columns per MMA
             // B = Y[64 stream rows (K), 256 D-columns (N)], N contiguous: MN-major, 4 boxes of 64 columns 8 KB
             // apart (leading offset), 8-row groups 1 KB apart (stride offset); a K step of 16 rows = 2 KB
             const uint64_t bdesc = make_smem_desc_sw128_mn(smem_u32(smem + NB_OFF_YT + ts * NB_YT_STAGE), 8192);
 #pragma unroll
             for (int k4 = 0; k4 < 4; ++k4)
-              mma_f16(tmem_base, advance_desc_k(adesc, k4 * 32), advance_desc_k(bdesc, k4 * 2048), p.idesc2,
-                      (i > 1 || k4 != 0) ? 1u : 0u);
-            mma_commit(&bars->p_empty);
+              mma_f16_ts(tmem_base, a_tmem + k4 * 8, advance_desc_k(bdesc, k4 * 2048), p.idesc2,
+                         (i > 0 || k4 != 0) ? 1u : 0u);
+            mma_commit(&bars->p_empty[pb]);
             mma_commit(&bars->yt_empty[ts]);
             if (++ts == NB_YT_STAGES) { ts = 0; tph ^= 1; }
             ++p_ctr;
@@ -203,8 +226,8 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
         mma_commit(&bars->xl_empty);
       }
     }
-  } else {
-    // ===================== softmax + epilogue warps (2..5) =====================
+  } else if (warp < 10) {
+    // ===================== softmax + epilogue warps (2..9) =====================
     const int quad = warp & 3;
     const uint32_t group = (uint32_t)(warp - 2) >> 2;
     const int tid128 = ((warp - 2) & 3) * 32 + lane;
@@ -214,8 +237,6 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
     const float scale = __ldg(p.scale_dev);
     const float scale_log2 = scale * 1.4426950408889634f;
     uint32_t tile_ctr = 0, it = 0;
-    uint8_t* p_row = smem + NB_OFF_P + r_in_tile * 128;
-    const int sw = r_in_tile & 7;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
       const int split = item % p.nsplit, lh = item / p.nsplit;
       const int half = lh % p.num_halves, lt = lh / p.num_halves;
@@ -226,24 +247,36 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
                                            : (long long)row - p.label_offset;  // lane row == label_offset + stream j
       const bool row_ok = row < p.RL;
       const float lse_lane = (MODE != 1 && row_ok) ? __ldg(p.lse_lane + row) * 1.4426950408889634f : 0.f;
+      // fast path: lane weight folded into the exponent; rows beyond RL give finite garbage that is never stored
+      const float lane_off = __log2f(wl) - lse_lane;
+      // stream columns that hold the labels of this lane tile: [label_lo, label_lo + 128)
+      const long long label_lo = p.label_by_lane ? p.label_offset + (long long)lt * 128 : (long long)lt * 128 - p.label_offset;
       float ds_acc = 0.f;
       for (int t = t_begin; t < t_end; ++t, ++tile_ctr) {
         const uint32_t sb = tile_ctr & 1, sph = (tile_ctr >> 1) & 1;
         if (sb != group) continue;  // the other softmax group converts this tile
         const int j0 = t * 64;
-        float* c_wl = bars->col_wl[sb];
         float* c_ws = bars->col_ws[sb];
         float* c_l2 = bars->col_l2[sb];
+        float* c_lf = bars->col_lf[sb];
         if (tid128 < 64) {
           const long long n = (long long)j0 + tid128;
           const bool ok = n < p.RS;
-          c_wl[tid128] = ok ? wl : 0.f;
+          bool neg = wl < 0.f;
           if (MODE != 0) {
-            c_ws[tid128] = ok ? __ldg(p.go_stream + n / p.rows_per_go) * p.inv_2b : 0.f;
-            c_l2[tid128] = ok ? __ldg(p.lse_stream + n) * 1.4426950408889634f : 0.f;
+            const float ws = ok ? __ldg(p.go_stream + n / p.rows_per_go) * p.inv_2b : 0.f;
+            const float l2 = ok ? __ldg(p.lse_stream + n) * 1.4426950408889634f : 0.f;
+            c_ws[tid128] = ws;
+            c_l2[tid128] = l2;
+            c_lf[tid128] = __log2f(ws) - l2;     // ws == 0 -> -inf -> ex2 gives 0; ws < 0 -> general path (flag below)
+            neg = neg || ws < 0.f;
           }
+          const bool any_neg = __any_sync(0xffffffffu, neg);
+          if (lane == 0) bars->col_neg[sb][tid128 >> 5] = any_neg ? 1u : 0u;
         }
         named_bar_sync(1 + (int)group, 128);
+        // the general path is needed only by tiles that hold a label column of this lane tile or a negative weight
+        const bool general = (j0 < label_lo + 128 && j0 + 64 > label_lo) || (bars->col_neg[sb][0] | bars->col_neg[sb][1]) != 0u;
         const int jd = (jl >= j0 && jl < (long long)j0 + 64) ? (int)(jl - j0) : -1;
         mbar_wait(&bars->s_full[sb], sph);
         fence_after_sync();
@@ -255,39 +288,69 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->s_empty[sb]);
         uint32_t packed[32];
+        if (!general) {
+          // fast path: weights folded into the exponent, P = 2^(a - L_i') + 2^(a - l_j'), no label term
+          float ds_e = 0.f;
 #pragma unroll
-        for (int h2 = 0; h2 < 2; ++h2) {
+          for (int h2 = 0; h2 < 2; ++h2) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 2) {
-            float pv[2];
+            for (int j = 0; j < 32; j += 4) {
+              float4 lf = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (MODE != 0) lf = *reinterpret_cast<const float4*>(c_lf + h2 * 32 + j);
+              const float lfa[4] = {lf.x, lf.y, lf.z, lf.w};
+              float pv[4];
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              const int jj = h2 * 32 + j + e;
-              const float s_raw = __uint_as_float(h2 == 0 ? v0[j + e] : v1[j + e]);
-              const float dlt = (jj == jd) ? 1.f : 0.f;
-              float pr = 0.f;
-              if (MODE != 1) {
-                pr = (exp2f(fmaf(s_raw, scale_log2, -lse_lane)) - dlt) * c_wl[jj];
-                ds_acc = fmaf(pr, s_raw, ds_acc);   // dLoss/dscale of the LANE rows' own logits only
+              for (int e = 0; e < 4; ++e) {
+                const float s_raw = __uint_as_float(h2 == 0 ? v0[j + e] : v1[j + e]);
+                float pr = 0.f;
+                if (MODE != 1) {
+                  pr = ex2_approx(fmaf(s_raw, scale_log2, lane_off));
+                  ds_e = fmaf(pr, s_raw, ds_e);
+                }
+                if (MODE != 0) pr += ex2_approx(fmaf(s_raw, scale_log2, lfa[e]));
+                pv[e] = pr;
               }
-              if (MODE != 0) pr = fmaf(exp2f(fmaf(s_raw, scale_log2, -c_l2[jj])) - dlt, c_ws[jj], pr);
-              pv[e] = pr;
+              __nv_bfloat162 b01 = __floats2bfloat162_rn(pv[0], pv[1]);
+              __nv_bfloat162 b23 = __floats2bfloat162_rn(pv[2], pv[3]);
+              packed[h2 * 16 + (j >> 1)] = *reinterpret_cast<uint32_t*>(&b01);
+              packed[h2 * 16 + (j >> 1) + 1] = *reinterpret_cast<uint32_t*>(&b23);
             }
-            __nv_bfloat162 b2 = __floats2bfloat162_rn(pv[0], pv[1]);
-            packed[h2 * 16 + (j >> 1)] = *reinterpret_cast<uint32_t*>(&b2);
+          }
+          ds_acc += ds_e;
+        } else {
+#pragma unroll
+          for (int h2 = 0; h2 < 2; ++h2) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              float pv[2];
+#pragma unroll
+              for (int e = 0; e < 2; ++e) {
+                const int jj = h2 * 32 + j + e;
+                const float s_raw = __uint_as_float(h2 == 0 ? v0[j + e] : v1[j + e]);
+                const float dlt = (jj == jd) ? 1.f : 0.f;
+                float pr = 0.f;
+                if (MODE != 1) {
+                  pr = (exp2f(fmaf(s_raw, scale_log2, -lse_lane)) - dlt) * wl;
+                  ds_acc = fmaf(pr, s_raw, ds_acc);   // dLoss/dscale of the LANE rows' own logits only
+                }
+                if (MODE != 0) pr = fmaf(exp2f(fmaf(s_raw, scale_log2, -c_l2[jj])) - dlt, c_ws[jj], pr);
+                pv[e] = pr;
+              }
+              __nv_bfloat162 b2 = __floats2bfloat162_rn(pv[0], pv[1]);
+              packed[h2 * 16 + (j >> 1)] = *reinterpret_cast<uint32_t*>(&b2);
+            }
           }
         }
         // P buffer free? (MMA2 of the previous tile finished reading it)
-        mbar_wait(&bars->p_empty, (tile_ctr & 1) ^ 1);  // P is single-buffered: phases follow the global tile index
-        // 8 chunks of 16 B (8 bf16 each), 128-byte swizzle: chunk c of row r lives at c ^ (r & 7)
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          uint4 val = make_uint4(packed[c * 4], packed[c * 4 + 1], packed[c * 4 + 2], packed[c * 4 + 3]);
-          *reinterpret_cast<uint4*>(p_row + ((c ^ sw) << 4)) = val;
-        }
-        fence_proxy_async_smem();  // make the generic-proxy writes visible to the tensor core (async proxy)
+        // one P buffer per group: the group's previous tile (two tiles back) must have been consumed by MMA2.
+        // (A single shared buffer would alias mbarrier parities now that S runs two tiles ahead of MMA2.)
+        mbar_wait(&bars->p_empty[group], ((tile_ctr >> 1) & 1) ^ 1);
+        // P stays on chip as the TMEM A operand of MMA2: thread = lane row, 32 columns of bf16 pairs (K = 64)
+        tmem_st32(tmem_base + lane_addr + NB_TMEM_P + group * 32, packed);
+        tmem_st_wait();
+        fence_before_sync();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bars->p_full);
+        if (lane == 0) mbar_arrive(&bars->p_full[group]);
         named_bar_sync(1 + (int)group, 128);  // every reader of col_* is done before the next tile's values land
       }
       // ---- epilogue: dOut (TMEM columns 0..255) -> global ----
