@@ -16,7 +16,7 @@
 //   epilogue warps (both CTAs)      each CTA drains its own TMEM lanes (its 128 codes) with the same statically
 //                                   unrolled max/argmax body; every epilogue warp of both CTAs arrives on the
 //                                   LEADER's tmem_empty[acc] (remote arrive for the peer)
-#include "umma.cuh"
+#include "umma_pair.cuh"
 #include "poolmax.cuh"
 #include "launch.h"
 #include <algorithm>
@@ -32,7 +32,6 @@ constexpr int G2_B_BYTES = 128 * 64 * 2;      // 16 KB per stage: this CTA's hal
 constexpr int G2_STAGES = 6;
 constexpr int G2_DATA_BYTES = 8 * G2_A_BYTES + G2_STAGES * G2_B_BYTES;   // 224 KB
 constexpr int G2_SMEM_BYTES = G2_DATA_BYTES + 1024 + 256;
-constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;   // shared::cluster address of the same offset in the pair's even CTA
 
 struct G2Params {
   int num_m_pairs, nchunk, tiles_per_chunk, num_n_tiles, nkb;
@@ -52,59 +51,6 @@ struct G2Bars {
   uint64_t full[G2_STAGES], empty[G2_STAGES], tmem_full[2], tmem_empty[2], a_full, a_empty;
   uint32_t tmem_ptr;
 };
-
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-// arrive on the mbarrier at the same shared-memory offset in CTA `rank` of the cluster
-__device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t rank) {
-  asm volatile(
-      "{\n\t.reg .b32 ra;\n\t"
-      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}\n"
-      ::"r"(smem_u32(bar)), "r"(rank)
-      : "memory");
-}
-// TMA load of a CTA pair: data into this CTA's smem, transaction bytes onto the pair leader's mbarrier
-__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
-                                                 uint64_t hint) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
-      " [%0], [%1, {%3, %4}], [%2], %5;"
-      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1),
-        "l"(hint)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_alloc_pair(uint32_t* smem_dst, uint32_t ncols) {
-  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols)
-               : "memory");
-}
-__device__ __forceinline__ void tmem_relinquish_pair() {
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
-  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void mma_f16_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
-                                             uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}\n"
-      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-// arrive on the mbarrier at this offset in BOTH CTAs once all tcgen05.mma issued so far have completed
-__device__ __forceinline__ void mma_commit_pair(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-               ::"r"(smem_u32(bar)), "h"((uint16_t)3)
-               : "memory");
-}
 
 template <int NTOK>
 __global__ void __launch_bounds__(G2_THREADS, 1)

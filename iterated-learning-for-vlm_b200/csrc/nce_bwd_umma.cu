@@ -20,9 +20,8 @@
 // A CTA owns (lane tile, 256-wide half of D, slice of the stream range); S is recomputed for each half
 // (TMEM holds 512 columns: 256 for dOut + 2 x 64 for S).  The MMA thread software-pipelines MMA1(t+1)
 // ahead of MMA2(t) so the tensor pipe stays busy while the softmax warps convert tile t.
-#include "umma.cuh"
-#include "launch.h"
 #include <algorithm>
+#include "nce_bwd_common.cuh"
 
 namespace ilfdt {
 
@@ -42,25 +41,6 @@ constexpr int NB_TMEM_COLS = 512;
 constexpr int NB_TMEM_S = 256;  // S buffers at columns 256 and 320
 constexpr int NB_TMEM_P = 384;  // P (bf16 pairs, the A operand of MMA2) at columns 384 and 416, one buffer per softmax group
 
-struct NceBwdParams {
-  int RL, RS, D;
-  int nkb;              // ceil(D / 64)
-  int num_lane_tiles, num_halves, nsplit, tiles_per_split, num_stream_tiles;
-  int label_by_lane;    // 1: label(lane i) = stream label_offset + i;  0: label(stream j) = lane label_offset + j
-  long long label_offset;
-  const float* lse_lane;    // [RL]  (MODE 0, 2)
-  const float* lse_stream;  // [RS]  (MODE 1, 2)
-  const float* go_lane;     // 1 float: upstream dLoss of the rank owning the lane rows
-  const float* go_stream;   // [ceil(RS / rows_per_go)]: upstream dLoss of the rank owning each stream row
-  long long rows_per_go;
-  float inv_2b;
-  const float* scale_dev;
-  float* out;           // [RL, D]
-  int use_atomic;
-  float* dscale;        // accumulated only by lse_by_lane launches, half 0
-  uint32_t idesc1, idesc2;
-};
-
 struct NceBwdBars {
   uint64_t xl_full, xl_empty;
   uint64_t y_full[NB_Y_STAGES], y_empty[NB_Y_STAGES];
@@ -69,28 +49,11 @@ struct NceBwdBars {
   uint64_t p_full[2], p_empty[2];
   uint64_t d_full, d_empty;
   uint32_t tmem_ptr;
-  // per-stream-column constants of the tile a softmax group is converting, [group][..]: stream weight,
-  // stream lse * log2(e).  (Columns beyond RS need no masking: TMA zero-fills their Y rows, so S = 0 and
-  // whatever finite P they get multiplies zeros in MMA2.)
-  alignas(16) float col_ws[2][64];
-  alignas(16) float col_l2[2][64];
-  // fast path: -(stream lse * log2(e) - log2(stream weight)); +inf exponent offset (=> 0) beyond RS or for weight 0
-  alignas(16) float col_lf[2][64];
-  uint32_t col_neg[2][2];   // [group][loader warp]: some weight of the tile is negative (general path needed)
+  NceColBuf cols[2];   // one per softmax group
 };
 
 static_assert(sizeof(NceBwdBars) <= 2048, "barrier block outgrew its shared-memory slot");
 static_assert(NB_SMEM_BYTES <= 232448, "over the sm_100 dynamic shared memory limit");
-
-__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
-}
-
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
 
 template <int MODE>
 __global__ void __launch_bounds__(NB_THREADS, 1)
@@ -256,27 +219,15 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
         const uint32_t sb = tile_ctr & 1, sph = (tile_ctr >> 1) & 1;
         if (sb != group) continue;  // the other softmax group converts this tile
         const int j0 = t * 64;
-        float* c_ws = bars->col_ws[sb];
-        float* c_l2 = bars->col_l2[sb];
-        float* c_lf = bars->col_lf[sb];
+        NceColBuf* cols = &bars->cols[sb];
         if (tid128 < 64) {
-          const long long n = (long long)j0 + tid128;
-          const bool ok = n < p.RS;
-          bool neg = wl < 0.f;
-          if (MODE != 0) {
-            const float ws = ok ? __ldg(p.go_stream + n / p.rows_per_go) * p.inv_2b : 0.f;
-            const float l2 = ok ? __ldg(p.lse_stream + n) * 1.4426950408889634f : 0.f;
-            c_ws[tid128] = ws;
-            c_l2[tid128] = l2;
-            c_lf[tid128] = __log2f(ws) - l2;     // ws == 0 -> -inf -> ex2 gives 0; ws < 0 -> general path (flag below)
-            neg = neg || ws < 0.f;
-          }
-          const bool any_neg = __any_sync(0xffffffffu, neg);
-          if (lane == 0) bars->col_neg[sb][tid128 >> 5] = any_neg ? 1u : 0u;
+          float ws, l2;
+          nce_fetch_cols<MODE>(p, j0, tid128, ws, l2);
+          nce_publish_cols<MODE>(cols, tid128, lane, wl, ws, l2);
         }
         named_bar_sync(1 + (int)group, 128);
         // the general path is needed only by tiles that hold a label column of this lane tile or a negative weight
-        const bool general = (j0 < label_lo + 128 && j0 + 64 > label_lo) || (bars->col_neg[sb][0] | bars->col_neg[sb][1]) != 0u;
+        const bool general = (j0 < label_lo + 128 && j0 + 64 > label_lo) || (cols->neg[0] | cols->neg[1]) != 0u;
         const int jd = (jl >= j0 && jl < (long long)j0 + 64) ? (int)(jl - j0) : -1;
         mbar_wait(&bars->s_full[sb], sph);
         fence_after_sync();
@@ -288,60 +239,7 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->s_empty[sb]);
         uint32_t packed[32];
-        if (!general) {
-          // fast path: weights folded into the exponent, P = 2^(a - L_i') + 2^(a - l_j'), no label term
-          float ds_e = 0.f;
-#pragma unroll
-          for (int h2 = 0; h2 < 2; ++h2) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              float4 lf = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (MODE != 0) lf = *reinterpret_cast<const float4*>(c_lf + h2 * 32 + j);
-              const float lfa[4] = {lf.x, lf.y, lf.z, lf.w};
-              float pv[4];
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float s_raw = __uint_as_float(h2 == 0 ? v0[j + e] : v1[j + e]);
-                float pr = 0.f;
-                if (MODE != 1) {
-                  pr = ex2_approx(fmaf(s_raw, scale_log2, lane_off));
-                  ds_e = fmaf(pr, s_raw, ds_e);
-                }
-                if (MODE != 0) pr += ex2_approx(fmaf(s_raw, scale_log2, lfa[e]));
-                pv[e] = pr;
-              }
-              __nv_bfloat162 b01 = __floats2bfloat162_rn(pv[0], pv[1]);
-              __nv_bfloat162 b23 = __floats2bfloat162_rn(pv[2], pv[3]);
-              packed[h2 * 16 + (j >> 1)] = *reinterpret_cast<uint32_t*>(&b01);
-              packed[h2 * 16 + (j >> 1) + 1] = *reinterpret_cast<uint32_t*>(&b23);
-            }
-          }
-          ds_acc += ds_e;
-        } else {
-#pragma unroll
-          for (int h2 = 0; h2 < 2; ++h2) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              float pv[2];
-#pragma unroll
-              for (int e = 0; e < 2; ++e) {
-                const int jj = h2 * 32 + j + e;
-                const float s_raw = __uint_as_float(h2 == 0 ? v0[j + e] : v1[j + e]);
-                const float dlt = (jj == jd) ? 1.f : 0.f;
-                float pr = 0.f;
-                if (MODE != 1) {
-                  pr = (exp2f(fmaf(s_raw, scale_log2, -lse_lane)) - dlt) * wl;
-                  ds_acc = fmaf(pr, s_raw, ds_acc);   // dLoss/dscale of the LANE rows' own logits only
-                }
-                if (MODE != 0) pr = fmaf(exp2f(fmaf(s_raw, scale_log2, -c_l2[jj])) - dlt, c_ws[jj], pr);
-                pv[e] = pr;
-              }
-              __nv_bfloat162 b2 = __floats2bfloat162_rn(pv[0], pv[1]);
-              packed[h2 * 16 + (j >> 1)] = *reinterpret_cast<uint32_t*>(&b2);
-            }
-          }
-        }
-        // P buffer free? (MMA2 of the previous tile finished reading it)
+        nce_convert<MODE>(v0, v1, packed, general, jd, scale_log2, lane_off, lse_lane, wl, cols, p, j0, ds_acc);
         // one P buffer per group: the group's previous tile (two tiles back) must have been consumed by MMA2.
         // (A single shared buffer would alias mbarrier parities now that S runs two tiles ahead of MMA2.)
         mbar_wait(&bars->p_empty[group], ((tile_ctr >> 1) & 1) ^ 1);
@@ -406,21 +304,8 @@ int64_t nce_bwd_bf16_ws_bytes(int64_t b, int64_t B, int64_t D) {
   return 256;
 }
 
-struct NceBwdLaunch {
-  const void* XL; const void* Y;      // lane matrix [RL, D], stream matrix [RS, D] (bf16)
-  int64_t RL, RS, D;
-  int mode;                            // 0 lane softmax, 1 stream softmax, 2 both
-  int label_by_lane;
-  int64_t label_offset;
-  const float* lse_lane; const float* lse_stream;
-  const float* go_lane; const float* go_stream;
-  int64_t rows_per_go;
-  float inv_2b;
-  const float* scale;
-  float* out; float* dscale;
-};
-
 static int32_t launch_one(const NceBwdLaunch& a, cudaStream_t st) {
+  if (nce_bwd_pair_enabled() && a.RL >= 256) return nce_bwd_pair_launch(a, st);
   NceBwdParams p{};
   const int64_t RL = a.RL, RS = a.RS, D = a.D;
   p.RL = (int)RL; p.RS = (int)RS; p.D = (int)D;
@@ -430,22 +315,7 @@ static int32_t launch_one(const NceBwdLaunch& a, cudaStream_t st) {
   p.num_stream_tiles = (int)cdiv(RS, 64);
   const int base_items = p.num_lane_tiles * p.num_halves;
   const int sms = sm_count();
-  // split the stream range so that the persistent grid is full and even: items = base_items * nsplit
-  int nsplit = 1;
-  if (base_items % sms != 0) {
-    double best = -1.0;
-    const int max_split = (int)std::min<int64_t>(p.num_stream_tiles, std::max<int64_t>(1, cdiv(4 * sms, base_items)));
-    for (int c = 1; c <= max_split; ++c) {
-      const int tps = (int)cdiv(p.num_stream_tiles, c);
-      const int rc = (int)cdiv(p.num_stream_tiles, tps);
-      const int64_t items = (int64_t)base_items * rc;
-      double eff = (double)items / (double)(cdiv(items, sms) * sms);
-      eff *= (double)tps / (double)(tps + 6.0);   // every item pays a lane-tile load, an epilogue and (split) atomics
-      if (eff > best + 1e-9) { best = eff; nsplit = rc; }
-    }
-  }
-  p.tiles_per_split = (int)cdiv(p.num_stream_tiles, nsplit);
-  p.nsplit = (int)cdiv(p.num_stream_tiles, p.tiles_per_split);
+  nce_bwd_plan(p, base_items, sms);
   p.label_by_lane = a.label_by_lane;
   p.label_offset = a.label_offset;
   p.lse_lane = a.lse_lane;
@@ -456,7 +326,6 @@ static int32_t launch_one(const NceBwdLaunch& a, cudaStream_t st) {
   p.inv_2b = a.inv_2b;
   p.scale_dev = a.scale;
   p.out = a.out;
-  p.use_atomic = p.nsplit > 1 ? 1 : 0;
   p.dscale = a.dscale;
   p.idesc1 = make_idesc_bf16(128, 64);
   p.idesc2 = make_idesc_bf16(128, 256, 0, 1);   // B = Y box read MN-major
