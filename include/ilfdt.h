@@ -220,6 +220,13 @@ int32_t ilfdt_ce_rows_bwd(const float* logits, int64_t b, int64_t B, int64_t lab
  * exceed it.  logits f32 [b,B]. */
 int32_t ilfdt_topk_hits(const float* logits, int64_t b, int64_t B, int64_t label_offset,
                         int32_t* counts, void* stream);
+/* The same counts WITHOUT the [b,B] matrix: logits = scale[0] * x[b,:] . g[B,:]^T is recomputed tile by
+ * tile on the tensor cores and each entry compared with the row's label logit `diag` (ilfdt_nce_fwd's diag_i for
+ * logits_per_image) -- the comparison accuracy() makes at train_solver.py:421, entry for entry. counts[2] int32;
+ * ws: ilfdt_nce_ws_bytes(dtype, b, B, D) bytes (BF16 uses b*4 of it; F32 streams row chunks of logits through it). */
+int32_t ilfdt_nce_topk_hits(const void* x, const void* g, int32_t dtype, int64_t b, int64_t B, int64_t D,
+                            const float* scale, int64_t label_offset, const float* diag, int32_t* counts, void* ws,
+                            int64_t ws_bytes, void* stream);
 
 /* ---- a12: codebook reset / store / keep, clip_fdt.py:281-283, train_solver.py:211-215,549-553 -- */
 /* dst[i] ~ N(0,1): Philox4x32-10 keyed by seed, counter (i/4, generation), Box-Muller. Same values

@@ -446,6 +446,31 @@ int32_t ilfdt_ce_rows_bwd(const float* logits, int64_t b, int64_t B, int64_t lab
                                   ST(stream));
 }
 
+int32_t ilfdt_nce_topk_hits(const void* x, const void* g, int32_t dtype, int64_t b, int64_t B, int64_t D,
+                            const float* scale, int64_t label_offset, const float* diag, int32_t* counts, void* ws,
+                            int64_t ws_bytes, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(dtype);
+  ILFDT_REQUIRE(b >= 1 && B >= b && D >= 1, ILFDT_E_INVALID_ARG, "nce_topk_hits: need 1 <= b <= B");
+  ILFDT_REQUIRE(label_offset >= 0 && label_offset + b <= B, ILFDT_E_INVALID_ARG, "nce_topk_hits: labels out of range");
+  ILFDT_REQUIRE(x && g && scale && diag && counts, ILFDT_E_INVALID_ARG, "nce_topk_hits: null pointer");
+  if (dtype == ILFDT_BF16)
+    return launch_nce_topk_bf16(x, g, b, B, D, scale, label_offset, diag, counts, ws, ws_bytes, ST(stream));
+  // F32: stream the logits through `ws` in row chunks (same chunking as ilfdt_nce_fwd) and count per chunk
+  const int64_t R = nce_f32_chunk_rows(b, B);
+  ILFDT_REQUIRE(ws != nullptr && ws_bytes >= R * B * 4, ILFDT_E_INVALID_ARG, "nce_topk_hits(f32): workspace too small");
+  float* L = reinterpret_cast<float*>(ws);
+  ILFDT_CUDA_OK(cudaMemsetAsync(counts, 0, 8, ST(stream)));
+  for (int64_t r0 = 0; r0 < b; r0 += R) {
+    const int64_t rows = std::min(R, b - r0);
+    int32_t rc = launch_gemm_f32(reinterpret_cast<const float*>(x) + r0 * D, D, 1, reinterpret_cast<const float*>(g), D, 1,
+                                 L, B, 1, rows, B, D, 1.f, scale, 0, ST(stream));
+    if (rc != ILFDT_OK) return rc;
+    if ((rc = launch_topk_hits_acc(L, rows, B, label_offset + r0, counts, ST(stream))) != ILFDT_OK) return rc;
+  }
+  return ILFDT_OK;
+}
+
 int32_t ilfdt_topk_hits(const float* logits, int64_t b, int64_t B, int64_t label_offset, int32_t* counts,
                         void* stream) {
   ARCH_GUARD();

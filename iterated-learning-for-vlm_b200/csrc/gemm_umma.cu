@@ -38,7 +38,7 @@ constexpr int UM_SMEM_BYTES = UM_DATA_BYTES + 1024 /*alignment slack*/ + 256 /*b
 constexpr int UM_TMEM_COLS = 512;
 constexpr int UM_ACC_COLS = 256;
 
-enum { EPI_STORE_T = 0, EPI_POOLMAX = 1, EPI_LSE = 2 };
+enum { EPI_STORE_T = 0, EPI_POOLMAX = 1, EPI_LSE = 2, EPI_RANK = 3 };
 
 struct UmmaParams {
   int num_m_tiles, num_n_tiles, nchunk, tiles_per_chunk;
@@ -69,6 +69,8 @@ struct UmmaParams {
   float* part_m;
   float* part_s;
   float* diag;
+  // EPI_RANK (N1): rank[row] += #{columns whose logit exceeds the row's label logit diag[row]}
+  int* rank;
 };
 
 struct UmmaBars {
@@ -216,7 +218,9 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const bool row_ok = row < p.m_rows;
       // EPI_LSE state (base-2 domain)
       float run_m = -INFINITY, run_s = 0.f;
-      const float scale = (EPI == EPI_LSE) ? __ldg(p.scale_dev) : 1.f;
+      const float scale = (EPI == EPI_LSE || EPI == EPI_RANK) ? __ldg(p.scale_dev) : 1.f;
+      const float rank_ref = (EPI == EPI_RANK && row_ok) ? __ldg(p.diag + row) : INFINITY;
+      int rank_cnt = 0;
       const float scale_log2 = scale * 1.4426950408889634f;
       const float alpha = (EPI == EPI_STORE_T) ? (p.alpha_dev ? p.alpha * __ldg(p.alpha_dev) : p.alpha) : 1.f;
       for (int n = n_begin; n < n_end; ++n, ++tile_seq) {
@@ -282,6 +286,18 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             }
           }
+        } else if (EPI == EPI_RANK) {
+          // same scale multiply as the EPI_LSE label pick and the materialising logits kernel: the comparison is the
+          // one accuracy() would make on stored logits (misc.py:464-477), column for column
+          const int ncols = min(p.n_step, p.n_rows - n0);
+          for (int c0 = 0; c0 < ncols; c0 += 32) {
+            uint32_t v[32];
+            tmem_ld32(taddr + c0, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              rank_cnt += (c0 + j < ncols && __uint_as_float(v[j]) * scale > rank_ref) ? 1 : 0;
+          }
         } else {  // EPI_LSE
           const int ncols = min(p.n_step, p.n_rows - n0);
           const long long label = p.label_offset + row;
@@ -315,6 +331,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
       }
+      if (EPI == EPI_RANK && row_ok && rank_cnt != 0) atomicAdd(p.rank + row, rank_cnt);
       if (EPI == EPI_LSE && row_ok) {  // one partial per (chunk, epilogue group)
         p.part_m[(int64_t)(chunk * 2 + group) * p.m_rows + row] = run_m;
         p.part_s[(int64_t)(chunk * 2 + group) * p.m_rows + row] = run_s;
@@ -611,6 +628,47 @@ int32_t launch_nce_fwd_bf16(const void* x_img, const void* x_txt, const void* g_
                                                               dir == 0 ? lse_i : lse_t);
     ILFDT_LAUNCH_OK();
   }
+  return ILFDT_OK;
+}
+
+
+// N1: top-1 / top-5 hits of logits = scale * x . g^T against labels label_offset + row, without storing the logits.
+__global__ void rank_hits_kernel(const int* __restrict__ rank, int64_t rows, int32_t* __restrict__ counts) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int h1 = 0, h5 = 0;
+  if (r < rows) {
+    const int q = rank[r];
+    h1 = q < 1;
+    h5 = q < 5;
+  }
+  h1 = warp_sum(h1);
+  h5 = warp_sum(h5);
+  if ((threadIdx.x & 31) == 0) {
+    if (h1) atomicAdd(counts + 0, h1);
+    if (h5) atomicAdd(counts + 1, h5);
+  }
+}
+
+int32_t launch_nce_topk_bf16(const void* x, const void* g, int64_t b, int64_t B, int64_t D, const float* scale,
+                             int64_t label_offset, const float* diag, int32_t* counts, void* ws, int64_t ws_bytes,
+                             cudaStream_t st) {
+  ILFDT_REQUIRE(D <= 512 && D % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "nce_topk(bf16): D=%lld must be <= 512, %% 8",
+                (long long)D);
+  ILFDT_REQUIRE(ws != nullptr && ws_bytes >= b * 4, ILFDT_E_INVALID_ARG, "nce_topk(bf16): workspace too small");
+  int* rank = reinterpret_cast<int*>(ws);
+  ILFDT_CUDA_OK(cudaMemsetAsync(rank, 0, (size_t)b * 4, st));
+  ILFDT_CUDA_OK(cudaMemsetAsync(counts, 0, 8, st));
+  UmmaParams p{};
+  p.block_n = (int)std::min<int64_t>(256, round_up(B, 16));
+  p.n_step = p.block_n;
+  p.scale_dev = scale;
+  p.label_offset = label_offset;
+  p.diag = const_cast<float*>(diag);
+  p.rank = rank;
+  int32_t rc = launch_umma<EPI_RANK>(x, g, b, B, D, p, st);
+  if (rc != ILFDT_OK) return rc;
+  rank_hits_kernel<<<(unsigned)cdiv(b, 256), 256, 0, st>>>(rank, b, counts);
+  ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }
 

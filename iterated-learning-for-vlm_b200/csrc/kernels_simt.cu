@@ -395,6 +395,13 @@ topk_hits_kernel(const float* __restrict__ L, int64_t cols, int64_t label0, int3
     if (gt < 5) atomicAdd(counts + 1, 1);
   }
 }
+// accumulating form (counts not cleared): one row chunk of a streamed logits matrix
+int32_t launch_topk_hits_acc(const float* L, int64_t rows, int64_t B, int64_t label0, int32_t* counts, cudaStream_t st) {
+  if (rows == 0) return ILFDT_OK;
+  topk_hits_kernel<<<(unsigned)rows, 256, 0, st>>>(L, B, label0, counts);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
 int32_t launch_topk_hits(const float* L, int64_t b, int64_t B, int64_t label0, int32_t* counts, cudaStream_t st) {
   ILFDT_CUDA_OK(cudaMemsetAsync(counts, 0, 8, st));
   if (b == 0) return ILFDT_OK;

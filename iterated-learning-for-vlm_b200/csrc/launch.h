@@ -90,6 +90,10 @@ int32_t launch_nce_bwd_bf16(const void* x_img, const void* x_txt, const void* g_
                             int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset, const float* lse_i,
                             const float* lse_t, const float* grad_out, float* dx_img, float* dx_txt, float* dg_img,
                             float* dg_txt, float* dscale, void* ws, int64_t ws_bytes, cudaStream_t st);
+int32_t launch_nce_topk_bf16(const void* x, const void* g, int64_t b, int64_t B, int64_t D, const float* scale,
+                             int64_t label_offset, const float* diag, int32_t* counts, void* ws, int64_t ws_bytes,
+                             cudaStream_t st);
+int32_t launch_topk_hits_acc(const float* L, int64_t rows, int64_t B, int64_t label0, int32_t* counts, cudaStream_t st);
 int32_t launch_nce_bwd_gathered_bf16(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt,
                                      int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset,
                                      const float* lse_i_all, const float* lse_t_all, const float* go_all,

@@ -57,6 +57,7 @@ SIGNATURES = {
     "ilfdt_ce_rows_fwd": (_i32, [_p, _i64, _i64, _i64, _p, _p, _p]),
     "ilfdt_ce_rows_bwd": (_i32, [_p, _i64, _i64, _i64, _p, _p, _f, _p, _p]),
     "ilfdt_topk_hits": (_i32, [_p, _i64, _i64, _i64, _p, _p]),
+    "ilfdt_nce_topk_hits": (_i32, [_p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _p, _p, _i64, _p]),
     "ilfdt_randn_fill": (_i32, [_p, _i64, _u64, _u32, _p]),
     "ilfdt_copy": (_i32, [_p, _p, _i64, _p]),
 }

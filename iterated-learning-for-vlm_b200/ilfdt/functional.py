@@ -287,14 +287,16 @@ class InfoNCEFunction(torch.autograd.Function):
     the same sum the reference's dX + all_reduce(dG)[rank] produces."""
 
     @staticmethod
-    def forward(ctx, x_img, x_txt, g_img, g_txt, scale, label_offset, mode, gathered=False):
+    def forward(ctx, x_img, x_txt, g_img, g_txt, scale, label_offset, mode, gathered=False, keep=None):
         ts = [t.contiguous().float() for t in (x_img, x_txt, g_img, g_txt)]
         sc = scale.detach().reshape(1).float().contiguous()
         # the tensor-core kernels need 16-byte TMA row pitches: D % 8. Other shapes take the fp32 kernels
         # (still CUDA, still fused per row chunk).
         if mode == "bf16" and ts[0].shape[1] % 8 == 0 and ts[0].shape[1] <= 512:
             ts = [ops.cast_bf16(t) for t in ts]
-        loss, lse_i, lse_t, _, _ = ops.nce_fwd(ts[0], ts[1], ts[2], ts[3], sc, label_offset)
+        loss, lse_i, lse_t, diag_i, _ = ops.nce_fwd(ts[0], ts[1], ts[2], ts[3], sc, label_offset)
+        if keep is not None:   # what a later top-k count on logits_per_image needs (lazy.ContrastiveStash.topk_hits)
+            keep.update(x=ts[0], g=ts[3], scale=sc, diag=diag_i, label_offset=int(label_offset))
         ctx.save_for_backward(ts[0], ts[1], ts[2], ts[3], sc, lse_i, lse_t)
         ctx.label_offset, ctx.scale_shape, ctx.gathered = int(label_offset), scale.shape, bool(gathered)
         return loss
@@ -317,10 +319,10 @@ class InfoNCEFunction(torch.autograd.Function):
                 go_all = every[:, 2 * b].contiguous()
             dx_img, dx_txt, dscale = ops.nce_bwd_gathered(x_img, x_txt, g_img, g_txt, sc, ctx.label_offset,
                                                           lse_i_all, lse_t_all, go_all)
-            return dx_img, dx_txt, None, None, dscale.reshape(ctx.scale_shape), None, None, None
+            return dx_img, dx_txt, None, None, dscale.reshape(ctx.scale_shape), None, None, None, None
         dx_img, dx_txt, dg_img, dg_txt, dscale = ops.nce_bwd(x_img, x_txt, g_img, g_txt, sc, ctx.label_offset,
                                                              lse_i, lse_t, go)
-        return dx_img, dx_txt, dg_img, dg_txt, dscale.reshape(ctx.scale_shape), None, None, None
+        return dx_img, dx_txt, dg_img, dg_txt, dscale.reshape(ctx.scale_shape), None, None, None, None
 
 
 class CrossEntropyRowsFunction(torch.autograd.Function):

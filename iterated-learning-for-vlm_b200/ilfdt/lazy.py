@@ -23,6 +23,7 @@ class ContrastiveStash:
         # needs no [B,D] gradient exchange (functional.InfoNCEFunction)
         self.gathered = gathered
         self._mat = [None, None]
+        self._kept = {}
 
     @property
     def b(self):
@@ -47,7 +48,22 @@ class ContrastiveStash:
 
     def fused_loss(self):
         return Fn.InfoNCEFunction.apply(self.x_img, self.x_txt, self.g_img, self.g_txt, self.scale,
-                                        self.label_offset(), self.mode, self.gathered)
+                                        self.label_offset(), self.mode, self.gathered, self._kept)
+
+    def topk_hits(self):
+        """int32[2]: rows of logits_per_image whose label logit is the row max / has fewer than 5 entries above it
+        (accuracy(logits_per_image, labels, topk=(1, 5)), train_solver.py:421) -- counted by the fused kernel from
+        the embeddings; the [b,B] matrix is not formed."""
+        from . import ops
+        if self._mat[0] is not None:
+            return ops.topk_hits(self._mat[0].detach().contiguous(), self.label_offset())
+        if not self._kept:   # accuracy() before the loss: run the forward kernels for the label logits
+            with torch.no_grad():
+                Fn.InfoNCEFunction.apply(self.x_img.detach(), self.x_txt.detach(), self.g_img.detach(),
+                                         self.g_txt.detach(), self.scale.detach(), self.label_offset(), self.mode,
+                                         False, self._kept)
+        k = self._kept
+        return ops.nce_topk_hits(k["x"], k["g"], k["scale"], k["label_offset"], k["diag"])
 
 
 class LazyLogits:

@@ -24,6 +24,7 @@ class ClipInfoCELoss(_Loss):
         device = logits_per_image.device
         offset = 0 if l_bs == bs else link.get_rank() * bs
         labels = offset + torch.arange(0, bs, dtype=torch.long, device=device)
+        labels._ilfdt_label_offset = offset   # lets ilfdt.utils.accuracy recognise these labels without reading them
         if (isinstance(logits_per_image, LazyLogits) and isinstance(logits_per_text, LazyLogits)
                 and logits_per_image._stash is logits_per_text._stash
                 and logits_per_image._which == 0 and logits_per_text._which == 1):

@@ -416,6 +416,21 @@ def topk_hits(logits_f32, label_offset):
     return counts
 
 
+def nce_topk_hits(x, g, scale, label_offset, diag):
+    """(top-1 hits, top-5 hits) int32[2] of logits = scale * x . g^T against labels label_offset + row, without the
+    [b,B] matrix (prototype/utils/misc.py:464-477 as called at train_solver.py:421).
+    diag = the rows' label logits (nce_fwd's diag_i for x = x_img, g = g_txt)."""
+    _req(x, None, "x"); _req(g, x.dtype, "g"); _req(scale, torch.float32, "scale"); _req(diag, torch.float32, "diag")
+    b, D = x.shape
+    B = g.shape[0]
+    dt = _DT[x.dtype]
+    counts = torch.empty(2, dtype=torch.int32, device=x.device)
+    ws, n = _nce_ws(dt, b, B, D, x.device)
+    _call("ilfdt_nce_topk_hits", _ptr(x), _ptr(g), dt, b, B, D, _ptr(scale), int(label_offset), _ptr(diag), _ptr(counts),
+          _ptr(ws), n, _stream())
+    return counts
+
+
 def randn_fill_(t, seed, generation):
     _req(t, torch.float32, "t")
     _call("ilfdt_randn_fill", _ptr(t), t.numel(), int(seed) & (2 ** 64 - 1), int(generation) & 0xFFFFFFFF,

@@ -390,7 +390,7 @@ def _nce_oracle(x_img, x_txt, g_img, g_txt, p, offset, upstream):
 
 
 @pytest.mark.parametrize("b,B,D,offset", [(8, 8, 32, 0), (64, 64, 512, 0), (128, 512, 512, 256), (200, 1000, 512, 400),
-                                         (256, 256, 512, 0), (40, 328, 64, 288)])
+                                         (256, 256, 512, 0), (40, 328, 64, 288), (384, 1024, 512, 256)])
 @pytest.mark.parametrize("mode", ["fp32", "bf16"])
 @pytest.mark.parametrize("pval", [math.log(1 / 0.07), 5.0])
 def test_infonce(ops, b, B, D, offset, mode, pval):
@@ -430,7 +430,52 @@ def test_infonce(ops, b, B, D, offset, mode, pval):
     assert counts[1].item() == (top5 == lab.view(-1, 1)).any(1).sum().item()
 
 
-@pytest.mark.parametrize("W,b,D", [(1, 64, 512), (2, 128, 512), (4, 72, 512), (3, 40, 64), (2, 300, 256)])
+@pytest.mark.parametrize("b,B,D,offset", [(64, 64, 512, 0), (128, 512, 512, 256), (300, 1000, 512, 400), (40, 328, 64, 288),
+                                         (512, 2048, 256, 1024)])
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_fused_topk_hits_equal_stored_logits(ops, b, B, D, offset, mode):
+    """accuracy(logits_per_image, labels, topk=(1,5)) (misc.py:464-477 at train_solver.py:421) counted
+    from the embeddings by ilfdt_nce_topk_hits must give exactly the integers torch.topk gives on the stored
+    logits of the same step, and the drop-in accuracy() must use it without materialising the matrix."""
+    from ilfdt.lazy import ContrastiveStash, LazyLogits
+    from ilfdt.loss_functions import ClipInfoCELoss
+    from ilfdt.utils import accuracy
+    g = torch.Generator().manual_seed(3 * b + B)
+    g_img = torch.nn.functional.normalize(torch.randn(B, D, generator=g), dim=-1)
+    # correlated pairs with enough noise that top-1 and top-5 differ and neither is 0 or 100 %
+    cos = 3.2 / math.sqrt(D)                      # pair similarity about 3 sigma above a random distractor's
+    g_txt = torch.nn.functional.normalize(g_img + math.sqrt(1 / cos ** 2 - 1) * torch.randn(B, D, generator=g) / math.sqrt(D), dim=-1)
+    dev = _dev()
+    gi, gt = g_img.to(dev), g_txt.to(dev)
+    xi, xt = gi[offset:offset + b].clone().requires_grad_(True), gt[offset:offset + b].clone().requires_grad_(True)
+    scale = torch.full((1,), 1 / 0.07, device=dev)
+    stash = ContrastiveStash(xi, xt, gi, gt, scale, mode)
+    stash.label_offset = lambda: offset          # single process: emulate rank = offset / b
+    li, lt = LazyLogits(stash, 0), LazyLogits(stash, 1)
+    labels = offset + torch.arange(b, device=dev)
+    labels._ilfdt_label_offset = offset
+    loss = stash.fused_loss()
+    acc1, acc5 = accuracy(li, labels, topk=(1, 5))
+    assert not li.is_materialized, "accuracy() formed the [b,B] matrix"
+    stored = li.materialize().detach()
+    top5 = stored.topk(min(5, B), 1).indices
+    ref1 = (top5[:, 0] == labels).sum().item()
+    ref5 = (top5 == labels.view(-1, 1)).any(1).sum().item()
+    assert round(acc1.item() * b / 100) == ref1 and round(acc5.item() * b / 100) == ref5, (acc1, acc5, ref1, ref5)
+    assert 0 < ref5 and ref1 <= ref5 and ref1 < b, (ref1, ref5)
+    # accuracy() before the loss was computed, and the generic fallback (other k / foreign labels)
+    stash2 = ContrastiveStash(xi.detach(), xt.detach(), gi, gt, scale, mode)
+    stash2.label_offset = lambda: offset
+    c = stash2.topk_hits().cpu()
+    assert (c[0].item(), c[1].item()) == (ref1, ref5)
+    acc3 = accuracy(LazyLogits(stash2, 0), offset + torch.arange(b, device=dev), topk=(3,))[0]
+    ref3 = (stored.topk(3, 1).indices == labels.view(-1, 1)).any(1).sum().item()
+    assert round(acc3.item() * b / 100) == ref3
+    loss.backward()
+
+
+@pytest.mark.parametrize("W,b,D", [(1, 64, 512), (2, 128, 512), (4, 72, 512), (3, 40, 64), (2, 300, 256), (2, 512, 512),
+                                   (1, 640, 384)])
 @pytest.mark.parametrize("mode", ["fp32", "bf16"])
 def test_infonce_gathered_backward(ops, W, b, D, mode):
     """ilfdt_nce_bwd_gathered: W ranks emulated on one GPU. Each rank's output must equal the gradient the
