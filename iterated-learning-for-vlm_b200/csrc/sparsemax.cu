@@ -164,17 +164,20 @@ sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__
   double tau = -INFINITY;
   int cnt_prev = -1;
   for (int it = 0; it < 256; ++it) {
-    double s = 0.0;
     int c = 0;
     const float tf = (it == 0) ? -INFINITY : (float)tau;  // compare in the precision the output uses
+    // per-thread partial over its <= 32 values in fp32 (two independent chains; |error| ~ 1e-8 of a partial that is
+    // itself 1/512 of the row), everything across threads in fp64: the iteration was issue-bound on F2F + DADD
+    float s0 = 0.f, s1 = 0.f;
 #pragma unroll
     for (int j = 0; j < SPX_MAXV; ++j) {
       // padding slots hold -inf: `> tf` is false for them even at tf = -inf
-      if (v[j].x > tf) { s += (double)v[j].x; ++c; }
-      if (v[j].y > tf) { s += (double)v[j].y; ++c; }
-      if (v[j].z > tf) { s += (double)v[j].z; ++c; }
-      if (v[j].w > tf) { s += (double)v[j].w; ++c; }
+      if (v[j].x > tf) { s0 += v[j].x; ++c; }
+      if (v[j].y > tf) { s1 += v[j].y; ++c; }
+      if (v[j].z > tf) { s0 += v[j].z; ++c; }
+      if (v[j].w > tf) { s1 += v[j].w; ++c; }
     }
+    double s = (double)s0 + (double)s1;
     s = warp_sum(s);
     c = warp_sum(c);
     if (lane == 0) { red_s[it & 1][warp] = s; red_c[it & 1][warp] = c; }

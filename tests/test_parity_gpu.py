@@ -430,6 +430,54 @@ def test_infonce(ops, b, B, D, offset, mode, pval):
     assert counts[1].item() == (top5 == lab.view(-1, 1)).any(1).sum().item()
 
 
+def test_graphed_step_equals_eager(ops):
+    """ilfdt.graphs.GraphedStep: forward + backward of the hot path captured in a CUDA graph (every launch is
+    allocation- and sync-free, the ragged text path reads its extents on the device) must replay to the eager
+    results, also after new inputs are copied into the captured buffers."""
+    from ilfdt import functional as Fn
+    from ilfdt.graphs import GraphedStep
+    dev = _dev()
+    b, P, T, K, D = 96, 49, 77, 1024, 512
+    sd = torch.nn.Parameter(torch.randn(K, D, device=dev))
+    p = torch.nn.Parameter(torch.full((1,), math.log(1 / 0.07), device=dev))
+    keep = {}
+
+    def make(seed):
+        g = torch.Generator(device=dev).manual_seed(seed)
+        qi = torch.randn(b, P, D, device=dev, generator=g)
+        qt = torch.randn(b, T, D, device=dev, generator=g)
+        lens = torch.randint(5, T + 1, (b,), device=dev, generator=g)
+        mk = torch.zeros(b, T, device=dev)
+        mk[torch.arange(T, device=dev).view(1, -1) >= lens.view(-1, 1)] = float("-inf")
+        return qi, qt, mk
+
+    def step(qi, qt, mk):
+        qi = qi.detach().requires_grad_(True)
+        qt = qt.detach().requires_grad_(True)
+        sd.grad = None
+        p.grad = None
+        _, f_i = Fn.GroundingFunction.apply(qi, sd, None, 1000.0, "bf16")
+        _, f_t = Fn.GroundingFunction.apply(qt, sd, mk, 1000.0, "bf16")
+        x_i, x_t = Fn.L2NormFunction.apply(f_i, 1e-10), Fn.L2NormFunction.apply(f_t, 1e-10)
+        s = p.exp()
+        loss = Fn.InfoNCEFunction.apply(x_i, x_t, x_i, x_t, s, 0, "bf16", True)
+        loss.backward()
+        keep["dq"] = (qi.grad, qt.grad)
+        return loss
+
+    a, c = make(1), make(2)
+    gs = GraphedStep(step, tuple(t.clone() for t in a), warmup=1)
+    g_sd, g_p, g_dq = sd.grad, p.grad, keep["dq"]     # the captured step's outputs: rewritten by every replay
+    for inp in (a, c, a):
+        l_g = gs(*inp).clone()
+        got = [g_sd.clone(), g_p.clone(), g_dq[0].clone(), g_dq[1].clone()]
+        l_e = step(*inp)
+        ref = [sd.grad, p.grad, keep["dq"][0], keep["dq"][1]]
+        assert torch.equal(l_g, l_e.detach())
+        for x, y in zip(got, ref):
+            assert_close(x.float(), y.float(), 1e-5, "graph replay vs eager")    # fp32 atomics may reorder sums
+
+
 @pytest.mark.parametrize("b,B,D,offset", [(64, 64, 512, 0), (128, 512, 512, 256), (300, 1000, 512, 400), (40, 328, 64, 288),
                                          (512, 2048, 256, 1024)])
 @pytest.mark.parametrize("mode", ["fp32", "bf16"])
