@@ -213,7 +213,8 @@ def test_sparsemax_bwd_closed_form(ops):
 # ---------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("b,n_tok,K,D,masked", [(7, 9, 200, 64, True), (5, 49, 256, 512, False), (6, 77, 384, 512, True),
                                                (4, 12, 9000, 256, True), (3, 20, 20000, 256, True),
-                                               (3, 120, 512, 512, True)])
+                                               (3, 120, 512, 512, True),
+                                               (6, 196, 1024, 512, False)])   # ViT-B/16 patches (BASELINE config 5)
 @pytest.mark.parametrize("mode", ["fp32", "bf16"])
 def test_grounding_fwd_bwd(ops, b, n_tok, K, D, masked, mode):
     from ilfdt.functional import GroundingFunction
