@@ -739,20 +739,24 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const float* __restrict__ w, cons
 // q rows in flight per warp (ncu r01: the 4x4/U=2 shape ran 3.5 warps per scheduler, stalled on the row
 // gathers with neither L2 nor the issue slots saturated -- the kernel is bound by loads in flight).
 // ---------------------------------------------------------------------------------------------
-template <typename T, int NV, int WARPS, int CPW, int U>
+template <typename T, int NV, int WARPS, int CPW, int U, int TS = 32>
 __global__ void __launch_bounds__(WARPS * 32)
 ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restrict__ arg, const T* __restrict__ q,
                          const int* __restrict__ row_base, int64_t b_total, int n_tok, int K, int D,
                          int64_t b_per_split, int use_atomic, float* __restrict__ dsd) {
-  constexpr int CODES = WARPS * CPW, THREADS = WARPS * 32, QUADS = CODES / 4, SLOTS = 32 * QUADS;
+  // TS samples per cooperative tile (one CTA barrier per tile). A/B on one box: TS = 32 is ~2 ms per step faster at the
+  // dense random-init statistics (the headline), TS = 128 is 3 ms faster when the support is a few tens of codes and
+  // the kernel is a pure scan of coef / arg (ILFDT_DSD_CFG=128)
+  constexpr int SUB = TS / 32;
+  constexpr int CODES = WARPS * CPW, THREADS = WARPS * 32, QUADS = CODES / 4, SLOTS = TS * QUADS;
   constexpr int LPT = (SLOTS + THREADS - 1) / THREADS;   // (sample, 4-code quad) slots per thread per tile
-  __shared__ float cf_s[2][CODES][33];
-  __shared__ int16_t tk_s[2][CODES][34];
+  __shared__ float cf_s[2][CODES][TS + 1];
+  __shared__ int16_t tk_s[2][CODES][TS + 2];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int k0 = blockIdx.x * CODES;
   const int64_t b_begin = (int64_t)blockIdx.y * b_per_split;
   const int64_t b_end = min(b_total, b_begin + b_per_split);
-  const int nblk = (int)((b_end - b_begin + 31) / 32);
+  const int nblk = (int)((b_end - b_begin + TS - 1) / TS);
 
   float acc[CPW][NV][8];
 #pragma unroll
@@ -769,7 +773,7 @@ ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restri
     for (int l = 0; l < LPT; ++l) {
       const int slot = threadIdx.x + l * THREADS;
       const int ld_s = slot / QUADS, ld_q = (slot % QUADS) * 4;
-      const int64_t bb = b_begin + (int64_t)blk * 32 + ld_s;
+      const int64_t bb = b_begin + (int64_t)blk * TS + ld_s;
       rc[l] = make_float4(0.f, 0.f, 0.f, 0.f);
       rt[l] = make_uint2(0u, 0u);
       if (slot < SLOTS && bb < b_end) {
@@ -800,13 +804,15 @@ ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restri
   for (int blk = 0; blk < nblk; ++blk) {
     const int buf = blk & 1;
     if (blk + 1 < nblk) load_tile(blk + 1);
-    const int64_t b0 = b_begin + (int64_t)blk * 32;
+    for (int sub = 0; sub < SUB; ++sub) {
+    const int64_t b0 = b_begin + (int64_t)blk * TS + sub * 32;
+    if (b0 >= b_end) break;
     // first q row of this lane's sample: sample * n_tok, or its slab in the compacted text operand (text_buckets.cu)
     const int64_t mybase = row_base ? (b0 + lane < b_end ? (int64_t)__ldg(row_base + b0 + lane) : 0) : (b0 + lane) * n_tok;
 #pragma unroll
     for (int c = 0; c < CPW; ++c) {
-      const float cf = cf_s[buf][warp * CPW + c][lane];
-      const int t = tk_s[buf][warp * CPW + c][lane];
+      const float cf = cf_s[buf][warp * CPW + c][sub * 32 + lane];
+      const int t = tk_s[buf][warp * CPW + c][sub * 32 + lane];
       const int64_t myrow = mybase + t;
       unsigned m = __ballot_sync(0xffffffffu, cf != 0.f);
       while (m) {
@@ -847,6 +853,7 @@ ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restri
         }
       }
     }
+    }
     if (blk + 1 < nblk) store_tile(buf ^ 1);
     __syncthreads();
   }
@@ -866,7 +873,7 @@ ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restri
   }
 }
 
-template <typename T, int NV, int WARPS, int CPW, int U>
+template <typename T, int NV, int WARPS, int CPW, int U, int TS = 32>
 static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, const int* row_base, int64_t b, int64_t n_tok,
                              int64_t K, int64_t D, float* dsd, cudaStream_t st) {
   constexpr int CODES = WARPS * CPW;
@@ -875,10 +882,10 @@ static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, con
   const int64_t target = 4ll * sm_count();
   if (groups < target) nsplit = std::min<int64_t>(cdiv(target, groups), std::max<int64_t>(1, b / 256));
   nsplit = std::min<int64_t>(std::max<int64_t>(nsplit, 1), 65535);
-  int64_t per = round_up(cdiv(b, nsplit), 32);
+  int64_t per = round_up(cdiv(b, nsplit), TS);
   nsplit = cdiv(b, per);
   dim3 grid((unsigned)groups, (unsigned)nsplit);
-  ground_bwd_dsd_v3_kernel<T, NV, WARPS, CPW, U><<<grid, WARPS * 32, 0, st>>>(g, arg, q, row_base, b, (int)n_tok, (int)K,
+  ground_bwd_dsd_v3_kernel<T, NV, WARPS, CPW, U, TS><<<grid, WARPS * 32, 0, st>>>(g, arg, q, row_base, b, (int)n_tok, (int)K,
                                                                              (int)D, per, nsplit > 1 ? 1 : 0, dsd);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
@@ -955,7 +962,8 @@ static int32_t launch_ground_bwd_t(float* g, const float* w, const int16_t* arg,
           case 5: return launch_dsd_v3<T, NV, 8, 1, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
           case 7: return launch_dsd_v3<T, NV, 4, 2, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
           case 14: return launch_dsd_v3<T, NV, 8, 1, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
-          default: return launch_dsd_v3<T, NV, 4, 1, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
+          case 128: return launch_dsd_v3<T, NV, 4, 1, 4, 128>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
+          default: return launch_dsd_v3<T, NV, 4, 1, 4, 32>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
         }
       } else {
         return launch_dsd_v3<T, NV, 4, 1, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
