@@ -258,9 +258,11 @@ def run_ours(args):
     sync()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     e0.record()
-    for _ in range(args.steps):
+    for i in range(args.steps):
         loss = run_step()
+        marks[i].record()
     e1.record()
     t_host = time.perf_counter()
     sync()
@@ -269,6 +271,7 @@ def run_ours(args):
     host_ms_per_step = (t_host - t0) * 1e3 / args.steps
     launches = launches_per_step * args.steps
     ms = e0.elapsed_time(e1)
+    per_step = [(e0 if i == 0 else marks[i - 1]).elapsed_time(marks[i]) for i in range(args.steps)]
     if world > 1:
         tms = torch.tensor([ms], device=dev)
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
@@ -431,6 +434,7 @@ def run_ours(args):
                 "vs_baseline": None, "dtype": args.mode, "data": "synthetic", "config": workload_config(args),
                 "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk,
                 "loss": loss_val, "kernel_ms_per_step": kernel_ms, "cuda_graph": graph_note, "secondary": secondary,
+                "step_ms_spread": {"min": min(per_step), "median": statistics.median(per_step), "max": max(per_step)},
                 "host_issue_ms_per_step": host_ms_per_step}
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -136,3 +136,14 @@ class LazyLogits:
     def __repr__(self):
         return "LazyLogits(which=%d, shape=%s, materialized=%s)" % (self._which, tuple(self.shape),
                                                                    self.is_materialized)
+
+
+def contrastive_logits(x_img, x_txt, g_img, g_txt, scale, mode=None, gathered=False):
+    """(logits_per_image, logits_per_text) = (scale * x_img @ g_txt.T, scale * x_txt @ g_img.T) as LazyLogits.
+
+    The building block for heads that form several logits pairs from one set of embeddings -- DeCLIP-FDT's eight
+    logits are four such pairs (two image views x masked / augmented captions, prototype/model/declip_fdt.py:389-399):
+    each pair handed to ClipInfoCELoss runs the fused kernels, none of the [b,B] matrices is stored.
+    gathered=True states that g_* are AllGather(x_*) of this step (see ContrastiveStash)."""
+    stash = ContrastiveStash(x_img, x_txt, g_img, g_txt, scale, mode or Fn.get_compute_dtype(), gathered)
+    return LazyLogits(stash, 0), LazyLogits(stash, 1)

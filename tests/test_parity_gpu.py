@@ -523,6 +523,62 @@ def test_fused_topk_hits_equal_stored_logits(ops, b, B, D, offset, mode):
     loss.backward()
 
 
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_declip_style_eight_logits(ops, mode):
+    """DeCLIP-FDT's head (prototype/model/declip_fdt.py:389-399) forms eight logits matrices from two
+    image views and two caption views. Built from ilfdt.lazy.contrastive_logits + ClipInfoCELoss they must give the
+    loss and gradients of the dense formulation, without storing a [b,B] matrix."""
+    from ilfdt.lazy import contrastive_logits
+    from ilfdt.loss_functions import ClipInfoCELoss
+    b, D = 192, 512
+    g = torch.Generator().manual_seed(11)
+    base = torch.randn(b, D, generator=g)
+    views = [torch.nn.functional.normalize(base + 0.5 * torch.randn(b, D, generator=g), dim=-1) for _ in range(4)]
+    if mode == "bf16":
+        views = [bf16_round(v) for v in views]
+    p = torch.full((1,), math.log(1 / 0.07))
+
+    def dense(vs, pp):
+        i1, i2, tm, ta = vs
+        s = pp.exp()
+        lab = torch.arange(b)
+        tot = 0
+        for im in (i1, i2):
+            for tx in (tm, ta):
+                li, lt = s * im @ tx.t(), s * tx @ im.t()
+                tot = tot + (torch.nn.functional.cross_entropy(li, lab) + torch.nn.functional.cross_entropy(lt, lab)) / 2
+        return tot / 4
+
+    ref_v = [v.double().requires_grad_(True) for v in views]
+    ref_p = p.double().requires_grad_(True)
+    ref = dense(ref_v, ref_p)
+    ref.backward()
+
+    dev = _dev()
+    vs = [v.to(dev).requires_grad_(True) for v in views]
+    pd = p.to(dev).requires_grad_(True)
+    s = pd.exp()
+    crit = ClipInfoCELoss()
+    tot, lazies = 0, []
+    for im in vs[:2]:
+        for tx in vs[2:]:
+            li, lt = contrastive_logits(im, tx, im, tx, s, mode)
+            lazies += [li, lt]
+            loss, labels = crit(li, lt)
+            assert torch.equal(labels.cpu(), torch.arange(b))
+            tot = tot + loss
+    tot = tot / 4
+    tot.backward()
+    assert not any(l.is_materialized for l in lazies)
+    tol = FP32_TOL if mode == "fp32" else BF16_TOL
+    assert_close(tot, ref.float(), tol, "loss")
+    for i, (v, r) in enumerate(zip(vs, ref_v)):
+        # every view's gradient is the sum of eight (softmax - onehot) products that largely cancel: fp32 rounding of
+        # the partial sums shows at the 1e-4 level against the fp64 arbiter (the same bound as the golden gradients)
+        assert_close(v.grad, r.grad.float(), tol * (10 if mode == "fp32" else 1), "d view %d" % i)
+    assert_close(pd.grad, ref_p.grad.float(), tol * (10 if mode == "fp32" else 1), "d logit_scale")
+
+
 @pytest.mark.parametrize("W,b,D", [(1, 64, 512), (2, 128, 512), (4, 72, 512), (3, 40, 64), (2, 300, 256), (2, 512, 512),
                                    (1, 640, 384)])
 @pytest.mark.parametrize("mode", ["fp32", "bf16"])
