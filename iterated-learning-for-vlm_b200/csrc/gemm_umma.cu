@@ -479,6 +479,8 @@ static int32_t launch_umma(const void* A, const void* B, int64_t M, int64_t N, i
 int32_t launch_gemm_nt_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha,
                             const float* alpha_dev, int accumulate, float* out, int64_t ldo, cudaStream_t st) {
   if (M == 0 || N == 0) return ILFDT_OK;
+  if (alpha_dev == nullptr && gemm_wide2_enabled() && gemm_wide2_supported(M, N, Kr, out, ldo))
+    return launch_gemm_wide2(A, B, M, N, Kr, alpha, accumulate, out, ldo, st);   // short A, long reduction: CTA pair
   UmmaParams p{};
   p.block_n = (int)std::min<int64_t>(256, round_up(N, 16));
   p.n_step = p.block_n;

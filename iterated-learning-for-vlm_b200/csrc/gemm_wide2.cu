@@ -1,0 +1,230 @@
+// a3 on a CTA pair: out[n, m] (+)= alpha * sum_k B[n,k] A[m,k] for a SHORT A (M <= 512 rows) and a long reduction --
+// the pooling f[b, D] = w[b, K] . sd[K, D] (clip_fdt.py:154; A = sd^T [D, K], B = w [b, K], Kr = K = 16384).
+//
+// Why: nothing of this product can stay resident (the reduction is 16384 long), so the single-CTA kernel streams
+// 48 KB per 128x256x64 block of MACs -- 24 TB/s over the whole chip at the tensor rate, twice what L2 delivers; it ran
+// at a third of the tensor peak. Here the lanes are the rows of B (256 per CTA pair, 128 per CTA) and ALL of A's rows
+// are the columns of up to two 256-column accumulators, so one 16 KB box of B rows per CTA is multiplied against the
+// whole of A, and the pair's tcgen05.mma.cta_group::2 lets each CTA stage only half of A's rows:
+// 48 KB per CTA per 128x512x64 block of MACs, half the bytes per FLOP.
+//
+// Protocol as in ground_umma2.cu (leader = CTA rank 0): producers of both CTAs load into their own smem with the
+// transaction bytes on the leader's full[stage]; the leader issues the MMAs and multicasts commits; the epilogue warps
+// of each CTA drain their own TMEM lanes (group g = accumulator g) and arrive on the leader's tmem_empty.
+#include <algorithm>
+#include <cstdlib>
+#include "umma_pair.cuh"
+#include "launch.h"
+
+namespace ilfdt {
+
+using namespace umma;
+
+constexpr int W2_THREADS = 320;
+constexpr int W2_BOX = 128 * 64 * 2;            // 16 KB: 128 rows x 64 k
+constexpr int W2_STAGE = 3 * W2_BOX;            // this CTA's B rows + its half of A's rows for each accumulator: 48 KB
+constexpr int W2_STAGES = 4;
+constexpr int W2_DATA_BYTES = W2_STAGES * W2_STAGE;   // 192 KB
+constexpr int W2_SMEM_BYTES = W2_DATA_BYTES + 1024 + 256;
+
+struct W2Params {
+  int n_rows, m_rows, nkb;      // lanes = rows of B (n), columns = rows of A (m)
+  int num_pairs;                // ceil(n_rows / 256)
+  int nacc;                     // accumulators in use: ceil(m_rows / 256)
+  int acc_n[2];                 // UMMA N of each accumulator (multiple of 16)
+  float alpha;
+  int accumulate;
+  float* out;
+  long long ldo;
+  uint32_t idesc[2];
+};
+
+struct W2Bars {
+  uint64_t full[W2_STAGES], empty[W2_STAGES], tmem_full, tmem_empty;
+  uint32_t tmem_ptr;
+};
+
+__global__ void __launch_bounds__(W2_THREADS, 1)
+gemm_wide2_kernel(const __grid_constant__ CUtensorMap tmLane, const __grid_constant__ CUtensorMap tmCol, const W2Params p) {
+  extern __shared__ uint8_t w2_smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(w2_smem_raw) + 1023) & ~(uintptr_t)1023);
+  W2Bars* bars = reinterpret_cast<W2Bars*>(smem + W2_DATA_BYTES);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < W2_STAGES; ++i) { mbar_init(&bars->full[i], 1); mbar_init(&bars->empty[i], 1); }
+    mbar_init(&bars->tmem_full, 1);
+    mbar_init(&bars->tmem_empty, 16);   // 8 epilogue warps in each CTA
+    fence_barrier_init();
+    tma_prefetch_desc(&tmLane);
+    tma_prefetch_desc(&tmCol);
+  }
+  if (warp == 1) {
+    tmem_alloc_pair(&bars->tmem_ptr, 512);
+    tmem_relinquish_pair();
+  }
+  fence_before_sync();
+  cluster_sync_all();
+  fence_after_sync();
+  const uint32_t tmem_base = bars->tmem_ptr;
+  const uint32_t stage_tx = 2u * (uint32_t)(1 + p.nacc) * W2_BOX;   // both CTAs: lane box + one A box per accumulator
+
+  if (warp == 0) {
+    // ===================== TMA producer (one thread in each CTA) =====================
+    if (elect_one()) {
+      uint32_t stage = 0, phase = 0;
+      for (int item = cluster_id; item < p.num_pairs; item += num_clusters) {
+        const int lane_row0 = (2 * item + (int)rank) * 128;
+        for (int kb = 0; kb < p.nkb; ++kb) {
+          mbar_wait(&bars->empty[stage], phase ^ 1);
+          if (leader) mbar_expect_tx(&bars->full[stage], stage_tx);
+          uint8_t* st = smem + stage * W2_STAGE;
+          tma_load_2d_pair(st, &tmLane, &bars->full[stage], kb * 64, lane_row0, kEvictFirst);
+          for (int a = 0; a < p.nacc; ++a)   // this CTA's half of accumulator a's columns (rows of A)
+            tma_load_2d_pair(st + (1 + a) * W2_BOX, &tmCol, &bars->full[stage], kb * 64,
+                             a * 256 + (int)rank * (p.acc_n[a] >> 1), kEvictLast);
+          if (++stage == W2_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (leader && elect_one()) {
+      uint32_t stage = 0, phase = 0, it = 0;
+      for (int item = cluster_id; item < p.num_pairs; item += num_clusters, ++it) {
+        mbar_wait(&bars->tmem_empty, (it & 1) ^ 1);   // both CTAs' epilogues of the previous item are done
+        fence_after_sync();
+        for (int kb = 0; kb < p.nkb; ++kb) {
+          mbar_wait(&bars->full[stage], phase);
+          fence_after_sync();
+          const uint8_t* st = smem + stage * W2_STAGE;
+          const uint64_t adesc = make_smem_desc_sw128(smem_u32(st));
+          for (int a = 0; a < p.nacc; ++a) {
+            const uint64_t bdesc = make_smem_desc_sw128(smem_u32(st + (1 + a) * W2_BOX));
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4)
+              mma_f16_pair(tmem_base + a * 256, advance_desc_k(adesc, k4 * 32), advance_desc_k(bdesc, k4 * 32),
+                           p.idesc[a], (kb | k4) != 0 ? 1u : 0u);
+          }
+          mma_commit_pair(&bars->empty[stage]);
+          if (++stage == W2_STAGES) { stage = 0; phase ^= 1; }
+        }
+        mma_commit_pair(&bars->tmem_full);
+      }
+    }
+  } else {
+    // ===================== epilogue warps (2..9) of both CTAs: group g stores accumulator g =====================
+    const int quad = warp & 3;
+    const int group = (warp - 2) >> 2;
+    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    uint32_t it = 0;
+    for (int item = cluster_id; item < p.num_pairs; item += num_clusters, ++it) {
+      const int row = (2 * item + (int)rank) * 128 + quad * 32 + lane;   // row of B = row of out owned by this thread
+      const bool row_ok = row < p.n_rows;
+      mbar_wait(&bars->tmem_full, it & 1);
+      fence_after_sync();
+      if (group < p.nacc) {
+        const int ncols = min(256, p.m_rows - group * 256);
+        float* o = p.out + (int64_t)row * p.ldo + group * 256;
+        for (int c0 = 0; c0 < ncols; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld32(tmem_base + lane_addr + group * 256 + c0, v);
+          tmem_ld_wait();
+          if (row_ok) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              if (c0 + j + 3 < ncols) {
+                float4 r = make_float4(__uint_as_float(v[j]) * p.alpha, __uint_as_float(v[j + 1]) * p.alpha,
+                                       __uint_as_float(v[j + 2]) * p.alpha, __uint_as_float(v[j + 3]) * p.alpha);
+                float4* dst = reinterpret_cast<float4*>(o + c0 + j);
+                if (p.accumulate) { const float4 q = *dst; r.x += q.x; r.y += q.y; r.z += q.z; r.w += q.w; }
+                *dst = r;
+              } else {
+                for (int e = 0; e < 4; ++e)
+                  if (c0 + j + e < ncols) {
+                    const float r = __uint_as_float(v[j + e]) * p.alpha;
+                    o[c0 + j + e] = p.accumulate ? o[c0 + j + e] + r : r;
+                  }
+              }
+            }
+          }
+        }
+      }
+      fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&bars->tmem_empty, 0);
+    }
+  }
+
+  fence_before_sync();
+  cluster_sync_all();
+  if (warp == 1) {
+    fence_after_sync();
+    tmem_dealloc_pair(tmem_base, 512);
+  }
+}
+
+bool gemm_wide2_enabled() {
+  static const int on = getenv("ILFDT_GEMM_WIDE") ? atoi(getenv("ILFDT_GEMM_WIDE")) : 1;
+  return on != 0;
+}
+// shapes the pair kernel takes: a short A (all of its rows fit two accumulators), many B rows, a long reduction
+bool gemm_wide2_supported(int64_t M, int64_t N, int64_t Kr, const float* out, int64_t ldo) {
+  return M >= 16 && M <= 512 && M % 16 == 0 && (M <= 256 || M % 32 == 0) && N >= 1024 && Kr >= 1024 && Kr % 8 == 0 &&
+         ldo % 4 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+}
+
+// out[n, m] (+)= alpha * sum_k B[n,k] A[m,k]; A [M, Kr], B [N, Kr] bf16 row-major
+int32_t launch_gemm_wide2(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha, int accumulate,
+                          float* out, int64_t ldo, cudaStream_t st) {
+  W2Params p{};
+  p.n_rows = (int)N;
+  p.m_rows = (int)M;
+  p.nkb = (int)cdiv(Kr, 64);
+  p.num_pairs = (int)cdiv(N, 256);
+  p.nacc = (int)cdiv(M, 256);
+  for (int a = 0; a < p.nacc; ++a) {
+    p.acc_n[a] = (int)round_up(std::min<int64_t>(256, M - a * 256), 32);   // halves stay multiples of 16 rows
+    p.idesc[a] = make_idesc_bf16(256, p.acc_n[a]);
+  }
+  p.alpha = alpha;
+  p.accumulate = accumulate;
+  p.out = out;
+  p.ldo = ldo;
+  CUtensorMap tmLane, tmCol;
+  int32_t rc = make_tmap_bf16(&tmLane, B, N, Kr, Kr, 128);
+  if (rc != ILFDT_OK) return rc;
+  if ((rc = make_tmap_bf16(&tmCol, A, M, Kr, Kr, 128)) != ILFDT_OK) return rc;
+  static thread_local int configured_dev = -1;
+  static thread_local int max_clusters = 0;
+  int dev = 0;
+  ILFDT_CUDA_OK(cudaGetDevice(&dev));
+  cudaLaunchConfig_t cfg{};
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.blockDim = dim3(W2_THREADS);
+  cfg.dynamicSmemBytes = W2_SMEM_BYTES;
+  cfg.stream = st;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (configured_dev != dev) {
+    ILFDT_CUDA_OK(cudaFuncSetAttribute(gemm_wide2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W2_SMEM_BYTES));
+    cfg.gridDim = dim3(2 * (sm_count() / 2));
+    int n = 0;
+    ILFDT_CUDA_OK(cudaOccupancyMaxActiveClusters(&n, gemm_wide2_kernel, &cfg));
+    ILFDT_REQUIRE(n >= 1, ILFDT_E_CUDA, "gemm_wide2: no CTA pair can be resident");
+    max_clusters = std::min(n, sm_count() / 2);
+    configured_dev = dev;
+  }
+  cfg.gridDim = dim3(2 * std::min(p.num_pairs, max_clusters));
+  ILFDT_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_wide2_kernel, tmLane, tmCol, p));
+  return ILFDT_OK;
+}
+
+}  // namespace ilfdt

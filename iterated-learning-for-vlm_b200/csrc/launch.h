@@ -90,6 +90,11 @@ int32_t launch_nce_bwd_bf16(const void* x_img, const void* x_txt, const void* g_
                             int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset, const float* lse_i,
                             const float* lse_t, const float* grad_out, float* dx_img, float* dx_txt, float* dg_img,
                             float* dg_txt, float* dscale, void* ws, int64_t ws_bytes, cudaStream_t st);
+// gemm_wide2.cu
+bool gemm_wide2_enabled();
+bool gemm_wide2_supported(int64_t M, int64_t N, int64_t Kr, const float* out, int64_t ldo);
+int32_t launch_gemm_wide2(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha, int accumulate,
+                          float* out, int64_t ldo, cudaStream_t st);
 int32_t launch_nce_topk_bf16(const void* x, const void* g, int64_t b, int64_t B, int64_t D, const float* scale,
                              int64_t label_offset, const float* diag, int32_t* counts, void* ws, int64_t ws_bytes,
                              cudaStream_t st);

@@ -65,6 +65,7 @@ def test_gemm_f32_strided(ops, M, N, K, a_t, b_t):
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 64, 64), (128, 256, 512), (256, 300, 512), (200, 77, 128), (512, 1000, 1024),
+                                   (512, 2048, 4096), (256, 1500, 2048), (64, 1024, 1032), (384, 1100, 16384),   # CTA-pair route
                                    (128, 16, 8), (384, 2050, 16384)])
 def test_gemm_nt_tcgen05(ops, M, N, K):
     g = torch.Generator().manual_seed(M + N + K)
