@@ -19,3 +19,8 @@ print("route wide=%s" % os.environ.get("ILFDT_GEMM_WIDE", "1"))
 print("pool  f = w.sd     [b,K]x[K,D]: %.3f ms  (%.0f TFLOP/s)" % ((tp := t(lambda: ops.gemm_nt(sd_kt, w_b))), 2 * b * K * D / tp / 1e9))
 print("g = df.sd^T        [b,D]x[D,K]: %.3f ms  (writes %.1f GB)" % (t(lambda: ops.gemm_nt(sd_k, df_b)), b * K * 4 / 1e9))
 print("dsd += w^T.df      gemm_tn    : %.3f ms" % t(lambda: ops.gemm_tn(df_b, w_b)))
+buf = torch.empty(b, K, device=dev)
+tf = t(lambda: buf.fill_(1.0))
+print("torch fill of [b,K] fp32 (2.1 GB): %.3f ms = %.2f TB/s" % (tf, b * K * 4 / tf / 1e9))
+src = torch.empty(b, K // 2, device=dev)
+tc = t(lambda: buf[:, :K // 2].copy_(src))
