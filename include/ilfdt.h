@@ -97,7 +97,8 @@ int32_t ilfdt_ground_fwd_text(const void* q_compact_bf16, const void* sd_bf16, c
                               int16_t* arg, void* stream);
 
 /* z [rows, K] -> w [rows, K] (simplex projection of each row), tau[rows], nnz[rows];
- * w_bf16 (optional, may be NULL) receives a bf16 copy of w for the pooling GEMM. */
+ * w_bf16 (optional, may be NULL) receives a bf16 copy of w for the pooling GEMM; w itself may be NULL
+ * when w_bf16 is given (the caller keeps only the bf16 copy, see ilfdt_ground_bwd_w16). */
 int32_t ilfdt_sparsemax_fwd(const float* z, int64_t rows, int64_t K, float* w, void* w_bf16,
                             float* tau, int32_t* nnz, void* stream);
 /* dz = nz * (g - mean_nz(g)),  nz = (w > 0): the gradient autograd derives through sort/cumsum. */
@@ -137,6 +138,14 @@ int32_t ilfdt_ground_bwd(float* g, const float* w, const int16_t* arg, const voi
                          int32_t dtype, const float* mask, const int32_t* q_row_base, int64_t b, int64_t n_tok,
                          int64_t K, int64_t D, float sqrt_d, float temperature,
                          void* dq, int32_t dq_dtype, float* dsd, void* stream);
+/* Same, with the support taken from the bf16 copy of the weights that ilfdt_sparsemax_fwd writes for the
+ * tensor-core pooling GEMM (w_bf16 [b,K], > 0 exactly where the fp32 weights are): half the bytes read, and
+ * a caller that discards att_weight (Clip_FDT.forward, clip_fdt.py:233-234) need not have the fp32 copy
+ * written at all. Needs D in {256,512,768,1024}, n_tok <= 96, K % 4 == 0 (ILFDT_E_UNSUPPORTED_SHAPE otherwise). */
+int32_t ilfdt_ground_bwd_w16(float* g, const void* w_bf16, const int16_t* arg, const void* q, const void* sd,
+                             int32_t dtype, const float* mask, const int32_t* q_row_base, int64_t b, int64_t n_tok,
+                             int64_t K, int64_t D, float sqrt_d, float temperature,
+                             void* dq, int32_t dq_dtype, float* dsd, void* stream);
 
 /* ---- non-default Query_model variants, clip_fdt.py:67-78,140-157 ----------------------------------- */
 enum { ILFDT_ATT_SOFTMAX = 1, ILFDT_ATT_SIGMOID = 2 };

@@ -234,7 +234,8 @@ int32_t ilfdt_ground_fwd_text(const void* q_compact_bf16, const void* sd_bf16, c
 int32_t ilfdt_sparsemax_fwd(const float* z, int64_t rows, int64_t K, float* w, void* w_bf16, float* tau,
                             int32_t* nnz, void* stream) {
   ARCH_GUARD();
-  ILFDT_REQUIRE(rows >= 0 && K >= 1 && (rows == 0 || (z && w)), ILFDT_E_INVALID_ARG, "sparsemax_fwd: bad arguments");
+  ILFDT_REQUIRE(rows >= 0 && K >= 1 && (rows == 0 || (z && (w || w_bf16))), ILFDT_E_INVALID_ARG,
+                "sparsemax_fwd: bad arguments");
   return launch_sparsemax_fwd(z, rows, K, w, w_bf16, tau, nnz, ST(stream));
 }
 
@@ -282,8 +283,22 @@ int32_t ilfdt_ground_bwd(float* g, const float* w, const int16_t* arg, const voi
   DTYPE_GUARD(dq_dtype);
   ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && K >= 1 && D >= 1, ILFDT_E_INVALID_ARG, "ground_bwd: bad shape");
   ILFDT_REQUIRE(b == 0 || (g && arg && q && sd && dq && dsd), ILFDT_E_INVALID_ARG, "ground_bwd: null pointer");
-  return launch_ground_bwd(g, w, arg, q, sd, dtype, mask, q_row_base, b, n_tok, K, D, sqrt_d, temperature, dq, dq_dtype,
-                           dsd, ST(stream));
+  return launch_ground_bwd(g, w, ILFDT_F32, arg, q, sd, dtype, mask, q_row_base, b, n_tok, K, D, sqrt_d, temperature, dq,
+                           dq_dtype, dsd, ST(stream));
+}
+
+int32_t ilfdt_ground_bwd_w16(float* g, const void* w_bf16, const int16_t* arg, const void* q, const void* sd,
+                             int32_t dtype, const float* mask, const int32_t* q_row_base, int64_t b, int64_t n_tok,
+                             int64_t K, int64_t D, float sqrt_d, float temperature, void* dq, int32_t dq_dtype,
+                             float* dsd, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(dtype);
+  DTYPE_GUARD(dq_dtype);
+  ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && K >= 1 && D >= 1, ILFDT_E_INVALID_ARG, "ground_bwd_w16: bad shape");
+  ILFDT_REQUIRE(b == 0 || (g && w_bf16 && arg && q && sd && dq && dsd), ILFDT_E_INVALID_ARG,
+                "ground_bwd_w16: null pointer");
+  return launch_ground_bwd(g, w_bf16, ILFDT_BF16, arg, q, sd, dtype, mask, q_row_base, b, n_tok, K, D, sqrt_d, temperature,
+                           dq, dq_dtype, dsd, ST(stream));
 }
 
 int32_t ilfdt_att_fwd(const float* z, int64_t rows, int64_t K, int32_t kind, float* w, float* rowsum, void* stream) {

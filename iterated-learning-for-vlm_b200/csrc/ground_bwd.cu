@@ -530,9 +530,27 @@ struct StoreRow8<__nv_bfloat16> {
   }
 };
 
-template <typename T, int NV, typename TO>
+// support bits of four consecutive sparsemax weights (bit i: w[i] > 0). TW = float: the fp32 att_weight;
+// TW = bf16: the tensor-core operand copy the forward keeps anyway (weights are >= 0 and bf16 has fp32's
+// exponent range, so w > 0 survives the rounding) -- half the bytes, and the fp32 copy need not exist.
+template <typename TW> struct Support4;
+template <> struct Support4<float> {
+  static __device__ __forceinline__ uint32_t ld(const float* p) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(p));
+    return (v.x > 0.f ? 1u : 0u) | (v.y > 0.f ? 2u : 0u) | (v.z > 0.f ? 4u : 0u) | (v.w > 0.f ? 8u : 0u);
+  }
+};
+template <> struct Support4<__nv_bfloat16> {
+  static __device__ __forceinline__ uint32_t pos(uint32_t h) { return (h & 0x8000u) == 0u && (h & 0x7fffu) != 0u; }
+  static __device__ __forceinline__ uint32_t ld(const __nv_bfloat16* p) {
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+    return pos(v.x & 0xffffu) | (pos(v.x >> 16) << 1) | (pos(v.y & 0xffffu) << 2) | (pos(v.y >> 16) << 3);
+  }
+};
+
+template <typename T, int NV, typename TO, typename TW>
 __global__ void __launch_bounds__(G3_THREADS, 3)
-ground_bwd_dq_v3_kernel(float* __restrict__ g, const float* __restrict__ w, const int16_t* __restrict__ arg,
+ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const int16_t* __restrict__ arg,
                         const T* __restrict__ sd, const float* __restrict__ mask, int n_tok, int K, int D,
                         float inv_scale, TO* __restrict__ dq) {
   extern __shared__ __align__(16) unsigned char gb_smem[];
@@ -546,7 +564,7 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const float* __restrict__ w, cons
   const int64_t b = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   float* gr = g + b * K;
-  const float* wr = w ? w + b * K : nullptr;
+  const TW* wr = w ? w + b * K : nullptr;
   const int16_t* ar = arg + b * K;
 
   for (int t = tid; t < n_tok; t += G3_THREADS) keep_s[t] = (mask == nullptr || mask[b * n_tok + t] == 0.f) ? 1.f : 0.f;
@@ -556,12 +574,12 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const float* __restrict__ w, cons
   int c = 0;
   if (wr != nullptr) {
     for (int i = tid * 4; i < K; i += G3_THREADS * 4) {
-      const float4 wv = __ldg(reinterpret_cast<const float4*>(wr + i));
+      const uint32_t m = Support4<TW>::ld(wr + i);
       const float4 gv = *reinterpret_cast<const float4*>(gr + i);
-      if (wv.x > 0.f) { s += (double)gv.x; ++c; }
-      if (wv.y > 0.f) { s += (double)gv.y; ++c; }
-      if (wv.z > 0.f) { s += (double)gv.z; ++c; }
-      if (wv.w > 0.f) { s += (double)gv.w; ++c; }
+      if (m & 1u) { s += (double)gv.x; ++c; }
+      if (m & 2u) { s += (double)gv.y; ++c; }
+      if (m & 4u) { s += (double)gv.z; ++c; }
+      if (m & 8u) { s += (double)gv.w; ++c; }
     }
   }
   s = warp_sum(s);
@@ -592,16 +610,16 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const float* __restrict__ w, cons
       const int k = k0 + kk;
       uint32_t lv = 0u, tkp = 0u;
       if (k < K) {
-        float4 wv = make_float4(1.f, 1.f, 1.f, 1.f);
-        if (wr != nullptr) wv = __ldg(reinterpret_cast<const float4*>(wr + k));
+        uint32_t m = 0xfu;
+        if (wr != nullptr) m = Support4<TW>::ld(wr + k);
         const float4 gv = *reinterpret_cast<const float4*>(gr + k);
         const uint2 av = __ldg(reinterpret_cast<const uint2*>(ar + k));
         const int t0 = av.x & 0xffff, t1 = av.x >> 16, t2 = av.y & 0xffff, t3 = av.y >> 16;
         float4 cf;
-        cf.x = wv.x > 0.f ? (gv.x - mean) * keep_s[t0] * inv_scale : 0.f;
-        cf.y = wv.y > 0.f ? (gv.y - mean) * keep_s[t1] * inv_scale : 0.f;
-        cf.z = wv.z > 0.f ? (gv.z - mean) * keep_s[t2] * inv_scale : 0.f;
-        cf.w = wv.w > 0.f ? (gv.w - mean) * keep_s[t3] * inv_scale : 0.f;
+        cf.x = (m & 1u) ? (gv.x - mean) * keep_s[t0] * inv_scale : 0.f;
+        cf.y = (m & 2u) ? (gv.y - mean) * keep_s[t1] * inv_scale : 0.f;
+        cf.z = (m & 4u) ? (gv.z - mean) * keep_s[t2] * inv_scale : 0.f;
+        cf.w = (m & 8u) ? (gv.w - mean) * keep_s[t3] * inv_scale : 0.f;
         *reinterpret_cast<float4*>(gr + k) = cf;   // g now holds coef for kernel 2
         tkp = (uint32_t)t0 | ((uint32_t)t1 << 8) | ((uint32_t)t2 << 16) | ((uint32_t)t3 << 24);
         if (cf.x != 0.f) { lv |= 1u; hist[t0 * G3_THREADS + tid] += 1; }
@@ -891,41 +909,53 @@ static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, con
   return ILFDT_OK;
 }
 
-template <typename T, int NV, typename TO>
-static int32_t launch_dq_v3(float* g, const float* w, const int16_t* arg, const T* sd, const float* mask, int64_t b,
+template <typename T, int NV, typename TO, typename TW>
+static int32_t launch_dq_v3(float* g, const TW* w, const int16_t* arg, const T* sd, const float* mask, int64_t b,
                             int64_t n_tok, int64_t K, int64_t D, float inv_scale, TO* dq, cudaStream_t st) {
   const size_t smem = (size_t)n_tok * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 + (G3_MAX_TOK + 1) * sizeof(int) +
                       G3_MAX_TOK * sizeof(float);
-  ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_v3_kernel<T, NV, TO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_v3_kernel<T, NV, TO, TW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)((size_t)G3_MAX_TOK * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 +
                                            (G3_MAX_TOK + 1) * sizeof(int) + G3_MAX_TOK * sizeof(float))));
-  ground_bwd_dq_v3_kernel<T, NV, TO><<<(unsigned)b, G3_THREADS, smem, st>>>(g, w, arg, sd, mask, (int)n_tok, (int)K,
+  ground_bwd_dq_v3_kernel<T, NV, TO, TW><<<(unsigned)b, G3_THREADS, smem, st>>>(g, w, arg, sd, mask, (int)n_tok, (int)K,
                                                                            (int)D, inv_scale, dq);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }
 
 template <typename T, int NV>
-static int32_t launch_ground_bwd_t(float* g, const float* w, const int16_t* arg, const T* q, const T* sd,
+static int32_t launch_ground_bwd_t(float* g, const void* w_v, int w_dtype, const int16_t* arg, const T* q, const T* sd,
                                    const float* mask, const int* row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D,
                                    float inv_scale, void* dq_v, int dq_dtype, float* dsd, cudaStream_t st) {
   bool done = false;
   float* dq = reinterpret_cast<float*>(dq_v);
+  // the support comes from the fp32 weights or (scatter kernel v3 only) from their bf16 copy
+  const float* w = w_dtype == ILFDT_F32 ? reinterpret_cast<const float*>(w_v) : nullptr;
+  const __nv_bfloat16* w16 = w_dtype == ILFDT_BF16 ? reinterpret_cast<const __nv_bfloat16*>(w_v) : nullptr;
   static const int skip = getenv("ILFDT_GBWD_SKIP") ? atoi(getenv("ILFDT_GBWD_SKIP")) : 0;  // tuning only: 1 = no dq, 2 = no dsd
   if (skip == 1) done = true;
   if constexpr (NV > 0) {
     const bool v3_ok = n_tok <= G3_MAX_TOK && K % 4 == 0 &&
                        ((reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(w)) & 15) == 0 &&
-                       (reinterpret_cast<uintptr_t>(arg) & 7) == 0;
+                       ((reinterpret_cast<uintptr_t>(arg) | reinterpret_cast<uintptr_t>(w16)) & 7) == 0;
     if (v3_ok && !done) {
-      int32_t rc = dq_dtype == ILFDT_BF16
-                       ? launch_dq_v3<T, NV, __nv_bfloat16>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale,
-                                                            reinterpret_cast<__nv_bfloat16*>(dq_v), st)
-                       : launch_dq_v3<T, NV, float>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, st);
+      int32_t rc;
+      if (w16 != nullptr)
+        rc = dq_dtype == ILFDT_BF16
+                 ? launch_dq_v3<T, NV, __nv_bfloat16, __nv_bfloat16>(g, w16, arg, sd, mask, b, n_tok, K, D, inv_scale,
+                                                                     reinterpret_cast<__nv_bfloat16*>(dq_v), st)
+                 : launch_dq_v3<T, NV, float, __nv_bfloat16>(g, w16, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, st);
+      else
+        rc = dq_dtype == ILFDT_BF16
+                 ? launch_dq_v3<T, NV, __nv_bfloat16, float>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale,
+                                                             reinterpret_cast<__nv_bfloat16*>(dq_v), st)
+                 : launch_dq_v3<T, NV, float, float>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, st);
       if (rc != ILFDT_OK) return rc;
       done = true;
     }
   }
+  ILFDT_REQUIRE(done || w16 == nullptr, ILFDT_E_UNSUPPORTED_SHAPE,
+                "ground_bwd: bf16 weights need D in {256,512,768,1024}, n_tok <= %d, K %% 4 == 0", G3_MAX_TOK);
   ILFDT_REQUIRE(done || dq_dtype == ILFDT_F32, ILFDT_E_UNSUPPORTED_SHAPE,
                 "ground_bwd: bf16 dq needs D in {256,512,768,1024}, n_tok <= %d, K %% 4 == 0", G3_MAX_TOK);
   if constexpr (NV > 0) {
@@ -988,20 +1018,20 @@ static int32_t launch_ground_bwd_t(float* g, const float* w, const int16_t* arg,
 }
 
 template <typename T>
-static int32_t dispatch_nv(float* g, const float* w, const int16_t* arg, const T* q, const T* sd, const float* mask,
+static int32_t dispatch_nv(float* g, const void* w, int w_dtype, const int16_t* arg, const T* q, const T* sd, const float* mask,
                            const int* row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D, float inv_scale, void* dq, int dq_dtype,
                            float* dsd, cudaStream_t st) {
   const bool aligned = ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(sd) |
                          reinterpret_cast<uintptr_t>(dq) | reinterpret_cast<uintptr_t>(dsd)) & 31) == 0;
-  if (aligned && D == 512) return launch_ground_bwd_t<T, 2>(g, w, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
-  if (aligned && D == 256) return launch_ground_bwd_t<T, 1>(g, w, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
-  if (aligned && D == 768) return launch_ground_bwd_t<T, 3>(g, w, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
-  if (aligned && D == 1024) return launch_ground_bwd_t<T, 4>(g, w, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 512) return launch_ground_bwd_t<T, 2>(g, w, w_dtype, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 256) return launch_ground_bwd_t<T, 1>(g, w, w_dtype, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 768) return launch_ground_bwd_t<T, 3>(g, w, w_dtype, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 1024) return launch_ground_bwd_t<T, 4>(g, w, w_dtype, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
   ILFDT_REQUIRE(D <= 1024, ILFDT_E_UNSUPPORTED_SHAPE, "ground_bwd: D=%lld > 1024", (long long)D);
-  return launch_ground_bwd_t<T, 0>(g, w, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  return launch_ground_bwd_t<T, 0>(g, w, w_dtype, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
 }
 
-int32_t launch_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd, int dtype,
+int32_t launch_ground_bwd(float* g, const void* w, int w_dtype, const int16_t* arg, const void* q, const void* sd, int dtype,
                           const float* mask, const int* row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
                           float temperature, void* dq, int dq_dtype, float* dsd, cudaStream_t st) {
   if (b == 0) return ILFDT_OK;
@@ -1009,9 +1039,9 @@ int32_t launch_ground_bwd(float* g, const float* w, const int16_t* arg, const vo
                 "ground_bwd: shape out of range");
   const float inv_scale = 1.f / (sqrt_d * temperature);
   if (dtype == ILFDT_F32)
-    return dispatch_nv<float>(g, w, arg, reinterpret_cast<const float*>(q), reinterpret_cast<const float*>(sd), mask,
+    return dispatch_nv<float>(g, w, w_dtype, arg, reinterpret_cast<const float*>(q), reinterpret_cast<const float*>(sd), mask,
                               row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
-  return dispatch_nv<__nv_bfloat16>(g, w, arg, reinterpret_cast<const __nv_bfloat16*>(q),
+  return dispatch_nv<__nv_bfloat16>(g, w, w_dtype, arg, reinterpret_cast<const __nv_bfloat16*>(q),
                                     reinterpret_cast<const __nv_bfloat16*>(sd), mask, row_base, b, n_tok, K, D, inv_scale, dq,
                                     dq_dtype, dsd, st);
 }

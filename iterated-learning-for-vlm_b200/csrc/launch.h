@@ -41,7 +41,7 @@ int32_t launch_sparsemax_fwd(const float* z, int64_t rows, int64_t K, float* w, 
 int32_t launch_sparsemax_bwd(const float* w, const float* g, int64_t rows, int64_t K, float* dz, cudaStream_t st);
 
 // ground_bwd.cu
-int32_t launch_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd, int dtype,
+int32_t launch_ground_bwd(float* g, const void* w, int w_dtype, const int16_t* arg, const void* q, const void* sd, int dtype,
                           const float* mask, const int* row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D,
                           float sqrt_d, float temperature, void* dq, int dq_dtype, float* dsd, cudaStream_t st);
 

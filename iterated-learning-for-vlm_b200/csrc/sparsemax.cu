@@ -93,7 +93,7 @@ sparsemax_fwd_kernel(const float* __restrict__ z, int K, float* __restrict__ w,
   }
   const float tf = (float)tau;
   int nz = 0;
-  float* wr = w + r * K;
+  float* wr = w ? w + r * K : nullptr;   // optional: the tuned training path keeps only the bf16 copy
   __nv_bfloat16* wbr = wb ? wb + r * K : nullptr;
   // the subtraction loop wrote stride-1 slots; the vector pass below reads float4 groups.
   __syncthreads();
@@ -103,7 +103,7 @@ sparsemax_fwd_kernel(const float* __restrict__ z, int K, float* __restrict__ w,
       float4 o = make_float4(fmaxf(v.x - tf, 0.f), fmaxf(v.y - tf, 0.f), fmaxf(v.z - tf, 0.f),
                              fmaxf(v.w - tf, 0.f));
       nz += (o.x > 0.f) + (o.y > 0.f) + (o.z > 0.f) + (o.w > 0.f);
-      *reinterpret_cast<float4*>(wr + i) = o;
+      if (wr) *reinterpret_cast<float4*>(wr + i) = o;
       if (wbr) {
         __nv_bfloat162 p[2] = {__floats2bfloat162_rn(o.x, o.y), __floats2bfloat162_rn(o.z, o.w)};
         *reinterpret_cast<uint2*>(wbr + i) = *reinterpret_cast<uint2*>(p);
@@ -113,7 +113,7 @@ sparsemax_fwd_kernel(const float* __restrict__ z, int K, float* __restrict__ w,
     for (int i = threadIdx.x; i < K; i += SPX_THREADS) {
       float o = fmaxf(row[i] - tf, 0.f);
       nz += (o > 0.f);
-      wr[i] = o;
+      if (wr) wr[i] = o;
       if (wbr) wbr[i] = __float2bfloat16_rn(o);
     }
   }
@@ -192,7 +192,7 @@ sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__
   }
   const float tf = (float)tau;
   int nz = 0;
-  float* wr = w + r * K;
+  float* wr = w ? w + r * K : nullptr;   // optional: the tuned training path keeps only the bf16 copy
   __nv_bfloat16* wbr = wb ? wb + r * K : nullptr;
 #pragma unroll
   for (int j = 0; j < SPX_MAXV; ++j) {
@@ -201,7 +201,7 @@ sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__
       const float4 o = make_float4(fmaxf(v[j].x - tf, 0.f), fmaxf(v[j].y - tf, 0.f), fmaxf(v[j].z - tf, 0.f),
                                    fmaxf(v[j].w - tf, 0.f));
       nz += (o.x > 0.f) + (o.y > 0.f) + (o.z > 0.f) + (o.w > 0.f);
-      *reinterpret_cast<float4*>(wr + i) = o;
+      if (wr) *reinterpret_cast<float4*>(wr + i) = o;
       if (wbr) {
         __nv_bfloat162 p2[2] = {__floats2bfloat162_rn(o.x, o.y), __floats2bfloat162_rn(o.z, o.w)};
         *reinterpret_cast<uint2*>(wbr + i) = *reinterpret_cast<uint2*>(p2);

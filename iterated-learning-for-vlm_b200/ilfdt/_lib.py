@@ -39,6 +39,7 @@ SIGNATURES = {
     "ilfdt_gemm_tn": (_i32, [_p, _p, _i64, _i64, _i64, _f, _i32, _p, _i64, _p]),
     "ilfdt_gemm_f32_strided": (_i32, [_p, _i64, _i64, _p, _i64, _i64, _p, _i64, _i64, _i64, _i64, _i64, _f, _i32, _p]),
     "ilfdt_ground_bwd": (_i32, [_p, _p, _p, _p, _p, _i32, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _p, _i32, _p, _p]),
+    "ilfdt_ground_bwd_w16": (_i32, [_p, _p, _p, _p, _p, _i32, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _p, _i32, _p, _p]),
     "ilfdt_att_fwd": (_i32, [_p, _i64, _i64, _i32, _p, _p, _p]),
     "ilfdt_att_bwd": (_i32, [_p, _p, _p, _i64, _i64, _i32, _p, _p]),
     "ilfdt_rownorm_fwd": (_i32, [_p, _p, _i64, _i64, _p, _p]),

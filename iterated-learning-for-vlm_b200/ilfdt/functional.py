@@ -41,6 +41,7 @@ class compute_dtype:
 
 # padded text in bf16 mode: contract only the rows that can matter (csrc/text_buckets.cu); 0 = full-width operand
 COMPACT_TEXT = os.environ.get("ILFDT_COMPACT_TEXT", "1") != "0"
+LEAN_WEIGHTS = os.environ.get("ILFDT_LEAN_WEIGHTS", "1") != "0"   # need_weights=False skips the fp32 att_weight
 
 # bf16 copies of the codebook are shared by the two Query_models of one step
 _sd_cache = {}
@@ -59,10 +60,13 @@ def _sd_bf16(sd):
 
 class GroundingFunction(torch.autograd.Function):
     """Query_model.forward from q onward (clip_fdt.py:113-157), sparsemax + max pooling:
-    (q [b,N,D], sd [K,D], mask [b,N] | None) -> (att_weight [b,K], att_ft [b,D])."""
+    (q [b,N,D], sd [K,D], mask [b,N] | None) -> (att_weight [b,K], att_ft [b,D]).
+    need_weights=False (what Clip_FDT.forward asks for: it drops att_weight, clip_fdt.py:233-234): on the
+    tensor-core route att_weight is returned as the non-differentiable bf16 copy the pooling GEMM consumes and
+    the fp32 one is never written (4 bytes/entry less written in the forward, 6 less read in the backward)."""
 
     @staticmethod
-    def forward(ctx, q, sd, mask, temperature, mode):
+    def forward(ctx, q, sd, mask, temperature, mode, need_weights=True):
         q = q.contiguous()
         sd_c = sd.contiguous()
         ctx.q_dtype = q.dtype
@@ -90,7 +94,10 @@ class GroundingFunction(torch.autograd.Function):
         else:
             q_k, sd_k, sd_kt = q, sd_c, None
             pooled, arg = ops.ground_fwd(q_k, sd_k, mask_f, temperature, "max")
-        w, w_b, _tau, _nnz = ops.sparsemax_fwd(pooled, want_bf16=(mode == "bf16"))
+        # the scatter kernel that reads the support from bf16 weights covers these shapes (ground_bwd.cu)
+        lean = LEAN_WEIGHTS and (not need_weights) and mode == "bf16" and q.shape[2] in (256, 512) and q.shape[1] <= 96 \
+            and sd.shape[0] % 4 == 0
+        w, w_b, _tau, _nnz = ops.sparsemax_fwd(pooled, want_bf16=(mode == "bf16"), want_f32=not lean)
         del pooled
         if mode == "bf16":
             f = ops.gemm_nt(sd_kt, w_b)                     # f[b,D] = w[b,K] . sdT[D,K]^T  (clip_fdt.py:154)
@@ -99,12 +106,17 @@ class GroundingFunction(torch.autograd.Function):
         ctx.mode, ctx.temperature = mode, float(temperature)
         ctx.n_tok = q.shape[1]
         ctx.save_for_backward(q_k, sd_k, mask_f, w, arg, w_b, row_base)
+        if lean:
+            ctx.mark_non_differentiable(w_b)
+            return w_b, f
         return w, f
 
     @staticmethod
     def backward(ctx, dw, df):
         q_k, sd_k, mask_f, w, arg, w_b, row_base = ctx.saved_tensors
         mode = ctx.mode
+        if w is None:
+            w = w_b          # lean route: the support is read from the bf16 weights
         b, K = w.shape
         D = sd_k.shape[1]
         dsd = torch.zeros(K, D, dtype=torch.float32, device=w.device)
@@ -129,7 +141,7 @@ class GroundingFunction(torch.autograd.Function):
         dq = ops.ground_bwd(g, w, arg, q_k, sd_k, mask_f, ctx.temperature, dsd, dq_dtype, row_base, ctx.n_tok)
         if dq.dtype != ctx.q_dtype:
             dq = ops.cast_bf16(dq)
-        return dq, dsd, None, None, None
+        return dq, dsd, None, None, None, None
 
 
 class GroundingVariantFunction(torch.autograd.Function):

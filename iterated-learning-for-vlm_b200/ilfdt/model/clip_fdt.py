@@ -48,14 +48,16 @@ class Query_model(nn.Module):
             nn.Linear(sd_dim, sd_dim),
         )
 
-    def forward(self, ft, sd, mask=None, return_token_att=False):
+    def forward(self, ft, sd, mask=None, return_token_att=False, need_weights=True):
+        # need_weights=False (an addition to the reference signature, used by Clip_FDT.forward which drops
+        # att_weight): the tuned route returns att_weight as its bf16 tensor-core copy, not differentiable
         q = self.q_map(ft)
         if mask is not None:
             assert mask.shape == q.shape[:2]
         if self.att_func_type == 'sparsemax' and self.pool_type == 'max':
             # the shipped configuration (config_cc3m.yaml:14-21): tuned tensor-core path
             att_weight, att_ft = Fn.GroundingFunction.apply(q, sd, mask, float(self.temperature),
-                                                            Fn.get_compute_dtype())
+                                                            Fn.get_compute_dtype(), need_weights)
         else:
             att_weight, att_ft = Fn.GroundingVariantFunction.apply(q, sd, mask, float(self.temperature),
                                                                    self.att_func_type, self.pool_type)
@@ -230,8 +232,8 @@ class Clip_FDT(nn.Module):
         patch_ft = self._image_features(images)
         _, word_ft, _, pad_mask = self.encode_text(texts, return_dense=True, return_padmask=True,
                                                    return_raw_feature=True)
-        _, sd_img_ft, img_k = self.img_query_model(patch_ft, self.space_dict)
-        _, sd_txt_ft, txt_k = self.txt_query_model(word_ft, self.space_dict, mask=pad_mask)
+        _, sd_img_ft, img_k = self.img_query_model(patch_ft, self.space_dict, need_weights=False)
+        _, sd_txt_ft, txt_k = self.txt_query_model(word_ft, self.space_dict, mask=pad_mask, need_weights=False)
 
         sd_img_ft = Fn.L2NormFunction.apply(sd_img_ft, 1e-10)       # :411
         sd_txt_ft = Fn.L2NormFunction.apply(sd_txt_ft, 1e-10)       # :412

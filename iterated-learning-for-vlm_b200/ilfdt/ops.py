@@ -20,7 +20,7 @@ LAUNCHES = 0          # kernels launched through this module since it was last z
 PROFILE_ON = False    # when True every C call is bracketed by CUDA events on the launching stream
 PROFILE = {}          # op name -> [(start_event, end_event), ...]
 _KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mask_rows_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_ground_fwd_text": 5, "ilfdt_text_compact": 3, "ilfdt_sparsemax_fwd": 1,
-                     "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2,
+                     "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2, "ilfdt_ground_bwd_w16": 2,
                      "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5,
                      "ilfdt_nce_bwd": 4, "ilfdt_nce_bwd_gathered": 2, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
                      "ilfdt_randn_fill": 1, "ilfdt_copy": 0}
@@ -167,10 +167,13 @@ def ground_fwd_text(q_compact, sd, plan, n_tok, temperature):
     return pooled, arg
 
 
-def sparsemax_fwd(z, want_bf16=False):
+def sparsemax_fwd(z, want_bf16=False, want_f32=True):
+    """-> (w f32 | None, w bf16 | None, tau, nnz); want_f32=False (needs want_bf16) keeps only the bf16 copy."""
     _req(z, torch.float32, "z")
     rows, K = z.shape
-    w = torch.empty_like(z)
+    if not (want_f32 or want_bf16):
+        raise ValueError("ilfdt: sparsemax_fwd needs at least one output")
+    w = torch.empty_like(z) if want_f32 else None
     wb = torch.empty(rows, K, dtype=torch.bfloat16, device=z.device) if want_bf16 else None
     tau = torch.empty(rows, dtype=torch.float32, device=z.device)
     nnz = torch.empty(rows, dtype=torch.int32, device=z.device)
@@ -235,7 +238,11 @@ def ground_bwd(g, w, arg, q, sd, mask, temperature, dsd, dq_dtype=torch.float32,
     """g [b,K] is overwritten with coef. Returns dq [b,N,D] (dq_dtype); accumulates into dsd [K,D] f32.
     row_base (int32 [b]) + n_tok: q is the compacted text operand [rows, D] of text_compact."""
     _req(g, torch.float32, "g"); _req(arg, torch.int16, "arg")
-    if w is not None:   # None: g already is dLoss/dpooled (softmax / sigmoid attention)
+    fn = "ilfdt_ground_bwd"
+    if w is not None and w.dtype == torch.bfloat16:   # support read from the bf16 copy of the weights
+        _req(w, torch.bfloat16, "w")
+        fn = "ilfdt_ground_bwd_w16"
+    elif w is not None:   # None: g already is dLoss/dpooled (softmax / sigmoid attention)
         _req(w, torch.float32, "w")
     _req(q, None, "q"); _req(sd, q.dtype, "sd"); _req(dsd, torch.float32, "dsd")
     if row_base is None:
@@ -245,7 +252,7 @@ def ground_bwd(g, w, arg, q, sd, mask, temperature, dsd, dq_dtype=torch.float32,
         b, D = g.shape[0], q.shape[-1]
     K = sd.shape[0]
     dq = torch.empty(b, n_tok, D, dtype=dq_dtype, device=q.device)
-    _call("ilfdt_ground_bwd", _ptr(g), _ptr(w), _ptr(arg), _ptr(q), _ptr(sd), _DT[q.dtype], _ptr(mask), _ptr(row_base), b,
+    _call(fn, _ptr(g), _ptr(w), _ptr(arg), _ptr(q), _ptr(sd), _DT[q.dtype], _ptr(mask), _ptr(row_base), b,
           n_tok, K, D, float(math.sqrt(D)), float(temperature), _ptr(dq), _DT[dq_dtype], _ptr(dsd), _stream())
     return dq
 

@@ -279,6 +279,37 @@ def test_grounding_bf16_q_input(ops, b, n_tok, K, D, masked):
         assert q16.grad.float()[pad].abs().max().item() == 0.0
 
 
+@pytest.mark.parametrize("b,n_tok,K,D,masked", [(33, 49, 512, 512, False), (70, 77, 1024, 512, True),
+                                               (16, 77, 256, 256, True), (5, 96, 384, 512, False)])
+@pytest.mark.parametrize("qdtype", ["f32", "bf16"])
+def test_grounding_without_fp32_weights(ops, b, n_tok, K, D, masked, qdtype):
+    """need_weights=False (Clip_FDT.forward drops att_weight, clip_fdt.py:233-234): the fp32 weights are never
+    written, att_weight comes back as the bf16 tensor-core copy, the backward reads the support from it
+    (ilfdt_ground_bwd_w16). att_ft, dq and dsd must be BIT-identical to the default route -- same support, same
+    coefficients, same scatter order."""
+    from ilfdt.functional import GroundingFunction
+    g = torch.Generator().manual_seed(7 * b + n_tok + K)
+    q = bf16_round(torch.randn(b, n_tok, D, generator=g))
+    sd = bf16_round(torch.randn(K, D, generator=g))
+    mask = _mask(b, n_tok, torch.randint(1, n_tok + 1, (b,), generator=g).tolist()) if masked else None
+    up_f = torch.randn(b, D, generator=g).to(_dev())
+    md = None if mask is None else mask.to(_dev())
+    dt = torch.bfloat16 if qdtype == "bf16" else torch.float32
+    res = []
+    for need in (True, False):
+        qd = q.to(_dev()).to(dt).requires_grad_(True)
+        sdd = sd.to(_dev()).requires_grad_(True)
+        w, f = GroundingFunction.apply(qd, sdd, md, 30.0, "bf16", need)
+        (f * up_f).sum().backward()
+        res.append((w, f.detach(), qd.grad, sdd.grad))
+    (w_full, f_full, dq_full, dsd_full), (w_lean, f_lean, dq_lean, dsd_lean) = res
+    assert w_full.dtype == torch.float32 and w_lean.dtype == torch.bfloat16 and not w_lean.requires_grad
+    assert torch.equal(w_lean, w_full.to(torch.bfloat16))
+    assert torch.equal(w_lean > 0, w_full > 0), "support changed by the bf16 rounding"
+    assert torch.equal(f_lean, f_full)
+    assert torch.equal(dq_lean, dq_full) and torch.equal(dsd_lean, dsd_full)
+
+
 @pytest.mark.parametrize("b,n_tok,K,D", [(37, 77, 384, 512), (300, 77, 1024, 512), (64, 49, 256, 256), (9, 64, 512, 64),
                                         (1500, 77, 256, 512)])
 @pytest.mark.parametrize("qdtype", ["f32", "bf16"])
