@@ -142,9 +142,23 @@ def _gloo_worker(rank, world, port, out):
     ok = torch.allclose(x.grad, expect)
     st = ContrastiveStash(x, x, flat, flat, torch.ones(1), "fp32")
     ok = ok and st.label_offset() == rank * 3 and torch.equal(y[rank], x.detach())
-    out[rank] = bool(ok) and _gathered_identity(rank, world)
+    out[rank] = bool(ok) and _gathered_identity(rank, world) and _meters_identity(rank, world)
     dist.barrier()
     dist.destroy_process_group()
+
+
+def _meters_identity(rank, world):
+    """reduce_update_many == the solver's three reduce_update calls (train_solver.py:447-449), one all-reduce."""
+    from ilfdt.utils import AverageMeter, reduce_update_many
+    a = [AverageMeter(), AverageMeter(10), AverageMeter()]
+    b = [AverageMeter(), AverageMeter(10), AverageMeter()]
+    for step in range(3):
+        vals = [torch.tensor(1.5 * rank + step), torch.tensor([2.0 + rank * step]), torch.tensor(0.25 * (rank + 1))]
+        for m, v in zip(a, vals):
+            m.reduce_update(v.clone())
+        reduce_update_many(b, [v.clone() for v in vals])
+    return all(abs(x.val - y.val) < 1e-6 and abs(x.avg - y.avg) < 1e-6 for x, y in zip(a, b)) and \
+        abs(a[2].val - 0.25 * sum(r + 1 for r in range(world))) < 1e-6
 
 
 def _gathered_identity(rank, world):
@@ -190,3 +204,21 @@ def test_allgather_semantics_world2_gloo(tmp_path):
     path = str(tmp_path / "res")
     mp.spawn(_gloo_entry, args=(2, 29577, path), nprocs=2, join=True)
     assert open(path + "0").read() == "ok" and open(path + "1").read() == "ok"
+
+
+def test_logit_scale_step_clip_matches_reference_rule():
+    """train_solver.py:384-393 ('logit_scale_param'): after the step the parameter is within `value` of where it was."""
+    sys.path.insert(0, PKG)
+    from ilfdt.utils import clip_logit_scale_step
+    for before, after, value in [(2.6593, 2.70, 0.01), (2.6593, 2.60, 0.01), (2.6593, 2.6650, 0.01), (4.0, 4.0, 0.5)]:
+        p = torch.nn.Parameter(torch.tensor([after], dtype=torch.float32))
+        b = torch.tensor([before], dtype=torch.float32)
+        bf, af = b.item(), p.data.item()
+        if (af - bf) > value:                     # the reference's host-side rule
+            want = torch.as_tensor(bf + value, dtype=torch.float32)
+        elif (bf - af) > value:
+            want = torch.as_tensor(bf - value, dtype=torch.float32)
+        else:
+            want = p.data.clone()
+        clip_logit_scale_step(p, b, value)
+        assert torch.equal(p.data.reshape(()), want.reshape(())), (before, after, value)

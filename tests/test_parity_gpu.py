@@ -916,3 +916,20 @@ def test_full_size_properties(ops):
     # idempotence of the projection: sparsemax(w) == w for points already on the simplex
     w2, _, _, _ = ops.sparsemax_fwd(w)
     assert (w2 - w).abs().max().item() <= 1e-6
+
+
+@pytest.mark.gpu
+def test_deferred_meters_never_block_and_match(ops):
+    """reduce_update_many(defer=True) queues the read behind an event; after flush the meters hold the
+    same values as the blocking route."""
+    from ilfdt.utils import AverageMeter, flush_meters, reduce_update_many
+    a = [AverageMeter(), AverageMeter(), AverageMeter(5)]
+    b = [AverageMeter(), AverageMeter(), AverageMeter(5)]
+    for step in range(4):
+        vals = [torch.tensor(0.5 * step, device=_dev()), torch.tensor([3.0 - step], device=_dev()),
+                torch.tensor(7.0 * step, device=_dev())]
+        reduce_update_many(a, vals)
+        reduce_update_many(b, vals, defer=True)
+    flush_meters()
+    for x, y in zip(a, b):
+        assert x.val == y.val and abs(x.avg - y.avg) < 1e-12
