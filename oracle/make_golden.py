@@ -195,12 +195,47 @@ def gen_clip_steps():
             np.savez_compressed(os.path.join(OUT, f"clip_step_{tag}.npz"), **merged)
 
 
+def gen_eval_extract():
+    """what CLIP_benchmark/clip_benchmark/models/fdt.py:16-91 does with a trained model -- a checkpoint
+    `{"model": {"module.<name>": tensor}}` is loaded (prefix stripped, :43-49) and `extract_img_sd_ft` /
+    `extract_txt_sd_ft` give the evaluation embeddings (:55-70) -- run on the unmodified reference in eval mode."""
+    H.ensure_process_group(0, 1, port=29547)
+    b, P, T, Fi, Ft, K, D = 7, 6, 9, 24, 20, 128, 32
+    patch, word, mask = _fdt_inputs(900, b, P, T, Fi, Ft, K, D)
+    torch.manual_seed(11)
+    model = H.build_reference_fdt(patch, word, mask, K, D, temperature=5.0)
+    with torch.no_grad():                                   # a "trained" state: nothing at its init value
+        for prm in model.parameters():
+            prm.add_(0.05 * torch.randn(prm.shape, generator=torch.Generator().manual_seed(prm.numel())))
+    model.eval()
+    out = dict(patch=_np(patch), word=_np(word), mask=_np(mask), temp=np.array(5.0))
+    for k, v in model.state_dict().items():
+        if not k.startswith(("visual.", "encode_text.")):
+            out["ckpt_module." + k] = _np(v)                # DDP-style key, as the solver saves it
+    with torch.no_grad():
+        w_i, f_i, _ = model.extract_img_sd_ft(torch.zeros(b, 1))
+        w_t, f_t, _ = model.extract_txt_sd_ft(["x"] * b, raw_text=True)
+        tok_i, _, _ = model.extract_img_sd_ft(torch.zeros(b, 1), return_token_att=True)
+        tok_t, _, _ = model.extract_txt_sd_ft(["x"] * b, return_token_att=True)
+        q_i = model.extract_patch_ft(torch.zeros(b, 1))
+        q_t, _ = model.extract_word_ft(["x"] * b)
+    out.update(img_att_weight=_np(w_i), img_sd_ft=_np(f_i), txt_att_weight=_np(w_t), txt_sd_ft=_np(f_t),
+               img_token_att=_np(tok_i), txt_token_att=_np(tok_t), patch_q=_np(q_i), word_q=_np(q_t))
+    np.savez_compressed(os.path.join(OUT, "eval_extract.npz"), **out)
+    import torch.distributed as dist
+    dist.destroy_process_group()
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(4)
+    if sys.argv[1:] == ["eval_extract"]:      # added later: leaves the earlier fixtures byte-identical
+        gen_eval_extract()
+        sys.exit(0)
     gen_sparsemax()
     gen_query_model()
     gen_fdt_steps()
     gen_clip_steps()
+    gen_eval_extract()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

@@ -933,3 +933,51 @@ def test_deferred_meters_never_block_and_match(ops):
     flush_meters()
     for x, y in zip(a, b):
         assert x.val == y.val and abs(x.avg - y.avg) < 1e-12
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_reference_checkpoint_eval_embeddings(ops, golden_dir, mode):
+    """the evaluation adapter's flow (CLIP_benchmark/clip_benchmark/models/fdt.py:43-70) on the drop-in:
+    a reference checkpoint ({"module.<name>": tensor}, prefix stripped) loads with no unexpected key, and
+    extract_img_sd_ft / extract_txt_sd_ft / extract_patch_ft / extract_word_ft in eval mode give the reference's
+    embeddings (tests/golden/eval_extract.npz, made by oracle/make_golden.py from the unmodified reference)."""
+    import ilfdt
+    from ilfdt.model.clip_fdt import Clip_FDT
+    z = np.load(os.path.join(golden_dir, "eval_extract.npz"))
+    dev = _dev()
+    patch, word, mask = (torch.tensor(z[k], device=dev) for k in ("patch", "word", "mask"))
+    ckpt = {"model": {k[5:]: torch.tensor(z[k]) for k in z.files if k.startswith("ckpt_")}}
+    state = {(k[7:] if k[:6] == "module" else k): v for k, v in ckpt["model"].items()}      # fdt.py:45-48
+    K, D = state["space_dict"].shape
+    m = Clip_FDT(_FakeVisual(patch), _FakeText(word, mask), True, K, D, patch.shape[-1], word.shape[-1], "sparsemax",
+                 "max", float(z["temp"])).to(dev)
+    missing, unexpected = m.load_state_dict(state, strict=False)
+    assert not unexpected and all(k.startswith(("visual.", "encode_text.")) for k in missing), (missing, unexpected)
+    m.eval()
+    b = patch.shape[0]
+    tol = FP32_TOL if mode == "fp32" else BF16_TOL
+    with ilfdt.compute_dtype(mode), torch.no_grad():
+        w_i, f_i, sd_i = m.extract_img_sd_ft(torch.zeros(b, 1, device=dev))
+        w_t, f_t, _ = m.extract_txt_sd_ft(["x"] * b, raw_text=True)
+        tok_i, _, _ = m.extract_img_sd_ft(torch.zeros(b, 1, device=dev), return_token_att=True)
+        tok_t, _, _ = m.extract_txt_sd_ft(["x"] * b, return_token_att=True)
+        q_i = m.extract_patch_ft(torch.zeros(b, 1, device=dev))
+        q_t, pm = m.extract_word_ft(["x"] * b)
+    assert w_i.dtype == torch.float32 and sd_i is m.space_dict
+    assert_close(f_i, torch.tensor(z["img_sd_ft"]), tol, "img sd_ft")
+    assert_close(f_t, torch.tensor(z["txt_sd_ft"]), tol, "txt sd_ft")
+    assert_close(w_i, torch.tensor(z["img_att_weight"]), tol, "img att_weight")
+    assert_close(w_t, torch.tensor(z["txt_att_weight"]), tol, "txt att_weight")
+    assert_close(q_i, torch.tensor(z["patch_q"]), FP32_TOL, "extract_patch_ft")
+    assert_close(q_t, torch.tensor(z["word_q"]), FP32_TOL, "extract_word_ft")
+    assert torch.equal(pm, mask)
+    if mode == "fp32":
+        assert torch.equal(w_i.cpu() > 0, torch.tensor(z["img_att_weight"]) > 0), "image support differs"
+        assert torch.equal(w_t.cpu() > 0, torch.tensor(z["txt_att_weight"]) > 0), "text support differs"
+        assert_close(tok_i, torch.tensor(z["img_token_att"]), FP32_TOL, "image token scores")
+        assert_close(tok_t, torch.tensor(z["txt_token_att"]), FP32_TOL, "text token scores")
+    # retrieval as the benchmark does it: cosine similarity of the two embeddings, same ranking as the reference's
+    ref_sim = torch.nn.functional.normalize(torch.tensor(z["img_sd_ft"]), dim=-1) @ \
+        torch.nn.functional.normalize(torch.tensor(z["txt_sd_ft"]), dim=-1).t()
+    sim = (torch.nn.functional.normalize(f_i, dim=-1) @ torch.nn.functional.normalize(f_t, dim=-1).t()).cpu()
+    assert_close(sim, ref_sim, tol, "retrieval similarities")
