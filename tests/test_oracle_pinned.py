@@ -72,6 +72,26 @@ def test_query_model_golden(golden_dir, name, att, pool, tag):
         _close(v.grad.numpy(), z[pre + "d_q_map." + k], rtol=1e-4, atol=1e-6)
 
 
+def test_eval_extract_golden(golden_dir):
+    """The evaluation flow's outputs (extract_*_sd_ft in eval mode on a loaded checkpoint)."""
+    z = _load(golden_dir, "eval_extract.npz")
+    state = {k[len("ckpt_module."):]: z[k] for k in z.files if k.startswith("ckpt_module.")}
+    sd = _t(state["space_dict"])
+    temp = float(z["temp"])
+    for mod, src, mask, tag in (("img_query_model", "patch", None, "img"), ("txt_query_model", "word", _t(z["mask"]), "txt")):
+        x = _t(z[src])
+        q_map = O.make_q_map(x.shape[-1], sd.shape[1], state, prefix=mod + ".q_map.")
+        with torch.no_grad():
+            q = q_map(x)
+            w, f, _ = O.grounding(q, sd, mask, temp, "sparsemax", "max")
+            _, tok = O.pooled_scores(q, sd, mask, temp, "max", return_token_scores=True)
+        _close(q.numpy(), z["patch_q" if tag == "img" else "word_q"])
+        _close(w.numpy(), z[tag + "_att_weight"])
+        _close(f.numpy(), z[tag + "_sd_ft"])
+        _close(tok.numpy(), z[tag + "_token_att"])
+        assert np.array_equal(w.numpy() > 0, z[tag + "_att_weight"] > 0)
+
+
 def _fdt_ranks(z, world):
     ranks, qmaps = [], []
     for r in range(world):
