@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the trained-like (peaked attention) secondary case")
+    ap.add_argument("--no-qmap", action="store_true", help="skip the q_map producer timing (SURVEY 8f N2)")
     ap.add_argument("--trained-scale", type=float, default=200.0, help="q multiplier of the trained-like secondary case")
     ap.add_argument("--cpu-sample", type=int, default=64, help="rows of the workload timed on the host cores")
     return ap.parse_args()
@@ -115,6 +116,62 @@ def workload_config(args, note=None):
     if note:
         c["note"] = note
     return c
+
+
+# ---------------------------------------------------------------------------------------------------
+# q_map producer: reported beside the headline, never inside it (8a row a0 keeps q_map out of the metric)
+# ---------------------------------------------------------------------------------------------------
+def measure_q_map(b, dev, steps):
+    """Forward + backward of both Query_model.q_map MLPs (clip_fdt.py:86-92) at the bench's batch: the library route
+    (ilfdt.functional.QMapFunction: tcgen05 Linear layers on bf16 operands, fp32 row kernels, q handed to the score
+    kernel in bf16) and the reference's route (fp32 nn.Sequential in PyTorch eager, TF32 off as in the reference) on a
+    2048-sample slice scaled to the batch."""
+    from ilfdt import functional as Fn
+    from ilfdt import ops
+    from ilfdt.model.clip_fdt import Query_model
+    out = {"ilfdt_bf16_ms": 0.0, "torch_fp32_eager_ms": 0.0, "parts": {}}
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for name, n_tok, width in (("image", P_TOK, 768), ("text", T_TOK, 512)):
+        torch.manual_seed(0)
+        qm = Query_model(width, D_DIM, TEMPERATURE, "sparsemax", "max").to(dev)
+        x = torch.randn(b, n_tok, width, device=dev, requires_grad=True)
+        up = torch.randn(b, n_tok, D_DIM, device=dev, dtype=torch.bfloat16)   # dq as the scatter backward returns it
+
+        def fused():
+            Fn.q_map_apply(qm.q_map, x).backward(up)
+
+        sample = min(b, 2048)
+
+        def eager():
+            xi = x[:sample].detach().requires_grad_(True)
+            qm.q_map(xi).backward(up[:sample].float())
+
+        part = {}
+        for tag, fn, scale in (("ilfdt_bf16_ms", fused, 1.0), ("torch_fp32_eager_ms", eager, b / float(sample))):
+            for _ in range(2):
+                fn()
+            torch.cuda.synchronize()
+            ops.PROFILE.clear()
+            ops.PROFILE_ON = tag == "ilfdt_bf16_ms"
+            e0.record()
+            for _ in range(steps):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ops.PROFILE_ON = False
+            part[tag] = e0.elapsed_time(e1) / steps * scale
+            out[tag] += part[tag]
+            if tag == "ilfdt_bf16_ms":
+                part["kernel_ms"] = {k: round(v[1] / steps, 3) for k, v in ops.profile_summary().items()}
+            ops.PROFILE.clear()
+        rows = b * n_tok
+        part["tflops_ilfdt"] = 3 * 2.0 * rows * (width * D_DIM + D_DIM * D_DIM) / (part["ilfdt_bf16_ms"] * 1e-3) / 1e12
+        out["parts"][name] = part
+        del qm, x, up
+        torch.cuda.empty_cache()
+    out["note"] = ("both q_map MLPs fwd+bwd at this batch; eager = fp32 nn.Sequential on a %d-sample slice scaled to "
+                   "the batch; not part of `value` (SURVEY 8a row a0)" % min(b, 2048))
+    return out
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -442,6 +499,15 @@ def run_ours(args):
                      "mean_support": support, "kernel_ms_per_step": sec_kernel_ms}
         del qi2, qt2, w_i
 
+    qmap = None
+    if world == 1 and args.mode == "bf16" and not args.no_qmap:
+        main_profile = dict(ops.PROFILE)
+        qmap = measure_q_map(b, dev, args.steps)
+        qmap["step_with_q_map_ms"] = ms_per_step + qmap["ilfdt_bf16_ms"]
+        qmap["step_with_eager_q_map_ms"] = ms_per_step + qmap["torch_fp32_eager_ms"]
+        ops.PROFILE.clear()
+        ops.PROFILE.update(main_profile)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu, _ = cpu_reference_run(args.cpu_sample, 3, 1, K)
@@ -451,7 +517,7 @@ def run_ours(args):
                 "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": args.mode, "data": "synthetic", "config": workload_config(args),
                 "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk,
-                "loss": loss_val, "kernel_ms_per_step": kernel_ms, "cuda_graph": graph_note, "secondary": secondary,
+                "loss": loss_val, "kernel_ms_per_step": kernel_ms, "cuda_graph": graph_note, "secondary": secondary, "q_map": qmap,
                 "step_ms_spread": {"min": min(per_step), "median": statistics.median(per_step), "max": max(per_step)},
                 "host_issue_ms_per_step": host_ms_per_step}
         print(json.dumps(line), flush=True)

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define ILFDT_ABI_VERSION 2
+#define ILFDT_ABI_VERSION 3
 
 enum {
   ILFDT_OK = 0,
@@ -116,6 +116,12 @@ int32_t ilfdt_gemm_nt(const void* A, const void* B, int32_t dtype, int64_t M, in
  * (clip_fdt.py:154): A = df, B = w, M = D, N = K, Kr = b. M, N multiples of 8. */
 int32_t ilfdt_gemm_tn(const void* A_bf16, const void* B_bf16, int64_t M, int64_t N, int64_t Kr, float alpha,
                       int32_t accumulate, float* out, int64_t ldo, void* stream);
+/* ilfdt_gemm_tn for weight-gradient shapes (short M and N, Kr in the millions: dW of q_map's Linear layers,
+ * clip_fdt.py:88,91): the reduction is split over the SMs into slabs of `ws` that a second kernel sums in a fixed
+ * order (deterministic, no atomics). ws: ilfdt_gemm_tn_splitk_ws_bytes(M, N, Kr) (0 = not split, plain launch). */
+int64_t ilfdt_gemm_tn_splitk_ws_bytes(int64_t M, int64_t N, int64_t Kr);
+int32_t ilfdt_gemm_tn_splitk(const void* A_bf16, const void* B_bf16, int64_t M, int64_t N, int64_t Kr, float alpha,
+                             int32_t accumulate, float* out, int64_t ldo, void* ws, int64_t ws_bytes, void* stream);
 /* fp32 only, arbitrary strides: C(m,n) (+)= alpha * sum_k A(m,k) B(n,k), X(i,j) = X[i*rs + j*cs] */
 int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs,
                                const float* B, int64_t b_rs, int64_t b_cs,
@@ -236,6 +242,33 @@ int32_t ilfdt_topk_hits(const float* logits, int64_t b, int64_t B, int64_t label
 int32_t ilfdt_nce_topk_hits(const void* x, const void* g, int32_t dtype, int64_t b, int64_t B, int64_t D,
                             const float* scale, int64_t label_offset, const float* diag, int32_t* counts, void* ws,
                             int64_t ws_bytes, void* stream);
+
+/* ---- q_map producer (clip_fdt.py:86-92: LayerNorm -> Linear -> GELU -> LayerNorm -> Linear) ------- */
+/* The two Linear layers are ilfdt_gemm_nt / ilfdt_gemm_tn calls on bf16 operands; these are the rows between them.
+ * Widths C in {256, 512, 768, 1024}. Column sums are two-stage and deterministic (no float atomics).
+ *
+ * y_bf16[r,:] = LayerNorm(act(src[r,:] + bias)) * gamma + beta with the biased variance and eps of nn.LayerNorm
+ * (clip_fdt.py:87,90); mean / rstd [rows] are saved for the backward. gelu = 0: act = identity, bias ignored, src f32
+ * or bf16. gelu = 1 (nn.GELU(), exact erf, clip_fdt.py:89): src is the fp32 output of the first Linear without its
+ * bias, and pre_bf16 [rows,C] receives the pre-activation src + bias that the backward differentiates. */
+int32_t ilfdt_ln_fwd(const void* src, int32_t src_dtype, const float* bias, const float* gamma, const float* beta,
+                     int64_t rows, int64_t C, float eps, int32_t gelu, void* y_bf16, void* pre_bf16, float* mean,
+                     float* rstd, void* stream);
+/* Backward of the above for dy [rows,C] f32. src = the forward's src (gelu = 0) or its pre_bf16 (gelu = 1).
+ * dsrc: f32 (gelu = 0) or bf16 (gelu = 1, the operand of the next contraction); dgamma, dbeta [C]; dbias [C] (gelu = 1,
+ * may be NULL) = column sum of dsrc. ws: ilfdt_ln_bwd_ws_bytes(rows, C). */
+int64_t ilfdt_ln_bwd_ws_bytes(int64_t rows, int64_t C);
+int32_t ilfdt_ln_bwd(const float* dy, const void* src, int32_t src_dtype, const float* gamma, const float* mean,
+                     const float* rstd, int64_t rows, int64_t C, int32_t gelu, void* dsrc, int32_t dsrc_dtype,
+                     float* dgamma, float* dbeta, float* dbias, void* ws, int64_t ws_bytes, void* stream);
+/* dst[r,:] = src[r,:] + bias  (the second Linear's bias, clip_fdt.py:91), written as bf16 (the score kernel's
+ * operand) or f32. */
+int32_t ilfdt_bias_cast(const float* src, const float* bias, int64_t rows, int64_t C, void* dst, int32_t dst_dtype,
+                        void* stream);
+/* out[c] = sum_r src[r,c]  (bias gradient of a Linear); ws: ilfdt_colsum_ws_bytes(rows, C). */
+int64_t ilfdt_colsum_ws_bytes(int64_t rows, int64_t C);
+int32_t ilfdt_colsum(const void* src, int32_t src_dtype, int64_t rows, int64_t C, float* out, void* ws,
+                     int64_t ws_bytes, void* stream);
 
 /* ---- a12: codebook reset / store / keep, clip_fdt.py:281-283, train_solver.py:211-215,549-553 -- */
 /* dst[i] ~ N(0,1): Philox4x32-10 keyed by seed, counter (i/4, generation), Box-Muller. Same values

@@ -18,7 +18,7 @@ OUT_DIR = os.path.join(HERE, "ilfdt")
 OUT = os.path.join(OUT_DIR, "libilfdt.so")
 OBJ_DIR = os.path.join(HERE, "build")
 SOURCES = ["api.cu", "kernels_simt.cu", "sparsemax.cu", "ground_bwd.cu", "gemm_umma.cu", "nce_bwd_umma.cu", "rowops.cu",
-           "text_buckets.cu", "ground_umma2.cu", "nce_bwd_umma2.cu", "gemm_wide2.cu"]
+           "text_buckets.cu", "ground_umma2.cu", "nce_bwd_umma2.cu", "gemm_wide2.cu", "qmap_rows.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC",
          "--expt-relaxed-constexpr", "-Xptxas", "-v"]

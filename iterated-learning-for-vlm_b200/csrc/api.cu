@@ -266,6 +266,18 @@ int32_t ilfdt_gemm_tn(const void* A, const void* B, int64_t M, int64_t N, int64_
   return launch_gemm_tn_bf16(A, B, M, N, Kr, alpha, accumulate, out, ldo, ST(stream));
 }
 
+int64_t ilfdt_gemm_tn_splitk_ws_bytes(int64_t M, int64_t N, int64_t Kr) { return gemm_tn_splitk_ws_floats(M, N, Kr) * 4; }
+
+int32_t ilfdt_gemm_tn_splitk(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha,
+                             int32_t accumulate, float* out, int64_t ldo, void* ws, int64_t ws_bytes, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(M >= 0 && N >= 0 && Kr >= 1 && ldo >= M, ILFDT_E_INVALID_ARG, "gemm_tn_splitk: bad shape");
+  ILFDT_REQUIRE((M == 0 || N == 0) || (A && B && out), ILFDT_E_INVALID_ARG, "gemm_tn_splitk: null pointer");
+  ILFDT_REQUIRE(ws_bytes >= ilfdt_gemm_tn_splitk_ws_bytes(M, N, Kr), ILFDT_E_INVALID_ARG,
+                "gemm_tn_splitk: workspace too small");
+  return launch_gemm_tn_splitk_bf16(A, B, M, N, Kr, alpha, accumulate, out, ldo, (float*)ws, ST(stream));
+}
+
 int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs, const float* B, int64_t b_rs, int64_t b_cs,
                                float* C, int64_t c_rs, int64_t c_cs, int64_t M, int64_t N, int64_t Kr, float alpha,
                                int32_t accumulate, void* stream) {
@@ -506,6 +518,51 @@ int32_t ilfdt_copy(void* dst, const void* src, int64_t bytes, void* stream) {
   if (bytes == 0) return ILFDT_OK;
   ILFDT_CUDA_OK(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice, ST(stream)));
   return ILFDT_OK;
+}
+
+/* ---- q_map producer rows (clip_fdt.py:86-92) ---------------------------------------------------- */
+int64_t ilfdt_ln_bwd_ws_bytes(int64_t rows, int64_t C) { return rows > 0 ? ln_bwd_ws_floats(rows, C) * 4 : 0; }
+int64_t ilfdt_colsum_ws_bytes(int64_t rows, int64_t C) { return rows > 0 ? colsum_ws_floats(rows, C) * 4 : 0; }
+
+int32_t ilfdt_ln_fwd(const void* src, int32_t src_dtype, const float* bias, const float* gamma, const float* beta,
+                     int64_t rows, int64_t C, float eps, int32_t gelu, void* y_bf16, void* pre_bf16, float* mean,
+                     float* rstd, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(src_dtype);
+  ILFDT_REQUIRE(rows >= 0 && C >= 1 && eps >= 0.f, ILFDT_E_INVALID_ARG, "ln_fwd: bad shape");
+  ILFDT_REQUIRE(rows == 0 || (src && gamma && beta && y_bf16 && mean && rstd), ILFDT_E_INVALID_ARG, "ln_fwd: null pointer");
+  return launch_ln_fwd(src, src_dtype, bias, gamma, beta, rows, C, eps, gelu, y_bf16, pre_bf16, mean, rstd, ST(stream));
+}
+
+int32_t ilfdt_ln_bwd(const float* dy, const void* src, int32_t src_dtype, const float* gamma, const float* mean,
+                     const float* rstd, int64_t rows, int64_t C, int32_t gelu, void* dsrc, int32_t dsrc_dtype,
+                     float* dgamma, float* dbeta, float* dbias, void* ws, int64_t ws_bytes, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(src_dtype);
+  DTYPE_GUARD(dsrc_dtype);
+  ILFDT_REQUIRE(rows >= 1 && C >= 1, ILFDT_E_INVALID_ARG, "ln_bwd: bad shape");
+  ILFDT_REQUIRE(dy && src && gamma && mean && rstd && dsrc && dgamma && dbeta && ws, ILFDT_E_INVALID_ARG,
+                "ln_bwd: null pointer");
+  ILFDT_REQUIRE(ws_bytes >= ilfdt_ln_bwd_ws_bytes(rows, C), ILFDT_E_INVALID_ARG, "ln_bwd: workspace too small");
+  return launch_ln_bwd(dy, src, src_dtype, gamma, mean, rstd, rows, C, gelu, dsrc, dsrc_dtype, dgamma, dbeta, dbias,
+                       (float*)ws, ST(stream));
+}
+
+int32_t ilfdt_bias_cast(const float* src, const float* bias, int64_t rows, int64_t C, void* dst, int32_t dst_dtype,
+                        void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(dst_dtype);
+  ILFDT_REQUIRE(rows >= 0 && C >= 1 && (rows == 0 || (src && bias && dst)), ILFDT_E_INVALID_ARG, "bias_cast: bad arguments");
+  return launch_bias_cast(src, bias, rows, C, dst, dst_dtype, ST(stream));
+}
+
+int32_t ilfdt_colsum(const void* src, int32_t src_dtype, int64_t rows, int64_t C, float* out, void* ws,
+                     int64_t ws_bytes, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(src_dtype);
+  ILFDT_REQUIRE(rows >= 1 && C >= 1 && src && out && ws, ILFDT_E_INVALID_ARG, "colsum: bad arguments");
+  ILFDT_REQUIRE(ws_bytes >= ilfdt_colsum_ws_bytes(rows, C), ILFDT_E_INVALID_ARG, "colsum: workspace too small");
+  return launch_colsum(src, src_dtype, rows, C, out, (float*)ws, ST(stream));
 }
 
 }  // extern "C"

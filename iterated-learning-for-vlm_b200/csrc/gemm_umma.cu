@@ -54,6 +54,10 @@ struct UmmaParams {
   float alpha;
   const float* alpha_dev;
   int accumulate;
+  // EPI_STORE_T, MN-major, split reduction (weight-gradient shapes: short M, N and a very long Kr): item chunk index
+  // = ks * num_n_tiles + n_tile; split ks contracts k-blocks [ks*kb_per, (ks+1)*kb_per) into its own output slab
+  int ksplit, kb_per;
+  int64_t split_stride;   // elements between slabs
   // EPI_POOLMAX
   const float* mask;
   int n_tok, spt, n_samples;
@@ -125,7 +129,14 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       uint32_t stage = 0, phase = 0, it = 0;
       const uint32_t tx_bytes = (A_RES ? 0u : (uint32_t)UM_A_BYTES) + (uint32_t)p.block_n * 128u;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
-        const int m_tile = item % p.num_m_tiles, chunk = item / p.num_m_tiles;
+        const int m_tile = item % p.num_m_tiles;
+        int chunk = item / p.num_m_tiles, kb0 = 0, kb1 = p.nkb;
+        if (EPI == EPI_STORE_T && !A_RES && p.ksplit > 1) {
+          const int ks = chunk / num_n_tiles;
+          chunk -= ks * num_n_tiles;
+          kb0 = ks * p.kb_per;
+          kb1 = min(p.nkb, kb0 + p.kb_per);
+        }
         const int n_begin = chunk * tiles_per_chunk, n_end = min(num_n_tiles, n_begin + tiles_per_chunk);
         if (A_RES) {
           mbar_wait(&bars->a_empty, (it & 1) ^ 1);
@@ -134,7 +145,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             tma_load_2d(smem + kb * UM_A_BYTES, &tmA, &bars->a_full, kb * UM_BK, m_tile * UM_BM, kEvictLast);
         }
         for (int n = n_begin; n < n_end; ++n) {
-          for (int kb = 0; kb < p.nkb; ++kb) {
+          for (int kb = kb0; kb < kb1; ++kb) {
             mbar_wait(&bars->empty[stage], phase ^ 1);
             mbar_expect_tx(&bars->full[stage], tx_bytes);
             uint8_t* st = ring + stage * STAGE_BYTES;
@@ -163,7 +174,13 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (elect_one()) {
       uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0, it = 0;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
-        const int chunk = item / p.num_m_tiles;
+        int chunk = item / p.num_m_tiles, kb0 = 0, kb1 = p.nkb;
+        if (EPI == EPI_STORE_T && !A_RES && p.ksplit > 1) {
+          const int ks = chunk / num_n_tiles;
+          chunk -= ks * num_n_tiles;
+          kb0 = ks * p.kb_per;
+          kb1 = min(p.nkb, kb0 + p.kb_per);
+        }
         const int n_begin = chunk * tiles_per_chunk, n_end = min(num_n_tiles, n_begin + tiles_per_chunk);
         if (A_RES) {
           mbar_wait(&bars->a_full, it & 1);
@@ -173,7 +190,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
           fence_after_sync();
           const uint32_t tmem_d = tmem_base + acc * UM_ACC_COLS;
-          for (int kb = 0; kb < p.nkb; ++kb) {
+          for (int kb = kb0; kb < kb1; ++kb) {
             mbar_wait(&bars->full[stage], phase);
             fence_after_sync();
             uint8_t* st = ring + stage * STAGE_BYTES;
@@ -184,7 +201,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
               for (int k4 = 0; k4 < UM_BK / 16; ++k4)
                 mma_f16(tmem_d, advance_desc_k(adesc, k4 * 2048), advance_desc_k(bdesc, k4 * 2048), p.idesc,
-                        (kb | k4) != 0 ? 1u : 0u);
+                        ((kb - kb0) | k4) != 0 ? 1u : 0u);
             } else {
             const uint64_t adesc = make_smem_desc_sw128(smem_u32(A_RES ? smem + kb * UM_A_BYTES : st));
             const uint64_t bdesc = make_smem_desc_sw128(smem_u32(A_RES ? st : st + UM_A_BYTES));
@@ -212,7 +229,14 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     uint32_t tile_seq = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
-      const int m_tile = item % p.num_m_tiles, chunk = item / p.num_m_tiles;
+      const int m_tile = item % p.num_m_tiles;
+      int chunk = item / p.num_m_tiles;
+      float* out_base = p.out;
+      if (EPI == EPI_STORE_T && !A_RES && p.ksplit > 1) {
+        const int ks = chunk / num_n_tiles;
+        chunk -= ks * num_n_tiles;
+        out_base += (int64_t)ks * p.split_stride;
+      }
       const int n_begin = chunk * tiles_per_chunk, n_end = min(num_n_tiles, n_begin + tiles_per_chunk);
       const int row = m_tile * UM_BM + quad * 32 + lane;  // A row owned by this thread
       const bool row_ok = row < p.m_rows;
@@ -241,7 +265,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if (row_ok) {
               // one pointer stepped by ldo; the full-chunk overwrite case is branch-free (the generic form cost ~24
               // instructions per stored value and made g = df.sd^T epilogue-bound: 1.07 ms for 0.26 ms of MMA)
-              float* o = p.out + (int64_t)(n0 + c0) * ldo_ + row;
+              float* o = out_base + (int64_t)(n0 + c0) * ldo_ + row;
               if (c0 + 32 <= ncols && !p.accumulate) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j, o += ldo_) *o = alpha * __uint_as_float(v[j]);
@@ -533,6 +557,77 @@ int32_t launch_gemm_tn_bf16(const void* A, const void* B, int64_t M, int64_t N, 
   rc = make_tmap_bf16(&tmB, B, Kr, N, N, 64);
   if (rc != ILFDT_OK) return rc;
   return launch_umma_t<EPI_STORE_T, false>(tmA, tmB, p, st);
+}
+
+// The same contraction for weight-gradient shapes (dW[N,M] = B[Kr,N]^T . A[Kr,M] with M, N of a few hundred and Kr in the
+// millions: q_map's Linear layers, clip_fdt.py:88,91): the plain launch has only ceil(M/128) * ceil(N/256) tiles. Here
+// the reduction is split so that tiles x splits fills the SMs once; every split writes its own [N, M] slab of `ws`
+// (no atomics) and a second kernel sums the slabs in a fixed order: deterministic.
+static void plan_ksplit(int64_t M, int64_t N, int64_t Kr, int& ksplit, int& kb_per) {
+  const int tiles = (int)(cdiv(M, UM_BM) * cdiv(N, std::min<int64_t>(256, round_up(N, 64))));
+  const int nkb = (int)cdiv(Kr, UM_BK);
+  int want = std::max(1, sm_count() / std::max(1, tiles));
+  want = std::min(want, std::max(1, nkb / 8));   // at least 8 k-blocks per split
+  kb_per = (int)cdiv(nkb, want);
+  ksplit = (int)cdiv(nkb, kb_per);
+}
+int64_t gemm_tn_splitk_ws_floats(int64_t M, int64_t N, int64_t Kr) {
+  if (M <= 0 || N <= 0 || Kr <= 0) return 0;
+  int ksplit, kb_per;
+  plan_ksplit(M, N, Kr, ksplit, kb_per);
+  return ksplit > 1 ? (int64_t)ksplit * N * M : 0;
+}
+
+__global__ void slab_reduce_kernel(const float* __restrict__ ws, int nslab, int64_t slab, int64_t M, int64_t ldo,
+                                   int accumulate, float* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= slab) return;
+  float t = 0.f;
+  for (int s = 0; s < nslab; ++s) t += ws[s * slab + i];
+  float* o = out + (i / M) * ldo + (i % M);
+  *o = accumulate ? *o + t : t;
+}
+
+int32_t launch_gemm_tn_splitk_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha,
+                                   int accumulate, float* out, int64_t ldo, float* ws, cudaStream_t st) {
+  if (M == 0 || N == 0) return ILFDT_OK;
+  int ksplit, kb_per;
+  plan_ksplit(M, N, Kr, ksplit, kb_per);
+  if (ksplit <= 1) return launch_gemm_tn_bf16(A, B, M, N, Kr, alpha, accumulate, out, ldo, st);
+  ILFDT_REQUIRE(M % 8 == 0 && N % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE,
+                "gemm_tn(bf16): M, N must be multiples of 8 (TMA row pitch)");
+  ILFDT_REQUIRE(M < (1ll << 31) && N < (1ll << 31) && Kr < (1ll << 31), ILFDT_E_UNSUPPORTED_SHAPE, "dimension too large");
+  ILFDT_REQUIRE(ws != nullptr, ILFDT_E_INVALID_ARG, "gemm_tn_splitk: workspace required");
+  UmmaParams p{};
+  p.block_n = (int)std::min<int64_t>(256, round_up(N, 64));
+  p.n_step = p.block_n;
+  p.out = ws;
+  p.ldo = M;
+  p.alpha = alpha;
+  p.accumulate = 0;
+  p.mn_major = 1;
+  p.m_rows = (int)M;
+  p.n_rows = (int)N;
+  p.nkb = (int)cdiv(Kr, UM_BK);
+  p.num_m_tiles = (int)cdiv(M, UM_BM);
+  p.num_n_tiles = (int)cdiv(N, p.n_step);
+  p.idesc = make_idesc_bf16(UM_BM, p.block_n, 1, 1);
+  p.ksplit = ksplit;
+  p.kb_per = kb_per;
+  p.split_stride = N * M;
+  p.nchunk = p.num_n_tiles * ksplit;
+  p.tiles_per_chunk = 1;
+  CUtensorMap tmA, tmB;
+  int32_t rc = make_tmap_bf16(&tmA, A, Kr, M, M, 64);
+  if (rc != ILFDT_OK) return rc;
+  rc = make_tmap_bf16(&tmB, B, Kr, N, N, 64);
+  if (rc != ILFDT_OK) return rc;
+  rc = launch_umma_t<EPI_STORE_T, false>(tmA, tmB, p, st);
+  if (rc != ILFDT_OK) return rc;
+  const int64_t slab = N * M;
+  slab_reduce_kernel<<<(unsigned)cdiv(slab, 256), 256, 0, st>>>(ws, ksplit, slab, M, ldo, accumulate, out);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
 }
 
 int32_t launch_ground_fwd_bf16(const void* q, const void* sd, const float* mask, int64_t b, int64_t n_tok, int64_t K,

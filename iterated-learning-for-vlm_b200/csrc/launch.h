@@ -50,6 +50,9 @@ int32_t launch_gemm_nt_bf16(const void* A, const void* B, int64_t M, int64_t N, 
                             const float* alpha_dev, int accumulate, float* out, int64_t ldo, cudaStream_t st);
 int32_t launch_gemm_tn_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha, int accumulate,
                             float* out, int64_t ldo, cudaStream_t st);
+int64_t gemm_tn_splitk_ws_floats(int64_t M, int64_t N, int64_t Kr);
+int32_t launch_gemm_tn_splitk_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha,
+                                   int accumulate, float* out, int64_t ldo, float* ws, cudaStream_t st);
 int32_t launch_ground_fwd_bf16(const void* q, const void* sd, const float* mask, int64_t b, int64_t n_tok, int64_t K,
                                int64_t D, float sqrt_d, float temperature, float* pooled, int16_t* arg,
                                cudaStream_t st);
@@ -103,5 +106,18 @@ int32_t launch_nce_bwd_gathered_bf16(const void* x_img, const void* x_txt, const
                                      int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset,
                                      const float* lse_i_all, const float* lse_t_all, const float* go_all,
                                      float* dx_img, float* dx_txt, float* dscale, cudaStream_t st);
+
+// qmap_rows.cu
+int64_t ln_bwd_ws_floats(int64_t rows, int64_t C);
+int64_t colsum_ws_floats(int64_t rows, int64_t C);
+int32_t launch_ln_fwd(const void* src, int src_dtype, const float* bias, const float* gamma, const float* beta,
+                      int64_t rows, int64_t C, float eps, int gelu, void* y, void* pre, float* mean, float* rstd,
+                      cudaStream_t st);
+int32_t launch_ln_bwd(const float* dy, const void* src, int src_dtype, const float* gamma, const float* mean,
+                      const float* rstd, int64_t rows, int64_t C, int gelu, void* dsrc, int dsrc_dtype, float* dgamma,
+                      float* dbeta, float* dbias, float* ws, cudaStream_t st);
+int32_t launch_bias_cast(const float* src, const float* bias, int64_t rows, int64_t C, void* dst, int dst_dtype,
+                         cudaStream_t st);
+int32_t launch_colsum(const void* src, int src_dtype, int64_t rows, int64_t C, float* out, float* ws, cudaStream_t st);
 
 }  // namespace ilfdt

@@ -1,0 +1,337 @@
+// Row kernels of the q_map producer (clip_fdt.py:86-92: LayerNorm -> Linear -> GELU -> LayerNorm ->
+// Linear). The two Linear layers run on the tcgen05 contraction kernels (gemm_umma.cu); everything between them is
+// here: LayerNorm forward with an optional bias + exact-erf GELU in front of it, its backward (through the GELU when
+// there is one) with deterministic two-stage column sums for the affine / bias gradients, the bias add + bf16 cast of
+// the last layer, and a column sum. All HBM-bound: one warp per row, the row held in registers (C/32 values per lane,
+// C in {256, 512, 768, 1024}), 16-byte accesses, no atomics.
+#include "common.cuh"
+#include "launch.h"
+#include <algorithm>
+
+namespace ilfdt {
+
+constexpr int QM_THREADS = 256;            // 8 warps = 8 rows in flight per CTA
+constexpr int QM_WARPS = QM_THREADS / 32;
+
+__device__ __forceinline__ float gelu_erf(float v) { return 0.5f * v * (1.f + erff(v * 0.70710678118654752440f)); }
+// d/dv [ v * Phi(v) ] = Phi(v) + v * phi(v)
+__device__ __forceinline__ float gelu_erf_grad(float v) {
+  const float cdf = 0.5f * (1.f + erff(v * 0.70710678118654752440f));
+  const float pdf = 0.39894228040143267794f * __expf(-0.5f * v * v);
+  return fmaf(v, pdf, cdf);
+}
+
+// 4 consecutive elements <-> fp32 registers, fp32 or bf16 storage
+__device__ __forceinline__ void ld4(const float* p, float (&v)[4]) {
+  float4 a = *reinterpret_cast<const float4*>(p);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+}
+__device__ __forceinline__ void ld4(const __nv_bfloat16* p, float (&v)[4]) {
+  uint2 r = *reinterpret_cast<const uint2*>(p);
+  v[0] = __uint_as_float(r.x << 16); v[1] = __uint_as_float(r.x & 0xffff0000u);
+  v[2] = __uint_as_float(r.y << 16); v[3] = __uint_as_float(r.y & 0xffff0000u);
+}
+__device__ __forceinline__ void st4(float* p, const float (&v)[4]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+__device__ __forceinline__ void st4(__nv_bfloat16* p, const float (&v)[4]) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]);
+  __nv_bfloat162 b = __floats2bfloat162_rn(v[2], v[3]);
+  uint2 r;
+  r.x = *reinterpret_cast<uint32_t*>(&a);
+  r.y = *reinterpret_cast<uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = r;
+}
+
+// y = LN(act(src + bias)) * gamma + beta, act = GELU (erf) or identity; mean / rstd saved per row.
+// GELU: the pre-activation u = src + bias is stored as bf16 (`pre`), which is what the backward differentiates.
+// NV = C / 128 float4 groups per lane; column of element e of group j: j*128 + lane*4 + e.
+template <int NV, bool GELU, typename TIn>
+__global__ void __launch_bounds__(QM_THREADS)
+ln_fwd_kernel(const TIn* __restrict__ src, const float* __restrict__ bias, const float* __restrict__ gamma,
+              const float* __restrict__ beta, int64_t rows, float eps, __nv_bfloat16* __restrict__ y,
+              __nv_bfloat16* __restrict__ pre, float* __restrict__ mean, float* __restrict__ rstd) {
+  constexpr int C = NV * 128;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = (int64_t)blockIdx.x * QM_WARPS + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)gridDim.x * QM_WARPS;
+  float gm[NV][4], bt[NV][4], bs[NV][4];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    ld4(gamma + j * 128 + lane * 4, gm[j]);
+    ld4(beta + j * 128 + lane * 4, bt[j]);
+    if (GELU) ld4(bias + j * 128 + lane * 4, bs[j]);
+  }
+  for (int64_t r = warp0; r < rows; r += nwarps) {
+    float v[NV][4];
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      ld4(src + r * C + j * 128 + lane * 4, v[j]);
+      if (GELU) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) v[j][e] += bs[j][e];
+        st4(pre + r * C + j * 128 + lane * 4, v[j]);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) v[j][e] = gelu_erf(v[j][e]);
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) s += v[j][e];
+    }
+    const float mu = warp_sum(s) * (1.f / C);
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float d = v[j][e] - mu;
+        q = fmaf(d, d, q);
+      }
+    const float rs = rsqrtf(warp_sum(q) * (1.f / C) + eps);   // biased variance, as nn.LayerNorm
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      float o[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) o[e] = fmaf((v[j][e] - mu) * rs, gm[j][e], bt[j][e]);
+      st4(y + r * C + j * 128 + lane * 4, o);
+    }
+    if (lane == 0) {
+      mean[r] = mu;
+      rstd[r] = rs;
+    }
+  }
+}
+
+// Backward of y = LN(act(src)) * gamma + beta for a given dy [rows, C] (fp32):
+//   xhat = (act(src) - mean) * rstd;  dxhat = dy * gamma
+//   d act = rstd * (dxhat - mean_c(dxhat) - xhat * mean_c(dxhat * xhat));  dsrc = d act * act'(src)
+// and the per-CTA column partials part[cta][0] = sum_r dy*xhat (dgamma), [1] = sum_r dy (dbeta), [2] = sum_r dsrc (the
+// gradient of the bias in front of the GELU). dsrc is written as TOut (bf16 when it feeds the next contraction).
+template <int NV, bool GELU, typename TIn, typename TOut>
+__global__ void __launch_bounds__(QM_THREADS)
+ln_bwd_kernel(const float* __restrict__ dy, const TIn* __restrict__ src, const float* __restrict__ gamma,
+              const float* __restrict__ mean, const float* __restrict__ rstd, int64_t rows, TOut* __restrict__ dsrc,
+              float* __restrict__ part) {
+  constexpr int C = NV * 128;
+  __shared__ float red[QM_WARPS][128];
+  const int lane = threadIdx.x & 31;
+  const int wid = threadIdx.x >> 5;
+  const int64_t warp0 = (int64_t)blockIdx.x * QM_WARPS + wid;
+  const int64_t nwarps = (int64_t)gridDim.x * QM_WARPS;
+  float gm[NV][4], ag[NV][4], ab[NV][4], as[NV][4];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    ld4(gamma + j * 128 + lane * 4, gm[j]);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) ag[j][e] = ab[j][e] = as[j][e] = 0.f;
+  }
+  for (int64_t r = warp0; r < rows; r += nwarps) {
+    const float mu = mean[r], rs = rstd[r];
+    float xh[NV][4], dx[NV][4], gp[NV][4];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      float u[4], d[4];
+      ld4(src + r * C + j * 128 + lane * 4, u);
+      ld4(dy + r * C + j * 128 + lane * 4, d);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float a = GELU ? gelu_erf(u[e]) : u[e];
+        gp[j][e] = GELU ? gelu_erf_grad(u[e]) : 1.f;
+        xh[j][e] = (a - mu) * rs;
+        ag[j][e] = fmaf(d[e], xh[j][e], ag[j][e]);
+        ab[j][e] += d[e];
+        dx[j][e] = d[e] * gm[j][e];
+        s1 += dx[j][e];
+        s2 = fmaf(dx[j][e], xh[j][e], s2);
+      }
+    }
+    s1 = warp_sum(s1) * (1.f / C);
+    s2 = warp_sum(s2) * (1.f / C);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      float o[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        o[e] = rs * (dx[j][e] - s1 - xh[j][e] * s2) * gp[j][e];
+        as[j][e] += o[e];
+      }
+      st4(dsrc + r * C + j * 128 + lane * 4, o);
+    }
+  }
+  // CTA partials: fixed order over the 8 warps, one 128-column group at a time
+  float* out = part + (int64_t)blockIdx.x * 3 * C;
+#pragma unroll
+  for (int which = 0; which < (GELU ? 3 : 2); ++which) {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const float(&a)[4] = which == 0 ? ag[j] : which == 1 ? ab[j] : as[j];
+      __syncthreads();
+#pragma unroll
+      for (int e = 0; e < 4; ++e) red[wid][lane * 4 + e] = a[e];
+      __syncthreads();
+      if (threadIdx.x < 128) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < QM_WARPS; ++w) t += red[w][threadIdx.x];
+        out[which * C + j * 128 + threadIdx.x] = t;
+      }
+    }
+  }
+}
+
+// out[c] = sum_p part[p * stride + c]  (fixed order: deterministic), c < cols
+__global__ void partial_reduce_kernel(const float* __restrict__ part, int n_part, int64_t stride, int cols,
+                                      float* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float t = 0.f;
+  for (int p = 0; p < n_part; ++p) t += part[p * stride + c];
+  out[c] = t;
+}
+
+// dst[r, :] = src[r, :] + bias   (bf16 or fp32 out)
+template <typename TOut>
+__global__ void bias_cast_kernel(const float* __restrict__ src, const float* __restrict__ bias, int64_t n4, int C,
+                                 TOut* __restrict__ dst) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float v[4], b[4];
+    ld4(src + i * 4, v);
+    ld4(bias + (int)((i * 4) % C), b);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) v[e] += b[e];
+    st4(dst + i * 4, v);
+  }
+}
+
+// part[cta][c] = sum over the CTA's rows of src[r, c]
+template <typename TIn>
+__global__ void __launch_bounds__(QM_THREADS)
+colsum_partial_kernel(const TIn* __restrict__ src, int64_t rows, int C, float* __restrict__ part) {
+  // thread t owns the 4 columns [4t, 4t+4) of each 1024-column slab; rows strided over CTAs
+  for (int c0 = threadIdx.x * 4; c0 < C; c0 += QM_THREADS * 4) {
+    float a[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
+      float v[4];
+      ld4(src + r * C + c0, v);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) a[e] += v[e];
+    }
+    st4(part + (int64_t)blockIdx.x * C + c0, a);
+  }
+}
+
+static int qm_grid(int64_t rows) {
+  const int64_t want = cdiv(rows, QM_WARPS);
+  return (int)std::max<int64_t>(1, std::min<int64_t>(want, (int64_t)sm_count() * 4));
+}
+
+int64_t ln_bwd_ws_floats(int64_t rows, int64_t C) { return (int64_t)qm_grid(rows) * 3 * C; }
+int64_t colsum_ws_floats(int64_t rows, int64_t C) { return (int64_t)qm_grid(rows) * C; }
+
+template <int NV>
+static int32_t ln_fwd_nv(const void* src, int src_dtype, const float* bias, const float* gamma, const float* beta,
+                         int64_t rows, float eps, int gelu, void* y, void* pre, float* mean, float* rstd,
+                         cudaStream_t st) {
+  const int grid = qm_grid(rows);
+  auto* yb = (__nv_bfloat16*)y;
+  auto* pb = (__nv_bfloat16*)pre;
+  if (gelu) {
+    ILFDT_REQUIRE(src_dtype == ILFDT_F32 && bias && pre, ILFDT_E_INVALID_ARG,
+                  "ln_fwd: the GELU form takes an fp32 src, a bias and a `pre` buffer");
+    ln_fwd_kernel<NV, true, float><<<grid, QM_THREADS, 0, st>>>((const float*)src, bias, gamma, beta, rows, eps, yb, pb,
+                                                                 mean, rstd);
+  } else if (src_dtype == ILFDT_F32) {
+    ln_fwd_kernel<NV, false, float><<<grid, QM_THREADS, 0, st>>>((const float*)src, nullptr, gamma, beta, rows, eps, yb,
+                                                                  nullptr, mean, rstd);
+  } else {
+    ln_fwd_kernel<NV, false, __nv_bfloat16><<<grid, QM_THREADS, 0, st>>>((const __nv_bfloat16*)src, nullptr, gamma, beta,
+                                                                          rows, eps, yb, nullptr, mean, rstd);
+  }
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
+int32_t launch_ln_fwd(const void* src, int src_dtype, const float* bias, const float* gamma, const float* beta,
+                      int64_t rows, int64_t C, float eps, int gelu, void* y, void* pre, float* mean, float* rstd,
+                      cudaStream_t st) {
+  if (rows == 0) return ILFDT_OK;
+  switch (C) {
+    case 256: return ln_fwd_nv<2>(src, src_dtype, bias, gamma, beta, rows, eps, gelu, y, pre, mean, rstd, st);
+    case 512: return ln_fwd_nv<4>(src, src_dtype, bias, gamma, beta, rows, eps, gelu, y, pre, mean, rstd, st);
+    case 768: return ln_fwd_nv<6>(src, src_dtype, bias, gamma, beta, rows, eps, gelu, y, pre, mean, rstd, st);
+    case 1024: return ln_fwd_nv<8>(src, src_dtype, bias, gamma, beta, rows, eps, gelu, y, pre, mean, rstd, st);
+  }
+  return fail(ILFDT_E_UNSUPPORTED_SHAPE, "ln_fwd: width %lld not in {256,512,768,1024}", (long long)C);
+}
+
+template <int NV>
+static int32_t ln_bwd_nv(const float* dy, const void* src, int src_dtype, const float* gamma, const float* mean,
+                         const float* rstd, int64_t rows, int gelu, void* dsrc, int dsrc_dtype, float* dgamma,
+                         float* dbeta, float* dbias, float* ws, cudaStream_t st) {
+  constexpr int C = NV * 128;
+  const int grid = qm_grid(rows);
+  if (gelu) {
+    ILFDT_REQUIRE(src_dtype == ILFDT_BF16 && dsrc_dtype == ILFDT_BF16, ILFDT_E_INVALID_ARG,
+                  "ln_bwd: the GELU form reads the bf16 pre-activation and writes a bf16 gradient");
+    ln_bwd_kernel<NV, true, __nv_bfloat16, __nv_bfloat16><<<grid, QM_THREADS, 0, st>>>(
+        dy, (const __nv_bfloat16*)src, gamma, mean, rstd, rows, (__nv_bfloat16*)dsrc, ws);
+  } else {
+    ILFDT_REQUIRE(dsrc_dtype == ILFDT_F32, ILFDT_E_INVALID_ARG, "ln_bwd: the plain form writes an fp32 gradient");
+    if (src_dtype == ILFDT_F32)
+      ln_bwd_kernel<NV, false, float, float><<<grid, QM_THREADS, 0, st>>>(dy, (const float*)src, gamma, mean, rstd, rows,
+                                                                         (float*)dsrc, ws);
+    else
+      ln_bwd_kernel<NV, false, __nv_bfloat16, float><<<grid, QM_THREADS, 0, st>>>(dy, (const __nv_bfloat16*)src, gamma,
+                                                                                 mean, rstd, rows, (float*)dsrc, ws);
+  }
+  ILFDT_LAUNCH_OK();
+  const int tb = 128, gb = (int)cdiv(C, tb);
+  partial_reduce_kernel<<<gb, tb, 0, st>>>(ws, grid, 3 * C, C, dgamma);
+  partial_reduce_kernel<<<gb, tb, 0, st>>>(ws + C, grid, 3 * C, C, dbeta);
+  if (gelu && dbias) partial_reduce_kernel<<<gb, tb, 0, st>>>(ws + 2 * C, grid, 3 * C, C, dbias);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
+int32_t launch_ln_bwd(const float* dy, const void* src, int src_dtype, const float* gamma, const float* mean,
+                      const float* rstd, int64_t rows, int64_t C, int gelu, void* dsrc, int dsrc_dtype, float* dgamma,
+                      float* dbeta, float* dbias, float* ws, cudaStream_t st) {
+  ILFDT_REQUIRE(rows > 0, ILFDT_E_INVALID_ARG, "ln_bwd: no rows");
+  switch (C) {
+    case 256: return ln_bwd_nv<2>(dy, src, src_dtype, gamma, mean, rstd, rows, gelu, dsrc, dsrc_dtype, dgamma, dbeta, dbias, ws, st);
+    case 512: return ln_bwd_nv<4>(dy, src, src_dtype, gamma, mean, rstd, rows, gelu, dsrc, dsrc_dtype, dgamma, dbeta, dbias, ws, st);
+    case 768: return ln_bwd_nv<6>(dy, src, src_dtype, gamma, mean, rstd, rows, gelu, dsrc, dsrc_dtype, dgamma, dbeta, dbias, ws, st);
+    case 1024: return ln_bwd_nv<8>(dy, src, src_dtype, gamma, mean, rstd, rows, gelu, dsrc, dsrc_dtype, dgamma, dbeta, dbias, ws, st);
+  }
+  return fail(ILFDT_E_UNSUPPORTED_SHAPE, "ln_bwd: width %lld not in {256,512,768,1024}", (long long)C);
+}
+
+int32_t launch_bias_cast(const float* src, const float* bias, int64_t rows, int64_t C, void* dst, int dst_dtype,
+                         cudaStream_t st) {
+  if (rows == 0) return ILFDT_OK;
+  ILFDT_REQUIRE(C % 4 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "bias_cast: width must be a multiple of 4");
+  const int64_t n4 = rows * C / 4;
+  const int grid = (int)std::min<int64_t>(cdiv(n4, 256), (int64_t)sm_count() * 16);
+  if (dst_dtype == ILFDT_BF16)
+    bias_cast_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(src, bias, n4, (int)C, (__nv_bfloat16*)dst);
+  else
+    bias_cast_kernel<float><<<grid, 256, 0, st>>>(src, bias, n4, (int)C, (float*)dst);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
+int32_t launch_colsum(const void* src, int src_dtype, int64_t rows, int64_t C, float* out, float* ws, cudaStream_t st) {
+  ILFDT_REQUIRE(rows > 0 && C % 4 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "colsum: rows > 0 and width a multiple of 4");
+  const int grid = qm_grid(rows);
+  if (src_dtype == ILFDT_BF16)
+    colsum_partial_kernel<__nv_bfloat16><<<grid, QM_THREADS, 0, st>>>((const __nv_bfloat16*)src, rows, (int)C, ws);
+  else
+    colsum_partial_kernel<float><<<grid, QM_THREADS, 0, st>>>((const float*)src, rows, (int)C, ws);
+  ILFDT_LAUNCH_OK();
+  partial_reduce_kernel<<<(int)cdiv(C, 128), 128, 0, st>>>(ws, grid, C, (int)C, out);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
+}  // namespace ilfdt

@@ -37,6 +37,8 @@ SIGNATURES = {
     "ilfdt_sparsemax_bwd": (_i32, [_p, _p, _i64, _i64, _p, _p]),
     "ilfdt_gemm_nt": (_i32, [_p, _p, _i32, _i64, _i64, _i64, _f, _i32, _p, _i64, _p]),
     "ilfdt_gemm_tn": (_i32, [_p, _p, _i64, _i64, _i64, _f, _i32, _p, _i64, _p]),
+    "ilfdt_gemm_tn_splitk_ws_bytes": (_i64, [_i64, _i64, _i64]),
+    "ilfdt_gemm_tn_splitk": (_i32, [_p, _p, _i64, _i64, _i64, _f, _i32, _p, _i64, _p, _i64, _p]),
     "ilfdt_gemm_f32_strided": (_i32, [_p, _i64, _i64, _p, _i64, _i64, _p, _i64, _i64, _i64, _i64, _i64, _f, _i32, _p]),
     "ilfdt_ground_bwd": (_i32, [_p, _p, _p, _p, _p, _i32, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _p, _i32, _p, _p]),
     "ilfdt_ground_bwd_w16": (_i32, [_p, _p, _p, _p, _p, _i32, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _p, _i32, _p, _p]),
@@ -59,6 +61,12 @@ SIGNATURES = {
     "ilfdt_ce_rows_bwd": (_i32, [_p, _i64, _i64, _i64, _p, _p, _f, _p, _p]),
     "ilfdt_topk_hits": (_i32, [_p, _i64, _i64, _i64, _p, _p]),
     "ilfdt_nce_topk_hits": (_i32, [_p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _p, _p, _i64, _p]),
+    "ilfdt_ln_fwd": (_i32, [_p, _i32, _p, _p, _p, _i64, _i64, _f, _i32, _p, _p, _p, _p, _p]),
+    "ilfdt_ln_bwd_ws_bytes": (_i64, [_i64, _i64]),
+    "ilfdt_ln_bwd": (_i32, [_p, _p, _i32, _p, _p, _p, _i64, _i64, _i32, _p, _i32, _p, _p, _p, _p, _i64, _p]),
+    "ilfdt_bias_cast": (_i32, [_p, _p, _i64, _i64, _p, _i32, _p]),
+    "ilfdt_colsum_ws_bytes": (_i64, [_i64, _i64]),
+    "ilfdt_colsum": (_i32, [_p, _i32, _i64, _i64, _p, _p, _i64, _p]),
     "ilfdt_randn_fill": (_i32, [_p, _i64, _u64, _u32, _p]),
     "ilfdt_copy": (_i32, [_p, _p, _i64, _p]),
 }
@@ -80,7 +88,7 @@ def load():
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.ilfdt_abi_version() != 2:
+    if lib.ilfdt_abi_version() != 3:
         raise RuntimeError("libilfdt ABI version mismatch")
     _lib = lib
     return lib

@@ -144,6 +144,78 @@ class GroundingFunction(torch.autograd.Function):
         return dq, dsd, None, None, None, None
 
 
+# q_map on the library's kernels: off by default -- the reference keeps it an fp32 nn.Sequential and
+# the fp32 parity mode always does; ilfdt.set_fused_q_map(True) / ILFDT_FUSED_QMAP=1 turns it on for the bf16 mode
+FUSED_QMAP = os.environ.get("ILFDT_FUSED_QMAP", "0") != "0"
+QMAP_WIDTHS = (256, 512, 768, 1024)
+
+
+def set_fused_q_map(on):
+    global FUSED_QMAP
+    FUSED_QMAP = bool(on)
+
+
+def fused_q_map_enabled():
+    return FUSED_QMAP and _COMPUTE_DTYPE == "bf16"
+
+
+class QMapFunction(torch.autograd.Function):
+    """Query_model.q_map (clip_fdt.py:86-92,111): LayerNorm(F) -> Linear(F,D) -> GELU -> LayerNorm(D) -> Linear(D,D),
+    x [b,N,F] (f32 or bf16) -> q [b,N,D] in bf16, the operand the score kernel streams (no cast pass, half the bytes).
+    Both Linear layers are tcgen05 contractions on bf16 operands with fp32 accumulation; LayerNorm, bias and the exact
+    GELU are row kernels in fp32 (csrc/qmap_rows.cu). Saved for the backward: the two bf16 LayerNorm outputs, the bf16
+    pre-GELU activation and the per-row mean / rstd -- 6 bytes per element of the hidden width."""
+
+    @staticmethod
+    def forward(ctx, x, ln1_w, ln1_b, w1, b1, ln2_w, ln2_b, w2, b2, eps1, eps2):
+        D, F = w1.shape
+        if F not in QMAP_WIDTHS or D not in QMAP_WIDTHS or tuple(w2.shape) != (D, D):
+            raise NotImplementedError("ilfdt fused q_map: widths %s -> %s outside %s" % (F, D, (QMAP_WIDTHS,)))
+        x2 = x.detach().reshape(-1, F).contiguous()
+        f32 = lambda t: t.detach().float().contiguous()
+        ln1_w, ln1_b, b1, ln2_w, ln2_b, b2 = map(f32, (ln1_w, ln1_b, b1, ln2_w, ln2_b, b2))
+        xn, _, mean1, rstd1 = ops.ln_fwd(x2, ln1_w, ln1_b, eps1)
+        h = ops.gemm_nt(ops.cast_bf16(f32(w1)), xn)                    # [R,D] = xn . W1^T
+        a2, u, mean2, rstd2 = ops.ln_fwd(h, ln2_w, ln2_b, eps2, bias=b1)
+        del h
+        h = ops.gemm_nt(ops.cast_bf16(f32(w2)), a2)                    # [R,D] = a2 . W2^T
+        q = ops.bias_cast(h, b2, torch.bfloat16)
+        ctx.save_for_backward(x2, xn, mean1, rstd1, ln1_w, w1, u, a2, mean2, rstd2, ln2_w, w2)
+        ctx.x_shape, ctx.x_dtype = x.shape, x.dtype
+        return q.view(*x.shape[:-1], D)
+
+    @staticmethod
+    def backward(ctx, dq):
+        x2, xn, mean1, rstd1, ln1_w, w1, u, a2, mean2, rstd2, ln2_w, w2 = ctx.saved_tensors
+        D, F = w1.shape
+        dq2 = dq.reshape(-1, D).contiguous()
+        db2 = ops.colsum(dq2)
+        dq_b = dq2 if dq2.dtype == torch.bfloat16 else ops.cast_bf16(dq2.float())
+        dw2 = ops.gemm_tn_splitk(a2, dq_b)                                     # [D_out, D_in] = dq^T . a2
+        da2 = ops.gemm_nt(ops.transpose_bf16(w2.detach().float().contiguous()), dq_b)   # [R, D_in] = dq . W2
+        du, dln2_w, dln2_b, db1 = ops.ln_bwd(da2, u, ln2_w, mean2, rstd2, gelu=True)
+        del da2
+        dw1 = ops.gemm_tn_splitk(xn, du)                                       # [D, F] = du^T . xn
+        dxn = ops.gemm_nt(ops.transpose_bf16(w1.detach().float().contiguous()), du)     # [R, F] = du . W1
+        dx, dln1_w, dln1_b, _ = ops.ln_bwd(dxn, x2, ln1_w, mean1, rstd1, gelu=False)
+        del dxn
+        if not ctx.needs_input_grad[0]:
+            dx = None
+        else:
+            if ctx.x_dtype == torch.bfloat16:
+                dx = ops.cast_bf16(dx)
+            dx = dx.view(ctx.x_shape)
+        return dx, dln1_w, dln1_b, dw1, db1, dln2_w, dln2_b, dw2, db2, None, None
+
+
+def q_map_apply(q_map, x):
+    """Runs a reference-shaped q_map nn.Sequential (LayerNorm, Linear, GELU, LayerNorm, Linear) through QMapFunction;
+    parameter names and shapes are untouched, so checkpoints interchange."""
+    ln1, fc1, _act, ln2, fc2 = q_map
+    return QMapFunction.apply(x, ln1.weight, ln1.bias, fc1.weight, fc1.bias, ln2.weight, ln2.bias, fc2.weight, fc2.bias,
+                              ln1.eps, ln2.eps)
+
+
 class GroundingVariantFunction(torch.autograd.Function):
     """Query_model.forward from q onward for the non-default-tuned combinations of
     att_func_type in {softmax, sigmoid, sparsemax} x pool_type in {sum, mean, max} (clip_fdt.py:67-78,

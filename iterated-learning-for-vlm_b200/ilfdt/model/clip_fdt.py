@@ -51,7 +51,11 @@ class Query_model(nn.Module):
     def forward(self, ft, sd, mask=None, return_token_att=False, need_weights=True):
         # need_weights=False (an addition to the reference signature, used by Clip_FDT.forward which drops
         # att_weight): the tuned route returns att_weight as its bf16 tensor-core copy, not differentiable
-        q = self.q_map(ft)
+        if Fn.fused_q_map_enabled():
+            # the MLP on the library's kernels, q handed over in bf16 (same parameters, same names)
+            q = Fn.q_map_apply(self.q_map, ft)
+        else:
+            q = self.q_map(ft)
         if mask is not None:
             assert mask.shape == q.shape[:2]
         if self.att_func_type == 'sparsemax' and self.pool_type == 'max':

@@ -23,7 +23,8 @@ _KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mas
                      "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2, "ilfdt_ground_bwd_w16": 2,
                      "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5,
                      "ilfdt_nce_bwd": 4, "ilfdt_nce_bwd_gathered": 2, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
-                     "ilfdt_randn_fill": 1, "ilfdt_copy": 0}
+                     "ilfdt_randn_fill": 1, "ilfdt_copy": 0,
+                     "ilfdt_gemm_tn_splitk": 2, "ilfdt_ln_fwd": 1, "ilfdt_ln_bwd": 4, "ilfdt_bias_cast": 1, "ilfdt_colsum": 2}
 
 
 def _call(name, *args):
@@ -214,6 +215,23 @@ def gemm_tn(A, B, alpha=1.0, out=None, accumulate=False):
         out = torch.empty(N, M, dtype=torch.float32, device=A.device)
     _req(out, torch.float32, "out")
     _call("ilfdt_gemm_tn", _ptr(A), _ptr(B), M, N, Kr, float(alpha), int(accumulate), _ptr(out), out.shape[1], _stream())
+    return out
+
+
+def gemm_tn_splitk(A, B, alpha=1.0, out=None, accumulate=False):
+    """gemm_tn with the reduction split over the SMs (weight-gradient shapes); same contract."""
+    _req(A, torch.bfloat16, "A"); _req(B, torch.bfloat16, "B")
+    Kr, M = A.shape
+    N = B.shape[1]
+    assert B.shape[0] == Kr
+    if out is None:
+        assert not accumulate
+        out = torch.empty(N, M, dtype=torch.float32, device=A.device)
+    _req(out, torch.float32, "out")
+    nws = _lib.load().ilfdt_gemm_tn_splitk_ws_bytes(M, N, Kr)
+    ws = torch.empty(max(nws, 4), dtype=torch.uint8, device=A.device)
+    _call("ilfdt_gemm_tn_splitk", _ptr(A), _ptr(B), M, N, Kr, float(alpha), int(accumulate), _ptr(out), out.shape[1],
+          _ptr(ws), nws, _stream())
     return out
 
 
@@ -450,3 +468,55 @@ def copy_(dst, src):
     assert dst.numel() == src.numel()
     _call("ilfdt_copy", _ptr(dst), _ptr(src), dst.numel() * dst.element_size(), _stream())
     return dst
+
+
+# ---- q_map producer rows (clip_fdt.py:86-92) -----------------------------------------
+def ln_fwd(src, gamma, beta, eps, bias=None):
+    """y = LayerNorm(act(src + bias)) as bf16 [R,C] with mean, rstd [R]. bias given: act = exact GELU, src is the fp32
+    output of the preceding Linear without its bias, and the bf16 pre-activation is returned as well."""
+    _req(src, None, "src"); _req(gamma, torch.float32, "gamma"); _req(beta, torch.float32, "beta")
+    R, C = src.shape
+    y = torch.empty(R, C, dtype=torch.bfloat16, device=src.device)
+    mean = torch.empty(R, dtype=torch.float32, device=src.device)
+    rstd = torch.empty_like(mean)
+    pre = None
+    if bias is not None:
+        _req(bias, torch.float32, "bias")
+        pre = torch.empty_like(y)
+    _call("ilfdt_ln_fwd", _ptr(src), _DT[src.dtype], _ptr(bias), _ptr(gamma), _ptr(beta), R, C, float(eps),
+          int(bias is not None), _ptr(y), _ptr(pre), _ptr(mean), _ptr(rstd), _stream())
+    return y, pre, mean, rstd
+
+
+def ln_bwd(dy, src, gamma, mean, rstd, gelu):
+    """-> dsrc (bf16 through the GELU, else f32), dgamma, dbeta, dbias (GELU form only, else None)."""
+    _req(dy, torch.float32, "dy"); _req(src, None, "src"); _req(gamma, torch.float32, "gamma")
+    R, C = dy.shape
+    assert src.shape == dy.shape
+    dsrc = torch.empty(R, C, dtype=torch.bfloat16 if gelu else torch.float32, device=dy.device)
+    dgamma = torch.empty(C, dtype=torch.float32, device=dy.device)
+    dbeta = torch.empty_like(dgamma)
+    dbias = torch.empty_like(dgamma) if gelu else None
+    nws = _lib.load().ilfdt_ln_bwd_ws_bytes(R, C)
+    ws = torch.empty(nws, dtype=torch.uint8, device=dy.device)
+    _call("ilfdt_ln_bwd", _ptr(dy), _ptr(src), _DT[src.dtype], _ptr(gamma), _ptr(mean), _ptr(rstd), R, C, int(gelu),
+          _ptr(dsrc), _DT[dsrc.dtype], _ptr(dgamma), _ptr(dbeta), _ptr(dbias), _ptr(ws), nws, _stream())
+    return dsrc, dgamma, dbeta, dbias
+
+
+def bias_cast(src, bias, out_dtype=torch.bfloat16):
+    _req(src, torch.float32, "src"); _req(bias, torch.float32, "bias")
+    R, C = src.shape
+    out = torch.empty(R, C, dtype=out_dtype, device=src.device)
+    _call("ilfdt_bias_cast", _ptr(src), _ptr(bias), R, C, _ptr(out), _DT[out_dtype], _stream())
+    return out
+
+
+def colsum(src):
+    _req(src, None, "src")
+    R, C = src.shape
+    out = torch.empty(C, dtype=torch.float32, device=src.device)
+    nws = _lib.load().ilfdt_colsum_ws_bytes(R, C)
+    ws = torch.empty(nws, dtype=torch.uint8, device=src.device)
+    _call("ilfdt_colsum", _ptr(src), _DT[src.dtype], R, C, _ptr(out), _ptr(ws), nws, _stream())
+    return out

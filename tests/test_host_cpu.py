@@ -37,7 +37,7 @@ def test_abi_exports_every_declared_symbol(built_lib):
     for n in names:
         assert hasattr(lib, n), "libilfdt.so does not export %s" % n
     lib.ilfdt_abi_version.restype = ctypes.c_int32
-    assert lib.ilfdt_abi_version() == 2
+    assert lib.ilfdt_abi_version() == 3
 
 
 def test_python_binding_covers_the_header(built_lib):

@@ -93,6 +93,22 @@ def test_gemm_tn_tcgen05(ops, M, N, K):
     assert_close(out2, 1.5 * ref, 2e-5, "gemm_tn bf16 accumulate")
 
 
+@pytest.mark.parametrize("M,N,K", [(768, 512, 20000), (512, 512, 5003), (256, 8, 70001), (512, 16384, 300), (8, 8, 5)])
+def test_gemm_tn_splitk_qmap_weight_gradients(ops, M, N, K):
+    """Split-reduction form of gemm_tn (dW of q_map's Linear layers: short M, N, very long reduction): same values as
+    the fp64 product of the bf16 operands, deterministic (two runs bit-identical), accumulate honoured."""
+    g = torch.Generator().manual_seed(5 * M + N + K)
+    A = bf16_round(torch.randn(K, M, generator=g))
+    B = bf16_round(torch.randn(K, N, generator=g))
+    ref = B.double().t() @ A.double()
+    Ad, Bd = A.to(_dev()).to(torch.bfloat16), B.to(_dev()).to(torch.bfloat16)
+    out = ops.gemm_tn_splitk(Ad, Bd, alpha=0.5)
+    assert_close(out, 0.5 * ref, 2e-5, "gemm_tn_splitk")
+    assert torch.equal(out, ops.gemm_tn_splitk(Ad, Bd, alpha=0.5))
+    out2 = ops.gemm_tn_splitk(Ad, Bd, out=out.clone(), accumulate=True)
+    assert_close(out2, 1.5 * ref, 2e-5, "gemm_tn_splitk accumulate")
+
+
 # ---------------------------------------------------------------------------------------------------
 # a1: score block forward
 # ---------------------------------------------------------------------------------------------------
@@ -981,3 +997,136 @@ def test_reference_checkpoint_eval_embeddings(ops, golden_dir, mode):
         torch.nn.functional.normalize(torch.tensor(z["txt_sd_ft"]), dim=-1).t()
     sim = (torch.nn.functional.normalize(f_i, dim=-1) @ torch.nn.functional.normalize(f_t, dim=-1).t()).cpu()
     assert_close(sim, ref_sim, tol, "retrieval similarities")
+
+
+# ---------------------------------------------------------------------------------------------------
+# q_map on the library's kernels (clip_fdt.py:86-92)
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("R,C", [(1, 256), (37, 512), (300, 768), (9, 1024), (5000, 512)])
+@pytest.mark.parametrize("gelu", [False, True])
+def test_qmap_layernorm_rows(ops, R, C, gelu):
+    """ilfdt_ln_fwd / ilfdt_ln_bwd against nn.LayerNorm (+ bias + exact GELU in front) in fp64 on the CPU. fp32
+    outputs <= 1e-5 (column sums over R rows: 5e-5); bf16 outputs are the fp32 value rounded once: <= 2^-8."""
+    g = torch.Generator().manual_seed(R * 31 + C + int(gelu))
+    src = torch.randn(R, C, generator=g) * 1.5 + 0.3
+    bias = torch.randn(C, generator=g) * 0.2
+    gamma = 1 + 0.1 * torch.randn(C, generator=g)
+    beta = 0.1 * torch.randn(C, generator=g)
+    dy = torch.randn(R, C, generator=g)
+    eps = 1e-5
+    dev = _dev()
+    y, pre, mean, rstd = ops.ln_fwd(src.to(dev), gamma.to(dev), beta.to(dev), eps, bias=bias.to(dev) if gelu else None)
+    # reference: the same chain in fp64; for the GELU form the backward differentiates the stored bf16 pre-activation
+    u = (src + bias).double() if gelu else src.double()
+    a = torch.nn.functional.gelu(u) if gelu else u
+    ref = torch.nn.functional.layer_norm(a, (C,), gamma.double(), beta.double(), eps)
+    assert_close(y.float(), ref, 2 ** -8, "ln_fwd y")
+    assert_close(mean, a.mean(1), FP32_TOL, "mean")
+    assert_close(rstd, 1 / torch.sqrt(a.var(1, unbiased=False) + eps), FP32_TOL, "rstd")
+    if gelu:
+        assert_close(pre.float(), u, 2 ** -8, "pre-activation")
+        u_saved = pre.float().cpu().double().requires_grad_(True)
+        a2 = torch.nn.functional.gelu(u_saved)
+    else:
+        u_saved = src.double().requires_grad_(True)
+        a2 = u_saved
+    gm = gamma.double().requires_grad_(True)
+    bt = beta.double().requires_grad_(True)
+    # the kernel normalises with the forward's mean / rstd (of the unrounded activation): do the same
+    xhat = (a2 - mean.cpu().double()[:, None]) * rstd.cpu().double()[:, None]
+    mu_d, rs_d = a2.mean(1, keepdim=True), 1 / torch.sqrt(a2.var(1, unbiased=False, keepdim=True) + eps)
+    yy = ((a2 - mu_d) * rs_d) * gm + bt
+    yy.backward(dy.double())
+    dsrc, dgamma, dbeta, dbias = ops.ln_bwd(dy.to(dev), pre if gelu else src.to(dev), gamma.to(dev), mean, rstd, gelu)
+    col_tol = 5e-5
+    assert_close(dbeta, bt.grad, col_tol, "dbeta")
+    if gelu:
+        # mean / rstd belong to the unrounded activation, the bf16 pre-activation moves xhat by <= 2^-9 relative
+        assert_close(dgamma, gm.grad, 5e-3, "dgamma")
+        assert_close(dsrc.float(), u_saved.grad, 1e-2, "dsrc (bf16)")
+        assert_close(dbias, u_saved.grad.sum(0), 1e-2, "dbias")
+    else:
+        assert_close(dgamma, gm.grad, col_tol, "dgamma")
+        assert_close(dsrc, u_saved.grad, FP32_TOL * 2, "dsrc")
+        assert dbias is None
+    del xhat
+
+
+@pytest.mark.parametrize("R,C", [(1, 512), (77, 256), (4097, 768)])
+def test_qmap_bias_cast_and_colsum(ops, R, C):
+    g = torch.Generator().manual_seed(R + C)
+    src = torch.randn(R, C, generator=g)
+    bias = torch.randn(C, generator=g)
+    dev = _dev()
+    out32 = ops.bias_cast(src.to(dev), bias.to(dev), torch.float32)
+    assert torch.equal(out32.cpu(), src + bias)
+    out16 = ops.bias_cast(src.to(dev), bias.to(dev), torch.bfloat16)
+    assert torch.equal(out16.cpu(), (src + bias).to(torch.bfloat16))
+    assert_close(ops.colsum(src.to(dev)), src.double().sum(0), 5e-5, "colsum f32")
+    sb = src.to(torch.bfloat16)
+    assert_close(ops.colsum(sb.to(dev)), sb.double().sum(0), 5e-5, "colsum bf16")
+
+
+@pytest.mark.parametrize("b,N,F,D", [(5, 49, 768, 512), (6, 77, 512, 512), (3, 20, 256, 256), (2, 196, 768, 512)])
+@pytest.mark.parametrize("xdtype", ["f32", "bf16"])
+def test_fused_q_map_vs_oracle(ops, b, N, F, D, xdtype):
+    """QMapFunction (LN -> tcgen05 Linear -> GELU -> LN -> tcgen05 Linear, bf16 operands) against the oracle's q_map
+    (oracle/fdt_oracle.py:make_q_map = clip_fdt.py:86-92, pinned to the golden q_map gradients) run in fp64 on the same
+    parameters: q and every gradient <= 2e-2 relative (bf16 mode tolerance of BASELINE.json)."""
+    from ilfdt import functional as Fn
+    torch.manual_seed(b * 100 + N + F)
+    ref = O.make_q_map(F, D).double()
+    with torch.no_grad():   # non-trivial affine parameters
+        for m in (ref[0], ref[3]):
+            m.weight.add_(0.1 * torch.randn_like(m.weight))
+            m.bias.add_(0.1 * torch.randn_like(m.bias))
+    x = torch.randn(b, N, F)
+    if xdtype == "bf16":
+        x = x.to(torch.bfloat16)
+    up = torch.randn(b, N, D)
+    xr = x.double().requires_grad_(True)
+    qr = ref(xr)
+    (qr * up.double()).sum().backward()
+
+    dev = _dev()
+    mod = O.make_q_map(F, D)
+    mod.load_state_dict({k: v.float() for k, v in ref.state_dict().items()})
+    mod = mod.to(dev)
+    xg = x.to(dev).requires_grad_(True)
+    q = Fn.q_map_apply(mod, xg)
+    assert q.dtype == torch.bfloat16 and q.shape == (b, N, D)
+    (q.float() * up.to(dev)).sum().backward()
+    assert_close(q.float(), qr, BF16_TOL, "q")
+    assert xg.grad.dtype == x.dtype
+    assert_close(xg.grad.float(), xr.grad, BF16_TOL, "dx")
+    for (k, p), (_, pr) in zip(mod.named_parameters(), ref.named_parameters()):
+        assert_close(p.grad, pr.grad, BF16_TOL, "d " + k)
+
+
+def test_query_model_with_fused_q_map(ops):
+    """Query_model with ilfdt.set_fused_q_map(True): same parameters and outputs as the nn.Sequential route within the
+    bf16 tolerance on f (the pooled embedding is continuous in q; argmax / support are not, so dq is not compared
+    entry-wise), gradients reach every q_map parameter, and the fp32 parity mode ignores the switch."""
+    import ilfdt
+    from ilfdt.model.clip_fdt import Query_model
+    torch.manual_seed(5)
+    dev = _dev()
+    qm = Query_model(768, 512, temperature=1000.0, att_func_type="sparsemax", pool_type="max").to(dev)
+    sd = torch.randn(1024, 512, device=dev, requires_grad=True)
+    ft = torch.randn(12, 49, 768, device=dev)
+    try:
+        with ilfdt.compute_dtype("bf16"):
+            _, f0, _ = qm(ft, sd)
+            ilfdt.set_fused_q_map(True)
+            w1, f1, _ = qm(ft, sd)
+            f1.square().sum().backward()
+        # consistency, not the parity gate (that is test_fused_q_map_vs_oracle on q itself): bf16-level changes of q pass
+        # through the max-pool and the sparsemax threshold before they reach f
+        assert_close(f1, f0, 5e-2, "att_ft, fused vs nn.Sequential q_map")
+        for k, p in qm.named_parameters():
+            assert p.grad is not None and torch.isfinite(p.grad).all() and p.grad.abs().max() > 0, k
+        with ilfdt.compute_dtype("fp32"):
+            from ilfdt import functional as Fn
+            assert not Fn.fused_q_map_enabled()
+    finally:
+        ilfdt.set_fused_q_map(False)
