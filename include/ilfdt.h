@@ -116,6 +116,11 @@ int32_t ilfdt_gemm_nt(const void* A, const void* B, int32_t dtype, int64_t M, in
  * (clip_fdt.py:154): A = df, B = w, M = D, N = K, Kr = b. M, N multiples of 8. */
 int32_t ilfdt_gemm_tn(const void* A_bf16, const void* B_bf16, int64_t M, int64_t N, int64_t Kr, float alpha,
                       int32_t accumulate, float* out, int64_t ldo, void* stream);
+/* nn.Linear on bf16 operands (q_map, clip_fdt.py:88,91): out_bf16[n, m] = bf16(sum_k W[m,k] * X[n,k] + bias[m]), W [M = out
+ * features, Kr], X [N rows, Kr], bias [M] f32 or NULL. tcgen05 kernel with the bias add and the bf16 rounding in its
+ * TMEM read-out (the fp32 product never reaches HBM). M % 128 == 0, Kr % 64 == 0. */
+int32_t ilfdt_linear_bf16(const void* W_bf16, const void* X_bf16, int64_t M, int64_t N, int64_t Kr, const float* bias,
+                          void* out_bf16, int64_t ldo, void* stream);
 /* ilfdt_gemm_tn for weight-gradient shapes (short M and N, Kr in the millions: dW of q_map's Linear layers,
  * clip_fdt.py:88,91): the reduction is split over the SMs into slabs of `ws` that a second kernel sums in a fixed
  * order (deterministic, no atomics). ws: ilfdt_gemm_tn_splitk_ws_bytes(M, N, Kr) (0 = not split, plain launch). */
@@ -248,9 +253,10 @@ int32_t ilfdt_nce_topk_hits(const void* x, const void* g, int32_t dtype, int64_t
  * Widths C in {256, 512, 768, 1024}. Column sums are two-stage and deterministic (no float atomics).
  *
  * y_bf16[r,:] = LayerNorm(act(src[r,:] + bias)) * gamma + beta with the biased variance and eps of nn.LayerNorm
- * (clip_fdt.py:87,90); mean / rstd [rows] are saved for the backward. gelu = 0: act = identity, bias ignored, src f32
- * or bf16. gelu = 1 (nn.GELU(), exact erf, clip_fdt.py:89): src is the fp32 output of the first Linear without its
- * bias, and pre_bf16 [rows,C] receives the pre-activation src + bias that the backward differentiates. */
+ * (clip_fdt.py:87,90); mean / rstd [rows] are saved for the backward. gelu = 0: act = identity, bias ignored. gelu = 1
+ * (nn.GELU(), exact erf, clip_fdt.py:89): either src is the first Linear's pre-activation itself (bf16 from
+ * ilfdt_linear_bf16; bias and pre_bf16 NULL), or src is the fp32 product without its bias and pre_bf16 [rows,C]
+ * receives src + bias, the pre-activation that the backward differentiates. src f32 or bf16 in both forms. */
 int32_t ilfdt_ln_fwd(const void* src, int32_t src_dtype, const float* bias, const float* gamma, const float* beta,
                      int64_t rows, int64_t C, float eps, int32_t gelu, void* y_bf16, void* pre_bf16, float* mean,
                      float* rstd, void* stream);

@@ -266,6 +266,16 @@ int32_t ilfdt_gemm_tn(const void* A, const void* B, int64_t M, int64_t N, int64_
   return launch_gemm_tn_bf16(A, B, M, N, Kr, alpha, accumulate, out, ldo, ST(stream));
 }
 
+int32_t ilfdt_linear_bf16(const void* W_bf16, const void* X_bf16, int64_t M, int64_t N, int64_t Kr, const float* bias,
+                          void* out_bf16, int64_t ldo, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(M >= 0 && N >= 0 && Kr >= 1 && ldo >= M, ILFDT_E_INVALID_ARG, "linear_bf16: bad shape");
+  ILFDT_REQUIRE((M == 0 || N == 0) || (W_bf16 && X_bf16 && out_bf16), ILFDT_E_INVALID_ARG, "linear_bf16: null pointer");
+  ILFDT_REQUIRE(M % 128 == 0 && Kr % 64 == 0, ILFDT_E_UNSUPPORTED_SHAPE,
+                "linear_bf16: out features %% 128 and in features %% 64 required (got %lld, %lld)", (long long)M, (long long)Kr);
+  return launch_linear_bf16(W_bf16, X_bf16, M, N, Kr, bias, out_bf16, ldo, ST(stream));
+}
+
 int64_t ilfdt_gemm_tn_splitk_ws_bytes(int64_t M, int64_t N, int64_t Kr) { return gemm_tn_splitk_ws_floats(M, N, Kr) * 4; }
 
 int32_t ilfdt_gemm_tn_splitk(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha,

@@ -58,6 +58,9 @@ struct UmmaParams {
   // = ks * num_n_tiles + n_tile; split ks contracts k-blocks [ks*kb_per, (ks+1)*kb_per) into its own output slab
   int ksplit, kb_per;
   int64_t split_stride;   // elements between slabs
+  // EPI_STORE_T, Linear-layer form (q_map, clip_fdt.py:88,91): out_bf16[n, m] = bf16(alpha * acc + bias[m]) instead of `out`
+  __nv_bfloat16* out_bf16;
+  const float* bias;
   // EPI_POOLMAX
   const float* mask;
   int n_tok, spt, n_samples;
@@ -266,7 +269,22 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               // one pointer stepped by ldo; the full-chunk overwrite case is branch-free (the generic form cost ~24
               // instructions per stored value and made g = df.sd^T epilogue-bound: 1.07 ms for 0.26 ms of MMA)
               float* o = out_base + (int64_t)(n0 + c0) * ldo_ + row;
-              if (c0 + 32 <= ncols && !p.accumulate) {
+              if (p.out_bf16 != nullptr) {
+                // the thread owns output feature `row` of the Linear layer: its bias is one scalar
+                const float bias = p.bias != nullptr ? __ldg(p.bias + row) : 0.f;
+                __nv_bfloat16* ob = p.out_bf16 + (int64_t)(n0 + c0) * ldo_ + row;
+                if (c0 + 32 <= ncols) {
+#pragma unroll
+                  for (int j = 0; j < 32; ++j, ob += ldo_) *ob = __float2bfloat16_rn(fmaf(alpha, __uint_as_float(v[j]), bias));
+                } else {
+                  for (int j = 0; j < ncols - c0; ++j, ob += ldo_) {
+                    float r = 0.f;
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) r = (e == j) ? __uint_as_float(v[e]) : r;
+                    *ob = __float2bfloat16_rn(fmaf(alpha, r, bias));
+                  }
+                }
+              } else if (c0 + 32 <= ncols && !p.accumulate) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j, o += ldo_) *o = alpha * __uint_as_float(v[j]);
               } else if (c0 + 32 <= ncols) {
@@ -523,6 +541,22 @@ int32_t launch_gemm_nt_bf16(const void* A, const void* B, int64_t M, int64_t N, 
   p.alpha = alpha;
   p.alpha_dev = alpha_dev;
   p.accumulate = accumulate;
+  return launch_umma<EPI_STORE_T>(A, B, M, N, Kr, p, st);
+}
+
+// Linear layer: out_bf16[n, m] = bf16(sum_k A[m,k] * B[n,k] + bias[m]), A = weight [M = out features, Kr], B = activations
+// [N = rows, Kr]; the bias add and the bf16 rounding sit in the TMEM read-out, so the fp32 product never reaches HBM.
+int32_t launch_linear_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, const float* bias,
+                           void* out_bf16, int64_t ldo, cudaStream_t st) {
+  if (M == 0 || N == 0) return ILFDT_OK;
+  UmmaParams p{};
+  p.block_n = (int)std::min<int64_t>(256, round_up(N, 16));
+  p.n_step = p.block_n;
+  p.out = nullptr;
+  p.out_bf16 = (__nv_bfloat16*)out_bf16;
+  p.bias = bias;
+  p.ldo = ldo;
+  p.alpha = 1.f;
   return launch_umma<EPI_STORE_T>(A, B, M, N, Kr, p, st);
 }
 

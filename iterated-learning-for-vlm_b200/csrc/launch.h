@@ -50,6 +50,8 @@ int32_t launch_gemm_nt_bf16(const void* A, const void* B, int64_t M, int64_t N, 
                             const float* alpha_dev, int accumulate, float* out, int64_t ldo, cudaStream_t st);
 int32_t launch_gemm_tn_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha, int accumulate,
                             float* out, int64_t ldo, cudaStream_t st);
+int32_t launch_linear_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, const float* bias,
+                           void* out_bf16, int64_t ldo, cudaStream_t st);
 int64_t gemm_tn_splitk_ws_floats(int64_t M, int64_t N, int64_t Kr);
 int32_t launch_gemm_tn_splitk_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha,
                                    int accumulate, float* out, int64_t ldo, float* ws, cudaStream_t st);

@@ -60,7 +60,7 @@ ln_fwd_kernel(const TIn* __restrict__ src, const float* __restrict__ bias, const
   for (int j = 0; j < NV; ++j) {
     ld4(gamma + j * 128 + lane * 4, gm[j]);
     ld4(beta + j * 128 + lane * 4, bt[j]);
-    if (GELU) ld4(bias + j * 128 + lane * 4, bs[j]);
+    if (GELU && bias != nullptr) ld4(bias + j * 128 + lane * 4, bs[j]);
   }
   for (int64_t r = warp0; r < rows; r += nwarps) {
     float v[NV][4];
@@ -69,9 +69,11 @@ ln_fwd_kernel(const TIn* __restrict__ src, const float* __restrict__ bias, const
     for (int j = 0; j < NV; ++j) {
       ld4(src + r * C + j * 128 + lane * 4, v[j]);
       if (GELU) {
+        if (bias != nullptr) {
 #pragma unroll
-        for (int e = 0; e < 4; ++e) v[j][e] += bs[j][e];
-        st4(pre + r * C + j * 128 + lane * 4, v[j]);
+          for (int e = 0; e < 4; ++e) v[j][e] += bs[j][e];
+        }
+        if (pre != nullptr) st4(pre + r * C + j * 128 + lane * 4, v[j]);
 #pragma unroll
         for (int e = 0; e < 4; ++e) v[j][e] = gelu_erf(v[j][e]);
       }
@@ -236,11 +238,12 @@ static int32_t ln_fwd_nv(const void* src, int src_dtype, const float* bias, cons
   const int grid = qm_grid(rows);
   auto* yb = (__nv_bfloat16*)y;
   auto* pb = (__nv_bfloat16*)pre;
-  if (gelu) {
-    ILFDT_REQUIRE(src_dtype == ILFDT_F32 && bias && pre, ILFDT_E_INVALID_ARG,
-                  "ln_fwd: the GELU form takes an fp32 src, a bias and a `pre` buffer");
+  if (gelu && src_dtype == ILFDT_F32) {
     ln_fwd_kernel<NV, true, float><<<grid, QM_THREADS, 0, st>>>((const float*)src, bias, gamma, beta, rows, eps, yb, pb,
                                                                  mean, rstd);
+  } else if (gelu) {
+    ln_fwd_kernel<NV, true, __nv_bfloat16><<<grid, QM_THREADS, 0, st>>>((const __nv_bfloat16*)src, bias, gamma, beta, rows,
+                                                                         eps, yb, pb, mean, rstd);
   } else if (src_dtype == ILFDT_F32) {
     ln_fwd_kernel<NV, false, float><<<grid, QM_THREADS, 0, st>>>((const float*)src, nullptr, gamma, beta, rows, eps, yb,
                                                                   nullptr, mean, rstd);

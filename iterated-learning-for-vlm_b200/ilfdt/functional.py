@@ -162,9 +162,11 @@ def fused_q_map_enabled():
 class QMapFunction(torch.autograd.Function):
     """Query_model.q_map (clip_fdt.py:86-92,111): LayerNorm(F) -> Linear(F,D) -> GELU -> LayerNorm(D) -> Linear(D,D),
     x [b,N,F] (f32 or bf16) -> q [b,N,D] in bf16, the operand the score kernel streams (no cast pass, half the bytes).
-    Both Linear layers are tcgen05 contractions on bf16 operands with fp32 accumulation; LayerNorm, bias and the exact
-    GELU are row kernels in fp32 (csrc/qmap_rows.cu). Saved for the backward: the two bf16 LayerNorm outputs, the bf16
-    pre-GELU activation and the per-row mean / rstd -- 6 bytes per element of the hidden width."""
+    Both Linear layers are tcgen05 contractions on bf16 operands with fp32 accumulation whose read-out adds the bias
+    and rounds to bf16 (ilfdt_linear_bf16: the fp32 product never reaches HBM); LayerNorm and the exact GELU are fp32
+    row kernels (csrc/qmap_rows.cu). Saved for the backward: the two bf16 LayerNorm outputs, the bf16 pre-GELU
+    activation and the per-row mean / rstd -- 6 bytes per element of the hidden width. Weight gradients use the
+    split-reduction contraction (ilfdt_gemm_tn_splitk), bias / affine gradients deterministic two-stage column sums."""
 
     @staticmethod
     def forward(ctx, x, ln1_w, ln1_b, w1, b1, ln2_w, ln2_b, w2, b2, eps1, eps2):
@@ -175,11 +177,9 @@ class QMapFunction(torch.autograd.Function):
         f32 = lambda t: t.detach().float().contiguous()
         ln1_w, ln1_b, b1, ln2_w, ln2_b, b2 = map(f32, (ln1_w, ln1_b, b1, ln2_w, ln2_b, b2))
         xn, _, mean1, rstd1 = ops.ln_fwd(x2, ln1_w, ln1_b, eps1)
-        h = ops.gemm_nt(ops.cast_bf16(f32(w1)), xn)                    # [R,D] = xn . W1^T
-        a2, u, mean2, rstd2 = ops.ln_fwd(h, ln2_w, ln2_b, eps2, bias=b1)
-        del h
-        h = ops.gemm_nt(ops.cast_bf16(f32(w2)), a2)                    # [R,D] = a2 . W2^T
-        q = ops.bias_cast(h, b2, torch.bfloat16)
+        u = ops.linear_bf16(ops.cast_bf16(f32(w1)), xn, b1)             # [R,D] pre-activation xn . W1^T + b1, bf16
+        a2, _, mean2, rstd2 = ops.ln_fwd(u, ln2_w, ln2_b, eps2, gelu=True)
+        q = ops.linear_bf16(ops.cast_bf16(f32(w2)), a2, b2)             # [R,D] = a2 . W2^T + b2, bf16
         ctx.save_for_backward(x2, xn, mean1, rstd1, ln1_w, w1, u, a2, mean2, rstd2, ln2_w, w2)
         ctx.x_shape, ctx.x_dtype = x.shape, x.dtype
         return q.view(*x.shape[:-1], D)

@@ -24,7 +24,7 @@ _KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mas
                      "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5,
                      "ilfdt_nce_bwd": 4, "ilfdt_nce_bwd_gathered": 2, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
                      "ilfdt_randn_fill": 1, "ilfdt_copy": 0,
-                     "ilfdt_gemm_tn_splitk": 2, "ilfdt_ln_fwd": 1, "ilfdt_ln_bwd": 4, "ilfdt_bias_cast": 1, "ilfdt_colsum": 2}
+                     "ilfdt_gemm_tn_splitk": 2, "ilfdt_linear_bf16": 1, "ilfdt_ln_fwd": 1, "ilfdt_ln_bwd": 4, "ilfdt_bias_cast": 1, "ilfdt_colsum": 2}
 
 
 def _call(name, *args):
@@ -215,6 +215,19 @@ def gemm_tn(A, B, alpha=1.0, out=None, accumulate=False):
         out = torch.empty(N, M, dtype=torch.float32, device=A.device)
     _req(out, torch.float32, "out")
     _call("ilfdt_gemm_tn", _ptr(A), _ptr(B), M, N, Kr, float(alpha), int(accumulate), _ptr(out), out.shape[1], _stream())
+    return out
+
+
+def linear_bf16(W, X, bias=None):
+    """nn.Linear on bf16 operands: X [R,Kr] . W [M,Kr]^T + bias [M] -> bf16 [R,M] (bias add + rounding in the GEMM's epilogue)."""
+    _req(W, torch.bfloat16, "W"); _req(X, torch.bfloat16, "X")
+    M, Kr = W.shape
+    R = X.shape[0]
+    assert X.shape[1] == Kr
+    if bias is not None:
+        _req(bias, torch.float32, "bias")
+    out = torch.empty(R, M, dtype=torch.bfloat16, device=X.device)
+    _call("ilfdt_linear_bf16", _ptr(W), _ptr(X), M, R, Kr, _ptr(bias), _ptr(out), M, _stream())
     return out
 
 
@@ -471,10 +484,13 @@ def copy_(dst, src):
 
 
 # ---- q_map producer rows (clip_fdt.py:86-92) -----------------------------------------
-def ln_fwd(src, gamma, beta, eps, bias=None):
-    """y = LayerNorm(act(src + bias)) as bf16 [R,C] with mean, rstd [R]. bias given: act = exact GELU, src is the fp32
-    output of the preceding Linear without its bias, and the bf16 pre-activation is returned as well."""
+def ln_fwd(src, gamma, beta, eps, bias=None, gelu=None, want_pre=None):
+    """y = LayerNorm(act(src + bias)) as bf16 [R,C] with mean, rstd [R]. gelu (default: bias is given): act = exact GELU;
+    src is then either the bf16 pre-activation itself (no bias) or the fp32 product without its bias, in which case the
+    bf16 pre-activation src + bias is returned as well."""
     _req(src, None, "src"); _req(gamma, torch.float32, "gamma"); _req(beta, torch.float32, "beta")
+    gelu = (bias is not None) if gelu is None else gelu
+    want_pre = (bias is not None) if want_pre is None else want_pre
     R, C = src.shape
     y = torch.empty(R, C, dtype=torch.bfloat16, device=src.device)
     mean = torch.empty(R, dtype=torch.float32, device=src.device)
@@ -482,9 +498,10 @@ def ln_fwd(src, gamma, beta, eps, bias=None):
     pre = None
     if bias is not None:
         _req(bias, torch.float32, "bias")
+    if want_pre:
         pre = torch.empty_like(y)
     _call("ilfdt_ln_fwd", _ptr(src), _DT[src.dtype], _ptr(bias), _ptr(gamma), _ptr(beta), R, C, float(eps),
-          int(bias is not None), _ptr(y), _ptr(pre), _ptr(mean), _ptr(rstd), _stream())
+          int(gelu), _ptr(y), _ptr(pre), _ptr(mean), _ptr(rstd), _stream())
     return y, pre, mean, rstd
 
 

@@ -1052,6 +1052,40 @@ def test_qmap_layernorm_rows(ops, R, C, gelu):
     del xhat
 
 
+@pytest.mark.parametrize("R,C", [(3, 256), (300, 512), (41, 1024)])
+def test_qmap_gelu_layernorm_from_bf16_preactivation(ops, R, C):
+    """The form QMapFunction uses: src is already the bf16 pre-activation (ilfdt_linear_bf16 added the bias), so the
+    forward and the backward see the same rounded value."""
+    g = torch.Generator().manual_seed(R + 7 * C)
+    u = (torch.randn(R, C, generator=g) * 1.5).to(torch.bfloat16)
+    gamma = 1 + 0.1 * torch.randn(C, generator=g)
+    beta = 0.1 * torch.randn(C, generator=g)
+    dev = _dev()
+    y, pre, mean, rstd = ops.ln_fwd(u.to(dev), gamma.to(dev), beta.to(dev), 1e-5, gelu=True)
+    assert pre is None
+    a = torch.nn.functional.gelu(u.double())
+    ref = torch.nn.functional.layer_norm(a, (C,), gamma.double(), beta.double(), 1e-5)
+    assert_close(y.float(), ref, 2 ** -8, "y")
+    assert_close(mean, a.mean(1), FP32_TOL, "mean")
+    assert_close(rstd, 1 / torch.sqrt(a.var(1, unbiased=False) + 1e-5), FP32_TOL, "rstd")
+
+
+@pytest.mark.parametrize("M,N,K,with_bias", [(512, 300, 768, True), (768, 1000, 512, True), (128, 7, 64, False),
+                                             (256, 513, 256, True)])
+def test_linear_bf16_fused_bias_epilogue(ops, M, N, K, with_bias):
+    """ilfdt_linear_bf16: bf16(X . W^T + bias) with the bias add and the rounding in the tcgen05 kernel's read-out,
+    against the fp64 product of the same bf16 operands rounded once."""
+    g = torch.Generator().manual_seed(M + 3 * N + K)
+    W = bf16_round(torch.randn(M, K, generator=g) / math.sqrt(K))
+    X = bf16_round(torch.randn(N, K, generator=g))
+    bias = torch.randn(M, generator=g) if with_bias else None
+    ref = X.double() @ W.double().t() + (bias.double() if with_bias else 0)
+    out = ops.linear_bf16(W.to(_dev()).to(torch.bfloat16), X.to(_dev()).to(torch.bfloat16),
+                          bias.to(_dev()) if with_bias else None)
+    assert out.dtype == torch.bfloat16 and out.shape == (N, M)
+    assert_close(out.float(), ref, 2 ** -8, "linear_bf16")
+
+
 @pytest.mark.parametrize("R,C", [(1, 512), (77, 256), (4097, 768)])
 def test_qmap_bias_cast_and_colsum(ops, R, C):
     g = torch.Generator().manual_seed(R + C)
