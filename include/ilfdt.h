@@ -260,13 +260,15 @@ int32_t ilfdt_nce_topk_hits(const void* x, const void* g, int32_t dtype, int64_t
 int32_t ilfdt_ln_fwd(const void* src, int32_t src_dtype, const float* bias, const float* gamma, const float* beta,
                      int64_t rows, int64_t C, float eps, int32_t gelu, void* y_bf16, void* pre_bf16, float* mean,
                      float* rstd, void* stream);
-/* Backward of the above for dy [rows,C] f32. src = the forward's src (gelu = 0) or its pre_bf16 (gelu = 1).
- * dsrc: f32 (gelu = 0) or bf16 (gelu = 1, the operand of the next contraction); dgamma, dbeta [C]; dbias [C] (gelu = 1,
- * may be NULL) = column sum of dsrc. ws: ilfdt_ln_bwd_ws_bytes(rows, C). */
+/* Backward of the above for dy [rows,C] (f32, or bf16 as ilfdt_linear_bf16 writes it). src = the forward's src
+ * (gelu = 0) or the bf16 pre-activation (gelu = 1). dsrc: f32 (gelu = 0) or bf16 (gelu = 1, the operand of the next
+ * contraction); dgamma, dbeta [C]; dbias [C] (gelu = 1, may be NULL) = column sum of dsrc.
+ * ws: ilfdt_ln_bwd_ws_bytes(rows, C). */
 int64_t ilfdt_ln_bwd_ws_bytes(int64_t rows, int64_t C);
-int32_t ilfdt_ln_bwd(const float* dy, const void* src, int32_t src_dtype, const float* gamma, const float* mean,
-                     const float* rstd, int64_t rows, int64_t C, int32_t gelu, void* dsrc, int32_t dsrc_dtype,
-                     float* dgamma, float* dbeta, float* dbias, void* ws, int64_t ws_bytes, void* stream);
+int32_t ilfdt_ln_bwd(const void* dy, int32_t dy_dtype, const void* src, int32_t src_dtype, const float* gamma,
+                     const float* mean, const float* rstd, int64_t rows, int64_t C, int32_t gelu, void* dsrc,
+                     int32_t dsrc_dtype, float* dgamma, float* dbeta, float* dbias, void* ws, int64_t ws_bytes,
+                     void* stream);
 /* dst[r,:] = src[r,:] + bias  (the second Linear's bias, clip_fdt.py:91), written as bf16 (the score kernel's
  * operand) or f32. */
 int32_t ilfdt_bias_cast(const float* src, const float* bias, int64_t rows, int64_t C, void* dst, int32_t dst_dtype,

@@ -544,18 +544,20 @@ int32_t ilfdt_ln_fwd(const void* src, int32_t src_dtype, const float* bias, cons
   return launch_ln_fwd(src, src_dtype, bias, gamma, beta, rows, C, eps, gelu, y_bf16, pre_bf16, mean, rstd, ST(stream));
 }
 
-int32_t ilfdt_ln_bwd(const float* dy, const void* src, int32_t src_dtype, const float* gamma, const float* mean,
-                     const float* rstd, int64_t rows, int64_t C, int32_t gelu, void* dsrc, int32_t dsrc_dtype,
-                     float* dgamma, float* dbeta, float* dbias, void* ws, int64_t ws_bytes, void* stream) {
+int32_t ilfdt_ln_bwd(const void* dy, int32_t dy_dtype, const void* src, int32_t src_dtype, const float* gamma,
+                     const float* mean, const float* rstd, int64_t rows, int64_t C, int32_t gelu, void* dsrc,
+                     int32_t dsrc_dtype, float* dgamma, float* dbeta, float* dbias, void* ws, int64_t ws_bytes,
+                     void* stream) {
   ARCH_GUARD();
+  DTYPE_GUARD(dy_dtype);
   DTYPE_GUARD(src_dtype);
   DTYPE_GUARD(dsrc_dtype);
   ILFDT_REQUIRE(rows >= 1 && C >= 1, ILFDT_E_INVALID_ARG, "ln_bwd: bad shape");
   ILFDT_REQUIRE(dy && src && gamma && mean && rstd && dsrc && dgamma && dbeta && ws, ILFDT_E_INVALID_ARG,
                 "ln_bwd: null pointer");
   ILFDT_REQUIRE(ws_bytes >= ilfdt_ln_bwd_ws_bytes(rows, C), ILFDT_E_INVALID_ARG, "ln_bwd: workspace too small");
-  return launch_ln_bwd(dy, src, src_dtype, gamma, mean, rstd, rows, C, gelu, dsrc, dsrc_dtype, dgamma, dbeta, dbias,
-                       (float*)ws, ST(stream));
+  return launch_ln_bwd(dy, dy_dtype, src, src_dtype, gamma, mean, rstd, rows, C, gelu, dsrc, dsrc_dtype, dgamma, dbeta,
+                       dbias, (float*)ws, ST(stream));
 }
 
 int32_t ilfdt_bias_cast(const float* src, const float* bias, int64_t rows, int64_t C, void* dst, int32_t dst_dtype,

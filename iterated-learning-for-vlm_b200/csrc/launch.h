@@ -115,7 +115,7 @@ int64_t colsum_ws_floats(int64_t rows, int64_t C);
 int32_t launch_ln_fwd(const void* src, int src_dtype, const float* bias, const float* gamma, const float* beta,
                       int64_t rows, int64_t C, float eps, int gelu, void* y, void* pre, float* mean, float* rstd,
                       cudaStream_t st);
-int32_t launch_ln_bwd(const float* dy, const void* src, int src_dtype, const float* gamma, const float* mean,
+int32_t launch_ln_bwd(const void* dy, int dy_dtype, const void* src, int src_dtype, const float* gamma, const float* mean,
                       const float* rstd, int64_t rows, int64_t C, int gelu, void* dsrc, int dsrc_dtype, float* dgamma,
                       float* dbeta, float* dbias, float* ws, cudaStream_t st);
 int32_t launch_bias_cast(const float* src, const float* bias, int64_t rows, int64_t C, void* dst, int dst_dtype,

@@ -109,9 +109,9 @@ ln_fwd_kernel(const TIn* __restrict__ src, const float* __restrict__ bias, const
 //   d act = rstd * (dxhat - mean_c(dxhat) - xhat * mean_c(dxhat * xhat));  dsrc = d act * act'(src)
 // and the per-CTA column partials part[cta][0] = sum_r dy*xhat (dgamma), [1] = sum_r dy (dbeta), [2] = sum_r dsrc (the
 // gradient of the bias in front of the GELU). dsrc is written as TOut (bf16 when it feeds the next contraction).
-template <int NV, bool GELU, typename TIn, typename TOut>
+template <int NV, bool GELU, typename TIn, typename TOut, typename TDy>
 __global__ void __launch_bounds__(QM_THREADS)
-ln_bwd_kernel(const float* __restrict__ dy, const TIn* __restrict__ src, const float* __restrict__ gamma,
+ln_bwd_kernel(const TDy* __restrict__ dy, const TIn* __restrict__ src, const float* __restrict__ gamma,
               const float* __restrict__ mean, const float* __restrict__ rstd, int64_t rows, TOut* __restrict__ dsrc,
               float* __restrict__ part) {
   constexpr int C = NV * 128;
@@ -206,20 +206,45 @@ __global__ void bias_cast_kernel(const float* __restrict__ src, const float* __r
   }
 }
 
-// part[cta][c] = sum over the CTA's rows of src[r, c]
+// part[cta][c] = sum over the CTA's rows of src[r, c]. The 256 threads form RL row lanes x (C/4) column groups of four
+// columns; each lane keeps 4 rows in flight, the row lanes are folded through shared memory in a fixed order.
 template <typename TIn>
 __global__ void __launch_bounds__(QM_THREADS)
 colsum_partial_kernel(const TIn* __restrict__ src, int64_t rows, int C, float* __restrict__ part) {
-  // thread t owns the 4 columns [4t, 4t+4) of each 1024-column slab; rows strided over CTAs
-  for (int c0 = threadIdx.x * 4; c0 < C; c0 += QM_THREADS * 4) {
-    float a[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
+  __shared__ float red[QM_THREADS * 4];
+  const int groups = C >> 2;                               // column groups of 4
+  const int rl_n = max(1, QM_THREADS / groups);            // row lanes per CTA (C <= 1024)
+  const int cg = threadIdx.x % groups, rl = threadIdx.x / groups;
+  const bool active = rl < rl_n && groups <= QM_THREADS;
+  float a[4] = {0.f, 0.f, 0.f, 0.f};
+  if (active) {
+    const int64_t stride = (int64_t)gridDim.x * rl_n;
+    int64_t r = (int64_t)blockIdx.x * rl_n + rl;
+    for (; r + 3 * stride < rows; r += 4 * stride) {
+      float v0[4], v1[4], v2[4], v3[4];
+      ld4(src + r * C + cg * 4, v0);
+      ld4(src + (r + stride) * C + cg * 4, v1);
+      ld4(src + (r + 2 * stride) * C + cg * 4, v2);
+      ld4(src + (r + 3 * stride) * C + cg * 4, v3);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) a[e] += (v0[e] + v1[e]) + (v2[e] + v3[e]);
+    }
+    for (; r < rows; r += stride) {
       float v[4];
-      ld4(src + r * C + c0, v);
+      ld4(src + r * C + cg * 4, v);
 #pragma unroll
       for (int e = 0; e < 4; ++e) a[e] += v[e];
     }
-    st4(part + (int64_t)blockIdx.x * C + c0, a);
+  }
+#pragma unroll
+  for (int e = 0; e < 4; ++e) red[threadIdx.x * 4 + e] = active ? a[e] : 0.f;
+  __syncthreads();
+  if (threadIdx.x < groups && groups <= QM_THREADS) {
+    float t[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int l = 0; l < rl_n; ++l)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) t[e] += red[(l * groups + threadIdx.x) * 4 + e];
+    st4(part + (int64_t)blockIdx.x * C + threadIdx.x * 4, t);
   }
 }
 
@@ -268,8 +293,8 @@ int32_t launch_ln_fwd(const void* src, int src_dtype, const float* bias, const f
   return fail(ILFDT_E_UNSUPPORTED_SHAPE, "ln_fwd: width %lld not in {256,512,768,1024}", (long long)C);
 }
 
-template <int NV>
-static int32_t ln_bwd_nv(const float* dy, const void* src, int src_dtype, const float* gamma, const float* mean,
+template <int NV, typename TDy>
+static int32_t ln_bwd_nv(const TDy* dy, const void* src, int src_dtype, const float* gamma, const float* mean,
                          const float* rstd, int64_t rows, int gelu, void* dsrc, int dsrc_dtype, float* dgamma,
                          float* dbeta, float* dbias, float* ws, cudaStream_t st) {
   constexpr int C = NV * 128;
@@ -277,16 +302,16 @@ static int32_t ln_bwd_nv(const float* dy, const void* src, int src_dtype, const 
   if (gelu) {
     ILFDT_REQUIRE(src_dtype == ILFDT_BF16 && dsrc_dtype == ILFDT_BF16, ILFDT_E_INVALID_ARG,
                   "ln_bwd: the GELU form reads the bf16 pre-activation and writes a bf16 gradient");
-    ln_bwd_kernel<NV, true, __nv_bfloat16, __nv_bfloat16><<<grid, QM_THREADS, 0, st>>>(
+    ln_bwd_kernel<NV, true, __nv_bfloat16, __nv_bfloat16, TDy><<<grid, QM_THREADS, 0, st>>>(
         dy, (const __nv_bfloat16*)src, gamma, mean, rstd, rows, (__nv_bfloat16*)dsrc, ws);
   } else {
     ILFDT_REQUIRE(dsrc_dtype == ILFDT_F32, ILFDT_E_INVALID_ARG, "ln_bwd: the plain form writes an fp32 gradient");
     if (src_dtype == ILFDT_F32)
-      ln_bwd_kernel<NV, false, float, float><<<grid, QM_THREADS, 0, st>>>(dy, (const float*)src, gamma, mean, rstd, rows,
-                                                                         (float*)dsrc, ws);
+      ln_bwd_kernel<NV, false, float, float, TDy><<<grid, QM_THREADS, 0, st>>>(dy, (const float*)src, gamma, mean, rstd,
+                                                                              rows, (float*)dsrc, ws);
     else
-      ln_bwd_kernel<NV, false, __nv_bfloat16, float><<<grid, QM_THREADS, 0, st>>>(dy, (const __nv_bfloat16*)src, gamma,
-                                                                                 mean, rstd, rows, (float*)dsrc, ws);
+      ln_bwd_kernel<NV, false, __nv_bfloat16, float, TDy><<<grid, QM_THREADS, 0, st>>>(
+          dy, (const __nv_bfloat16*)src, gamma, mean, rstd, rows, (float*)dsrc, ws);
   }
   ILFDT_LAUNCH_OK();
   const int tb = 128, gb = (int)cdiv(C, tb);
@@ -297,10 +322,10 @@ static int32_t ln_bwd_nv(const float* dy, const void* src, int src_dtype, const 
   return ILFDT_OK;
 }
 
-int32_t launch_ln_bwd(const float* dy, const void* src, int src_dtype, const float* gamma, const float* mean,
-                      const float* rstd, int64_t rows, int64_t C, int gelu, void* dsrc, int dsrc_dtype, float* dgamma,
-                      float* dbeta, float* dbias, float* ws, cudaStream_t st) {
-  ILFDT_REQUIRE(rows > 0, ILFDT_E_INVALID_ARG, "ln_bwd: no rows");
+template <typename TDy>
+static int32_t ln_bwd_c(const TDy* dy, const void* src, int src_dtype, const float* gamma, const float* mean,
+                        const float* rstd, int64_t rows, int64_t C, int gelu, void* dsrc, int dsrc_dtype, float* dgamma,
+                        float* dbeta, float* dbias, float* ws, cudaStream_t st) {
   switch (C) {
     case 256: return ln_bwd_nv<2>(dy, src, src_dtype, gamma, mean, rstd, rows, gelu, dsrc, dsrc_dtype, dgamma, dbeta, dbias, ws, st);
     case 512: return ln_bwd_nv<4>(dy, src, src_dtype, gamma, mean, rstd, rows, gelu, dsrc, dsrc_dtype, dgamma, dbeta, dbias, ws, st);
@@ -308,6 +333,17 @@ int32_t launch_ln_bwd(const float* dy, const void* src, int src_dtype, const flo
     case 1024: return ln_bwd_nv<8>(dy, src, src_dtype, gamma, mean, rstd, rows, gelu, dsrc, dsrc_dtype, dgamma, dbeta, dbias, ws, st);
   }
   return fail(ILFDT_E_UNSUPPORTED_SHAPE, "ln_bwd: width %lld not in {256,512,768,1024}", (long long)C);
+}
+
+int32_t launch_ln_bwd(const void* dy, int dy_dtype, const void* src, int src_dtype, const float* gamma, const float* mean,
+                      const float* rstd, int64_t rows, int64_t C, int gelu, void* dsrc, int dsrc_dtype, float* dgamma,
+                      float* dbeta, float* dbias, float* ws, cudaStream_t st) {
+  ILFDT_REQUIRE(rows > 0, ILFDT_E_INVALID_ARG, "ln_bwd: no rows");
+  if (dy_dtype == ILFDT_BF16)
+    return ln_bwd_c((const __nv_bfloat16*)dy, src, src_dtype, gamma, mean, rstd, rows, C, gelu, dsrc, dsrc_dtype, dgamma,
+                    dbeta, dbias, ws, st);
+  return ln_bwd_c((const float*)dy, src, src_dtype, gamma, mean, rstd, rows, C, gelu, dsrc, dsrc_dtype, dgamma, dbeta,
+                  dbias, ws, st);
 }
 
 int32_t launch_bias_cast(const float* src, const float* bias, int64_t rows, int64_t C, void* dst, int dst_dtype,
@@ -325,7 +361,8 @@ int32_t launch_bias_cast(const float* src, const float* bias, int64_t rows, int6
 }
 
 int32_t launch_colsum(const void* src, int src_dtype, int64_t rows, int64_t C, float* out, float* ws, cudaStream_t st) {
-  ILFDT_REQUIRE(rows > 0 && C % 4 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "colsum: rows > 0 and width a multiple of 4");
+  ILFDT_REQUIRE(rows > 0 && C % 4 == 0 && C <= 1024, ILFDT_E_UNSUPPORTED_SHAPE,
+                "colsum: rows > 0 and width a multiple of 4, <= 1024");
   const int grid = qm_grid(rows);
   if (src_dtype == ILFDT_BF16)
     colsum_partial_kernel<__nv_bfloat16><<<grid, QM_THREADS, 0, st>>>((const __nv_bfloat16*)src, rows, (int)C, ws);

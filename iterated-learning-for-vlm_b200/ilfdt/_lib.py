@@ -64,7 +64,7 @@ SIGNATURES = {
     "ilfdt_nce_topk_hits": (_i32, [_p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _p, _p, _i64, _p]),
     "ilfdt_ln_fwd": (_i32, [_p, _i32, _p, _p, _p, _i64, _i64, _f, _i32, _p, _p, _p, _p, _p]),
     "ilfdt_ln_bwd_ws_bytes": (_i64, [_i64, _i64]),
-    "ilfdt_ln_bwd": (_i32, [_p, _p, _i32, _p, _p, _p, _i64, _i64, _i32, _p, _i32, _p, _p, _p, _p, _i64, _p]),
+    "ilfdt_ln_bwd": (_i32, [_p, _i32, _p, _i32, _p, _p, _p, _i64, _i64, _i32, _p, _i32, _p, _p, _p, _p, _i64, _p]),
     "ilfdt_bias_cast": (_i32, [_p, _p, _i64, _i64, _p, _i32, _p]),
     "ilfdt_colsum_ws_bytes": (_i64, [_i64, _i64]),
     "ilfdt_colsum": (_i32, [_p, _i32, _i64, _i64, _p, _p, _i64, _p]),

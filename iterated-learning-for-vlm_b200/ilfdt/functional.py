@@ -192,11 +192,11 @@ class QMapFunction(torch.autograd.Function):
         db2 = ops.colsum(dq2)
         dq_b = dq2 if dq2.dtype == torch.bfloat16 else ops.cast_bf16(dq2.float())
         dw2 = ops.gemm_tn_splitk(a2, dq_b)                                     # [D_out, D_in] = dq^T . a2
-        da2 = ops.gemm_nt(ops.transpose_bf16(w2.detach().float().contiguous()), dq_b)   # [R, D_in] = dq . W2
+        da2 = ops.linear_bf16(ops.transpose_bf16(w2.detach().float().contiguous()), dq_b)   # [R, D_in] = dq . W2, bf16
         du, dln2_w, dln2_b, db1 = ops.ln_bwd(da2, u, ln2_w, mean2, rstd2, gelu=True)
         del da2
         dw1 = ops.gemm_tn_splitk(xn, du)                                       # [D, F] = du^T . xn
-        dxn = ops.gemm_nt(ops.transpose_bf16(w1.detach().float().contiguous()), du)     # [R, F] = du . W1
+        dxn = ops.linear_bf16(ops.transpose_bf16(w1.detach().float().contiguous()), du)     # [R, F] = du . W1, bf16
         dx, dln1_w, dln1_b, _ = ops.ln_bwd(dxn, x2, ln1_w, mean1, rstd1, gelu=False)
         del dxn
         if not ctx.needs_input_grad[0]:

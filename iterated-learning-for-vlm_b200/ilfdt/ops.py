@@ -507,7 +507,7 @@ def ln_fwd(src, gamma, beta, eps, bias=None, gelu=None, want_pre=None):
 
 def ln_bwd(dy, src, gamma, mean, rstd, gelu):
     """-> dsrc (bf16 through the GELU, else f32), dgamma, dbeta, dbias (GELU form only, else None)."""
-    _req(dy, torch.float32, "dy"); _req(src, None, "src"); _req(gamma, torch.float32, "gamma")
+    _req(dy, None, "dy"); _req(src, None, "src"); _req(gamma, torch.float32, "gamma")
     R, C = dy.shape
     assert src.shape == dy.shape
     dsrc = torch.empty(R, C, dtype=torch.bfloat16 if gelu else torch.float32, device=dy.device)
@@ -516,7 +516,7 @@ def ln_bwd(dy, src, gamma, mean, rstd, gelu):
     dbias = torch.empty_like(dgamma) if gelu else None
     nws = _lib.load().ilfdt_ln_bwd_ws_bytes(R, C)
     ws = torch.empty(nws, dtype=torch.uint8, device=dy.device)
-    _call("ilfdt_ln_bwd", _ptr(dy), _ptr(src), _DT[src.dtype], _ptr(gamma), _ptr(mean), _ptr(rstd), R, C, int(gelu),
+    _call("ilfdt_ln_bwd", _ptr(dy), _DT[dy.dtype], _ptr(src), _DT[src.dtype], _ptr(gamma), _ptr(mean), _ptr(rstd), R, C, int(gelu),
           _ptr(dsrc), _DT[dsrc.dtype], _ptr(dgamma), _ptr(dbeta), _ptr(dbias), _ptr(ws), nws, _stream())
     return dsrc, dgamma, dbeta, dbias
 
