@@ -71,6 +71,32 @@ def test_no_cpu_fallback(built_lib):
         qm(torch.randn(2, 3, 8), torch.randn(5, 8))  # CPU tensors: loud, not a silent torch fallback
 
 
+def test_fused_q_map_switch_is_loud_and_bf16_only(built_lib):
+    """SURVEY 8f N2 host logic: the switch acts only in the bf16 compute mode (the fp32 parity mode keeps the
+    reference's nn.Sequential), unsupported widths raise NotImplementedError, CPU tensors raise -- never a fallback."""
+    import ilfdt
+    from ilfdt import functional as Fn
+    from ilfdt.model.clip_fdt import Query_model
+    assert not Fn.fused_q_map_enabled()          # off by default
+    try:
+        ilfdt.set_fused_q_map(True)
+        with ilfdt.compute_dtype("bf16"):
+            assert Fn.fused_q_map_enabled()
+            qm = Query_model(24, 32, 1000.0, "sparsemax", "max")      # widths outside the row kernels' set
+            with pytest.raises(NotImplementedError):
+                qm(torch.randn(2, 3, 24), torch.randn(8, 32))
+            qm = Query_model(512, 512, 1000.0, "sparsemax", "max")
+            with pytest.raises(RuntimeError):                          # CPU tensors: no CPU path
+                qm(torch.randn(2, 3, 512), torch.randn(8, 512))
+        with ilfdt.compute_dtype("fp32"):
+            assert not Fn.fused_q_map_enabled()
+    finally:
+        ilfdt.set_fused_q_map(False)
+    # the producer keeps the reference's parameter names (checkpoint interchange)
+    assert [k for k, _ in Query_model(512, 512).q_map.named_parameters()] == [
+        "0.weight", "0.bias", "1.weight", "1.bias", "3.weight", "3.bias", "4.weight", "4.bias"]
+
+
 def test_product_path_never_imports_the_oracle():
     for dirpath, _, files in os.walk(os.path.join(PKG, "ilfdt")):
         for f in files:
