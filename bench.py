@@ -87,6 +87,33 @@ def cpu_reference_run(sample_rows, steps, warmup, codes):
                        % (sample_rows, P_TOK, T_TOK, codes, D_DIM, sample_rows, sample_rows, len(times), t)), t
 
 
+def gpu_eager_reference_run(sample_rows, steps, warmup, codes, dev):
+    """Context number of SURVEY 8d: the same restatement of the reference's path (fp32 PyTorch eager: dense [b,N,K]
+    matmuls, sort-based sparsemax, F.cross_entropy, autograd; TF32 off as in the reference) on the SAME B200. Not the
+    target and not the product: the practical bar a user of the reference sees today."""
+    from oracle import fdt_oracle as O
+    torch.backends.cuda.matmul.allow_tf32 = False
+    inp = O.synth_inputs(sample_rows, P_TOK, T_TOK, codes, D_DIM, seed=0)
+    inp = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in inp.items()}
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ms = 0.0
+    for i in range(warmup + steps):
+        ranks = [dict(q_img=O.make_leaf(inp["q_img"]), q_txt=O.make_leaf(inp["q_txt"]), mask=inp["mask"],
+                      sd=O.make_leaf(inp["sd"]), p=O.make_leaf(inp["p"]))]
+        e0.record()
+        O.step(ranks, temperature=TEMPERATURE)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= warmup:
+            ms += e0.elapsed_time(e1)
+        del ranks
+    ms /= steps
+    torch.cuda.empty_cache()
+    return dict(value=sample_rows / (ms * 1e-3), unit="pairs/s", ms_per_step=ms,
+                sample="%d rows of the workload (logits %dx%d), fp32 PyTorch eager on the same B200, TF32 off, %d steps"
+                       % (sample_rows, sample_rows, sample_rows, steps))
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
@@ -511,6 +538,10 @@ def run_ours(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu, _ = cpu_reference_run(args.cpu_sample, 3, 1, K)
+        try:
+            cpu["gpu_eager"] = gpu_eager_reference_run(256, 3, 1, K, dev)
+        except Exception as e:  # noqa: BLE001 -- a context number must not take the bench line down
+            cpu["gpu_eager"] = {"unavailable": str(e).splitlines()[0][:160]}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,

@@ -109,17 +109,21 @@ ln_fwd_kernel(const TIn* __restrict__ src, const float* __restrict__ bias, const
 //   d act = rstd * (dxhat - mean_c(dxhat) - xhat * mean_c(dxhat * xhat));  dsrc = d act * act'(src)
 // and the per-CTA column partials part[cta][0] = sum_r dy*xhat (dgamma), [1] = sum_r dy (dbeta), [2] = sum_r dsrc (the
 // gradient of the bias in front of the GELU). dsrc is written as TOut (bf16 when it feeds the next contraction).
+// 128-thread CTAs: at 120-210 registers per thread this keeps 3 (F = 768) to 4 CTAs resident per SM instead of one
+// 256-thread CTA, i.e. more rows (loads) in flight per SM
+constexpr int LB_THREADS = 128, LB_WARPS = LB_THREADS / 32;
+
 template <int NV, bool GELU, typename TIn, typename TOut, typename TDy>
-__global__ void __launch_bounds__(QM_THREADS)
+__global__ void __launch_bounds__(LB_THREADS)
 ln_bwd_kernel(const TDy* __restrict__ dy, const TIn* __restrict__ src, const float* __restrict__ gamma,
               const float* __restrict__ mean, const float* __restrict__ rstd, int64_t rows, TOut* __restrict__ dsrc,
               float* __restrict__ part) {
   constexpr int C = NV * 128;
-  __shared__ float red[QM_WARPS][128];
+  __shared__ float red[LB_WARPS][128];
   const int lane = threadIdx.x & 31;
   const int wid = threadIdx.x >> 5;
-  const int64_t warp0 = (int64_t)blockIdx.x * QM_WARPS + wid;
-  const int64_t nwarps = (int64_t)gridDim.x * QM_WARPS;
+  const int64_t warp0 = (int64_t)blockIdx.x * LB_WARPS + wid;
+  const int64_t nwarps = (int64_t)gridDim.x * LB_WARPS;
   float gm[NV][4], ag[NV][4], ab[NV][4], as[NV][4];
 #pragma unroll
   for (int j = 0; j < NV; ++j) {
@@ -161,7 +165,7 @@ ln_bwd_kernel(const TDy* __restrict__ dy, const TIn* __restrict__ src, const flo
       st4(dsrc + r * C + j * 128 + lane * 4, o);
     }
   }
-  // CTA partials: fixed order over the 8 warps, one 128-column group at a time
+  // CTA partials: fixed order over the 4 warps, one 128-column group at a time
   float* out = part + (int64_t)blockIdx.x * 3 * C;
 #pragma unroll
   for (int which = 0; which < (GELU ? 3 : 2); ++which) {
@@ -172,24 +176,35 @@ ln_bwd_kernel(const TDy* __restrict__ dy, const TIn* __restrict__ src, const flo
 #pragma unroll
       for (int e = 0; e < 4; ++e) red[wid][lane * 4 + e] = a[e];
       __syncthreads();
-      if (threadIdx.x < 128) {
+      {
         float t = 0.f;
 #pragma unroll
-        for (int w = 0; w < QM_WARPS; ++w) t += red[w][threadIdx.x];
+        for (int w = 0; w < LB_WARPS; ++w) t += red[w][threadIdx.x];
         out[which * C + j * 128 + threadIdx.x] = t;
       }
     }
   }
 }
 
-// out[c] = sum_p part[p * stride + c]  (fixed order: deterministic), c < cols
-__global__ void partial_reduce_kernel(const float* __restrict__ part, int n_part, int64_t stride, int cols,
-                                      float* __restrict__ out) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= cols) return;
+// out[c] = sum_p part[p * stride + c], c < cols. 32 columns x 8 partial lanes per CTA; every lane sums its partials
+// p = lane, lane + 8, ... and the 8 lanes are folded in a fixed order: deterministic, and 8 loads in flight per column
+// instead of one dependent chain over several hundred partials.
+__global__ void __launch_bounds__(256)
+partial_reduce_kernel(const float* __restrict__ part, int n_part, int64_t stride, int cols, float* __restrict__ out) {
+  __shared__ float red[8][32];
+  const int cx = threadIdx.x & 31, ly = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cx;
   float t = 0.f;
-  for (int p = 0; p < n_part; ++p) t += part[p * stride + c];
-  out[c] = t;
+  if (c < cols)
+    for (int p = ly; p < n_part; p += 8) t += part[p * stride + c];
+  red[ly][cx] = t;
+  __syncthreads();
+  if (ly == 0 && c < cols) {
+    float a = 0.f;
+#pragma unroll
+    for (int l = 0; l < 8; ++l) a += red[l][cx];
+    out[c] = a;
+  }
 }
 
 // dst[r, :] = src[r, :] + bias   (bf16 or fp32 out)
@@ -253,7 +268,10 @@ static int qm_grid(int64_t rows) {
   return (int)std::max<int64_t>(1, std::min<int64_t>(want, (int64_t)sm_count() * 4));
 }
 
-int64_t ln_bwd_ws_floats(int64_t rows, int64_t C) { return (int64_t)qm_grid(rows) * 3 * C; }
+static int lb_grid(int64_t rows) {
+  return (int)std::max<int64_t>(1, std::min<int64_t>(cdiv(rows, LB_WARPS), (int64_t)sm_count() * 6));
+}
+int64_t ln_bwd_ws_floats(int64_t rows, int64_t C) { return (int64_t)lb_grid(rows) * 3 * C; }
 int64_t colsum_ws_floats(int64_t rows, int64_t C) { return (int64_t)qm_grid(rows) * C; }
 
 template <int NV>
@@ -298,23 +316,23 @@ static int32_t ln_bwd_nv(const TDy* dy, const void* src, int src_dtype, const fl
                          const float* rstd, int64_t rows, int gelu, void* dsrc, int dsrc_dtype, float* dgamma,
                          float* dbeta, float* dbias, float* ws, cudaStream_t st) {
   constexpr int C = NV * 128;
-  const int grid = qm_grid(rows);
+  const int grid = lb_grid(rows);
   if (gelu) {
     ILFDT_REQUIRE(src_dtype == ILFDT_BF16 && dsrc_dtype == ILFDT_BF16, ILFDT_E_INVALID_ARG,
                   "ln_bwd: the GELU form reads the bf16 pre-activation and writes a bf16 gradient");
-    ln_bwd_kernel<NV, true, __nv_bfloat16, __nv_bfloat16, TDy><<<grid, QM_THREADS, 0, st>>>(
+    ln_bwd_kernel<NV, true, __nv_bfloat16, __nv_bfloat16, TDy><<<grid, LB_THREADS, 0, st>>>(
         dy, (const __nv_bfloat16*)src, gamma, mean, rstd, rows, (__nv_bfloat16*)dsrc, ws);
   } else {
     ILFDT_REQUIRE(dsrc_dtype == ILFDT_F32, ILFDT_E_INVALID_ARG, "ln_bwd: the plain form writes an fp32 gradient");
     if (src_dtype == ILFDT_F32)
-      ln_bwd_kernel<NV, false, float, float, TDy><<<grid, QM_THREADS, 0, st>>>(dy, (const float*)src, gamma, mean, rstd,
+      ln_bwd_kernel<NV, false, float, float, TDy><<<grid, LB_THREADS, 0, st>>>(dy, (const float*)src, gamma, mean, rstd,
                                                                               rows, (float*)dsrc, ws);
     else
-      ln_bwd_kernel<NV, false, __nv_bfloat16, float, TDy><<<grid, QM_THREADS, 0, st>>>(
+      ln_bwd_kernel<NV, false, __nv_bfloat16, float, TDy><<<grid, LB_THREADS, 0, st>>>(
           dy, (const __nv_bfloat16*)src, gamma, mean, rstd, rows, (float*)dsrc, ws);
   }
   ILFDT_LAUNCH_OK();
-  const int tb = 128, gb = (int)cdiv(C, tb);
+  const int tb = 256, gb = (int)cdiv(C, 32);
   partial_reduce_kernel<<<gb, tb, 0, st>>>(ws, grid, 3 * C, C, dgamma);
   partial_reduce_kernel<<<gb, tb, 0, st>>>(ws + C, grid, 3 * C, C, dbeta);
   if (gelu && dbias) partial_reduce_kernel<<<gb, tb, 0, st>>>(ws + 2 * C, grid, 3 * C, C, dbias);
@@ -369,7 +387,7 @@ int32_t launch_colsum(const void* src, int src_dtype, int64_t rows, int64_t C, f
   else
     colsum_partial_kernel<float><<<grid, QM_THREADS, 0, st>>>((const float*)src, rows, (int)C, ws);
   ILFDT_LAUNCH_OK();
-  partial_reduce_kernel<<<(int)cdiv(C, 128), 128, 0, st>>>(ws, grid, C, (int)C, out);
+  partial_reduce_kernel<<<(int)cdiv(C, 32), 256, 0, st>>>(ws, grid, C, (int)C, out);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }

@@ -38,7 +38,7 @@ def sparsemax(x: torch.Tensor, dim: int = -1) -> torch.Tensor:
     n = z.shape[-1]
     z = z - z.max(dim=1, keepdim=True)[0]                       # sparsemax.py:40
     zs = torch.sort(z, dim=1, descending=True)[0]               # :45
-    ks = torch.arange(1, n + 1, dtype=z.dtype).view(1, -1)      # :46-47
+    ks = torch.arange(1, n + 1, dtype=z.dtype, device=z.device).view(1, -1)      # :46-47
     bound = 1 + ks * zs                                         # :50
     csum = torch.cumsum(zs, dim=1)                              # :51
     is_gt = (bound > csum).to(z.dtype)                          # :52
@@ -147,9 +147,9 @@ def info_nce(logits_per_image, logits_per_text, rank=0):
     """loss.py:40-50. labels = arange(b) when the logits are square, else rank*b + arange(b)."""
     bs, l_bs = logits_per_image.shape
     if l_bs == bs:
-        labels = torch.arange(bs)
+        labels = torch.arange(bs, device=logits_per_image.device)
     else:
-        labels = rank * bs + torch.arange(0, bs, dtype=torch.long)
+        labels = rank * bs + torch.arange(0, bs, dtype=torch.long, device=logits_per_image.device)
     loss_i = F.cross_entropy(logits_per_image, labels)
     loss_t = F.cross_entropy(logits_per_text, labels)
     return (loss_i + loss_t) / 2, labels

@@ -3,7 +3,7 @@
 # included) and one --set full capture of the q_map kernels; each only after the same command exited 0 without ncu.
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out; O=gpurun_out
-ARGS="--steps 1 --warmup 1 --global-batch 4096 --no-cpu-baseline --no-e2e --no-secondary"
+ARGS="--steps 1 --warmup 1 --global-batch 4096 --no-cpu-baseline --no-e2e --no-secondary --no-qmap"
 timeout 600 python bench.py $ARGS > $O/plain_small.log 2>&1 || { echo "plain bench failed"; tail -5 $O/plain_small.log; exit 1; }
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/launches_final.csv python bench.py $ARGS > $O/ncu_launches.log 2>&1
 echo "exit=$? ncu launch list"; wc -l $O/launches_final.csv
