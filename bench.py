@@ -51,7 +51,7 @@ def parse():
     ap.add_argument("--no-secondary", action="store_true", help="skip the trained-like (peaked attention) secondary case")
     ap.add_argument("--no-qmap", action="store_true", help="skip the q_map producer timing (SURVEY 8f N2)")
     ap.add_argument("--trained-scale", type=float, default=200.0, help="q multiplier of the trained-like secondary case")
-    ap.add_argument("--cpu-sample", type=int, default=64, help="rows of the workload timed on the host cores")
+    ap.add_argument("--cpu-sample", type=int, default=256, help="rows of the workload timed on the host cores")
     return ap.parse_args()
 
 
@@ -537,7 +537,7 @@ def run_ours(args):
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu, _ = cpu_reference_run(args.cpu_sample, 3, 1, K)
+        cpu, _ = cpu_reference_run(args.cpu_sample, 5, 1, K)   # ~10 s of host work at 256 rows
         try:
             cpu["gpu_eager"] = gpu_eager_reference_run(256, 3, 1, K, dev)
         except Exception as e:  # noqa: BLE001 -- a context number must not take the bench line down

