@@ -899,6 +899,10 @@ static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, con
   int64_t nsplit = 1;
   const int64_t target = 4ll * sm_count();
   if (groups < target) nsplit = std::min<int64_t>(cdiv(target, groups), std::max<int64_t>(1, b / 256));
+  // tuning knob: ILFDT_DSD_SPLIT=n splits the sample sweep of large batches into n ranges (grid.y, atomics): shorter
+  // sweeps keep the resident CTAs on the same L2-resident slice of q
+  static const int force_split = getenv("ILFDT_DSD_SPLIT") ? atoi(getenv("ILFDT_DSD_SPLIT")) : 0;
+  if (force_split > 1 && b >= 4096) nsplit = force_split;
   nsplit = std::min<int64_t>(std::max<int64_t>(nsplit, 1), 65535);
   int64_t per = round_up(cdiv(b, nsplit), TS);
   nsplit = cdiv(b, per);

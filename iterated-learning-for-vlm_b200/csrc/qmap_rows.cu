@@ -13,12 +13,33 @@ namespace ilfdt {
 constexpr int QM_THREADS = 256;            // 8 warps = 8 rows in flight per CTA
 constexpr int QM_WARPS = QM_THREADS / 32;
 
-__device__ __forceinline__ float gelu_erf(float v) { return 0.5f * v * (1.f + erff(v * 0.70710678118654752440f)); }
-// d/dv [ v * Phi(v) ] = Phi(v) + v * phi(v)
-__device__ __forceinline__ float gelu_erf_grad(float v) {
-  const float cdf = 0.5f * (1.f + erff(v * 0.70710678118654752440f));
-  const float pdf = 0.39894228040143267794f * __expf(-0.5f * v * v);
-  return fmaf(v, pdf, cdf);
+// Exact-erf GELU (nn.GELU(), clip_fdt.py:89) with erf from Abramowitz & Stegun 7.1.26 (|error| <= 1.5e-7, below fp32
+// rounding of the products it enters): Phi(v) = 0.5 (1 + erf(v / sqrt 2)), erf(x) = sign(x) (1 - P(t) e^{-x^2}),
+// t = 1 / (1 + p |x|). With x = v / sqrt 2 the exponential is e^{-v^2 / 2}: the same one the density phi(v) needs, so the
+// backward pays one MUFU.EX2 and one MUFU.RCP per element instead of erff's branchy polynomial plus an expf
+// (ncu r01: the GELU forms of ln_fwd / ln_bwd were issue-bound at 58 instructions per element).
+__device__ __forceinline__ void gelu_parts(float v, float& cdf, float& e) {
+  const float ax = fabsf(v) * 0.70710678118654752440f;
+  const float t = __fdividef(1.f, fmaf(0.3275911f, ax, 1.f));
+  e = exp2f(v * v * -0.72134752044448170368f);                 // e^{-v^2/2}
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float half_tail = 0.5f * poly * t * e;                 // 0.5 (1 - erf|x|)
+  cdf = v >= 0.f ? 1.f - half_tail : half_tail;
+}
+__device__ __forceinline__ float gelu_erf(float v) {
+  float cdf, e;
+  gelu_parts(v, cdf, e);
+  return v * cdf;
+}
+// a = v Phi(v) and d a / d v = Phi(v) + v phi(v)
+__device__ __forceinline__ void gelu_erf_and_grad(float v, float& a, float& g) {
+  float cdf, e;
+  gelu_parts(v, cdf, e);
+  a = v * cdf;
+  g = fmaf(v * 0.39894228040143267794f, e, cdf);
 }
 
 // 4 consecutive elements <-> fp32 registers, fp32 or bf16 storage
@@ -142,8 +163,9 @@ ln_bwd_kernel(const TDy* __restrict__ dy, const TIn* __restrict__ src, const flo
       ld4(dy + r * C + j * 128 + lane * 4, d);
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
-        const float a = GELU ? gelu_erf(u[e]) : u[e];
-        gp[j][e] = GELU ? gelu_erf_grad(u[e]) : 1.f;
+        float a = u[e];
+        gp[j][e] = 1.f;
+        if (GELU) gelu_erf_and_grad(u[e], a, gp[j][e]);
         xh[j][e] = (a - mu) * rs;
         ag[j][e] = fmaf(d[e], xh[j][e], ag[j][e]);
         ab[j][e] += d[e];
