@@ -494,6 +494,22 @@ constexpr int G3_THREADS = 256, G3_WARPS = G3_THREADS / 32, G3_PER = 64, G3_CHUN
 constexpr int G3_GROUPS = G3_PER / 4;
 constexpr int G3_MAX_TOK = 96;
 
+// L2 eviction policy for the gathered rows: the rows that are reused by every CTA (the codebook in kernel 1, the current
+// slice of q in kernel 2) are loaded evict-last so that the streamed per-sample arrays (g / w / arg, coef) do not push
+// them out of L2.
+__device__ __forceinline__ uint64_t l2_policy(bool keep) {
+  uint64_t pol;
+  if (keep) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint4 ldg_hint(const void* p, uint64_t pol) {
+  uint4 r;
+  asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(pol));
+  return r;
+}
+
 template <typename TO>
 struct StoreRow8;
 template <>
@@ -552,8 +568,9 @@ template <typename T, int NV, typename TO, typename TW>
 __global__ void __launch_bounds__(G3_THREADS, 3)
 ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const int16_t* __restrict__ arg,
                         const T* __restrict__ sd, const float* __restrict__ mask, int n_tok, int K, int D,
-                        float inv_scale, TO* __restrict__ dq) {
+                        float inv_scale, TO* __restrict__ dq, int keep_rows) {
   extern __shared__ __align__(16) unsigned char gb_smem[];
+  const uint64_t row_pol = l2_policy(keep_rows != 0);
   uint16_t* hist = reinterpret_cast<uint16_t*>(gb_smem);                                    // [n_tok][256]
   uint16_t* sorted_k = reinterpret_cast<uint16_t*>(gb_smem + (size_t)n_tok * G3_THREADS * 2);  // [G3_CHUNK]
   int* base = reinterpret_cast<int*>(sorted_k + G3_CHUNK);                                  // [n_tok + 1]
@@ -724,7 +741,7 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const i
             cc[u] = __shfl_sync(0xffffffffu, myc, j + u);
             const T* row = sd + (int64_t)(k0 + kq) * D;
 #pragma unroll
-            for (int i = 0; i < NV; ++i) raw[u][i] = __ldg(reinterpret_cast<const uint4*>(row + (i * 32 + lane) * 8));
+            for (int i = 0; i < NV; ++i) raw[u][i] = ldg_hint(row + (i * 32 + lane) * 8, row_pol);
           }
 #pragma unroll
           for (int u = 0; u < 4; ++u)
@@ -766,6 +783,7 @@ ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restri
   // dense random-init statistics (the headline), TS = 128 is 3 ms faster when the support is a few tens of codes and
   // the kernel is a pure scan of coef / arg (ILFDT_DSD_CFG=128)
   constexpr int SUB = TS / 32;
+  const uint64_t row_pol = l2_policy((use_atomic & 4) != 0);
   constexpr int CODES = WARPS * CPW, THREADS = WARPS * 32, QUADS = CODES / 4, SLOTS = TS * QUADS;
   constexpr int LPT = (SLOTS + THREADS - 1) / THREADS;   // (sample, 4-code quad) slots per thread per tile
   __shared__ float cf_s[2][CODES][TS + 1];
@@ -795,8 +813,13 @@ ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restri
       rc[l] = make_float4(0.f, 0.f, 0.f, 0.f);
       rt[l] = make_uint2(0u, 0u);
       if (slot < SLOTS && bb < b_end) {
-        rc[l] = __ldg(reinterpret_cast<const float4*>(coef + bb * K + k0 + ld_q));
-        rt[l] = __ldg(reinterpret_cast<const uint2*>(arg + bb * K + k0 + ld_q));
+        if (use_atomic & 2) {   // streaming (evict-first) loads: coef / arg are read once, the q rows are the reused data
+          rc[l] = __ldcs(reinterpret_cast<const float4*>(coef + bb * K + k0 + ld_q));
+          rt[l] = __ldcs(reinterpret_cast<const uint2*>(arg + bb * K + k0 + ld_q));
+        } else {
+          rc[l] = __ldg(reinterpret_cast<const float4*>(coef + bb * K + k0 + ld_q));
+          rt[l] = __ldg(reinterpret_cast<const uint2*>(arg + bb * K + k0 + ld_q));
+        }
       }
     }
   };
@@ -847,7 +870,7 @@ ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restri
             const T* row = q + rr * D;
             if constexpr (sizeof(T) == 2) {
 #pragma unroll
-              for (int i = 0; i < NV; ++i) raw[u][i] = __ldg(reinterpret_cast<const uint4*>(row + (i * 32 + lane) * 8));
+              for (int i = 0; i < NV; ++i) raw[u][i] = ldg_hint(row + (i * 32 + lane) * 8, row_pol);
             } else {
               gb_axpy<T, NV>(row, cc[u], lane, acc[c]);
             }
@@ -881,9 +904,13 @@ ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restri
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       float* o = out + (i * 32 + lane) * 8;
-      if (use_atomic) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) atomicAdd(o + j, acc[c][i][j]);
+      if (use_atomic & 1) {
+        // a lane owns 8 consecutive floats = one 32-byte sector: two 16-byte vector reductions (REDG.E.ADD.F32x4)
+        // instead of eight scalar atomics
+        asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o), "f"(acc[c][i][0]), "f"(acc[c][i][1]),
+                     "f"(acc[c][i][2]), "f"(acc[c][i][3]) : "memory");
+        asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o + 4), "f"(acc[c][i][4]), "f"(acc[c][i][5]),
+                     "f"(acc[c][i][6]), "f"(acc[c][i][7]) : "memory");
       } else {
         StoreRow8<float>::st(o, acc[c][i], true);
       }
@@ -899,16 +926,21 @@ static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, con
   int64_t nsplit = 1;
   const int64_t target = 4ll * sm_count();
   if (groups < target) nsplit = std::min<int64_t>(cdiv(target, groups), std::max<int64_t>(1, b / 256));
-  // tuning knob: ILFDT_DSD_SPLIT=n splits the sample sweep of large batches into n ranges (grid.y, atomics): shorter
-  // sweeps keep the resident CTAs on the same L2-resident slice of q
-  static const int force_split = getenv("ILFDT_DSD_SPLIT") ? atoi(getenv("ILFDT_DSD_SPLIT")) : 0;
-  if (force_split > 1 && b >= 4096) nsplit = force_split;
+  // Large batches: the sample sweep is cut into ranges (grid.y; partial rows combined with vector reductions). One
+  // CTA sweeping all of q drifts away from its neighbours, and the q rows the ~740 resident CTAs gather stop sharing
+  // L2 lines (ncu r01: 70 % hit rate); short sweeps restart them together: 48.3 -> 43.8 ms per step at b = 32768
+  // (A/B on one box, 8 ranges). ILFDT_DSD_SPLIT overrides the rows per range (0 = never split).
+  static const int split_rows = getenv("ILFDT_DSD_SPLIT") ? atoi(getenv("ILFDT_DSD_SPLIT")) : 1024;
+  if (split_rows > 0 && b >= 2 * (int64_t)split_rows) nsplit = std::max<int64_t>(nsplit, b / split_rows);
+  // coef / arg are read once per launch: streaming loads (41.2 vs 42.3 ms per step for the scatter pair, ABAB on one box)
+  static const int stream_flag = ((getenv("ILFDT_DSD_STREAM") && atoi(getenv("ILFDT_DSD_STREAM")) == 0) ? 0 : 2) |
+                                 ((getenv("ILFDT_GBWD_KEEP") && (atoi(getenv("ILFDT_GBWD_KEEP")) & 2)) ? 4 : 0);
   nsplit = std::min<int64_t>(std::max<int64_t>(nsplit, 1), 65535);
   int64_t per = round_up(cdiv(b, nsplit), TS);
   nsplit = cdiv(b, per);
   dim3 grid((unsigned)groups, (unsigned)nsplit);
   ground_bwd_dsd_v3_kernel<T, NV, WARPS, CPW, U, TS><<<grid, WARPS * 32, 0, st>>>(g, arg, q, row_base, b, (int)n_tok, (int)K,
-                                                                             (int)D, per, nsplit > 1 ? 1 : 0, dsd);
+                                                                             (int)D, per, (nsplit > 1 ? 1 : 0) | stream_flag, dsd);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }
@@ -921,8 +953,9 @@ static int32_t launch_dq_v3(float* g, const TW* w, const int16_t* arg, const T* 
   ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_v3_kernel<T, NV, TO, TW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)((size_t)G3_MAX_TOK * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 +
                                            (G3_MAX_TOK + 1) * sizeof(int) + G3_MAX_TOK * sizeof(float))));
+  static const int keep = getenv("ILFDT_GBWD_KEEP") ? atoi(getenv("ILFDT_GBWD_KEEP")) : 0;
   ground_bwd_dq_v3_kernel<T, NV, TO, TW><<<(unsigned)b, G3_THREADS, smem, st>>>(g, w, arg, sd, mask, (int)n_tok, (int)K,
-                                                                           (int)D, inv_scale, dq);
+                                                                           (int)D, inv_scale, dq, keep & 1);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }
