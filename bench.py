@@ -290,8 +290,9 @@ def run_ours(args):
         sd.grad = None
         p.grad = None
         mode = Fn.get_compute_dtype()
-        _, f_i = Fn.GroundingFunction.apply(qi, sd, None, TEMPERATURE, mode, False)   # att_weight is dropped there
-        _, f_t = Fn.GroundingFunction.apply(qt, sd, mk, TEMPERATURE, mode, False)
+        with Fn.codebook_scope():   # as Clip_FDT.forward: one bf16 copy of the codebook for both modalities
+            _, f_i = Fn.GroundingFunction.apply(qi, sd, None, TEMPERATURE, mode, False)   # att_weight is dropped there
+            _, f_t = Fn.GroundingFunction.apply(qt, sd, mk, TEMPERATURE, mode, False)
         x_i = Fn.L2NormFunction.apply(f_i, 1e-10)
         x_t = Fn.L2NormFunction.apply(f_t, 1e-10)
         s = p.exp()

@@ -12,7 +12,8 @@
  *     last failure on the calling thread is ilfdt_last_error().
  *   - the caller owns ALL memory. Pointers are device pointers unless named host_*. Tensors are
  *     dense row-major with the shapes given. Nothing here allocates user-visible buffers,
- *     synchronises the host, or keeps global mutable state (one small per-thread error string).
+ *     synchronises the host, or keeps global mutable state (one small per-thread error string and the
+ *     ilfdt_tune_* knobs).
  *   - `stream` is a cudaStream_t passed as void*. Work is enqueued on it and the call returns.
  *   - dtype arguments are ILFDT_F32 or ILFDT_BF16. F32 selects the fp32-exact SIMT kernels
  *     (parity mode, <=1e-5 rel); BF16 selects the tcgen05/TMEM/TMA tensor-core kernels with fp32
@@ -30,7 +31,7 @@
 extern "C" {
 #endif
 
-#define ILFDT_ABI_VERSION 3
+#define ILFDT_ABI_VERSION 4
 
 enum {
   ILFDT_OK = 0,
@@ -49,6 +50,21 @@ int32_t ilfdt_abi_version(void);
 const char* ilfdt_last_error(void);
 /* 0 if `device` is an sm_100 part and the kernels can run there, ILFDT_E_ARCH otherwise. */
 int32_t ilfdt_device_check(int32_t device);
+
+/* Tuning knobs: process-wide, explicit (never read from the environment), none changes a result beyond fp32
+ * summation order. They exist so that tests and tools can A/B the routes in one process. */
+enum {
+  ILFDT_TUNE_DSD_SPLIT_ROWS = 0, /* ilfdt_ground_bwd: samples per range of the codebook-gradient sweep (default 1024);
+                                    0 = one sweep, order-deterministic, no float reductions */
+  ILFDT_TUNE_DSD_TILE = 1,       /* ilfdt_ground_bwd: 32 (default) or 128 samples per cooperative tile */
+  ILFDT_TUNE_DSD_STREAM = 2,     /* ilfdt_ground_bwd: 1 (default) = evict-first loads of the once-read coef / arg */
+  ILFDT_TUNE_GROUND_2CTA = 3,    /* ilfdt_ground_fwd*: 1 (default) = cta_group::2 kernel, 0 = single-CTA kernel */
+  ILFDT_TUNE_GEMM_WIDE2 = 4,     /* ilfdt_gemm_nt: 1 (default) = CTA-pair kernel for short-operand / long-reduction shapes */
+  ILFDT_TUNE_NCE_2CTA = 5,       /* ilfdt_nce_bwd*: 1 (default) = cta_group::2 kernel */
+  ILFDT_TUNE_COUNT_ = 6
+};
+int32_t ilfdt_tune_set(int32_t key, int64_t value);
+int64_t ilfdt_tune_get(int32_t key);
 
 /* ---- layout helpers (feed the bf16 tensor-core kernels) ----------------------------------- */
 /* dst_bf16[i] = bf16(src[i]) */

@@ -2,8 +2,13 @@
 #include "common.cuh"
 #include "launch.h"
 #include <algorithm>
+#include <atomic>
 
 namespace ilfdt {
+
+// tuning knobs: explicit API state instead of environment variables read into statics (defaults = the tuned values)
+static std::atomic<int64_t> g_tune[ILFDT_TUNE_COUNT_] = {{1024}, {32}, {1}, {1}, {1}, {1}};
+int64_t tune_get(int key) { return (key >= 0 && key < ILFDT_TUNE_COUNT_) ? g_tune[key].load(std::memory_order_relaxed) : 0; }
 
 int sm_count() {
   static thread_local int cached_dev = -1, cached = 148;
@@ -140,6 +145,16 @@ extern "C" {
 
 int32_t ilfdt_abi_version(void) { return ILFDT_ABI_VERSION; }
 const char* ilfdt_last_error(void) { return err_buf(); }
+
+int32_t ilfdt_tune_set(int32_t key, int64_t value) {
+  ILFDT_REQUIRE(key >= 0 && key < ILFDT_TUNE_COUNT_, ILFDT_E_INVALID_ARG, "tune_set: unknown key %d", key);
+  ILFDT_REQUIRE(value >= 0, ILFDT_E_INVALID_ARG, "tune_set: negative value");
+  ILFDT_REQUIRE(key != ILFDT_TUNE_DSD_TILE || value == 32 || value == 128, ILFDT_E_INVALID_ARG,
+                "tune_set: ILFDT_TUNE_DSD_TILE is 32 or 128");
+  g_tune[key].store(value, std::memory_order_relaxed);
+  return ILFDT_OK;
+}
+int64_t ilfdt_tune_get(int32_t key) { return tune_get(key); }
 
 int32_t ilfdt_device_check(int32_t device) {
   int major = 0;

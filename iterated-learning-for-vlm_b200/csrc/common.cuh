@@ -48,6 +48,8 @@ inline int32_t fail(int32_t code, const char* fmt, ...) {
 // Refuse to run anywhere but on an sm_100 part: there is deliberately no other code path.
 int32_t require_sm100();
 int sm_count();
+// process-wide tuning knobs (ilfdt_tune_set / ilfdt_tune_get, include/ilfdt.h); key = ILFDT_TUNE_*
+int64_t tune_get(int key);
 
 inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 inline int64_t round_up(int64_t a, int64_t b) { return cdiv(a, b) * b; }

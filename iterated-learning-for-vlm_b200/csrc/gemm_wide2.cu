@@ -168,8 +168,7 @@ gemm_wide2_kernel(const __grid_constant__ CUtensorMap tmLane, const __grid_const
 }
 
 bool gemm_wide2_enabled() {
-  static const int on = getenv("ILFDT_GEMM_WIDE") ? atoi(getenv("ILFDT_GEMM_WIDE")) : 1;
-  return on != 0;
+  return tune_get(ILFDT_TUNE_GEMM_WIDE2) != 0;
 }
 // shapes the pair kernel takes: a short A (all of its rows fit two accumulators), many B rows, a long reduction
 bool gemm_wide2_supported(int64_t M, int64_t N, int64_t Kr, const float* out, int64_t ldo) {

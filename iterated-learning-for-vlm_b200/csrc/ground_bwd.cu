@@ -929,12 +929,11 @@ static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, con
   // Large batches: the sample sweep is cut into ranges (grid.y; partial rows combined with vector reductions). One
   // CTA sweeping all of q drifts away from its neighbours, and the q rows the ~740 resident CTAs gather stop sharing
   // L2 lines (ncu r01: 70 % hit rate); short sweeps restart them together: 48.3 -> 43.8 ms per step at b = 32768
-  // (A/B on one box, 8 ranges). ILFDT_DSD_SPLIT overrides the rows per range (0 = never split).
-  static const int split_rows = getenv("ILFDT_DSD_SPLIT") ? atoi(getenv("ILFDT_DSD_SPLIT")) : 1024;
-  if (split_rows > 0 && b >= 2 * (int64_t)split_rows) nsplit = std::max<int64_t>(nsplit, b / split_rows);
+  // (A/B on one box, 8 ranges). ilfdt_tune_set(ILFDT_TUNE_DSD_SPLIT_ROWS) overrides the rows per range (0 = never split).
+  const int64_t split_rows = tune_get(ILFDT_TUNE_DSD_SPLIT_ROWS);
+  if (split_rows > 0 && b >= 2 * split_rows) nsplit = std::max<int64_t>(nsplit, b / split_rows);
   // coef / arg are read once per launch: streaming loads (41.2 vs 42.3 ms per step for the scatter pair, ABAB on one box)
-  static const int stream_flag = ((getenv("ILFDT_DSD_STREAM") && atoi(getenv("ILFDT_DSD_STREAM")) == 0) ? 0 : 2) |
-                                 ((getenv("ILFDT_GBWD_KEEP") && (atoi(getenv("ILFDT_GBWD_KEEP")) & 2)) ? 4 : 0);
+  const int stream_flag = tune_get(ILFDT_TUNE_DSD_STREAM) ? 2 : 0;
   nsplit = std::min<int64_t>(std::max<int64_t>(nsplit, 1), 65535);
   int64_t per = round_up(cdiv(b, nsplit), TS);
   nsplit = cdiv(b, per);
@@ -953,9 +952,8 @@ static int32_t launch_dq_v3(float* g, const TW* w, const int16_t* arg, const T* 
   ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_v3_kernel<T, NV, TO, TW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)((size_t)G3_MAX_TOK * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 +
                                            (G3_MAX_TOK + 1) * sizeof(int) + G3_MAX_TOK * sizeof(float))));
-  static const int keep = getenv("ILFDT_GBWD_KEEP") ? atoi(getenv("ILFDT_GBWD_KEEP")) : 0;
   ground_bwd_dq_v3_kernel<T, NV, TO, TW><<<(unsigned)b, G3_THREADS, smem, st>>>(g, w, arg, sd, mask, (int)n_tok, (int)K,
-                                                                           (int)D, inv_scale, dq, keep & 1);
+                                                                           (int)D, inv_scale, dq, 0);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }
@@ -969,8 +967,6 @@ static int32_t launch_ground_bwd_t(float* g, const void* w_v, int w_dtype, const
   // the support comes from the fp32 weights or (scatter kernel v3 only) from their bf16 copy
   const float* w = w_dtype == ILFDT_F32 ? reinterpret_cast<const float*>(w_v) : nullptr;
   const __nv_bfloat16* w16 = w_dtype == ILFDT_BF16 ? reinterpret_cast<const __nv_bfloat16*>(w_v) : nullptr;
-  static const int skip = getenv("ILFDT_GBWD_SKIP") ? atoi(getenv("ILFDT_GBWD_SKIP")) : 0;  // tuning only: 1 = no dq, 2 = no dsd
-  if (skip == 1) done = true;
   if constexpr (NV > 0) {
     const bool v3_ok = n_tok <= G3_MAX_TOK && K % 4 == 0 &&
                        ((reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(w)) & 15) == 0 &&
@@ -1015,23 +1011,15 @@ static int32_t launch_ground_bwd_t(float* g, const void* w_v, int w_dtype, const
                                                                       (int)D, inv_scale, dq);
     ILFDT_LAUNCH_OK();
   }
-  if (skip == 2) return ILFDT_OK;
   if constexpr (NV > 0) {
     // shape of kernel 2 (warps x codes per warp, rows in flight), tuned on B200 at b = 8192, K = 16384, D = 512
-    // (tools/tune_gbwd.py): 4x1 codes with 4 rows in flight beat the original 4x4/2 by 1.4x. ILFDT_DSD_CFG
-    // overrides the shape for tuning runs.
-    static const int cfg = getenv("ILFDT_DSD_CFG") ? atoi(getenv("ILFDT_DSD_CFG")) : 0;
+    // (profiles/r01_tune_dsd_shapes.txt): 4x1 codes with 4 rows in flight beat the original 4x4/2 by 1.4x.
+    // ILFDT_TUNE_DSD_TILE = 128 selects the 128-sample cooperative tile (better when the support is tens of codes).
     if (K % 32 == 0 && ((reinterpret_cast<uintptr_t>(g) & 15) | (reinterpret_cast<uintptr_t>(arg) & 7)) == 0) {
       if constexpr (NV <= 2) {
-        switch (cfg) {
-          case 1: return launch_dsd_v3<T, NV, 4, 4, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
-          case 2: return launch_dsd_v3<T, NV, 4, 4, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
-          case 5: return launch_dsd_v3<T, NV, 8, 1, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
-          case 7: return launch_dsd_v3<T, NV, 4, 2, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
-          case 14: return launch_dsd_v3<T, NV, 8, 1, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
-          case 128: return launch_dsd_v3<T, NV, 4, 1, 4, 128>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
-          default: return launch_dsd_v3<T, NV, 4, 1, 4, 32>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
-        }
+        if (tune_get(ILFDT_TUNE_DSD_TILE) == 128)
+          return launch_dsd_v3<T, NV, 4, 1, 4, 128>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
+        return launch_dsd_v3<T, NV, 4, 1, 4, 32>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
       } else {
         return launch_dsd_v3<T, NV, 4, 1, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
       }

@@ -237,8 +237,7 @@ static int32_t launch_g2_t(const CUtensorMap& tmA, const CUtensorMap& tmB, G2Par
 }
 
 bool ground2_enabled() {
-  static const int on = getenv("ILFDT_GROUND_2CTA") ? atoi(getenv("ILFDT_GROUND_2CTA")) : 1;
-  return on != 0;
+  return tune_get(ILFDT_TUNE_GROUND_2CTA) != 0;
 }
 bool ground2_supported(int64_t n_tok, int64_t D) {
   return D <= 512 && D % 8 == 0 &&

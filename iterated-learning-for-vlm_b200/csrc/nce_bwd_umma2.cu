@@ -311,8 +311,7 @@ nce_bwd2_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant_
 
 // ---- host side --------------------------------------------------------------------------------------
 bool nce_bwd_pair_enabled() {
-  static const int on = getenv("ILFDT_NCE_2CTA") ? atoi(getenv("ILFDT_NCE_2CTA")) : 1;
-  return on != 0;
+  return tune_get(ILFDT_TUNE_NCE_2CTA) != 0;
 }
 
 template <int MODE>

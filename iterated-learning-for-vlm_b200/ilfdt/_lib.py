@@ -23,6 +23,8 @@ SIGNATURES = {
     "ilfdt_abi_version": (_i32, []),
     "ilfdt_last_error": (ctypes.c_char_p, []),
     "ilfdt_device_check": (_i32, [_i32]),
+    "ilfdt_tune_set": (_i32, [_i32, _i64]),
+    "ilfdt_tune_get": (_i64, [_i32]),
     "ilfdt_cast_bf16": (_i32, [_p, _p, _i64, _p]),
     "ilfdt_cast_bf16_rows": (_i32, [_p, _p, _i64, _i64, _p, _p]),
     "ilfdt_mask_rows_bf16": (_i32, [_p, _p, _i64, _i64, _p, _p]),
@@ -72,6 +74,8 @@ SIGNATURES = {
     "ilfdt_copy": (_i32, [_p, _p, _i64, _p]),
 }
 
+TUNE = {"dsd_split_rows": 0, "dsd_tile": 1, "dsd_stream": 2, "ground_2cta": 3, "gemm_wide2": 4, "nce_2cta": 5}
+
 _lib = None
 
 
@@ -89,7 +93,7 @@ def load():
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.ilfdt_abi_version() != 3:
+    if lib.ilfdt_abi_version() != 4:
         raise RuntimeError("libilfdt ABI version mismatch")
     _lib = lib
     return lib

@@ -3,6 +3,7 @@ the seams between the reference-shaped nn.Modules (ilfdt.model, ilfdt.loss_funct
 kernels. Reference lines cited are relative to the reference repo root."""
 import math
 import os
+import warnings
 
 import torch
 import torch.distributed as dist
@@ -43,19 +44,51 @@ class compute_dtype:
 COMPACT_TEXT = os.environ.get("ILFDT_COMPACT_TEXT", "1") != "0"
 LEAN_WEIGHTS = os.environ.get("ILFDT_LEAN_WEIGHTS", "1") != "0"   # need_weights=False skips the fp32 att_weight
 
-# bf16 copies of the codebook are shared by the two Query_models of one step
-_sd_cache = {}
+# bf16 copies of the codebook ([K,D] and its [D,K] transpose). They are recomputed on every call (two small
+# kernels) unless the caller opens an explicit `codebook_scope()` around calls that provably see the same
+# codebook values -- Clip_FDT.forward does, around its two Query_models. There is deliberately NO cache keyed on
+# (data_ptr, _version): writes through `.data`, raw pointers (reset_codebook, keep_codebook_value) or a CUDA-graph
+# replay do not bump `_version`, and a stale bf16 codebook is a silent wrong answer.
+_sd_scope = None
+
+
+class codebook_scope:
+    """with codebook_scope(): ... -- calls inside share one bf16 copy per codebook tensor. The scope must not span
+    any write to the codebook; it is re-entrant (an inner scope reuses the outer one) and is closed on exit, so the
+    casts are issued (and captured, under CUDA-graph capture) once per step."""
+
+    def __enter__(self):
+        global _sd_scope
+        self.outer = _sd_scope
+        if _sd_scope is None:
+            _sd_scope = {}
+        return self
+
+    def __exit__(self, *a):
+        global _sd_scope
+        _sd_scope = self.outer
 
 
 def _sd_bf16(sd):
-    key = (sd.data_ptr(), sd._version, tuple(sd.shape))
-    hit = _sd_cache.get("k")
-    if hit is not None and hit[0] == key:
-        return hit[1], hit[2]
+    key = (sd.data_ptr(), tuple(sd.shape), sd.device)
+    if _sd_scope is not None:
+        hit = _sd_scope.get(key)
+        if hit is not None:
+            return hit
     sd_b = ops.cast_bf16(sd.detach())
     sd_bt = ops.transpose_bf16(sd_b)
-    _sd_cache["k"] = (key, sd_b, sd_bt)
+    if _sd_scope is not None:
+        _sd_scope[key] = (sd_b, sd_bt)
     return sd_b, sd_bt
+
+
+_warned = set()
+
+
+def _warn_once(msg):
+    if msg not in _warned:
+        _warned.add(msg)
+        warnings.warn(msg, RuntimeWarning, stacklevel=3)
 
 
 class GroundingFunction(torch.autograd.Function):
@@ -76,7 +109,12 @@ class GroundingFunction(torch.autograd.Function):
         mask_f = None if mask is None else mask.to(torch.float32).contiguous()
         if mode == "bf16" and not (q.shape[2] % 8 == 0 and q.shape[2] <= 512 and q.shape[1] <= 256
                                    and sd.shape[0] % 8 == 0):
-            mode = "fp32"   # shapes outside the tcgen05 kernel's tiling take the fp32 CUDA kernels
+            # shapes outside the tcgen05 kernel's tiling take the fp32 CUDA kernels (still libilfdt, never PyTorch math)
+            _warn_once("ilfdt: grounding shape q%s x codebook%s is outside the tensor-core tiling (D %% 8 == 0, D <= 512, "
+                       "N <= 256, K %% 8 == 0): running the fp32 SIMT kernels" % (tuple(q.shape), tuple(sd.shape)))
+            mode = "fp32"
+            if q.dtype == torch.bfloat16:
+                q = q.float()      # dq is cast back to bf16 at the end of backward
         row_base = None
         if mode == "bf16":
             sd_k, sd_kt = _sd_bf16(sd_c)

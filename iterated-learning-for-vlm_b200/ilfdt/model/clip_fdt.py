@@ -19,10 +19,15 @@ from .sparsemax import Sparsemax
 
 
 def weight_reset(m):
-    """clip_fdt.py:42-46: re-run a layer's own initialiser if it has one."""
-    reset = getattr(m, "reset_parameters", None)
-    if callable(reset):
+    """clip_fdt.py:36-44: ONLY Conv2d / Linear / ConvTranspose2d / BatchNorm2d (+ running stats) / LayerNorm are
+    re-initialised. Everything else -- nn.Embedding (the text encoder's token_embedding, initialised with std 0.02),
+    nn.MultiheadAttention's in_proj, bare nn.Parameters -- survives a reset, exactly as in the reference."""
+    if isinstance(m, (nn.Conv2d, nn.Linear, nn.ConvTranspose2d, nn.LayerNorm)):
         m.reset_parameters()
+    elif isinstance(m, nn.BatchNorm2d):
+        m.reset_parameters()
+        m.running_mean.zero_()
+        m.running_var.fill_(1)
 
 
 class Query_model(nn.Module):
@@ -101,8 +106,30 @@ class Clip_FDT(nn.Module):
         nn.init.constant_(self.logit_scale_sd, np.log(1 / 0.07))
         self.stored_vision_encoder_weight = None
         self.stored_codebook = None
+        # (seed, generation) key the Philox stream of reset_codebook(); they travel with checkpoints as the optional
+        # state_dict entry `codebook_rng` (see _save_to_state_dict) so that a resumed run does not redraw the
+        # codebooks of earlier generations
         self.codebook_generation = 0
         self.codebook_seed = 0
+
+    _RNG_KEY = "codebook_rng"
+
+    def _save_to_state_dict(self, destination, prefix, keep_vars):
+        """The key set equals the reference's (checkpoints interchange) until reset_codebook() has run; from then on
+        one extra int64[2] entry carries (seed, generation). The reference's loader is non-strict
+        (prototype/utils/misc.py:495) and ignores it."""
+        super()._save_to_state_dict(destination, prefix, keep_vars)
+        if self.codebook_generation or self.codebook_seed:
+            destination[prefix + self._RNG_KEY] = torch.tensor([self.codebook_seed, self.codebook_generation],
+                                                              dtype=torch.int64)
+
+    def _load_from_state_dict(self, state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys,
+                              error_msgs):
+        rng = state_dict.pop(prefix + self._RNG_KEY, None)   # optional: absent from reference checkpoints
+        if rng is not None:
+            self.codebook_seed, self.codebook_generation = int(rng[0]), int(rng[1])
+        super()._load_from_state_dict(state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys,
+                                      error_msgs)
 
     # ---- helpers the solver / eval adapters call (clip_fdt.py:236-386) --------------------------
     @property
@@ -236,8 +263,9 @@ class Clip_FDT(nn.Module):
         patch_ft = self._image_features(images)
         _, word_ft, _, pad_mask = self.encode_text(texts, return_dense=True, return_padmask=True,
                                                    return_raw_feature=True)
-        _, sd_img_ft, img_k = self.img_query_model(patch_ft, self.space_dict, need_weights=False)
-        _, sd_txt_ft, txt_k = self.txt_query_model(word_ft, self.space_dict, mask=pad_mask, need_weights=False)
+        with Fn.codebook_scope():   # both Query_models read the same codebook values: one bf16 copy for the two
+            _, sd_img_ft, img_k = self.img_query_model(patch_ft, self.space_dict, need_weights=False)
+            _, sd_txt_ft, txt_k = self.txt_query_model(word_ft, self.space_dict, mask=pad_mask, need_weights=False)
 
         sd_img_ft = Fn.L2NormFunction.apply(sd_img_ft, 1e-10)       # :411
         sd_txt_ft = Fn.L2NormFunction.apply(sd_txt_ft, 1e-10)       # :412

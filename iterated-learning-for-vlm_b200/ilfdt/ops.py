@@ -48,6 +48,25 @@ def profile_summary():
     return {k: (len(v), sum(a.elapsed_time(b) for a, b in v)) for k, v in PROFILE.items()}
 
 
+class tune:
+    """with ops.tune(dsd_split_rows=0): ... -- sets ilfdt_tune_* knobs (include/ilfdt.h) and restores them on exit."""
+
+    def __init__(self, **kv):
+        self.kv = kv
+
+    def __enter__(self):
+        lib = _lib.load()
+        self.prev = {k: lib.ilfdt_tune_get(_lib.TUNE[k]) for k in self.kv}
+        for k, v in self.kv.items():
+            check(lib.ilfdt_tune_set(_lib.TUNE[k], int(v)))
+        return self
+
+    def __exit__(self, *a):
+        lib = _lib.load()
+        for k, v in self.prev.items():
+            lib.ilfdt_tune_set(_lib.TUNE[k], int(v))
+
+
 def _ptr(t):
     return 0 if t is None else t.data_ptr()
 

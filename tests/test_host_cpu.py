@@ -37,7 +37,7 @@ def test_abi_exports_every_declared_symbol(built_lib):
     for n in names:
         assert hasattr(lib, n), "libilfdt.so does not export %s" % n
     lib.ilfdt_abi_version.restype = ctypes.c_int32
-    assert lib.ilfdt_abi_version() == 3
+    assert lib.ilfdt_abi_version() == 4
 
 
 def test_python_binding_covers_the_header(built_lib):
@@ -248,3 +248,103 @@ def test_logit_scale_step_clip_matches_reference_rule():
             want = p.data.clone()
         clip_logit_scale_step(p, b, value)
         assert torch.equal(p.data.reshape(()), want.reshape(())), (before, after, value)
+
+
+def test_weight_reset_whitelist_matches_reference():
+    """clip_fdt.py:36-44: only Conv2d / Linear / ConvTranspose2d / BatchNorm2d / LayerNorm are re-initialised by
+    reset_text_encoder / reset_vision_encoder; an nn.Embedding (token_embedding, std 0.02) and bare Parameters survive."""
+    from ilfdt.model.clip_fdt import Clip_FDT, weight_reset
+
+    class Txt(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.token_embedding = torch.nn.Embedding(11, 8)
+            torch.nn.init.normal_(self.token_embedding.weight, std=0.02)
+            self.positional_embedding = torch.nn.Parameter(torch.full((4, 8), 0.5))
+            self.ln = torch.nn.LayerNorm(8)
+            self.fc = torch.nn.Linear(8, 8)
+            self.bn = torch.nn.BatchNorm2d(3)
+
+    t = Txt()
+    with torch.no_grad():
+        t.ln.weight.fill_(3.0)
+        t.fc.weight.fill_(7.0)
+        t.bn.running_mean.fill_(2.0)
+        t.bn.running_var.fill_(9.0)
+        t.bn.weight.fill_(4.0)
+    emb, pos = t.token_embedding.weight.clone(), t.positional_embedding.clone()
+    m = Clip_FDT(torch.nn.Identity(), t, True, 16, 8, 8, 8, "sparsemax", "max", 10.0)
+    q_before = m.txt_query_model.q_map[1].weight.clone()
+    m.reset_text_encoder(seed=5)
+    assert torch.equal(t.token_embedding.weight, emb), "nn.Embedding must survive reset_text_encoder"
+    assert torch.equal(t.positional_embedding, pos)
+    assert torch.all(t.ln.weight == 1) and not torch.all(t.fc.weight == 7.0)
+    assert torch.all(t.bn.running_mean == 0) and torch.all(t.bn.running_var == 1) and torch.all(t.bn.weight == 1)
+    assert not torch.equal(m.txt_query_model.q_map[1].weight, q_before)
+    ref_root = "/root/reference"
+    if os.path.isdir(os.path.join(ref_root, "prototype", "model")):     # same behaviour as the live reference
+        sys.path.insert(0, ROOT)
+        from oracle import ref_harness as H
+        H.load_reference()
+        import prototype.model.clip_fdt as ref_mod
+        t2 = Txt()
+        emb2 = t2.token_embedding.weight.clone()
+        t2.apply(ref_mod.weight_reset)
+        assert torch.equal(t2.token_embedding.weight, emb2)
+        t3 = Txt()
+        torch.manual_seed(9); t2.apply(ref_mod.weight_reset)
+        torch.manual_seed(9); t3.apply(weight_reset)
+        for (k, a), (_, b) in zip(t2.state_dict().items(), t3.state_dict().items()):
+            if k != "token_embedding.weight":
+                assert torch.equal(a, b), k
+
+
+def test_codebook_rng_state_travels_with_checkpoints():
+    """A fresh model's state_dict has exactly the reference's keys; once reset_codebook() has run, (seed, generation)
+    ride along as one optional entry so a resumed run continues the Philox stream instead of repeating it."""
+    from ilfdt.model.clip_fdt import Clip_FDT
+    mk = lambda: Clip_FDT(torch.nn.Identity(), torch.nn.Identity(), True, 16, 8, 8, 8, "sparsemax", "max", 10.0)
+    m = mk()
+    assert "codebook_rng" not in m.state_dict()
+    m.reset_codebook(seed=3)
+    m.reset_codebook()
+    sd = m.state_dict()
+    assert sd["codebook_rng"].tolist() == [3, 2]
+    m2 = mk()
+    missing, unexpected = m2.load_state_dict(sd, strict=True)
+    assert not missing and not unexpected
+    assert (m2.codebook_seed, m2.codebook_generation) == (3, 2)
+    assert torch.equal(m2.space_dict, m.space_dict)
+    m.reset_codebook(); m2.reset_codebook()
+    assert torch.equal(m2.space_dict, m.space_dict)            # the resumed run draws generation 3, not generation 1 again
+    m3 = mk()
+    ref_ckpt = {k: v for k, v in sd.items() if k != "codebook_rng"}   # a reference checkpoint has no such key
+    m3.load_state_dict(ref_ckpt, strict=True)
+
+
+def test_codebook_scope_never_outlives_a_step():
+    """no bf16 codebook copy may survive a write that does not bump `_version`. The cache exists
+    only inside an explicit scope; outside it every call recasts."""
+    from ilfdt import functional as Fn
+    assert Fn._sd_scope is None
+    with Fn.codebook_scope():
+        assert Fn._sd_scope == {}
+        with Fn.codebook_scope():
+            assert Fn._sd_scope is not None
+        assert Fn._sd_scope is not None
+    assert Fn._sd_scope is None
+    assert not hasattr(Fn, "_sd_cache")
+
+
+def test_tune_knobs_are_explicit_api_not_environment(built_lib):
+    from ilfdt import _lib, ops
+    lib = _lib.load()
+    assert lib.ilfdt_tune_get(_lib.TUNE["dsd_split_rows"]) == 1024
+    with ops.tune(dsd_split_rows=0, dsd_tile=128):
+        assert lib.ilfdt_tune_get(_lib.TUNE["dsd_split_rows"]) == 0
+        assert lib.ilfdt_tune_get(_lib.TUNE["dsd_tile"]) == 128
+    assert lib.ilfdt_tune_get(_lib.TUNE["dsd_split_rows"]) == 1024 and lib.ilfdt_tune_get(_lib.TUNE["dsd_tile"]) == 32
+    assert lib.ilfdt_tune_set(_lib.TUNE["dsd_tile"], 64) != 0       # only 32 / 128 exist
+    assert lib.ilfdt_tune_set(99, 1) != 0
+    for f in os.listdir(os.path.join(PKG, "csrc")):
+        assert "getenv" not in open(os.path.join(PKG, "csrc", f)).read(), f
