@@ -305,3 +305,67 @@ def make_q_map(ft_dim, sd_dim, state=None, prefix="q_map."):
     if state is not None:
         m.load_state_dict({k[len(prefix):]: torch.as_tensor(v) for k, v in state.items() if k.startswith(prefix)})
     return m
+
+
+# --------------------------------------------------------------------------------------------
+# BASELINE.json config 1 (b=64, P=49, T=77, K=16384, D=512): inputs, parameters and gradient
+# projections REGENERATED FROM SEEDS on both sides -- oracle/make_golden.py feeds them to the
+# unmodified reference and stores only small outputs (tests/golden/config1_*.npz); the tests feed
+# the same tensors to the CUDA path. `fingerprint` of every regenerated tensor is stored in the
+# golden file so a drifting generator fails loudly instead of comparing different inputs.
+# --------------------------------------------------------------------------------------------
+
+CFG1 = dict(b=64, P=49, T=77, K=16384, D=512, Fi=768, Ft=512, temperature=1000.0, n_proj=16)
+
+
+def config1_case(variant, b=None, K=None):
+    """variant "qmap": raw features + real q_map MLPs (clip_fdt.py:86-92), fp32 values.
+    variant "bf16in": q_map = identity, queries and codebook pre-rounded to bf16 so that the bf16
+    tensor-core mode and the reference see bit-identical operands."""
+    c = dict(CFG1)
+    if b is not None:
+        c["b"] = b
+    if K is not None:
+        c["K"] = K
+    b, P, T, K, D = c["b"], c["P"], c["T"], c["K"], c["D"]
+    Fi, Ft = (c["Fi"], c["Ft"]) if variant == "qmap" else (D, D)
+    g = torch.Generator().manual_seed(20261105 + (0 if variant == "qmap" else 1))
+    patch = torch.randn(b, P, Fi, generator=g)
+    word = torch.randn(b, T, Ft, generator=g)
+    lens = torch.randint(5, T + 1, (b,), generator=g)
+    lens[0] = T                                                   # one caption without padding
+    mask = torch.zeros(b, T)
+    mask[torch.arange(T).view(1, -1) >= lens.view(-1, 1)] = float("-inf")
+    state = {"space_dict": torch.randn(K, D, generator=g),
+             "logit_scale": torch.full((1,), math.log(1 / 0.07)),
+             "logit_scale_sd": torch.full((1,), math.log(1 / 0.07))}
+    if variant == "qmap":
+        for name, F_in in (("img_query_model", Fi), ("txt_query_model", Ft)):
+            pre = name + ".q_map."
+            state[pre + "0.weight"] = 1 + 0.1 * torch.randn(F_in, generator=g)
+            state[pre + "0.bias"] = 0.1 * torch.randn(F_in, generator=g)
+            state[pre + "1.weight"] = torch.randn(D, F_in, generator=g) / math.sqrt(F_in)
+            state[pre + "1.bias"] = 0.1 * torch.randn(D, generator=g)
+            state[pre + "3.weight"] = 1 + 0.1 * torch.randn(D, generator=g)
+            state[pre + "3.bias"] = 0.1 * torch.randn(D, generator=g)
+            state[pre + "4.weight"] = torch.randn(D, D, generator=g) / math.sqrt(D)
+            state[pre + "4.bias"] = 0.1 * torch.randn(D, generator=g)
+    else:
+        patch = patch.to(torch.bfloat16).float()
+        word = word.to(torch.bfloat16).float()
+        state["space_dict"] = state["space_dict"].to(torch.bfloat16).float()
+    n = c["n_proj"]
+    sign = lambda rows: (torch.randint(0, 2, (n, rows), generator=g).float() * 2 - 1)
+    proj = dict(patch=sign(b * P), word=sign(b * T), space_dict=sign(K))
+    return dict(cfg=c, variant=variant, patch=patch, word=word, mask=mask, state=state, proj=proj)
+
+
+def fingerprint(t):
+    t = t.detach().double().reshape(-1)
+    return np.array([t.sum().item(), t.abs().sum().item(), t[0].item(), t[-1].item(), float(t.numel())])
+
+
+def project(R, grad):
+    """R [n, rows] (+-1) times a gradient viewed as [rows, cols] -> [n, cols], accumulated in fp64."""
+    g2 = grad.detach().double().reshape(R.shape[1], -1)
+    return (R.double().to(g2.device) @ g2)

@@ -226,16 +226,109 @@ def gen_eval_extract():
     dist.destroy_process_group()
 
 
+def _run_reference_config1(case, dtype):
+    """The unmodified reference (Clip_FDT.forward + ClipInfoCELoss + backward) on one regenerated config-1 case."""
+    ref = H.load_reference()
+    from oracle import fdt_oracle as O
+    c = case["cfg"]
+    patch = case["patch"].detach().clone().to(dtype).requires_grad_(True)
+    word = case["word"].detach().clone().to(dtype).requires_grad_(True)
+    mask = case["mask"].to(dtype)
+    model = H.build_reference_fdt(patch, word, mask, c["K"], c["D"], temperature=c["temperature"])
+    if case["variant"] == "bf16in":       # row a0 (q_map) out of the picture: the kernels' input q IS the feature
+        model.img_query_model.q_map = torch.nn.Identity()
+        model.txt_query_model.q_map = torch.nn.Identity()
+    missing, unexpected = model.load_state_dict({k: v.clone() for k, v in case["state"].items()}, strict=False)
+    assert not unexpected and all(k.startswith(("visual.", "encode_text.")) for k in missing), (missing, unexpected)
+    model = model.to(dtype)
+    crit = ref["ClipInfoCELoss"]()
+    b = c["b"]
+    with H.cpu_cuda_identity():
+        (l_i, l_t), _ = model(torch.zeros(b, 1), ["x"] * b)
+        loss, labels = crit(l_i, l_t)
+    loss.backward()
+    with torch.no_grad():
+        w_i, f_i, _ = model.extract_img_sd_ft(torch.zeros(b, 1))
+        w_t, f_t, _ = model.extract_txt_sd_ft(["x"] * b)
+    out = dict(loss=_np(loss), labels=_np(labels), logits_per_image=_np(l_i), logits_per_text=_np(l_t),
+               att_ft_img=_np(f_i), att_ft_txt=_np(f_t),
+               support_img=np.packbits(_np(w_i) > 0, axis=1), support_txt=np.packbits(_np(w_t) > 0, axis=1),
+               nnz_img=(_np(w_i) > 0).sum(1).astype(np.int32), nnz_txt=(_np(w_t) > 0).sum(1).astype(np.int32),
+               wmax_img=_np(w_i).max(1), wmax_txt=_np(w_t).max(1),
+               proj_d_patch=_np(O.project(case["proj"]["patch"], patch.grad)),
+               proj_d_word=_np(O.project(case["proj"]["word"], word.grad)),
+               proj_d_space_dict=_np(O.project(case["proj"]["space_dict"], model.space_dict.grad)),
+               d_patch_rows=_np(patch.grad[:1]), d_word_rows=_np(word.grad[:1]),           # one whole sample, exact
+               d_space_dict_rows=_np(model.space_dict.grad[:64]),
+               d_logit_scale=_np(model.logit_scale.grad))
+    for k, v in model.named_parameters():
+        if ".q_map." in k:
+            out["grad_" + k] = _np(v.grad) if v.dim() == 1 else _np(v.grad[:8])    # 1-D in full, 8 rows of the matrices
+    raw = dict(d_patch=patch.grad.detach().double(), d_word=word.grad.detach().double(),
+               d_space_dict=model.space_dict.grad.detach().double(), d_logit_scale=model.logit_scale.grad.detach().double(),
+               loss=loss.detach().double(), logits_per_image=l_i.detach().double(), att_ft_img=f_i.double())
+    return out, raw
+
+
+def gen_config1():
+    """BASELINE.json config 1 (b=64, P=49, T=77, K=16384, D=512): the unmodified reference on CPU in fp32 (the golden)
+    and in fp64 (the arbiter), inputs regenerated from seeds (oracle.fdt_oracle.config1_case). Also records how far
+    the REFERENCE'S OWN fp32 run sits from its fp64 run: the noise floor any fp32 implementation of this path has."""
+    import json
+    from oracle import fdt_oracle as O
+    H.ensure_process_group(0, 1, port=29549)
+    floor = {}
+    for variant in ("qmap", "bf16in"):
+        case = O.config1_case(variant)
+        out32, raw32 = _run_reference_config1(case, torch.float32)
+        out64, raw64 = _run_reference_config1(case, torch.float64)
+        merged = {"f32_" + k: v for k, v in out32.items()}
+        for k, v in out64.items():      # the arbiter run: big arrays stored as float32 (6e-8 relative, far below any gate)
+            if k.startswith("support_"):
+                merged["f64_flips_" + k] = np.flatnonzero(np.unpackbits(v ^ out32[k], axis=1))   # vs the fp32 run
+            elif v.dtype == np.float64 and v.size > 4096 and not k.startswith("proj_"):
+                merged["f64_" + k] = v.astype(np.float32)
+            else:
+                merged["f64_" + k] = v
+        merged["fp_patch"] = O.fingerprint(case["patch"])
+        merged["fp_word"] = O.fingerprint(case["word"])
+        merged["fp_mask"] = O.fingerprint(torch.isinf(case["mask"]).float())
+        merged["fp_space_dict"] = O.fingerprint(case["state"]["space_dict"])
+        for k, v in case["proj"].items():
+            merged["fp_proj_" + k] = O.fingerprint(v)
+        for k, v in case["state"].items():
+            if ".q_map." in k:
+                merged["fp_state_" + k] = O.fingerprint(v)
+        np.savez_compressed(os.path.join(OUT, f"config1_{variant}.npz"), **merged)
+        rel = lambda a, r: float((a - r).abs().max() / r.abs().max().clamp_min(1e-300))
+        floor[variant] = {k: rel(raw32[k], raw64[k]) for k in raw32}
+        floor[variant]["support_bits_differing_img"] = int(np.unpackbits(out32["support_img"] ^ out64["support_img"]).sum())
+        floor[variant]["support_bits_differing_txt"] = int(np.unpackbits(out32["support_txt"] ^ out64["support_txt"]).sum())
+    floor["note"] = ("max-norm relative distance ||fp32 - fp64||_inf / ||fp64||_inf of the UNMODIFIED reference run in "
+                     "fp32 against the same code run in fp64 (CPU, torch %s), config 1; written by oracle/make_golden.py "
+                     "config1" % torch.__version__)
+    with open(os.path.join(OUT, "config1_reference_fp32_noise_floor.json"), "w") as fh:
+        json.dump(floor, fh, indent=1, sort_keys=True)
+    print(json.dumps(floor, indent=1, sort_keys=True))
+    import torch.distributed as dist
+    dist.destroy_process_group()
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(4)
     if sys.argv[1:] == ["eval_extract"]:      # added later: leaves the earlier fixtures byte-identical
         gen_eval_extract()
         sys.exit(0)
+    if sys.argv[1:] == ["config1"]:           # round 2: full-size golden (BASELINE.json config 1)
+        torch.set_num_threads(8)
+        gen_config1()
+        sys.exit(0)
     gen_sparsemax()
     gen_query_model()
     gen_fdt_steps()
     gen_clip_steps()
     gen_eval_extract()
+    gen_config1()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

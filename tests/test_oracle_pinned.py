@@ -223,3 +223,53 @@ def test_live_reference_matches_oracle_when_present():
     w, f, _ = O.grounding(qm.q_map(ft), sd, mask, 1000.0)
     _close(w.detach().numpy(), w_ref.detach().numpy(), rtol=1e-6, atol=1e-9)
     _close(f.detach().numpy(), f_ref.detach().numpy(), rtol=1e-6, atol=1e-9)
+
+
+@pytest.mark.parametrize("variant", ["qmap", "bf16in"])
+def test_config1_golden_pins_the_oracle_at_full_size(golden_dir, variant):
+    """BASELINE.json config 1 (b=64, P=49, T=77, K=16384, D=512): the oracle restatement on the regenerated inputs
+    against what the unmodified reference produced (tests/golden/config1_*.npz, oracle/make_golden.py config1)."""
+    z = _load(golden_dir, "config1_%s.npz" % variant)
+    case = O.config1_case(variant)
+    for name, t in (("patch", case["patch"]), ("word", case["word"]), ("mask", torch.isinf(case["mask"]).float()),
+                    ("space_dict", case["state"]["space_dict"])):
+        assert np.allclose(O.fingerprint(t), z["fp_" + name], rtol=1e-12, atol=0), name
+    c = case["cfg"]
+    patch = case["patch"].clone().requires_grad_(True)
+    word = case["word"].clone().requires_grad_(True)
+    if variant == "qmap":
+        qi = O.make_q_map(c["Fi"], c["D"], case["state"], prefix="img_query_model.q_map.")
+        qt = O.make_q_map(c["Ft"], c["D"], case["state"], prefix="txt_query_model.q_map.")
+        q_img, q_txt = qi(patch), qt(word)
+    else:
+        q_img, q_txt = patch * 1.0, word * 1.0
+    sd = O.make_leaf(case["state"]["space_dict"])
+    p = O.make_leaf(case["state"]["logit_scale"])
+    out = O.step([dict(q_img=q_img, q_txt=q_txt, mask=case["mask"], sd=sd, p=p)], temperature=c["temperature"])[0]
+    _close(out["loss"].numpy(), z["f32_loss"], rtol=1e-6)
+    assert np.array_equal(out["labels"].numpy(), z["f32_labels"])
+    _close(out["logits_per_image"].numpy(), z["f32_logits_per_image"])
+    _close(out["logits_per_text"].numpy(), z["f32_logits_per_text"])
+    _close(out["f_img"].numpy(), z["f32_att_ft_img"])
+    _close(out["f_txt"].numpy(), z["f32_att_ft_txt"])
+    for tag in ("img", "txt"):
+        bits = np.unpackbits(z["f32_support_" + tag], axis=1)[:, :c["K"]].astype(bool)
+        assert (bits != (out["w_" + tag].numpy() > 0)).sum() <= 2, "support sets differ from the reference"
+    # projections see every gradient row; the rows stored verbatim are compared with the same rule the GPU tests use
+    _close(O.project(case["proj"]["patch"], patch.grad).numpy(), z["f32_proj_d_patch"], rtol=2e-4)
+    _close(O.project(case["proj"]["word"], word.grad).numpy(), z["f32_proj_d_word"], rtol=2e-4)
+    _close(O.project(case["proj"]["space_dict"], sd.grad).numpy(), z["f32_proj_d_space_dict"], rtol=2e-4)
+    _close(p.grad.numpy(), z["f32_d_logit_scale"], rtol=2e-4)
+    _close(patch.grad[:1].numpy(), z["f32_d_patch_rows"], rtol=2e-4)
+    _close(sd.grad[:64].numpy(), z["f32_d_space_dict_rows"], rtol=2e-4)
+
+
+def test_reference_fp32_noise_floor_is_recorded(golden_dir):
+    """The tolerance argument of tests/test_fullsize_gpu.py rests on these committed numbers: the reference's own fp32
+    run vs its fp64 run on config 1."""
+    import json
+    f = json.load(open(os.path.join(golden_dir, "config1_reference_fp32_noise_floor.json")))
+    exact = f["bf16in"]                  # no argmax ties on these inputs: pure fp32 rounding
+    assert exact["loss"] < 1e-7 and exact["logits_per_image"] < 2e-6
+    assert 1e-6 < max(exact["d_patch"], exact["d_word"], exact["d_space_dict"]) < 1e-5
+    assert f["qmap"]["d_space_dict"] > 1e-3   # an argmax / support tie: O(1e-2) even for the reference itself
