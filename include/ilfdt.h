@@ -219,6 +219,15 @@ int32_t ilfdt_nce_fwd(const void* x_img, const void* x_txt, const void* g_img, c
                       int32_t dtype, int64_t b, int64_t B, int64_t D, const float* scale,
                       int64_t label_offset, float* lse_i, float* lse_t, float* diag_i, float* diag_t,
                       float* loss, void* ws, int64_t ws_bytes, void* stream);
+/* The two halves of ilfdt_nce_fwd as separate calls, for callers that overlap the all-gather of one modality with the
+ * direction that does not need it: logits_per_text = x_txt.g_img^T only needs the IMAGE gather, so its log-sum-exp runs
+ * while the text gather (clip_fdt.py:418-419) is still in flight. ilfdt_nce_lse: lse[r], diag[r] of the rows
+ * scale * x[r,:].g^T with label label_offset + r (x [b,D], g [B,D]; ws: ilfdt_nce_ws_bytes). ilfdt_nce_loss:
+ * loss[0] = (mean(lse_i - diag_i) + mean(lse_t - diag_t)) / 2  (loss.py:47-49), fp64 accumulation, deterministic. */
+int32_t ilfdt_nce_lse(const void* x, const void* g, int32_t dtype, int64_t b, int64_t B, int64_t D, const float* scale,
+                      int64_t label_offset, float* lse, float* diag, void* ws, int64_t ws_bytes, void* stream);
+int32_t ilfdt_nce_loss(const float* lse_i, const float* diag_i, const float* lse_t, const float* diag_t, int64_t b,
+                       float* loss, void* stream);
 /* Fused InfoNCE backward. grad_out: device pointer to dLoss (scalar). P = (softmax - onehot) *
  * grad_out/(2b) is recomputed tile by tile from lse_*. Outputs (all f32, overwritten):
  * dx_img, dx_txt [b,D]; dg_img, dg_txt [B,D] (gradient w.r.t. the gathered copies, to be

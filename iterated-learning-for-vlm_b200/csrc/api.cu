@@ -43,26 +43,28 @@ static int64_t nce_f32_chunk_rows(int64_t b, int64_t B) {
   return std::max<int64_t>(1, std::min<int64_t>(b, budget_elems / std::max<int64_t>(B, 1)));
 }
 
+static int32_t nce_lse_f32(const float* X, const float* G, int64_t b, int64_t B, int64_t D, const float* scale,
+                           int64_t label_offset, float* lse, float* diag, void* ws, int64_t ws_bytes, cudaStream_t st) {
+  const int64_t R = nce_f32_chunk_rows(b, B);
+  ILFDT_REQUIRE(ws != nullptr && ws_bytes >= R * B * 4, ILFDT_E_INVALID_ARG, "nce_lse(f32): workspace too small");
+  float* L = reinterpret_cast<float*>(ws);
+  for (int64_t r0 = 0; r0 < b; r0 += R) {
+    const int64_t rows = std::min(R, b - r0);
+    int32_t rc = launch_gemm_f32(X + r0 * D, D, 1, G, D, 1, L, B, 1, rows, B, D, 1.f, scale, 0, st);
+    if (rc != ILFDT_OK) return rc;
+    rc = launch_lse_rows(L, B, rows, B, label_offset + r0, lse + r0, diag + r0, st);
+    if (rc != ILFDT_OK) return rc;
+  }
+  return ILFDT_OK;
+}
+
 static int32_t nce_fwd_f32(const float* x_img, const float* x_txt, const float* g_img, const float* g_txt, int64_t b,
                            int64_t B, int64_t D, const float* scale, int64_t label_offset, float* lse_i, float* lse_t,
                            float* diag_i, float* diag_t, void* ws, int64_t ws_bytes, cudaStream_t st) {
-  const int64_t R = nce_f32_chunk_rows(b, B);
-  ILFDT_REQUIRE(ws != nullptr && ws_bytes >= R * B * 4, ILFDT_E_INVALID_ARG, "nce_fwd(f32): workspace too small");
-  float* L = reinterpret_cast<float*>(ws);
-  for (int dir = 0; dir < 2; ++dir) {
-    const float* X = dir == 0 ? x_img : x_txt;
-    const float* G = dir == 0 ? g_txt : g_img;  // clip_fdt.py:421-422
-    float* lse = dir == 0 ? lse_i : lse_t;
-    float* diag = dir == 0 ? diag_i : diag_t;
-    for (int64_t r0 = 0; r0 < b; r0 += R) {
-      const int64_t rows = std::min(R, b - r0);
-      int32_t rc = launch_gemm_f32(X + r0 * D, D, 1, G, D, 1, L, B, 1, rows, B, D, 1.f, scale, 0, st);
-      if (rc != ILFDT_OK) return rc;
-      rc = launch_lse_rows(L, B, rows, B, label_offset + r0, lse + r0, diag + r0, st);
-      if (rc != ILFDT_OK) return rc;
-    }
-  }
-  return ILFDT_OK;
+  // logits_per_image = x_img . g_txt^T ; logits_per_text = x_txt . g_img^T  (clip_fdt.py:421-422)
+  int32_t rc = nce_lse_f32(x_img, g_txt, b, B, D, scale, label_offset, lse_i, diag_i, ws, ws_bytes, st);
+  if (rc != ILFDT_OK) return rc;
+  return nce_lse_f32(x_txt, g_img, b, B, D, scale, label_offset, lse_t, diag_t, ws, ws_bytes, st);
 }
 
 static int32_t nce_bwd_f32(const float* x_img, const float* x_txt, const float* g_img, const float* g_txt, int64_t b,
@@ -435,6 +437,26 @@ int32_t ilfdt_nce_fwd(const void* x_img, const void* x_txt, const void* g_img, c
     rc = launch_nce_fwd_bf16(x_img, x_txt, g_img, g_txt, b, B, D, scale, label_offset, lse_i, lse_t, diag_i, diag_t,
                              ws, ws_bytes, ST(stream));
   if (rc != ILFDT_OK) return rc;
+  return launch_nce_loss(lse_i, diag_i, lse_t, diag_t, b, loss, ST(stream));
+}
+
+int32_t ilfdt_nce_lse(const void* x, const void* g, int32_t dtype, int64_t b, int64_t B, int64_t D, const float* scale,
+                      int64_t label_offset, float* lse, float* diag, void* ws, int64_t ws_bytes, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(dtype);
+  ILFDT_REQUIRE(b >= 1 && B >= b && D >= 1, ILFDT_E_INVALID_ARG, "nce_lse: need 1 <= b <= B");
+  ILFDT_REQUIRE(label_offset >= 0 && label_offset + b <= B, ILFDT_E_INVALID_ARG, "nce_lse: labels out of range");
+  ILFDT_REQUIRE(x && g && lse && diag && scale, ILFDT_E_INVALID_ARG, "nce_lse: null pointer");
+  if (dtype == ILFDT_F32)
+    return nce_lse_f32(reinterpret_cast<const float*>(x), reinterpret_cast<const float*>(g), b, B, D, scale, label_offset,
+                       lse, diag, ws, ws_bytes, ST(stream));
+  return launch_nce_lse_bf16(x, g, b, B, D, scale, label_offset, lse, diag, ws, ws_bytes, ST(stream));
+}
+
+int32_t ilfdt_nce_loss(const float* lse_i, const float* diag_i, const float* lse_t, const float* diag_t, int64_t b,
+                       float* loss, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(b >= 1 && lse_i && diag_i && lse_t && diag_t && loss, ILFDT_E_INVALID_ARG, "nce_loss: bad arguments");
   return launch_nce_loss(lse_i, diag_i, lse_t, diag_t, b, loss, ST(stream));
 }
 

@@ -744,32 +744,40 @@ int64_t nce_fwd_bf16_ws_bytes(int64_t b, int64_t B) {
   return 2 * 2 * max_chunks * b * 4 + 256;
 }
 
+// one direction: lse[r], diag[r] of the rows scale * x[r,:] . g^T (labels label_offset + r)
+int32_t launch_nce_lse_bf16(const void* x, const void* g, int64_t b, int64_t B, int64_t D, const float* scale,
+                            int64_t label_offset, float* lse, float* diag, void* ws, int64_t ws_bytes, cudaStream_t st) {
+  ILFDT_REQUIRE(D <= 512 && D % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "nce_lse(bf16): D=%lld must be <= 512, %% 8",
+                (long long)D);
+  ILFDT_REQUIRE(ws != nullptr && ws_bytes >= nce_fwd_bf16_ws_bytes(b, B) / 2, ILFDT_E_INVALID_ARG,
+                "nce_lse(bf16): workspace too small");
+  const int64_t max_chunks = 2 * cdiv(B, 256);
+  UmmaParams p{};
+  p.block_n = (int)std::min<int64_t>(256, round_up(B, 16));
+  p.n_step = p.block_n;
+  p.scale_dev = scale;
+  p.label_offset = label_offset;
+  p.part_m = reinterpret_cast<float*>(ws);
+  p.part_s = p.part_m + max_chunks * b;
+  p.diag = diag;
+  int32_t rc = launch_umma<EPI_LSE>(x, g, b, B, D, p, st);
+  if (rc != ILFDT_OK) return rc;
+  lse_combine_kernel<<<(unsigned)cdiv(b, 256), 256, 0, st>>>(p.part_m, p.part_s, 2 * p.nchunk, b, lse);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
 int32_t launch_nce_fwd_bf16(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt, int64_t b,
                             int64_t B, int64_t D, const float* scale, int64_t label_offset, float* lse_i, float* lse_t,
                             float* diag_i, float* diag_t, void* ws, int64_t ws_bytes, cudaStream_t st) {
-  ILFDT_REQUIRE(D <= 512 && D % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "nce_fwd(bf16): D=%lld must be <= 512, %% 8",
-                (long long)D);
   ILFDT_REQUIRE(ws != nullptr && ws_bytes >= nce_fwd_bf16_ws_bytes(b, B), ILFDT_E_INVALID_ARG,
                 "nce_fwd(bf16): workspace too small");
-  const int64_t max_chunks = 2 * cdiv(B, 256);
-  float* part = reinterpret_cast<float*>(ws);
-  for (int dir = 0; dir < 2; ++dir) {
-    UmmaParams p{};
-    p.block_n = (int)std::min<int64_t>(256, round_up(B, 16));
-    p.n_step = p.block_n;
-    p.scale_dev = scale;
-    p.label_offset = label_offset;
-    p.part_m = part + (int64_t)dir * 2 * max_chunks * b;
-    p.part_s = p.part_m + max_chunks * b;
-    p.diag = dir == 0 ? diag_i : diag_t;
-    // logits_per_image = x_img . g_txt^T ; logits_per_text = x_txt . g_img^T  (clip_fdt.py:421-422)
-    int32_t rc = launch_umma<EPI_LSE>(dir == 0 ? x_img : x_txt, dir == 0 ? g_txt : g_img, b, B, D, p, st);
-    if (rc != ILFDT_OK) return rc;
-    lse_combine_kernel<<<(unsigned)cdiv(b, 256), 256, 0, st>>>(p.part_m, p.part_s, 2 * p.nchunk, b,
-                                                              dir == 0 ? lse_i : lse_t);
-    ILFDT_LAUNCH_OK();
-  }
-  return ILFDT_OK;
+  const int64_t half = (nce_fwd_bf16_ws_bytes(b, B) / 2) & ~(int64_t)15;
+  // logits_per_image = x_img . g_txt^T ; logits_per_text = x_txt . g_img^T  (clip_fdt.py:421-422)
+  int32_t rc = launch_nce_lse_bf16(x_img, g_txt, b, B, D, scale, label_offset, lse_i, diag_i, ws, ws_bytes, st);
+  if (rc != ILFDT_OK) return rc;
+  return launch_nce_lse_bf16(x_txt, g_img, b, B, D, scale, label_offset, lse_t, diag_t,
+                             reinterpret_cast<char*>(ws) + half, ws_bytes - half, st);
 }
 
 

@@ -309,6 +309,98 @@ ground_bwd_dsd_kernel(const float* __restrict__ coef, const int16_t* __restrict_
 }
 
 // ---------------------------------------------------------------------------------------------
+// kernel 1, v3: per-sample CTA of 256 threads; the preprocessing that dominated the sorted kernel above
+// (ncu r01: ~60 % of its stall samples sat in the scalar, dependent-load coef / histogram / placement
+// passes) is rebuilt around coalesced 16-byte loads and thread-private counters:
+//   pass 0  mean of g over the support (float4 loads, fp64 accumulation)
+//   pass A  each thread owns 64 codes of the 16384-code chunk as 16 coalesced float4 groups: coef is
+//           computed, written back over g (for kernel 2) and the thread's per-token counts go to its
+//           private column of hist[token][thread] (uint16, no atomics, no match_any)
+//   scan    per token over the 256 thread columns, then over tokens -> bucket bases
+//   pass B  the thread re-walks its (register-resident) live mask / tokens and drops each code index at
+//           base[token] + its running column offset: a counting sort whose order (thread, group, element)
+//           is fixed, so the summation order and the result are deterministic
+//   gather  warps take tokens dynamically; a bucket is read 32 entries at a time (code index from shared
+//           memory, coef from the L2-resident row just written), 4 codebook rows in flight per warp.
+// ---------------------------------------------------------------------------------------------
+constexpr int G3_THREADS = 256, G3_WARPS = G3_THREADS / 32, G3_PER = 64, G3_CHUNK = G3_THREADS * G3_PER;  // 16384
+constexpr int G3_GROUPS = G3_PER / 4;
+constexpr int G3_MAX_TOK = 96;
+
+// L2 eviction policy for the gathered rows: the rows that are reused by every CTA (the codebook in kernel 1, the current
+// slice of q in kernel 2) are loaded evict-last so that the streamed per-sample arrays (g / w / arg, coef) do not push
+// them out of L2.
+__device__ __forceinline__ uint64_t l2_policy(bool keep) {
+  uint64_t pol;
+  if (keep) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint4 ldg_hint(const void* p, uint64_t pol) {
+  uint4 r;
+  asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(pol));
+  return r;
+}
+
+template <typename TO>
+struct StoreRow8;
+template <>
+struct StoreRow8<float> {
+  __device__ __forceinline__ static void st(float* o, const float (&a)[8], bool add) {
+    float4 x = make_float4(a[0], a[1], a[2], a[3]), y = make_float4(a[4], a[5], a[6], a[7]);
+    if (add) {
+      const float4 px = *reinterpret_cast<float4*>(o), py = *reinterpret_cast<float4*>(o + 4);
+      x.x += px.x; x.y += px.y; x.z += px.z; x.w += px.w;
+      y.x += py.x; y.y += py.y; y.z += py.z; y.w += py.w;
+    }
+    *reinterpret_cast<float4*>(o) = x;
+    *reinterpret_cast<float4*>(o + 4) = y;
+  }
+};
+template <>
+struct StoreRow8<__nv_bfloat16> {
+  __device__ __forceinline__ static void st(__nv_bfloat16* o, const float (&a)[8], bool add) {
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = a[j];
+    if (add) {
+      float p[8];
+      Load8<__nv_bfloat16>::ld(o, p);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += p[j];
+    }
+    uint4 r;
+    __nv_bfloat162 b0 = __floats2bfloat162_rn(v[0], v[1]), b1 = __floats2bfloat162_rn(v[2], v[3]);
+    __nv_bfloat162 b2 = __floats2bfloat162_rn(v[4], v[5]), b3 = __floats2bfloat162_rn(v[6], v[7]);
+    r.x = *reinterpret_cast<uint32_t*>(&b0); r.y = *reinterpret_cast<uint32_t*>(&b1);
+    r.z = *reinterpret_cast<uint32_t*>(&b2); r.w = *reinterpret_cast<uint32_t*>(&b3);
+    *reinterpret_cast<uint4*>(o) = r;
+  }
+};
+
+// support bits of four consecutive sparsemax weights (bit i: w[i] > 0). TW = float: the fp32 att_weight;
+// TW = bf16: the tensor-core operand copy the forward keeps anyway (weights are >= 0 and bf16 has fp32's
+// exponent range, so w > 0 survives the rounding) -- half the bytes, and the fp32 copy need not exist.
+template <typename TW> struct Support4;
+template <> struct Support4<float> {
+  static __device__ __forceinline__ uint32_t ld(const float* p) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(p));
+    return (v.x > 0.f ? 1u : 0u) | (v.y > 0.f ? 2u : 0u) | (v.z > 0.f ? 4u : 0u) | (v.w > 0.f ? 8u : 0u);
+  }
+};
+template <> struct Support4<__nv_bfloat16> {
+  static __device__ __forceinline__ uint32_t pos(uint32_t h) { return (h & 0x8000u) == 0u && (h & 0x7fffu) != 0u; }
+  static __device__ __forceinline__ uint32_t ld(const __nv_bfloat16* p) {
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+    return pos(v.x & 0xffffu) | (pos(v.x >> 16) << 1) | (pos(v.y & 0xffffu) << 2) | (pos(v.y >> 16) << 3);
+  }
+};
+
+__device__ __forceinline__ bool weight_pos(float v) { return v > 0.f; }
+__device__ __forceinline__ bool weight_pos(__nv_bfloat16 v) { return __bfloat162float(v) > 0.f; }
+
+// ---------------------------------------------------------------------------------------------
 // kernel 1, token-sorted: same per-sample structure, but the support entries of a chunk are bucketed by
 // token with a stable counting sort (per-warp histograms over contiguous code ranges, __match_any_sync
 // for the rank inside a 32-entry group), so a token's warp walks only its own entries instead of
@@ -320,11 +412,13 @@ struct __align__(8) GbEnt2 {
   float coef;
 };
 
-template <typename T, int NV>
+// TW / TO as in the v3 kernel: the support may be read from the bf16 copy of the weights and dq written in bf16
+// (token counts above G3_MAX_TOK -- ViT-B/16's 196 patches, BASELINE.json config 5 -- take this kernel).
+template <typename T, int NV, typename TO, typename TW>
 __global__ void __launch_bounds__(GB_THREADS)
-ground_bwd_dq_sorted_kernel(float* __restrict__ g, const float* __restrict__ w, const int16_t* __restrict__ arg,
+ground_bwd_dq_sorted_kernel(float* __restrict__ g, const TW* __restrict__ w, const int16_t* __restrict__ arg,
                             const T* __restrict__ sd, const float* __restrict__ mask, int n_tok, int K, int D,
-                            float inv_scale, float* __restrict__ dq) {
+                            float inv_scale, TO* __restrict__ dq) {
   extern __shared__ __align__(16) unsigned char gb_smem[];
   GbEnt2* ent = reinterpret_cast<GbEnt2*>(gb_smem);
   int* hist = reinterpret_cast<int*>(gb_smem + GB_CHUNK * sizeof(GbEnt2));  // [GB_WARPS][n_tok]
@@ -335,7 +429,7 @@ ground_bwd_dq_sorted_kernel(float* __restrict__ g, const float* __restrict__ w, 
   const int64_t b = blockIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float* gr = g + b * K;
-  const float* wr = w ? w + b * K : nullptr;
+  const TW* wr = w ? w + b * K : nullptr;
   const int16_t* ar = arg + b * K;
   const float* mr = mask ? mask + b * n_tok : nullptr;
   int* myhist = hist + warp * n_tok;
@@ -343,7 +437,7 @@ ground_bwd_dq_sorted_kernel(float* __restrict__ g, const float* __restrict__ w, 
   double s = 0.0;
   int c = 0;
   for (int i = threadIdx.x; i < K; i += GB_THREADS)
-    if (wr != nullptr && wr[i] > 0.f) { s += (double)gr[i]; ++c; }
+    if (wr != nullptr && weight_pos(wr[i])) { s += (double)gr[i]; ++c; }
   s = warp_sum(s);
   c = warp_sum(c);
   if (lane == 0) { red_s[warp] = s; red_c[warp] = c; }
@@ -365,7 +459,7 @@ ground_bwd_dq_sorted_kernel(float* __restrict__ g, const float* __restrict__ w, 
       float cf = 0.f;
       int t = 0;
       if (i < we) {
-        if (wr == nullptr || wr[k0 + i] > 0.f) {
+        if (wr == nullptr || weight_pos(wr[k0 + i])) {
           t = ar[k0 + i];
           const float keep = (mr == nullptr || mr[t] == 0.f) ? 1.f : 0.f;
           cf = (gr[k0 + i] - mean) * keep * inv_scale;
@@ -457,112 +551,13 @@ ground_bwd_dq_sorted_kernel(float* __restrict__ g, const float* __restrict__ w, 
         const GbEnt2 e0 = ent[e];
         gb_axpy<T, NV>(sd + (int64_t)e0.k * D, e0.coef, lane, acc);
       }
-      float* out = dq + (b * n_tok + t) * (int64_t)D;
+      TO* out = dq + (b * n_tok + t) * (int64_t)D;
 #pragma unroll
-      for (int i = 0; i < NV; ++i) {
-        float* o = out + (i * 32 + lane) * 8;
-        float4 a = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
-        float4 bb = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
-        if (k0 > 0) {
-          const float4 pa = *reinterpret_cast<float4*>(o), pb = *reinterpret_cast<float4*>(o + 4);
-          a.x += pa.x; a.y += pa.y; a.z += pa.z; a.w += pa.w;
-          bb.x += pb.x; bb.y += pb.y; bb.z += pb.z; bb.w += pb.w;
-        }
-        *reinterpret_cast<float4*>(o) = a;
-        *reinterpret_cast<float4*>(o + 4) = bb;
-      }
+      for (int i = 0; i < NV; ++i) StoreRow8<TO>::st(out + (i * 32 + lane) * 8, acc[i], k0 > 0);
     }
   }
 }
 
-// ---------------------------------------------------------------------------------------------
-// kernel 1, v3: per-sample CTA of 256 threads; the preprocessing that dominated the sorted kernel above
-// (ncu r01: ~60 % of its stall samples sat in the scalar, dependent-load coef / histogram / placement
-// passes) is rebuilt around coalesced 16-byte loads and thread-private counters:
-//   pass 0  mean of g over the support (float4 loads, fp64 accumulation)
-//   pass A  each thread owns 64 codes of the 16384-code chunk as 16 coalesced float4 groups: coef is
-//           computed, written back over g (for kernel 2) and the thread's per-token counts go to its
-//           private column of hist[token][thread] (uint16, no atomics, no match_any)
-//   scan    per token over the 256 thread columns, then over tokens -> bucket bases
-//   pass B  the thread re-walks its (register-resident) live mask / tokens and drops each code index at
-//           base[token] + its running column offset: a counting sort whose order (thread, group, element)
-//           is fixed, so the summation order and the result are deterministic
-//   gather  warps take tokens dynamically; a bucket is read 32 entries at a time (code index from shared
-//           memory, coef from the L2-resident row just written), 4 codebook rows in flight per warp.
-// ---------------------------------------------------------------------------------------------
-constexpr int G3_THREADS = 256, G3_WARPS = G3_THREADS / 32, G3_PER = 64, G3_CHUNK = G3_THREADS * G3_PER;  // 16384
-constexpr int G3_GROUPS = G3_PER / 4;
-constexpr int G3_MAX_TOK = 96;
-
-// L2 eviction policy for the gathered rows: the rows that are reused by every CTA (the codebook in kernel 1, the current
-// slice of q in kernel 2) are loaded evict-last so that the streamed per-sample arrays (g / w / arg, coef) do not push
-// them out of L2.
-__device__ __forceinline__ uint64_t l2_policy(bool keep) {
-  uint64_t pol;
-  if (keep) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
-  else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-__device__ __forceinline__ uint4 ldg_hint(const void* p, uint64_t pol) {
-  uint4 r;
-  asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(pol));
-  return r;
-}
-
-template <typename TO>
-struct StoreRow8;
-template <>
-struct StoreRow8<float> {
-  __device__ __forceinline__ static void st(float* o, const float (&a)[8], bool add) {
-    float4 x = make_float4(a[0], a[1], a[2], a[3]), y = make_float4(a[4], a[5], a[6], a[7]);
-    if (add) {
-      const float4 px = *reinterpret_cast<float4*>(o), py = *reinterpret_cast<float4*>(o + 4);
-      x.x += px.x; x.y += px.y; x.z += px.z; x.w += px.w;
-      y.x += py.x; y.y += py.y; y.z += py.z; y.w += py.w;
-    }
-    *reinterpret_cast<float4*>(o) = x;
-    *reinterpret_cast<float4*>(o + 4) = y;
-  }
-};
-template <>
-struct StoreRow8<__nv_bfloat16> {
-  __device__ __forceinline__ static void st(__nv_bfloat16* o, const float (&a)[8], bool add) {
-    float v[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = a[j];
-    if (add) {
-      float p[8];
-      Load8<__nv_bfloat16>::ld(o, p);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] += p[j];
-    }
-    uint4 r;
-    __nv_bfloat162 b0 = __floats2bfloat162_rn(v[0], v[1]), b1 = __floats2bfloat162_rn(v[2], v[3]);
-    __nv_bfloat162 b2 = __floats2bfloat162_rn(v[4], v[5]), b3 = __floats2bfloat162_rn(v[6], v[7]);
-    r.x = *reinterpret_cast<uint32_t*>(&b0); r.y = *reinterpret_cast<uint32_t*>(&b1);
-    r.z = *reinterpret_cast<uint32_t*>(&b2); r.w = *reinterpret_cast<uint32_t*>(&b3);
-    *reinterpret_cast<uint4*>(o) = r;
-  }
-};
-
-// support bits of four consecutive sparsemax weights (bit i: w[i] > 0). TW = float: the fp32 att_weight;
-// TW = bf16: the tensor-core operand copy the forward keeps anyway (weights are >= 0 and bf16 has fp32's
-// exponent range, so w > 0 survives the rounding) -- half the bytes, and the fp32 copy need not exist.
-template <typename TW> struct Support4;
-template <> struct Support4<float> {
-  static __device__ __forceinline__ uint32_t ld(const float* p) {
-    const float4 v = __ldg(reinterpret_cast<const float4*>(p));
-    return (v.x > 0.f ? 1u : 0u) | (v.y > 0.f ? 2u : 0u) | (v.z > 0.f ? 4u : 0u) | (v.w > 0.f ? 8u : 0u);
-  }
-};
-template <> struct Support4<__nv_bfloat16> {
-  static __device__ __forceinline__ uint32_t pos(uint32_t h) { return (h & 0x8000u) == 0u && (h & 0x7fffu) != 0u; }
-  static __device__ __forceinline__ uint32_t ld(const __nv_bfloat16* p) {
-    const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
-    return pos(v.x & 0xffffu) | (pos(v.x >> 16) << 1) | (pos(v.y & 0xffffu) << 2) | (pos(v.y >> 16) << 3);
-  }
-};
 
 template <typename T, int NV, typename TO, typename TW>
 __global__ void __launch_bounds__(G3_THREADS, 3)
@@ -987,22 +982,34 @@ static int32_t launch_ground_bwd_t(float* g, const void* w_v, int w_dtype, const
       done = true;
     }
   }
-  ILFDT_REQUIRE(done || w16 == nullptr, ILFDT_E_UNSUPPORTED_SHAPE,
-                "ground_bwd: bf16 weights need D in {256,512,768,1024}, n_tok <= %d, K %% 4 == 0", G3_MAX_TOK);
-  ILFDT_REQUIRE(done || dq_dtype == ILFDT_F32, ILFDT_E_UNSUPPORTED_SHAPE,
-                "ground_bwd: bf16 dq needs D in {256,512,768,1024}, n_tok <= %d, K %% 4 == 0", G3_MAX_TOK);
   if constexpr (NV > 0) {
     if (!done && n_tok <= 256) {
       const size_t smem2 = GB_CHUNK * sizeof(GbEnt2) + (size_t)(GB_WARPS * n_tok + n_tok + 1) * sizeof(int);
-      ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_sorted_kernel<T, NV>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)(GB_CHUNK * sizeof(GbEnt2) + (GB_WARPS * 256 + 257) * sizeof(int))));
-      ground_bwd_dq_sorted_kernel<T, NV><<<(unsigned)b, GB_THREADS, smem2, st>>>(g, w, arg, sd, mask, (int)n_tok,
-                                                                                (int)K, (int)D, inv_scale, dq);
+      const int smem_max = (int)(GB_CHUNK * sizeof(GbEnt2) + (GB_WARPS * 256 + 257) * sizeof(int));
+#define ILFDT_DQ_SORTED(TO_, TW_, WPTR, DQPTR)                                                                         \
+  do {                                                                                                                 \
+    ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_sorted_kernel<T, NV, TO_, TW_>,                                   \
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));                        \
+    ground_bwd_dq_sorted_kernel<T, NV, TO_, TW_><<<(unsigned)b, GB_THREADS, smem2, st>>>(                             \
+        g, WPTR, arg, sd, mask, (int)n_tok, (int)K, (int)D, inv_scale, DQPTR);                                         \
+  } while (0)
+      __nv_bfloat16* dq16 = reinterpret_cast<__nv_bfloat16*>(dq_v);
+      if (w16 != nullptr) {
+        if (dq_dtype == ILFDT_BF16) ILFDT_DQ_SORTED(__nv_bfloat16, __nv_bfloat16, w16, dq16);
+        else ILFDT_DQ_SORTED(float, __nv_bfloat16, w16, dq);
+      } else {
+        if (dq_dtype == ILFDT_BF16) ILFDT_DQ_SORTED(__nv_bfloat16, float, w, dq16);
+        else ILFDT_DQ_SORTED(float, float, w, dq);
+      }
+#undef ILFDT_DQ_SORTED
       ILFDT_LAUNCH_OK();
       done = true;
     }
   }
+  ILFDT_REQUIRE(done || w16 == nullptr, ILFDT_E_UNSUPPORTED_SHAPE,
+                "ground_bwd: bf16 weights need D in {256,512,768,1024}, n_tok <= 256, K %% 4 == 0");
+  ILFDT_REQUIRE(done || dq_dtype == ILFDT_F32, ILFDT_E_UNSUPPORTED_SHAPE,
+                "ground_bwd: bf16 dq needs D in {256,512,768,1024}, n_tok <= 256, K %% 4 == 0");
   if (!done) {
     const size_t smem = (size_t)std::min<int64_t>(GB_CHUNK, K) * sizeof(GbEntry);
     ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_kernel<T, NV>, cudaFuncAttributeMaxDynamicSharedMemorySize,

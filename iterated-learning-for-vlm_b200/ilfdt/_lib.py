@@ -56,6 +56,8 @@ SIGNATURES = {
     "ilfdt_logits": (_i32, [_p, _p, _i32, _i64, _i64, _i64, _p, _p, _p]),
     "ilfdt_nce_ws_bytes": (_i64, [_i32, _i64, _i64, _i64]),
     "ilfdt_nce_fwd": (_i32, [_p, _p, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _i64, _p]),
+    "ilfdt_nce_lse": (_i32, [_p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _p, _p, _i64, _p]),
+    "ilfdt_nce_loss": (_i32, [_p, _p, _p, _p, _i64, _p, _p]),
     "ilfdt_nce_bwd": (_i32, [_p, _p, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _p, _p,
                              _p, _p, _p, _p, _p, _p, _i64, _p]),
     "ilfdt_nce_bwd_gathered": (_i32, [_p, _p, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _p, _p,

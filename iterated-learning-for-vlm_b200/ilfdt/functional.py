@@ -133,7 +133,8 @@ class GroundingFunction(torch.autograd.Function):
             q_k, sd_k, sd_kt = q, sd_c, None
             pooled, arg = ops.ground_fwd(q_k, sd_k, mask_f, temperature, "max")
         # the scatter kernel that reads the support from bf16 weights covers these shapes (ground_bwd.cu)
-        lean = LEAN_WEIGHTS and (not need_weights) and mode == "bf16" and q.shape[2] in (256, 512) and q.shape[1] <= 96 \
+        # (token counts up to 96 run the v3 scatter kernel, up to 256 -- ViT-B/16's 196 patches -- the token-sorted one)
+        lean = LEAN_WEIGHTS and (not need_weights) and mode == "bf16" and q.shape[2] in (256, 512) and q.shape[1] <= 256 \
             and sd.shape[0] % 4 == 0
         w, w_b, _tau, _nnz = ops.sparsemax_fwd(pooled, want_bf16=(mode == "bf16"), want_f32=not lean)
         del pooled
@@ -173,7 +174,7 @@ class GroundingFunction(torch.autograd.Function):
         else:
             g = dw.contiguous().float().clone()
         dq_dtype = torch.float32
-        if ctx.q_dtype == torch.bfloat16 and mode == "bf16" and D in (256, 512, 768, 1024) and ctx.n_tok <= 96 \
+        if ctx.q_dtype == torch.bfloat16 and mode == "bf16" and D in (256, 512, 768, 1024) and ctx.n_tok <= 256 \
                 and K % 4 == 0:
             dq_dtype = torch.bfloat16      # written directly by the scatter kernel
         dq = ops.ground_bwd(g, w, arg, q_k, sd_k, mask_f, ctx.temperature, dsd, dq_dtype, row_base, ctx.n_tok)
@@ -325,19 +326,55 @@ class SparsemaxFunction(torch.autograd.Function):
 
 
 class L2NormFunction(torch.autograd.Function):
-    """x = f / (||f|| + eps)   (clip_fdt.py:411-412; clip.py:133-134)"""
+    """x = f / (||f|| + eps)   (clip_fdt.py:411-412; clip.py:133-134).
+    want_lp=True additionally returns the bf16 copy the same kernel writes (non-differentiable): the operand of the
+    tensor-core InfoNCE kernels and the payload of the all-gather (half the NVLink bytes, no cast pass afterwards)."""
 
     @staticmethod
-    def forward(ctx, f, eps):
-        x, _, norm = ops.l2norm_fwd(f.contiguous().float(), eps)
+    def forward(ctx, f, eps, want_lp=False):
+        x, xb, norm = ops.l2norm_fwd(f.contiguous().float(), eps, want_bf16=bool(want_lp))
         ctx.eps = eps
         ctx.save_for_backward(x, norm)
+        if want_lp:
+            ctx.mark_non_differentiable(xb)
+            return x, xb
         return x
 
     @staticmethod
-    def backward(ctx, g):
+    def backward(ctx, g, *unused):
         x, norm = ctx.saved_tensors
-        return ops.l2norm_bwd(x, norm, g.contiguous().float(), ctx.eps), None
+        return ops.l2norm_bwd(x, norm, g.contiguous().float(), ctx.eps), None, None
+
+
+def lp_embeddings(mode, dim):
+    """True when the contrastive head runs on the tensor cores for this width (bf16 operands, 16-byte TMA row pitch)."""
+    return mode == "bf16" and dim % 8 == 0 and dim <= 512
+
+
+class GatherHandle:
+    """Rows of every rank, rank-major [W*b, D] (the forward of clip_fdt.py:164-188), gathered ASYNCHRONOUSLY: the NCCL
+    all-gather is enqueued at construction on the process group's own stream and `wait()` makes the current stream
+    depend on it. Clip_FDT.forward starts the image gather before the text grounding and the text gather before the
+    logits_per_text half of the loss (which only needs the image rows), so neither sits on the critical path.
+    No autograd through it: the fused loss forms the local rows' total gradient from all-gathered log-sum-exps
+    (InfoNCEFunction, gathered form); callers that need d/dG use AllGather.apply."""
+
+    def __init__(self, local):
+        self.local = local.contiguous()
+        self.work = None
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            w = dist.get_world_size()
+            self.out = torch.empty((w * self.local.shape[0],) + tuple(self.local.shape[1:]), dtype=self.local.dtype,
+                                   device=self.local.device)
+            self.work = dist.all_gather_into_tensor(self.out, self.local, async_op=True)
+        else:
+            self.out = self.local
+
+    def wait(self):
+        if self.work is not None:
+            self.work.wait()
+            self.work = None
+        return self.out
 
 
 class AllGather(torch.autograd.Function):
@@ -379,8 +416,11 @@ class LogitsFunction(torch.autograd.Function):
         x, g = x.contiguous(), g.contiguous()
         sc = scale.detach().reshape(1).float().contiguous()
         if mode == "bf16":
-            out = ops.logits(ops.cast_bf16(x), ops.cast_bf16(g), sc)
+            lp = lambda t: t if t.dtype == torch.bfloat16 else ops.cast_bf16(t.float())
+            out = ops.logits(lp(x), lp(g), sc)
+            x, g = x.float(), g.float()
         else:
+            x, g = x.float(), g.float()
             out = ops.logits(x, g, sc)
         ctx.save_for_backward(x, g, sc, out)
         ctx.scale_shape = scale.shape
@@ -410,13 +450,33 @@ class InfoNCEFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x_img, x_txt, g_img, g_txt, scale, label_offset, mode, gathered=False, keep=None):
-        ts = [t.contiguous().float() for t in (x_img, x_txt, g_img, g_txt)]
         sc = scale.detach().reshape(1).float().contiguous()
+        D = x_img.shape[1]
         # the tensor-core kernels need 16-byte TMA row pitches: D % 8. Other shapes take the fp32 kernels
         # (still CUDA, still fused per row chunk).
-        if mode == "bf16" and ts[0].shape[1] % 8 == 0 and ts[0].shape[1] <= 512:
-            ts = [ops.cast_bf16(t) for t in ts]
-        loss, lse_i, lse_t, diag_i, _ = ops.nce_fwd(ts[0], ts[1], ts[2], ts[3], sc, label_offset)
+        lp = lp_embeddings(mode, D)
+        want = torch.bfloat16 if lp else torch.float32
+
+        def operand(t):
+            t = t.detach().contiguous()
+            if t.dtype == want:
+                return t
+            return ops.cast_bf16(t.float()) if lp else t.float()
+
+        if isinstance(g_img, GatherHandle):
+            # gathers in flight (Clip_FDT / CLIP.forward): the handles carry the local rows in the operand dtype.
+            # logits_per_text = x_txt . G_img^T needs only the image gather and runs while the text one completes
+            assert gathered and isinstance(g_txt, GatherHandle)
+            xl_i, xl_t = operand(g_img.local), operand(g_txt.local)
+            G_i = operand(g_img.wait())
+            lse_t, diag_t = ops.nce_lse(xl_t, G_i, sc, label_offset)
+            G_t = operand(g_txt.wait())
+            lse_i, diag_i = ops.nce_lse(xl_i, G_t, sc, label_offset)
+            loss = ops.nce_loss(lse_i, diag_i, lse_t, diag_t)
+            ts = [xl_i, xl_t, G_i, G_t]
+        else:
+            ts = [operand(t) for t in (x_img, x_txt, g_img, g_txt)]
+            loss, lse_i, lse_t, diag_i, _ = ops.nce_fwd(ts[0], ts[1], ts[2], ts[3], sc, label_offset)
         if keep is not None:   # what a later top-k count on logits_per_image needs (lazy.ContrastiveStash.topk_hits)
             keep.update(x=ts[0], g=ts[3], scale=sc, diag=diag_i, label_offset=int(label_offset))
         ctx.save_for_backward(ts[0], ts[1], ts[2], ts[3], sc, lse_i, lse_t)

@@ -31,6 +31,14 @@ class GraphedStep:
     def pool(self):
         return self.graph.pool()
 
+    def release(self):
+        """Destroy the captured graph and drop its tensors. A graph that captured NCCL collectives must be released
+        BEFORE dist.destroy_process_group(): tearing the communicator down under a live graph can block."""
+        if self.graph is not None:
+            torch.cuda.synchronize()
+            self.graph.reset()
+        self.graph, self.outputs, self.inputs = None, None, ()
+
     def __call__(self, *new_inputs):
         if new_inputs:
             with torch.no_grad():

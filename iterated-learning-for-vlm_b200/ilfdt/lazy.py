@@ -7,6 +7,8 @@ drop-in ClipInfoCELoss recognises them and runs the fused kernels on the stashed
 consumer (accuracy(), visualisation, indexing, torch functions) transparently materialises the matrix
 with the logits kernel, with autograd intact.
 """
+import dataclasses
+
 import torch
 import torch.distributed as dist
 
@@ -17,6 +19,7 @@ class ContrastiveStash:
     """What clip_fdt.py:411-419 produced: normalised local rows, gathered rows, clamped scale."""
 
     def __init__(self, x_img, x_txt, g_img, g_txt, scale, mode, gathered=False):
+        # g_img / g_txt: [B,D] tensors, or functional.GatherHandle objects whose all-gather is still in flight
         self.x_img, self.x_txt, self.g_img, self.g_txt = x_img, x_txt, g_img, g_txt
         self.scale, self.mode = scale, mode
         # True when g_* are AllGather(x_*) of this very step (the models' forward): enables the backward that
@@ -31,7 +34,20 @@ class ContrastiveStash:
 
     @property
     def B(self):
-        return self.g_img.shape[0]
+        g = self.g_img
+        return (g.out if isinstance(g, Fn.GatherHandle) else g).shape[0]
+
+    def _gathered_tensor(self, which):
+        """The gathered rows as an autograd-connected tensor. With in-flight handles (the models' forward) the
+        differentiable form is rebuilt with AllGather.apply, whose backward is the reference's reduce of the [B,D]
+        gradient (clip_fdt.py:182-188): a materialised logits matrix back-propagates exactly as the reference's does."""
+        g, x = (self.g_img, self.x_img) if which == 0 else (self.g_txt, self.x_txt)
+        if not isinstance(g, Fn.GatherHandle):
+            return g
+        if torch.is_grad_enabled() and x.requires_grad:
+            out = Fn.AllGather.apply(x)
+            return out.view(-1, *out.shape[2:])
+        return g.wait()
 
     def label_offset(self):
         """loss.py:41-45: arange(b) when the logits are square, else rank*b + arange(b)."""
@@ -42,7 +58,7 @@ class ContrastiveStash:
 
     def materialize(self, which):
         if self._mat[which] is None:
-            x, g = (self.x_img, self.g_txt) if which == 0 else (self.x_txt, self.g_img)
+            x, g = (self.x_img, self._gathered_tensor(1)) if which == 0 else (self.x_txt, self._gathered_tensor(0))
             self._mat[which] = Fn.LogitsFunction.apply(x, g, self.scale, self.mode)
         return self._mat[which]
 
@@ -59,19 +75,30 @@ class ContrastiveStash:
             return ops.topk_hits(self._mat[0].detach().contiguous(), self.label_offset())
         if not self._kept:   # accuracy() before the loss: run the forward kernels for the label logits
             with torch.no_grad():
-                Fn.InfoNCEFunction.apply(self.x_img.detach(), self.x_txt.detach(), self.g_img.detach(),
-                                         self.g_txt.detach(), self.scale.detach(), self.label_offset(), self.mode,
-                                         False, self._kept)
+                Fn.InfoNCEFunction.apply(self.x_img.detach(), self.x_txt.detach(), self._gathered_tensor(0).detach(),
+                                         self._gathered_tensor(1).detach(), self.scale.detach(), self.label_offset(),
+                                         self.mode, False, self._kept)
         k = self._kept
         return ops.nce_topk_hits(k["x"], k["g"], k["scale"], k["label_offset"], k["diag"])
 
 
+@dataclasses.dataclass(eq=False, repr=False, init=False)
 class LazyLogits:
-    """Stands in for logits_per_image (which=0) / logits_per_text (which=1)."""
+    """Stands in for logits_per_image (which=0) / logits_per_text (which=1).
+
+    It is a dataclass on purpose: the reference wraps the model in DistributedDataParallel with
+    find_unused_parameters=True (prototype/utils/torch_ddp_dist.py:65), and DDP discovers the autograd graph of a
+    forward from the TENSORS IT CAN FIND in the returned object -- tuples, lists, dicts and dataclass fields
+    (torch/nn/parallel/distributed.py:_find_tensors). `autograd_anchors` exposes the graph-connected tensors the
+    lazy matrix is a function of (normalised local embeddings, scale); without it DDP would see no tensor at all,
+    declare every parameter unused and fail on the real backward."""
+    autograd_anchors: tuple = ()
 
     def __init__(self, stash, which):
         object.__setattr__(self, "_stash", stash)
         object.__setattr__(self, "_which", which)
+        object.__setattr__(self, "autograd_anchors", tuple(
+            t for t in (stash.x_img, stash.x_txt, stash.scale) if isinstance(t, torch.Tensor) and t.requires_grad))
 
     # -- cheap metadata that does not need the matrix --
     @property

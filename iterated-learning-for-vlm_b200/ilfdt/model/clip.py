@@ -38,14 +38,23 @@ class CLIP(nn.Module):
         image_features = self.encode_image(images)
         text_features = self.encode_text(texts)
         # clip.py:133-134: the image side is normalised WITHOUT an epsilon, the text side with 1e-10 (F10)
-        image_features = Fn.L2NormFunction.apply(image_features, 0.0)
-        text_features = Fn.L2NormFunction.apply(text_features, 1e-10)
+        mode = Fn.get_compute_dtype()
+        lp = Fn.lp_embeddings(mode, image_features.shape[1])
+        image_features, gathered_image_features = self._normalise_and_gather(image_features, 0.0, lp)
+        text_features, gathered_text_features = self._normalise_and_gather(text_features, 1e-10, lp)
         logit_scale = self.logit_scale.exp()                          # clip.py:137-138 (F7)
         logit_scale.data = torch.clamp(logit_scale.data, max=100)
-        gathered_image_features = self.all_gather(image_features)
-        gathered_text_features = self.all_gather(text_features)
         # clip.py:146-147 scales the features before the matmul; the kernels scale the product, which
         # differs by rounding only (tolerance stated in tests/test_parity_gpu.py)
         stash = ContrastiveStash(image_features, text_features, gathered_image_features, gathered_text_features,
-                                 logit_scale, Fn.get_compute_dtype(), gathered=True)
+                                 logit_scale, mode, gathered=True)
         return LazyLogits(stash, 0), LazyLogits(stash, 1)
+
+    @staticmethod
+    def _normalise_and_gather(ft, eps, lp):
+        """clip.py:133-134 + :140-141; the all-gather starts at once and is awaited inside the fused loss."""
+        if lp:
+            x, xb = Fn.L2NormFunction.apply(ft, eps, True)
+            return x, Fn.GatherHandle(xb)
+        x = Fn.L2NormFunction.apply(ft, eps)
+        return x, Fn.GatherHandle(x.detach())

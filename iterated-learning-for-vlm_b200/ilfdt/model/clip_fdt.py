@@ -263,25 +263,32 @@ class Clip_FDT(nn.Module):
         patch_ft = self._image_features(images)
         _, word_ft, _, pad_mask = self.encode_text(texts, return_dense=True, return_padmask=True,
                                                    return_raw_feature=True)
+        mode = Fn.get_compute_dtype()
+        lp = Fn.lp_embeddings(mode, self.space_dict.shape[1])
         with Fn.codebook_scope():   # both Query_models read the same codebook values: one bf16 copy for the two
             _, sd_img_ft, img_k = self.img_query_model(patch_ft, self.space_dict, need_weights=False)
+            # :411 + :418 for the image side right away: its all-gather (bf16 rows in the tensor-core mode) travels
+            # over NVLink while the text side is still being grounded
+            sd_img_ft, gathered_img = self._normalise_and_gather(sd_img_ft, lp)
             _, sd_txt_ft, txt_k = self.txt_query_model(word_ft, self.space_dict, mask=pad_mask, need_weights=False)
-
-        sd_img_ft = Fn.L2NormFunction.apply(sd_img_ft, 1e-10)       # :411
-        sd_txt_ft = Fn.L2NormFunction.apply(sd_txt_ft, 1e-10)       # :412
+        sd_txt_ft, gathered_txt = self._normalise_and_gather(sd_txt_ft, lp)       # :412, :419
 
         # :415-416 -- forward value clamped to 100 through .data, backward through the unclamped exp (F7)
         logit_scale = self.logit_scale.exp()
         logit_scale.data = torch.clamp(logit_scale.data, max=100)
 
-        gathered_img = self.all_gather(sd_img_ft)                   # :418
-        gathered_txt = self.all_gather(sd_txt_ft)                   # :419
-
         # :421-422 -- the two [b,B] logit matrices are returned lazily: ClipInfoCELoss consumes the stash
         # through the fused kernels; any other use materialises them with the logits kernel.
-        stash = ContrastiveStash(sd_img_ft, sd_txt_ft, gathered_img, gathered_txt, logit_scale,
-                                 Fn.get_compute_dtype(), gathered=True)
+        stash = ContrastiveStash(sd_img_ft, sd_txt_ft, gathered_img, gathered_txt, logit_scale, mode, gathered=True)
         return (LazyLogits(stash, 0), LazyLogits(stash, 1)), (img_k, txt_k)
+
+    @staticmethod
+    def _normalise_and_gather(ft, lp):
+        if lp:
+            x, xb = Fn.L2NormFunction.apply(ft, 1e-10, True)
+            return x, Fn.GatherHandle(xb)
+        x = Fn.L2NormFunction.apply(ft, 1e-10)
+        return x, Fn.GatherHandle(x.detach())
 
 
 def _reference_encoders():

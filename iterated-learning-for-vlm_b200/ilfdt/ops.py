@@ -21,7 +21,7 @@ PROFILE_ON = False    # when True every C call is bracketed by CUDA events on th
 PROFILE = {}          # op name -> [(start_event, end_event), ...]
 _KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mask_rows_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_ground_fwd_text": 5, "ilfdt_text_compact": 3, "ilfdt_sparsemax_fwd": 1,
                      "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2, "ilfdt_ground_bwd_w16": 2,
-                     "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5,
+                     "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5, "ilfdt_nce_lse": 2, "ilfdt_nce_loss": 1,
                      "ilfdt_nce_bwd": 4, "ilfdt_nce_bwd_gathered": 2, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
                      "ilfdt_randn_fill": 1, "ilfdt_copy": 0,
                      "ilfdt_gemm_tn_splitk": 2, "ilfdt_linear_bf16": 1, "ilfdt_ln_fwd": 1, "ilfdt_ln_bwd": 4, "ilfdt_bias_cast": 1, "ilfdt_colsum": 2}
@@ -407,6 +407,28 @@ def nce_fwd(x_img, x_txt, g_img, g_txt, scale, label_offset):
                                     int(label_offset), _ptr(lse_i), _ptr(lse_t), _ptr(diag_i), _ptr(diag_t),
                                     _ptr(loss), _ptr(ws), n, _stream())
     return loss, lse_i, lse_t, diag_i, diag_t
+
+
+def nce_lse(x, g, scale, label_offset):
+    """One direction of nce_fwd: (lse [b], diag [b]) of the rows scale * x . g^T, labels label_offset + row."""
+    _req(x, None, "x"); _req(g, x.dtype, "g"); _req(scale, torch.float32, "scale")
+    b, D = x.shape
+    B = g.shape[0]
+    dt = _DT[x.dtype]
+    lse = torch.empty(b, dtype=torch.float32, device=x.device)
+    diag = torch.empty_like(lse)
+    ws, n = _nce_ws(dt, b, B, D, x.device)
+    _call("ilfdt_nce_lse", _ptr(x), _ptr(g), dt, b, B, D, _ptr(scale), int(label_offset), _ptr(lse), _ptr(diag), _ptr(ws), n,
+          _stream())
+    return lse, diag
+
+
+def nce_loss(lse_i, diag_i, lse_t, diag_t):
+    for t in (lse_i, diag_i, lse_t, diag_t):
+        _req(t, torch.float32, "lse / diag")
+    loss = torch.empty((), dtype=torch.float32, device=lse_i.device)
+    _call("ilfdt_nce_loss", _ptr(lse_i), _ptr(diag_i), _ptr(lse_t), _ptr(diag_t), lse_i.numel(), _ptr(loss), _stream())
+    return loss
 
 
 def nce_bwd(x_img, x_txt, g_img, g_txt, scale, label_offset, lse_i, lse_t, grad_out):

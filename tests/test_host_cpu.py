@@ -348,3 +348,64 @@ def test_tune_knobs_are_explicit_api_not_environment(built_lib):
     assert lib.ilfdt_tune_set(99, 1) != 0
     for f in os.listdir(os.path.join(PKG, "csrc")):
         assert "getenv" not in open(os.path.join(PKG, "csrc", f)).read(), f
+
+
+def _ddp_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sys.path.insert(0, PKG)
+    from torch.nn.parallel import DistributedDataParallel as DDP
+    from torch.nn.parallel.distributed import _find_tensors
+    from ilfdt.lazy import ContrastiveStash, LazyLogits
+
+    class Net(torch.nn.Module):
+        """Returns what Clip_FDT.forward returns: ((LazyLogits, LazyLogits), (codebook, codebook))."""
+
+        def __init__(self):
+            super().__init__()
+            self.fc_i, self.fc_t = torch.nn.Linear(6, 4), torch.nn.Linear(6, 4)
+            self.space_dict = torch.nn.Parameter(torch.randn(5, 4))
+            self.logit_scale = torch.nn.Parameter(torch.ones(1))
+            self.unused = torch.nn.Parameter(torch.ones(1))      # logit_scale_sd: declared, never used (clip_fdt.py:227)
+
+        def forward(self, a, b):
+            x_i = self.fc_i(a) @ self.space_dict.t() @ self.space_dict
+            x_t = self.fc_t(b) @ self.space_dict.t() @ self.space_dict
+            st = ContrastiveStash(x_i, x_t, x_i.detach(), x_t.detach(), self.logit_scale.exp(), "fp32", gathered=True)
+            return (LazyLogits(st, 0), LazyLogits(st, 1)), (self.space_dict, self.space_dict)
+
+    torch.manual_seed(0)
+    net = DDP(Net(), find_unused_parameters=True)
+    ok = True
+    for step in range(2):                       # a second step: the reducer must have been left in a clean state
+        g = torch.Generator().manual_seed(10 * rank + step)
+        (l_i, l_t), _ = net(torch.randn(3, 6, generator=g), torch.randn(3, 6, generator=g))
+        found = list(_find_tensors(((l_i, l_t),)))
+        ok = ok and len(found) >= 4 and all(t.requires_grad for t in found)
+        st = l_i._stash                          # stand-in for the fused loss (CPU): any function of the anchors
+        loss = (st.x_img * st.x_txt).sum() * st.scale.sum()
+        loss.backward()                          # raises "mark a variable ready only once" if DDP saw no tensors
+        grads = [p.grad.clone() for n, p in net.named_parameters() if "unused" not in n]
+        for gr in grads:                         # DDP averaged them: identical on every rank
+            ref = gr.clone()
+            dist.broadcast(ref, 0)
+            ok = ok and torch.allclose(gr, ref)
+        net.zero_grad()
+    q.put((rank, ok))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_lazy_logits_are_visible_to_ddp_find_unused_parameters():
+    """The solver wraps the model in DDP(find_unused_parameters=True) (torch_ddp_dist.py:65). DDP must be able to walk
+    from the forward's return value (LazyLogits handles) to the parameters, or every real backward fails."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_ddp_worker, args=(r, 2, 29611, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert res == [(0, True), (1, True)]

@@ -267,7 +267,8 @@ def test_grounding_fwd_bwd(ops, b, n_tok, K, D, masked, mode):
             assert margin < 1e-8, "support sets differ at entries with weight up to %.3e" % margin
 
 
-@pytest.mark.parametrize("b,n_tok,K,D,masked", [(6, 49, 1024, 512, False), (5, 77, 2048, 512, True), (3, 20, 20000, 256, True)])
+@pytest.mark.parametrize("b,n_tok,K,D,masked", [(6, 49, 1024, 512, False), (5, 77, 2048, 512, True), (3, 20, 20000, 256, True),
+                                               (4, 196, 2048, 512, False)])
 def test_grounding_bf16_q_input(ops, b, n_tok, K, D, masked):
     """A q that already is bf16 (producer under autocast / bf16 host buffers) skips the cast: forward outputs are
     bit-identical to the fp32-q call on the same values and dq comes back in bf16 from the scatter kernel."""
@@ -296,7 +297,8 @@ def test_grounding_bf16_q_input(ops, b, n_tok, K, D, masked):
 
 
 @pytest.mark.parametrize("b,n_tok,K,D,masked", [(33, 49, 512, 512, False), (70, 77, 1024, 512, True),
-                                               (16, 77, 256, 256, True), (5, 96, 384, 512, False)])
+                                               (16, 77, 256, 256, True), (5, 96, 384, 512, False),
+                                               (9, 196, 1024, 512, False), (4, 120, 512, 512, True)])
 @pytest.mark.parametrize("qdtype", ["f32", "bf16"])
 def test_grounding_without_fp32_weights(ops, b, n_tok, K, D, masked, qdtype):
     """need_weights=False (Clip_FDT.forward drops att_weight, clip_fdt.py:233-234): the fp32 weights are never
