@@ -38,10 +38,18 @@ int32_t require_sm100() {
 }
 
 // F32 route of the InfoNCE step: logits are streamed through the workspace in row chunks.
+// F32 workspace: [chunk of logits R x B floats][2 b doubles: per-row d scale contributions of the two directions]
+static int64_t nce_f32_logits_bytes(int64_t b, int64_t B);
+static double* nce_f32_row_acc(void* ws, int64_t b, int64_t B) {
+  return reinterpret_cast<double*>(reinterpret_cast<char*>(ws) + nce_f32_logits_bytes(b, B));
+}
 static int64_t nce_f32_chunk_rows(int64_t b, int64_t B) {
   const int64_t budget_elems = 1ll << 26;  // 256 MiB of fp32
   return std::max<int64_t>(1, std::min<int64_t>(b, budget_elems / std::max<int64_t>(B, 1)));
 }
+
+static int64_t nce_f32_logits_bytes(int64_t b, int64_t B) { return round_up(nce_f32_chunk_rows(b, B) * B * 4, 16); }
+static int64_t nce_f32_ws_bytes(int64_t b, int64_t B) { return nce_f32_logits_bytes(b, B) + 2 * b * 8; }
 
 static int32_t nce_lse_f32(const float* X, const float* G, int64_t b, int64_t B, int64_t D, const float* scale,
                            int64_t label_offset, float* lse, float* diag, void* ws, int64_t ws_bytes, cudaStream_t st) {
@@ -72,9 +80,9 @@ static int32_t nce_bwd_f32(const float* x_img, const float* x_txt, const float* 
                            const float* lse_t, const float* grad_out, float* dx_img, float* dx_txt, float* dg_img,
                            float* dg_txt, float* dscale, void* ws, int64_t ws_bytes, cudaStream_t st) {
   const int64_t R = nce_f32_chunk_rows(b, B);
-  ILFDT_REQUIRE(ws != nullptr && ws_bytes >= R * B * 4, ILFDT_E_INVALID_ARG, "nce_bwd(f32): workspace too small");
+  ILFDT_REQUIRE(ws != nullptr && ws_bytes >= nce_f32_ws_bytes(b, B), ILFDT_E_INVALID_ARG, "nce_bwd(f32): workspace too small");
   float* L = reinterpret_cast<float*>(ws);
-  ILFDT_CUDA_OK(cudaMemsetAsync(dscale, 0, 4, st));
+  double* row_acc = nce_f32_row_acc(ws, b, B);
   const float coef = 1.f / (2.f * (float)b);  // CE mean over the local rows, then /2 (loss.py:47-49)
   for (int dir = 0; dir < 2; ++dir) {
     const float* X = dir == 0 ? x_img : x_txt;
@@ -86,7 +94,8 @@ static int32_t nce_bwd_f32(const float* x_img, const float* x_txt, const float* 
       const int64_t rows = std::min(R, b - r0);
       int32_t rc = launch_gemm_f32(X + r0 * D, D, 1, G, D, 1, L, B, 1, rows, B, D, 1.f, scale, 0, st);
       if (rc != ILFDT_OK) return rc;
-      rc = launch_softmax_grad_rows(L, L, B, rows, B, label_offset + r0, lse + r0, grad_out, coef, scale, dscale, st);
+      rc = launch_softmax_grad_rows(L, L, B, rows, B, label_offset + r0, lse + r0, grad_out, coef, scale,
+                                    row_acc + dir * b + r0, st);
       if (rc != ILFDT_OK) return rc;
       // dX[r,:] = scale * sum_c P[r,c] G[c,:]
       rc = launch_gemm_f32(L, B, 1, G, 1, D, dX + r0 * D, D, 1, rows, D, B, 1.f, scale, 0, st);
@@ -96,7 +105,7 @@ static int32_t nce_bwd_f32(const float* x_img, const float* x_txt, const float* 
       if (rc != ILFDT_OK) return rc;
     }
   }
-  return ILFDT_OK;
+  return launch_sum_rows(row_acc, 2 * b, dscale, st);
 }
 
 // Gathered form of the F32 route (see ilfdt_nce_bwd_gathered): per direction, for a chunk of local rows,
@@ -106,9 +115,9 @@ static int32_t nce_bwd_gathered_f32(const float* x_img, const float* x_txt, cons
                                     const float* lse_i_all, const float* lse_t_all, const float* go_all, float* dx_img,
                                     float* dx_txt, float* dscale, void* ws, int64_t ws_bytes, cudaStream_t st) {
   const int64_t R = nce_f32_chunk_rows(b, B);
-  ILFDT_REQUIRE(ws != nullptr && ws_bytes >= R * B * 4, ILFDT_E_INVALID_ARG, "nce_bwd(f32): workspace too small");
+  ILFDT_REQUIRE(ws != nullptr && ws_bytes >= nce_f32_ws_bytes(b, B), ILFDT_E_INVALID_ARG, "nce_bwd(f32): workspace too small");
   float* L = reinterpret_cast<float*>(ws);
-  ILFDT_CUDA_OK(cudaMemsetAsync(dscale, 0, 4, st));
+  double* row_acc = nce_f32_row_acc(ws, b, B);
   const float coef = 1.f / (2.f * (float)b);
   for (int dir = 0; dir < 2; ++dir) {
     const float* X = dir == 0 ? x_img : x_txt;
@@ -121,13 +130,13 @@ static int32_t nce_bwd_gathered_f32(const float* x_img, const float* x_txt, cons
       int32_t rc = launch_gemm_f32(X + r0 * D, D, 1, G, D, 1, L, B, 1, rows, B, D, 1.f, scale, 0, st);
       if (rc != ILFDT_OK) return rc;
       rc = launch_softmax_grad_sym_rows(L, L, B, rows, B, label_offset + r0, lse_lane + r0, lse_stream,
-                                        go_all + label_offset / b, go_all, b, coef, scale, dscale, st);
+                                        go_all + label_offset / b, go_all, b, coef, scale, row_acc + dir * b + r0, st);
       if (rc != ILFDT_OK) return rc;
       rc = launch_gemm_f32(L, B, 1, G, 1, D, dX + r0 * D, D, 1, rows, D, B, 1.f, scale, 0, st);
       if (rc != ILFDT_OK) return rc;
     }
   }
-  return ILFDT_OK;
+  return launch_sum_rows(row_acc, 2 * b, dscale, st);
 }
 
 }  // namespace ilfdt
@@ -414,7 +423,7 @@ int32_t ilfdt_logits(const void* x, const void* g, int32_t dtype, int64_t b, int
 }
 
 int64_t ilfdt_nce_ws_bytes(int32_t dtype, int64_t b, int64_t B, int64_t D) {
-  if (dtype == ILFDT_F32) return nce_f32_chunk_rows(b, B) * B * 4;
+  if (dtype == ILFDT_F32) return nce_f32_ws_bytes(b, B);
   return std::max(nce_fwd_bf16_ws_bytes(b, B), nce_bwd_bf16_ws_bytes(b, B, D));
 }
 

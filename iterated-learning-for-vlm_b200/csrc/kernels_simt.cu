@@ -260,34 +260,44 @@ lse_rows_kernel(const float* __restrict__ L, int64_t ld, int64_t cols, int64_t l
   }
 }
 
-// In place: L[r,c] <- (exp(L[r,c] - lse[r]) - [c == label0 + r]) * go[0] * coef;
-// per-row sum of P * L (for dscale) accumulated into dscale_acc with one atomic per CTA.
+// In place: L[r,c] <- (exp(L[r,c] - lse[r]) - [c == label0 + r]) * go[0] * coef.
+// d scale: the row's sum_c P[r,c] * L[r,c] / scale is formed WITHOUT its cancellation: since sum_c softmax = 1,
+//   sum_c (softmax_c - [c == label]) * L_c  ==  sum_c softmax_c * (L_c - L_label),
+// every term of the right-hand side is small where the left-hand side subtracts two O(|L|) numbers (the reference's
+// autograd sits at 1e-7 of the fp64 value on config 1; the naive fp32 form sat at 1e-4). Threads sum in fp32, warps and
+// rows in fp64; the per-row results go to row_acc[row] and are added in a fixed order by sum_rows_kernel (no atomics).
+__device__ __forceinline__ void block_row_acc(float part, double* __restrict__ row_acc, int64_t row) {
+  double dpart = warp_sum((double)part);
+  __shared__ double sm[8];
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = dpart;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w2 = 1; w2 < (int)(blockDim.x >> 5); ++w2) dpart += sm[w2];
+    row_acc[row] = dpart;
+  }
+}
+
 __global__ void __launch_bounds__(256)
 softmax_grad_rows_kernel(const float* L, float* out, int64_t ld, int64_t cols, int64_t label0,
                          const float* __restrict__ lse, const float* __restrict__ go, float coef,
-                         const float* __restrict__ scale_dev, float* __restrict__ dscale_acc) {
+                         const float* __restrict__ scale_dev, double* __restrict__ row_acc) {
   const int64_t row = blockIdx.x;
   const float* lr = L + row * ld;
   float* orow = out + row * ld;
   const float l = lse[row];
   const float w = go[0] * coef;
   const float inv_scale = scale_dev ? 1.f / __ldg(scale_dev) : 0.f;
+  const float v_lab = lr[label0 + row];
+  __syncthreads();   // out may alias L: everyone has the label logit before anyone overwrites it
   float part = 0.f;
   for (int64_t c = threadIdx.x; c < cols; c += blockDim.x) {
     float v = lr[c];
-    float p = (expf(v - l) - ((c == label0 + row) ? 1.f : 0.f)) * w;
-    part = fmaf(p, v * inv_scale, part);
-    orow[c] = p;
+    float e = expf(v - l);
+    part = fmaf(e * w, (v - v_lab) * inv_scale, part);
+    orow[c] = (e - ((c == label0 + row) ? 1.f : 0.f)) * w;
   }
-  if (dscale_acc == nullptr) return;
-  part = warp_sum(part);
-  __shared__ float sm[8];
-  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = part;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    for (int w2 = 1; w2 < (int)(blockDim.x >> 5); ++w2) part += sm[w2];
-    atomicAdd(dscale_acc, part);
-  }
+  if (row_acc == nullptr) return;
+  block_row_acc(part, row_acc, row);
 }
 
 // Gathered form (ilfdt_nce_bwd_gathered, fp32 route), in place on a chunk of stored logits:
@@ -298,39 +308,53 @@ softmax_grad_sym_rows_kernel(const float* L, float* out, int64_t ld, int64_t col
                              const float* __restrict__ lse_lane, const float* __restrict__ lse_stream,
                              const float* __restrict__ go_lane, const float* __restrict__ go_stream,
                              int64_t rows_per_go, float coef, const float* __restrict__ scale_dev,
-                             float* __restrict__ dscale_acc) {
+                             double* __restrict__ row_acc) {
   const int64_t row = blockIdx.x;
   const float* lr = L + row * ld;
   float* orow = out + row * ld;
   const float l = lse_lane[row];
   const float wl = go_lane[0] * coef;
   const float inv_scale = 1.f / __ldg(scale_dev);
+  const float v_lab = lr[label0 + row];
+  __syncthreads();
   float part = 0.f;
   for (int64_t c = threadIdx.x; c < cols; c += blockDim.x) {
     const float v = lr[c];
     const float d = (c == label0 + row) ? 1.f : 0.f;
-    const float pl = (expf(v - l) - d) * wl;
+    const float e = expf(v - l);
     const float ps = (expf(v - lse_stream[c]) - d) * (go_stream[c / rows_per_go] * coef);
-    part = fmaf(pl, v * inv_scale, part);
-    orow[c] = pl + ps;
+    part = fmaf(e * wl, (v - v_lab) * inv_scale, part);
+    orow[c] = (e - d) * wl + ps;
   }
-  part = warp_sum(part);
-  __shared__ float sm[8];
-  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = part;
+  block_row_acc(part, row_acc, row);
+}
+
+// out[0] = sum of n doubles in a fixed order (single CTA): the rows' d scale contributions
+__global__ void __launch_bounds__(256) sum_rows_kernel(const double* __restrict__ acc, int64_t n, float* __restrict__ out) {
+  double s = 0.0;
+  for (int64_t i = threadIdx.x; i < n; i += 256) s += acc[i];
+  s = warp_sum(s);
+  __shared__ double sm[8];
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = s;
   __syncthreads();
   if (threadIdx.x == 0) {
-    for (int w2 = 1; w2 < (int)(blockDim.x >> 5); ++w2) part += sm[w2];
-    atomicAdd(dscale_acc, part);
+    for (int w = 1; w < 8; ++w) s += sm[w];
+    out[0] = (float)s;
   }
+}
+int32_t launch_sum_rows(const double* acc, int64_t n, float* out, cudaStream_t st) {
+  sum_rows_kernel<<<1, 256, 0, st>>>(acc, n, out);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
 }
 
 int32_t launch_softmax_grad_sym_rows(const float* L, float* out, int64_t ld, int64_t rows, int64_t cols, int64_t label0,
                                      const float* lse_lane, const float* lse_stream, const float* go_lane,
                                      const float* go_stream, int64_t rows_per_go, float coef, const float* scale_dev,
-                                     float* dscale_acc, cudaStream_t st) {
+                                     double* row_acc, cudaStream_t st) {
   if (rows == 0) return ILFDT_OK;
   softmax_grad_sym_rows_kernel<<<(unsigned)rows, 256, 0, st>>>(L, out, ld, cols, label0, lse_lane, lse_stream, go_lane,
-                                                              go_stream, rows_per_go, coef, scale_dev, dscale_acc);
+                                                              go_stream, rows_per_go, coef, scale_dev, row_acc);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }
@@ -344,10 +368,10 @@ int32_t launch_lse_rows(const float* L, int64_t ld, int64_t rows, int64_t cols, 
 }
 int32_t launch_softmax_grad_rows(const float* L, float* out, int64_t ld, int64_t rows, int64_t cols, int64_t label0,
                                  const float* lse, const float* go, float coef, const float* scale_dev,
-                                 float* dscale_acc, cudaStream_t st) {
+                                 double* row_acc, cudaStream_t st) {
   if (rows == 0) return ILFDT_OK;
   softmax_grad_rows_kernel<<<(unsigned)rows, 256, 0, st>>>(L, out, ld, cols, label0, lse, go, coef, scale_dev,
-                                                          dscale_acc);
+                                                          row_acc);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }

@@ -19,11 +19,12 @@ int32_t launch_l2norm_bwd(const float* x, const float* norm, const float* g, int
 int32_t launch_lse_rows(const float* L, int64_t ld, int64_t rows, int64_t cols, int64_t label0, float* lse,
                         float* diag, cudaStream_t st);
 int32_t launch_softmax_grad_rows(const float* L, float* out, int64_t ld, int64_t rows, int64_t cols, int64_t label0, const float* lse,
-                                 const float* go, float coef, const float* scale_dev, float* dscale_acc, cudaStream_t st);
+                                 const float* go, float coef, const float* scale_dev, double* row_acc, cudaStream_t st);
+int32_t launch_sum_rows(const double* acc, int64_t n, float* out, cudaStream_t st);
 int32_t launch_softmax_grad_sym_rows(const float* L, float* out, int64_t ld, int64_t rows, int64_t cols, int64_t label0,
                                      const float* lse_lane, const float* lse_stream, const float* go_lane,
                                      const float* go_stream, int64_t rows_per_go, float coef, const float* scale_dev,
-                                     float* dscale_acc, cudaStream_t st);
+                                     double* row_acc, cudaStream_t st);
 int32_t launch_nce_loss(const float* lse_i, const float* diag_i, const float* lse_t, const float* diag_t, int64_t b,
                         float* loss, cudaStream_t st);
 int32_t launch_topk_hits(const float* L, int64_t b, int64_t B, int64_t label0, int32_t* counts, cudaStream_t st);

@@ -214,8 +214,14 @@ def test_config1_reference_golden(ops, golden_dir, variant, mode):
         d_sd = m.space_dict.grad
         for name, g_ in (("patch", patch.grad), ("word", word.grad), ("space_dict", d_sd)):
             ours = O.project(case["proj"][name], g_)
-            for pre in ("f32_", "f64_"):
-                report[pre + "proj_" + name] = assert_close(ours, T(pre + "proj_d_" + name), ptol, pre + "proj d_" + name)
+            p32, p64 = T("f32_proj_d_" + name).double(), T("f64_proj_d_" + name).double()
+            # how far the REFERENCE'S OWN fp32 run sits from its fp64 run on this very projection: ~1e-6 on the bf16-exact
+            # inputs, ~1e-3 on the unrounded ones, where a single argmax tie moves one gradient row (see module docstring)
+            ref_floor = ((p32 - p64).abs().max() / p64.abs().max()).item()
+            gate = max(ptol, 3 * ref_floor)
+            report["f64_proj_" + name] = assert_close(ours, p64, gate, "proj d_%s vs the fp64 run (reference fp32-vs-fp64: %.1e)" % (name, ref_floor))
+            report["f32_proj_" + name] = assert_close(ours, p32, gate + ref_floor, "proj d_%s vs the fp32 run" % name)
+            report["ref_floor_proj_" + name] = ref_floor
         for name, g_ in (("patch", patch.grad[:1]), ("word", word.grad[:1]), ("space_dict", d_sd[:64])):
             r32, r64 = T("f32_d_%s_rows" % name).double(), T("f64_d_%s_rows" % name).double()
             ref_floor = ((r32 - r64).abs().max() / r64.abs().max()).item()
@@ -405,8 +411,9 @@ def test_infonce_rank_of_eight_at_32k(ops, mode):
     g_ = torch.Generator(device="cuda").manual_seed(32)
     # correlated pairs so that top-1 / top-5 are neither 0 nor b
     base = torch.randn(B, D, device=dev, generator=g_)
-    xi = torch.nn.functional.normalize(base + 0.9 * torch.randn(B, D, device=dev, generator=g_), dim=1)
-    xt = torch.nn.functional.normalize(base + 0.9 * torch.randn(B, D, device=dev, generator=g_), dim=1)
+    # pair cosine a^2/(1+a^2) = 0.17 against the best of 32767 random negatives (~4 sigma of 1/sqrt(512) = 0.18)
+    xi = torch.nn.functional.normalize(0.45 * base + torch.randn(B, D, device=dev, generator=g_), dim=1)
+    xt = torch.nn.functional.normalize(0.45 * base + torch.randn(B, D, device=dev, generator=g_), dim=1)
     if mode == "bf16":
         xi, xt = bf16_round(xi), bf16_round(xt)
     pval = math.log(1 / 0.07)
