@@ -26,17 +26,30 @@ import torch.nn.functional as F
 # --------------------------------------------------------------------------------------------
 
 
-def sparsemax(x: torch.Tensor, dim: int = -1) -> torch.Tensor:
+def sparsemax(x: torch.Tensor, dim: int = -1, force_support=None) -> torch.Tensor:
     """Simplex projection along `dim` by the sorted-prefix rule of sparsemax.py:40-63.
 
     Layout juggling of sparsemax.py:31-35,66-69 (swap dim with 0, flatten the rest, transpose so the
     logits are the trailing axis) is restated with movedim; the arithmetic per row is identical.
+
+    force_support (TEST HOOK, bool, same shape as x with `dim` last): evaluate the projection ON A GIVEN
+    SUPPORT S -- tau = (sum_S z - 1)/|S|, out = (z - tau) on S, 0 elsewhere -- which is what the sorted
+    rule computes once S is known. The projection is continuous in z but its JACOBIAN is not: an entry that
+    sits at the threshold to within rounding carries weight ~0 and a full-size gradient, so two correct
+    evaluations that disagree on that one membership bit disagree on the gradient by O(1). Gradient parity is
+    therefore stated on the same piece: the tests pass the support (and argmax tokens) the implementation
+    under test chose, after checking that those choices differ from the free-running rule only at
+    rounding-ambiguous entries.
     """
     z = x.movedim(dim, -1)
     lead_shape = z.shape
     z = z.reshape(-1, z.shape[-1])
     n = z.shape[-1]
     z = z - z.max(dim=1, keepdim=True)[0]                       # sparsemax.py:40
+    if force_support is not None:
+        nz = force_support.reshape(z.shape).to(z.dtype)
+        tau = ((z * nz).sum(dim=1, keepdim=True) - 1) / nz.sum(dim=1, keepdim=True)
+        return ((z - tau) * nz).reshape(lead_shape).movedim(-1, dim)
     zs = torch.sort(z, dim=1, descending=True)[0]               # :45
     ks = torch.arange(1, n + 1, dtype=z.dtype, device=z.device).view(1, -1)      # :46-47
     bound = 1 + ks * zs                                         # :50
@@ -69,7 +82,7 @@ def sparsemax_tau_exact(z_row: np.ndarray):
 # --------------------------------------------------------------------------------------------
 
 
-def pooled_scores(q, sd, mask=None, temperature=1.0, pool_type="max", return_token_scores=False):
+def pooled_scores(q, sd, mask=None, temperature=1.0, pool_type="max", return_token_scores=False, force_arg=None):
     """q [b,N,D], sd [K,D], mask [b,N] (0 = real token, -inf = pad) -> pooled [b,K].
 
     Operation ORDER is the reference's (clip_fdt.py:118 matmul, :123 /sqrt(D), :125-130 multiply by
@@ -87,6 +100,8 @@ def pooled_scores(q, sd, mask=None, temperature=1.0, pool_type="max", return_tok
         s = s.sum(1)
     elif pool_type == "mean":
         s = s.mean(1)
+    elif pool_type == "max" and force_arg is not None:          # TEST HOOK: the max taken at GIVEN tokens (see sparsemax)
+        s = torch.gather(s, 1, force_arg.long().unsqueeze(1)).squeeze(1)
     elif pool_type == "max":
         s = s.max(1)[0]                                         # :145
     else:
@@ -96,9 +111,9 @@ def pooled_scores(q, sd, mask=None, temperature=1.0, pool_type="max", return_tok
     return s
 
 
-def attention_weights(pooled, att_func_type="sparsemax"):
+def attention_weights(pooled, att_func_type="sparsemax", force_support=None):
     if att_func_type == "sparsemax":
-        return sparsemax(pooled, dim=-1)                        # clip_fdt.py:74,149
+        return sparsemax(pooled, dim=-1, force_support=force_support)   # clip_fdt.py:74,149
     if att_func_type == "softmax":
         return torch.softmax(pooled, dim=-1)                    # :72
     if att_func_type == "sigmoid":
@@ -106,10 +121,12 @@ def attention_weights(pooled, att_func_type="sparsemax"):
     raise ValueError(att_func_type)
 
 
-def grounding(q, sd, mask=None, temperature=1.0, att_func_type="sparsemax", pool_type="max"):
-    """Returns (att_weight [b,K], att_ft [b,D], pooled [b,K])   clip_fdt.py:113-161."""
-    pooled = pooled_scores(q, sd, mask, temperature, pool_type)
-    w = attention_weights(pooled, att_func_type)
+def grounding(q, sd, mask=None, temperature=1.0, att_func_type="sparsemax", pool_type="max", force_arg=None,
+              force_support=None):
+    """Returns (att_weight [b,K], att_ft [b,D], pooled [b,K])   clip_fdt.py:113-161.
+    force_arg / force_support: test hooks, see sparsemax()."""
+    pooled = pooled_scores(q, sd, mask, temperature, pool_type, force_arg=force_arg)
+    w = attention_weights(pooled, att_func_type, force_support=force_support)
     f = w @ sd                                                  # :154
     if att_func_type == "sigmoid":
         f = f / w.sum(dim=-1, keepdim=True)                     # :156-157
@@ -161,7 +178,7 @@ def info_nce(logits_per_image, logits_per_text, rank=0):
 
 
 def step(ranks, temperature=1000.0, head="fdt", upstream=None, eps_img=1e-10, eps_txt=1e-10,
-         att_func_type="sparsemax", pool_type="max"):
+         att_func_type="sparsemax", pool_type="max", force=None):
     """Forward + backward of the hot path for W emulated ranks in one process.
 
     `ranks` is a list (length W) of dicts with leaf tensors:
@@ -179,11 +196,14 @@ def step(ranks, temperature=1000.0, head="fdt", upstream=None, eps_img=1e-10, ep
     upstream = upstream if upstream is not None else [1.0] * W
     inter = []
     xs_img, xs_txt = [], []
-    for r in ranks:
+    for ri, r in enumerate(ranks):
         d = {}
         if head == "fdt":
-            w_i, f_i, pooled_i = grounding(r["q_img"], r["sd"], None, temperature, att_func_type, pool_type)
-            w_t, f_t, pooled_t = grounding(r["q_txt"], r["sd"], r.get("mask"), temperature, att_func_type, pool_type)
+            fc = force[ri] if force is not None else {}   # test hook: discrete choices given (see sparsemax())
+            w_i, f_i, pooled_i = grounding(r["q_img"], r["sd"], None, temperature, att_func_type, pool_type,
+                                           fc.get("arg_img"), fc.get("supp_img"))
+            w_t, f_t, pooled_t = grounding(r["q_txt"], r["sd"], r.get("mask"), temperature, att_func_type, pool_type,
+                                           fc.get("arg_txt"), fc.get("supp_txt"))
             d.update(w_img=w_i, w_txt=w_t, f_img=f_i, f_txt=f_t, pooled_img=pooled_i, pooled_txt=pooled_t)
         else:
             f_i, f_t = r["f_img"], r["f_txt"]

@@ -6,12 +6,18 @@ compute modes.
 
 Gates (BASELINE.json north_star): fp32 mode <= 1e-5 relative on loss / logits / embeddings; bf16 mode <= 2e-2; integer
 outputs exact. Gradients in fp32 mode: <= 5e-5 -- 10x the distance between the REFERENCE'S OWN fp32 and fp64 runs on
-config 1 (2.7e-6 .. 4.6e-6, tests/golden/config1_reference_fp32_noise_floor.json). Max-pooling routes each (sample,
-code) gradient to ONE token: where the two best tokens tie to within rounding, any two fp32 evaluations (the reference's
-CPU matmul and cuBLAS included) may pick different tokens and the gradient ROWS involved differ by O(1) of their size
-(the reference's own fp32-vs-fp64 distance on the unrounded config-1 inputs is 2.9e-2 .. 5.7e-2 for exactly this
-reason, same JSON). Such ties are identified from the fp64 scores and the rows they touch are excluded from the
-max-norm check (their count is asserted small); everything else must meet the gate.
+config 1 (2.7e-6 .. 4.6e-6, tests/golden/config1_reference_fp32_noise_floor.json).
+
+The path has two DISCRETE choices per (sample, code): the token the max-pool picks and whether the code is in the
+sparsemax support. Outputs are continuous across both, GRADIENTS ARE NOT: the max-pool routes the whole gradient of a
+code to one token, and a code that sits at the sparsemax threshold to within rounding carries weight ~0 but a full-size
+coefficient g_k - mean_S(g) (and moves mean_S for the whole sample). Two correct evaluations that differ in one such bit
+differ in the gradient by O(1) of a row -- the reference's own fp32 run is 2.9e-2 .. 5.7e-2 away from its fp64 run on the
+unrounded config-1 inputs for exactly this reason (same JSON; one support bit). Parity of gradients is therefore
+stated ON THE SAME PIECE: (1) the implementation's discrete choices are compared with the free-running fp64 oracle and
+may differ only at rounding-ambiguous entries (top-2 token gap <= 4e-6 max|score|; |score - tau| <= 1e-6 max|pooled|),
+whose count is asserted tiny; (2) the fp64 oracle is then evaluated with those choices given
+(oracle.fdt_oracle.step(force=...)) and EVERY gradient row must meet the gate against it, nothing skipped.
 """
 import json
 import math
@@ -65,50 +71,57 @@ def _free():
     torch.cuda.empty_cache()
 
 
-def _tie_rows(q64, sd64, mask, w_ref, eps=TIE_EPS):
-    """(ambiguous dq rows [b,N] bool, ambiguous dsd rows [K] bool, count): (sample, code) pairs inside the support whose
-    two best token scores (after the reference's pad-zeroing, clip_fdt.py:125-130) are closer than eps * max|score|."""
+MARGIN_EPS = 1e-6         # relative (to max |pooled|) distance from the sparsemax threshold below which membership is ambiguous
+
+
+def _our_choices(ops, q, sd, mask, temp, mode):
+    """(arg [b,K] int64, pooled) exactly as GroundingFunction computes them (same kernels, same operands)."""
+    if mode == "bf16":
+        sd_k = ops.cast_bf16(sd.contiguous())
+        if mask is not None and ops.text_supported(q.shape[1]):
+            q_k, plan = ops.text_compact(q.contiguous(), mask)
+            pooled, arg = ops.ground_fwd_text(q_k, sd_k, plan, q.shape[1], temp)
+        else:
+            pooled, arg = ops.ground_fwd(ops.cast_bf16_rows(q.contiguous(), mask), sd_k, None, temp, "max")
+    else:
+        pooled, arg = ops.ground_fwd(q.contiguous(), sd.contiguous(), mask, temp, "max")
+    return arg.long(), pooled
+
+
+def _check_choices(q64, sd64, mask, temp, arg, w, w_ref, what, max_ambiguous=64):
+    """The implementation's argmax tokens (inside its support) and support set vs the free-running fp64 rule: every
+    disagreement must be rounding-ambiguous. Returns (#argmax disagreements, #support disagreements)."""
     b, N, D = q64.shape
-    K = sd64.shape[0]
-    rows = torch.zeros(b, N, dtype=torch.bool, device=q64.device)
-    codes = torch.zeros(K, dtype=torch.bool, device=q64.device)
-    n = 0
+    n_arg = 0
+    supp = w > 0
     for b0 in range(0, b, 64):
         s = torch.matmul(q64[b0:b0 + 64], sd64.t())
         if mask is not None:
             s = s * (mask[b0:b0 + 64] == 0).to(s.dtype).unsqueeze(-1)
-        top, idx = s.topk(2, dim=1)                                  # [c,2,K]
-        amb = ((top[:, 0] - top[:, 1]) <= eps * s.abs().max()) & (w_ref[b0:b0 + 64] > 0)
-        if amb.any():
-            bi, ki = amb.nonzero(as_tuple=True)
-            n += bi.numel()
-            rows[b0 + bi, idx[bi, 0, ki]] = True
-            rows[b0 + bi, idx[bi, 1, ki]] = True
-            codes[ki] = True
-    return rows, codes, n
-
-
-def _assert_rows_close(a, ref, skip_rows, tol, what, max_skip_frac=0.03):
-    """max-norm relative error over the rows not flagged rounding-ambiguous; the flagged fraction must be small."""
-    a = a.detach().double().reshape(-1, a.shape[-1])
-    ref = ref.detach().double().reshape(-1, ref.shape[-1]).to(a.device)
-    skip = skip_rows.reshape(-1)
-    frac = skip.float().mean().item()
-    assert frac <= max_skip_frac, "%s: %.2f%% of rows flagged as argmax ties" % (what, 100 * frac)
-    scale = max(ref.abs().max().item(), 1e-30)
-    err = ((a - ref).abs().amax(1))[~skip].max().item() / scale
-    assert err <= tol, "%s: relative error %.3e > %.1e over %d unambiguous rows (%d tie rows skipped)" % (
-        what, err, tol, int((~skip).sum()), int(skip.sum()))
-    return err
-
-
-def _support_mismatch(w, w_ref):
-    """number of support bits that differ, and the largest weight among them (a flip is legitimate only at weight ~ 0)"""
-    mism = (w > 0) != (w_ref.to(w.device) > 0)
-    if not mism.any():
-        return 0, 0.0
-    big = torch.maximum(w.double(), w_ref.to(w.device).double())[mism].max().item()
-    return int(mism.sum()), big
+        top, idx = s.topk(2, dim=1)
+        mis = (idx[:, 0] != arg[b0:b0 + 64]) & supp[b0:b0 + 64]
+        if mask is not None:     # every pad token scores exactly 0 (clip_fdt.py:125-130): which pad holds the max is immaterial
+            pad = mask[b0:b0 + 64] != 0
+            mis &= ~(torch.gather(pad, 1, arg[b0:b0 + 64]) & torch.gather(pad, 1, idx[:, 0]))
+        if mis.any():
+            gap = (top[:, 0] - top[:, 1])[mis]
+            picked_second = (idx[:, 1] == arg[b0:b0 + 64])[mis]
+            assert bool(picked_second.all()) and gap.max().item() <= TIE_EPS * s.abs().max().item(), \
+                "%s: argmax differs from the fp64 rule at a gap of %.3e (max|score| %.1f)" % (what, gap.max().item(), s.abs().max().item())
+            n_arg += int(mis.sum())
+    # support: tau of the free-running rule per row from any support entry: tau = pooled - w
+    pooled_ref = O.pooled_scores(q64, sd64, mask, temp, "max")
+    pooled_ref = pooled_ref - pooled_ref.max(1, keepdim=True)[0]
+    k_star = w_ref.argmax(1, keepdim=True)
+    tau = torch.gather(pooled_ref, 1, k_star) - torch.gather(w_ref, 1, k_star)
+    mis = supp != (w_ref > 0)
+    n_sup = int(mis.sum())
+    if n_sup:
+        margin = (pooled_ref - tau).abs()[mis].max().item()
+        assert margin <= MARGIN_EPS * pooled_ref.abs().max().item(), \
+            "%s: support differs at an entry %.3e from the threshold (max|pooled| %.3e)" % (what, margin, pooled_ref.abs().max().item())
+    assert n_arg + n_sup <= max_ambiguous, "%s: %d argmax + %d support disagreements" % (what, n_arg, n_sup)
+    return n_arg, n_sup
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -260,14 +273,15 @@ def test_whole_step_vs_fp64_oracle(ops, b, K, mode):
         for k in ("q_img", "q_txt", "sd"):
             inp[k] = bf16_round(inp[k])
     inp = {k: v.to(dev) for k, v in inp.items()}
-    ranks = [dict(q_img=O.make_leaf(inp["q_img"].double()), q_txt=O.make_leaf(inp["q_txt"].double()),
-                  mask=inp["mask"].double(), sd=O.make_leaf(inp["sd"].double()), p=O.make_leaf(inp["p"].double()))]
-    ref = O.step(ranks, temperature=temp)[0]
-    rows_i, codes_i, n_i = _tie_rows(ranks[0]["q_img"].detach(), ranks[0]["sd"].detach(), None, ref["w_img"])
-    rows_t, codes_t, n_t = _tie_rows(ranks[0]["q_txt"].detach(), ranks[0]["sd"].detach(), ranks[0]["mask"], ref["w_txt"])
-    del ranks
-    torch.cuda.empty_cache()
+    def oracle(force=None):
+        ranks = [dict(q_img=O.make_leaf(inp["q_img"].double()), q_txt=O.make_leaf(inp["q_txt"].double()),
+                      mask=inp["mask"].double(), sd=O.make_leaf(inp["sd"].double()), p=O.make_leaf(inp["p"].double()))]
+        out = O.step(ranks, temperature=temp, force=force)[0]
+        del ranks
+        torch.cuda.empty_cache()
+        return out
 
+    ref = oracle()                                   # free-running fp64 rule: values and discrete choices
     qi = inp["q_img"].clone().requires_grad_(True)
     qt = inp["q_txt"].clone().requires_grad_(True)
     sd = inp["sd"].clone().requires_grad_(True)
@@ -289,20 +303,22 @@ def test_whole_step_vs_fp64_oracle(ops, b, K, mode):
     e["f_img"] = assert_close(f_i, ref["f_img"], tol, "att_ft img")
     e["f_txt"] = assert_close(f_t, ref["f_txt"], tol, "att_ft txt")
     e["x_img"] = assert_close(x_i, ref["x_img"], tol, "normalised img")
-    from ilfdt import ops as _ops
     sc = s.detach().reshape(1).float().contiguous()
-    logits = _ops.logits(x_i.detach().contiguous(), x_t.detach().contiguous(), sc) if mode == "fp32" else \
-        _ops.logits(_ops.cast_bf16(x_i.detach().contiguous()), _ops.cast_bf16(x_t.detach().contiguous()), sc)
+    logits = ops.logits(x_i.detach().contiguous(), x_t.detach().contiguous(), sc) if mode == "fp32" else \
+        ops.logits(ops.cast_bf16(x_i.detach().contiguous()), ops.cast_bf16(x_t.detach().contiguous()), sc)
     e["logits"] = assert_close(logits, ref["logits_per_image"], tol, "logits_per_image")
-    for tag, w, wr in (("img", w_i, ref["w_img"]), ("txt", w_t, ref["w_txt"])):
-        nm, big = _support_mismatch(w.detach(), wr)
-        e["support_flips_" + tag] = nm
-        assert nm <= 16 and big <= 1e-7, "support (%s): %d entries differ, largest weight %.3e" % (tag, nm, big)
-    e["dq_img"] = _assert_rows_close(qi.grad, ref["d_q_img"], rows_i, gtol, "d q_img")
-    e["dq_txt"] = _assert_rows_close(qt.grad, ref["d_q_txt"], rows_t, gtol, "d q_txt")
-    e["dsd"] = _assert_rows_close(sd.grad, ref["d_sd"], codes_i | codes_t, gtol, "d space_dict", max_skip_frac=0.05)
+    # (1) discrete choices agree with the free-running rule except at rounding-ambiguous entries
+    arg_i, _ = _our_choices(ops, inp["q_img"], inp["sd"], None, temp, mode)
+    arg_t, _ = _our_choices(ops, inp["q_txt"], inp["sd"], inp["mask"], temp, mode)
+    q64i, q64t, sd64, m64 = inp["q_img"].double(), inp["q_txt"].double(), inp["sd"].double(), inp["mask"].double()
+    e["ambiguous_img"] = _check_choices(q64i, sd64, None, temp, arg_i, w_i.detach(), ref["w_img"], "img")
+    e["ambiguous_txt"] = _check_choices(q64t, sd64, m64, temp, arg_t, w_t.detach(), ref["w_txt"], "txt")
+    # (2) gradients against the fp64 oracle evaluated on the same piece: every row, nothing skipped
+    ref = oracle([dict(arg_img=arg_i, arg_txt=arg_t, supp_img=w_i.detach() > 0, supp_txt=w_t.detach() > 0)])
+    e["dq_img"] = assert_close(qi.grad, ref["d_q_img"], gtol, "d q_img")
+    e["dq_txt"] = assert_close(qt.grad, ref["d_q_txt"], gtol, "d q_txt")
+    e["dsd"] = assert_close(sd.grad, ref["d_sd"], gtol, "d space_dict")
     e["dp"] = assert_close(p.grad, ref["d_p"], 1e-4 if mode == "fp32" else tol, "d logit_scale")
-    e["ties"] = (n_i, n_t)
     # pad rows beyond the first pad never win the max: exactly zero gradient
     lens = (inp["mask"] == 0).sum(1)
     far = torch.arange(T, device=dev).view(1, -1) > lens.view(-1, 1)
@@ -491,34 +507,34 @@ def test_config5_grounding_vs_oracle_in_row_chunks(ops, need_weights):
     sdd = sd.clone().requires_grad_(True)
     w, f = Fn.GroundingFunction.apply(qd, sdd, None, temp, "bf16", need_weights)
     (f * up).sum().backward()
+    arg, _ = _our_choices(ops, q, sd, None, temp, "bf16")
     dsd64 = torch.zeros(K, D, dtype=torch.float64, device=dev)
     worst = dict(w=0.0, f=0.0, dq=0.0)
-    ties = flips = 0
-    tie_codes = torch.zeros(K, dtype=torch.bool, device=dev)
+    n_arg = n_sup = 0
     sd64 = sd.double()
     for b0 in range(0, b, 64):
-        qo = q[b0:b0 + 64].double().requires_grad_(True)
+        sl = slice(b0, b0 + 64)
+        with torch.no_grad():
+            w_ref, f_ref, _ = O.grounding(q[sl].double(), sd64, None, temp)          # free-running rule
+        worst["f"] = max(worst["f"], rel_err(f[sl], f_ref))
+        worst["w"] = max(worst["w"], rel_err(w[sl].float(), w_ref))
+        a_, s_ = _check_choices(q[sl].double(), sd64, None, temp, arg[sl], w[sl].float(), w_ref, "chunk %d" % b0,
+                                max_ambiguous=16)
+        n_arg += a_
+        n_sup += s_
+        qo = q[sl].double().requires_grad_(True)
         so = sd64.clone().requires_grad_(True)
-        w_ref, f_ref, _ = O.grounding(qo, so, None, temp)
-        (f_ref * up[b0:b0 + 64].double()).sum().backward()
-        rows, codes, n = _tie_rows(qo.detach(), sd64, None, w_ref.detach())
-        ties += n
-        tie_codes |= codes
+        _, f_same, _ = O.grounding(qo, so, None, temp, force_arg=arg[sl], force_support=w[sl] > 0)   # same piece
+        (f_same * up[sl].double()).sum().backward()
         dsd64 += so.grad
-        worst["f"] = max(worst["f"], rel_err(f[b0:b0 + 64], f_ref))
-        worst["w"] = max(worst["w"], rel_err(w[b0:b0 + 64].float(), w_ref))
-        worst["dq"] = max(worst["dq"], _assert_rows_close(qd.grad[b0:b0 + 64], qo.grad, rows, BF16_TOL, "dq chunk %d" % b0,
-                                                          max_skip_frac=0.05))
-        nm, big = _support_mismatch(w[b0:b0 + 64].float(), w_ref.detach())
-        flips += nm
-        assert big <= 1e-7, "support differs at weight %.3e" % big
-        del qo, so, w_ref, f_ref
+        worst["dq"] = max(worst["dq"], assert_close(qd.grad[sl], qo.grad, BF16_TOL, "dq chunk %d" % b0))
+        del qo, so, w_ref, f_ref, f_same
     assert worst["w"] <= BF16_TOL and worst["f"] <= BF16_TOL
-    e_dsd = _assert_rows_close(sdd.grad, dsd64, tie_codes, BF16_TOL, "d space_dict", max_skip_frac=0.05)
+    e_dsd = assert_close(sdd.grad, dsd64, BF16_TOL, "d space_dict")
     if not need_weights:
         assert w.dtype == torch.bfloat16
-    print("config5[need_weights=%s] w %.2e f %.2e dq %.2e dsd %.2e; %d argmax ties, %d support flips" % (
-        need_weights, worst["w"], worst["f"], worst["dq"], e_dsd, ties, flips))
+    print("config5[need_weights=%s] w %.2e f %.2e dq %.2e dsd %.2e; ambiguous: %d argmax, %d support bits of %d" % (
+        need_weights, worst["w"], worst["f"], worst["dq"], e_dsd, n_arg, n_sup, b * K))
 
 
 # ---------------------------------------------------------------------------------------------------

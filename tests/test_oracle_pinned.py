@@ -273,3 +273,31 @@ def test_reference_fp32_noise_floor_is_recorded(golden_dir):
     assert exact["loss"] < 1e-7 and exact["logits_per_image"] < 2e-6
     assert 1e-6 < max(exact["d_patch"], exact["d_word"], exact["d_space_dict"]) < 1e-5
     assert f["qmap"]["d_space_dict"] > 1e-3   # an argmax / support tie: O(1e-2) even for the reference itself
+
+
+def test_forced_discrete_choices_reproduce_the_free_running_oracle():
+    """The test hooks (force_arg / force_support: evaluate max-pool and sparsemax on GIVEN argmax tokens and support)
+    change nothing when handed the free-running rule's own choices -- values and gradients are identical -- and make
+    the discontinuity of the sparsemax Jacobian explicit: flipping ONE membership bit of weight ~0 moves the gradient
+    by O(1) of a coefficient although the output moves by ~0."""
+    inp = O.synth_inputs(6, 9, 11, 96, 32, seed=4)
+    def run(force=None):
+        r = [dict(q_img=O.make_leaf(inp["q_img"].double()), q_txt=O.make_leaf(inp["q_txt"].double()),
+                  mask=inp["mask"].double(), sd=O.make_leaf(inp["sd"].double()), p=O.make_leaf(inp["p"].double()))]
+        return O.step(r, temperature=10.0, force=force)[0]
+    free = run()
+    _, tok_i = O.pooled_scores(inp["q_img"].double(), inp["sd"].double(), None, 10.0, "max", True)
+    _, tok_t = O.pooled_scores(inp["q_txt"].double(), inp["sd"].double(), inp["mask"].double(), 10.0, "max", True)
+    force = [dict(arg_img=tok_i.argmax(1), arg_txt=tok_t.argmax(1), supp_img=free["w_img"] > 0, supp_txt=free["w_txt"] > 0)]
+    forced = run(force)
+    for k in ("loss", "w_img", "w_txt", "f_img", "d_q_img", "d_q_txt", "d_sd", "d_p"):
+        _close(forced[k].numpy(), free[k].numpy(), rtol=1e-12, atol=1e-15)
+    # flip the support entry with the smallest weight of sample 0: output barely moves, gradient moves a lot
+    w0 = free["w_img"][0]
+    k = int(torch.where(w0 > 0, w0, torch.full_like(w0, 9.0)).argmin())
+    supp = (free["w_img"] > 0).clone()
+    supp[0, k] = False
+    flipped = run([dict(force[0], supp_img=supp)])
+    dw = (flipped["w_img"] - free["w_img"]).abs().max().item()
+    dg = (flipped["d_q_img"][0] - free["d_q_img"][0]).abs().max().item() / free["d_q_img"][0].abs().max().item()
+    assert dg > 0.1 and dg > 5 * dw / w0.max().item(), (dw, dg)   # 44 % of the gradient for 3.5 % of a weight
