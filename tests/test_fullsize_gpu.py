@@ -5,8 +5,9 @@ configs 1 / 3 / 3b / 5 and the 32768-row InfoNCE take seconds. Reference-generat
 compute modes.
 
 Gates (BASELINE.json north_star): fp32 mode <= 1e-5 relative on loss / logits / embeddings; bf16 mode <= 2e-2; integer
-outputs exact. Gradients in fp32 mode: <= 5e-5 -- 10x the distance between the REFERENCE'S OWN fp32 and fp64 runs on
-config 1 (2.7e-6 .. 4.6e-6, tests/golden/config1_reference_fp32_noise_floor.json).
+outputs exact. Gradients in fp32 mode: <= 1e-5 as well (measured ~2e-6, i.e. at the distance between the REFERENCE'S
+OWN fp32 and fp64 runs on config 1: 2.7e-6 .. 4.6e-6, tests/golden/config1_reference_fp32_noise_floor.json); the one
+wider gate is 2e-5 on the InfoNCE gradient at B = 32768, a sum of 32768 fp32 products per element (measured 1.04e-5).
 
 The path has two DISCRETE choices per (sample, code): the token the max-pool picks and whether the code is in the
 sparsemax support. Outputs are continuous across both, GRADIENTS ARE NOT: the max-pool routes the whole gradient of a
@@ -32,7 +33,7 @@ pytestmark = pytest.mark.gpu
 from oracle import fdt_oracle as O  # noqa: E402
 
 FP32_TOL = 1e-5
-FP32_GRAD_TOL = 5e-5
+FP32_GRAD_TOL = 1e-5       # on the same piece (see the module docstring); measured 2e-6 at b = 256, K = 16384
 BF16_TOL = 2e-2
 TIE_EPS = 4e-6            # relative (to max |score|) top-2 token gap below which the argmax is rounding-ambiguous
 
@@ -222,7 +223,7 @@ def test_config1_reference_golden(ops, golden_dir, variant, mode):
         # gradients. Projections (16 random +-1 combinations of all rows) see every row and are robust to the handful of
         # argmax ties; one whole sample and 64 codebook rows are compared entry by entry with a gate tied to the
         # reference's own fp32-vs-fp64 distance on those very rows.
-        gtol = FP32_GRAD_TOL if mode == "fp32" else BF16_TOL
+        gtol = 5e-5 if mode == "fp32" else BF16_TOL     # free-running golden: 10x the reference's own fp32 noise floor
         ptol = 1e-4 if mode == "fp32" else BF16_TOL
         d_sd = m.space_dict.grad
         for name, g_ in (("patch", patch.grad), ("word", word.grad), ("space_dict", d_sd)):
@@ -232,6 +233,12 @@ def test_config1_reference_golden(ops, golden_dir, variant, mode):
             # inputs, ~1e-3 on the unrounded ones, where a single argmax tie moves one gradient row (see module docstring)
             ref_floor = ((p32 - p64).abs().max() / p64.abs().max()).item()
             gate = max(ptol, 3 * ref_floor)
+            if variant == "qmap":
+                # unrounded inputs: the golden cannot be evaluated on our piece, and each of the (<= 8, asserted above)
+                # rounding-level membership / argmax bits that differ moves a projection by ~2e-3 (one row of ~3000 with
+                # random signs) -- the reference's own fp32 run shows 7.8e-4 .. 1.4e-3 here from ONE bit. Strict gradient
+                # parity is asserted on the bf16-exact variant and in the same-piece tests below.
+                gate = max(gate, BF16_TOL)
             report["f64_proj_" + name] = assert_close(ours, p64, gate, "proj d_%s vs the fp64 run (reference fp32-vs-fp64: %.1e)" % (name, ref_floor))
             report["f32_proj_" + name] = assert_close(ours, p32, gate + ref_floor, "proj d_%s vs the fp32 run" % name)
             report["ref_floor_proj_" + name] = ref_floor
@@ -239,6 +246,8 @@ def test_config1_reference_golden(ops, golden_dir, variant, mode):
             r32, r64 = T("f32_d_%s_rows" % name).double(), T("f64_d_%s_rows" % name).double()
             ref_floor = ((r32 - r64).abs().max() / r64.abs().max()).item()
             gate = max(gtol, 10 * ref_floor)
+            if variant == "qmap":
+                gate = max(gate, BF16_TOL)
             report["rows_" + name] = assert_close(g_, r64, gate, "d_%s rows (reference fp32-vs-fp64 on them: %.1e)" % (name, ref_floor))
         report["d_logit_scale"] = assert_close(m.logit_scale.grad, T("f64_d_logit_scale"), 1e-4 if mode == "fp32" else tol,
                                                "d logit_scale")
@@ -318,7 +327,7 @@ def test_whole_step_vs_fp64_oracle(ops, b, K, mode):
     e["dq_img"] = assert_close(qi.grad, ref["d_q_img"], gtol, "d q_img")
     e["dq_txt"] = assert_close(qt.grad, ref["d_q_txt"], gtol, "d q_txt")
     e["dsd"] = assert_close(sd.grad, ref["d_sd"], gtol, "d space_dict")
-    e["dp"] = assert_close(p.grad, ref["d_p"], 1e-4 if mode == "fp32" else tol, "d logit_scale")
+    e["dp"] = assert_close(p.grad, ref["d_p"], FP32_TOL if mode == "fp32" else tol, "d logit_scale")
     # pad rows beyond the first pad never win the max: exactly zero gradient
     lens = (inp["mask"] == 0).sum(1)
     far = torch.arange(T, device=dev).view(1, -1) > lens.view(-1, 1)
@@ -474,9 +483,9 @@ def test_infonce_rank_of_eight_at_32k(ops, mode):
              lse_i=assert_close(lse_i_all, lse_row, tol, "row lse, logits_per_image, all ranks"),
              lse_t=assert_close(lse_t_all, lse_col, tol, "row lse, logits_per_text, all ranks"),
              logits=assert_close(stored, (xi[r * b:(r + 1) * b].double() @ xt.double().t()) * scale.double(), tol, "logits"),
-             dx_img=assert_close(dx_i, dXi[r * b:(r + 1) * b], FP32_GRAD_TOL if mode == "fp32" else tol, "dx_img (gathered form)"),
-             dx_txt=assert_close(dx_t, dXt[r * b:(r + 1) * b], FP32_GRAD_TOL if mode == "fp32" else tol, "dx_txt (gathered form)"),
-             dscale=assert_close(dscale, ds_local, 1e-4 if mode == "fp32" else tol, "d scale (rank-local)"))
+             dx_img=assert_close(dx_i, dXi[r * b:(r + 1) * b], 2e-5 if mode == "fp32" else tol, "dx_img (gathered form)"),
+             dx_txt=assert_close(dx_t, dXt[r * b:(r + 1) * b], 2e-5 if mode == "fp32" else tol, "dx_txt (gathered form)"),
+             dscale=assert_close(dscale, ds_local, FP32_TOL if mode == "fp32" else tol, "d scale (rank-local)"))
     c = counts.cpu().tolist()
     assert c == counts_stored.cpu().tolist(), "fused top-k counts != counts on the stored logits"
     assert 0 < c[0] < b and c[0] <= c[1]
