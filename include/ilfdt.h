@@ -61,7 +61,9 @@ enum {
   ILFDT_TUNE_GROUND_2CTA = 3,    /* ilfdt_ground_fwd*: 1 (default) = cta_group::2 kernel, 0 = single-CTA kernel */
   ILFDT_TUNE_GEMM_WIDE2 = 4,     /* ilfdt_gemm_nt: 1 (default) = CTA-pair kernel for short-operand / long-reduction shapes */
   ILFDT_TUNE_NCE_2CTA = 5,       /* ilfdt_nce_bwd*: 1 (default) = cta_group::2 kernel */
-  ILFDT_TUNE_COUNT_ = 6
+  ILFDT_TUNE_SPARSE_BWD_NNZ = 6, /* ilfdt_ground_bwd*: mean support (codes per row) up to which the sparse-regime kernel
+                                    serves the launch (default 128; 0 = always the dense sweeps) */
+  ILFDT_TUNE_COUNT_ = 7
 };
 int32_t ilfdt_tune_set(int32_t key, int64_t value);
 int64_t ilfdt_tune_get(int32_t key);
@@ -151,7 +153,7 @@ int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs,
                                void* stream);
 
 /* ---- a13: backward of the score block through max-pool + sparsemax ------------------------- */
-/* Inputs: g [b,K] = dLoss/dw (f32, OVERWRITTEN with coef), w [b,K], arg [b,K], q, sd, mask as in
+/* Inputs: g [b,K] = dLoss/dw (f32, scratch: OVERWRITTEN), w [b,K], arg [b,K], q, sd, mask as in
  * ilfdt_ground_fwd.  coef[b,k] = nz*(g - mean_nz g) * keep[b,arg] / (sqrt_d*temperature);
  * dq[b,arg[b,k],:] += coef*sd[k,:]  (dq [b,n_tok,D], dq_dtype F32 or BF16 = the dtype q had at the caller,
  * fully written);
@@ -160,19 +162,23 @@ int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs,
  * w == NULL: g already holds dLoss/dpooled (softmax / sigmoid attention): no support, no mean to
  * subtract, every non-zero entry is scattered.
  * q_row_base: NULL when q is the full [b,n_tok,D] operand; else row_base[b] of ilfdt_text_compact's plan
- * (q is then the compacted text operand: token t of sample s lives in row q_row_base[s] + t). */
+ * (q is then the compacted text operand: token t of sample s lives in row q_row_base[s] + t).
+ * nnz (optional, NULL = off): nnz[b] from ilfdt_sparsemax_fwd, with regime_ws = one int32 of device scratch. When the
+ * MEAN support is at most ILFDT_TUNE_SPARSE_BWD_NNZ codes per row (trained, peaked attention) the launch is served by a
+ * per-sample kernel that touches only the support instead of the two dense sweeps over [b,K]; the decision is taken on
+ * the device (no host synchronisation, CUDA-graph safe), results agree up to fp32 summation order. */
 int32_t ilfdt_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd,
-                         int32_t dtype, const float* mask, const int32_t* q_row_base, int64_t b, int64_t n_tok,
-                         int64_t K, int64_t D, float sqrt_d, float temperature,
-                         void* dq, int32_t dq_dtype, float* dsd, void* stream);
+                         int32_t dtype, const float* mask, const int32_t* q_row_base, const int32_t* nnz,
+                         int32_t* regime_ws, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
+                         float temperature, void* dq, int32_t dq_dtype, float* dsd, void* stream);
 /* Same, with the support taken from the bf16 copy of the weights that ilfdt_sparsemax_fwd writes for the
  * tensor-core pooling GEMM (w_bf16 [b,K], > 0 exactly where the fp32 weights are): half the bytes read, and
  * a caller that discards att_weight (Clip_FDT.forward, clip_fdt.py:233-234) need not have the fp32 copy
- * written at all. Needs D in {256,512,768,1024}, n_tok <= 96, K % 4 == 0 (ILFDT_E_UNSUPPORTED_SHAPE otherwise). */
+ * written at all. Needs D in {256,512,768,1024}, n_tok <= 256, K % 4 == 0 (ILFDT_E_UNSUPPORTED_SHAPE otherwise). */
 int32_t ilfdt_ground_bwd_w16(float* g, const void* w_bf16, const int16_t* arg, const void* q, const void* sd,
-                             int32_t dtype, const float* mask, const int32_t* q_row_base, int64_t b, int64_t n_tok,
-                             int64_t K, int64_t D, float sqrt_d, float temperature,
-                             void* dq, int32_t dq_dtype, float* dsd, void* stream);
+                             int32_t dtype, const float* mask, const int32_t* q_row_base, const int32_t* nnz,
+                             int32_t* regime_ws, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
+                             float temperature, void* dq, int32_t dq_dtype, float* dsd, void* stream);
 
 /* ---- non-default Query_model variants, clip_fdt.py:67-78,140-157 ----------------------------------- */
 enum { ILFDT_ATT_SOFTMAX = 1, ILFDT_ATT_SIGMOID = 2 };

@@ -7,7 +7,7 @@
 namespace ilfdt {
 
 // tuning knobs: explicit API state instead of environment variables read into statics (defaults = the tuned values)
-static std::atomic<int64_t> g_tune[ILFDT_TUNE_COUNT_] = {{1024}, {32}, {1}, {1}, {1}, {1}};
+static std::atomic<int64_t> g_tune[ILFDT_TUNE_COUNT_] = {{1024}, {32}, {1}, {1}, {1}, {1}, {128}};
 int64_t tune_get(int key) { return (key >= 0 && key < ILFDT_TUNE_COUNT_) ? g_tune[key].load(std::memory_order_relaxed) : 0; }
 
 int sm_count() {
@@ -324,29 +324,30 @@ int32_t ilfdt_gemm_f32_strided(const float* A, int64_t a_rs, int64_t a_cs, const
 }
 
 int32_t ilfdt_ground_bwd(float* g, const float* w, const int16_t* arg, const void* q, const void* sd, int32_t dtype,
-                         const float* mask, const int32_t* q_row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D,
-                         float sqrt_d, float temperature, void* dq, int32_t dq_dtype, float* dsd, void* stream) {
+                         const float* mask, const int32_t* q_row_base, const int32_t* nnz, int32_t* regime_ws, int64_t b,
+                         int64_t n_tok, int64_t K, int64_t D, float sqrt_d, float temperature, void* dq, int32_t dq_dtype,
+                         float* dsd, void* stream) {
   ARCH_GUARD();
   DTYPE_GUARD(dtype);
   DTYPE_GUARD(dq_dtype);
   ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && K >= 1 && D >= 1, ILFDT_E_INVALID_ARG, "ground_bwd: bad shape");
   ILFDT_REQUIRE(b == 0 || (g && arg && q && sd && dq && dsd), ILFDT_E_INVALID_ARG, "ground_bwd: null pointer");
-  return launch_ground_bwd(g, w, ILFDT_F32, arg, q, sd, dtype, mask, q_row_base, b, n_tok, K, D, sqrt_d, temperature, dq,
-                           dq_dtype, dsd, ST(stream));
+  return launch_ground_bwd(g, w, ILFDT_F32, arg, q, sd, dtype, mask, q_row_base, nnz, regime_ws, b, n_tok, K, D, sqrt_d,
+                           temperature, dq, dq_dtype, dsd, ST(stream));
 }
 
 int32_t ilfdt_ground_bwd_w16(float* g, const void* w_bf16, const int16_t* arg, const void* q, const void* sd,
-                             int32_t dtype, const float* mask, const int32_t* q_row_base, int64_t b, int64_t n_tok,
-                             int64_t K, int64_t D, float sqrt_d, float temperature, void* dq, int32_t dq_dtype,
-                             float* dsd, void* stream) {
+                             int32_t dtype, const float* mask, const int32_t* q_row_base, const int32_t* nnz,
+                             int32_t* regime_ws, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
+                             float temperature, void* dq, int32_t dq_dtype, float* dsd, void* stream) {
   ARCH_GUARD();
   DTYPE_GUARD(dtype);
   DTYPE_GUARD(dq_dtype);
   ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && K >= 1 && D >= 1, ILFDT_E_INVALID_ARG, "ground_bwd_w16: bad shape");
   ILFDT_REQUIRE(b == 0 || (g && w_bf16 && arg && q && sd && dq && dsd), ILFDT_E_INVALID_ARG,
                 "ground_bwd_w16: null pointer");
-  return launch_ground_bwd(g, w_bf16, ILFDT_BF16, arg, q, sd, dtype, mask, q_row_base, b, n_tok, K, D, sqrt_d, temperature,
-                           dq, dq_dtype, dsd, ST(stream));
+  return launch_ground_bwd(g, w_bf16, ILFDT_BF16, arg, q, sd, dtype, mask, q_row_base, nnz, regime_ws, b, n_tok, K, D, sqrt_d,
+                           temperature, dq, dq_dtype, dsd, ST(stream));
 }
 
 int32_t ilfdt_att_fwd(const float* z, int64_t rows, int64_t K, int32_t kind, float* w, float* rowsum, void* stream) {

@@ -563,9 +563,10 @@ template <typename T, int NV, typename TO, typename TW>
 __global__ void __launch_bounds__(G3_THREADS, 3)
 ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const int16_t* __restrict__ arg,
                         const T* __restrict__ sd, const float* __restrict__ mask, int n_tok, int K, int D,
-                        float inv_scale, TO* __restrict__ dq, int keep_rows) {
+                        float inv_scale, TO* __restrict__ dq, const int* __restrict__ sparse_flag) {
   extern __shared__ __align__(16) unsigned char gb_smem[];
-  const uint64_t row_pol = l2_policy(keep_rows != 0);
+  if (sparse_flag != nullptr && *sparse_flag != 0) return;   // the sparse-regime kernel handles this launch
+  const uint64_t row_pol = l2_policy(false);
   uint16_t* hist = reinterpret_cast<uint16_t*>(gb_smem);                                    // [n_tok][256]
   uint16_t* sorted_k = reinterpret_cast<uint16_t*>(gb_smem + (size_t)n_tok * G3_THREADS * 2);  // [G3_CHUNK]
   int* base = reinterpret_cast<int*>(sorted_k + G3_CHUNK);                                  // [n_tok + 1]
@@ -773,7 +774,9 @@ template <typename T, int NV, int WARPS, int CPW, int U, int TS = 32>
 __global__ void __launch_bounds__(WARPS * 32)
 ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restrict__ arg, const T* __restrict__ q,
                          const int* __restrict__ row_base, int64_t b_total, int n_tok, int K, int D,
-                         int64_t b_per_split, int use_atomic, float* __restrict__ dsd) {
+                         int64_t b_per_split, int use_atomic, float* __restrict__ dsd,
+                         const int* __restrict__ sparse_flag) {
+  if (sparse_flag != nullptr && *sparse_flag != 0) return;   // the sparse-regime kernel handles this launch
   // TS samples per cooperative tile (one CTA barrier per tile). A/B on one box: TS = 32 is ~2 ms per step faster at the
   // dense random-init statistics (the headline), TS = 128 is 3 ms faster when the support is a few tens of codes and
   // the kernel is a pure scan of coef / arg (ILFDT_DSD_CFG=128)
@@ -913,9 +916,140 @@ ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restri
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Sparse regime (trained, peaked attention: a support of tens of codes per row instead of ~0.2 K). The two kernels above
+// are dense SCANS of three [b,K] arrays (coef written and re-read, w, arg) that find ~0.1 % useful entries: 13 ms per
+// step at the headline shape for ~23 entries per row. Here one CTA per sample scans only the bf16 / fp32 weights of its
+// row (the support), and for each of its few entries does both updates itself:
+//     dq[b, arg, :] += coef * sd[k, :]   into a shared-memory copy of the sample's [n_tok, D] gradient block
+//     dsd[k, :]     += coef * q[b, arg, :]   with 16-byte vector reductions to global memory
+// No coef array, no second sweep. Which regime a launch is in is decided ON THE DEVICE (gb_regime_kernel: mean support
+// from the forward's nnz[b]) -- no host synchronisation, CUDA-graph safe: both code paths are enqueued and the one that
+// does not apply returns at once. fp32 sums are taken in arrival order (shared / global reductions).
+// ---------------------------------------------------------------------------------------------
+constexpr int GSP_THREADS = 256, GSP_WARPS = GSP_THREADS / 32;
+
+__global__ void __launch_bounds__(256) gb_regime_kernel(const int* __restrict__ nnz, int64_t b, int64_t max_total,
+                                                        int* __restrict__ flag) {
+  __shared__ long long sm[8];
+  long long s = 0;
+  for (int64_t i = threadIdx.x; i < b; i += 256) s += nnz[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long t = 0;
+    for (int w = 0; w < 8; ++w) t += sm[w];
+    flag[0] = (t <= max_total) ? 1 : 0;
+  }
+}
+
+template <typename T, int NV, typename TO, typename TW>
+__global__ void __launch_bounds__(GSP_THREADS)
+ground_bwd_sparse_kernel(const float* __restrict__ g, const TW* __restrict__ w, const int16_t* __restrict__ arg,
+                         const T* __restrict__ q, const T* __restrict__ sd, const float* __restrict__ mask,
+                         const int* __restrict__ row_base, const int* __restrict__ sparse_flag, int n_tok, int K, int D,
+                         float inv_scale, TO* __restrict__ dq, float* __restrict__ dsd) {
+  if (*sparse_flag == 0) return;
+  extern __shared__ __align__(16) float gsp_acc[];   // [n_tok][D]
+  __shared__ double red_s[GSP_WARPS];
+  __shared__ int red_c[GSP_WARPS];
+  const int64_t b = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const float* gr = g + b * K;
+  const TW* wr = w + b * K;
+  const int16_t* ar = arg + b * K;
+  for (int i = tid * 4; i < n_tok * D; i += GSP_THREADS * 4) *reinterpret_cast<float4*>(gsp_acc + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+  // pass 1: mean of g over the support
+  double s = 0.0;
+  int c = 0;
+  for (int i = tid * 4; i < K; i += GSP_THREADS * 4) {
+    uint32_t m = Support4<TW>::ld(wr + i);
+    while (m) {
+      const int j = __ffs(m) - 1;
+      m &= m - 1;
+      s += (double)gr[i + j];
+      ++c;
+    }
+  }
+  s = warp_sum(s);
+  c = warp_sum(c);
+  if (lane == 0) { red_s[warp] = s; red_c[warp] = c; }
+  __syncthreads();
+  s = 0.0; c = 0;
+#pragma unroll
+  for (int i = 0; i < GSP_WARPS; ++i) { s += red_s[i]; c += red_c[i]; }
+  const float mean = c > 0 ? (float)(s / (double)c) : 0.f;
+  const int64_t qbase = row_base ? (int64_t)row_base[b] : b * n_tok;
+  // pass 2: a warp scans 128 codes at a time; every hit is processed by the whole warp (lane = 8 columns per 256)
+  for (int i0 = warp * 128; i0 < K; i0 += GSP_WARPS * 128) {
+    const int i = i0 + lane * 4;
+    const uint32_t m = (i < K) ? Support4<TW>::ld(wr + i) : 0u;   // second read of the row: L1 / L2 hit
+    unsigned any = __ballot_sync(0xffffffffu, m != 0u);
+    while (any) {
+      const int src = __ffs(any) - 1;
+      any &= any - 1;
+      uint32_t mm = __shfl_sync(0xffffffffu, m, src);
+      while (mm) {
+        const int j = __ffs(mm) - 1;
+        mm &= mm - 1;
+        const int k = i0 + src * 4 + j;
+        const int t = ar[k];
+        const float keep = (mask == nullptr || mask[b * n_tok + t] == 0.f) ? 1.f : 0.f;
+        const float cf = (gr[k] - mean) * keep * inv_scale;
+        if (cf == 0.f) continue;
+        const T* srow = sd + (int64_t)k * D;
+        const T* qrow = q + (qbase + t) * (int64_t)D;
+        float* arow = gsp_acc + t * D;
+        float* drow = dsd + (int64_t)k * D;
+#pragma unroll
+        for (int u = 0; u < NV; ++u) {
+          float vs[8], vq[8];
+          Load8<T>::ld(srow + (u * 32 + lane) * 8, vs);
+          Load8<T>::ld(qrow + (u * 32 + lane) * 8, vq);
+          float* a = arow + (u * 32 + lane) * 8;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) atomicAdd(a + e, cf * vs[e]);
+          float* o = drow + (u * 32 + lane) * 8;
+          asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o), "f"(cf * vq[0]), "f"(cf * vq[1]),
+                       "f"(cf * vq[2]), "f"(cf * vq[3]) : "memory");
+          asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o + 4), "f"(cf * vq[4]), "f"(cf * vq[5]),
+                       "f"(cf * vq[6]), "f"(cf * vq[7]) : "memory");
+        }
+      }
+    }
+  }
+  __syncthreads();
+  for (int t = warp; t < n_tok; t += GSP_WARPS) {
+    TO* out = dq + (b * n_tok + t) * (int64_t)D;
+#pragma unroll
+    for (int u = 0; u < NV; ++u) {
+      float a[8];
+      const float4 x = *reinterpret_cast<const float4*>(gsp_acc + t * D + (u * 32 + lane) * 8);
+      const float4 y = *reinterpret_cast<const float4*>(gsp_acc + t * D + (u * 32 + lane) * 8 + 4);
+      a[0] = x.x; a[1] = x.y; a[2] = x.z; a[3] = x.w; a[4] = y.x; a[5] = y.y; a[6] = y.z; a[7] = y.w;
+      StoreRow8<TO>::st(out + (u * 32 + lane) * 8, a, false);
+    }
+  }
+}
+
+template <typename T, int NV, typename TO, typename TW>
+static int32_t launch_sparse(const float* g, const TW* w, const int16_t* arg, const T* q, const T* sd, const float* mask,
+                             const int* row_base, const int* flag, int64_t b, int64_t n_tok, int64_t K, int64_t D,
+                             float inv_scale, TO* dq, float* dsd, cudaStream_t st) {
+  const size_t smem = (size_t)n_tok * D * sizeof(float);
+  ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_sparse_kernel<T, NV, TO, TW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem));
+  ground_bwd_sparse_kernel<T, NV, TO, TW><<<(unsigned)b, GSP_THREADS, smem, st>>>(g, w, arg, q, sd, mask, row_base, flag,
+                                                                             (int)n_tok, (int)K, (int)D, inv_scale, dq, dsd);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
 template <typename T, int NV, int WARPS, int CPW, int U, int TS = 32>
 static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, const int* row_base, int64_t b, int64_t n_tok,
-                             int64_t K, int64_t D, float* dsd, cudaStream_t st) {
+                             int64_t K, int64_t D, float* dsd, const int* sparse_flag, cudaStream_t st) {
   constexpr int CODES = WARPS * CPW;
   const int64_t groups = K / CODES;
   int64_t nsplit = 1;
@@ -934,30 +1068,34 @@ static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, con
   nsplit = cdiv(b, per);
   dim3 grid((unsigned)groups, (unsigned)nsplit);
   ground_bwd_dsd_v3_kernel<T, NV, WARPS, CPW, U, TS><<<grid, WARPS * 32, 0, st>>>(g, arg, q, row_base, b, (int)n_tok, (int)K,
-                                                                             (int)D, per, (nsplit > 1 ? 1 : 0) | stream_flag, dsd);
+                                                                             (int)D, per, (nsplit > 1 ? 1 : 0) | stream_flag, dsd,
+                                                                             sparse_flag);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }
 
 template <typename T, int NV, typename TO, typename TW>
 static int32_t launch_dq_v3(float* g, const TW* w, const int16_t* arg, const T* sd, const float* mask, int64_t b,
-                            int64_t n_tok, int64_t K, int64_t D, float inv_scale, TO* dq, cudaStream_t st) {
+                            int64_t n_tok, int64_t K, int64_t D, float inv_scale, TO* dq, const int* sparse_flag,
+                            cudaStream_t st) {
   const size_t smem = (size_t)n_tok * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 + (G3_MAX_TOK + 1) * sizeof(int) +
                       G3_MAX_TOK * sizeof(float);
   ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_v3_kernel<T, NV, TO, TW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)((size_t)G3_MAX_TOK * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 +
                                            (G3_MAX_TOK + 1) * sizeof(int) + G3_MAX_TOK * sizeof(float))));
   ground_bwd_dq_v3_kernel<T, NV, TO, TW><<<(unsigned)b, G3_THREADS, smem, st>>>(g, w, arg, sd, mask, (int)n_tok, (int)K,
-                                                                           (int)D, inv_scale, dq, 0);
+                                                                           (int)D, inv_scale, dq, sparse_flag);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }
 
 template <typename T, int NV>
 static int32_t launch_ground_bwd_t(float* g, const void* w_v, int w_dtype, const int16_t* arg, const T* q, const T* sd,
-                                   const float* mask, const int* row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D,
-                                   float inv_scale, void* dq_v, int dq_dtype, float* dsd, cudaStream_t st) {
+                                   const float* mask, const int* row_base, const int* nnz, int* regime_ws, int64_t b,
+                                   int64_t n_tok, int64_t K, int64_t D, float inv_scale, void* dq_v, int dq_dtype, float* dsd,
+                                   cudaStream_t st) {
   bool done = false;
+  const int* flag = nullptr;   // device flag: 1 = this launch is handled by the sparse-regime kernel
   float* dq = reinterpret_cast<float*>(dq_v);
   // the support comes from the fp32 weights or (scatter kernel v3 only) from their bf16 copy
   const float* w = w_dtype == ILFDT_F32 ? reinterpret_cast<const float*>(w_v) : nullptr;
@@ -966,18 +1104,41 @@ static int32_t launch_ground_bwd_t(float* g, const void* w_v, int w_dtype, const
     const bool v3_ok = n_tok <= G3_MAX_TOK && K % 4 == 0 &&
                        ((reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(w)) & 15) == 0 &&
                        ((reinterpret_cast<uintptr_t>(arg) | reinterpret_cast<uintptr_t>(w16)) & 7) == 0;
+    // sparse regime (device-side decision, see ground_bwd_sparse_kernel): needs the forward's nnz[b], one int of scratch,
+    // the shapes both v3 kernels take, and a [n_tok, D] fp32 block that fits shared memory
+    const int64_t sparse_nnz = tune_get(ILFDT_TUNE_SPARSE_BWD_NNZ);
+    if constexpr (NV <= 2) {
+      const bool dsd_v3_ok = K % 32 == 0 && ((reinterpret_cast<uintptr_t>(g) & 15) | (reinterpret_cast<uintptr_t>(arg) & 7)) == 0;
+      if (v3_ok && dsd_v3_ok && !done && nnz != nullptr && regime_ws != nullptr && sparse_nnz > 0 &&
+          (w != nullptr || w16 != nullptr) && n_tok * D * 4 <= 200 * 1024) {
+        gb_regime_kernel<<<1, 256, 0, st>>>(nnz, b, sparse_nnz * b, regime_ws);
+        ILFDT_LAUNCH_OK();
+        flag = regime_ws;
+        int32_t rc;
+        __nv_bfloat16* dq16 = reinterpret_cast<__nv_bfloat16*>(dq_v);
+        if (w16 != nullptr)
+          rc = dq_dtype == ILFDT_BF16
+                   ? launch_sparse<T, NV, __nv_bfloat16, __nv_bfloat16>(g, w16, arg, q, sd, mask, row_base, flag, b, n_tok, K, D, inv_scale, dq16, dsd, st)
+                   : launch_sparse<T, NV, float, __nv_bfloat16>(g, w16, arg, q, sd, mask, row_base, flag, b, n_tok, K, D, inv_scale, dq, dsd, st);
+        else
+          rc = dq_dtype == ILFDT_BF16
+                   ? launch_sparse<T, NV, __nv_bfloat16, float>(g, w, arg, q, sd, mask, row_base, flag, b, n_tok, K, D, inv_scale, dq16, dsd, st)
+                   : launch_sparse<T, NV, float, float>(g, w, arg, q, sd, mask, row_base, flag, b, n_tok, K, D, inv_scale, dq, dsd, st);
+        if (rc != ILFDT_OK) return rc;
+      }
+    }
     if (v3_ok && !done) {
       int32_t rc;
       if (w16 != nullptr)
         rc = dq_dtype == ILFDT_BF16
                  ? launch_dq_v3<T, NV, __nv_bfloat16, __nv_bfloat16>(g, w16, arg, sd, mask, b, n_tok, K, D, inv_scale,
-                                                                     reinterpret_cast<__nv_bfloat16*>(dq_v), st)
-                 : launch_dq_v3<T, NV, float, __nv_bfloat16>(g, w16, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, st);
+                                                                     reinterpret_cast<__nv_bfloat16*>(dq_v), flag, st)
+                 : launch_dq_v3<T, NV, float, __nv_bfloat16>(g, w16, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, flag, st);
       else
         rc = dq_dtype == ILFDT_BF16
                  ? launch_dq_v3<T, NV, __nv_bfloat16, float>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale,
-                                                             reinterpret_cast<__nv_bfloat16*>(dq_v), st)
-                 : launch_dq_v3<T, NV, float, float>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, st);
+                                                             reinterpret_cast<__nv_bfloat16*>(dq_v), flag, st)
+                 : launch_dq_v3<T, NV, float, float>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, flag, st);
       if (rc != ILFDT_OK) return rc;
       done = true;
     }
@@ -1025,10 +1186,10 @@ static int32_t launch_ground_bwd_t(float* g, const void* w_v, int w_dtype, const
     if (K % 32 == 0 && ((reinterpret_cast<uintptr_t>(g) & 15) | (reinterpret_cast<uintptr_t>(arg) & 7)) == 0) {
       if constexpr (NV <= 2) {
         if (tune_get(ILFDT_TUNE_DSD_TILE) == 128)
-          return launch_dsd_v3<T, NV, 4, 1, 4, 128>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
-        return launch_dsd_v3<T, NV, 4, 1, 4, 32>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
+          return launch_dsd_v3<T, NV, 4, 1, 4, 128>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
+        return launch_dsd_v3<T, NV, 4, 1, 4, 32>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
       } else {
-        return launch_dsd_v3<T, NV, 4, 1, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, st);
+        return launch_dsd_v3<T, NV, 4, 1, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
       }
     }
   }
@@ -1051,31 +1212,32 @@ static int32_t launch_ground_bwd_t(float* g, const void* w_v, int w_dtype, const
 
 template <typename T>
 static int32_t dispatch_nv(float* g, const void* w, int w_dtype, const int16_t* arg, const T* q, const T* sd, const float* mask,
-                           const int* row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D, float inv_scale, void* dq, int dq_dtype,
-                           float* dsd, cudaStream_t st) {
+                           const int* row_base, const int* nnz, int* regime_ws, int64_t b, int64_t n_tok, int64_t K, int64_t D,
+                           float inv_scale, void* dq, int dq_dtype, float* dsd, cudaStream_t st) {
   const bool aligned = ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(sd) |
                          reinterpret_cast<uintptr_t>(dq) | reinterpret_cast<uintptr_t>(dsd)) & 31) == 0;
-  if (aligned && D == 512) return launch_ground_bwd_t<T, 2>(g, w, w_dtype, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
-  if (aligned && D == 256) return launch_ground_bwd_t<T, 1>(g, w, w_dtype, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
-  if (aligned && D == 768) return launch_ground_bwd_t<T, 3>(g, w, w_dtype, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
-  if (aligned && D == 1024) return launch_ground_bwd_t<T, 4>(g, w, w_dtype, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 512) return launch_ground_bwd_t<T, 2>(g, w, w_dtype, arg, q, sd, mask, row_base, nnz, regime_ws, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 256) return launch_ground_bwd_t<T, 1>(g, w, w_dtype, arg, q, sd, mask, row_base, nnz, regime_ws, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 768) return launch_ground_bwd_t<T, 3>(g, w, w_dtype, arg, q, sd, mask, row_base, nnz, regime_ws, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  if (aligned && D == 1024) return launch_ground_bwd_t<T, 4>(g, w, w_dtype, arg, q, sd, mask, row_base, nnz, regime_ws, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
   ILFDT_REQUIRE(D <= 1024, ILFDT_E_UNSUPPORTED_SHAPE, "ground_bwd: D=%lld > 1024", (long long)D);
-  return launch_ground_bwd_t<T, 0>(g, w, w_dtype, arg, q, sd, mask, row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+  return launch_ground_bwd_t<T, 0>(g, w, w_dtype, arg, q, sd, mask, row_base, nnz, regime_ws, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
 }
 
 int32_t launch_ground_bwd(float* g, const void* w, int w_dtype, const int16_t* arg, const void* q, const void* sd, int dtype,
-                          const float* mask, const int* row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D, float sqrt_d,
-                          float temperature, void* dq, int dq_dtype, float* dsd, cudaStream_t st) {
+                          const float* mask, const int* row_base, const int* nnz, int* regime_ws, int64_t b, int64_t n_tok,
+                          int64_t K, int64_t D, float sqrt_d, float temperature, void* dq, int dq_dtype, float* dsd,
+                          cudaStream_t st) {
   if (b == 0) return ILFDT_OK;
   ILFDT_REQUIRE(b < (1ll << 31) && K < (1ll << 31) && n_tok <= 32767, ILFDT_E_UNSUPPORTED_SHAPE,
                 "ground_bwd: shape out of range");
   const float inv_scale = 1.f / (sqrt_d * temperature);
   if (dtype == ILFDT_F32)
     return dispatch_nv<float>(g, w, w_dtype, arg, reinterpret_cast<const float*>(q), reinterpret_cast<const float*>(sd), mask,
-                              row_base, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
+                              row_base, nnz, regime_ws, b, n_tok, K, D, inv_scale, dq, dq_dtype, dsd, st);
   return dispatch_nv<__nv_bfloat16>(g, w, w_dtype, arg, reinterpret_cast<const __nv_bfloat16*>(q),
-                                    reinterpret_cast<const __nv_bfloat16*>(sd), mask, row_base, b, n_tok, K, D, inv_scale, dq,
-                                    dq_dtype, dsd, st);
+                                    reinterpret_cast<const __nv_bfloat16*>(sd), mask, row_base, nnz, regime_ws, b, n_tok, K, D,
+                                    inv_scale, dq, dq_dtype, dsd, st);
 }
 
 }  // namespace ilfdt

@@ -43,8 +43,9 @@ int32_t launch_sparsemax_bwd(const float* w, const float* g, int64_t rows, int64
 
 // ground_bwd.cu
 int32_t launch_ground_bwd(float* g, const void* w, int w_dtype, const int16_t* arg, const void* q, const void* sd, int dtype,
-                          const float* mask, const int* row_base, int64_t b, int64_t n_tok, int64_t K, int64_t D,
-                          float sqrt_d, float temperature, void* dq, int dq_dtype, float* dsd, cudaStream_t st);
+                          const float* mask, const int* row_base, const int* nnz, int* regime_ws, int64_t b, int64_t n_tok,
+                          int64_t K, int64_t D, float sqrt_d, float temperature, void* dq, int dq_dtype, float* dsd,
+                          cudaStream_t st);
 
 // gemm_umma.cu (tcgen05)
 int32_t launch_gemm_nt_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha,

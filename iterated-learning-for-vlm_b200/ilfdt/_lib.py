@@ -43,8 +43,8 @@ SIGNATURES = {
     "ilfdt_gemm_tn_splitk_ws_bytes": (_i64, [_i64, _i64, _i64]),
     "ilfdt_gemm_tn_splitk": (_i32, [_p, _p, _i64, _i64, _i64, _f, _i32, _p, _i64, _p, _i64, _p]),
     "ilfdt_gemm_f32_strided": (_i32, [_p, _i64, _i64, _p, _i64, _i64, _p, _i64, _i64, _i64, _i64, _i64, _f, _i32, _p]),
-    "ilfdt_ground_bwd": (_i32, [_p, _p, _p, _p, _p, _i32, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _p, _i32, _p, _p]),
-    "ilfdt_ground_bwd_w16": (_i32, [_p, _p, _p, _p, _p, _i32, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _p, _i32, _p, _p]),
+    "ilfdt_ground_bwd": (_i32, [_p, _p, _p, _p, _p, _i32, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _p, _i32, _p, _p]),
+    "ilfdt_ground_bwd_w16": (_i32, [_p, _p, _p, _p, _p, _i32, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _p, _i32, _p, _p]),
     "ilfdt_att_fwd": (_i32, [_p, _i64, _i64, _i32, _p, _p, _p]),
     "ilfdt_att_bwd": (_i32, [_p, _p, _p, _i64, _i64, _i32, _p, _p]),
     "ilfdt_rownorm_fwd": (_i32, [_p, _p, _i64, _i64, _p, _p]),
@@ -76,7 +76,8 @@ SIGNATURES = {
     "ilfdt_copy": (_i32, [_p, _p, _i64, _p]),
 }
 
-TUNE = {"dsd_split_rows": 0, "dsd_tile": 1, "dsd_stream": 2, "ground_2cta": 3, "gemm_wide2": 4, "nce_2cta": 5}
+TUNE = {"dsd_split_rows": 0, "dsd_tile": 1, "dsd_stream": 2, "ground_2cta": 3, "gemm_wide2": 4, "nce_2cta": 5,
+        "sparse_bwd_nnz": 6}
 
 _lib = None
 

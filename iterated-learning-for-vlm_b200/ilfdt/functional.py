@@ -136,7 +136,7 @@ class GroundingFunction(torch.autograd.Function):
         # (token counts up to 96 run the v3 scatter kernel, up to 256 -- ViT-B/16's 196 patches -- the token-sorted one)
         lean = LEAN_WEIGHTS and (not need_weights) and mode == "bf16" and q.shape[2] in (256, 512) and q.shape[1] <= 256 \
             and sd.shape[0] % 4 == 0
-        w, w_b, _tau, _nnz = ops.sparsemax_fwd(pooled, want_bf16=(mode == "bf16"), want_f32=not lean)
+        w, w_b, _tau, nnz = ops.sparsemax_fwd(pooled, want_bf16=(mode == "bf16"), want_f32=not lean)
         del pooled
         if mode == "bf16":
             f = ops.gemm_nt(sd_kt, w_b)                     # f[b,D] = w[b,K] . sdT[D,K]^T  (clip_fdt.py:154)
@@ -144,7 +144,7 @@ class GroundingFunction(torch.autograd.Function):
             f = ops.gemm_f32(w, sd_c)
         ctx.mode, ctx.temperature = mode, float(temperature)
         ctx.n_tok = q.shape[1]
-        ctx.save_for_backward(q_k, sd_k, mask_f, w, arg, w_b, row_base)
+        ctx.save_for_backward(q_k, sd_k, mask_f, w, arg, w_b, row_base, nnz)
         if lean:
             ctx.mark_non_differentiable(w_b)
             return w_b, f
@@ -152,7 +152,7 @@ class GroundingFunction(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dw, df):
-        q_k, sd_k, mask_f, w, arg, w_b, row_base = ctx.saved_tensors
+        q_k, sd_k, mask_f, w, arg, w_b, row_base, nnz = ctx.saved_tensors
         mode = ctx.mode
         if w is None:
             w = w_b          # lean route: the support is read from the bf16 weights
@@ -177,7 +177,7 @@ class GroundingFunction(torch.autograd.Function):
         if ctx.q_dtype == torch.bfloat16 and mode == "bf16" and D in (256, 512, 768, 1024) and ctx.n_tok <= 256 \
                 and K % 4 == 0:
             dq_dtype = torch.bfloat16      # written directly by the scatter kernel
-        dq = ops.ground_bwd(g, w, arg, q_k, sd_k, mask_f, ctx.temperature, dsd, dq_dtype, row_base, ctx.n_tok)
+        dq = ops.ground_bwd(g, w, arg, q_k, sd_k, mask_f, ctx.temperature, dsd, dq_dtype, row_base, ctx.n_tok, nnz)
         if dq.dtype != ctx.q_dtype:
             dq = ops.cast_bf16(dq)
         return dq, dsd, None, None, None, None

@@ -20,7 +20,7 @@ LAUNCHES = 0          # kernels launched through this module since it was last z
 PROFILE_ON = False    # when True every C call is bracketed by CUDA events on the launching stream
 PROFILE = {}          # op name -> [(start_event, end_event), ...]
 _KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mask_rows_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_ground_fwd_text": 5, "ilfdt_text_compact": 3, "ilfdt_sparsemax_fwd": 1,
-                     "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2, "ilfdt_ground_bwd_w16": 2,
+                     "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2, "ilfdt_ground_bwd_w16": 2,   # + 2 regime launches that return at once
                      "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5, "ilfdt_nce_lse": 2, "ilfdt_nce_loss": 1,
                      "ilfdt_nce_bwd": 4, "ilfdt_nce_bwd_gathered": 2, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
                      "ilfdt_randn_fill": 1, "ilfdt_copy": 0,
@@ -284,9 +284,11 @@ def gemm_f32(A, B, a_t=False, b_t=False, alpha=1.0, out=None, accumulate=False):
     return out
 
 
-def ground_bwd(g, w, arg, q, sd, mask, temperature, dsd, dq_dtype=torch.float32, row_base=None, n_tok=None):
-    """g [b,K] is overwritten with coef. Returns dq [b,N,D] (dq_dtype); accumulates into dsd [K,D] f32.
-    row_base (int32 [b]) + n_tok: q is the compacted text operand [rows, D] of text_compact."""
+def ground_bwd(g, w, arg, q, sd, mask, temperature, dsd, dq_dtype=torch.float32, row_base=None, n_tok=None, nnz=None):
+    """g [b,K] is scratch (overwritten). Returns dq [b,N,D] (dq_dtype); accumulates into dsd [K,D] f32.
+    row_base (int32 [b]) + n_tok: q is the compacted text operand [rows, D] of text_compact.
+    nnz (int32 [b], from sparsemax_fwd): lets the library serve a launch whose mean support is a few tens of codes with
+    the sparse-regime kernel (decided on the device)."""
     _req(g, torch.float32, "g"); _req(arg, torch.int16, "arg")
     fn = "ilfdt_ground_bwd"
     if w is not None and w.dtype == torch.bfloat16:   # support read from the bf16 copy of the weights
@@ -302,8 +304,12 @@ def ground_bwd(g, w, arg, q, sd, mask, temperature, dsd, dq_dtype=torch.float32,
         b, D = g.shape[0], q.shape[-1]
     K = sd.shape[0]
     dq = torch.empty(b, n_tok, D, dtype=dq_dtype, device=q.device)
-    _call(fn, _ptr(g), _ptr(w), _ptr(arg), _ptr(q), _ptr(sd), _DT[q.dtype], _ptr(mask), _ptr(row_base), b,
-          n_tok, K, D, float(math.sqrt(D)), float(temperature), _ptr(dq), _DT[dq_dtype], _ptr(dsd), _stream())
+    regime = None
+    if nnz is not None:
+        _req(nnz, torch.int32, "nnz")
+        regime = torch.empty(1, dtype=torch.int32, device=q.device)
+    _call(fn, _ptr(g), _ptr(w), _ptr(arg), _ptr(q), _ptr(sd), _DT[q.dtype], _ptr(mask), _ptr(row_base), _ptr(nnz),
+          _ptr(regime), b, n_tok, K, D, float(math.sqrt(D)), float(temperature), _ptr(dq), _DT[dq_dtype], _ptr(dsd), _stream())
     return dq
 
 

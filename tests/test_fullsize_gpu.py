@@ -422,6 +422,76 @@ def test_scatter_backward_ranged_sweep_full_size(ops, n_tok, masked, lean):
                                                         json.dumps({k: float("%.3g" % v) for k, v in e.items()})))
 
 
+@pytest.mark.parametrize("n_tok,masked,K", [(49, False, 16384), (77, True, 16384), (49, False, 4096)])
+@pytest.mark.parametrize("lean", [False, True])
+def test_sparse_regime_backward(ops, n_tok, masked, K, lean):
+    """Trained-like, peaked attention (support of tens of codes): ilfdt_ground_bwd with the forward's nnz[b] serves the
+    launch with the per-sample sparse kernel (decided on the device). Checked against the fp64 index_add restatement,
+    against the dense sweeps (ILFDT_TUNE_SPARSE_BWD_NNZ = 0), and -- the same call on dense random-init statistics --
+    that the device-side decision falls back to the dense sweeps."""
+    dev = _dev()
+    b, D, temp = 1536, 512, 1000.0
+    g_ = torch.Generator(device="cuda").manual_seed(n_tok + K)
+    sd = torch.randn(K, D, device=dev, generator=g_)
+    sd_k = ops.cast_bf16(sd)
+    for scale, expect_sparse in ((200.0, True), (1.0, False)):
+        q = torch.randn(b, n_tok, D, device=dev, generator=g_) * scale
+        mask = row_base = None
+        if masked:
+            lens = torch.randint(5, n_tok + 1, (b,), device=dev, generator=g_)
+            mask = torch.zeros(b, n_tok, device=dev)
+            mask[torch.arange(n_tok, device=dev).view(1, -1) >= lens.view(-1, 1)] = float("-inf")
+            q_k, plan = ops.text_compact(q, mask)
+            row_base = plan.row_base
+            pooled, arg = ops.ground_fwd_text(q_k, sd_k, plan, n_tok, temp)
+        else:
+            q_k = ops.cast_bf16_rows(q, None)
+            pooled, arg = ops.ground_fwd(q_k, sd_k, None, temp, "max")
+        w, w_b, _, nnz = ops.sparsemax_fwd(pooled, want_bf16=True)
+        mean_nnz = nnz.float().mean().item()
+        assert (mean_nnz <= 128) == expect_sparse, mean_nnz
+        g = torch.randn(b, K, device=dev, generator=g_)
+        dq_dtype = torch.bfloat16 if lean else torch.float32
+        w_arg = w_b if lean else w
+
+        def run(use_nnz, **tune):
+            dsd = torch.zeros(K, D, device=dev)
+            gg = g.clone()
+            with ops.tune(**tune):
+                dq = ops.ground_bwd(gg, w_arg, arg, q_k, sd_k, mask, temp, dsd, dq_dtype, row_base, n_tok,
+                                    nnz if use_nnz else None)
+            return dq, dsd, gg
+
+        dq_a, dsd_a, g_after = run(True)                       # device-side decision
+        dq_d, dsd_d, _ = run(True, sparse_bwd_nnz=0)           # dense sweeps forced
+        # the dense sweeps leave coef in g; the sparse kernel never writes it: that is how the taken route is observed
+        took_sparse = torch.equal(g_after, g)
+        assert took_sparse == expect_sparse
+        nz = (w > 0)
+        mean = (g.double() * nz).sum(1, keepdim=True) / nz.sum(1, keepdim=True).clamp_min(1)
+        keep = torch.ones(b, K, dtype=torch.float64, device=dev)
+        if masked:
+            keep = (torch.gather(mask, 1, arg.long()) == 0).double()
+        coef = nz * (g.double() - mean) * keep / (math.sqrt(D) * temp)
+        if masked:
+            rb = row_base.long()
+            row_of = lambda bi, ti: (bi * n_tok + ti, rb[bi] + ti)
+        else:
+            row_of = lambda bi, ti: (bi * n_tok + ti, bi * n_tok + ti)
+        if expect_sparse:
+            dq64, dsd64 = _scatter_fp64(coef, arg, q_k.double().reshape(-1, D), row_of, sd_k.double(), b * n_tok, chunk=b)
+            tol_dq = 8e-3 if lean else 2e-5
+            e = dict(dq=assert_close(dq_a.reshape(-1, D), dq64, tol_dq, "dq (sparse kernel)"),
+                     dsd=assert_close(dsd_a, dsd64, 2e-5, "dsd (sparse kernel)"),
+                     dq_vs_dense=assert_close(dq_a.float(), dq_d.float(), tol_dq, "dq sparse vs dense sweeps"),
+                     dsd_vs_dense=assert_close(dsd_a, dsd_d, 2e-5, "dsd sparse vs dense sweeps"))
+            print("sparse_bwd[n_tok=%d,K=%d,lean=%s] mean support %.1f %s" % (n_tok, K, lean, mean_nnz,
+                                                                            json.dumps({k: float("%.3g" % v) for k, v in e.items()})))
+        else:
+            assert torch.equal(dq_a, dq_d), "dense statistics: the decision must fall back to the dense sweeps"
+            assert_close(dsd_a, dsd_d, 5e-6, "dsd")
+
+
 # ---------------------------------------------------------------------------------------------------
 # (iii) InfoNCE at b = 4096, B = 32768, rank 3 of 8: chunked LSE + combine, nce_bwd2 split plan, top-k counts
 # ---------------------------------------------------------------------------------------------------
