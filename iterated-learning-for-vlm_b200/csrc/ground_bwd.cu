@@ -921,8 +921,8 @@ ground_bwd_dsd_v3_kernel(const float* __restrict__ coef, const int16_t* __restri
 // are dense SCANS of three [b,K] arrays (coef written and re-read, w, arg) that find ~0.1 % useful entries: 13 ms per
 // step at the headline shape for ~23 entries per row. Here one CTA per sample scans only the bf16 / fp32 weights of its
 // row (the support), and for each of its few entries does both updates itself:
-//     dq[b, arg, :] += coef * sd[k, :]   into a shared-memory copy of the sample's [n_tok, D] gradient block
-//     dsd[k, :]     += coef * q[b, arg, :]   with 16-byte vector reductions to global memory
+//     dq[b, arg, :] += coef * sd[k, :]   a warp per token walks the sample's short entry list (fixed order: deterministic)
+//     dsd[k, :]     += coef * q[b, arg, :]   with 16-byte vector reductions to global memory (fp32 sum order free)
 // No coef array, no second sweep. Which regime a launch is in is decided ON THE DEVICE (gb_regime_kernel: mean support
 // from the forward's nnz[b]) -- no host synchronisation, CUDA-graph safe: both code paths are enqueued and the one that
 // does not apply returns at once. fp32 sums are taken in arrival order (shared / global reductions).
@@ -945,6 +945,8 @@ __global__ void __launch_bounds__(256) gb_regime_kernel(const int* __restrict__ 
   }
 }
 
+constexpr int GSP_CAP = 2048;   // support entries of one sample staged per round
+
 template <typename T, int NV, typename TO, typename TW>
 __global__ void __launch_bounds__(GSP_THREADS)
 ground_bwd_sparse_kernel(const float* __restrict__ g, const TW* __restrict__ w, const int16_t* __restrict__ arg,
@@ -952,84 +954,157 @@ ground_bwd_sparse_kernel(const float* __restrict__ g, const TW* __restrict__ w, 
                          const int* __restrict__ row_base, const int* __restrict__ sparse_flag, int n_tok, int K, int D,
                          float inv_scale, TO* __restrict__ dq, float* __restrict__ dsd) {
   if (*sparse_flag == 0) return;
-  extern __shared__ __align__(16) float gsp_acc[];   // [n_tok][D]
+  __shared__ int list_k[GSP_CAP];
+  __shared__ int16_t list_t[GSP_CAP];
+  __shared__ float list_c[GSP_CAP];
   __shared__ double red_s[GSP_WARPS];
   __shared__ int red_c[GSP_WARPS];
+  __shared__ int warp_off[GSP_WARPS + 1];
   const int64_t b = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const float* gr = g + b * K;
   const TW* wr = w + b * K;
   const int16_t* ar = arg + b * K;
-  for (int i = tid * 4; i < n_tok * D; i += GSP_THREADS * 4) *reinterpret_cast<float4*>(gsp_acc + i) = make_float4(0.f, 0.f, 0.f, 0.f);
-  // pass 1: mean of g over the support
-  double s = 0.0;
-  int c = 0;
-  for (int i = tid * 4; i < K; i += GSP_THREADS * 4) {
-    uint32_t m = Support4<TW>::ld(wr + i);
-    while (m) {
-      const int j = __ffs(m) - 1;
-      m &= m - 1;
-      s += (double)gr[i + j];
-      ++c;
-    }
-  }
-  s = warp_sum(s);
-  c = warp_sum(c);
-  if (lane == 0) { red_s[warp] = s; red_c[warp] = c; }
-  __syncthreads();
-  s = 0.0; c = 0;
-#pragma unroll
-  for (int i = 0; i < GSP_WARPS; ++i) { s += red_s[i]; c += red_c[i]; }
-  const float mean = c > 0 ? (float)(s / (double)c) : 0.f;
   const int64_t qbase = row_base ? (int64_t)row_base[b] : b * n_tok;
-  // pass 2: a warp scans 128 codes at a time; every hit is processed by the whole warp (lane = 8 columns per 256)
-  for (int i0 = warp * 128; i0 < K; i0 += GSP_WARPS * 128) {
-    const int i = i0 + lane * 4;
-    const uint32_t m = (i < K) ? Support4<TW>::ld(wr + i) : 0u;   // second read of the row: L1 / L2 hit
-    unsigned any = __ballot_sync(0xffffffffu, m != 0u);
-    while (any) {
-      const int src = __ffs(any) - 1;
-      any &= any - 1;
-      uint32_t mm = __shfl_sync(0xffffffffu, m, src);
-      while (mm) {
-        const int j = __ffs(mm) - 1;
-        mm &= mm - 1;
-        const int k = i0 + src * 4 + j;
-        const int t = ar[k];
-        const float keep = (mask == nullptr || mask[b * n_tok + t] == 0.f) ? 1.f : 0.f;
-        const float cf = (gr[k] - mean) * keep * inv_scale;
-        if (cf == 0.f) continue;
-        const T* srow = sd + (int64_t)k * D;
-        const T* qrow = q + (qbase + t) * (int64_t)D;
-        float* arow = gsp_acc + t * D;
-        float* drow = dsd + (int64_t)k * D;
+  // The row is walked in blocks of 256 threads x 4 codes x 16 = 16384 codes: per block, every thread issues its 16
+  // independent support loads at once and keeps the 64 membership bits in registers.
+  constexpr int PER = 16;
+  int done_rounds = 0;
+  for (int k0 = 0; k0 < K; k0 += GSP_THREADS * 4 * PER) {
+    uint64_t bits = 0;
 #pragma unroll
-        for (int u = 0; u < NV; ++u) {
-          float vs[8], vq[8];
-          Load8<T>::ld(srow + (u * 32 + lane) * 8, vs);
-          Load8<T>::ld(qrow + (u * 32 + lane) * 8, vq);
-          float* a = arow + (u * 32 + lane) * 8;
+    for (int j = 0; j < PER; ++j) {
+      const int k = k0 + (j * GSP_THREADS + tid) * 4;
+      if (k < K) bits |= (uint64_t)Support4<TW>::ld(wr + k) << (4 * j);
+    }
+    // (s, c) over the WHOLE row are needed before any coefficient: first block pass only counts when K <= 16384;
+    // longer rows take a separate counting pass below
+    int cnt = __popcll(bits);
+    // deterministic placement: exclusive scan of the per-thread counts (thread order, then bit order)
+    int incl = cnt;
 #pragma unroll
-          for (int e = 0; e < 8; ++e) atomicAdd(a + e, cf * vs[e]);
-          float* o = drow + (u * 32 + lane) * 8;
-          asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o), "f"(cf * vq[0]), "f"(cf * vq[1]),
-                       "f"(cf * vq[2]), "f"(cf * vq[3]) : "memory");
-          asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o + 4), "f"(cf * vq[4]), "f"(cf * vq[5]),
-                       "f"(cf * vq[6]), "f"(cf * vq[7]) : "memory");
-        }
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += n;
+    }
+    if (lane == 31) warp_off[warp + 1] = incl;
+    __syncthreads();
+    if (tid == 0) {
+      warp_off[0] = 0;
+      for (int i = 0; i < GSP_WARPS; ++i) warp_off[i + 1] += warp_off[i];
+    }
+    __syncthreads();
+    const int total = warp_off[GSP_WARPS];
+    int pos = warp_off[warp] + incl - cnt;
+    // mean of g over the support of the whole row (computed once, on the first block; rows longer than one block
+    // count the remaining blocks here as well)
+    if (k0 == 0) {
+      double s = 0.0;
+      int c = 0;
+      uint64_t bb = bits;
+      while (bb) {
+        const int bit = __ffsll((long long)bb) - 1;
+        bb &= bb - 1;
+        s += (double)gr[((bit >> 2) * GSP_THREADS + tid) * 4 + (bit & 3)];
+        ++c;
       }
+      for (int k1 = GSP_THREADS * 4 * PER; k1 < K; k1 += GSP_THREADS * 4 * PER)
+#pragma unroll 4
+        for (int j = 0; j < PER; ++j) {
+          const int k = k1 + (j * GSP_THREADS + tid) * 4;
+          if (k < K) {
+            uint32_t m = Support4<TW>::ld(wr + k);
+            while (m) {
+              const int e = __ffs(m) - 1;
+              m &= m - 1;
+              s += (double)gr[k + e];
+              ++c;
+            }
+          }
+        }
+      s = warp_sum(s);
+      c = warp_sum(c);
+      if (lane == 0) { red_s[warp] = s; red_c[warp] = c; }
+      __syncthreads();
+      if (tid == 0) {
+        double ts = 0.0;
+        int tc = 0;
+        for (int i = 0; i < GSP_WARPS; ++i) { ts += red_s[i]; tc += red_c[i]; }
+        red_s[0] = tc > 0 ? ts / (double)tc : 0.0;
+      }
+      __syncthreads();
+    }
+    const float mean = (float)red_s[0];
+    // rounds of at most GSP_CAP entries (one round unless a single sample of a sparse launch has > 2048 support codes)
+    for (int base = 0; base < total; base += GSP_CAP, ++done_rounds) {
+      uint64_t bb = bits;
+      int p = pos;
+      while (bb) {
+        const int bit = __ffsll((long long)bb) - 1;
+        bb &= bb - 1;
+        if (p >= base && p < base + GSP_CAP) {
+          const int k = k0 + ((bit >> 2) * GSP_THREADS + tid) * 4 + (bit & 3);
+          const int t = ar[k];
+          const float keep = (mask == nullptr || mask[b * n_tok + t] == 0.f) ? 1.f : 0.f;
+          list_k[p - base] = k;
+          list_t[p - base] = (int16_t)t;
+          list_c[p - base] = (gr[k] - mean) * keep * inv_scale;
+        }
+        ++p;
+      }
+      __syncthreads();
+      const int n_ent = min(GSP_CAP, total - base);
+      for (int t = warp; t < n_tok; t += GSP_WARPS) {
+        float acc[NV][8];
+#pragma unroll
+        for (int u = 0; u < NV; ++u)
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[u][e] = 0.f;
+        float vq[NV][8];
+        bool have_q = false;
+        for (int e0 = 0; e0 < n_ent; e0 += 32) {
+          const int e = e0 + lane;
+          const bool mine = e < n_ent && list_t[e] == t && list_c[e] != 0.f;
+          unsigned hits = __ballot_sync(0xffffffffu, mine);
+          while (hits) {
+            const int src = __ffs(hits) - 1;
+            hits &= hits - 1;
+            const int k = list_k[e0 + src];
+            const float cf = list_c[e0 + src];
+            if (!have_q) {
+#pragma unroll
+              for (int u = 0; u < NV; ++u) Load8<T>::ld(q + (qbase + t) * (int64_t)D + (u * 32 + lane) * 8, vq[u]);
+              have_q = true;
+            }
+            const T* srow = sd + (int64_t)k * D;
+            float* drow = dsd + (int64_t)k * D;
+#pragma unroll
+            for (int u = 0; u < NV; ++u) {
+              float vs[8];
+              Load8<T>::ld(srow + (u * 32 + lane) * 8, vs);
+#pragma unroll
+              for (int x = 0; x < 8; ++x) acc[u][x] = fmaf(cf, vs[x], acc[u][x]);
+              float* o = drow + (u * 32 + lane) * 8;
+              asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o), "f"(cf * vq[u][0]), "f"(cf * vq[u][1]),
+                           "f"(cf * vq[u][2]), "f"(cf * vq[u][3]) : "memory");
+              asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o + 4), "f"(cf * vq[u][4]), "f"(cf * vq[u][5]),
+                           "f"(cf * vq[u][6]), "f"(cf * vq[u][7]) : "memory");
+            }
+          }
+        }
+        TO* out = dq + (b * n_tok + t) * (int64_t)D;
+#pragma unroll
+        for (int u = 0; u < NV; ++u) StoreRow8<TO>::st(out + (u * 32 + lane) * 8, acc[u], done_rounds > 0);
+      }
+      __syncthreads();
     }
   }
-  __syncthreads();
-  for (int t = warp; t < n_tok; t += GSP_WARPS) {
-    TO* out = dq + (b * n_tok + t) * (int64_t)D;
+  if (done_rounds == 0) {   // a sample with an empty support: its gradient block is zero
+    for (int t = warp; t < n_tok; t += GSP_WARPS) {
+      TO* out = dq + (b * n_tok + t) * (int64_t)D;
+      float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int u = 0; u < NV; ++u) {
-      float a[8];
-      const float4 x = *reinterpret_cast<const float4*>(gsp_acc + t * D + (u * 32 + lane) * 8);
-      const float4 y = *reinterpret_cast<const float4*>(gsp_acc + t * D + (u * 32 + lane) * 8 + 4);
-      a[0] = x.x; a[1] = x.y; a[2] = x.z; a[3] = x.w; a[4] = y.x; a[5] = y.y; a[6] = y.z; a[7] = y.w;
-      StoreRow8<TO>::st(out + (u * 32 + lane) * 8, a, false);
+      for (int u = 0; u < NV; ++u) StoreRow8<TO>::st(out + (u * 32 + lane) * 8, z, false);
     }
   }
 }
@@ -1038,10 +1113,7 @@ template <typename T, int NV, typename TO, typename TW>
 static int32_t launch_sparse(const float* g, const TW* w, const int16_t* arg, const T* q, const T* sd, const float* mask,
                              const int* row_base, const int* flag, int64_t b, int64_t n_tok, int64_t K, int64_t D,
                              float inv_scale, TO* dq, float* dsd, cudaStream_t st) {
-  const size_t smem = (size_t)n_tok * D * sizeof(float);
-  ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_sparse_kernel<T, NV, TO, TW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)smem));
-  ground_bwd_sparse_kernel<T, NV, TO, TW><<<(unsigned)b, GSP_THREADS, smem, st>>>(g, w, arg, q, sd, mask, row_base, flag,
+  ground_bwd_sparse_kernel<T, NV, TO, TW><<<(unsigned)b, GSP_THREADS, 0, st>>>(g, w, arg, q, sd, mask, row_base, flag,
                                                                              (int)n_tok, (int)K, (int)D, inv_scale, dq, dsd);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
@@ -1105,12 +1177,12 @@ static int32_t launch_ground_bwd_t(float* g, const void* w_v, int w_dtype, const
                        ((reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(w)) & 15) == 0 &&
                        ((reinterpret_cast<uintptr_t>(arg) | reinterpret_cast<uintptr_t>(w16)) & 7) == 0;
     // sparse regime (device-side decision, see ground_bwd_sparse_kernel): needs the forward's nnz[b], one int of scratch,
-    // the shapes both v3 kernels take, and a [n_tok, D] fp32 block that fits shared memory
+    // and the shapes both v3 kernels take
     const int64_t sparse_nnz = tune_get(ILFDT_TUNE_SPARSE_BWD_NNZ);
     if constexpr (NV <= 2) {
       const bool dsd_v3_ok = K % 32 == 0 && ((reinterpret_cast<uintptr_t>(g) & 15) | (reinterpret_cast<uintptr_t>(arg) & 7)) == 0;
       if (v3_ok && dsd_v3_ok && !done && nnz != nullptr && regime_ws != nullptr && sparse_nnz > 0 &&
-          (w != nullptr || w16 != nullptr) && n_tok * D * 4 <= 200 * 1024) {
+          (w != nullptr || w16 != nullptr)) {
         gb_regime_kernel<<<1, 256, 0, st>>>(nnz, b, sparse_nnz * b, regime_ws);
         ILFDT_LAUNCH_OK();
         flag = regime_ws;
