@@ -970,6 +970,14 @@ ground_bwd_sparse_kernel(const float* __restrict__ g, const TW* __restrict__ w, 
   // independent support loads at once and keeps the 64 membership bits in registers.
   constexpr int PER = 16;
   int done_rounds = 0;
+  // Almost every row of this sample's [n_tok, D] gradient block is zero: the block is zero-filled up front with
+  // fire-and-forget 16-byte stores (they drain while the support loads below are in flight) and only the rows that own
+  // entries are written again afterwards (the CTA barriers in between order the two stores to the same address).
+  {
+    uint4* z16 = reinterpret_cast<uint4*>(dq + b * n_tok * (int64_t)D);
+    const int n16 = (int)((size_t)n_tok * D * sizeof(TO) / 16);
+    for (int i = tid; i < n16; i += GSP_THREADS) z16[i] = make_uint4(0u, 0u, 0u, 0u);
+  }
   for (int k0 = 0; k0 < K; k0 += GSP_THREADS * 4 * PER) {
     uint64_t bits = 0;
 #pragma unroll
@@ -1061,7 +1069,7 @@ ground_bwd_sparse_kernel(const float* __restrict__ g, const TW* __restrict__ w, 
 #pragma unroll
           for (int e = 0; e < 8; ++e) acc[u][e] = 0.f;
         float vq[NV][8];
-        bool have_q = false;
+        bool have_q = false;   // also: this token owns at least one entry
         for (int e0 = 0; e0 < n_ent; e0 += 32) {
           const int e = e0 + lane;
           const bool mine = e < n_ent && list_t[e] == t && list_c[e] != 0.f;
@@ -1092,19 +1100,13 @@ ground_bwd_sparse_kernel(const float* __restrict__ g, const TW* __restrict__ w, 
             }
           }
         }
-        TO* out = dq + (b * n_tok + t) * (int64_t)D;
+        if (have_q) {
+          TO* out = dq + (b * n_tok + t) * (int64_t)D;
 #pragma unroll
-        for (int u = 0; u < NV; ++u) StoreRow8<TO>::st(out + (u * 32 + lane) * 8, acc[u], done_rounds > 0);
+          for (int u = 0; u < NV; ++u) StoreRow8<TO>::st(out + (u * 32 + lane) * 8, acc[u], done_rounds > 0);
+        }
       }
       __syncthreads();
-    }
-  }
-  if (done_rounds == 0) {   // a sample with an empty support: its gradient block is zero
-    for (int t = warp; t < n_tok; t += GSP_WARPS) {
-      TO* out = dq + (b * n_tok + t) * (int64_t)D;
-      float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-      for (int u = 0; u < NV; ++u) StoreRow8<TO>::st(out + (u * 32 + lane) * 8, z, false);
     }
   }
 }

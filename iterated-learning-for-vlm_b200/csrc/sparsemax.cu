@@ -89,7 +89,7 @@ sparsemax_fwd_kernel(const float* __restrict__ z, int K, float* __restrict__ w,
     block_sum_cnt(s, c, red);
     if (c == cnt_prev) break;
     cnt_prev = c;
-    tau = (s - 1.0) / (double)c;
+    tau = fmax((s - 1.0) / (double)c, -1.0);   // tau >= max - 1: every weight is <= 1
   }
   const float tf = (float)tau;
   int nz = 0;
@@ -188,7 +188,9 @@ sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__
     for (int i = 0; i < SPX_THREADS / 32; ++i) { ts += red_s[it & 1][i]; tc += red_c[it & 1][i]; }
     if (tc == cnt_prev) break;
     cnt_prev = tc;
-    tau = (ts - 1.0) / (double)tc;
+    // every weight is <= 1, so tau >= max - 1 = -1 after the shift: for peaked rows that bound is far above the
+    // whole-row mean the first iterations would otherwise crawl up from
+    tau = fmax((ts - 1.0) / (double)tc, -1.0);
   }
   const float tf = (float)tau;
   int nz = 0;

@@ -1,18 +1,20 @@
-"""Prints the key metrics of an .ncu-rep (via `ncu --page raw --csv`) -- used to write profiles/*.md."""
-import csv, subprocess, sys
-rep = sys.argv[1]
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-rows = list(csv.reader(raw.splitlines()))
-H = rows[0]
-want = ['Kernel Name', 'gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum',
-        'sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed', 'lts__t_bytes.sum',
-        'lts__throughput.avg.pct_of_peak_sustained_elapsed', 'lts__t_sector_hit_rate.pct',
-        'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'l1tex__m_xbar2l1tex_read_bytes.sum',
-        'launch__grid_size', 'launch__registers_per_thread', 'sm__cycles_elapsed.max',
-        'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed', 'sm__warps_active.avg.pct_of_peak_sustained_active',
-        'smsp__inst_executed.sum', 'sm__inst_executed_pipe_uniform.sum', 'smsp__cycles_active.avg',
-        'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum', 'smsp__inst_executed_op_shared_ld.sum']
-for i, k in enumerate(H):
-    base = k.split('TriageCompute.')[-1]
-    if base in want or (len(sys.argv) > 2 and any(s in base for s in sys.argv[2:])):
-        print("%-85s %-10s %s" % (base, rows[1][i], [r[i][:70] for r in rows[2:]]))
+"""python tools/ncu_summary.py launches.csv [skip_first_n_launches_of_each_kernel]
+Condenses an `ncu --metrics gpu__time_duration.sum --csv` launch list into one row per kernel: launches, total and mean
+duration, share of the total."""
+import csv, sys, re, collections
+rows = list(csv.reader(l for l in open(sys.argv[1]) if l.startswith('"')))
+hdr = rows[0]
+ki, vi = hdr.index("Kernel Name"), hdr.index("Metric Value")
+ui = hdr.index("Metric Unit")
+tot = collections.OrderedDict()
+for r in rows[1:]:
+    name = re.sub(r"\(.*", "", r[ki])[:90]
+    v = float(r[vi].replace(",", ""))
+    v = v / 1e6 if r[ui] in ("ns", "nsecond") else (v / 1e3 if r[ui] in ("us", "usecond") else v)
+    t = tot.setdefault(name, [0, 0.0])
+    t[0] += 1; t[1] += v
+s = sum(v[1] for v in tot.values())
+print("%-92s %6s %10s %9s %6s" % ("kernel", "n", "total ms", "mean ms", "share"))
+for k, (n, v) in sorted(tot.items(), key=lambda kv: -kv[1][1]):
+    print("%-92s %6d %10.3f %9.4f %5.1f%%" % (k, n, v, v / n, 100 * v / s))
+print("%-92s %6s %10.3f" % ("TOTAL", "", s))
