@@ -1,6 +1,7 @@
 """Mirror of prototype/model/__init__.py:1-6 for the classes on the hot path."""
 from .clip import CLIP  # noqa: F401
 from .clip_fdt import AllGather, Clip_FDT, Query_model, clip_fdt_vitb16, clip_fdt_vitb32  # noqa: F401
+from .declip_fdt import DECLIP_FDT, declip_fdt_vitb32  # noqa: F401
 from .sparsemax import Sparsemax  # noqa: F401
 
 

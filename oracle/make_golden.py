@@ -314,11 +314,62 @@ def gen_config1():
     dist.destroy_process_group()
 
 
+
+def gen_declip():
+    """DeCLIP-FDT's own Query_model copy (declip_fdt.py:120-210, `return_token_att` = activated per-token
+    attention) and the eight-logits head (declip_fdt.py:381-412) run on the unmodified reference code. The head lines are
+    executed through DECLIP_FDT.__dict__-free helpers: its constructor needs `textaugment` (absent), so the normalise /
+    scale / logits lines are evaluated on tensors produced by the reference's Query_model instances."""
+    H.load_reference()
+    import prototype.model.declip_fdt as D
+    out = {}
+    b, N, Fd, Dm, K = 6, 7, 24, 32, 96
+    g = torch.Generator().manual_seed(77)
+    sd = torch.randn(K, Dm, generator=g)
+    mask = _mask(b, N, [7, 3, 1, 5, 7, 2])
+    for name, att in (("smax", "sparsemax"), ("soft", "softmax")):
+        torch.manual_seed(5)
+        qm = D.Query_model(ft_dim=Fd, sd_dim=Dm, temperature=4.0, att_func_type=att, pool_type="max")
+        ft = torch.randn(b, N, Fd, generator=g)
+        with torch.no_grad():
+            D.Sparsemax  # noqa: B018 -- the module-level import the activation uses
+            import prototype.model.sparsemax as ref_sp
+            ref_sp.device = torch.device("cpu")
+            for tag, m in (("nomask", None), ("mask", mask)):
+                tok, f, _ = qm(ft, sd, mask=m, return_token_att=True)
+                w, f2, _ = qm(ft, sd, mask=m)
+                out[f"{name}_{tag}_token_att"] = _np(tok)
+                out[f"{name}_{tag}_f"] = _np(f)
+                out[f"{name}_{tag}_w"] = _np(w)
+        out[name + "_ft"] = _np(ft)
+        for k, v in qm.state_dict().items():
+            out[name + "_state_" + k] = _np(v)
+    out["sd"], out["mask"], out["temp"] = _np(sd), _np(mask), np.array(4.0)
+    # eight logits (declip_fdt.py:382-408) on given pooled features, single process (gathered == local)
+    f1, f2, tm, ta = (torch.randn(b, Dm, generator=g) for _ in range(4))
+    p = torch.tensor([2.0])
+    i1 = f1 / f1.norm(dim=-1, keepdim=True)                 # :382
+    i2 = f2 / f2.norm(dim=-1, keepdim=True)                 # :383
+    t1 = tm / (tm.norm(dim=-1, keepdim=True) + 1e-10)       # :384
+    t2 = ta / (ta.norm(dim=-1, keepdim=True) + 1e-10)       # :385
+    s = p.exp()
+    s.data = torch.clamp(s.data, max=100)                   # :388-389
+    logits = dict(i1=s * i1 @ t1.t(), i2=s * i2 @ t1.t(), i1a=s * i1 @ t2.t(), i2a=s * i2 @ t2.t(),     # :399-402
+                  t1=s * t1 @ i1.t(), t2=s * t1 @ i2.t(), t1a=s * t2 @ i1.t(), t2a=s * t2 @ i2.t())     # :405-408
+    for k, v in logits.items():
+        out["logits_" + k] = _np(v)
+    out.update(head_f1=_np(f1), head_f2=_np(f2), head_tm=_np(tm), head_ta=_np(ta), head_p=_np(p))
+    np.savez_compressed(os.path.join(OUT, "declip_fdt.npz"), **out)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(4)
     if sys.argv[1:] == ["eval_extract"]:      # added later: leaves the earlier fixtures byte-identical
         gen_eval_extract()
+        sys.exit(0)
+    if sys.argv[1:] == ["declip"]:
+        gen_declip()
         sys.exit(0)
     if sys.argv[1:] == ["config1"]:           # round 2: full-size golden (BASELINE.json config 1)
         torch.set_num_threads(8)
@@ -330,5 +381,6 @@ if __name__ == "__main__":
     gen_clip_steps()
     gen_eval_extract()
     gen_config1()
+    gen_declip()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

@@ -409,3 +409,32 @@ def test_lazy_logits_are_visible_to_ddp_find_unused_parameters():
         p.join(60)
         assert p.exitcode == 0
     assert res == [(0, True), (1, True)]
+
+
+def test_declip_fdt_binding_state_dict_names():
+    """the DeCLIP-FDT drop-in keeps the reference's parameter names for the FDT part
+    (prototype/model/declip_fdt.py:212-247) and its registry entry exists."""
+    from ilfdt.model import model_entry  # noqa: F401
+    from ilfdt.model.declip_fdt import DECLIP_FDT, Query_model
+    m = DECLIP_FDT(torch.nn.Identity(), torch.nn.Identity(), True, sd_num=64, sd_dim=16, sd_temperature=1000.0,
+                   pool_type="max", att_func_type="sparsemax", raw_img_ft_dim=24, raw_txt_ft_dim=20,
+                   nn_size=128, EDA=True, text_mask_type="MLM")      # the auxiliary-head options are accepted and ignored
+    names = {k: tuple(v.shape) for k, v in m.state_dict().items()}
+    assert names["space_dict"] == (64, 16) and names["logit_scale"] == (1,)
+    for pre, ft in (("img_query_model", 24), ("txt_query_model", 20)):
+        assert names[pre + ".q_map.1.weight"] == (16, ft) and names[pre + ".q_map.4.weight"] == (16, 16)
+    if os.path.isdir("/root/reference/prototype"):
+        sys.path.insert(0, ROOT)
+        from oracle import ref_harness as H
+        H.load_reference()
+        import prototype.model.declip_fdt as D
+        r = D.Query_model(ft_dim=24, sd_dim=16, temperature=1000.0, att_func_type="sparsemax", pool_type="max")
+        ours = Query_model(ft_dim=24, sd_dim=16, temperature=1000.0, att_func_type="sparsemax", pool_type="max")
+        assert list(r.state_dict().keys()) == list(ours.state_dict().keys())
+        import inspect
+        src = inspect.getsource(D.DECLIP_FDT.__init__)
+        for attr in ("self.space_dict", "self.img_query_model", "self.txt_query_model"):
+            assert attr in src
+    with pytest.raises(NotImplementedError):     # eval / no all-gather: the reference raises too (declip_fdt.py:429-430)
+        m.eval()
+        m.fdt_head(torch.zeros(2, 16), torch.zeros(2, 16), torch.zeros(2, 16), torch.zeros(2, 16))
