@@ -114,10 +114,15 @@ def main():
         del ddp, m2
         # ---- 3. CUDA graph of the step incl. collectives; release before the process group goes away
         if mode == "bf16":
+            # (a fresh model: its parameters' gradient accumulators must first be used on the stream the graph is
+            # captured on, as with any torch.cuda.graph capture of a backward pass)
+            m = build(K, D, dev, mine["sd"], mine["p"])
+
             def step_fn(a, c_, mk):
                 a = a.detach().requires_grad_(True)
                 c_ = c_.detach().requires_grad_(True)
-                m.zero_grad(set_to_none=True)
+                for prm in m.parameters():
+                    prm.grad = None
                 (l_i, l_t), _ = m(a, (c_, mk))
                 ls, _ = crit(l_i, l_t)
                 (ls / world).backward()
