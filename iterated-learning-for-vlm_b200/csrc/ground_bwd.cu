@@ -559,8 +559,11 @@ ground_bwd_dq_sorted_kernel(float* __restrict__ g, const TW* __restrict__ w, con
 }
 
 
-template <typename T, int NV, typename TO, typename TW>
-__global__ void __launch_bounds__(G3_THREADS, 3)
+// PG > 0 (bf16 rows): the gather loop is software-pipelined like kernel 2 v4 -- groups of PG codebook rows, the loads of
+// group i+1 issued before group i is consumed, the next 32-entry chunk's indices and coefficients prefetched behind the
+// current chunk's gathers -- so the per-batch L2 latency is no longer exposed (see ground_bwd_dsd_v4_kernel).
+template <typename T, int NV, typename TO, typename TW, int PG = 0, int MINB = 3>
+__global__ void __launch_bounds__(G3_THREADS, MINB)
 ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const int16_t* __restrict__ arg,
                         const T* __restrict__ sd, const float* __restrict__ mask, int n_tok, int K, int D,
                         float inv_scale, TO* __restrict__ dq, const int* __restrict__ sparse_flag) {
@@ -718,43 +721,113 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const i
       for (int i = 0; i < NV; ++i)
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
-      for (int e0 = lo; e0 < hi; e0 += 32) {
+      if constexpr (PG > 0 && sizeof(T) == 2) {
+        uint4 bufA[PG][NV], bufB[PG][NV];
+        float cfA[PG], cfB[PG];
+        int nA = 0, nB = 0, phase = 0;
+        bool pend = false;
         int myk = 0;
         float myc = 0.f;
-        if (e0 + lane < hi) {
-          myk = sorted_k[e0 + lane];
+        if (lo + lane < hi) {
+          myk = sorted_k[lo + lane];
           myc = coef_row[myk];
         }
-        const int n = min(32, hi - e0);
-        int j = 0;
-        if constexpr (sizeof(T) == 2)  // bf16 rows: keep 4 of them in flight as raw 16-byte vectors
-        for (; j + 4 <= n; j += 4) {
-          uint4 raw[4][NV];
-          float cc[4];
+        auto issue = [&](uint4 (&buf)[PG][NV], float (&cf)[PG], int& n, int j, int cnt) {
+          n = cnt;
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const int kq = __shfl_sync(0xffffffffu, myk, j + u);
-            cc[u] = __shfl_sync(0xffffffffu, myc, j + u);
-            const T* row = sd + (int64_t)(k0 + kq) * D;
+          for (int u = 0; u < PG; ++u) {
+            const int kq = __shfl_sync(0xffffffffu, myk, (j + u) & 31);
+            cf[u] = __shfl_sync(0xffffffffu, myc, (j + u) & 31);
+            if (u < cnt) {
+              const T* row = sd + (int64_t)(k0 + kq) * D;
 #pragma unroll
-            for (int i = 0; i < NV; ++i) raw[u][i] = ldg_hint(row + (i * 32 + lane) * 8, row_pol);
+              for (int i = 0; i < NV; ++i) buf[u][i] = ldg_hint(row + (i * 32 + lane) * 8, row_pol);
+            }
           }
+        };
+        auto consume = [&](const uint4 (&buf)[PG][NV], const float (&cf)[PG], int n) {
 #pragma unroll
-          for (int u = 0; u < 4; ++u)
+          for (int u = 0; u < PG; ++u) {
+            if (u < n) {
 #pragma unroll
-            for (int i = 0; i < NV; ++i) {
-              const uint32_t ww[4] = {raw[u][i].x, raw[u][i].y, raw[u][i].z, raw[u][i].w};
+              for (int i = 0; i < NV; ++i) {
+                const uint32_t ww[4] = {buf[u][i].x, buf[u][i].y, buf[u][i].z, buf[u][i].w};
 #pragma unroll
-              for (int q2 = 0; q2 < 4; ++q2) {
-                acc[i][2 * q2] = fmaf(cc[u], __uint_as_float(ww[q2] << 16), acc[i][2 * q2]);
-                acc[i][2 * q2 + 1] = fmaf(cc[u], __uint_as_float(ww[q2] & 0xffff0000u), acc[i][2 * q2 + 1]);
+                for (int q2 = 0; q2 < 4; ++q2) {
+                  acc[i][2 * q2] = fmaf(cf[u], __uint_as_float(ww[q2] << 16), acc[i][2 * q2]);
+                  acc[i][2 * q2 + 1] = fmaf(cf[u], __uint_as_float(ww[q2] & 0xffff0000u), acc[i][2 * q2 + 1]);
+                }
               }
             }
+          }
+        };
+        for (int e0 = lo; e0 < hi; e0 += 32) {
+          int nk = 0;
+          float nc = 0.f;
+          if (e0 + 32 + lane < hi) {     // next chunk's indices + coefficients: in flight behind this chunk's gathers
+            nk = sorted_k[e0 + 32 + lane];
+            nc = coef_row[nk];
+          }
+          const int n = min(32, hi - e0);
+          for (int j = 0; j < n; j += PG) {
+            const int cnt = min(PG, n - j);
+            if (phase == 0) {
+              issue(bufA, cfA, nA, j, cnt);
+              if (pend) consume(bufB, cfB, nB);
+              phase = 1;
+            } else {
+              issue(bufB, cfB, nB, j, cnt);
+              if (pend) consume(bufA, cfA, nA);
+              phase = 0;
+            }
+            pend = true;
+          }
+          myk = nk;
+          myc = nc;
         }
-        for (; j < n; ++j) {
-          const int kq = __shfl_sync(0xffffffffu, myk, j);
-          const float c0 = __shfl_sync(0xffffffffu, myc, j);
-          gb_axpy<T, NV>(sd + (int64_t)(k0 + kq) * D, c0, lane, acc);
+        if (pend) {
+          if (phase == 1) consume(bufA, cfA, nA);
+          else consume(bufB, cfB, nB);
+        }
+      } else {
+      for (int e0 = lo; e0 < hi; e0 += 32) {
+          int myk = 0;
+          float myc = 0.f;
+          if (e0 + lane < hi) {
+            myk = sorted_k[e0 + lane];
+            myc = coef_row[myk];
+          }
+          const int n = min(32, hi - e0);
+          int j = 0;
+          if constexpr (sizeof(T) == 2)  // bf16 rows: keep 4 of them in flight as raw 16-byte vectors
+          for (; j + 4 <= n; j += 4) {
+            uint4 raw[4][NV];
+            float cc[4];
+  #pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int kq = __shfl_sync(0xffffffffu, myk, j + u);
+              cc[u] = __shfl_sync(0xffffffffu, myc, j + u);
+              const T* row = sd + (int64_t)(k0 + kq) * D;
+  #pragma unroll
+              for (int i = 0; i < NV; ++i) raw[u][i] = ldg_hint(row + (i * 32 + lane) * 8, row_pol);
+            }
+  #pragma unroll
+            for (int u = 0; u < 4; ++u)
+  #pragma unroll
+              for (int i = 0; i < NV; ++i) {
+                const uint32_t ww[4] = {raw[u][i].x, raw[u][i].y, raw[u][i].z, raw[u][i].w};
+  #pragma unroll
+                for (int q2 = 0; q2 < 4; ++q2) {
+                  acc[i][2 * q2] = fmaf(cc[u], __uint_as_float(ww[q2] << 16), acc[i][2 * q2]);
+                  acc[i][2 * q2 + 1] = fmaf(cc[u], __uint_as_float(ww[q2] & 0xffff0000u), acc[i][2 * q2 + 1]);
+                }
+              }
+          }
+          for (; j < n; ++j) {
+            const int kq = __shfl_sync(0xffffffffu, myk, j);
+            const float c0 = __shfl_sync(0xffffffffu, myc, j);
+            gb_axpy<T, NV>(sd + (int64_t)(k0 + kq) * D, c0, lane, acc);
+          }
         }
       }
       TO* out = dq + (b * n_tok + t) * (int64_t)D;
@@ -1121,6 +1194,202 @@ static int32_t launch_sparse(const float* g, const TW* w, const int16_t* arg, co
   return ILFDT_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// kernel 2, v4 (bf16 rows): the gather stream of v3 without its bubbles. A measured L2 -> SM gather of 1 KB rows runs
+// at 18.2 TB/s on this part (tools/l2_probe.cu: 64 B/clk/SM, the SM's L2 ingest port; profiles/r02_l2_probe.jsonl),
+// v3 reached 12.3: a warp found ~6 entries per 32-sample tile, gathered them as one batch of 4 and one of 2 and waited
+// out a full L2 latency for each, with a CTA barrier per tile. Here entry DISCOVERY and row GATHERING are decoupled:
+// a warp (one code) pushes the (row, coef) pairs it finds in a tile into a private ring in shared memory and the
+// gather loop pops groups of G rows through a two-deep register pipeline -- the loads of group i+1 are issued before
+// group i is consumed, across tile boundaries and barriers -- so G..2G rows stay in flight per warp at all times.
+// Summation order per code is still sample order: results equal v3's bit for bit.
+// ---------------------------------------------------------------------------------------------
+template <typename T, int NV, int WARPS, int TS, int G>
+__global__ void __launch_bounds__(WARPS * 32)
+ground_bwd_dsd_v4_kernel(const float* __restrict__ coef, const int16_t* __restrict__ arg, const T* __restrict__ q,
+                         const int* __restrict__ row_base, int64_t b_total, int n_tok, int K, int D,
+                         int64_t b_per_split, int use_atomic, float* __restrict__ dsd,
+                         const int* __restrict__ sparse_flag) {
+  static_assert(sizeof(T) == 2, "v4 gathers raw bf16 rows");
+  if (sparse_flag != nullptr && *sparse_flag != 0) return;
+  constexpr int CODES = WARPS, THREADS = WARPS * 32, QUADS = CODES / 4, SLOTS = TS * QUADS;
+  constexpr int LPT = (SLOTS + THREADS - 1) / THREADS, RING = 2 * TS, SUB = TS / 32;
+  static_assert(CODES % 4 == 0 && TS % 32 == 0 && (RING & (RING - 1)) == 0 && RING >= TS + G, "shape");
+  const uint64_t row_pol = l2_policy(false);
+  __shared__ float cf_s[2][CODES][TS + 1];
+  __shared__ int16_t tk_s[2][CODES][TS + 2];
+  __shared__ int rb_s[2][TS];
+  __shared__ int ring_row[WARPS][RING];
+  __shared__ float ring_cf[WARPS][RING];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int k0 = blockIdx.x * CODES;
+  const int64_t b_begin = (int64_t)blockIdx.y * b_per_split;
+  const int64_t b_end = min(b_total, b_begin + b_per_split);
+  const int nblk = (int)((b_end - b_begin + TS - 1) / TS);
+
+  float acc[NV][8];
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+
+  float4 rc[LPT];
+  uint2 rt[LPT];
+  int rb[LPT];
+  auto load_tile = [&](int blk) {
+#pragma unroll
+    for (int l = 0; l < LPT; ++l) {
+      const int slot = threadIdx.x + l * THREADS;
+      const int ld_s = slot / QUADS, ld_q = (slot % QUADS) * 4;
+      const int64_t bb = b_begin + (int64_t)blk * TS + ld_s;
+      rc[l] = make_float4(0.f, 0.f, 0.f, 0.f);
+      rt[l] = make_uint2(0u, 0u);
+      rb[l] = 0;
+      if (slot < SLOTS && bb < b_end) {
+        if (use_atomic & 2) {   // streaming (evict-first) loads: coef / arg are read once, the q rows are the reused data
+          rc[l] = __ldcs(reinterpret_cast<const float4*>(coef + bb * K + k0 + ld_q));
+          rt[l] = __ldcs(reinterpret_cast<const uint2*>(arg + bb * K + k0 + ld_q));
+        } else {
+          rc[l] = __ldg(reinterpret_cast<const float4*>(coef + bb * K + k0 + ld_q));
+          rt[l] = __ldg(reinterpret_cast<const uint2*>(arg + bb * K + k0 + ld_q));
+        }
+        // first q row of the sample: sample * n_tok, or its slab in the compacted text operand (text_buckets.cu)
+        if (ld_q == 0) rb[l] = row_base ? __ldg(row_base + bb) : (int)(bb * n_tok);
+      }
+    }
+  };
+  auto store_tile = [&](int buf) {
+#pragma unroll
+    for (int l = 0; l < LPT; ++l) {
+      const int slot = threadIdx.x + l * THREADS;
+      if (slot < SLOTS) {
+        const int ld_s = slot / QUADS, ld_q = (slot % QUADS) * 4;
+        cf_s[buf][ld_q + 0][ld_s] = rc[l].x; cf_s[buf][ld_q + 1][ld_s] = rc[l].y;
+        cf_s[buf][ld_q + 2][ld_s] = rc[l].z; cf_s[buf][ld_q + 3][ld_s] = rc[l].w;
+        tk_s[buf][ld_q + 0][ld_s] = (int16_t)(rt[l].x & 0xffff); tk_s[buf][ld_q + 1][ld_s] = (int16_t)(rt[l].x >> 16);
+        tk_s[buf][ld_q + 2][ld_s] = (int16_t)(rt[l].y & 0xffff); tk_s[buf][ld_q + 3][ld_s] = (int16_t)(rt[l].y >> 16);
+        if (ld_q == 0) rb_s[buf][ld_s] = rb[l];
+      }
+    }
+  };
+
+  // two-deep register pipeline over the ring
+  uint4 bufA[G][NV], bufB[G][NV];
+  float cfA[G], cfB[G];
+  int nA = 0, nB = 0, phase = 0, head = 0, tail = 0;
+  bool pend = false;
+  int* my_row = ring_row[warp];
+  float* my_cf = ring_cf[warp];
+  auto issue = [&](uint4 (&buf)[G][NV], float (&cf)[G], int& n) {
+    n = min(G, tail - head);
+#pragma unroll
+    for (int u = 0; u < G; ++u) {
+      if (u < n) {
+        const int idx = (head + u) & (RING - 1);
+        cf[u] = my_cf[idx];
+        const T* row = q + (int64_t)my_row[idx] * D;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) buf[u][i] = ldg_hint(row + (i * 32 + lane) * 8, row_pol);
+      }
+    }
+    head += n;
+  };
+  auto consume = [&](const uint4 (&buf)[G][NV], const float (&cf)[G], int n) {
+#pragma unroll
+    for (int u = 0; u < G; ++u) {
+      if (u < n) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+          const uint32_t ww[4] = {buf[u][i].x, buf[u][i].y, buf[u][i].z, buf[u][i].w};
+#pragma unroll
+          for (int q2 = 0; q2 < 4; ++q2) {
+            acc[i][2 * q2] = fmaf(cf[u], __uint_as_float(ww[q2] << 16), acc[i][2 * q2]);
+            acc[i][2 * q2 + 1] = fmaf(cf[u], __uint_as_float(ww[q2] & 0xffff0000u), acc[i][2 * q2 + 1]);
+          }
+        }
+      }
+    }
+  };
+  auto step = [&]() {
+    if (phase == 0) {
+      issue(bufA, cfA, nA);
+      if (pend) consume(bufB, cfB, nB);
+      phase = 1;
+    } else {
+      issue(bufB, cfB, nB);
+      if (pend) consume(bufA, cfA, nA);
+      phase = 0;
+    }
+    pend = true;
+  };
+
+  if (nblk > 0) {
+    load_tile(0);
+    store_tile(0);
+  }
+  __syncthreads();
+  for (int blk = 0; blk < nblk; ++blk) {
+    const int buf = blk & 1;
+    if (blk + 1 < nblk) load_tile(blk + 1);
+    // discovery: this warp's code over the TS samples of the tile -> ring (sample order)
+#pragma unroll
+    for (int sub = 0; sub < SUB; ++sub) {
+      const float cf = cf_s[buf][warp][sub * 32 + lane];
+      const int row = rb_s[buf][sub * 32 + lane] + tk_s[buf][warp][sub * 32 + lane];
+      const unsigned m = __ballot_sync(0xffffffffu, cf != 0.f);
+      if (cf != 0.f) {
+        const int pos = (tail + __popc(m & ((1u << lane) - 1u))) & (RING - 1);
+        my_row[pos] = row;
+        my_cf[pos] = cf;
+      }
+      tail += __popc(m);
+    }
+    __syncwarp();
+    while (tail - head >= G) step();
+    if (blk + 1 < nblk) store_tile(buf ^ 1);
+    __syncthreads();
+  }
+  while (tail - head > 0) step();
+  if (pend) {
+    if (phase == 1) consume(bufA, cfA, nA);
+    else consume(bufB, cfB, nB);
+  }
+  float* out = dsd + (int64_t)(k0 + warp) * D;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    float* o = out + (i * 32 + lane) * 8;
+    if (use_atomic & 1) {
+      asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o), "f"(acc[i][0]), "f"(acc[i][1]), "f"(acc[i][2]),
+                   "f"(acc[i][3]) : "memory");
+      asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o + 4), "f"(acc[i][4]), "f"(acc[i][5]), "f"(acc[i][6]),
+                   "f"(acc[i][7]) : "memory");
+    } else {
+      StoreRow8<float>::st(o, acc[i], true);
+    }
+  }
+}
+
+template <typename T, int NV, int WARPS, int TS, int G>
+static int32_t launch_dsd_v4(const float* g, const int16_t* arg, const T* q, const int* row_base, int64_t b, int64_t n_tok,
+                             int64_t K, int64_t D, float* dsd, const int* sparse_flag, cudaStream_t st) {
+  constexpr int CODES = WARPS;
+  const int64_t groups = K / CODES;
+  int64_t nsplit = 1;
+  const int64_t target = 4ll * sm_count();
+  if (groups < target) nsplit = std::min<int64_t>(cdiv(target, groups), std::max<int64_t>(1, b / 256));
+  const int64_t split_rows = tune_get(ILFDT_TUNE_DSD_SPLIT_ROWS);   // see launch_dsd_v3
+  if (split_rows > 0 && b >= 2 * split_rows) nsplit = std::max<int64_t>(nsplit, b / split_rows);
+  const int stream_flag = tune_get(ILFDT_TUNE_DSD_STREAM) ? 2 : 0;
+  nsplit = std::min<int64_t>(std::max<int64_t>(nsplit, 1), 65535);
+  int64_t per = round_up(cdiv(b, nsplit), TS);
+  nsplit = cdiv(b, per);
+  dim3 grid((unsigned)groups, (unsigned)nsplit);
+  ground_bwd_dsd_v4_kernel<T, NV, WARPS, TS, G><<<grid, WARPS * 32, 0, st>>>(g, arg, q, row_base, b, (int)n_tok, (int)K, (int)D,
+                                                                        per, (nsplit > 1 ? 1 : 0) | stream_flag, dsd, sparse_flag);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
 template <typename T, int NV, int WARPS, int CPW, int U, int TS = 32>
 static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, const int* row_base, int64_t b, int64_t n_tok,
                              int64_t K, int64_t D, float* dsd, const int* sparse_flag, cudaStream_t st) {
@@ -1148,19 +1417,31 @@ static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, con
   return ILFDT_OK;
 }
 
+template <typename T, int NV, typename TO, typename TW, int PG, int MINB>
+static int32_t launch_dq_v3_t(float* g, const TW* w, const int16_t* arg, const T* sd, const float* mask, int64_t b,
+                              int64_t n_tok, int64_t K, int64_t D, float inv_scale, TO* dq, const int* sparse_flag,
+                              cudaStream_t st) {
+  const size_t smem = (size_t)n_tok * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 + (G3_MAX_TOK + 1) * sizeof(int) +
+                      G3_MAX_TOK * sizeof(float);
+  ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_v3_kernel<T, NV, TO, TW, PG, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)((size_t)G3_MAX_TOK * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 +
+                                           (G3_MAX_TOK + 1) * sizeof(int) + G3_MAX_TOK * sizeof(float))));
+  ground_bwd_dq_v3_kernel<T, NV, TO, TW, PG, MINB><<<(unsigned)b, G3_THREADS, smem, st>>>(g, w, arg, sd, mask, (int)n_tok,
+                                                                                     (int)K, (int)D, inv_scale, dq, sparse_flag);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
 template <typename T, int NV, typename TO, typename TW>
 static int32_t launch_dq_v3(float* g, const TW* w, const int16_t* arg, const T* sd, const float* mask, int64_t b,
                             int64_t n_tok, int64_t K, int64_t D, float inv_scale, TO* dq, const int* sparse_flag,
                             cudaStream_t st) {
-  const size_t smem = (size_t)n_tok * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 + (G3_MAX_TOK + 1) * sizeof(int) +
-                      G3_MAX_TOK * sizeof(float);
-  ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_v3_kernel<T, NV, TO, TW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)((size_t)G3_MAX_TOK * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 +
-                                           (G3_MAX_TOK + 1) * sizeof(int) + G3_MAX_TOK * sizeof(float))));
-  ground_bwd_dq_v3_kernel<T, NV, TO, TW><<<(unsigned)b, G3_THREADS, smem, st>>>(g, w, arg, sd, mask, (int)n_tok, (int)K,
-                                                                           (int)D, inv_scale, dq, sparse_flag);
-  ILFDT_LAUNCH_OK();
-  return ILFDT_OK;
+  if constexpr (sizeof(T) == 2 && NV <= 2) {
+    const int64_t pipe = tune_get(ILFDT_TUNE_DQ_PIPE);   // 0 = batches of 4 with exposed latency (r1), 1 / 2 = pipelined
+    if (pipe == 1) return launch_dq_v3_t<T, NV, TO, TW, 2, 3>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, sparse_flag, st);
+    if (pipe == 2) return launch_dq_v3_t<T, NV, TO, TW, 4, 2>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, sparse_flag, st);
+  }
+  return launch_dq_v3_t<T, NV, TO, TW, 0, 3>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, sparse_flag, st);
 }
 
 template <typename T, int NV>
@@ -1258,6 +1539,17 @@ static int32_t launch_ground_bwd_t(float* g, const void* w_v, int w_dtype, const
     // (profiles/r01_tune_dsd_shapes.txt): 4x1 codes with 4 rows in flight beat the original 4x4/2 by 1.4x.
     // ILFDT_TUNE_DSD_TILE = 128 selects the 128-sample cooperative tile (better when the support is tens of codes).
     if (K % 32 == 0 && ((reinterpret_cast<uintptr_t>(g) & 15) | (reinterpret_cast<uintptr_t>(arg) & 7)) == 0) {
+      if constexpr (NV <= 2 && sizeof(T) == 2) {
+        // bf16 rows: pipelined gather stream (v4); ILFDT_TUNE_DSD_PIPE = 0 selects the v3 kernel, 2 / 3 other shapes
+        const int64_t pipe = tune_get(ILFDT_TUNE_DSD_PIPE);
+        if (b * n_tok < (1ll << 31)) {
+          if (pipe == 1) return launch_dsd_v4<T, NV, 4, 64, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
+          if (pipe == 2) return launch_dsd_v4<T, NV, 8, 64, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
+          if (pipe == 3) return launch_dsd_v4<T, NV, 4, 128, 8>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
+          if (pipe == 4) return launch_dsd_v4<T, NV, 4, 64, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
+          if (pipe == 5) return launch_dsd_v4<T, NV, 8, 32, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
+        }
+      }
       if constexpr (NV <= 2) {
         if (tune_get(ILFDT_TUNE_DSD_TILE) == 128)
           return launch_dsd_v3<T, NV, 4, 1, 4, 128>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
