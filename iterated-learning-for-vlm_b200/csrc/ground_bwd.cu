@@ -1540,14 +1540,14 @@ static int32_t launch_ground_bwd_t(float* g, const void* w_v, int w_dtype, const
     // ILFDT_TUNE_DSD_TILE = 128 selects the 128-sample cooperative tile (better when the support is tens of codes).
     if (K % 32 == 0 && ((reinterpret_cast<uintptr_t>(g) & 15) | (reinterpret_cast<uintptr_t>(arg) & 7)) == 0) {
       if constexpr (NV <= 2 && sizeof(T) == 2) {
-        // bf16 rows: pipelined gather stream (v4); ILFDT_TUNE_DSD_PIPE = 0 selects the v3 kernel, 2 / 3 other shapes
+        // bf16 rows: pipelined gather stream (v4); ILFDT_TUNE_DSD_PIPE = 0 selects the v3 kernel, 2 = groups of 4 rows
         const int64_t pipe = tune_get(ILFDT_TUNE_DSD_PIPE);
         if (b * n_tok < (1ll << 31)) {
-          if (pipe == 1) return launch_dsd_v4<T, NV, 4, 64, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
-          if (pipe == 2) return launch_dsd_v4<T, NV, 8, 64, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
-          if (pipe == 3) return launch_dsd_v4<T, NV, 4, 128, 8>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
-          if (pipe == 4) return launch_dsd_v4<T, NV, 4, 64, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
-          if (pipe == 5) return launch_dsd_v4<T, NV, 8, 32, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
+          // shapes measured at b = 32768 (tools/time_gbwd.py, profiles/r02_time_gbwd.txt; both kernels, image + text):
+          // v3 33.6 ms, 4 codes x 64 samples with groups of 2 rows 31.5 ms (default: 80 registers, 6 CTAs / SM),
+          // groups of 4 rows 33.3 ms (118 registers), 128-sample tiles 31.5 ms, 8 codes per CTA 32.8 ms
+          if (pipe == 1) return launch_dsd_v4<T, NV, 4, 64, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
+          if (pipe == 2) return launch_dsd_v4<T, NV, 4, 64, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
         }
       }
       if constexpr (NV <= 2) {
