@@ -1,9 +1,11 @@
 #!/bin/bash
-# one ncu --set full capture of the two tensor-core kernels of the step at global batch ${GB:-32768}:
-# ground2_kernel<49> (image grounding) and nce_bwd_kernel (InfoNCE backward). usage: ncu_step.sh <out> [count]
-cd "$(dirname "$0")/.."
-ARGS="--steps 1 --warmup 1 --global-batch ${GB:-32768} --no-cpu-baseline --no-e2e"
-python bench.py $ARGS > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/plain.log; exit 1; }
-ncu --set full --clock-control none --import-source on --kernel-name-base demangled \
-    -k 'regex:ground2_kernel<.int.49|nce_bwd_kernel' -c ${2:-4} -f -o gpurun_out/${1:-prof_step} python bench.py $ARGS > gpurun_out/ncu_step.log 2>&1
-tail -2 gpurun_out/ncu_step.log
+# ncu --set full capture of the hot kernels inside one headline-size step (second step of tools/step_once.py).
+#   gpurun --timeout 1800 -- 'bash tools/ncu_step.sh'   -> gpurun_out/r02_step.ncu-rep + r02_step_raw.csv
+set -x
+mkdir -p gpurun_out
+python tools/step_once.py --steps 2 > /dev/null 2>&1 || exit 1
+ncu --set full --import-source on --clock-control none \
+    -k regex:"sparsemax_fwd_reg_kernel|nce_bwd2_kernel|ground_bwd_dq_v3_kernel|ground_bwd_dsd_v4_kernel|ground2_kernel" \
+    --launch-skip 14 --launch-count 14 -f -o gpurun_out/r02_step python tools/step_once.py --steps 2 > gpurun_out/ncu_step.log 2>&1
+ncu -i gpurun_out/r02_step.ncu-rep --page raw --csv > gpurun_out/r02_step_raw.csv 2>/dev/null
+ls -la gpurun_out/r02_step.ncu-rep gpurun_out/r02_step_raw.csv
