@@ -134,6 +134,13 @@ int32_t ilfdt_sparsemax_bwd(const float* w, const float* g, int64_t rows, int64_
  * BF16: tcgen05 kernel (M % 128 == 0, Kr % 64 == 0 required); F32: SIMT kernel, any shape. */
 int32_t ilfdt_gemm_nt(const void* A, const void* B, int32_t dtype, int64_t M, int64_t N, int64_t Kr,
                       float alpha, int32_t accumulate, float* out, int64_t ldo, void* stream);
+/* ilfdt_gemm_nt (BF16) for a SHORT A, FEW B rows and a long reduction -- the pooling f[b,D] = w[b,K] . sd[K,D] of
+ * clip_fdt.py:154 at a per-GPU batch of a few hundred rows (run.sh: 256), where the unsplit launch has 1..16 tiles for 148
+ * SMs: the reduction is cut over the CTA pairs into slabs of `ws`, added in a fixed order (deterministic, no atomics).
+ * ws: ilfdt_gemm_nt_splitk_ws_bytes(M, N, Kr); 0 = this shape is not split (the call then equals ilfdt_gemm_nt). */
+int64_t ilfdt_gemm_nt_splitk_ws_bytes(int64_t M, int64_t N, int64_t Kr);
+int32_t ilfdt_gemm_nt_splitk(const void* A_bf16, const void* B_bf16, int64_t M, int64_t N, int64_t Kr, float alpha,
+                             int32_t accumulate, float* out, int64_t ldo, void* ws, int64_t ws_bytes, void* stream);
 /* out[N, M] (+)= alpha * B[Kr,N]^T . A[Kr,M] for bf16 operands stored with the REDUCTION index outermost (tcgen05
  * MN-major operands: no transposed copies). dsd[K,D] += w[b,K]^T . df[b,D] of the pooling backward
  * (clip_fdt.py:154): A = df, B = w, M = D, N = K, Kr = b. M, N multiples of 8. */

@@ -37,6 +37,12 @@ struct W2Params {
   float* out;
   long long ldo;
   uint32_t idesc[2];
+  // split reduction (few B rows, e.g. a per-GPU batch of 256: one CTA pair would do the whole 16384-long reduction
+  // alone): item = pair * ksplit + ks contracts k-blocks [ks * kb_per, (ks + 1) * kb_per) into slab ks (dense
+  // [n_rows, m_rows] fp32); w2_reduce_kernel adds the slabs in a fixed order (deterministic, no atomics)
+  int ksplit, kb_per;
+  float* slab;
+  long long slab_stride;
 };
 
 struct W2Bars {
@@ -76,9 +82,11 @@ gemm_wide2_kernel(const __grid_constant__ CUtensorMap tmLane, const __grid_const
     // ===================== TMA producer (one thread in each CTA) =====================
     if (elect_one()) {
       uint32_t stage = 0, phase = 0;
-      for (int item = cluster_id; item < p.num_pairs; item += num_clusters) {
-        const int lane_row0 = (2 * item + (int)rank) * 128;
-        for (int kb = 0; kb < p.nkb; ++kb) {
+      for (int item = cluster_id; item < p.num_pairs * p.ksplit; item += num_clusters) {
+        const int pair = item / p.ksplit, ks = item - pair * p.ksplit;
+        const int lane_row0 = (2 * pair + (int)rank) * 128;
+        const int kb_end = min(p.nkb, (ks + 1) * p.kb_per);
+        for (int kb = ks * p.kb_per; kb < kb_end; ++kb) {
           mbar_wait(&bars->empty[stage], phase ^ 1);
           if (leader) mbar_expect_tx(&bars->full[stage], stage_tx);
           uint8_t* st = smem + stage * W2_STAGE;
@@ -94,10 +102,12 @@ gemm_wide2_kernel(const __grid_constant__ CUtensorMap tmLane, const __grid_const
     // ===================== MMA issuer (leader CTA only) =====================
     if (leader && elect_one()) {
       uint32_t stage = 0, phase = 0, it = 0;
-      for (int item = cluster_id; item < p.num_pairs; item += num_clusters, ++it) {
+      for (int item = cluster_id; item < p.num_pairs * p.ksplit; item += num_clusters, ++it) {
+        const int ks = item % p.ksplit;
+        const int kb0 = ks * p.kb_per, kb_end = min(p.nkb, (ks + 1) * p.kb_per);
         mbar_wait(&bars->tmem_empty, (it & 1) ^ 1);   // both CTAs' epilogues of the previous item are done
         fence_after_sync();
-        for (int kb = 0; kb < p.nkb; ++kb) {
+        for (int kb = kb0; kb < kb_end; ++kb) {
           mbar_wait(&bars->full[stage], phase);
           fence_after_sync();
           const uint8_t* st = smem + stage * W2_STAGE;
@@ -107,7 +117,7 @@ gemm_wide2_kernel(const __grid_constant__ CUtensorMap tmLane, const __grid_const
 #pragma unroll
             for (int k4 = 0; k4 < 4; ++k4)
               mma_f16_pair(tmem_base + a * 256, advance_desc_k(adesc, k4 * 32), advance_desc_k(bdesc, k4 * 32),
-                           p.idesc[a], (kb | k4) != 0 ? 1u : 0u);
+                           p.idesc[a], ((kb - kb0) | k4) != 0 ? 1u : 0u);
           }
           mma_commit_pair(&bars->empty[stage]);
           if (++stage == W2_STAGES) { stage = 0; phase ^= 1; }
@@ -121,14 +131,19 @@ gemm_wide2_kernel(const __grid_constant__ CUtensorMap tmLane, const __grid_const
     const int group = (warp - 2) >> 2;
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     uint32_t it = 0;
-    for (int item = cluster_id; item < p.num_pairs; item += num_clusters, ++it) {
-      const int row = (2 * item + (int)rank) * 128 + quad * 32 + lane;   // row of B = row of out owned by this thread
+    for (int item = cluster_id; item < p.num_pairs * p.ksplit; item += num_clusters, ++it) {
+      const int pair = item / p.ksplit, ks = item - pair * p.ksplit;
+      const int row = (2 * pair + (int)rank) * 128 + quad * 32 + lane;   // row of B = row of out owned by this thread
       const bool row_ok = row < p.n_rows;
       mbar_wait(&bars->tmem_full, it & 1);
       fence_after_sync();
       if (group < p.nacc) {
         const int ncols = min(256, p.m_rows - group * 256);
-        float* o = p.out + (int64_t)row * p.ldo + group * 256;
+        const bool split = p.ksplit > 1;
+        float* o = split ? p.slab + ks * p.slab_stride + (int64_t)row * p.m_rows + group * 256
+                         : p.out + (int64_t)row * p.ldo + group * 256;
+        const float alpha = split ? 1.f : p.alpha;
+        const int accumulate = split ? 0 : p.accumulate;
         for (int c0 = 0; c0 < ncols; c0 += 32) {
           uint32_t v[32];
           tmem_ld32(tmem_base + lane_addr + group * 256 + c0, v);
@@ -137,16 +152,16 @@ gemm_wide2_kernel(const __grid_constant__ CUtensorMap tmLane, const __grid_const
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
               if (c0 + j + 3 < ncols) {
-                float4 r = make_float4(__uint_as_float(v[j]) * p.alpha, __uint_as_float(v[j + 1]) * p.alpha,
-                                       __uint_as_float(v[j + 2]) * p.alpha, __uint_as_float(v[j + 3]) * p.alpha);
+                float4 r = make_float4(__uint_as_float(v[j]) * alpha, __uint_as_float(v[j + 1]) * alpha,
+                                       __uint_as_float(v[j + 2]) * alpha, __uint_as_float(v[j + 3]) * alpha);
                 float4* dst = reinterpret_cast<float4*>(o + c0 + j);
-                if (p.accumulate) { const float4 q = *dst; r.x += q.x; r.y += q.y; r.z += q.z; r.w += q.w; }
+                if (accumulate) { const float4 q = *dst; r.x += q.x; r.y += q.y; r.z += q.z; r.w += q.w; }
                 *dst = r;
               } else {
                 for (int e = 0; e < 4; ++e)
                   if (c0 + j + e < ncols) {
-                    const float r = __uint_as_float(v[j + e]) * p.alpha;
-                    o[c0 + j + e] = p.accumulate ? o[c0 + j + e] + r : r;
+                    const float r = __uint_as_float(v[j + e]) * alpha;
+                    o[c0 + j + e] = accumulate ? o[c0 + j + e] + r : r;
                   }
               }
             }
@@ -176,10 +191,52 @@ bool gemm_wide2_supported(int64_t M, int64_t N, int64_t Kr, const float* out, in
          ldo % 4 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
 }
 
-// out[n, m] (+)= alpha * sum_k B[n,k] A[m,k]; A [M, Kr], B [N, Kr] bf16 row-major
+// out[n, m] (+)= alpha * sum_ks slab[ks][n, m]   (m_rows % 4 == 0)
+__global__ void __launch_bounds__(256) w2_reduce_kernel(const float* __restrict__ slab, int ksplit, long long stride,
+                                                        int n_rows, int m_rows, float alpha, int accumulate,
+                                                        float* __restrict__ out, long long ldo) {
+  const long long i4 = (long long)blockIdx.x * 256 + threadIdx.x;     // float4 index over [n_rows, m_rows]
+  const int m4 = m_rows >> 2;
+  if (i4 >= (long long)n_rows * m4) return;
+  const int n = (int)(i4 / m4), m = (int)(i4 - (long long)n * m4) * 4;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int ks = 0; ks < ksplit; ++ks) {
+    const float4 v = __ldcs(reinterpret_cast<const float4*>(slab + ks * stride + (long long)n * m_rows + m));
+    acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+  }
+  float4* dst = reinterpret_cast<float4*>(out + (long long)n * ldo + m);
+  float4 r = make_float4(acc.x * alpha, acc.y * alpha, acc.z * alpha, acc.w * alpha);
+  if (accumulate) { const float4 q = *dst; r.x += q.x; r.y += q.y; r.z += q.z; r.w += q.w; }
+  *dst = r;
+}
+
+static int w2_clusters() {
+  return std::max(1, sm_count() / 2);
+}
+// how the reduction is cut for a launch with few B rows: 1 = not at all
+static int w2_ksplit(int64_t M, int64_t N, int64_t Kr) {
+  const int64_t pairs = cdiv(N, 256), nkb = cdiv(Kr, 64);
+  if (M % 4 != 0 || pairs * 2 > w2_clusters() || nkb < 16) return 1;
+  return (int)std::max<int64_t>(1, std::min<int64_t>(w2_clusters() / pairs, nkb / 4));
+}
+bool gemm_wide2_split_supported(int64_t M, int64_t N, int64_t Kr, const float* out, int64_t ldo) {
+  return M >= 16 && M <= 512 && M % 16 == 0 && (M <= 256 || M % 32 == 0) && N >= 1 && Kr >= 1024 && Kr % 8 == 0 && ldo % 4 == 0 &&
+         (reinterpret_cast<uintptr_t>(out) & 15) == 0 && w2_ksplit(M, N, Kr) > 1;
+}
+int64_t gemm_wide2_ws_floats(int64_t M, int64_t N, int64_t Kr) {
+  const int ks = w2_ksplit(M, N, Kr);
+  return ks > 1 ? (int64_t)ks * round_up(N, 256) * M : 0;
+}
+
+// out[n, m] (+)= alpha * sum_k B[n,k] A[m,k]; A [M, Kr], B [N, Kr] bf16 row-major. ws != nullptr: split reduction.
 int32_t launch_gemm_wide2(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha, int accumulate,
-                          float* out, int64_t ldo, cudaStream_t st) {
+                          float* out, int64_t ldo, cudaStream_t st, float* ws) {
   W2Params p{};
+  p.ksplit = ws != nullptr ? w2_ksplit(M, N, Kr) : 1;
+  p.kb_per = (int)cdiv(cdiv(Kr, 64), p.ksplit);
+  p.ksplit = (int)cdiv(cdiv(Kr, 64), p.kb_per);
+  p.slab = ws;
+  p.slab_stride = round_up(N, 256) * M;
   p.n_rows = (int)N;
   p.m_rows = (int)M;
   p.nkb = (int)cdiv(Kr, 64);
@@ -221,8 +278,14 @@ int32_t launch_gemm_wide2(const void* A, const void* B, int64_t M, int64_t N, in
     max_clusters = std::min(n, sm_count() / 2);
     configured_dev = dev;
   }
-  cfg.gridDim = dim3(2 * std::min(p.num_pairs, max_clusters));
+  cfg.gridDim = dim3(2 * std::min(p.num_pairs * p.ksplit, max_clusters));
   ILFDT_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_wide2_kernel, tmLane, tmCol, p));
+  if (p.ksplit > 1) {
+    const long long n4 = (long long)N * (M / 4);
+    w2_reduce_kernel<<<(unsigned)cdiv(n4, 256), 256, 0, st>>>(ws, p.ksplit, p.slab_stride, (int)N, (int)M, alpha, accumulate, out,
+                                                            ldo);
+    ILFDT_LAUNCH_OK();
+  }
   return ILFDT_OK;
 }
 

@@ -1204,7 +1204,7 @@ static int32_t launch_sparse(const float* g, const TW* w, const int16_t* arg, co
 // group i is consumed, across tile boundaries and barriers -- so G..2G rows stay in flight per warp at all times.
 // Summation order per code is still sample order: results equal v3's bit for bit.
 // ---------------------------------------------------------------------------------------------
-template <typename T, int NV, int WARPS, int TS, int G>
+template <typename T, int NV, int WARPS, int TS, int G, bool F2 = false>
 __global__ void __launch_bounds__(WARPS * 32)
 ground_bwd_dsd_v4_kernel(const float* __restrict__ coef, const int16_t* __restrict__ arg, const T* __restrict__ q,
                          const int* __restrict__ row_base, int64_t b_total, int n_tok, int K, int D,
@@ -1303,8 +1303,13 @@ ground_bwd_dsd_v4_kernel(const float* __restrict__ coef, const int16_t* __restri
           const uint32_t ww[4] = {buf[u][i].x, buf[u][i].y, buf[u][i].z, buf[u][i].w};
 #pragma unroll
           for (int q2 = 0; q2 < 4; ++q2) {
-            acc[i][2 * q2] = fmaf(cf[u], __uint_as_float(ww[q2] << 16), acc[i][2 * q2]);
-            acc[i][2 * q2 + 1] = fmaf(cf[u], __uint_as_float(ww[q2] & 0xffff0000u), acc[i][2 * q2 + 1]);
+            if constexpr (F2) {
+              ffma2(acc[i][2 * q2], acc[i][2 * q2 + 1], cf[u], __uint_as_float(ww[q2] << 16),
+                    __uint_as_float(ww[q2] & 0xffff0000u));
+            } else {
+              acc[i][2 * q2] = fmaf(cf[u], __uint_as_float(ww[q2] << 16), acc[i][2 * q2]);
+              acc[i][2 * q2 + 1] = fmaf(cf[u], __uint_as_float(ww[q2] & 0xffff0000u), acc[i][2 * q2 + 1]);
+            }
           }
         }
       }
@@ -1369,7 +1374,7 @@ ground_bwd_dsd_v4_kernel(const float* __restrict__ coef, const int16_t* __restri
   }
 }
 
-template <typename T, int NV, int WARPS, int TS, int G>
+template <typename T, int NV, int WARPS, int TS, int G, bool F2 = false>
 static int32_t launch_dsd_v4(const float* g, const int16_t* arg, const T* q, const int* row_base, int64_t b, int64_t n_tok,
                              int64_t K, int64_t D, float* dsd, const int* sparse_flag, cudaStream_t st) {
   constexpr int CODES = WARPS;
@@ -1384,8 +1389,9 @@ static int32_t launch_dsd_v4(const float* g, const int16_t* arg, const T* q, con
   int64_t per = round_up(cdiv(b, nsplit), TS);
   nsplit = cdiv(b, per);
   dim3 grid((unsigned)groups, (unsigned)nsplit);
-  ground_bwd_dsd_v4_kernel<T, NV, WARPS, TS, G><<<grid, WARPS * 32, 0, st>>>(g, arg, q, row_base, b, (int)n_tok, (int)K, (int)D,
-                                                                        per, (nsplit > 1 ? 1 : 0) | stream_flag, dsd, sparse_flag);
+  ground_bwd_dsd_v4_kernel<T, NV, WARPS, TS, G, F2><<<grid, WARPS * 32, 0, st>>>(g, arg, q, row_base, b, (int)n_tok, (int)K, (int)D,
+                                                                            per, (nsplit > 1 ? 1 : 0) | stream_flag, dsd,
+                                                                            sparse_flag);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
 }
@@ -1548,6 +1554,8 @@ static int32_t launch_ground_bwd_t(float* g, const void* w_v, int w_dtype, const
           // groups of 4 rows 33.3 ms (118 registers), 128-sample tiles 31.5 ms, 8 codes per CTA 32.8 ms
           if (pipe == 1) return launch_dsd_v4<T, NV, 4, 64, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
           if (pipe == 2) return launch_dsd_v4<T, NV, 4, 64, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
+          if (pipe == 3) return launch_dsd_v4<T, NV, 4, 64, 2, true>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
+          if (pipe == 4) return launch_dsd_v4<T, NV, 4, 64, 4, true>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
         }
       }
       if constexpr (NV <= 2) {

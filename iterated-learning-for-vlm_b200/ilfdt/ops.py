@@ -20,7 +20,7 @@ LAUNCHES = 0          # kernels launched through this module since it was last z
 PROFILE_ON = False    # when True every C call is bracketed by CUDA events on the launching stream
 PROFILE = {}          # op name -> [(start_event, end_event), ...]
 _KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mask_rows_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_ground_fwd_text": 5, "ilfdt_text_compact": 3, "ilfdt_sparsemax_fwd": 1,
-                     "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2, "ilfdt_ground_bwd_w16": 2,   # + 2 regime launches that return at once
+                     "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_nt_splitk": 2, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2, "ilfdt_ground_bwd_w16": 2,   # + 2 regime launches that return at once
                      "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5, "ilfdt_nce_lse": 2, "ilfdt_nce_loss": 1,
                      "ilfdt_nce_bwd": 4, "ilfdt_nce_bwd_gathered": 2, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
                      "ilfdt_randn_fill": 1, "ilfdt_copy": 0,
@@ -218,6 +218,13 @@ def gemm_nt(A, B, alpha=1.0, out=None, accumulate=False):
         assert not accumulate
         out = torch.empty(N, M, dtype=torch.float32, device=A.device)
     _req(out, torch.float32, "out")
+    if A.dtype == torch.bfloat16:
+        nws = _lib.load().ilfdt_gemm_nt_splitk_ws_bytes(M, N, Kr)   # > 0: few rows, long reduction (pooling at small batch)
+        if nws > 0:
+            ws = torch.empty(nws, dtype=torch.uint8, device=A.device)
+            _call("ilfdt_gemm_nt_splitk", _ptr(A), _ptr(B), M, N, Kr, float(alpha), int(accumulate), _ptr(out), out.shape[1],
+                  _ptr(ws), nws, _stream())
+            return out
     _call("ilfdt_gemm_nt", _ptr(A), _ptr(B), _DT[A.dtype], M, N, Kr, float(alpha), int(accumulate),
                                     _ptr(out), out.shape[1], _stream())
     return out

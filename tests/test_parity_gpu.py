@@ -66,7 +66,8 @@ def test_gemm_f32_strided(ops, M, N, K, a_t, b_t):
 
 @pytest.mark.parametrize("M,N,K", [(128, 64, 64), (128, 256, 512), (256, 300, 512), (200, 77, 128), (512, 1000, 1024),
                                    (512, 2048, 4096), (256, 1500, 2048), (64, 1024, 1032), (384, 1100, 16384),   # CTA-pair route
-                                   (128, 16, 8), (384, 2050, 16384)])
+                                   (128, 16, 8), (384, 2050, 16384),
+                                   (512, 256, 16384), (512, 64, 4096), (256, 4096, 16384), (384, 300, 2048), (512, 7, 1024)])  # split reduction
 def test_gemm_nt_tcgen05(ops, M, N, K):
     g = torch.Generator().manual_seed(M + N + K)
     A = bf16_round(torch.randn(M, K, generator=g))
