@@ -284,6 +284,24 @@ int32_t ilfdt_gemm_nt(const void* A, const void* B, int32_t dtype, int64_t M, in
   return launch_gemm_nt_bf16(A, B, M, N, Kr, alpha, nullptr, accumulate, out, ldo, ST(stream));
 }
 
+int64_t ilfdt_gemm_nt_splitk_ws_bytes(int64_t M, int64_t N, int64_t Kr) {
+  return gemm_wide2_enabled() ? gemm_wide2_ws_floats(M, N, Kr) * 4 : 0;
+}
+
+int32_t ilfdt_gemm_nt_splitk(const void* A_bf16, const void* B_bf16, int64_t M, int64_t N, int64_t Kr, float alpha,
+                             int32_t accumulate, float* out, int64_t ldo, void* ws, int64_t ws_bytes, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(M >= 0 && N >= 0 && Kr >= 1 && ldo >= M, ILFDT_E_INVALID_ARG, "gemm_nt_splitk: bad shape");
+  ILFDT_REQUIRE(M == 0 || N == 0 || (A_bf16 && B_bf16 && out), ILFDT_E_INVALID_ARG, "gemm_nt_splitk: null pointer");
+  if (M == 0 || N == 0) return ILFDT_OK;
+  const int64_t need = ilfdt_gemm_nt_splitk_ws_bytes(M, N, Kr);
+  if (need > 0 && gemm_wide2_split_supported(M, N, Kr, out, ldo)) {
+    ILFDT_REQUIRE(ws != nullptr && ws_bytes >= need, ILFDT_E_INVALID_ARG, "gemm_nt_splitk: workspace too small");
+    return launch_gemm_wide2(A_bf16, B_bf16, M, N, Kr, alpha, accumulate, out, ldo, ST(stream), reinterpret_cast<float*>(ws));
+  }
+  return launch_gemm_nt_bf16(A_bf16, B_bf16, M, N, Kr, alpha, nullptr, accumulate, out, ldo, ST(stream));
+}
+
 int32_t ilfdt_gemm_tn(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha, int32_t accumulate,
                       float* out, int64_t ldo, void* stream) {
   ARCH_GUARD();
