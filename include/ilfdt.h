@@ -64,8 +64,8 @@ enum {
   ILFDT_TUNE_SPARSE_BWD_NNZ = 6, /* ilfdt_ground_bwd*: mean support (codes per row) up to which the sparse-regime kernel
                                     serves the launch (default 128; 0 = always the dense sweeps) */
   ILFDT_TUNE_DSD_PIPE = 7,       /* ilfdt_ground_bwd* (bf16 rows): 1 (default) = pipelined gather stream (dsd v4: 4 codes x 64
-                                    samples per tile, groups of 2 rows in a two-deep register pipeline); 2 = groups of 4
-                                    rows; 0 = the v3 kernel. Same summation order: identical results */
+                                    samples per tile, groups of 2 rows in a two-deep register pipeline, packed FFMA2); 2 =
+                                    groups of 4 rows; 3 = scalar FMAs; 0 = the v3 kernel. Same summation order: identical results */
   ILFDT_TUNE_DQ_PIPE = 8,        /* ilfdt_ground_bwd* (bf16 rows): per-sample kernel's gather loop: 0 = batches of 4 rows, 1 =
                                     pipelined groups of 2 (3 CTAs / SM), 2 = pipelined groups of 4 (2 CTAs / SM). Same order */
   ILFDT_TUNE_COUNT_ = 9

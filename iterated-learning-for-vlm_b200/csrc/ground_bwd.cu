@@ -803,24 +803,23 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const i
           for (; j + 4 <= n; j += 4) {
             uint4 raw[4][NV];
             float cc[4];
-  #pragma unroll
+#pragma unroll
             for (int u = 0; u < 4; ++u) {
               const int kq = __shfl_sync(0xffffffffu, myk, j + u);
               cc[u] = __shfl_sync(0xffffffffu, myc, j + u);
               const T* row = sd + (int64_t)(k0 + kq) * D;
-  #pragma unroll
+#pragma unroll
               for (int i = 0; i < NV; ++i) raw[u][i] = ldg_hint(row + (i * 32 + lane) * 8, row_pol);
             }
-  #pragma unroll
+#pragma unroll
             for (int u = 0; u < 4; ++u)
-  #pragma unroll
+#pragma unroll
               for (int i = 0; i < NV; ++i) {
                 const uint32_t ww[4] = {raw[u][i].x, raw[u][i].y, raw[u][i].z, raw[u][i].w};
-  #pragma unroll
-                for (int q2 = 0; q2 < 4; ++q2) {
-                  acc[i][2 * q2] = fmaf(cc[u], __uint_as_float(ww[q2] << 16), acc[i][2 * q2]);
-                  acc[i][2 * q2 + 1] = fmaf(cc[u], __uint_as_float(ww[q2] & 0xffff0000u), acc[i][2 * q2 + 1]);
-                }
+#pragma unroll
+                for (int q2 = 0; q2 < 4; ++q2)   // packed fp32x2 FMA: same bits, half the issue slots
+                  ffma2(acc[i][2 * q2], acc[i][2 * q2 + 1], cc[u], __uint_as_float(ww[q2] << 16),
+                        __uint_as_float(ww[q2] & 0xffff0000u));
               }
           }
           for (; j < n; ++j) {
@@ -1552,10 +1551,10 @@ static int32_t launch_ground_bwd_t(float* g, const void* w_v, int w_dtype, const
           // shapes measured at b = 32768 (tools/time_gbwd.py, profiles/r02_time_gbwd.txt; both kernels, image + text):
           // v3 33.6 ms, 4 codes x 64 samples with groups of 2 rows 31.5 ms (default: 80 registers, 6 CTAs / SM),
           // groups of 4 rows 33.3 ms (118 registers), 128-sample tiles 31.5 ms, 8 codes per CTA 32.8 ms
-          if (pipe == 1) return launch_dsd_v4<T, NV, 4, 64, 2>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
-          if (pipe == 2) return launch_dsd_v4<T, NV, 4, 64, 4>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
-          if (pipe == 3) return launch_dsd_v4<T, NV, 4, 64, 2, true>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
-          if (pipe == 4) return launch_dsd_v4<T, NV, 4, 64, 4, true>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
+          // packed fp32x2 FMAs (FFMA2) in the accumulation: 30.73 against 31.26 ms (same bits)
+          if (pipe == 1) return launch_dsd_v4<T, NV, 4, 64, 2, true>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
+          if (pipe == 2) return launch_dsd_v4<T, NV, 4, 64, 4, true>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
+          if (pipe == 3) return launch_dsd_v4<T, NV, 4, 64, 2, false>(g, arg, q, row_base, b, n_tok, K, D, dsd, flag, st);
         }
       }
       if constexpr (NV <= 2) {

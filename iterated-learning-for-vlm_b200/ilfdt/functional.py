@@ -118,7 +118,9 @@ class GroundingFunction(torch.autograd.Function):
         row_base = None
         if mode == "bf16":
             sd_k, sd_kt = _sd_bf16(sd_c)
-            if mask_f is not None and COMPACT_TEXT and ops.text_supported(q.shape[1]):
+            # (the backward of the compacted operand runs the v3 / v4 scatter kernels: D in {256, 512}, K % 32 == 0)
+            if mask_f is not None and COMPACT_TEXT and ops.text_supported(q.shape[1]) and sd.shape[0] % 32 == 0 \
+                    and q.shape[2] in (256, 512):
                 # padded text: valid rows + ONE pad per sample can change the max over tokens (every pad scores
                 # exactly 0, clip_fdt.py:125-130); the cast writes that compacted, bucketed operand directly
                 q_k, plan = ops.text_compact(q, mask_f)

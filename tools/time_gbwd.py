@@ -32,7 +32,7 @@ for name, n_tok, masked in (("image", 49, False), ("text", 77, True)):
     dsd = torch.zeros(K, D, device=dev)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     res = {}
-    variants = [dict(dsd_pipe=p) for p in (0, 1, 2, 3, 4)] + [dict(dq_pipe=p) for p in (1, 2, 3)]
+    variants = [dict(dsd_pipe=p) for p in (0, 1, 2, 3)] + [dict(dq_pipe=p) for p in (1, 2)]
     for tune in variants:
         try:
             with ops.tune(**tune):
