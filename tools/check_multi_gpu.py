@@ -47,6 +47,28 @@ def rel(a, ref):
     return ((a.detach().double() - ref).abs().max() / ref.abs().max().clamp_min(1e-30)).item()
 
 
+def choices(inp, mode, dev):
+    """The discrete choices of the kernels on one rank's inputs (argmax token per (sample, code), sparsemax support):
+    gradients are compared with the oracle ON THE SAME PIECE (tests/test_fullsize_gpu.py, module docstring) -- a support
+    bit at rounding level otherwise moves whole gradient rows for any two fp32 evaluations, the reference's included."""
+    from ilfdt import ops
+    out = {}
+    sd = inp["sd"].to(dev)
+    for tag, q, mask in (("img", inp["q_img"].to(dev), None), ("txt", inp["q_txt"].to(dev), inp["mask"].to(dev))):
+        if mode == "bf16":
+            sd_k = ops.cast_bf16(sd.contiguous())
+            if mask is not None and ops.text_supported(q.shape[1]):
+                q_k, plan = ops.text_compact(q.contiguous(), mask)
+                pooled, arg = ops.ground_fwd_text(q_k, sd_k, plan, q.shape[1], 1000.0)
+            else:
+                pooled, arg = ops.ground_fwd(ops.cast_bf16_rows(q.contiguous(), mask), sd_k, None, 1000.0, "max")
+        else:
+            pooled, arg = ops.ground_fwd(q.contiguous(), sd.contiguous(), mask, 1000.0, "max")
+        out["arg_" + tag] = arg.long()
+        out["supp_" + tag] = ops.sparsemax_fwd(pooled)[0] > 0
+    return out
+
+
 def build(K, D, dev, sd0, p0):
     m = Clip_FDT(_Visual(), _Text(), True, K, D, D, D, "sparsemax", "max", 1000.0).to(dev)
     m.img_query_model.q_map = _Identity()
@@ -78,8 +100,18 @@ def main():
         ranks = [dict(q_img=O.make_leaf(i["q_img"].double().to(dev)), q_txt=O.make_leaf(i["q_txt"].double().to(dev)),
                       mask=i["mask"].double().to(dev), sd=O.make_leaf(i["sd"].double().to(dev)),
                       p=O.make_leaf(i["p"].double().to(dev))) for i in per_rank]
-        ref = O.step(ranks, temperature=1000.0, upstream=[1.0 / world] * world)
-        del ranks
+        free = O.step(ranks, temperature=1000.0, upstream=[1.0 / world] * world)      # free-running rule
+        force = [choices(i, mode, dev) for i in per_rank]
+        flips = sum(int((f["supp_" + t] != (fr["w_" + t] > 0)).sum()) for f, fr in zip(force, free) for t in ("img", "txt"))
+        for rk in ranks:
+            for v in rk.values():
+                if isinstance(v, torch.Tensor) and v.grad is not None:
+                    v.grad = None
+        ref = O.step(ranks, temperature=1000.0, upstream=[1.0 / world] * world, force=force)
+        if rank == 0:
+            print("%s: %d support bits (of %d) differ from the free-running fp64 rule over all ranks; loss of rank 0 free %.9f / "
+                  "same piece %.9f" % (mode, flips, world * 2 * b * K, free[0]["loss"].item(), ref[0]["loss"].item()), flush=True)
+        del ranks, free
         # ---- 1. plain module, W ranks over NCCL
         m = build(K, D, dev, mine["sd"], mine["p"])
         qi = mine["q_img"].clone().requires_grad_(True)
