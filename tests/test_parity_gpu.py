@@ -1395,8 +1395,13 @@ def test_no_write_outside_output_buffers(ops, monkeypatch):
         keep = {}
         Fn.InfoNCEFunction.apply(xi, xt, gi, gt, s, off, mode, False, keep).backward()
         ops.nce_topk_hits(keep["x"], keep["g"], keep["scale"], off, keep["diag"])
-        if B % b == 0:
-            Fn.InfoNCEFunction.apply(xi, xt, gi.detach(), gt.detach(), s, off, mode, True).backward()
+        if B % b == 0:   # gathered form (what W ranks run): the all-gathered row log-sum-exps come from the same kernels
+            lp = (lambda t: ops.cast_bf16(t.detach().contiguous())) if (mode == "bf16" and D % 8 == 0) else (lambda t: t.detach().contiguous())
+            Gi, Gt, sc = lp(gi), lp(gt), keep["scale"]
+            lse_i_all, _ = ops.nce_lse(Gi, Gt, sc, 0)
+            lse_t_all, _ = ops.nce_lse(Gt, Gi, sc, 0)
+            ops.nce_bwd_gathered(Gi[off:off + b].contiguous(), Gt[off:off + b].contiguous(), Gi, Gt, sc, off, lse_i_all,
+                                 lse_t_all, guard.zeros(B // b, device=dev) + 1.0)
         Fn.LogitsFunction.apply(xi, gt, s, mode).sum().backward()
     # contractions on odd shapes, sparsemax (register and shared-memory kernels), row ops, RNG
     for M, N, Kr in [(128, 77, 64), (200, 300, 136), (512, 1100, 2048)]:
