@@ -68,7 +68,9 @@ enum {
                                     groups of 4 rows; 3 = scalar FMAs; 0 = the v3 kernel. Same summation order: identical results */
   ILFDT_TUNE_DQ_PIPE = 8,        /* ilfdt_ground_bwd* (bf16 rows): per-sample kernel's gather loop: 0 = batches of 4 rows, 1 =
                                     pipelined groups of 2 (3 CTAs / SM), 2 = pipelined groups of 4 (2 CTAs / SM). Same order */
-  ILFDT_TUNE_COUNT_ = 9
+  ILFDT_TUNE_F32_X3 = 9,         /* F32 InfoNCE entry points: 1 (default) = the logits contractions run on the tensor cores as a
+                                    3-term bf16 split (ilfdt_split3_bf16; fp32-grade: 7e-7 of fp64), 0 = SIMT FFMA kernels */
+  ILFDT_TUNE_COUNT_ = 10
 };
 int32_t ilfdt_tune_set(int32_t key, int64_t value);
 int64_t ilfdt_tune_get(int32_t key);
@@ -84,6 +86,12 @@ int32_t ilfdt_cast_bf16_rows(const float* src, const float* rowmask, int64_t row
  * bf16): dst_bf16[r, :] = rowmask[r] == 0 ? src_bf16[r, :] : 0. */
 int32_t ilfdt_mask_rows_bf16(const void* src_bf16, const float* rowmask, int64_t rows, int64_t cols,
                              void* dst_bf16, void* stream);
+/* fp32-grade contractions on the bf16 tensor cores: src [rows, cols] f32 -> dst_bf16 [rows, 6*cols], six
+ * concatenated copies of the row's three bf16 terms hi + mid + lo (= src to 2^-24) in the order [2 1 0 1 0 0] (side 0, the
+ * A operand) or [0 1 2 0 1 0] (side 1, the B operand; smallest partial products first, the leading one last): a single bf16 contraction over 6*cols then accumulates, in fp32,
+ * every partial product down to 2^-16 of the leading one. rowmask (optional): rows with a non-zero entry are zeroed. */
+int32_t ilfdt_split3_bf16(const float* src, const float* rowmask, int64_t rows, int64_t cols, int32_t side, void* dst_bf16,
+                          void* stream);
 /* src [rows, cols] f32 or bf16 -> dst_bf16 [cols, rows] */
 int32_t ilfdt_transpose_bf16(const void* src, int32_t src_dtype, int64_t rows, int64_t cols,
                              void* dst_bf16, void* stream);

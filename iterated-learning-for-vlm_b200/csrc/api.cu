@@ -7,7 +7,7 @@
 namespace ilfdt {
 
 // tuning knobs: explicit API state instead of environment variables read into statics (defaults = the tuned values)
-static std::atomic<int64_t> g_tune[ILFDT_TUNE_COUNT_] = {{1024}, {32}, {1}, {1}, {1}, {1}, {128}, {1}, {0}};
+static std::atomic<int64_t> g_tune[ILFDT_TUNE_COUNT_] = {{1024}, {32}, {1}, {1}, {1}, {1}, {128}, {1}, {0}, {1}};
 int64_t tune_get(int key) { return (key >= 0 && key < ILFDT_TUNE_COUNT_) ? g_tune[key].load(std::memory_order_relaxed) : 0; }
 
 int sm_count() {
@@ -49,16 +49,50 @@ static int64_t nce_f32_chunk_rows(int64_t b, int64_t B) {
 }
 
 static int64_t nce_f32_logits_bytes(int64_t b, int64_t B) { return round_up(nce_f32_chunk_rows(b, B) * B * 4, 16); }
-static int64_t nce_f32_ws_bytes(int64_t b, int64_t B) { return nce_f32_logits_bytes(b, B) + 2 * b * 8; }
+// fp32-grade logits on the tensor cores: L = scale * X . G^T as one bf16 contraction over the 3-term split of both
+// operands (launch_split3_bf16; the reduction is the embedding width, a few dozen leading-term steps, see
+// kernels_simt.cu). The products with a reduction over B (dX = P . G) stay on the SIMT kernel.
+static bool nce_f32_x3(int64_t D) { return tune_get(ILFDT_TUNE_F32_X3) != 0 && D % 8 == 0 && D <= 1024; }
+static int64_t nce_f32_x3_bytes(int64_t b, int64_t B, int64_t D) {
+  return (D % 8 == 0 && D <= 1024) ? round_up((b + B) * 6 * D * 2, 256) + 256 : 0;
+}
+static int64_t nce_f32_ws_bytes(int64_t b, int64_t B, int64_t D = 0) {
+  return round_up(nce_f32_logits_bytes(b, B) + 2 * b * 8, 256) + nce_f32_x3_bytes(b, B, D);
+}
+struct NceX3 {
+  bool on = false;
+  char* X6 = nullptr;   // [b, 6 D] bf16, B-operand order
+  char* G6 = nullptr;   // [B, 6 D] bf16, A-operand order
+};
+static int32_t nce_x3_prepare(NceX3& x3, const float* X, const float* G, int64_t b, int64_t B, int64_t D, void* ws,
+                              int64_t ws_bytes, cudaStream_t st) {
+  x3.on = nce_f32_x3(D) && ws_bytes >= nce_f32_ws_bytes(b, B, D);
+  if (!x3.on) return ILFDT_OK;
+  x3.X6 = reinterpret_cast<char*>(ws) + round_up(nce_f32_logits_bytes(b, B) + 2 * b * 8, 256);
+  x3.G6 = x3.X6 + round_up(b * 6 * D * 2, 256);
+  int32_t rc = launch_split3_bf16(X, nullptr, b, D, 1, x3.X6, st);
+  if (rc != ILFDT_OK) return rc;
+  return launch_split3_bf16(G, nullptr, B, D, 0, x3.G6, st);
+}
+// L[rows, B] = scale * X[r0 : r0 + rows, :] . G^T
+static int32_t nce_f32_logits(const NceX3& x3, const float* X, const float* G, int64_t r0, int64_t rows, int64_t B, int64_t D,
+                              const float* scale, float* L, cudaStream_t st) {
+  if (x3.on)
+    return launch_gemm_nt_bf16(x3.G6, x3.X6 + r0 * 6 * D * 2, B, rows, 6 * D, 1.f, scale, 0, L, B, st);
+  return launch_gemm_f32(X + r0 * D, D, 1, G, D, 1, L, B, 1, rows, B, D, 1.f, scale, 0, st);
+}
 
 static int32_t nce_lse_f32(const float* X, const float* G, int64_t b, int64_t B, int64_t D, const float* scale,
                            int64_t label_offset, float* lse, float* diag, void* ws, int64_t ws_bytes, cudaStream_t st) {
   const int64_t R = nce_f32_chunk_rows(b, B);
   ILFDT_REQUIRE(ws != nullptr && ws_bytes >= R * B * 4, ILFDT_E_INVALID_ARG, "nce_lse(f32): workspace too small");
   float* L = reinterpret_cast<float*>(ws);
+  NceX3 x3;
+  int32_t rc0 = nce_x3_prepare(x3, X, G, b, B, D, ws, ws_bytes, st);
+  if (rc0 != ILFDT_OK) return rc0;
   for (int64_t r0 = 0; r0 < b; r0 += R) {
     const int64_t rows = std::min(R, b - r0);
-    int32_t rc = launch_gemm_f32(X + r0 * D, D, 1, G, D, 1, L, B, 1, rows, B, D, 1.f, scale, 0, st);
+    int32_t rc = nce_f32_logits(x3, X, G, r0, rows, B, D, scale, L, st);
     if (rc != ILFDT_OK) return rc;
     rc = launch_lse_rows(L, B, rows, B, label_offset + r0, lse + r0, diag + r0, st);
     if (rc != ILFDT_OK) return rc;
@@ -90,9 +124,12 @@ static int32_t nce_bwd_f32(const float* x_img, const float* x_txt, const float* 
     const float* lse = dir == 0 ? lse_i : lse_t;
     float* dX = dir == 0 ? dx_img : dx_txt;
     float* dG = dir == 0 ? dg_txt : dg_img;
+    NceX3 x3;
+    int32_t rc0 = nce_x3_prepare(x3, X, G, b, B, D, ws, ws_bytes, st);
+    if (rc0 != ILFDT_OK) return rc0;
     for (int64_t r0 = 0; r0 < b; r0 += R) {
       const int64_t rows = std::min(R, b - r0);
-      int32_t rc = launch_gemm_f32(X + r0 * D, D, 1, G, D, 1, L, B, 1, rows, B, D, 1.f, scale, 0, st);
+      int32_t rc = nce_f32_logits(x3, X, G, r0, rows, B, D, scale, L, st);
       if (rc != ILFDT_OK) return rc;
       rc = launch_softmax_grad_rows(L, L, B, rows, B, label_offset + r0, lse + r0, grad_out, coef, scale,
                                     row_acc + dir * b + r0, st);
@@ -125,9 +162,12 @@ static int32_t nce_bwd_gathered_f32(const float* x_img, const float* x_txt, cons
     const float* lse_lane = (dir == 0 ? lse_i_all : lse_t_all) + label_offset;
     const float* lse_stream = dir == 0 ? lse_t_all : lse_i_all;
     float* dX = dir == 0 ? dx_img : dx_txt;
+    NceX3 x3;
+    int32_t rc0 = nce_x3_prepare(x3, X, G, b, B, D, ws, ws_bytes, st);
+    if (rc0 != ILFDT_OK) return rc0;
     for (int64_t r0 = 0; r0 < b; r0 += R) {
       const int64_t rows = std::min(R, b - r0);
-      int32_t rc = launch_gemm_f32(X + r0 * D, D, 1, G, D, 1, L, B, 1, rows, B, D, 1.f, scale, 0, st);
+      int32_t rc = nce_f32_logits(x3, X, G, r0, rows, B, D, scale, L, st);
       if (rc != ILFDT_OK) return rc;
       rc = launch_softmax_grad_sym_rows(L, L, B, rows, B, label_offset + r0, lse_lane + r0, lse_stream,
                                         go_all + label_offset / b, go_all, b, coef, scale, row_acc + dir * b + r0, st);
@@ -186,6 +226,14 @@ int32_t ilfdt_cast_bf16_rows(const float* src, const float* rowmask, int64_t row
   ILFDT_REQUIRE(rows >= 0 && cols >= 0 && (rows * cols == 0 || (src && dst_bf16)), ILFDT_E_INVALID_ARG,
                 "cast_bf16_rows: bad arguments");
   return launch_cast_bf16_rows(src, rowmask, rows, cols, dst_bf16, ST(stream));
+}
+
+int32_t ilfdt_split3_bf16(const float* src, const float* rowmask, int64_t rows, int64_t cols, int32_t side, void* dst_bf16,
+                          void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(rows >= 0 && cols >= 0 && (side == 0 || side == 1) && (rows * cols == 0 || (src && dst_bf16)),
+                ILFDT_E_INVALID_ARG, "split3_bf16: bad arguments");
+  return launch_split3_bf16(src, rowmask, rows, cols, side, dst_bf16, ST(stream));
 }
 
 int32_t ilfdt_mask_rows_bf16(const void* src_bf16, const float* rowmask, int64_t rows, int64_t cols, void* dst_bf16,
@@ -442,7 +490,7 @@ int32_t ilfdt_logits(const void* x, const void* g, int32_t dtype, int64_t b, int
 }
 
 int64_t ilfdt_nce_ws_bytes(int32_t dtype, int64_t b, int64_t B, int64_t D) {
-  if (dtype == ILFDT_F32) return nce_f32_ws_bytes(b, B);
+  if (dtype == ILFDT_F32) return nce_f32_ws_bytes(b, B, D);
   return std::max(nce_fwd_bf16_ws_bytes(b, B), nce_bwd_bf16_ws_bytes(b, B, D));
 }
 

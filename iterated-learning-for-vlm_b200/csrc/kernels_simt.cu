@@ -488,6 +488,52 @@ int32_t launch_cast_bf16_rows(const float* src, const float* rowmask, int64_t ro
   return ILFDT_OK;
 }
 
+// fp32 -> three bf16 terms hi + mid + lo (8 + 8 + 8 mantissa bits: the sum reproduces the fp32 value to 2^-24), laid out
+// as SIX concatenated copies of the row so that ONE bf16 tensor-core contraction over 6*cols accumulates the six
+// partial products a0*b0 + a0*b1 + a1*b0 + a0*b2 + a1*b1 + a2*b0 in fp32 (everything down to 2^-16 of the leading term;
+// the dropped a1*b2, a2*b1, a2*b2 are below 2^-24): side 0 (A operand) = [2 1 0 1 0 0], side 1 (B operand) = [0 1 2 0 1 0].
+// This is the fp32-grade score contraction on tcgen05. Masked rows (rowmask != 0) are zeroed.
+__global__ void split3_bf16_kernel(const float* __restrict__ src, const float* __restrict__ rowmask, int64_t rows, int cols,
+                                   int side, __nv_bfloat16* __restrict__ dst) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // one thread per 4 source elements
+  const int c4 = cols >> 2;
+  if (i >= rows * c4) return;
+  const int64_t r = i / c4;
+  const int c = (int)(i - r * c4) * 4;
+  float4 v = __ldg(reinterpret_cast<const float4*>(src + r * cols + c));
+  if (rowmask != nullptr && __ldg(rowmask + r) != 0.f) v = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float x[4] = {v.x, v.y, v.z, v.w};
+  __nv_bfloat16 t[3][4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const __nv_bfloat16 h = __float2bfloat16_rn(x[e]);
+    const float r1 = x[e] - __bfloat162float(h);
+    const __nv_bfloat16 m = __float2bfloat16_rn(r1);
+    const float r2 = r1 - __bfloat162float(m);
+    t[0][e] = h; t[1][e] = m; t[2][e] = __float2bfloat16_rn(r2);
+  }
+  // smallest products first: the tensor core adds each 16-term partial into the fp32 accumulator with truncation, so the
+  // error of an add scales with the accumulator's magnitude -- keep it small until the leading term comes last
+  const int pat[2][6] = {{2, 1, 0, 1, 0, 0}, {0, 1, 2, 0, 1, 0}};
+  __nv_bfloat16* o = dst + r * (int64_t)(6 * cols) + c;
+#pragma unroll
+  for (int s6 = 0; s6 < 6; ++s6) {
+    const int w = pat[side][s6];
+    *reinterpret_cast<uint2*>(o + (int64_t)s6 * cols) = *reinterpret_cast<const uint2*>(t[w]);
+  }
+}
+int32_t launch_split3_bf16(const float* src, const float* rowmask, int64_t rows, int64_t cols, int side, void* dst,
+                           cudaStream_t st) {
+  if (rows * cols == 0) return ILFDT_OK;
+  ILFDT_REQUIRE(cols % 4 == 0 && ((reinterpret_cast<uintptr_t>(src) & 15) | (reinterpret_cast<uintptr_t>(dst) & 7)) == 0,
+                ILFDT_E_UNSUPPORTED_SHAPE, "split3_bf16: cols %% 4 == 0 and aligned pointers required");
+  const int64_t total = rows * (cols / 4);
+  split3_bf16_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(src, rowmask, rows, (int)cols, side,
+                                                                reinterpret_cast<__nv_bfloat16*>(dst));
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
 // bf16 -> bf16 copy with the masked (pad) rows zeroed: the q operand of the tensor-core score kernel when
 // the caller already holds q in bf16 (same contract as cast_bf16_rows for fp32 q).
 __global__ void mask_rows_bf16_kernel(const uint4* __restrict__ src, const float* __restrict__ rowmask, int64_t rows,

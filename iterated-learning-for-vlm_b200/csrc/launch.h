@@ -31,6 +31,8 @@ int32_t launch_topk_hits(const float* L, int64_t b, int64_t B, int64_t label0, i
 int32_t launch_cast_bf16(const float* src, void* dst, int64_t n, cudaStream_t st);
 int32_t launch_cast_bf16_rows(const float* src, const float* rowmask, int64_t rows, int64_t cols, void* dst,
                               cudaStream_t st);
+int32_t launch_split3_bf16(const float* src, const float* rowmask, int64_t rows, int64_t cols, int side, void* dst,
+                           cudaStream_t st);
 int32_t launch_mask_rows_bf16(const void* src, const float* rowmask, int64_t rows, int64_t cols, void* dst,
                               cudaStream_t st);
 int32_t launch_transpose_bf16(const void* src, int src_dtype, int64_t rows, int64_t cols, void* dst, cudaStream_t st);

@@ -8,7 +8,8 @@ Public surface mirrors the reference's module layout:
     ilfdt.linklink         get_rank / get_world_size / barrier ...                (prototype/linklink/__init__.py)
 All arithmetic of the path runs in libilfdt.so (include/ilfdt.h); there is no CPU or PyTorch fallback.
 """
-from .functional import compute_dtype, get_compute_dtype, set_compute_dtype, set_fused_q_map  # noqa: F401
+from .functional import (compute_dtype, get_compute_dtype, set_compute_dtype, set_fp32_tensor_cores,  # noqa: F401
+                         set_fused_q_map)
 from . import _lib  # noqa: F401
 
-__all__ = ["compute_dtype", "get_compute_dtype", "set_compute_dtype", "set_fused_q_map"]
+__all__ = ["compute_dtype", "get_compute_dtype", "set_compute_dtype", "set_fp32_tensor_cores", "set_fused_q_map"]

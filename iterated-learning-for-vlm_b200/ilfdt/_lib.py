@@ -27,6 +27,7 @@ SIGNATURES = {
     "ilfdt_tune_get": (_i64, [_i32]),
     "ilfdt_cast_bf16": (_i32, [_p, _p, _i64, _p]),
     "ilfdt_cast_bf16_rows": (_i32, [_p, _p, _i64, _i64, _p, _p]),
+    "ilfdt_split3_bf16": (_i32, [_p, _p, _i64, _i64, _i32, _p, _p]),
     "ilfdt_mask_rows_bf16": (_i32, [_p, _p, _i64, _i64, _p, _p]),
     "ilfdt_transpose_bf16": (_i32, [_p, _i32, _i64, _i64, _p, _p]),
     "ilfdt_ground_fwd_ws_bytes": (_i64, [_i32, _i64, _i64, _i64, _i64]),
@@ -79,7 +80,7 @@ SIGNATURES = {
 }
 
 TUNE = {"dsd_split_rows": 0, "dsd_tile": 1, "dsd_stream": 2, "ground_2cta": 3, "gemm_wide2": 4, "nce_2cta": 5,
-        "sparse_bwd_nnz": 6, "dsd_pipe": 7, "dq_pipe": 8}
+        "sparse_bwd_nnz": 6, "dsd_pipe": 7, "dq_pipe": 8, "f32_x3": 9}
 
 _lib = None
 

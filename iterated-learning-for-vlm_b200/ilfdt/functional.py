@@ -40,6 +40,28 @@ class compute_dtype:
         set_compute_dtype(self.prev)
 
 
+# fp32 mode: run the contractions whose reduction is the model width (the score block q.sd^T and g = df.sd^T) as ONE bf16
+# tensor-core contraction over a 3-term split of both operands (ops.split3_bf16: six partial products, smallest first,
+# fp32 accumulation in tensor memory). Measured against fp64: 7.4e-7 relative (the SIMT fp32 kernel: 1.1e-6) at 4.5 x its
+# speed. Long reductions (pooling over K, dX over B) stay on the SIMT kernels: the tensor core adds each 16-term partial
+# into its fp32 accumulator with truncation, which is only harmless for a few dozen leading-term steps.
+FP32_TENSOR_CORES = os.environ.get("ILFDT_FP32_TENSOR_CORES", "1") != "0"
+
+
+def set_fp32_tensor_cores(on):
+    """fp32 mode: True (default) = contractions over the model width run on the tensor cores as a 3-term bf16 split;
+    False = SIMT FFMA kernels everywhere."""
+    global FP32_TENSOR_CORES
+    from . import _lib
+    FP32_TENSOR_CORES = bool(on)
+    _lib.check(_lib.load().ilfdt_tune_set(_lib.TUNE["f32_x3"], int(bool(on))))
+
+
+def _x3_ok(q, sd):
+    return FP32_TENSOR_CORES and q.dtype == torch.float32 and q.shape[2] % 8 == 0 and q.shape[2] <= 1024 \
+        and q.shape[1] <= 256 and q.shape[0] * q.shape[1] < 2 ** 31 // 8
+
+
 # padded text in bf16 mode: contract only the rows that can matter (csrc/text_buckets.cu); 0 = full-width operand
 COMPACT_TEXT = os.environ.get("ILFDT_COMPACT_TEXT", "1") != "0"
 LEAN_WEIGHTS = os.environ.get("ILFDT_LEAN_WEIGHTS", "1") != "0"   # need_weights=False skips the fp32 att_weight
@@ -133,7 +155,13 @@ class GroundingFunction(torch.autograd.Function):
                 pooled, arg = ops.ground_fwd(q_k, sd_k, None, temperature, "max")
         else:
             q_k, sd_k, sd_kt = q, sd_c, None
-            pooled, arg = ops.ground_fwd(q_k, sd_k, mask_f, temperature, "max")
+            if _x3_ok(q, sd_c):
+                # pad rows are zeroed in the split operand: their score is exactly the 0 of clip_fdt.py:125-130
+                rowmask = None if mask_f is None else mask_f.reshape(-1)
+                pooled, arg = ops.ground_fwd(ops.split3_bf16(q, 1, rowmask), ops.split3_bf16(sd_c, 0), None, temperature,
+                                             "max", sqrt_d=math.sqrt(q.shape[2]))
+            else:
+                pooled, arg = ops.ground_fwd(q_k, sd_k, mask_f, temperature, "max")
         # the scatter kernel that reads the support from bf16 weights covers these shapes (ground_bwd.cu)
         # (token counts up to 96 run the v3 scatter kernel, up to 256 -- ViT-B/16's 196 patches -- the token-sorted one)
         lean = LEAN_WEIGHTS and (not need_weights) and mode == "bf16" and q.shape[2] in (256, 512) and q.shape[1] <= 256 \
@@ -169,7 +197,10 @@ class GroundingFunction(torch.autograd.Function):
                 # dsd[K,D] += w^T . df straight from the row-major w [b,K] and df [b,D] (MN-major tensor-core operands)
                 ops.gemm_tn(df_b, w_b, out=dsd, accumulate=True)
             else:
-                g = ops.gemm_f32(df, sd_k, b_t=True)
+                if FP32_TENSOR_CORES and D % 8 == 0 and D <= 1024:
+                    g = ops.gemm_nt(ops.split3_bf16(sd_k, 0), ops.split3_bf16(df, 1))     # g = df . sd^T, reduction D
+                else:
+                    g = ops.gemm_f32(df, sd_k, b_t=True)
                 ops.gemm_f32(w, df, a_t=True, out=dsd, accumulate=True)
             if dw is not None:
                 g.add_(dw)

@@ -19,7 +19,7 @@ def _stream():
 LAUNCHES = 0          # kernels launched through this module since it was last zeroed
 PROFILE_ON = False    # when True every C call is bracketed by CUDA events on the launching stream
 PROFILE = {}          # op name -> [(start_event, end_event), ...]
-_KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mask_rows_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_ground_fwd_text": 5, "ilfdt_text_compact": 3, "ilfdt_sparsemax_fwd": 1,
+_KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_split3_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mask_rows_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_ground_fwd_text": 5, "ilfdt_text_compact": 3, "ilfdt_sparsemax_fwd": 1,
                      "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_nt_splitk": 2, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2, "ilfdt_ground_bwd_w16": 2,   # + 2 regime launches that return at once
                      "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5, "ilfdt_nce_lse": 2, "ilfdt_nce_loss": 1,
                      "ilfdt_nce_bwd": 4, "ilfdt_nce_bwd_gathered": 2, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
@@ -113,6 +113,20 @@ def cast_bf16_rows(x, rowmask):
     return out
 
 
+def split3_bf16(x, side, rowmask=None):
+    """x [..., C] f32 -> bf16 [..., 6C]: the three-term bf16 split laid out for ONE fp32-grade tensor-core contraction
+    (side 0 = A operand, 1 = B operand; see ilfdt_split3_bf16). Rows whose rowmask entry is non-zero are zeroed."""
+    _req(x, torch.float32, "x")
+    cols = x.shape[-1]
+    rows = x.numel() // cols
+    if rowmask is not None:
+        _req(rowmask, torch.float32, "rowmask")
+        assert rowmask.numel() == rows
+    out = torch.empty(tuple(x.shape[:-1]) + (6 * cols,), dtype=torch.bfloat16, device=x.device)
+    _call("ilfdt_split3_bf16", _ptr(x), _ptr(rowmask), rows, cols, int(side), _ptr(out), _stream())
+    return out
+
+
 def transpose_bf16(x):
     """x [R, C] (f32 or bf16) -> bf16 [C, R]"""
     _req(x, None, "x")
@@ -122,9 +136,10 @@ def transpose_bf16(x):
     return out
 
 
-def ground_fwd(q, sd, mask, temperature, pool_type="max"):
+def ground_fwd(q, sd, mask, temperature, pool_type="max", sqrt_d=None):
     """q [b,N,D], sd [K,D] (both f32 or both bf16), mask [b,N] f32 (0 / -inf) or None
-    -> pooled [b,K] f32, arg [b,K] int16 (max pooling) or None."""
+    -> pooled [b,K] f32, arg [b,K] int16 (max pooling) or None. sqrt_d: the score scale when D is not the model width
+    (the 6x-wide operands of the 3 x bf16 contraction)."""
     lib = _lib.load()
     _req(q, None, "q"); _req(sd, q.dtype, "sd")
     b, n_tok, D = q.shape
@@ -139,8 +154,9 @@ def ground_fwd(q, sd, mask, temperature, pool_type="max"):
     arg = torch.empty(b, K, dtype=torch.int16, device=q.device) if pool_type == "max" else None
     ws_bytes = lib.ilfdt_ground_fwd_ws_bytes(dt, b, n_tok, K, D) if pool_type == "max" else 0
     ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=q.device) if ws_bytes else None
-    _call("ilfdt_ground_fwd", _ptr(q), _ptr(sd), dt, _ptr(mask), b, n_tok, K, D, float(math.sqrt(D)),
-                               float(temperature), pt, _ptr(pooled), _ptr(arg), _ptr(ws), ws_bytes, _stream())
+    _call("ilfdt_ground_fwd", _ptr(q), _ptr(sd), dt, _ptr(mask), b, n_tok, K, D,
+          float(math.sqrt(D) if sqrt_d is None else sqrt_d), float(temperature), pt, _ptr(pooled), _ptr(arg), _ptr(ws),
+          ws_bytes, _stream())
     return pooled, arg
 
 
