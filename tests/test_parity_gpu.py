@@ -1507,3 +1507,58 @@ def test_declip_query_model_and_eight_logits_golden(ops, golden_dir, name, att):
                            torch.nn.functional.cross_entropy(torch.tensor(z["logits_" + b_]), torch.arange(6)) / 2
                            for a, b_ in (("i1", "t1"), ("i2", "t2"), ("i1a", "t1a"), ("i2a", "t2a")))
             assert_close(loss, ref_loss, FP32_TOL, "sum of the four ClipInfoCELoss terms")
+
+
+@pytest.mark.parametrize("b,n_tok,K,D,masked", [(64, 49, 4096, 512, False), (40, 77, 2048, 512, True), (7, 13, 520, 64, True)])
+def test_fp32_grade_split_contraction_on_tensor_cores(ops, b, n_tok, K, D, masked):
+    """fp32 mode's score block as ONE bf16 tcgen05 contraction over the 3-term split of both operands
+    (ilfdt_split3_bf16) against fp64: at least as close as the SIMT fp32 kernel, pads score exactly 0,
+    and the three terms reproduce the fp32 value."""
+    dev = _dev()
+    g = torch.Generator(device="cuda").manual_seed(K + n_tok)
+    q = torch.randn(b, n_tok, D, device=dev, generator=g)
+    sd = torch.randn(K, D, device=dev, generator=g)
+    mask = _mask(b, n_tok, torch.randint(1, n_tok + 1, (b,)).tolist()).to(dev) if masked else None
+    parts = ops.split3_bf16(sd, 0).float().view(K, 6, D)
+    assert torch.equal(parts[:, 2] + parts[:, 1] + parts[:, 0], sd) or \
+        (parts[:, 2].double() + parts[:, 1].double() + parts[:, 0].double() - sd.double()).abs().max() <= 2.0 ** -23 * sd.abs().max()
+    qb = ops.split3_bf16(q, 1, None if mask is None else mask.reshape(-1))
+    p3, a3 = ops.ground_fwd(qb, ops.split3_bf16(sd, 0), None, 1000.0, "max", sqrt_d=math.sqrt(D))
+    p32, a32 = ops.ground_fwd(q, sd, mask, 1000.0, "max")
+    ref = O.pooled_scores(q.double(), sd.double(), None if mask is None else mask.double(), 1000.0, "max")
+    e3, e32 = rel_err(p3, ref), rel_err(p32, ref)
+    assert e3 <= 2e-6, "3-term split contraction: %.2e of fp64" % e3
+    assert e32 <= 4e-6
+    print("x3 score block: %.2e of fp64 (SIMT fp32 kernel: %.2e); argmax equal at %.4f %% of the entries" % (
+        e3, e32, 100.0 * (a3 == a32).float().mean().item()))
+    assert (a3 == a32).float().mean().item() > 0.9999
+
+
+def test_fp32_mode_routes_agree(ops):
+    """fp32 mode with and without the tensor-core split route (ilfdt.set_fp32_tensor_cores): both within the fp32 gates of
+    the fp64 oracle on the same piece is asserted by the full-size tests; here: the two routes agree with each other."""
+    import ilfdt
+    from ilfdt import functional as Fn
+    dev = _dev()
+    inp = {k: v.to(dev) for k, v in O.synth_inputs(48, 49, 77, 2048, 512, seed=21).items()}
+
+    def run():
+        qi, qt = inp["q_img"].clone().requires_grad_(True), inp["q_txt"].clone().requires_grad_(True)
+        sd, p = inp["sd"].clone().requires_grad_(True), inp["p"].clone().requires_grad_(True)
+        _, f_i = Fn.GroundingFunction.apply(qi, sd, None, 1000.0, "fp32")
+        _, f_t = Fn.GroundingFunction.apply(qt, sd, inp["mask"], 1000.0, "fp32")
+        x_i, x_t = Fn.L2NormFunction.apply(f_i, 1e-10), Fn.L2NormFunction.apply(f_t, 1e-10)
+        s = p.exp()
+        loss = Fn.InfoNCEFunction.apply(x_i, x_t, x_i, x_t, s, 0, "fp32", True)
+        loss.backward()
+        return loss.detach(), qi.grad, qt.grad, sd.grad, p.grad
+
+    try:
+        a = run()
+        ilfdt.set_fp32_tensor_cores(False)
+        b_ = run()
+    finally:
+        ilfdt.set_fp32_tensor_cores(True)
+    assert_close(a[0], b_[0], 1e-6, "loss")
+    for x, y, nm in zip(a[1:], b_[1:], ("dq_img", "dq_txt", "dsd", "dp")):
+        assert_close(x, y, 5e-5, nm)       # free-running: a membership bit at rounding level may differ between the routes
