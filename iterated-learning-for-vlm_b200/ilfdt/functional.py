@@ -113,6 +113,51 @@ def _warn_once(msg):
         warnings.warn(msg, RuntimeWarning, stacklevel=3)
 
 
+def _score_pool(q, sd_c, mask_f, temperature, mode):
+    """q . sd^T -> token max-pool, on the route `mode` and the shapes select: (pooled [b,K], arg [b,K], and the operands
+    the backward re-reads: q_k, sd_k, sd_kt, row_base). The one place that picks the route -- `grounding_choices` below
+    (the parity tests' view of the kernels' discrete choices) goes through it too."""
+    row_base = None
+    if mode == "bf16":
+        sd_k, sd_kt = _sd_bf16(sd_c)
+        # (the backward of the compacted operand runs the v3 / v4 scatter kernels: D in {256, 512}, K % 32 == 0)
+        if mask_f is not None and COMPACT_TEXT and ops.text_supported(q.shape[1]) and sd_c.shape[0] % 32 == 0 \
+                and q.shape[2] in (256, 512):
+            # padded text: valid rows + ONE pad per sample can change the max over tokens (every pad scores
+            # exactly 0, clip_fdt.py:125-130); the cast writes that compacted, bucketed operand directly
+            q_k, plan = ops.text_compact(q, mask_f)
+            row_base = plan.row_base
+            pooled, arg = ops.ground_fwd_text(q_k, sd_k, plan, q.shape[1], temperature)
+        else:
+            # pad rows are zeroed in the bf16 operand: their tensor-core score is exactly the 0 the
+            # reference's mask multiply yields (clip_fdt.py:125-130), so the fused epilogue needs no mask
+            q_k = ops.cast_bf16_rows(q, mask_f)
+            pooled, arg = ops.ground_fwd(q_k, sd_k, None, temperature, "max")
+    else:
+        q_k, sd_k, sd_kt = q, sd_c, None
+        if _x3_ok(q, sd_c):
+            # pad rows are zeroed in the split operand: their score is exactly the 0 of clip_fdt.py:125-130
+            rowmask = None if mask_f is None else mask_f.reshape(-1)
+            pooled, arg = ops.ground_fwd(ops.split3_bf16(q, 1, rowmask), ops.split3_bf16(sd_c, 0), None, temperature,
+                                         "max", sqrt_d=math.sqrt(q.shape[2]))
+        else:
+            pooled, arg = ops.ground_fwd(q_k, sd_k, mask_f, temperature, "max")
+    return pooled, arg, q_k, sd_k, sd_kt, row_base
+
+
+def grounding_choices(q, sd, mask, temperature, mode=None):
+    """(arg [b,K] int64, pooled [b,K] fp32, support [b,K] bool): the discrete choices GroundingFunction.forward makes on
+    these inputs -- same route, same kernels, same operands. Test / diagnostic helper (tests/test_fullsize_gpu.py,
+    tools/check_multi_gpu.py): gradients are compared with the fp64 reference rule on the same piece of the piecewise-linear map."""
+    mode = get_compute_dtype() if mode is None else mode
+    q = q.detach().contiguous()
+    if mode == "bf16" and not (q.shape[2] % 8 == 0 and q.shape[2] <= 512 and q.shape[1] <= 256 and sd.shape[0] % 8 == 0):
+        mode, q = "fp32", q.float()
+    mask_f = None if mask is None else mask.to(torch.float32).contiguous()
+    pooled, arg = _score_pool(q, sd.detach().contiguous(), mask_f, temperature, mode)[:2]
+    return arg.long(), pooled, ops.sparsemax_fwd(pooled)[0] > 0
+
+
 class GroundingFunction(torch.autograd.Function):
     """Query_model.forward from q onward (clip_fdt.py:113-157), sparsemax + max pooling:
     (q [b,N,D], sd [K,D], mask [b,N] | None) -> (att_weight [b,K], att_ft [b,D]).
@@ -137,31 +182,7 @@ class GroundingFunction(torch.autograd.Function):
             mode = "fp32"
             if q.dtype == torch.bfloat16:
                 q = q.float()      # dq is cast back to bf16 at the end of backward
-        row_base = None
-        if mode == "bf16":
-            sd_k, sd_kt = _sd_bf16(sd_c)
-            # (the backward of the compacted operand runs the v3 / v4 scatter kernels: D in {256, 512}, K % 32 == 0)
-            if mask_f is not None and COMPACT_TEXT and ops.text_supported(q.shape[1]) and sd.shape[0] % 32 == 0 \
-                    and q.shape[2] in (256, 512):
-                # padded text: valid rows + ONE pad per sample can change the max over tokens (every pad scores
-                # exactly 0, clip_fdt.py:125-130); the cast writes that compacted, bucketed operand directly
-                q_k, plan = ops.text_compact(q, mask_f)
-                row_base = plan.row_base
-                pooled, arg = ops.ground_fwd_text(q_k, sd_k, plan, q.shape[1], temperature)
-            else:
-                # pad rows are zeroed in the bf16 operand: their tensor-core score is exactly the 0 the
-                # reference's mask multiply yields (clip_fdt.py:125-130), so the fused epilogue needs no mask
-                q_k = ops.cast_bf16_rows(q, mask_f)
-                pooled, arg = ops.ground_fwd(q_k, sd_k, None, temperature, "max")
-        else:
-            q_k, sd_k, sd_kt = q, sd_c, None
-            if _x3_ok(q, sd_c):
-                # pad rows are zeroed in the split operand: their score is exactly the 0 of clip_fdt.py:125-130
-                rowmask = None if mask_f is None else mask_f.reshape(-1)
-                pooled, arg = ops.ground_fwd(ops.split3_bf16(q, 1, rowmask), ops.split3_bf16(sd_c, 0), None, temperature,
-                                             "max", sqrt_d=math.sqrt(q.shape[2]))
-            else:
-                pooled, arg = ops.ground_fwd(q_k, sd_k, mask_f, temperature, "max")
+        pooled, arg, q_k, sd_k, sd_kt, row_base = _score_pool(q, sd_c, mask_f, temperature, mode)
         # the scatter kernel that reads the support from bf16 weights covers these shapes (ground_bwd.cu)
         # (token counts up to 96 run the v3 scatter kernel, up to 256 -- ViT-B/16's 196 patches -- the token-sorted one)
         lean = LEAN_WEIGHTS and (not need_weights) and mode == "bf16" and q.shape[2] in (256, 512) and q.shape[1] <= 256 \

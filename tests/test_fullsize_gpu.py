@@ -76,17 +76,11 @@ MARGIN_EPS = 1e-6         # relative (to max |pooled|) distance from the sparsem
 
 
 def _our_choices(ops, q, sd, mask, temp, mode):
-    """(arg [b,K] int64, pooled) exactly as GroundingFunction computes them (same kernels, same operands)."""
-    if mode == "bf16":
-        sd_k = ops.cast_bf16(sd.contiguous())
-        if mask is not None and ops.text_supported(q.shape[1]):
-            q_k, plan = ops.text_compact(q.contiguous(), mask)
-            pooled, arg = ops.ground_fwd_text(q_k, sd_k, plan, q.shape[1], temp)
-        else:
-            pooled, arg = ops.ground_fwd(ops.cast_bf16_rows(q.contiguous(), mask), sd_k, None, temp, "max")
-    else:
-        pooled, arg = ops.ground_fwd(q.contiguous(), sd.contiguous(), mask, temp, "max")
-    return arg.long(), pooled
+    """(arg [b,K] int64, pooled) exactly as GroundingFunction computes them: through the same route selection
+    (ilfdt.functional._score_pool), so the fp32 mode's tensor-core split route is what is looked at when it is taken."""
+    from ilfdt import functional as Fn
+    arg, pooled, _ = Fn.grounding_choices(q, sd, mask, temp, mode)
+    return arg, pooled
 
 
 def _check_choices(q64, sd64, mask, temp, arg, w, w_ref, what, max_ambiguous=64):

@@ -51,21 +51,12 @@ def choices(inp, mode, dev):
     """The discrete choices of the kernels on one rank's inputs (argmax token per (sample, code), sparsemax support):
     gradients are compared with the oracle ON THE SAME PIECE (tests/test_fullsize_gpu.py, module docstring) -- a support
     bit at rounding level otherwise moves whole gradient rows for any two fp32 evaluations, the reference's included."""
-    from ilfdt import ops
+    from ilfdt import functional as Fn
     out = {}
     sd = inp["sd"].to(dev)
     for tag, q, mask in (("img", inp["q_img"].to(dev), None), ("txt", inp["q_txt"].to(dev), inp["mask"].to(dev))):
-        if mode == "bf16":
-            sd_k = ops.cast_bf16(sd.contiguous())
-            if mask is not None and ops.text_supported(q.shape[1]):
-                q_k, plan = ops.text_compact(q.contiguous(), mask)
-                pooled, arg = ops.ground_fwd_text(q_k, sd_k, plan, q.shape[1], 1000.0)
-            else:
-                pooled, arg = ops.ground_fwd(ops.cast_bf16_rows(q.contiguous(), mask), sd_k, None, 1000.0, "max")
-        else:
-            pooled, arg = ops.ground_fwd(q.contiguous(), sd.contiguous(), mask, 1000.0, "max")
-        out["arg_" + tag] = arg.long()
-        out["supp_" + tag] = ops.sparsemax_fwd(pooled)[0] > 0
+        # the same route selection as GroundingFunction.forward (fp32 mode: the tensor-core split route when it applies)
+        out["arg_" + tag], _, out["supp_" + tag] = Fn.grounding_choices(q, sd, mask, 1000.0, mode)
     return out
 
 
