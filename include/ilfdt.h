@@ -328,6 +328,21 @@ int32_t ilfdt_bias_cast(const float* src, const float* bias, int64_t rows, int64
 int64_t ilfdt_colsum_ws_bytes(int64_t rows, int64_t C);
 int32_t ilfdt_colsum(const void* src, int32_t src_dtype, int64_t rows, int64_t C, float* out, void* ws,
                      int64_t ws_bytes, void* stream);
+/* ilfdt_colsum for callers that cannot allocate a workspace (CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE.
+ * Same kernels, same grid and therefore the same bits as ilfdt_colsum; the per-CTA partial sums go to a file-scope
+ * `static __device__` array of ILFDT_COLSUM_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until
+ * the process exits. The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine); the
+ * caller passes src and out as usual, and `stream` must belong to the CURRENT device (the array's address is looked
+ * up once per device, on the first call with that device current -- make that first call outside stream capture).
+ * Limit: (number of CTAs, at most 4 per SM) * C * 4 bytes <= ILFDT_COLSUM_STATIC_SCRATCH_BYTES -- on a 148-SM B200
+ * every rows x C with C <= 884 fits (the q_map widths 512 and 768 always do); C up to 1024 fits while
+ * rows <= 512 * 8. Beyond it: ILFDT_E_INVALID_ARG with a message naming the sizes -- use ilfdt_colsum.
+ * The array is SHARED by all calls on a device and keeps the last call's contents (nothing in it needs to start at
+ * zero: each call overwrites every entry it later reads). Calls that overlap on the GPU -- different streams, or
+ * different host threads without stream ordering between them -- RACE on it; serialise them on one stream. */
+#define ILFDT_COLSUM_STATIC_SCRATCH_BYTES (2 * 1024 * 1024)
+int32_t ilfdt_colsum_static(const void* src, int32_t src_dtype, int64_t rows, int64_t C, float* out, void* stream);
 
 /* ---- a12: codebook reset / store / keep, clip_fdt.py:281-283, train_solver.py:211-215,549-553 -- */
 /* dst[i] ~ N(0,1): Philox4x32-10 keyed by seed, counter (i/4, generation), Box-Muller. Same values

@@ -690,4 +690,11 @@ int32_t ilfdt_colsum(const void* src, int32_t src_dtype, int64_t rows, int64_t C
   return launch_colsum(src, src_dtype, rows, C, out, (float*)ws, ST(stream));
 }
 
+int32_t ilfdt_colsum_static(const void* src, int32_t src_dtype, int64_t rows, int64_t C, float* out, void* stream) {
+  ARCH_GUARD();
+  DTYPE_GUARD(src_dtype);
+  ILFDT_REQUIRE(rows >= 1 && C >= 1 && src && out, ILFDT_E_INVALID_ARG, "colsum_static: bad arguments");
+  return launch_colsum_static(src, src_dtype, rows, C, out, ST(stream));
+}
+
 }  // extern "C"

@@ -129,5 +129,6 @@ int32_t launch_ln_bwd(const void* dy, int dy_dtype, const void* src, int src_dty
 int32_t launch_bias_cast(const float* src, const float* bias, int64_t rows, int64_t C, void* dst, int dst_dtype,
                          cudaStream_t st);
 int32_t launch_colsum(const void* src, int src_dtype, int64_t rows, int64_t C, float* out, float* ws, cudaStream_t st);
+int32_t launch_colsum_static(const void* src, int src_dtype, int64_t rows, int64_t C, float* out, cudaStream_t st);
 
 }  // namespace ilfdt

@@ -7,6 +7,7 @@
 #include "common.cuh"
 #include "launch.h"
 #include <algorithm>
+#include <mutex>
 
 namespace ilfdt {
 
@@ -404,6 +405,53 @@ int32_t launch_colsum(const void* src, int src_dtype, int64_t rows, int64_t C, f
   ILFDT_REQUIRE(rows > 0 && C % 4 == 0 && C <= 1024, ILFDT_E_UNSUPPORTED_SHAPE,
                 "colsum: rows > 0 and width a multiple of 4, <= 1024");
   const int grid = qm_grid(rows);
+  if (src_dtype == ILFDT_BF16)
+    colsum_partial_kernel<__nv_bfloat16><<<grid, QM_THREADS, 0, st>>>((const __nv_bfloat16*)src, rows, (int)C, ws);
+  else
+    colsum_partial_kernel<float><<<grid, QM_THREADS, 0, st>>>((const float*)src, rows, (int)C, ws);
+  ILFDT_LAUNCH_OK();
+  partial_reduce_kernel<<<(int)cdiv(C, 32), 256, 0, st>>>(ws, grid, C, (int)C, out);
+  ILFDT_LAUNCH_OK();
+  return ILFDT_OK;
+}
+
+// ---- colsum without any allocation (ilfdt_colsum_static; no counterpart in the reference) ---------------------------
+// The per-CTA partial sums of launch_colsum live in a file-scope device array instead of a caller workspace: every GPU
+// that loads libilfdt holds these COLSUM_STATIC_FLOATS * 4 bytes until the process exits. `g_colsum_static_scratch` is,
+// in HOST code, only a stand-in for the symbol: the device address is fetched once per device with
+// cudaGetSymbolAddress (that device current) and that pointer is what the kernels get.
+// Nothing in it has to start at zero: colsum_partial_kernel writes every part[cta][c] the reduce kernel reads.
+static __device__ __align__(256) float g_colsum_static_scratch[ILFDT_COLSUM_STATIC_SCRATCH_BYTES / 4];
+
+static int32_t colsum_static_scratch(float** out) {
+  constexpr int MAX_DEV = 64;
+  static std::mutex mu;
+  static float* ptr[MAX_DEV] = {};
+  int dev = -1;
+  ILFDT_CUDA_OK(cudaGetDevice(&dev));
+  ILFDT_REQUIRE(dev >= 0 && dev < MAX_DEV, ILFDT_E_INVALID_ARG, "colsum_static: device ordinal %d outside 0..%d", dev, MAX_DEV - 1);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptr[dev] == nullptr) {
+    void* p = nullptr;
+    ILFDT_CUDA_OK(cudaGetSymbolAddress(&p, g_colsum_static_scratch));
+    ILFDT_REQUIRE(p != nullptr, ILFDT_E_CUDA, "colsum_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+    ptr[dev] = reinterpret_cast<float*>(p);
+  }
+  *out = ptr[dev];
+  return ILFDT_OK;
+}
+
+int32_t launch_colsum_static(const void* src, int src_dtype, int64_t rows, int64_t C, float* out, cudaStream_t st) {
+  ILFDT_REQUIRE(rows > 0 && C % 4 == 0 && C <= 1024, ILFDT_E_UNSUPPORTED_SHAPE,
+                "colsum_static: rows > 0 and width a multiple of 4, <= 1024");
+  const int grid = qm_grid(rows);                        // the same grid as launch_colsum: bit-identical sums
+  const int64_t need = (int64_t)grid * C * 4;
+  ILFDT_REQUIRE(need <= (int64_t)ILFDT_COLSUM_STATIC_SCRATCH_BYTES, ILFDT_E_INVALID_ARG,
+                "colsum_static: %lld rows x %lld columns need %lld bytes of partial sums (%d CTAs), the static scratch "
+                "holds %lld: use ilfdt_colsum with a caller workspace",
+                (long long)rows, (long long)C, (long long)need, grid, (long long)ILFDT_COLSUM_STATIC_SCRATCH_BYTES);
+  float* ws = nullptr;
+  if (int32_t rc = colsum_static_scratch(&ws)) return rc;
   if (src_dtype == ILFDT_BF16)
     colsum_partial_kernel<__nv_bfloat16><<<grid, QM_THREADS, 0, st>>>((const __nv_bfloat16*)src, rows, (int)C, ws);
   else

@@ -75,6 +75,7 @@ SIGNATURES = {
     "ilfdt_bias_cast": (_i32, [_p, _p, _i64, _i64, _p, _i32, _p]),
     "ilfdt_colsum_ws_bytes": (_i64, [_i64, _i64]),
     "ilfdt_colsum": (_i32, [_p, _i32, _i64, _i64, _p, _p, _i64, _p]),
+    "ilfdt_colsum_static": (_i32, [_p, _i32, _i64, _i64, _p, _p]),
     "ilfdt_randn_fill": (_i32, [_p, _i64, _u64, _u32, _p]),
     "ilfdt_copy": (_i32, [_p, _p, _i64, _p]),
 }

@@ -24,7 +24,7 @@ _KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_split3_bf16": 1, "ilfdt_cast_b
                      "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5, "ilfdt_nce_lse": 2, "ilfdt_nce_loss": 1,
                      "ilfdt_nce_bwd": 4, "ilfdt_nce_bwd_gathered": 2, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
                      "ilfdt_randn_fill": 1, "ilfdt_copy": 0,
-                     "ilfdt_gemm_tn_splitk": 2, "ilfdt_linear_bf16": 1, "ilfdt_ln_fwd": 1, "ilfdt_ln_bwd": 4, "ilfdt_bias_cast": 1, "ilfdt_colsum": 2}
+                     "ilfdt_gemm_tn_splitk": 2, "ilfdt_linear_bf16": 1, "ilfdt_ln_fwd": 1, "ilfdt_ln_bwd": 4, "ilfdt_bias_cast": 1, "ilfdt_colsum": 2, "ilfdt_colsum_static": 2}
 
 
 def _call(name, *args):
@@ -606,4 +606,16 @@ def colsum(src):
     nws = _lib.load().ilfdt_colsum_ws_bytes(R, C)
     ws = torch.empty(nws, dtype=torch.uint8, device=src.device)
     _call("ilfdt_colsum", _ptr(src), _DT[src.dtype], R, C, _ptr(out), _ptr(ws), nws, _stream())
+    return out
+
+
+def colsum_static(src, out):
+    """ilfdt_colsum_static (include/ilfdt.h): out[c] = sum_r src[r,c] into the caller's `out`, partial sums in the library's
+    static device scratch -- nothing is allocated here or in the library. Calls that overlap on the GPU race on that scratch."""
+    _req(src, None, "src")
+    _req(out, torch.float32, "out")
+    R, C = src.shape
+    if out.numel() != C:
+        raise ValueError("colsum_static: out must hold %d floats" % C)
+    _call("ilfdt_colsum_static", _ptr(src), _DT[src.dtype], R, C, _ptr(out), _stream())
     return out
