@@ -130,6 +130,13 @@ sparsemax_fwd_kernel(const float* __restrict__ z, int K, float* __restrict__ w,
 // by its ~8 passes over the staged row) and one barrier each (double-buffered partials).
 constexpr int SPX_MAXV = 8;
 
+// shared-memory accesses by 32-bit shared address (pointer arithmetic on the integer keeps the .shared state space)
+__device__ __forceinline__ uint32_t spx_saddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void spx_sts(uint32_t a, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory"); }
+__device__ __forceinline__ void spx_sts(uint32_t a, int v) { asm volatile("st.shared.s32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ double spx_lds_f64(uint32_t a) { double v; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a) : "memory"); return v; }
+__device__ __forceinline__ int spx_lds_s32(uint32_t a) { int v; asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a) : "memory"); return v; }
+
 // (s0, s1) += (m0, m1) * (x0, x1);  (c0, c1) += (m0, m1)   -- one packed fp32x2 FMA and one packed add
 __device__ __forceinline__ void masked_acc2(float& s0, float& s1, float& c0, float& c1, float m0, float m1, float x0, float x1) {
   asm("{\n .reg .b64 rm, rx, rs, rc;\n mov.b64 rm, {%4, %5};\n mov.b64 rx, {%6, %7};\n mov.b64 rs, {%0, %1};\n"
@@ -142,8 +149,8 @@ __device__ __forceinline__ void masked_acc2(float& s0, float& s1, float& c0, flo
 __global__ void __launch_bounds__(SPX_THREADS, 2)
 sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__ w, __nv_bfloat16* __restrict__ wb,
                          float* __restrict__ tau_out, int* __restrict__ nnz_out) {
-  __shared__ double red_s[2][SPX_THREADS / 32];
-  __shared__ int red_c[2][SPX_THREADS / 32];
+  __shared__ __align__(256) double red_s[2][SPX_THREADS / 32];
+  __shared__ __align__(128) int red_c[2][SPX_THREADS / 32];
   __shared__ float red_f[SPX_THREADS / 32];
   __shared__ double red_q[SPX_THREADS / 32];
   const int64_t r = blockIdx.x;
@@ -151,45 +158,42 @@ sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float4 v[SPX_MAXV];
   float mx = -INFINITY;
+  // one pass, one barrier: row maximum (exact: it is the shift of sparsemax.py:40) and the raw first two moments of
+  // the row. The moments only place the START of the threshold iteration (fp32 per thread, two chains; fp64 across
+  // threads): their rounding cannot change the result.
+  float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
   for (int j = 0; j < SPX_MAXV; ++j) {
     const int i = (j * SPX_THREADS + threadIdx.x) * 4;
     if (i < K) {
       v[j] = __ldg(reinterpret_cast<const float4*>(zr + i));
       mx = fmaxf(fmaxf(mx, fmaxf(v[j].x, v[j].y)), fmaxf(v[j].z, v[j].w));
+      s0 += v[j].x; s1 += v[j].y; s0 += v[j].z; s1 += v[j].w;
+      q0 = fmaf(v[j].x, v[j].x, q0); q1 = fmaf(v[j].y, v[j].y, q1);
+      q0 = fmaf(v[j].z, v[j].z, q0); q1 = fmaf(v[j].w, v[j].w, q1);
     } else {
       v[j] = make_float4(-1e30f, -1e30f, -1e30f, -1e30f);  // never above any threshold (tau >= -1), never counted
     }
   }
-  mx = warp_max(mx);
-  if (lane == 0) red_f[warp] = mx;
-  __syncthreads();
-  mx = red_f[0];
+  double ts, tq;
+  {
+    mx = warp_max(mx);
+    const double s = warp_sum((double)s0 + (double)s1), q = warp_sum((double)q0 + (double)q1);
+    if (lane == 0) { red_f[warp] = mx; red_s[0][warp] = s; red_q[warp] = q; }
+    __syncthreads();
+    mx = red_f[lane & 15];
+    ts = red_s[0][lane & 15];
+    tq = red_q[lane & 15];
 #pragma unroll
-  for (int i = 1; i < SPX_THREADS / 32; ++i) mx = fmaxf(mx, red_f[i]);
+    for (int o = 8; o > 0; o >>= 1) {
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      ts += __shfl_xor_sync(0xffffffffu, ts, o);
+      tq += __shfl_xor_sync(0xffffffffu, tq, o);
+    }
+  }
   // z <- z - max (sparsemax.py:40), in fp32 like the reference
 #pragma unroll
   for (int j = 0; j < SPX_MAXV; ++j) { v[j].x -= mx; v[j].y -= mx; v[j].z -= mx; v[j].w -= mx; }
-
-  // ---- pass 0: sum and sum of squares of the shifted row (fp32 per thread, two chains; fp64 across threads)
-  float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-#pragma unroll
-  for (int j = 0; j < SPX_MAXV; ++j) {
-    if ((j * SPX_THREADS + (int)threadIdx.x) * 4 < K) {
-      s0 += v[j].x; s1 += v[j].y; s0 += v[j].z; s1 += v[j].w;
-      q0 = fmaf(v[j].x, v[j].x, q0); q1 = fmaf(v[j].y, v[j].y, q1);
-      q0 = fmaf(v[j].z, v[j].z, q0); q1 = fmaf(v[j].w, v[j].w, q1);
-    }
-  }
-  double ts, tq;
-  {
-    const double s = warp_sum((double)s0 + (double)s1), q = warp_sum((double)q0 + (double)q1);
-    if (lane == 0) { red_s[0][warp] = s; red_q[warp] = q; }
-    __syncthreads();
-    ts = 0.0; tq = 0.0;
-#pragma unroll
-    for (int i = 0; i < SPX_THREADS / 32; ++i) { ts += red_s[0][i]; tq += red_q[i]; }
-  }
   // Michelot's iteration tau <- (sum_{z > tau} z - 1) / |{z > tau}| is Newton's method on the convex, decreasing
   // f(tau) = sum max(z - tau, 0) - 1: from ANY tau below the row maximum one step lands at or left of the root and the
   // iterates then increase monotonically to it, the support only shrinking. Started from the whole row (tau = mean - 1/K)
@@ -197,10 +201,10 @@ sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__
   // mean and variance -- K sigma g(t) = 1, g(t) = phi(t) - t Q(t), ln g(t) ~ -0.919 - 1.207 t - 0.359 t^2 on [-1.7, 3] --
   // and 3-4 passes remain. The final tau is the fixed point of the same update on the same (unique) support: the
   // result does not depend on the start.
-  const double kd = (double)K, mu = ts / kd;
-  double tau = fmax((ts - 1.0) / kd, -1.0);          // the whole-row step: always a valid start
+  const double kd = (double)K, mu_raw = ts / kd, mu = mu_raw - (double)mx;   // mean of the shifted row
+  double tau = fmax(mu - 1.0 / kd, -1.0);            // the whole-row step: always a valid start
   {
-    const double var = tq / kd - mu * mu;
+    const double var = tq / kd - mu_raw * mu_raw;    // (the variance does not see the shift)
     if (var > 0.0) {
       const float sigma = sqrtf((float)var);
       const float L = -__logf(1.f / ((float)K * sigma)) - 0.919f;
@@ -215,6 +219,10 @@ sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__
   // still below every value, its count is K although tau is not the fixed point. From the second pass on, equal counts
   // mean equal sets: a start right of the root sees a subset A of the support, the next one a superset B of it)
   int cnt_prev = -1;
+  // this pass writes buffer 1 first (pass 0 used red_s[0]); the buffers are 128-byte / 64-byte aligned blocks, so
+  // "the other buffer" is the same address with one bit flipped
+  uint32_t wr_s = spx_saddr(&red_s[1][warp]), rd_s = spx_saddr(&red_s[1][lane & 15]);
+  uint32_t wr_c = spx_saddr(&red_c[1][warp]), rd_c = spx_saddr(&red_c[1][lane & 15]);
   for (int it = 1; it < 256; ++it) {
     const float tf = (float)tau;  // compare in the precision the output uses
     // per-thread partial over its <= 32 values in fp32 (two independent chains; |error| ~ 1e-8 of a partial that is
@@ -230,19 +238,33 @@ sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__
     }
     const double s = warp_sum((double)a0 + (double)a1);
     const int c = __reduce_add_sync(0xffffffffu, (int)(c0 + c1));
-    if (lane == 0) { red_s[it & 1][warp] = s; red_c[it & 1][warp] = c; }
+    if (lane == 0) { spx_sts(wr_s, s); spx_sts(wr_c, c); }
     __syncthreads();
-    double ws = 0.0;
-    int tc = 0;
+    // second stage: the 16 warp partials, one per lane (both half-warps hold the same 16), folded with shuffles --
+    // 4 steps instead of a serial sum over 16 shared-memory loads in every thread
+    static_assert(SPX_THREADS / 32 == 16, "second-stage reduction folds 16 partials");
+    double ws = spx_lds_f64(rd_s);
+    int tc = spx_lds_s32(rd_c);
+    // (the two partial buffers alternate: pointers swapped by a constant XOR of their shared-memory byte offsets)
+    wr_s ^= (uint32_t)sizeof(double) * (SPX_THREADS / 32); rd_s ^= (uint32_t)sizeof(double) * (SPX_THREADS / 32);
+    wr_c ^= (uint32_t)sizeof(int) * (SPX_THREADS / 32); rd_c ^= (uint32_t)sizeof(int) * (SPX_THREADS / 32);
 #pragma unroll
-    for (int i = 0; i < SPX_THREADS / 32; ++i) { ws += red_s[it & 1][i]; tc += red_c[it & 1][i]; }
+    for (int o = 8; o > 0; o >>= 1) ws += __shfl_xor_sync(0xffffffffu, ws, o);
+    tc = __reduce_add_sync(0xffffffffu, tc) >> 1;
     if (tc == cnt_prev) break;
     cnt_prev = tc;
-    // every weight is <= 1, so tau >= max - 1 = -1 after the shift
-    tau = fmax((ws - 1.0) / (double)tc, -1.0);
+    // every weight is <= 1, so tau >= max - 1 = -1 after the shift. Quotient by a refined reciprocal (the IEEE fp64
+    // division is a ~40-instruction subroutine per thread and pass): relative error ~1e-15, tau is then rounded to fp32.
+    const double num = ws - 1.0, den = (double)tc;
+    float rcp_f;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rcp_f) : "f"((float)tc));
+    const double rcp = (double)rcp_f;
+    double qt = num * rcp;
+    qt = fma(fma(-qt, den, num), rcp, qt);
+    qt = fma(fma(-qt, den, num), rcp, qt);
+    tau = fmax(qt, -1.0);
   }
   const float tf = (float)tau;
-  int nz = 0;
   float* wr = w ? w + r * K : nullptr;   // optional: the tuned training path keeps only the bf16 copy
   __nv_bfloat16* wbr = wb ? wb + r * K : nullptr;
 #pragma unroll
@@ -251,7 +273,6 @@ sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__
     if (i < K) {
       const float4 o = make_float4(fmaxf(v[j].x - tf, 0.f), fmaxf(v[j].y - tf, 0.f), fmaxf(v[j].z - tf, 0.f),
                                    fmaxf(v[j].w - tf, 0.f));
-      nz += (o.x > 0.f) + (o.y > 0.f) + (o.z > 0.f) + (o.w > 0.f);
       if (wr) *reinterpret_cast<float4*>(wr + i) = o;
       if (wbr) {
         __nv_bfloat162 p2[2] = {__floats2bfloat162_rn(o.x, o.y), __floats2bfloat162_rn(o.z, o.w)};
@@ -259,16 +280,10 @@ sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__
       }
     }
   }
-  nz = warp_sum(nz);
-  __syncthreads();   // the last iteration's readers are done with red_c
-  if (lane == 0) red_c[0][warp] = nz;
-  __syncthreads();
   if (threadIdx.x == 0) {
-    int tn = 0;
-#pragma unroll
-    for (int i = 0; i < SPX_THREADS / 32; ++i) tn += red_c[0][i];
     if (tau_out) tau_out[r] = tf;
-    if (nnz_out) nnz_out[r] = tn;
+    // the support size is the count the iteration stopped on: z - tf > 0 exactly when z > tf
+    if (nnz_out) nnz_out[r] = cnt_prev;
   }
 }
 
