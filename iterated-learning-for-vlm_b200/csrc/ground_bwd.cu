@@ -790,12 +790,20 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const i
           else consume(bufB, cfB, nB);
         }
       } else {
+      int nxk = 0;
+      float nxc = 0.f;
+      if (lo + lane < hi) {
+        nxk = sorted_k[lo + lane];
+        nxc = coef_row[nxk];
+      }
       for (int e0 = lo; e0 < hi; e0 += 32) {
-          int myk = 0;
-          float myc = 0.f;
-          if (e0 + lane < hi) {
-            myk = sorted_k[e0 + lane];
-            myc = coef_row[myk];
+          const int myk = nxk;
+          const float myc = nxc;
+          nxk = 0;
+          nxc = 0.f;
+          if (e0 + 32 + lane < hi) {   // the next chunk's indices and coefficients: in flight behind this chunk's gathers
+            nxk = sorted_k[e0 + 32 + lane];
+            nxc = coef_row[nxk];
           }
           const int n = min(32, hi - e0);
           int j = 0;
@@ -821,6 +829,38 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const i
                   ffma2(acc[i][2 * q2], acc[i][2 * q2 + 1], cc[u], __uint_as_float(ww[q2] << 16),
                         __uint_as_float(ww[q2] & 0xffff0000u));
               }
+          }
+          if constexpr (sizeof(T) == 2) {
+            // the last 1..3 rows of the chunk as ONE partial batch: one at a time they cost a full L2 latency each --
+            // with ~39 entries per token (text, 77 tokens) that was 3 of the 12 round trips of a token
+            const int rem = n - j;   // warp-uniform
+            if (rem > 0) {
+              uint4 raw[3][NV];
+              float cc[3];
+#pragma unroll
+              for (int u = 0; u < 3; ++u) {
+                const int kq = __shfl_sync(0xffffffffu, myk, (j + u) & 31);
+                cc[u] = __shfl_sync(0xffffffffu, myc, (j + u) & 31);
+                if (u < rem) {
+                  const T* row = sd + (int64_t)(k0 + kq) * D;
+#pragma unroll
+                  for (int i = 0; i < NV; ++i) raw[u][i] = ldg_hint(row + (i * 32 + lane) * 8, row_pol);
+                }
+              }
+#pragma unroll
+              for (int u = 0; u < 3; ++u)
+                if (u < rem) {
+#pragma unroll
+                  for (int i = 0; i < NV; ++i) {
+                    const uint32_t ww[4] = {raw[u][i].x, raw[u][i].y, raw[u][i].z, raw[u][i].w};
+#pragma unroll
+                    for (int q2 = 0; q2 < 4; ++q2)
+                      ffma2(acc[i][2 * q2], acc[i][2 * q2 + 1], cc[u], __uint_as_float(ww[q2] << 16),
+                            __uint_as_float(ww[q2] & 0xffff0000u));
+                  }
+                }
+              j = n;
+            }
           }
           for (; j < n; ++j) {
             const int kq = __shfl_sync(0xffffffffu, myk, j);
