@@ -215,6 +215,56 @@ def test_sparsemax_large_rows(ops, rows, K, scale):
     assert_close(wb.float(), ref, 1e-2, "bf16 copy of w")
 
 
+def _sparsemax_rows(kind, rows, K, g):
+    """Row families that stress the START of the threshold iteration (the normal-model root, csrc/sparsemax.cu): the result
+    must not depend on it."""
+    if kind == "constant":            # zero variance: the model start is skipped
+        return torch.full((rows, K), 0.37)
+    if kind == "offset":              # |mean| >> sigma: the raw-moment variance is rounding noise (possibly negative)
+        return 1.0e4 + torch.randn(rows, K, generator=g) * 1e-2
+    if kind == "one_hot":             # one code far above the rest: support 1, tau = max - 1
+        x = torch.randn(rows, K, generator=g) * 1e-3
+        x[torch.arange(rows), torch.randint(0, K, (rows,), generator=g)] += 50.0
+        return x
+    if kind == "two_level":           # half the codes tied at the top
+        x = torch.zeros(rows, K)
+        x[:, ::2] = 3.0
+        return x
+    if kind == "heavy_tail":          # the normal model is far off: start right of the root
+        return torch.empty(rows, K).cauchy_(generator=g).clamp_(-1e4, 1e4) * 0.01
+    if kind == "skewed":              # max over tokens of normals, as the pooled scores are
+        return (torch.randn(rows, 49, K, generator=g) * 4e-4).max(1)[0]
+    if kind == "wide":                # support of a few codes, start left of the root
+        return torch.randn(rows, K, generator=g) * 30.0
+    if kind == "tiny":                # all weights ~ 1/K
+        return torch.randn(rows, K, generator=g) * 1e-7
+    raise ValueError(kind)
+
+
+@pytest.mark.parametrize("K", [16384, 4096, 8, 4, 1000, 2052])
+@pytest.mark.parametrize("kind", ["constant", "offset", "one_hot", "two_level", "heavy_tail", "skewed", "wide", "tiny"])
+def test_sparsemax_does_not_depend_on_the_start_of_the_iteration(ops, kind, K):
+    g = torch.Generator().manual_seed(K + len(kind))
+    rows = 6
+    x = _sparsemax_rows(kind, rows, K, g).float().contiguous()
+    w, wb, tau, nnz = ops.sparsemax_fwd(x.to(_dev()), want_bf16=True)
+    torch.cuda.synchronize()
+    wc = w.cpu()
+    assert torch.isfinite(wc).all()
+    assert torch.allclose(wc.sum(1), torch.ones(rows), atol=2e-4), wc.sum(1)
+    assert torch.equal((w > 0).sum(1).int().cpu(), nnz.cpu()), "nnz is not the support size"
+    for i in range(rows):
+        t64, supp, _ = O.sparsemax_tau_exact(x[i].numpy())
+        zi = (x[i] - x[i].max()).double().numpy()      # the shift is exact in fp32 and in fp64
+        ref = np.maximum(zi - t64, 0.0)
+        scale = max(1.0, float(np.abs(zi).max()) * 1e-7 / 1e-6)   # fp32 rounding of z - tau for rows with a large spread
+        assert np.abs(wc[i].numpy().astype(np.float64) - ref).max() <= 2e-6 * scale, (kind, K, i)
+        diff = np.nonzero((wc[i].numpy() > 0) != (ref > 0))[0]
+        for j in diff:
+            assert abs(zi[j] - t64) <= 1e-7 * max(1.0, abs(t64)), "support mismatch at (%d,%d) with margin %.3e" % (i, j, abs(zi[j] - t64))
+    assert_close(wb.float(), w, 1e-2, "bf16 copy of w")
+
+
 def test_sparsemax_bwd_closed_form(ops):
     g = torch.Generator().manual_seed(3)
     x = (torch.randn(9, 3000, generator=g) * 0.01).requires_grad_(True)
