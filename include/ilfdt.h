@@ -70,7 +70,9 @@ enum {
                                     pipelined groups of 2 (3 CTAs / SM), 2 = pipelined groups of 4 (2 CTAs / SM). Same order */
   ILFDT_TUNE_F32_X3 = 9,         /* F32 InfoNCE entry points: 1 (default) = the logits contractions run on the tensor cores as a
                                     3-term bf16 split (ilfdt_split3_bf16; fp32-grade: 7e-7 of fp64), 0 = SIMT FFMA kernels */
-  ILFDT_TUNE_COUNT_ = 10
+  ILFDT_TUNE_DQ_DEEP = 10,       /* ilfdt_ground_bwd* (bf16 rows): 1 (default) = launches with at most 2 x SM count samples keep 8
+                                    codebook rows in flight per warp instead of 4 (2 CTAs / SM); 0 = always 4. Same order */
+  ILFDT_TUNE_COUNT_ = 11
 };
 int32_t ilfdt_tune_set(int32_t key, int64_t value);
 int64_t ilfdt_tune_get(int32_t key);

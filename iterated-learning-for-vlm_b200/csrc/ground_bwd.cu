@@ -562,7 +562,10 @@ ground_bwd_dq_sorted_kernel(float* __restrict__ g, const TW* __restrict__ w, con
 // PG > 0 (bf16 rows): the gather loop is software-pipelined like kernel 2 v4 -- groups of PG codebook rows, the loads of
 // group i+1 issued before group i is consumed, the next 32-entry chunk's indices and coefficients prefetched behind the
 // current chunk's gathers -- so the per-batch L2 latency is no longer exposed (see ground_bwd_dsd_v4_kernel).
-template <typename T, int NV, typename TO, typename TW, int PG = 0, int MINB = 3>
+// NB = codebook rows a warp keeps in flight in the plain (PG == 0) gather loop: 4 at 3 CTAs per SM; 8 (MINB = 2) for
+// launches with fewer samples than resident CTA slots, where a sample's 3000 gathers are a latency chain on an SM that
+// holds one or two CTAs (ncu launch list of a 256-row step: 95 us per dq launch at 8.5 TB/s).
+template <typename T, int NV, typename TO, typename TW, int PG = 0, int MINB = 3, int NB = 4>
 __global__ void __launch_bounds__(G3_THREADS, MINB)
 ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const int16_t* __restrict__ arg,
                         const T* __restrict__ sd, const float* __restrict__ mask, int n_tok, int K, int D,
@@ -807,12 +810,12 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const i
           }
           const int n = min(32, hi - e0);
           int j = 0;
-          if constexpr (sizeof(T) == 2)  // bf16 rows: keep 4 of them in flight as raw 16-byte vectors
-          for (; j + 4 <= n; j += 4) {
-            uint4 raw[4][NV];
-            float cc[4];
+          if constexpr (sizeof(T) == 2)  // bf16 rows: keep NB of them in flight as raw 16-byte vectors
+          for (; j + NB <= n; j += NB) {
+            uint4 raw[NB][NV];
+            float cc[NB];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < NB; ++u) {
               const int kq = __shfl_sync(0xffffffffu, myk, j + u);
               cc[u] = __shfl_sync(0xffffffffu, myc, j + u);
               const T* row = sd + (int64_t)(k0 + kq) * D;
@@ -820,7 +823,7 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const i
               for (int i = 0; i < NV; ++i) raw[u][i] = ldg_hint(row + (i * 32 + lane) * 8, row_pol);
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < NB; ++u)
 #pragma unroll
               for (int i = 0; i < NV; ++i) {
                 const uint32_t ww[4] = {raw[u][i].x, raw[u][i].y, raw[u][i].z, raw[u][i].w};
@@ -831,14 +834,14 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const i
               }
           }
           if constexpr (sizeof(T) == 2) {
-            // the last 1..3 rows of the chunk as ONE partial batch: one at a time they cost a full L2 latency each --
+            // the last 1..NB-1 rows of the chunk as ONE partial batch: one at a time they cost a full L2 latency each --
             // with ~39 entries per token (text, 77 tokens) that was 3 of the 12 round trips of a token
-            const int rem = n - j;   // warp-uniform
+            const int rem = n - j;   // warp-uniform, < NB
             if (rem > 0) {
-              uint4 raw[3][NV];
-              float cc[3];
+              uint4 raw[NB - 1][NV];
+              float cc[NB - 1];
 #pragma unroll
-              for (int u = 0; u < 3; ++u) {
+              for (int u = 0; u < NB - 1; ++u) {
                 const int kq = __shfl_sync(0xffffffffu, myk, (j + u) & 31);
                 cc[u] = __shfl_sync(0xffffffffu, myc, (j + u) & 31);
                 if (u < rem) {
@@ -848,7 +851,7 @@ ground_bwd_dq_v3_kernel(float* __restrict__ g, const TW* __restrict__ w, const i
                 }
               }
 #pragma unroll
-              for (int u = 0; u < 3; ++u)
+              for (int u = 0; u < NB - 1; ++u)
                 if (u < rem) {
 #pragma unroll
                   for (int i = 0; i < NV; ++i) {
@@ -1462,16 +1465,16 @@ static int32_t launch_dsd_v3(const float* g, const int16_t* arg, const T* q, con
   return ILFDT_OK;
 }
 
-template <typename T, int NV, typename TO, typename TW, int PG, int MINB>
+template <typename T, int NV, typename TO, typename TW, int PG, int MINB, int NB = 4>
 static int32_t launch_dq_v3_t(float* g, const TW* w, const int16_t* arg, const T* sd, const float* mask, int64_t b,
                               int64_t n_tok, int64_t K, int64_t D, float inv_scale, TO* dq, const int* sparse_flag,
                               cudaStream_t st) {
   const size_t smem = (size_t)n_tok * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 + (G3_MAX_TOK + 1) * sizeof(int) +
                       G3_MAX_TOK * sizeof(float);
-  ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_v3_kernel<T, NV, TO, TW, PG, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  ILFDT_CUDA_OK(cudaFuncSetAttribute(ground_bwd_dq_v3_kernel<T, NV, TO, TW, PG, MINB, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)((size_t)G3_MAX_TOK * G3_THREADS * 2 + (size_t)G3_CHUNK * 2 +
                                            (G3_MAX_TOK + 1) * sizeof(int) + G3_MAX_TOK * sizeof(float))));
-  ground_bwd_dq_v3_kernel<T, NV, TO, TW, PG, MINB><<<(unsigned)b, G3_THREADS, smem, st>>>(g, w, arg, sd, mask, (int)n_tok,
+  ground_bwd_dq_v3_kernel<T, NV, TO, TW, PG, MINB, NB><<<(unsigned)b, G3_THREADS, smem, st>>>(g, w, arg, sd, mask, (int)n_tok,
                                                                                      (int)K, (int)D, inv_scale, dq, sparse_flag);
   ILFDT_LAUNCH_OK();
   return ILFDT_OK;
@@ -1485,6 +1488,9 @@ static int32_t launch_dq_v3(float* g, const TW* w, const int16_t* arg, const T* 
     const int64_t pipe = tune_get(ILFDT_TUNE_DQ_PIPE);   // 0 = batches of 4 with exposed latency (r1), 1 / 2 = pipelined
     if (pipe == 1) return launch_dq_v3_t<T, NV, TO, TW, 2, 3>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, sparse_flag, st);
     if (pipe == 2) return launch_dq_v3_t<T, NV, TO, TW, 4, 2>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, sparse_flag, st);
+    // fewer samples than two thirds of the resident CTA slots (3 per SM): 8 rows in flight per warp
+    if (pipe == 0 && tune_get(ILFDT_TUNE_DQ_DEEP) != 0 && b <= 2ll * sm_count())
+      return launch_dq_v3_t<T, NV, TO, TW, 0, 2, 8>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, sparse_flag, st);
   }
   return launch_dq_v3_t<T, NV, TO, TW, 0, 3>(g, w, arg, sd, mask, b, n_tok, K, D, inv_scale, dq, sparse_flag, st);
 }
