@@ -27,9 +27,11 @@ inline int32_t fail(int32_t code, const char* fmt, ...) {
 #define ILFDT_CUDA_OK(expr)                                                                    \
   do {                                                                                         \
     cudaError_t e__ = (expr);                                                                  \
-    if (e__ != cudaSuccess)                                                                    \
+    if (e__ != cudaSuccess) {                                                                  \
+      (void)cudaGetLastError(); /* reported here: do not leave it for the next launch check */ \
       return ::ilfdt::fail(ILFDT_E_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #expr,          \
                            cudaGetErrorString(e__));                                           \
+    }                                                                                          \
   } while (0)
 
 #define ILFDT_LAUNCH_OK()                                                                      \
