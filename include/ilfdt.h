@@ -125,6 +125,12 @@ int64_t ilfdt_text_plan_ints(int64_t b);
 int32_t ilfdt_ground_fwd_text_supported(int64_t n_tok);
 int32_t ilfdt_text_compact(const void* q, int32_t q_dtype, const float* mask, int64_t b, int64_t n_tok, int64_t D,
                            void* groups_ws, int32_t* plan, void* q_compact_bf16, void* stream);
+/* The same compaction for the fp32-grade score contraction (ilfdt_split3_bf16, clip_fdt.py:118 in fp32 arithmetic): row
+ * (row_base[s] + t) of q_compact_x3_bf16 (room for b*n_tok rows of 6*D bf16) holds the side-1 split of the fp32 source row,
+ * zeros for a pad. ilfdt_ground_fwd_text then takes it with the side-0 split of the codebook, D = 6 * the model width and
+ * sqrt_d = sqrt(model width). */
+int32_t ilfdt_text_compact_x3(const float* q, const float* mask, int64_t b, int64_t n_tok, int64_t D, void* groups_ws,
+                              int32_t* plan, void* q_compact_x3_bf16, void* stream);
 int32_t ilfdt_ground_fwd_text(const void* q_compact_bf16, const void* sd_bf16, const int32_t* plan, int64_t b,
                               int64_t n_tok, int64_t K, int64_t D, float sqrt_d, float temperature, float* pooled,
                               int16_t* arg, void* stream);

@@ -294,6 +294,16 @@ int32_t ilfdt_text_compact(const void* q, int32_t q_dtype, const float* mask, in
                              ST(stream));
 }
 
+int32_t ilfdt_text_compact_x3(const float* q, const float* mask, int64_t b, int64_t n_tok, int64_t D, void* groups_ws,
+                              int32_t* plan, void* q_compact_x3_bf16, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(b >= 0 && n_tok >= 1 && D >= 1, ILFDT_E_INVALID_ARG, "text_compact_x3: bad shape");
+  ILFDT_REQUIRE(b == 0 || (q && mask && groups_ws && plan && q_compact_x3_bf16), ILFDT_E_INVALID_ARG,
+                "text_compact_x3: null pointer");
+  return launch_text_compact(q, ILFDT_F32, mask, b, n_tok, D, reinterpret_cast<uint8_t*>(groups_ws), plan,
+                             q_compact_x3_bf16, ST(stream), 1);
+}
+
 int32_t ilfdt_ground_fwd_text(const void* q_compact_bf16, const void* sd_bf16, const int32_t* plan, int64_t b,
                               int64_t n_tok, int64_t K, int64_t D, float sqrt_d, float temperature, float* pooled,
                               int16_t* arg, void* stream) {

@@ -519,19 +519,29 @@ static int32_t launch_umma(const void* A, const void* B, int64_t M, int64_t N, i
   if (rc != ILFDT_OK) return rc;
   rc = make_tmap_bf16(&tmB, B, N, Kr, Kr, p.block_n);
   if (rc != ILFDT_OK) return rc;
-  if (EPI == EPI_POOLMAX && a_res && p.mask == nullptr) {
+  if (EPI == EPI_POOLMAX && p.mask == nullptr) {
+    // static token counts: unrolled max-pool epilogue. With a streamed A operand (reduction longer than 512: the 6x-wide
+    // operands of the fp32-grade contraction) the same epilogues exist for the bucket launches of the compacted text
+    // operand, which the generic epilogue does not serve (it has no slot map).
+#define ILFDT_POOLMAX_CASE(NT)                                                        \
+  case NT:                                                                            \
+    return a_res ? launch_umma_t<EPI_POOLMAX, true, NT>(tmA, tmB, p, st)              \
+                 : launch_umma_t<EPI_POOLMAX, false, NT>(tmA, tmB, p, st);
     switch (p.n_tok) {
-      case 16: return launch_umma_t<EPI_POOLMAX, true, 16>(tmA, tmB, p, st);
-      case 32: return launch_umma_t<EPI_POOLMAX, true, 32>(tmA, tmB, p, st);
-      case 48: return launch_umma_t<EPI_POOLMAX, true, 48>(tmA, tmB, p, st);
-      case 64: return launch_umma_t<EPI_POOLMAX, true, 64>(tmA, tmB, p, st);
-      case 49: return launch_umma_t<EPI_POOLMAX, true, 49>(tmA, tmB, p, st);
-      case 77: return launch_umma_t<EPI_POOLMAX, true, 77>(tmA, tmB, p, st);
-      case 196: return launch_umma_t<EPI_POOLMAX, true, 196>(tmA, tmB, p, st);
-      case 256: return launch_umma_t<EPI_POOLMAX, true, 256>(tmA, tmB, p, st);
+      ILFDT_POOLMAX_CASE(16)
+      ILFDT_POOLMAX_CASE(32)
+      ILFDT_POOLMAX_CASE(48)
+      ILFDT_POOLMAX_CASE(64)
+      ILFDT_POOLMAX_CASE(49)
+      ILFDT_POOLMAX_CASE(77)
+      ILFDT_POOLMAX_CASE(196)
+      ILFDT_POOLMAX_CASE(256)
       default: break;
     }
+#undef ILFDT_POOLMAX_CASE
   }
+  ILFDT_REQUIRE(!(EPI == EPI_POOLMAX && p.dyn != nullptr), ILFDT_E_UNSUPPORTED_SHAPE,
+                "bucket launch with %d tokens per sample has no static epilogue", p.n_tok);
   return a_res ? launch_umma_t<EPI, true>(tmA, tmB, p, st) : launch_umma_t<EPI, false>(tmA, tmB, p, st);
 }
 
@@ -712,7 +722,8 @@ int32_t launch_ground_fwd_text_bf16(const void* q_compact, const void* sd, const
   if (b == 0) return ILFDT_OK;
   ILFDT_REQUIRE(ground_fwd_text_supported(n_tok), ILFDT_E_UNSUPPORTED_SHAPE,
                 "ground_fwd_text: n_tok=%lld has a bucket size without a static epilogue", (long long)n_tok);
-  ILFDT_REQUIRE(D <= 512 && D % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "ground_fwd_text: D=%lld must be <= 512, %% 8",
+  // (D > 512: the 6x-wide operands of the fp32-grade 3 x bf16 contraction; both operands are streamed by the single-CTA kernel)
+  ILFDT_REQUIRE(D <= 6144 && D % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE, "ground_fwd_text: D=%lld must be <= 6144, %% 8",
                 (long long)D);
   ILFDT_REQUIRE(b * n_tok < (1ll << 31), ILFDT_E_UNSUPPORTED_SHAPE, "ground_fwd_text: b*n_tok too large");
   const int ngmax = (int)cdiv(n_tok, 16);

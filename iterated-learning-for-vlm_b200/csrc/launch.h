@@ -76,7 +76,7 @@ int32_t launch_ground2(const void* q, const void* sd, int64_t q_rows, int64_t n_
 // text_buckets.cu
 int64_t text_plan_ints(int64_t b);
 int32_t launch_text_compact(const void* q, int q_dtype, const float* mask, int64_t b, int64_t n_tok, int64_t D,
-                            uint8_t* groups_ws, int* plan, void* q_out, cudaStream_t st);
+                            uint8_t* groups_ws, int* plan, void* q_out, cudaStream_t st, int x3 = 0);
 int32_t launch_nce_lse_bf16(const void* x, const void* g, int64_t b, int64_t B, int64_t D, const float* scale,
                             int64_t label_offset, float* lse, float* diag, void* ws, int64_t ws_bytes, cudaStream_t st);
 int32_t launch_nce_fwd_bf16(const void* x_img, const void* x_txt, const void* g_img, const void* g_txt, int64_t b,

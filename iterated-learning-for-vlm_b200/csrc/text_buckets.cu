@@ -129,11 +129,46 @@ __global__ void text_compact_kernel(const T* __restrict__ q, const float* __rest
   }
 }
 
+// The same compaction for the fp32-grade score contraction (3-term bf16 split, kernels_simt.cu split3_bf16_kernel, side 1):
+// row (row_base[s] + t) of the output holds the six concatenated bf16 copies [x0 x1 x2 x0 x1 x0] of the fp32 source row
+// (zeros for a pad), 6 * D wide. One warp per (sample, token row).
+__global__ void text_compact_x3_kernel(const float* __restrict__ q, const float* __restrict__ mask,
+                                       const uint8_t* __restrict__ groups, const int* __restrict__ row_base, int b,
+                                       int n_tok, int D, __nv_bfloat16* __restrict__ out) {
+  const int64_t wid = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const int s = (int)(wid / n_tok), t = (int)(wid % n_tok);
+  if (s >= b) return;
+  const int rows = min(16 * (int)groups[s], n_tok);
+  if (t >= rows) return;
+  const bool keep = __ldg(mask + (int64_t)s * n_tok + t) == 0.f;
+  const float* src = q + ((int64_t)s * n_tok + t) * D;
+  __nv_bfloat16* dst = out + ((int64_t)row_base[s] + t) * (int64_t)(6 * D);
+  for (int c = lane * 4; c < D; c += 128) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (keep) v = __ldg(reinterpret_cast<const float4*>(src + c));
+    const float x[4] = {v.x, v.y, v.z, v.w};
+    __nv_bfloat16 tm[3][4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const __nv_bfloat16 h = __float2bfloat16_rn(x[e]);
+      const float r1 = x[e] - __bfloat162float(h);
+      const __nv_bfloat16 m = __float2bfloat16_rn(r1);
+      const float r2 = r1 - __bfloat162float(m);
+      tm[0][e] = h; tm[1][e] = m; tm[2][e] = __float2bfloat16_rn(r2);
+    }
+    const int pat[6] = {0, 1, 2, 0, 1, 0};   // side 1 of split3_bf16_kernel
+#pragma unroll
+    for (int s6 = 0; s6 < 6; ++s6)
+      *reinterpret_cast<uint2*>(dst + (int64_t)s6 * D + c) = *reinterpret_cast<const uint2*>(tm[pat[s6]]);
+  }
+}
+
 int64_t text_plan_ints(int64_t b) { return 4 * TB_MAX_BUCKETS + 3 * b; }
 
 // groups_ws: b bytes of scratch. plan: text_plan_ints(b) ints. q_out: [b * min(16*ceil(n_tok/16), n_tok) rows... upper bound b*n_tok, D] bf16.
 int32_t launch_text_compact(const void* q, int q_dtype, const float* mask, int64_t b, int64_t n_tok, int64_t D,
-                            uint8_t* groups_ws, int* plan, void* q_out, cudaStream_t st) {
+                            uint8_t* groups_ws, int* plan, void* q_out, cudaStream_t st, int x3) {
   if (b == 0) return ILFDT_OK;
   ILFDT_REQUIRE(n_tok >= 1 && n_tok <= 256 && D % 8 == 0, ILFDT_E_UNSUPPORTED_SHAPE,
                 "text_compact: n_tok in [1,256], D %% 8 == 0 required");
@@ -146,7 +181,13 @@ int32_t launch_text_compact(const void* q, int q_dtype, const float* mask, int64
   ILFDT_LAUNCH_OK();
   const int64_t warps = b * n_tok;
   const int* row_base = plan + 4 * TB_MAX_BUCKETS + b;
-  if (q_dtype == ILFDT_F32)
+  if (x3) {
+    ILFDT_REQUIRE(q_dtype == ILFDT_F32 && D % 4 == 0, ILFDT_E_UNSUPPORTED_SHAPE,
+                  "text_compact_x3: fp32 rows with D %% 4 == 0 required");
+    text_compact_x3_kernel<<<(unsigned)cdiv(warps * 32, 256), 256, 0, st>>>(
+        reinterpret_cast<const float*>(q), mask, groups_ws, row_base, (int)b, (int)n_tok, (int)D,
+        reinterpret_cast<__nv_bfloat16*>(q_out));
+  } else if (q_dtype == ILFDT_F32)
     text_compact_kernel<float><<<(unsigned)cdiv(warps * 32, 256), 256, 0, st>>>(
         reinterpret_cast<const float*>(q), mask, groups_ws, row_base, (int)b, (int)n_tok, (int)D,
         reinterpret_cast<__nv_bfloat16*>(q_out));

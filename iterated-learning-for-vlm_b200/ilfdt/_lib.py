@@ -35,6 +35,7 @@ SIGNATURES = {
     "ilfdt_text_plan_ints": (_i64, [_i64]),
     "ilfdt_ground_fwd_text_supported": (_i32, [_i64]),
     "ilfdt_text_compact": (_i32, [_p, _i32, _p, _i64, _i64, _i64, _p, _p, _p, _p]),
+    "ilfdt_text_compact_x3": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _p]),
     "ilfdt_ground_fwd_text": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _p, _p, _p]),
     "ilfdt_sparsemax_fwd": (_i32, [_p, _i64, _i64, _p, _p, _p, _p, _p]),
     "ilfdt_sparsemax_bwd": (_i32, [_p, _p, _i64, _i64, _p, _p]),

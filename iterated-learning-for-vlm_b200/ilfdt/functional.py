@@ -137,9 +137,16 @@ def _score_pool(q, sd_c, mask_f, temperature, mode):
         q_k, sd_k, sd_kt = q, sd_c, None
         if _x3_ok(q, sd_c):
             # pad rows are zeroed in the split operand: their score is exactly the 0 of clip_fdt.py:125-130
-            rowmask = None if mask_f is None else mask_f.reshape(-1)
-            pooled, arg = ops.ground_fwd(ops.split3_bf16(q, 1, rowmask), ops.split3_bf16(sd_c, 0), None, temperature,
-                                         "max", sqrt_d=math.sqrt(q.shape[2]))
+            sd_x3 = ops.split3_bf16(sd_c, 0)
+            if mask_f is not None and COMPACT_TEXT and ops.text_supported(q.shape[1]):
+                # padded text: only the valid rows + one pad per sample are split and contracted (as in the bf16 mode;
+                # the backward reads the fp32 q itself, so nothing else changes)
+                q_x3, plan = ops.text_compact_x3(q, mask_f)
+                pooled, arg = ops.ground_fwd_text(q_x3, sd_x3, plan, q.shape[1], temperature, sqrt_d=math.sqrt(q.shape[2]))
+            else:
+                rowmask = None if mask_f is None else mask_f.reshape(-1)
+                pooled, arg = ops.ground_fwd(ops.split3_bf16(q, 1, rowmask), sd_x3, None, temperature, "max",
+                                             sqrt_d=math.sqrt(q.shape[2]))
         else:
             pooled, arg = ops.ground_fwd(q_k, sd_k, mask_f, temperature, "max")
     return pooled, arg, q_k, sd_k, sd_kt, row_base

@@ -19,7 +19,7 @@ def _stream():
 LAUNCHES = 0          # kernels launched through this module since it was last zeroed
 PROFILE_ON = False    # when True every C call is bracketed by CUDA events on the launching stream
 PROFILE = {}          # op name -> [(start_event, end_event), ...]
-_KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_split3_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mask_rows_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_ground_fwd_text": 5, "ilfdt_text_compact": 3, "ilfdt_sparsemax_fwd": 1,
+_KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_split3_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mask_rows_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_ground_fwd_text": 5, "ilfdt_text_compact": 3, "ilfdt_text_compact_x3": 3, "ilfdt_sparsemax_fwd": 1,
                      "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_nt_splitk": 2, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2, "ilfdt_ground_bwd_w16": 2,   # + 2 regime launches that return at once
                      "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5, "ilfdt_nce_lse": 2, "ilfdt_nce_loss": 1,
                      "ilfdt_nce_bwd": 4, "ilfdt_nce_bwd_gathered": 2, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
@@ -191,15 +191,30 @@ def text_compact(q, mask):
     return out, TextPlan(plan, b)
 
 
-def ground_fwd_text(q_compact, sd, plan, n_tok, temperature):
-    """compacted bf16 operand + plan, bf16 sd [K,D] -> pooled [b,K] f32, arg [b,K] int16 (max pooling)."""
+def text_compact_x3(q, mask):
+    """q [b,N,D] f32, mask [b,N] -> (compacted side-1 split3 operand [b*N, 6D] bf16 of which only the planned rows are
+    written, TextPlan): text_compact for the fp32-grade 3 x bf16 score contraction."""
+    lib = _lib.load()
+    _req(q, torch.float32, "q"); _req(mask, torch.float32, "mask")
+    b, n_tok, D = q.shape
+    assert tuple(mask.shape) == (b, n_tok)
+    plan = torch.empty(lib.ilfdt_text_plan_ints(b), dtype=torch.int32, device=q.device)
+    groups = torch.empty(max(b, 1), dtype=torch.uint8, device=q.device)
+    out = torch.empty(b * n_tok, 6 * D, dtype=torch.bfloat16, device=q.device)
+    _call("ilfdt_text_compact_x3", _ptr(q), _ptr(mask), b, n_tok, D, _ptr(groups), _ptr(plan), _ptr(out), _stream())
+    return out, TextPlan(plan, b)
+
+
+def ground_fwd_text(q_compact, sd, plan, n_tok, temperature, sqrt_d=None):
+    """compacted bf16 operand + plan, bf16 sd [K,D] -> pooled [b,K] f32, arg [b,K] int16 (max pooling). sqrt_d: the score
+    scale when D is not the model width (the 6x-wide operands of the 3 x bf16 contraction)."""
     _req(q_compact, torch.bfloat16, "q_compact"); _req(sd, torch.bfloat16, "sd")
     b = plan.b
     K, D = sd.shape
     pooled = torch.empty(b, K, dtype=torch.float32, device=sd.device)
     arg = torch.empty(b, K, dtype=torch.int16, device=sd.device)
-    _call("ilfdt_ground_fwd_text", _ptr(q_compact), _ptr(sd), _ptr(plan.buf), b, n_tok, K, D, float(math.sqrt(D)),
-          float(temperature), _ptr(pooled), _ptr(arg), _stream())
+    _call("ilfdt_ground_fwd_text", _ptr(q_compact), _ptr(sd), _ptr(plan.buf), b, n_tok, K, D,
+          float(math.sqrt(D) if sqrt_d is None else sqrt_d), float(temperature), _ptr(pooled), _ptr(arg), _stream())
     return pooled, arg
 
 
