@@ -56,6 +56,25 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return y;
 }
 
+// dOut epilogue of a split item: 32 consecutive columns of one output row added into global memory. A thread owns a row,
+// so a warp's scalar atomics are 32 uncoalesced requests per instruction and 128 instructions per thread: ~17 us of
+// LSU time per item, more than the whole tile loop at b <= 256 (ncu, 256-row step: 39 us per launch). 16-byte vector
+// reductions (REDG.E.ADD.F32x4) need a quarter of the requests.
+__device__ __forceinline__ void nce_red_row32(float* o, const uint32_t (&v)[32], float scale, int c0, int dcols, bool vec_ok) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 4) {
+    if (vec_ok && c0 + j + 3 < dcols) {
+      asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o + j), "f"(__uint_as_float(v[j]) * scale),
+                   "f"(__uint_as_float(v[j + 1]) * scale), "f"(__uint_as_float(v[j + 2]) * scale),
+                   "f"(__uint_as_float(v[j + 3]) * scale) : "memory");
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if (c0 + j + e < dcols) atomicAdd(o + j + e, __uint_as_float(v[j + e]) * scale);
+    }
+  }
+}
+
 // Executed by the first two warps (tid128 < 64) of a softmax group: fetch (global -> registers; may be issued a
 // tile ahead) and publish (registers -> shared, before the group's named barrier).
 template <int MODE>

@@ -262,9 +262,7 @@ nce_bwd_kernel(const __grid_constant__ CUtensorMap tmXL, const __grid_constant__
         if (row_ok) {
           float* o = p.out + (int64_t)row * p.D + half * 256 + c0;
           if (p.use_atomic) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (c0 + j < dcols) atomicAdd(o + j, __uint_as_float(v[j]) * scale);
+            nce_red_row32(o, v, scale, c0, dcols, (p.D & 3) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
           } else {
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
