@@ -727,6 +727,10 @@ int32_t launch_ground_fwd_text_bf16(const void* q_compact, const void* sd, const
                 (long long)D);
   ILFDT_REQUIRE(b * n_tok < (1ll << 31), ILFDT_E_UNSUPPORTED_SHAPE, "ground_fwd_text: b*n_tok too large");
   const int ngmax = (int)cdiv(n_tok, 16);
+  // small batches: one launch over the tiles of all buckets (ground_umma2.cu); large ones keep a static kernel per bucket
+  if (ground2_enabled() && b <= tune_get(ILFDT_TUNE_TEXT_MERGED_MAX_B) && ground2_text_merged_supported(n_tok, D))
+    return launch_ground2_text_merged(q_compact, sd, b * n_tok, b, n_tok, K, D, 1.f / (sqrt_d * temperature), pooled, arg, plan,
+                                      plan + 4 * 16 + 2 * b, st);
   for (int g = 1; g <= ngmax; ++g) {
     const int R = (int)std::min<int64_t>(16 * g, n_tok);
     if (ground2_enabled() && ground2_supported(R, D)) {

@@ -183,6 +183,191 @@ ground2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 }
 
+// ---- all text buckets in ONE launch (small batches) ---------------------------------------------------
+// Five launches of ground2_kernel<R> (one per bucket of the compacted text operand, text_buckets.cu) each end in their own
+// partial wave, and the host cannot size their items because the bucket populations only exist on the device: at 256 rows
+// the five launches take 185 us for 156 us of tensor work, at 64 rows 88 us for 40. This kernel walks the tiles of ALL
+// buckets as one flat list: work unit w = code-tile pair * T + t, t = 0 .. T-1 over the buckets' token tiles in bucket
+// order (T read from the plan on the device); cluster c takes the contiguous range [c W / C, (c + 1) W / C) -- equal to
+// within one tile, and the resident codebook tile changes at most twice per cluster. What varies per bucket (rows per
+// sample, samples per tile, UMMA N, the TMA box) is looked up per tile; the epilogue dispatches to the same statically
+// unrolled bodies. Results are the same bits as the per-bucket launches (same MMAs per tile, same epilogue).
+constexpr int G2T_MAX_BUCKETS = 5;
+
+struct G2TextMaps {
+  CUtensorMap b[G2T_MAX_BUCKETS];   // one per bucket: box = block_n / 2 rows x 64
+};
+
+struct G2TextParams {
+  int ng;                      // buckets
+  int num_m_pairs, nkb, m_rows;
+  int rows[G2T_MAX_BUCKETS];   // token rows per sample of the bucket (R)
+  int spt[G2T_MAX_BUCKETS], n_step[G2T_MAX_BUCKETS], block_n[G2T_MAX_BUCKETS];
+  uint32_t idesc[G2T_MAX_BUCKETS];
+  float pool_scale;
+  float* pooled;
+  int16_t* arg;
+  const int* plan;             // 4 ints per bucket {samples, first row, first slot, rows per sample}
+  const int* sample_map;
+};
+
+struct G2TextSched {
+  int tile0[G2T_MAX_BUCKETS + 1];   // first flat tile index of each bucket; [ng] = T
+  int samples[G2T_MAX_BUCKETS], row0[G2T_MAX_BUCKETS], slot0[G2T_MAX_BUCKETS];
+};
+
+__device__ __forceinline__ int g2t_bucket_of(const G2TextSched& sc, int ng, int t) {
+  int g = 0;
+#pragma unroll
+  for (int i = 1; i < G2T_MAX_BUCKETS; ++i)
+    if (i < ng && t >= sc.tile0[i]) g = i;
+  return g;
+}
+
+__global__ void __launch_bounds__(G2_THREADS, 1)
+ground2_text_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ G2TextMaps tmB, const G2TextParams p) {
+  extern __shared__ uint8_t g2_smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(g2_smem_raw) + 1023) & ~(uintptr_t)1023);
+  G2Bars* bars = reinterpret_cast<G2Bars*>(smem + G2_DATA_BYTES);
+  uint8_t* ring = smem + 8 * G2_A_BYTES;
+  __shared__ G2TextSched sc;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < G2_STAGES; ++i) { mbar_init(&bars->full[i], 1); mbar_init(&bars->empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&bars->tmem_full[i], 1); mbar_init(&bars->tmem_empty[i], 8); }
+    mbar_init(&bars->a_full, 1);
+    mbar_init(&bars->a_empty, 1);
+    fence_barrier_init();
+    tma_prefetch_desc(&tmA);
+    int t = 0;
+    for (int g = 0; g < p.ng; ++g) {
+      const int n = __ldg(p.plan + 4 * g);
+      sc.samples[g] = n;
+      sc.row0[g] = __ldg(p.plan + 4 * g + 1);
+      sc.slot0[g] = __ldg(p.plan + 4 * g + 2);
+      sc.tile0[g] = t;
+      t += (n + p.spt[g] - 1) / p.spt[g];
+    }
+    for (int g = p.ng; g <= G2T_MAX_BUCKETS; ++g) sc.tile0[g] = t;
+  }
+  if (warp == 1) {
+    tmem_alloc_pair(&bars->tmem_ptr, 512);
+    tmem_relinquish_pair();
+  }
+  fence_before_sync();
+  __syncthreads();
+  cluster_sync_all();
+  fence_after_sync();
+  const uint32_t tmem_base = bars->tmem_ptr;
+  const int T = sc.tile0[p.ng];
+  const long long W = (long long)p.num_m_pairs * T;
+  const int w_begin = (int)(W * cluster_id / num_clusters), w_end = (int)(W * (cluster_id + 1) / num_clusters);
+
+  if (warp == 0) {
+    // ===================== TMA producer (one thread in each CTA) =====================
+    if (elect_one()) {
+      uint32_t stage = 0, phase = 0, it = 0;
+      int cur_m = -1;
+      for (int w = w_begin; w < w_end; ++w) {
+        const int m_pair = w / T, t = w - m_pair * T;
+        if (m_pair != cur_m) {
+          cur_m = m_pair;
+          mbar_wait(&bars->a_empty, (it & 1) ^ 1);
+          if (leader) mbar_expect_tx(&bars->a_full, 2u * (uint32_t)p.nkb * G2_A_BYTES);
+          for (int kb = 0; kb < p.nkb; ++kb)
+            tma_load_2d_pair(smem + kb * G2_A_BYTES, &tmA, &bars->a_full, kb * 64, (2 * m_pair + (int)rank) * 128, kEvictLast);
+          ++it;
+        }
+        const int g = g2t_bucket_of(sc, p.ng, t);
+        const int n = t - sc.tile0[g];
+        const int r0 = sc.row0[g] + n * p.n_step[g] + (int)rank * (p.block_n[g] >> 1);
+        for (int kb = 0; kb < p.nkb; ++kb) {
+          mbar_wait(&bars->empty[stage], phase ^ 1);
+          if (leader) mbar_expect_tx(&bars->full[stage], (uint32_t)p.block_n[g] * 128u);
+          tma_load_2d_pair(ring + stage * G2_B_BYTES, &tmB.b[g], &bars->full[stage], kb * 64, r0, kEvictNormal);
+          if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (leader && elect_one()) {
+      uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0, it = 0;
+      int cur_m = -1;
+      for (int w = w_begin; w < w_end; ++w) {
+        const int m_pair = w / T, t = w - m_pair * T;
+        if (m_pair != cur_m) {
+          if (cur_m >= 0) mma_commit_pair(&bars->a_empty);   // every MMA that reads the previous resident tile has been issued
+          cur_m = m_pair;
+          mbar_wait(&bars->a_full, it & 1);
+          fence_after_sync();
+          ++it;
+        }
+        const int g = g2t_bucket_of(sc, p.ng, t);
+        const uint32_t idesc = p.idesc[g];
+        mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
+        fence_after_sync();
+        const uint32_t tmem_d = tmem_base + acc * 256;
+        for (int kb = 0; kb < p.nkb; ++kb) {
+          mbar_wait(&bars->full[stage], phase);
+          fence_after_sync();
+          const uint64_t adesc = make_smem_desc_sw128(smem_u32(smem + kb * G2_A_BYTES));
+          const uint64_t bdesc = make_smem_desc_sw128(smem_u32(ring + stage * G2_B_BYTES));
+#pragma unroll
+          for (int k4 = 0; k4 < 4; ++k4)
+            mma_f16_pair(tmem_d, advance_desc_k(adesc, k4 * 32), advance_desc_k(bdesc, k4 * 32), idesc, (kb | k4) != 0 ? 1u : 0u);
+          mma_commit_pair(&bars->empty[stage]);
+          if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
+        }
+        mma_commit_pair(&bars->tmem_full[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ===================== epilogue warps (2..9) of both CTAs: group g drains accumulator g =====================
+    const int quad = warp & 3;
+    const uint32_t group = (uint32_t)(warp - 2) >> 2;
+    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    uint32_t tile_seq = 0;
+    for (int w = w_begin; w < w_end; ++w, ++tile_seq) {
+      const uint32_t acc = tile_seq & 1, acc_phase = (tile_seq >> 1) & 1;
+      if (acc != group) continue;
+      const int m_pair = w / T, t = w - m_pair * T;
+      const int g = g2t_bucket_of(sc, p.ng, t);
+      const int n = t - sc.tile0[g];
+      const int row = (2 * m_pair + (int)rank) * 128 + quad * 32 + lane;  // code owned by this thread
+      const bool row_ok = row < p.m_rows;
+      const uint32_t taddr = tmem_base + lane_addr + acc * 256;
+      const int s0 = n * p.spt[g], ns = sc.samples[g], slot0 = sc.slot0[g];
+      mbar_wait(&bars->tmem_full[acc], acc_phase);
+      fence_after_sync();
+      switch (p.rows[g]) {
+        case 16: poolmax_static<16>(taddr, s0, ns, row, row_ok, p.m_rows, p.pool_scale, p.pooled, p.arg, p.sample_map, slot0); break;
+        case 32: poolmax_static<32>(taddr, s0, ns, row, row_ok, p.m_rows, p.pool_scale, p.pooled, p.arg, p.sample_map, slot0); break;
+        case 48: poolmax_static<48>(taddr, s0, ns, row, row_ok, p.m_rows, p.pool_scale, p.pooled, p.arg, p.sample_map, slot0); break;
+        case 64: poolmax_static<64>(taddr, s0, ns, row, row_ok, p.m_rows, p.pool_scale, p.pooled, p.arg, p.sample_map, slot0); break;
+        default: poolmax_static<77>(taddr, s0, ns, row, row_ok, p.m_rows, p.pool_scale, p.pooled, p.arg, p.sample_map, slot0); break;
+      }
+      fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&bars->tmem_empty[acc], 0);
+    }
+  }
+
+  fence_before_sync();
+  cluster_sync_all();   // neither CTA may free TMEM or exit while its peer can still touch its barriers / smem
+  if (warp == 1) {
+    fence_after_sync();
+    tmem_dealloc_pair(tmem_base, 512);
+  }
+}
+
 // ---- host side --------------------------------------------------------------------------------------
 static void g2_plan(int num_m, int num_n_tiles, int workers, int& nchunk, int& tiles_per_chunk) {
   int best_c = 1;
@@ -282,6 +467,71 @@ int32_t launch_ground2(const void* q, const void* sd, int64_t q_rows, int64_t n_
     default: break;
   }
   return fail(ILFDT_E_UNSUPPORTED_SHAPE, "ground2: n_tok=%lld has no static epilogue", (long long)n_tok);
+}
+
+// All buckets of the compacted text operand in one launch (ground2_text_kernel). n_tok's buckets must be 16 / 32 / 48 / 64 / 77.
+bool ground2_text_merged_supported(int64_t n_tok, int64_t D) {
+  if (!(D <= 512 && D % 8 == 0)) return false;
+  if (n_tok > 77 || cdiv(n_tok, 16) > G2T_MAX_BUCKETS) return false;
+  const int64_t last = n_tok;
+  return last == 16 || last == 32 || last == 48 || last == 64 || last == 77;
+}
+
+int32_t launch_ground2_text_merged(const void* q, const void* sd, int64_t q_rows, int64_t b, int64_t n_tok, int64_t K, int64_t D,
+                                   float pool_scale, float* pooled, int16_t* arg, const int* plan, const int* sample_map,
+                                   cudaStream_t st) {
+  G2TextParams p{};
+  G2TextMaps maps{};
+  p.ng = (int)cdiv(n_tok, 16);
+  p.nkb = (int)cdiv(D, 64);
+  p.m_rows = (int)K;
+  p.num_m_pairs = (int)cdiv(K, 256);
+  p.pool_scale = pool_scale;
+  p.pooled = pooled;
+  p.arg = arg;
+  p.plan = plan;
+  p.sample_map = sample_map;
+  CUtensorMap tmA;
+  int32_t rc = make_tmap_bf16(&tmA, sd, K, D, D, 128);
+  if (rc != ILFDT_OK) return rc;
+  for (int g = 0; g < p.ng; ++g) {
+    const int R = (int)std::min<int64_t>(16 * (g + 1), n_tok);
+    p.rows[g] = R;
+    p.spt[g] = 256 / R;
+    p.n_step[g] = p.spt[g] * R;
+    p.block_n[g] = (int)round_up(p.n_step[g], 16);
+    p.idesc[g] = make_idesc_bf16(256, p.block_n[g]);
+    if ((rc = make_tmap_bf16(&maps.b[g], q, q_rows, D, D, p.block_n[g] / 2)) != ILFDT_OK) return rc;
+  }
+  static thread_local int configured_dev = -1;
+  static thread_local int max_clusters = 0;
+  int dev = 0;
+  ILFDT_CUDA_OK(cudaGetDevice(&dev));
+  cudaLaunchConfig_t cfg{};
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.blockDim = dim3(G2_THREADS);
+  cfg.dynamicSmemBytes = G2_SMEM_BYTES;
+  cfg.stream = st;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (configured_dev != dev) {
+    ILFDT_CUDA_OK(cudaFuncSetAttribute(ground2_text_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G2_SMEM_BYTES));
+    cfg.gridDim = dim3(2 * (sm_count() / 2));
+    int n = 0;
+    ILFDT_CUDA_OK(cudaOccupancyMaxActiveClusters(&n, ground2_text_kernel, &cfg));
+    ILFDT_REQUIRE(n >= 1, ILFDT_E_CUDA, "ground2_text: no CTA pair can be resident");
+    max_clusters = std::min(n, sm_count() / 2);
+    configured_dev = dev;
+  }
+  // upper bound of the flat tile count (every sample in the bucket with the fewest samples per tile) caps the grid
+  const int64_t max_tiles = cdiv(b, 256 / std::min<int64_t>(n_tok, 77)) + p.ng;
+  cfg.gridDim = dim3(2 * (unsigned)std::min<int64_t>(max_clusters, std::max<int64_t>(1, p.num_m_pairs * max_tiles)));
+  ILFDT_CUDA_OK(cudaLaunchKernelEx(&cfg, ground2_text_kernel, tmA, maps, p));
+  return ILFDT_OK;
 }
 
 }  // namespace ilfdt

@@ -73,6 +73,10 @@ bool ground2_supported(int64_t n_tok, int64_t D);
 int32_t launch_ground2(const void* q, const void* sd, int64_t q_rows, int64_t n_samples, int64_t n_tok, int64_t K, int64_t D,
                        float pool_scale, float* pooled, int16_t* arg, const int* dyn, const int* sample_map,
                        int64_t est_samples, cudaStream_t st);
+bool ground2_text_merged_supported(int64_t n_tok, int64_t D);
+int32_t launch_ground2_text_merged(const void* q, const void* sd, int64_t q_rows, int64_t b, int64_t n_tok, int64_t K, int64_t D,
+                                   float pool_scale, float* pooled, int16_t* arg, const int* plan, const int* sample_map,
+                                   cudaStream_t st);
 // text_buckets.cu
 int64_t text_plan_ints(int64_t b);
 int32_t launch_text_compact(const void* q, int q_dtype, const float* mask, int64_t b, int64_t n_tok, int64_t D,

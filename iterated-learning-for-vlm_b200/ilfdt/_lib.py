@@ -82,7 +82,7 @@ SIGNATURES = {
 }
 
 TUNE = {"dsd_split_rows": 0, "dsd_tile": 1, "dsd_stream": 2, "ground_2cta": 3, "gemm_wide2": 4, "nce_2cta": 5,
-        "sparse_bwd_nnz": 6, "dsd_pipe": 7, "dq_pipe": 8, "f32_x3": 9, "dq_deep": 10}
+        "sparse_bwd_nnz": 6, "dsd_pipe": 7, "dq_pipe": 8, "f32_x3": 9, "dq_deep": 10, "text_merged_max_b": 11}
 
 _lib = None
 

@@ -396,10 +396,13 @@ def test_grounding_without_fp32_weights(ops, b, n_tok, K, D, masked, qdtype):
 @pytest.mark.parametrize("b,n_tok,K,D", [(37, 77, 384, 512), (300, 77, 1024, 512), (64, 49, 256, 256), (9, 64, 512, 64),
                                         (1500, 77, 256, 512)])
 @pytest.mark.parametrize("qdtype", ["f32", "bf16"])
-def test_ground_fwd_text_buckets_equal_full_width(ops, b, n_tok, K, D, qdtype):
+@pytest.mark.parametrize("merged", [True, False])
+def test_ground_fwd_text_buckets_equal_full_width(ops, b, n_tok, K, D, qdtype, merged):
     """ilfdt_text_compact + ilfdt_ground_fwd_text (valid rows + one pad per sample, bucketed by 16-row groups) must
     reproduce the full-width tensor-core kernel bit for bit -- pooled AND argmax: every pad scores exactly 0
-    (clip_fdt.py:125-130). Also checks the device-side plan (a permutation, slabs disjoint and in range)."""
+    (clip_fdt.py:125-130). Also checks the device-side plan (a permutation, slabs disjoint and in range).
+    merged: all buckets in one launch (ILFDT_TUNE_TEXT_MERGED_MAX_B, the default for small batches where n_tok's
+    buckets allow it) / one launch per bucket."""
     g = torch.Generator().manual_seed(b + n_tok)
     q = torch.randn(b, n_tok, D, generator=g)
     sd = torch.randn(K, D, generator=g)
@@ -418,7 +421,8 @@ def test_ground_fwd_text_buckets_equal_full_width(ops, b, n_tok, K, D, qdtype):
     sd_k = ops.cast_bf16(sd.to(dev))
     pooled_f, arg_f = ops.ground_fwd(q_full, sd_k, None, 30.0, "max")
     q_c, plan = ops.text_compact(qd, mask.to(dev))
-    pooled_t, arg_t = ops.ground_fwd_text(q_c, sd_k, plan, n_tok, 30.0)
+    with ops.tune(text_merged_max_b=(1 << 20) if merged else 0):
+        pooled_t, arg_t = ops.ground_fwd_text(q_c, sd_k, plan, n_tok, 30.0)
     assert torch.equal(pooled_f, pooled_t)
     assert torch.equal(arg_f, arg_t)
     # plan sanity
