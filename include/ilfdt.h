@@ -159,6 +159,15 @@ int32_t ilfdt_gemm_nt(const void* A, const void* B, int32_t dtype, int64_t M, in
 int64_t ilfdt_gemm_nt_splitk_ws_bytes(int64_t M, int64_t N, int64_t Kr);
 int32_t ilfdt_gemm_nt_splitk(const void* A_bf16, const void* B_bf16, int64_t M, int64_t N, int64_t Kr, float alpha,
                              int32_t accumulate, float* out, int64_t ldo, void* ws, int64_t ws_bytes, void* stream);
+/* The same product with A given as [Kr, M] row-major -- the reduction index OUTERMOST, i.e. the bf16 codebook sd [K, D] itself
+ * for the pooling f[b,D] = w[b,K] . sd[K,D] of clip_fdt.py:154: no transposed copy of the codebook is made (tcgen05 reads the
+ * staged 64 x 64 boxes as an MN-major operand). out[n, m] (+)= alpha * sum_k A[k,m] * B[n,k]; B [N,Kr] bf16. CTA-pair kernel
+ * only: ilfdt_gemm_nn_supported(M, N, Kr) != 0 (M = 256 or 512, Kr >= 1024, and N >= 1024 or a split reduction), else
+ * ILFDT_E_UNSUPPORTED_SHAPE -- transpose and call ilfdt_gemm_nt then. ws: ilfdt_gemm_nt_splitk_ws_bytes(M, N, Kr) bytes
+ * (may be NULL when that is 0). Same k order per output element as ilfdt_gemm_nt(_splitk): identical results. */
+int32_t ilfdt_gemm_nn_supported(int64_t M, int64_t N, int64_t Kr);
+int32_t ilfdt_gemm_nn(const void* A_bf16, const void* B_bf16, int64_t M, int64_t N, int64_t Kr, float alpha,
+                      int32_t accumulate, float* out, int64_t ldo, void* ws, int64_t ws_bytes, void* stream);
 /* out[N, M] (+)= alpha * B[Kr,N]^T . A[Kr,M] for bf16 operands stored with the REDUCTION index outermost (tcgen05
  * MN-major operands: no transposed copies). dsd[K,D] += w[b,K]^T . df[b,D] of the pooling backward
  * (clip_fdt.py:154): A = df, B = w, M = D, N = K, Kr = b. M, N multiples of 8. */

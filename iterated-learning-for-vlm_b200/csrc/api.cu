@@ -360,6 +360,30 @@ int32_t ilfdt_gemm_nt_splitk(const void* A_bf16, const void* B_bf16, int64_t M, 
   return launch_gemm_nt_bf16(A_bf16, B_bf16, M, N, Kr, alpha, nullptr, accumulate, out, ldo, ST(stream));
 }
 
+int32_t ilfdt_gemm_nn_supported(int64_t M, int64_t N, int64_t Kr) {
+  return gemm_wide2_enabled() && gemm_wide2_mn_supported(M, N, Kr, nullptr, 4) ? 1 : 0;
+}
+
+int32_t ilfdt_gemm_nn(const void* A_bf16, const void* B_bf16, int64_t M, int64_t N, int64_t Kr, float alpha, int32_t accumulate,
+                      float* out, int64_t ldo, void* ws, int64_t ws_bytes, void* stream) {
+  ARCH_GUARD();
+  ILFDT_REQUIRE(M >= 0 && N >= 0 && Kr >= 1 && ldo >= M, ILFDT_E_INVALID_ARG, "gemm_nn: bad shape");
+  ILFDT_REQUIRE(M == 0 || N == 0 || (A_bf16 && B_bf16 && out), ILFDT_E_INVALID_ARG, "gemm_nn: null pointer");
+  if (M == 0 || N == 0) return ILFDT_OK;
+  ILFDT_REQUIRE(gemm_wide2_enabled() && gemm_wide2_mn_supported(M, N, Kr, out, ldo), ILFDT_E_UNSUPPORTED_SHAPE,
+                "gemm_nn: M in {256, 512}, Kr >= 1024, 16-byte aligned out with ldo %% 4 == 0 and either N >= 1024 or a split "
+                "reduction required (got M=%lld N=%lld Kr=%lld); see ilfdt_gemm_nn_supported", (long long)M, (long long)N,
+                (long long)Kr);
+  ILFDT_REQUIRE((reinterpret_cast<uintptr_t>(A_bf16) & 15) == 0, ILFDT_E_INVALID_ARG, "gemm_nn: A must be 16-byte aligned");
+  const int64_t need = ilfdt_gemm_nt_splitk_ws_bytes(M, N, Kr);
+  float* slabs = nullptr;
+  if (need > 0 && gemm_wide2_split_supported(M, N, Kr, out, ldo)) {
+    ILFDT_REQUIRE(ws != nullptr && ws_bytes >= need, ILFDT_E_INVALID_ARG, "gemm_nn: workspace too small");
+    slabs = reinterpret_cast<float*>(ws);
+  }
+  return launch_gemm_wide2(A_bf16, B_bf16, M, N, Kr, alpha, accumulate, out, ldo, ST(stream), slabs, 1);
+}
+
 int32_t ilfdt_gemm_tn(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha, int32_t accumulate,
                       float* out, int64_t ldo, void* stream) {
   ARCH_GUARD();

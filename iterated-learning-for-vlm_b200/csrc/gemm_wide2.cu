@@ -43,6 +43,9 @@ struct W2Params {
   int ksplit, kb_per;
   float* slab;
   long long slab_stride;
+  // 1: A is given as [Kr, M] row-major (the reduction index outermost: the codebook sd [K, D] itself, no transposed copy);
+  // each CTA stages its 128 columns of a 64-k block as two 64 x 64 boxes read as an MN-major operand
+  int col_mn;
 };
 
 struct W2Bars {
@@ -91,9 +94,16 @@ gemm_wide2_kernel(const __grid_constant__ CUtensorMap tmLane, const __grid_const
           if (leader) mbar_expect_tx(&bars->full[stage], stage_tx);
           uint8_t* st = smem + stage * W2_STAGE;
           tma_load_2d_pair(st, &tmLane, &bars->full[stage], kb * 64, lane_row0, kEvictFirst);
-          for (int a = 0; a < p.nacc; ++a)   // this CTA's half of accumulator a's columns (rows of A)
-            tma_load_2d_pair(st + (1 + a) * W2_BOX, &tmCol, &bars->full[stage], kb * 64,
-                             a * 256 + (int)rank * (p.acc_n[a] >> 1), kEvictLast);
+          for (int a = 0; a < p.nacc; ++a) {  // this CTA's half of accumulator a's columns (rows of A)
+            if (p.col_mn) {
+              const int n0 = a * 256 + (int)rank * 128;
+              tma_load_2d_pair(st + (1 + a) * W2_BOX, &tmCol, &bars->full[stage], n0, kb * 64, kEvictLast);
+              tma_load_2d_pair(st + (1 + a) * W2_BOX + 8192, &tmCol, &bars->full[stage], n0 + 64, kb * 64, kEvictLast);
+            } else {
+              tma_load_2d_pair(st + (1 + a) * W2_BOX, &tmCol, &bars->full[stage], kb * 64,
+                               a * 256 + (int)rank * (p.acc_n[a] >> 1), kEvictLast);
+            }
+          }
           if (++stage == W2_STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -113,10 +123,13 @@ gemm_wide2_kernel(const __grid_constant__ CUtensorMap tmLane, const __grid_const
           const uint8_t* st = smem + stage * W2_STAGE;
           const uint64_t adesc = make_smem_desc_sw128(smem_u32(st));
           for (int a = 0; a < p.nacc; ++a) {
-            const uint64_t bdesc = make_smem_desc_sw128(smem_u32(st + (1 + a) * W2_BOX));
+            // K-major: 16 k = 32 bytes inside the swizzle atom; MN-major: 16 k-rows of 128 bytes, the second 64 columns 8 KB on
+            const uint64_t bdesc = p.col_mn ? make_smem_desc_sw128_mn(smem_u32(st + (1 + a) * W2_BOX), 8192)
+                                            : make_smem_desc_sw128(smem_u32(st + (1 + a) * W2_BOX));
+            const uint32_t bstep = p.col_mn ? 2048u : 32u;
 #pragma unroll
             for (int k4 = 0; k4 < 4; ++k4)
-              mma_f16_pair(tmem_base + a * 256, advance_desc_k(adesc, k4 * 32), advance_desc_k(bdesc, k4 * 32),
+              mma_f16_pair(tmem_base + a * 256, advance_desc_k(adesc, k4 * 32), advance_desc_k(bdesc, k4 * bstep),
                            p.idesc[a], ((kb - kb0) | k4) != 0 ? 1u : 0u);
           }
           mma_commit_pair(&bars->empty[stage]);
@@ -229,9 +242,16 @@ int64_t gemm_wide2_ws_floats(int64_t M, int64_t N, int64_t Kr) {
 }
 
 // out[n, m] (+)= alpha * sum_k B[n,k] A[m,k]; A [M, Kr], B [N, Kr] bf16 row-major. ws != nullptr: split reduction.
+// A given as [Kr, M] (reduction outermost): both halves of every accumulator must be full 128-column boxes
+bool gemm_wide2_mn_supported(int64_t M, int64_t N, int64_t Kr, const float* out, int64_t ldo) {
+  return (M == 256 || M == 512) && N >= 1 && Kr >= 1024 && ldo % 4 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
+         (gemm_wide2_supported(M, N, Kr, out, ldo) || w2_ksplit(M, N, Kr) > 1);
+}
+
 int32_t launch_gemm_wide2(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha, int accumulate,
-                          float* out, int64_t ldo, cudaStream_t st, float* ws) {
+                          float* out, int64_t ldo, cudaStream_t st, float* ws, int col_mn) {
   W2Params p{};
+  p.col_mn = col_mn;
   p.ksplit = ws != nullptr ? w2_ksplit(M, N, Kr) : 1;
   p.kb_per = (int)cdiv(cdiv(Kr, 64), p.ksplit);
   p.ksplit = (int)cdiv(cdiv(Kr, 64), p.kb_per);
@@ -244,7 +264,7 @@ int32_t launch_gemm_wide2(const void* A, const void* B, int64_t M, int64_t N, in
   p.nacc = (int)cdiv(M, 256);
   for (int a = 0; a < p.nacc; ++a) {
     p.acc_n[a] = (int)round_up(std::min<int64_t>(256, M - a * 256), 32);   // halves stay multiples of 16 rows
-    p.idesc[a] = make_idesc_bf16(256, p.acc_n[a]);
+    p.idesc[a] = make_idesc_bf16(256, p.acc_n[a], 0, col_mn);
   }
   p.alpha = alpha;
   p.accumulate = accumulate;
@@ -253,7 +273,9 @@ int32_t launch_gemm_wide2(const void* A, const void* B, int64_t M, int64_t N, in
   CUtensorMap tmLane, tmCol;
   int32_t rc = make_tmap_bf16(&tmLane, B, N, Kr, Kr, 128);
   if (rc != ILFDT_OK) return rc;
-  if ((rc = make_tmap_bf16(&tmCol, A, M, Kr, Kr, 128)) != ILFDT_OK) return rc;
+  if (col_mn) rc = make_tmap_bf16(&tmCol, A, Kr, M, M, 64);    // [Kr, M] row-major, box = 64 k-rows x 64 columns
+  else rc = make_tmap_bf16(&tmCol, A, M, Kr, Kr, 128);
+  if (rc != ILFDT_OK) return rc;
   static thread_local int configured_dev = -1;
   static thread_local int max_clusters = 0;
   int dev = 0;

@@ -109,7 +109,8 @@ int32_t launch_nce_bwd_bf16(const void* x_img, const void* x_txt, const void* g_
 bool gemm_wide2_enabled();
 bool gemm_wide2_supported(int64_t M, int64_t N, int64_t Kr, const float* out, int64_t ldo);
 int32_t launch_gemm_wide2(const void* A, const void* B, int64_t M, int64_t N, int64_t Kr, float alpha, int accumulate,
-                          float* out, int64_t ldo, cudaStream_t st, float* ws = nullptr);
+                          float* out, int64_t ldo, cudaStream_t st, float* ws = nullptr, int col_mn = 0);
+bool gemm_wide2_mn_supported(int64_t M, int64_t N, int64_t Kr, const float* out, int64_t ldo);
 bool gemm_wide2_split_supported(int64_t M, int64_t N, int64_t Kr, const float* out, int64_t ldo);
 int64_t gemm_wide2_ws_floats(int64_t M, int64_t N, int64_t Kr);
 int32_t launch_nce_topk_bf16(const void* x, const void* g, int64_t b, int64_t B, int64_t D, const float* scale,

@@ -42,6 +42,8 @@ SIGNATURES = {
     "ilfdt_gemm_nt": (_i32, [_p, _p, _i32, _i64, _i64, _i64, _f, _i32, _p, _i64, _p]),
     "ilfdt_gemm_nt_splitk_ws_bytes": (_i64, [_i64, _i64, _i64]),
     "ilfdt_gemm_nt_splitk": (_i32, [_p, _p, _i64, _i64, _i64, _f, _i32, _p, _i64, _p, _i64, _p]),
+    "ilfdt_gemm_nn_supported": (_i32, [_i64, _i64, _i64]),
+    "ilfdt_gemm_nn": (_i32, [_p, _p, _i64, _i64, _i64, _f, _i32, _p, _i64, _p, _i64, _p]),
     "ilfdt_gemm_tn": (_i32, [_p, _p, _i64, _i64, _i64, _f, _i32, _p, _i64, _p]),
     "ilfdt_linear_bf16": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _i64, _p]),
     "ilfdt_gemm_tn_splitk_ws_bytes": (_i64, [_i64, _i64, _i64]),

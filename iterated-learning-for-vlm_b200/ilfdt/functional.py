@@ -98,10 +98,29 @@ def _sd_bf16(sd):
         if hit is not None:
             return hit
     sd_b = ops.cast_bf16(sd.detach())
-    sd_bt = ops.transpose_bf16(sd_b)
+    sd_bt = _LazyTranspose(sd_b)
     if _sd_scope is not None:
         _sd_scope[key] = (sd_b, sd_bt)
     return sd_b, sd_bt
+
+
+class _LazyTranspose:
+    """The [D, K] copy of the bf16 codebook, made only if a pooling shape needs it (ilfdt_gemm_nn reads sd [K, D] itself)."""
+
+    def __init__(self, src):
+        self.src, self.t = src, None
+
+    def get(self):
+        if self.t is None:
+            self.t = ops.transpose_bf16(self.src)
+        return self.t
+
+
+def _pool_codes(w_b, sd_k, sd_kt):
+    """f[b,D] = w[b,K] . sd[K,D]  (clip_fdt.py:154) on the tensor cores."""
+    if ops.gemm_nn_supported(sd_k.shape[1], w_b.shape[0], sd_k.shape[0]):
+        return ops.gemm_nn(sd_k, w_b)
+    return ops.gemm_nt(sd_kt.get(), w_b)
 
 
 _warned = set()
@@ -197,7 +216,7 @@ class GroundingFunction(torch.autograd.Function):
         w, w_b, _tau, nnz = ops.sparsemax_fwd(pooled, want_bf16=(mode == "bf16"), want_f32=not lean)
         del pooled
         if mode == "bf16":
-            f = ops.gemm_nt(sd_kt, w_b)                     # f[b,D] = w[b,K] . sdT[D,K]^T  (clip_fdt.py:154)
+            f = _pool_codes(w_b, sd_k, sd_kt)               # f[b,D] = w[b,K] . sd[K,D]  (clip_fdt.py:154)
         else:
             f = ops.gemm_f32(w, sd_c)
         ctx.mode, ctx.temperature = mode, float(temperature)

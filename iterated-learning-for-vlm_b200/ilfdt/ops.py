@@ -20,7 +20,7 @@ LAUNCHES = 0          # kernels launched through this module since it was last z
 PROFILE_ON = False    # when True every C call is bracketed by CUDA events on the launching stream
 PROFILE = {}          # op name -> [(start_event, end_event), ...]
 _KERNELS_PER_CALL = {"ilfdt_cast_bf16": 1, "ilfdt_split3_bf16": 1, "ilfdt_cast_bf16_rows": 1, "ilfdt_mask_rows_bf16": 1, "ilfdt_transpose_bf16": 1, "ilfdt_ground_fwd": 1, "ilfdt_ground_fwd_text": 5, "ilfdt_text_compact": 3, "ilfdt_text_compact_x3": 3, "ilfdt_sparsemax_fwd": 1,
-                     "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_nt_splitk": 2, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2, "ilfdt_ground_bwd_w16": 2,   # + 2 regime launches that return at once
+                     "ilfdt_sparsemax_bwd": 1, "ilfdt_gemm_nt": 1, "ilfdt_gemm_nt_splitk": 2, "ilfdt_gemm_nn": 2, "ilfdt_gemm_f32_strided": 1, "ilfdt_ground_bwd": 2, "ilfdt_ground_bwd_w16": 2,   # + 2 regime launches that return at once
                      "ilfdt_l2norm_fwd": 1, "ilfdt_l2norm_bwd": 1, "ilfdt_logits": 1, "ilfdt_nce_fwd": 5, "ilfdt_nce_lse": 2, "ilfdt_nce_loss": 1,
                      "ilfdt_nce_bwd": 4, "ilfdt_nce_bwd_gathered": 2, "ilfdt_ce_rows_fwd": 1, "ilfdt_ce_rows_bwd": 1, "ilfdt_topk_hits": 1,
                      "ilfdt_randn_fill": 1, "ilfdt_copy": 0,
@@ -215,6 +215,13 @@ def ground_fwd_text(q_compact, sd, plan, n_tok, temperature, sqrt_d=None):
     arg = torch.empty(b, K, dtype=torch.int16, device=sd.device)
     _call("ilfdt_ground_fwd_text", _ptr(q_compact), _ptr(sd), _ptr(plan.buf), b, n_tok, K, D,
           float(math.sqrt(D) if sqrt_d is None else sqrt_d), float(temperature), _ptr(pooled), _ptr(arg), _stream())
+    lib = _lib.load()
+    global LAUNCHES
+    if lib.ilfdt_tune_get(_lib.TUNE["ground_2cta"]) and b <= lib.ilfdt_tune_get(_lib.TUNE["text_merged_max_b"]) \
+            and D <= 512 and n_tok in (16, 32, 48, 64, 77):
+        LAUNCHES -= 4          # small batches: the tiles of all length buckets in ONE launch (ground2_text_kernel)
+    else:
+        LAUNCHES += -5 + (n_tok + 15) // 16
     return pooled, arg
 
 
@@ -258,6 +265,31 @@ def gemm_nt(A, B, alpha=1.0, out=None, accumulate=False):
             return out
     _call("ilfdt_gemm_nt", _ptr(A), _ptr(B), _DT[A.dtype], M, N, Kr, float(alpha), int(accumulate),
                                     _ptr(out), out.shape[1], _stream())
+    return out
+
+
+def gemm_nn_supported(M, N, Kr):
+    return _lib.load().ilfdt_gemm_nn_supported(int(M), int(N), int(Kr)) != 0
+
+
+def gemm_nn(A, B, alpha=1.0, out=None, accumulate=False):
+    """out[N, M] (+)= alpha * B[N,Kr] . A[Kr,M]   (bf16; A with the reduction index OUTERMOST -- the codebook sd [K, D] as it
+    is, no transposed copy: the pooling of clip_fdt.py:154). Shapes: gemm_nn_supported(M, N, Kr)."""
+    _req(A, torch.bfloat16, "A"); _req(B, torch.bfloat16, "B")
+    Kr, M = A.shape
+    N = B.shape[0]
+    assert B.shape[1] == Kr
+    if out is None:
+        assert not accumulate
+        out = torch.empty(N, M, dtype=torch.float32, device=A.device)
+    _req(out, torch.float32, "out")
+    nws = _lib.load().ilfdt_gemm_nt_splitk_ws_bytes(M, N, Kr)
+    ws = torch.empty(nws, dtype=torch.uint8, device=A.device) if nws > 0 else None
+    _call("ilfdt_gemm_nn", _ptr(A), _ptr(B), M, N, Kr, float(alpha), int(accumulate), _ptr(out), out.shape[1], _ptr(ws), nws,
+          _stream())
+    if nws == 0:
+        global LAUNCHES
+        LAUNCHES -= 1          # no slab reduction behind the unsplit launch
     return out
 
 

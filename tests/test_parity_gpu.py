@@ -81,6 +81,29 @@ def test_gemm_nt_tcgen05(ops, M, N, K):
     assert_close(out2, 3.0 * ref, 2e-5, "gemm_nt bf16 accumulate")
 
 
+@pytest.mark.parametrize("M,N,K", [(512, 256, 16384), (512, 64, 4096), (512, 2048, 4096), (256, 1500, 2048), (256, 300, 2048),
+                                   (512, 7, 1024), (512, 1100, 1096), (256, 4096, 16384)])
+def test_gemm_nn_reads_the_codebook_untransposed(ops, M, N, K):
+    """ilfdt_gemm_nn: the pooling f[b,D] = w[b,K] . sd[K,D] (clip_fdt.py:154) with sd given as it is ([K, D], reduction index
+    outermost; staged as an MN-major tcgen05 operand): the fp64 product of the bf16 operands, the SAME bits as ilfdt_gemm_nt
+    on a transposed copy (same MMAs in the same k order, split or not), accumulate honoured; other shapes are refused."""
+    g = torch.Generator().manual_seed(7 * M + N + K)
+    A = bf16_round(torch.randn(K, M, generator=g))          # sd [K, D]
+    B = bf16_round(torch.randn(N, K, generator=g))          # w [b, K]
+    ref = B.double() @ A.double()
+    assert ops.gemm_nn_supported(M, N, K)
+    Ad, Bd = A.to(_dev()).to(torch.bfloat16), B.to(_dev()).to(torch.bfloat16)
+    out = ops.gemm_nn(Ad, Bd, alpha=2.0)
+    assert_close(out, 2.0 * ref, 2e-5, "gemm_nn bf16")
+    if K % 8 == 0:
+        assert torch.equal(out, ops.gemm_nt(ops.transpose_bf16(Ad), Bd, alpha=2.0))
+    out2 = ops.gemm_nn(Ad, Bd, out=out.clone(), accumulate=True)
+    assert_close(out2, 3.0 * ref, 2e-5, "gemm_nn bf16 accumulate")
+    assert not ops.gemm_nn_supported(128, N, K) and not ops.gemm_nn_supported(M, N, 512)
+    with pytest.raises(RuntimeError):
+        ops.gemm_nn(Ad[:, :128].contiguous(), Bd)
+
+
 @pytest.mark.parametrize("M,N,K", [(512, 256, 64), (512, 16384, 300), (64, 200, 1000), (256, 384, 37), (8, 8, 5)])
 def test_gemm_tn_tcgen05(ops, M, N, K):
     """MN-major tensor-core operands: out[N,M] = B[K,N]^T . A[K,M] from row-major A, B (reduction index outermost)."""
