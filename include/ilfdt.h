@@ -72,7 +72,7 @@ enum {
                                     3-term bf16 split (ilfdt_split3_bf16; fp32-grade: 7e-7 of fp64), 0 = SIMT FFMA kernels */
   ILFDT_TUNE_DQ_DEEP = 10,       /* ilfdt_ground_bwd* (bf16 rows): 1 (default) = launches with at most 2 x SM count samples keep 8
                                     codebook rows in flight per warp instead of 4 (2 CTAs / SM); 0 = always 4. Same order */
-  ILFDT_TUNE_TEXT_MERGED_MAX_B = 11, /* ilfdt_ground_fwd_text: batches of at most this many samples (default 4096) run the tiles
+  ILFDT_TUNE_TEXT_MERGED_MAX_B = 11, /* ilfdt_ground_fwd_text: batches of at most this many samples (default 1024) run the tiles
                                     of ALL length buckets in one launch, larger ones one launch per bucket; 0 = never. Same bits */
   ILFDT_TUNE_COUNT_ = 12
 };

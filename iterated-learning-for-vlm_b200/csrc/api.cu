@@ -7,7 +7,7 @@
 namespace ilfdt {
 
 // tuning knobs: explicit API state instead of environment variables read into statics (defaults = the tuned values)
-static std::atomic<int64_t> g_tune[ILFDT_TUNE_COUNT_] = {{1024}, {32}, {1}, {1}, {1}, {1}, {128}, {1}, {0}, {1}, {1}, {4096}};
+static std::atomic<int64_t> g_tune[ILFDT_TUNE_COUNT_] = {{1024}, {32}, {1}, {1}, {1}, {1}, {128}, {1}, {0}, {1}, {1}, {1024}};
 int64_t tune_get(int key) { return (key >= 0 && key < ILFDT_TUNE_COUNT_) ? g_tune[key].load(std::memory_order_relaxed) : 0; }
 
 int sm_count() {
