@@ -21,8 +21,8 @@ print("FFMA2 = packed fp32x2 FMA, REDG = red.global (x4 = 16-byte vector form). 
 print("%-72s" % "kernel" + "".join("%9s" % c for c, _ in cols))
 rows = []
 for n, d, body in zip(names, dem or names, bodies):
-    short = re.sub(r"^void\s+", "", d)
-    short = re.sub(r"\(.*$", "", short).replace("ilfdt::", "").replace("(int)", "").replace("(bool)", "")
+    short = re.sub(r"^void\s+", "", d).replace("ilfdt::", "").replace("(int)", "").replace("(bool)", "")
+    short = re.sub(r"\(.*$", "", short)
     counts = [len(re.findall(rx, body)) for _, rx in cols]
     rows.append((short, counts))
 rows.sort(key=lambda r: (-r[1][0], -r[1][7], r[0]))
