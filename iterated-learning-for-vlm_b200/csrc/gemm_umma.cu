@@ -774,6 +774,17 @@ int32_t launch_nce_lse_bf16(const void* x, const void* g, int64_t b, int64_t B, 
   ILFDT_REQUIRE(ws != nullptr && ws_bytes >= nce_fwd_bf16_ws_bytes(b, B) / 2, ILFDT_E_INVALID_ARG,
                 "nce_lse(bf16): workspace too small");
   const int64_t max_chunks = 2 * cdiv(B, 256);
+  if (tune_get(ILFDT_TUNE_NCE_2CTA) != 0 && ground2_enabled()) {
+    // CTA-pair kernel (ground_umma2.cu): 256 logits rows resident per pair, each CTA streams half of every gathered tile
+    float* part_m = reinterpret_cast<float*>(ws);
+    float* part_s = part_m + max_chunks * b;
+    int nchunk = 1;
+    int32_t rc2 = launch_nce_lse2(x, g, b, B, D, scale, label_offset, part_m, part_s, diag, &nchunk, st);
+    if (rc2 != ILFDT_OK) return rc2;
+    lse_combine_kernel<<<(unsigned)cdiv(b, 256), 256, 0, st>>>(part_m, part_s, 2 * nchunk, b, lse);
+    ILFDT_LAUNCH_OK();
+    return ILFDT_OK;
+  }
   UmmaParams p{};
   p.block_n = (int)std::min<int64_t>(256, round_up(B, 16));
   p.n_step = p.block_n;

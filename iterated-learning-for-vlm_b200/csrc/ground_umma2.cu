@@ -45,14 +45,30 @@ struct G2Params {
   const int* dyn;          // {samples, first row, first slot, rows per sample} (text buckets) or nullptr
   const int* sample_map;
   uint32_t idesc;
+  // EPI2 == G2_EPI_LSE (InfoNCE forward, a8 + a10): lanes = local logits rows, columns = gathered rows; per row an online
+  // base-2 log-sum-exp over the item's columns and the label logit; one partial per (chunk, epilogue group)
+  const float* scale_dev;
+  long long label_offset;
+  float* part_m;
+  float* part_s;
+  float* diag;
+  int n_rows;              // gathered rows (B)
 };
+
+enum { G2_EPI_POOLMAX = 0, G2_EPI_LSE = 1 };
+
+__device__ __forceinline__ float g2_ex2(float x) {   // 2^x for x <= 0 (or -inf): results in [0, 1], tiny ones flushed to 0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 struct G2Bars {
   uint64_t full[G2_STAGES], empty[G2_STAGES], tmem_full[2], tmem_empty[2], a_full, a_empty;
   uint32_t tmem_ptr;
 };
 
-template <int NTOK>
+template <int NTOK, int EPI2 = G2_EPI_POOLMAX>
 __global__ void __launch_bounds__(G2_THREADS, 1)
 ground2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const G2Params p) {
   extern __shared__ uint8_t g2_smem_raw[];
@@ -159,18 +175,69 @@ ground2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     for (int item = cluster_id; item < num_items; item += num_clusters) {
       const int m_pair = item % p.num_m_pairs, chunk = item / p.num_m_pairs;
       const int n_begin = chunk * tiles_per_chunk, n_end = min(num_n_tiles, n_begin + tiles_per_chunk);
-      const int row = (2 * m_pair + (int)rank) * 128 + quad * 32 + lane;  // code owned by this thread
+      const int row = (2 * m_pair + (int)rank) * 128 + quad * 32 + lane;  // code (LSE: logits row) owned by this thread
       const bool row_ok = row < p.m_rows;
+      float run_m = -INFINITY, run_s = 0.f;   // G2_EPI_LSE: running maximum and sum of the item's columns, base-2 domain
       for (int n = n_begin; n < n_end; ++n, ++tile_seq) {
         const uint32_t acc = tile_seq & 1, acc_phase = (tile_seq >> 1) & 1;
         if (acc != group) continue;
         mbar_wait(&bars->tmem_full[acc], acc_phase);
         fence_after_sync();
-        poolmax_static<NTOK>(tmem_base + lane_addr + acc * 256, n * p.spt, dyn_samples, row, row_ok, p.m_rows,
-                             p.pool_scale, p.pooled, p.arg, p.sample_map, dyn_slot0);
+        if (EPI2 == G2_EPI_POOLMAX) {
+          poolmax_static<NTOK>(tmem_base + lane_addr + acc * 256, n * p.spt, dyn_samples, row, row_ok, p.m_rows,
+                               p.pool_scale, p.pooled, p.arg, p.sample_map, dyn_slot0);
+        } else {
+          const float scale = __ldg(p.scale_dev);
+          const float scale_log2 = scale * 1.4426950408889634f;
+          const uint32_t taddr = tmem_base + lane_addr + acc * 256;
+          const int n0 = n * p.n_step;
+          const int ncols = min(p.n_step, p.n_rows - n0);
+          const long long label = p.label_offset + row;
+          const long long wl0 = p.label_offset + (2 * m_pair + (int)rank) * 128 + quad * 32;  // labels of this warp: [wl0, wl0 + 32)
+          for (int c0 = 0; c0 < ncols; c0 += 32) {
+            uint32_t v[32];
+            tmem_ld32(taddr + c0, v);
+            tmem_ld_wait();
+            // lean form (the kernel is epilogue-bound otherwise: ~8 issued instructions per logit with exp2f on scaled,
+            // masked copies): the chunk maximum is taken on the raw accumulators (scale > 0 keeps the order), and each
+            // term is one FFMA (scale and shift folded), one MUFU.EX2, one FADD
+            float cm = __uint_as_float(v[0]);
+            if (c0 + 32 <= ncols) {
+#pragma unroll
+              for (int j = 1; j < 32; ++j) cm = fmaxf(cm, __uint_as_float(v[j]));
+            } else {
+#pragma unroll
+              for (int j = 1; j < 32; ++j)
+                if (c0 + j < ncols) cm = fmaxf(cm, __uint_as_float(v[j]));
+            }
+            const float nm = fmaxf(run_m, cm * scale_log2);
+            const float shift = -nm;
+            float sum = 0.f;
+            if (c0 + 32 <= ncols) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) sum += g2_ex2(fmaf(__uint_as_float(v[j]), scale_log2, shift));
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (c0 + j < ncols) sum += g2_ex2(fmaf(__uint_as_float(v[j]), scale_log2, shift));
+            }
+            run_s = run_s * g2_ex2(run_m - nm) + sum;
+            run_m = nm;
+            const long long cbeg = (long long)n0 + c0;
+            if (wl0 < cbeg + 32 && wl0 + 32 > cbeg) {  // warp-uniform: some label falls in this chunk
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (row_ok && cbeg + j == label && c0 + j < ncols) p.diag[row] = __uint_as_float(v[j]) * scale;
+            }
+          }
+        }
         fence_before_sync();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(&bars->tmem_empty[acc], 0);
+      }
+      if (EPI2 == G2_EPI_LSE && row_ok) {  // one partial per (chunk, epilogue group); a group without a tile leaves (-inf, 0)
+        p.part_m[(int64_t)(chunk * 2 + (int)group) * p.m_rows + row] = run_m;
+        p.part_s[(int64_t)(chunk * 2 + (int)group) * p.m_rows + row] = run_s;
       }
     }
   }
@@ -387,7 +454,7 @@ static void g2_plan(int num_m, int num_n_tiles, int workers, int& nchunk, int& t
   nchunk = (int)cdiv(num_n_tiles, tiles_per_chunk);
 }
 
-template <int NTOK>
+template <int NTOK, int EPI2 = G2_EPI_POOLMAX>
 static int32_t launch_g2_t(const CUtensorMap& tmA, const CUtensorMap& tmB, G2Params& p, int est_tiles, cudaStream_t st) {
   static thread_local int configured_dev = -1;
   static thread_local int max_clusters = 0;
@@ -405,10 +472,10 @@ static int32_t launch_g2_t(const CUtensorMap& tmA, const CUtensorMap& tmB, G2Par
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   if (configured_dev != dev) {
-    ILFDT_CUDA_OK(cudaFuncSetAttribute(ground2_kernel<NTOK>, cudaFuncAttributeMaxDynamicSharedMemorySize, G2_SMEM_BYTES));
+    ILFDT_CUDA_OK(cudaFuncSetAttribute(ground2_kernel<NTOK, EPI2>, cudaFuncAttributeMaxDynamicSharedMemorySize, G2_SMEM_BYTES));
     cfg.gridDim = dim3(2 * (sm_count() / 2));
     int n = 0;
-    ILFDT_CUDA_OK(cudaOccupancyMaxActiveClusters(&n, ground2_kernel<NTOK>, &cfg));
+    ILFDT_CUDA_OK(cudaOccupancyMaxActiveClusters(&n, ground2_kernel<NTOK, EPI2>, &cfg));
     ILFDT_REQUIRE(n >= 1, ILFDT_E_CUDA, "ground2: no CTA pair can be resident");
     max_clusters = std::min(n, sm_count() / 2);
     configured_dev = dev;
@@ -417,8 +484,38 @@ static int32_t launch_g2_t(const CUtensorMap& tmA, const CUtensorMap& tmB, G2Par
   if (p.dyn == nullptr) p.tiles_per_chunk = (int)cdiv(p.num_n_tiles, p.nchunk);
   const int items = p.num_m_pairs * p.nchunk;
   cfg.gridDim = dim3(2 * std::min(items, max_clusters));
-  ILFDT_CUDA_OK(cudaLaunchKernelEx(&cfg, ground2_kernel<NTOK>, tmA, tmB, p));
+  ILFDT_CUDA_OK(cudaLaunchKernelEx(&cfg, ground2_kernel<NTOK, EPI2>, tmA, tmB, p));
   return ILFDT_OK;
+}
+
+// InfoNCE forward on the pair kernel: per local row r the partial (max, sum) of 2^(scale log2(e) x[r,:] . g[c,:]) over each
+// chunk of gathered rows c, and the label logit diag[r] = scale x[r,:] . g[label_offset + r,:]. Partials: [2 * nchunk, b]
+// (chunk-major, two epilogue groups per chunk) at part_m / part_s; nchunk is returned for the combine kernel.
+int32_t launch_nce_lse2(const void* x, const void* g, int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset,
+                        float* part_m, float* part_s, float* diag, int* nchunk_out, cudaStream_t st) {
+  G2Params p{};
+  p.block_n = (int)std::min<int64_t>(256, round_up(B, 16));
+  p.n_step = p.block_n;
+  p.spt = 1;
+  p.nkb = (int)cdiv(D, 64);
+  p.m_rows = (int)b;
+  p.num_m_pairs = (int)cdiv(b, 256);
+  p.n_rows = (int)B;
+  p.num_n_tiles = (int)cdiv(B, p.n_step);
+  p.n_samples = p.num_n_tiles;
+  p.scale_dev = scale;
+  p.label_offset = label_offset;
+  p.part_m = part_m;
+  p.part_s = part_s;
+  p.diag = diag;
+  p.idesc = make_idesc_bf16(256, p.block_n);
+  CUtensorMap tmA, tmB;
+  int32_t rc = make_tmap_bf16(&tmA, x, b, D, D, 128);
+  if (rc != ILFDT_OK) return rc;
+  if ((rc = make_tmap_bf16(&tmB, g, B, D, D, p.block_n / 2)) != ILFDT_OK) return rc;
+  rc = launch_g2_t<16, G2_EPI_LSE>(tmA, tmB, p, p.num_n_tiles, st);
+  *nchunk_out = p.nchunk;
+  return rc;
 }
 
 bool ground2_enabled() {

@@ -73,6 +73,8 @@ bool ground2_supported(int64_t n_tok, int64_t D);
 int32_t launch_ground2(const void* q, const void* sd, int64_t q_rows, int64_t n_samples, int64_t n_tok, int64_t K, int64_t D,
                        float pool_scale, float* pooled, int16_t* arg, const int* dyn, const int* sample_map,
                        int64_t est_samples, cudaStream_t st);
+int32_t launch_nce_lse2(const void* x, const void* g, int64_t b, int64_t B, int64_t D, const float* scale, int64_t label_offset,
+                        float* part_m, float* part_s, float* diag, int* nchunk_out, cudaStream_t st);
 bool ground2_text_merged_supported(int64_t n_tok, int64_t D);
 int32_t launch_ground2_text_merged(const void* q, const void* sd, int64_t q_rows, int64_t b, int64_t n_tok, int64_t K, int64_t D,
                                    float pool_scale, float* pooled, int16_t* arg, const int* plan, const int* sample_map,
