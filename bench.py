@@ -814,15 +814,37 @@ def run_ours(args):
     if kind == "fdt" and world == 1 and not args.no_secondary and not c["reset"]:
         with torch.no_grad():
             qi2, qt2 = q_img * args.trained_scale, q_txt * args.trained_scale
+        sec_step = lambda: model_step(qi2, qt2, mask)
+        sec_graph = None
+        if use_graph:                # replayed like the main case (at small batches eager issue would time Python)
+            try:
+                from ilfdt.graphs import GraphedStep
+                sec_graph = GraphedStep(model_step, (qi2, qt2, mask), warmup=1)
+                sec_step = sec_graph
+            except Exception:  # noqa: BLE001 -- measure eagerly
+                sec_graph = None
         for _ in range(2):
-            model_step(qi2, qt2, mask)
+            sec_step()
         sync()
-        e0.record()
-        for _ in range(args.steps):
-            model_step(qi2, qt2, mask)
-        e1.record()
-        sync()
-        sms = e0.elapsed_time(e1) / args.steps
+        if flush is None:
+            e0.record()
+            for _ in range(args.steps):
+                sec_step()
+            e1.record()
+            sync()
+            sms = e0.elapsed_time(e1) / args.steps
+        else:
+            sms = 0.0
+            for _ in range(args.steps):
+                flush.zero_()
+                e0.record()
+                sec_step()
+                e1.record()
+                sync()
+                sms += e0.elapsed_time(e1) / args.steps
+        if sec_graph is not None:
+            sec_graph.release()
+            del sec_graph
         ops.PROFILE.clear()
         ops.PROFILE_ON = True
         for _ in range(args.steps):
