@@ -463,6 +463,37 @@ def test_ground_fwd_text_buckets_equal_full_width(ops, b, n_tok, K, D, qdtype, m
         assert torch.equal(q_c[r0:r0 + n], q_full[s_, :n])
 
 
+@pytest.mark.parametrize("b,n_tok,K,D,lens_kind", [(1, 77, 128, 512, "rand"), (5, 16, 256, 512, "rand"), (300, 32, 768, 256, "rand"),
+                                                   (130, 77, 1024, 512, "same40"), (70, 77, 512, 512, "full"), (33, 77, 256, 512, "one"),
+                                                   (257, 48, 384, 128, "rand")])
+def test_text_one_launch_edge_shapes(ops, b, n_tok, K, D, lens_kind):
+    """ground2_text_kernel (all length buckets in one launch) against one launch per bucket: identical bits when a bucket is
+    empty, when every sample sits in one bucket, with a single sample, with fewer work units than CTA pairs, with a ragged last
+    code tile, and for every token count whose buckets the kernel takes (16 / 32 / 48 / 64 / 77)."""
+    g = torch.Generator().manual_seed(11 * b + n_tok + K)
+    q = torch.randn(b, n_tok, D, generator=g)
+    sd = torch.randn(K, D, generator=g)
+    if lens_kind == "rand":
+        lens = torch.randint(1, n_tok + 1, (b,), generator=g)
+    elif lens_kind == "same40":
+        lens = torch.full((b,), 40)
+    elif lens_kind == "full":
+        lens = torch.full((b,), n_tok)
+    else:
+        lens = torch.full((b,), 1)
+    dev = _dev()
+    mask = _mask(b, n_tok, lens.tolist()).to(dev)
+    sd_k = ops.cast_bf16(sd.to(dev))
+    q_c, plan = ops.text_compact(q.to(dev), mask)
+    with ops.tune(text_merged_max_b=0):
+        pooled_b, arg_b = ops.ground_fwd_text(q_c, sd_k, plan, n_tok, 30.0)
+    with ops.tune(text_merged_max_b=1 << 20):
+        pooled_m, arg_m = ops.ground_fwd_text(q_c, sd_k, plan, n_tok, 30.0)
+    assert torch.equal(pooled_b, pooled_m) and torch.equal(arg_b, arg_m)
+    pooled_f, arg_f = ops.ground_fwd(ops.cast_bf16_rows(q.to(dev), mask), sd_k, None, 30.0, "max")
+    assert torch.equal(pooled_f, pooled_m) and torch.equal(arg_f, arg_m)
+
+
 QM_VARIANTS = [("smax", "sparsemax", "max"), ("smaxT", "sparsemax", "max"), ("softsum", "softmax", "sum"),
                ("sigmean", "sigmoid", "mean"), ("softmax_max", "softmax", "max"), ("smax_mean", "sparsemax", "mean")]
 
