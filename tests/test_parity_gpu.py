@@ -1569,6 +1569,25 @@ def test_pair_kernels_bit_deterministic_under_repetition(ops):
             ref = o.clone()
         else:
             assert torch.equal(o, ref), "gemm_wide2_kernel is not deterministic"
+    # the one-launch text kernel, the pooling on the untransposed codebook and the InfoNCE forward on the pair kernel
+    qt = torch.randn(600, 77, D, device=dev, generator=g)
+    lens = torch.randint(1, 78, (600,), device=dev, generator=g)
+    mask = torch.zeros(600, 77, device=dev)
+    mask[torch.arange(77, device=dev).view(1, -1) >= lens.view(-1, 1)] = float("-inf")
+    q_c, plan = ops.text_compact(qt, mask)
+    wb = ops.cast_bf16(torch.rand(300, K, device=dev, generator=g))
+    ref = None
+    for _ in range(40):
+        with ops.tune(text_merged_max_b=1 << 20):
+            pooled, arg = ops.ground_fwd_text(q_c, sd, plan, 77, 1000.0)
+        f = ops.gemm_nn(sd, wb)
+        lse, diag = ops.nce_lse(xb, xb, sc, 0)
+        cur = (pooled, arg, f, lse, diag)
+        if ref is None:
+            ref = tuple(t.clone() for t in cur)
+        else:
+            for name_, a, r in zip(("ground2_text_kernel pooled", "ground2_text_kernel arg", "gemm_nn", "nce_lse", "nce_lse diag"), cur, ref):
+                assert torch.equal(a, r), name_ + " is not deterministic"
 
 
 @pytest.mark.parametrize("name,att", [("smax", "sparsemax"), ("soft", "softmax")])
