@@ -1,4 +1,4 @@
-"""python tools/time_gbwd.py [b]  -- CUDA-event timing of ilfdt_ground_bwd_w16 (dq + dsd kernels) at the headline statistics
+"""python tools/time_gbwd.py [b] [split]  -- CUDA-event timing of ilfdt_ground_bwd_w16 (dq + dsd kernels) at the headline statistics
 for the shapes of the codebook-gradient kernel (ILFDT_TUNE_DSD_PIPE) and the dq kernel variants; image and text."""
 import json, os, sys
 import torch
@@ -33,6 +33,8 @@ for name, n_tok, masked in (("image", 49, False), ("text", 77, True)):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     res = {}
     variants = [dict(dsd_pipe=p) for p in (0, 1, 2, 3)] + [dict(dq_pipe=p) for p in (1, 2)]
+    if "split" in sys.argv:      # python tools/time_gbwd.py 4096 split: samples per range of the codebook-gradient sweep
+        variants = [dict(dsd_split_rows=r) for r in (512, 1024, 2048, 4096, 0)]
     for tune in variants:
         try:
             with ops.tune(**tune):
